@@ -1,0 +1,226 @@
+"""Device-resident batched MPE: the mirror of `MPEEnv(args)` (onpolicy/envs/mpe/MPE_env.py:5-31) and of
+`SubprocVecEnv`/`DummyVecEnv` (onpolicy/envs/env_wrappers.py:235-290,661-689) in one object.
+
+The reference builds one `MultiAgentEnv` per OS process and fans a step out over pipes; here all envs
+of the shard live in HBM (float64 structure-of-arrays, see include/mappo_b200.h) and `step` is ONE kernel
+launch over envs x agents with auto-reset inside.  Spaces follow environment.py:54-100."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ... import _lib
+from ..spaces import Box, Discrete, MultiDiscrete, head_sizes
+
+SCENARIOS = {"simple_spread": 0, "simple_speaker_listener": 1, "simple_reference": 2}
+
+
+class _Infos:
+    """Lazy `infos`: infos[n][m]['individual_reward'] like the reference (environment.py:135),
+    materialised from a device tensor only when indexed (it is only read at log time,
+    runner/shared/mpe_runner.py:62-70)."""
+
+    def __init__(self, indiv):
+        self._indiv = indiv
+        self._host = None
+
+    def __len__(self):
+        return self._indiv.shape[0]
+
+    def __getitem__(self, n):
+        if self._host is None:
+            self._host = self._indiv.cpu().numpy()
+        return [{"individual_reward": float(r)} for r in self._host[n]]
+
+    def __iter__(self):
+        for n in range(len(self)):
+            yield self[n]
+
+    @property
+    def individual_reward(self):
+        """[N, M] float32 device tensor."""
+        return self._indiv
+
+
+class MPEVecEnv:
+    """`envs` object of the runners: reset() / step(actions) / step_async / step_wait / close, attributes
+    num_envs, observation_space, share_observation_space, action_space (lists of length M)."""
+
+    def __init__(self, args, num_envs=None, device="cuda", seed=None, env_id_offset=0):
+        name = args.scenario_name
+        if name not in SCENARIOS:
+            raise NotImplementedError("Can not support the %s scenario on the device env" % name)
+        self.scenario_name = name
+        self.scenario = SCENARIOS[name]
+        self.num_envs = int(num_envs if num_envs is not None else args.n_rollout_threads)
+        self.n = self.num_agents = int(args.num_agents)
+        self.num_landmarks = int(args.num_landmarks)
+        self.episode_length = int(args.episode_length)
+        if name != "simple_spread":
+            assert self.num_agents == 2, "only 2 agents is supported, check the config.py."
+        self.device = torch.device(device)
+        L = _lib.lib()
+        M, NL, N = self.num_agents, self.num_landmarks, self.num_envs
+        self.obs_dims = [L.mappo_env_obs_dim(self.scenario, M, NL, i) for i in range(M)]
+        self.obs_width = L.mappo_env_obs_width(self.scenario, M, NL)
+        self.homogeneous = len(set(self.obs_dims)) == 1
+        # spaces (environment.py:54-100)
+        if name == "simple_spread":
+            acts = [Discrete(5) for _ in range(M)]
+        elif name == "simple_speaker_listener":
+            acts = [Discrete(3), Discrete(5)]
+        else:
+            acts = [MultiDiscrete([[0, 4], [0, 9]]) for _ in range(M)]
+        self.action_space = acts
+        self.head_sizes = [head_sizes(a) for a in acts]
+        self.act_width = max(len(h) for h in self.head_sizes)
+        self.observation_space = [Box(-np.inf, np.inf, (d,), np.float32) for d in self.obs_dims]
+        self.share_observation_space = [Box(-np.inf, np.inf, (self.obs_width,), np.float32) for _ in range(M)]
+        # world state in HBM
+        dev = self.device
+        self.p_pos = torch.zeros(2, M, N, dtype=torch.float64, device=dev)
+        self.p_vel = torch.zeros(2, M, N, dtype=torch.float64, device=dev)
+        self.lm_pos = torch.zeros(2, NL, N, dtype=torch.float64, device=dev)
+        self.comm = torch.full((M, N), -1, dtype=torch.int32, device=dev)
+        self.goal = torch.full((M, N), -1, dtype=torch.int32, device=dev)
+        self.step_count = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.episode = torch.zeros(N, dtype=torch.int32, device=dev)
+        self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length, 0,
+                                   int(seed if seed is not None else getattr(args, "seed", 1)) & (2 ** 64 - 1),
+                                   int(env_id_offset))
+        self._st = self._state_struct(self)
+        # default outputs (callers may pass buffer slots instead)
+        self._obs = torch.empty(N, self.obs_width, dtype=torch.float32, device=dev)
+        self._rew = torch.empty(N, M, 1, dtype=torch.float32, device=dev)
+        self._masks = torch.empty(N, M, 1, dtype=torch.float32, device=dev)
+        self._dones = torch.empty(N, M, dtype=torch.uint8, device=dev)
+        self._indiv = torch.empty(N, M, dtype=torch.float32, device=dev)
+        self._pending = None
+        self.closed = False
+
+    @staticmethod
+    def _state_struct(o):
+        return _lib.EnvState(*[C.c_void_p(t.data_ptr()) for t in
+                               (o.p_pos, o.p_vel, o.lm_pos, o.comm, o.goal, o.step_count, o.episode)])
+
+    # ------------------------------------------------------------------ helpers
+    def _shape_obs(self, flat):
+        """[N, W] -> reference layout: [N, M, D] for homogeneous agents, else list of [N, D_m] views."""
+        if self.homogeneous:
+            return flat.view(self.num_envs, self.num_agents, self.obs_dims[0])
+        outs, off = [], 0
+        for d in self.obs_dims:
+            outs.append(flat[:, off:off + d])
+            off += d
+        return outs
+
+    def actions_to_ids(self, actions):
+        """Accept what the reference's runners pass (one-hot `actions_env`, shared/mpe_runner.py:110-121) or
+        the policy's action ids; return float32 [N, M, act_width] ids on the device."""
+        if isinstance(actions, (list, tuple)):  # ragged per-agent list (separated runner)
+            cols = [self.actions_to_ids_one(a, i) for i, a in enumerate(actions)]
+            return torch.stack(cols, dim=1).contiguous()
+        a = torch.as_tensor(actions, device=self.device) if not torch.is_tensor(actions) else actions.to(self.device)
+        N, M = self.num_envs, self.num_agents
+        a = a.reshape(N, M, -1)
+        if a.shape[-1] == self.act_width and all(len(h) == self.act_width for h in self.head_sizes):
+            return a.to(torch.float32).contiguous()
+        sizes = self.head_sizes[0]
+        assert all(h == sizes for h in self.head_sizes) and a.shape[-1] == sum(sizes), \
+            "actions must be ids [N,M,%d] or one-hot [N,M,%d]" % (self.act_width, sum(sizes))
+        ids, off = [], 0
+        for s in sizes:
+            ids.append(a[..., off:off + s].argmax(dim=-1))
+            off += s
+        return torch.stack(ids, dim=-1).to(torch.float32).contiguous()
+
+    def actions_to_ids_one(self, a, agent):
+        a = torch.as_tensor(a, device=self.device) if not torch.is_tensor(a) else a.to(self.device)
+        a = a.reshape(self.num_envs, -1)
+        sizes = self.head_sizes[agent]
+        if a.shape[-1] == len(sizes):
+            ids = a.to(torch.float32)
+        else:
+            cols, off = [], 0
+            for s in sizes:
+                cols.append(a[:, off:off + s].argmax(dim=-1))
+                off += s
+            ids = torch.stack(cols, dim=-1).to(torch.float32)
+        if ids.shape[-1] < self.act_width:
+            ids = torch.nn.functional.pad(ids, (0, self.act_width - ids.shape[-1]))
+        return ids
+
+    # ------------------------------------------------------------------ vec-env contract
+    def seed(self, seed):
+        self._cfg.seed = int(seed) & (2 ** 64 - 1)
+
+    def reset(self, out_obs=None, use_given_state=False):
+        obs = self._obs if out_obs is None else out_obs
+        assert obs.is_contiguous() and obs.numel() == self.num_envs * self.obs_width
+        _lib.check(_lib.lib().mappo_env_reset(C.byref(self._cfg), C.byref(self._st), _lib.ptr(obs),
+                                              1 if use_given_state else 0, _lib.stream_ptr()), "env_reset")
+        return self._shape_obs(obs.view(self.num_envs, self.obs_width))
+
+    def set_state(self, p_pos=None, p_vel=None, lm_pos=None, goal=None, comm=None, step_count=None):
+        """Install a world state given in the reference's per-env layout ([N,M,2], [N,L,2], [N,M]);
+        used by parity tests to inject the reference's own states."""
+        def put(dst, src, perm):
+            if src is not None:
+                dst.copy_(torch.as_tensor(np.asarray(src)).permute(*perm).to(dst.dtype))
+        put(self.p_pos, p_pos, (2, 1, 0)); put(self.p_vel, p_vel, (2, 1, 0)); put(self.lm_pos, lm_pos, (2, 1, 0))
+        put(self.goal, goal, (1, 0)); put(self.comm, comm, (1, 0))
+        if step_count is not None:
+            self.step_count.copy_(torch.as_tensor(np.asarray(step_count)).to(torch.int32))
+
+    def get_state(self):
+        return dict(p_pos=self.p_pos.permute(2, 1, 0).cpu().numpy(), p_vel=self.p_vel.permute(2, 1, 0).cpu().numpy(),
+                    lm_pos=self.lm_pos.permute(2, 1, 0).cpu().numpy(), goal=self.goal.t().cpu().numpy(),
+                    comm=self.comm.t().cpu().numpy(), step_count=self.step_count.cpu().numpy())
+
+    def step_ids(self, action_ids, out_obs=None, out_rewards=None, out_masks=None, reset_state=None):
+        """Hot-path entry: `action_ids` float32 [N, M, act_width] on the device (a SharedReplayBuffer.actions
+        slot); outputs may be buffer slots so the step writes straight into the rollout storage."""
+        obs = self._obs if out_obs is None else out_obs
+        rew = self._rew if out_rewards is None else out_rewards
+        masks = self._masks if out_masks is None else out_masks
+        rs = None
+        if reset_state is not None:
+            keep = []
+            class _RS: pass
+            o = _RS()
+            dev = self.device
+            o.p_pos = torch.as_tensor(np.asarray(reset_state["p_pos"])).permute(2, 1, 0).contiguous().to(dev, torch.float64)
+            o.lm_pos = torch.as_tensor(np.asarray(reset_state["lm_pos"])).permute(2, 1, 0).contiguous().to(dev, torch.float64)
+            o.goal = torch.as_tensor(np.asarray(reset_state["goal"])).t().contiguous().to(dev, torch.int32)
+            o.p_vel, o.comm, o.step_count, o.episode = o.p_pos, o.goal, o.goal, o.goal
+            self._rs_keep = o
+            rs = C.byref(self._state_struct(o))
+        _lib.check(_lib.lib().mappo_env_step(
+            C.byref(self._cfg), C.byref(self._st), _lib.ptr(action_ids), int(action_ids.shape[-1]),
+            _lib.ptr(obs), _lib.ptr(rew), _lib.ptr(masks), _lib.ptr(self._dones), _lib.ptr(self._indiv),
+            rs, _lib.stream_ptr()), "env_step")
+        return obs, rew, masks
+
+    def step_async(self, actions):
+        self._pending = self.actions_to_ids(actions)
+
+    def step_wait(self):
+        obs, rew, _ = self.step_ids(self._pending)
+        self._pending = None
+        return (self._shape_obs(obs.view(self.num_envs, self.obs_width)), rew.view(self.num_envs, self.num_agents, 1),
+                self._dones.bool(), _Infos(self._indiv))
+
+    def step(self, actions):
+        self.step_async(actions)
+        return self.step_wait()
+
+    def close(self):
+        self.closed = True
+
+    def render(self, mode="rgb_array"):
+        raise NotImplementedError("rendering (pyglet/OpenGL in the reference) is unavailable on this box")
+
+
+def MPEEnv(args, **kw):
+    """Name-compatible constructor (onpolicy/envs/mpe/MPE_env.py:5)."""
+    return MPEVecEnv(args, **kw)
