@@ -110,6 +110,55 @@ int mappo_env_step(const mappo_env_config* cfg, const mappo_env_state* st, const
                    int act_width, float* obs_out, float* rewards_out, float* masks_out,
                    uint8_t* dones_out, float* indiv_out, const mappo_env_state* reset_src, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------------
+ * 2. Returns / GAE / ValueNorm / advantages.
+ *    Replaces SharedReplayBuffer.compute_returns (all four branches)   onpolicy/utils/shared_buffer.py:168-224
+ *             ValueNorm.running_mean_var/update/normalize/denormalize   onpolicy/utils/valuenorm.py:31-78
+ *             the advantage prologue of R_MAPPO.train                   onpolicy/algorithms/r_mappo/r_mappo.py:174-182
+ *    All arithmetic is float32 with the reference's operation order and separately rounded ops
+ *    (the file is compiled without FMA contraction), so returns match numpy bit for bit.
+ *    Arrays are time-major [T or T+1][R] with R = N*M (shared buffer) or N (separated buffer) trajectories.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t T;                       /* episode_length */
+  int32_t R;                       /* trajectories */
+  float gamma;                     /* float32(args.gamma) */
+  float gamma_lambda;              /* float32(args.gamma * args.gae_lambda), product taken in double */
+  int32_t use_gae;
+  int32_t use_proper_time_limits;
+  int32_t use_value_norm;          /* ValueNorm or PopArt statistics in `vn_stats` */
+  int32_t reserved;
+} mappo_gae_config;
+
+/* vn_stats: float32[3] = {running_mean, running_mean_sq, debiasing_term} (valuenorm.py:19-21), or NULL.
+ * next_value: float32 [R] written to value_preds[T] first (shared_buffer.py:207), or NULL.
+ * bad_masks: [T+1][R] or NULL (= ones).  active_masks: [T+1][R] or NULL (= ones).
+ * Outputs: returns [T+1][R]; advantages_raw [T][R] = returns[:-1] - denorm(value_preds[:-1]);
+ * adv_partials: double [mappo_gae_num_partials(R)][3] per-block (sum, sum of squares, count) over active
+ * entries, reduced by mappo_adv_stats_reduce. */
+int mappo_gae_num_partials(int R);
+int mappo_gae_returns(const mappo_gae_config* cfg, const float* rewards, float* value_preds, float* returns,
+                      const float* masks, const float* bad_masks, const float* active_masks,
+                      const float* next_value, const float* vn_stats, float* advantages_raw,
+                      double* adv_partials, void* stream);
+/* Sum the per-block partials in a fixed order into stats3 = double {sum, sumsq, count}.  In a multi-GPU
+ * job the caller all-reduces stats3 (3 doubles) between this call and mappo_adv_normalize. */
+int mappo_adv_stats_reduce(const double* partials, int num_partials, double* stats3, void* stream);
+/* advantages = (raw - mean) / (std + 1e-5) with population std (np.nanmean / np.nanstd, r_mappo.py:180-182). */
+int mappo_adv_normalize(const float* advantages_raw, float* advantages, long long count, const double* stats3,
+                        void* stream);
+
+/* ValueNorm.update(batch) (valuenorm.py:38-54), split so that the batch moments can be all-reduced:
+ *   moments: per-block partial {sum x, sum x^2, n} of `x[count]` (optionally only where weights != 0)
+ *   -> mappo_adv_stats_reduce -> [all-reduce] -> mappo_valuenorm_apply: EMA update of vn_stats (float32[3]). */
+int mappo_moments_num_partials(long long count);
+int mappo_moments(const float* x, long long count, double* partials, void* stream);
+int mappo_valuenorm_apply(float* vn_stats, const double* stats3, double beta, void* stream);
+/* out = (x - mean) / sqrt(var)  or  out = x * sqrt(var) + mean  (valuenorm.py:56-78), elementwise float32 */
+int mappo_valuenorm_transform(const float* vn_stats, const float* x, float* out, long long count, int denormalize,
+                              void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -124,7 +124,154 @@ def gen_env():
         print("wrote", path, os.path.getsize(path))
 
 
-PARTS = {"env": gen_env}
+# ------------------------------------------------------------------ GAE / ValueNorm fixtures
+def _vn_with_history(seed, n_updates=10):
+    from onpolicy.utils.valuenorm import ValueNorm
+    g = torch.Generator().manual_seed(seed)
+    vn = ValueNorm(1)
+    hist = []
+    for _ in range(n_updates):
+        x = torch.randn(257, 1, generator=g) * 3.0 - 4.0
+        vn.update(x)
+        hist.append(x.numpy().copy())
+    return vn, np.stack(hist)
+
+
+def vn_stats(vn):
+    return np.array([vn.running_mean.item(), vn.running_mean_sq.item(), vn.debiasing_term.item()], dtype=np.float32)
+
+
+def gen_vnorm():
+    vn, hist = _vn_with_history(0)
+    from onpolicy.utils.valuenorm import ValueNorm
+    vn2 = ValueNorm(1)
+    stats_seq = []
+    for x in hist:
+        vn2.update(torch.from_numpy(x))
+        stats_seq.append(vn_stats(vn2))
+    x = (torch.randn(64, 1, generator=torch.Generator().manual_seed(5)) * 5).numpy()
+    out = dict(batches=hist, stats_seq=np.stack(stats_seq), x=x, normalized=vn.normalize(x).numpy(),
+               denormalized=vn.denormalize(x),
+               fresh_denormalized=ValueNorm(1).denormalize(x))       # first iteration: mean 0, std 0.1
+    path = os.path.join(HERE, "vnorm.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path))
+
+
+def _filled_buffer(args, M, obs_dim, share_dim, act_space, seed):
+    from onpolicy.utils.shared_buffer import SharedReplayBuffer
+    from gym import spaces
+    buf = SharedReplayBuffer(args, M, spaces.Box(-np.inf, np.inf, (obs_dim,), np.float32),
+                             spaces.Box(-np.inf, np.inf, (share_dim,), np.float32), act_space)
+    rng = np.random.RandomState(seed)
+    buf.rewards[:] = rng.normal(-5, 2, buf.rewards.shape)
+    buf.value_preds[:] = rng.normal(0, 1, buf.value_preds.shape)
+    buf.masks[:] = (rng.uniform(size=buf.masks.shape) > 0.1)
+    buf.bad_masks[:] = (rng.uniform(size=buf.bad_masks.shape) > 0.15)
+    buf.active_masks[:] = (rng.uniform(size=buf.active_masks.shape) > 0.1)
+    return buf, rng
+
+
+def gen_gae():
+    from gym import spaces
+    out = {}
+    T, N, M = 25, 5, 3
+    for use_gae in (1, 0):
+        for proper in (0, 1):
+            for norm in (1, 0):
+                extra = ("" if use_gae else "--use_gae ") + ("--use_proper_time_limits " if proper else "") + \
+                        ("" if norm else "--use_valuenorm ")
+                args = ref_args("simple_spread", M, 3, "mappo", "--n_rollout_threads %d %s" % (N, extra))
+                args.n_rollout_threads = N
+                assert args.use_gae == bool(use_gae) and args.use_valuenorm == bool(norm)
+                buf, rng = _filled_buffer(args, M, 18, 54, spaces.Discrete(5), seed=100 + use_gae * 4 + proper * 2 + norm)
+                vn, _ = _vn_with_history(3) if norm else (None, None)
+                nv = rng.normal(0, 1, (N, M, 1)).astype(np.float32)
+                tag = "g%dp%dn%d" % (use_gae, proper, norm)
+                out[tag + "_rewards"] = buf.rewards.copy(); out[tag + "_value_preds_in"] = buf.value_preds.copy()
+                out[tag + "_masks"] = buf.masks.copy(); out[tag + "_bad_masks"] = buf.bad_masks.copy()
+                out[tag + "_active_masks"] = buf.active_masks.copy(); out[tag + "_next_value"] = nv
+                if norm:
+                    out[tag + "_vn"] = vn_stats(vn)
+                buf.compute_returns(nv, vn)
+                out[tag + "_returns"] = buf.returns.copy(); out[tag + "_value_preds_out"] = buf.value_preds.copy()
+                # advantage prologue, verbatim from r_mappo.py:174-182
+                if norm:
+                    adv = buf.returns[:-1] - vn.denormalize(buf.value_preds[:-1])
+                else:
+                    adv = buf.returns[:-1] - buf.value_preds[:-1]
+                cp = adv.copy(); cp[buf.active_masks[:-1] == 0.0] = np.nan
+                out[tag + "_adv_raw"] = adv
+                out[tag + "_adv"] = (adv - np.nanmean(cp)) / (np.nanstd(cp) + 1e-5)
+    path = os.path.join(HERE, "gae.npz")
+    np.savez_compressed(path, T=T, N=N, M=M, gamma=0.99, gae_lambda=0.95, **out)
+    print("wrote", path, os.path.getsize(path))
+
+
+# ------------------------------------------------------------------ generator (minibatch indexing) fixtures
+FIELDS = ["share_obs", "obs", "rnn_states", "rnn_states_critic", "actions", "value_preds", "returns", "masks",
+          "active_masks", "old_action_log_probs", "adv_targ", "available_actions"]
+
+
+def _tag_rows(buf, rng):
+    """Fill every buffer field with distinct random values so gathered rows identify their source."""
+    for name in ("share_obs", "obs", "rnn_states", "rnn_states_critic", "value_preds", "returns", "masks",
+                 "active_masks", "actions", "action_log_probs", "rewards"):
+        a = getattr(buf, name)
+        a[:] = rng.standard_normal(a.shape)
+    if buf.available_actions is not None:
+        buf.available_actions[:] = rng.standard_normal(buf.available_actions.shape)
+
+
+def gen_gen():
+    from gym import spaces
+    from onpolicy.envs.mpe.multi_discrete import MultiDiscrete
+    from onpolicy.utils.separated_buffer import SeparatedReplayBuffer
+    out = {}
+    T, N, M = 25, 4, 3
+    args = ref_args("simple_spread", M, 3, "rmappo", "--n_rollout_threads %d --hidden_size 8" % N)
+    for space_tag, space in (("disc", spaces.Discrete(5)), ("multi", MultiDiscrete([[0, 4], [0, 9]]))):
+        buf, rng = _filled_buffer(args, M, 6, 7, space, seed=7)
+        _tag_rows(buf, rng)
+        adv = rng.standard_normal(buf.rewards.shape).astype(np.float32)
+        for name in ("share_obs", "obs", "rnn_states", "rnn_states_critic", "actions", "action_log_probs",
+                     "value_preds", "returns", "masks", "active_masks"):
+            out["shared_%s_buf_%s" % (space_tag, name)] = getattr(buf, name).copy()
+        if buf.available_actions is not None:
+            out["shared_%s_buf_available_actions" % space_tag] = buf.available_actions.copy()
+        out["shared_%s_buf_advantages" % space_tag] = adv
+        for gname, call in (("ff", lambda: buf.feed_forward_generator(adv, 2)),
+                            ("rec", lambda: buf.recurrent_generator(adv, 2, 10)),
+                            ("naive", lambda: buf.naive_recurrent_generator(adv, 2))):
+            torch.manual_seed(123)
+            for k, sample in enumerate(call()):
+                for f, v in zip(FIELDS, sample):
+                    if v is not None:
+                        out["shared_%s_%s_mb%d_%s" % (space_tag, gname, k, f)] = np.asarray(v)
+    # separated buffer (config 3): [T+1, N, .]
+    sb = SeparatedReplayBuffer(args, spaces.Box(-np.inf, np.inf, (11,), np.float32),
+                               spaces.Box(-np.inf, np.inf, (14,), np.float32), spaces.Discrete(5))
+    rng = np.random.RandomState(9)
+    _tag_rows(sb, rng)
+    adv = rng.standard_normal(sb.rewards.shape).astype(np.float32)
+    for name in ("share_obs", "obs", "rnn_states", "rnn_states_critic", "actions", "action_log_probs",
+                 "value_preds", "returns", "masks", "active_masks", "available_actions"):
+        out["sep_buf_%s" % name] = getattr(sb, name).copy()
+    out["sep_buf_advantages"] = adv
+    for gname, call in (("ff", lambda: sb.feed_forward_generator(adv, 2)),
+                        ("rec", lambda: sb.recurrent_generator(adv, 2, 10)),
+                        ("naive", lambda: sb.naive_recurrent_generator(adv, 2))):
+        torch.manual_seed(321)
+        for k, sample in enumerate(call()):
+            for f, v in zip(FIELDS, sample):
+                if v is not None:
+                    out["sep_%s_mb%d_%s" % (gname, k, f)] = np.asarray(v)
+    path = os.path.join(HERE, "generators.npz")
+    np.savez_compressed(path, T=T, N=N, M=M, **out)
+    print("wrote", path, os.path.getsize(path))
+
+
+PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen}
 
 if __name__ == "__main__":
     todo = sys.argv[1:] or list(PARTS)
