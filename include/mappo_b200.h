@@ -149,6 +149,12 @@ int mappo_adv_stats_reduce(const double* partials, int num_partials, double* sta
 int mappo_adv_normalize(const float* advantages_raw, float* advantages, long long count, const double* stats3,
                         void* stream);
 
+/* advantages_raw = returns[:-1] - denorm(value_preds[:-1]) (r_mappo.py:174-177) recomputed from the buffer,
+ * plus the per-block moments over active entries (as mappo_gae_returns produces them).  count = T*R elements;
+ * partials: double [mappo_moments_num_partials(count)][3]. */
+int mappo_advantages(const float* returns, const float* value_preds, const float* active_masks,
+                     const float* vn_stats, long long count, float* advantages_raw, double* partials, void* stream);
+
 /* ValueNorm.update(batch) (valuenorm.py:38-54), split so that the batch moments can be all-reduced:
  *   moments: per-block partial {sum x, sum x^2, n} of `x[count]` (optionally only where weights != 0)
  *   -> mappo_adv_stats_reduce -> [all-reduce] -> mappo_valuenorm_apply: EMA update of vn_stats (float32[3]). */
@@ -158,6 +164,135 @@ int mappo_valuenorm_apply(float* vn_stats, const double* stats3, double beta, vo
 /* out = (x - mean) / sqrt(var)  or  out = x * sqrt(var) + mean  (valuenorm.py:56-78), elementwise float32 */
 int mappo_valuenorm_transform(const float* vn_stats, const float* x, float* out, long long count, int denormalize,
                               void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 3. Actor / critic networks: fused forward (rollout) and fused forward + loss + backward (update).
+ *    Replaces R_Actor.forward / evaluate_actions, R_Critic.forward   onpolicy/algorithms/r_mappo/algorithm/r_actor_critic.py:43-107,146-165
+ *             MLPBase / MLPLayer (LayerNorm -> Linear -> act -> LayerNorm ...)   onpolicy/algorithms/utils/mlp.py:6-59
+ *             ACTLayer + FixedCategorical (sample / mode / log_probs / entropy)  onpolicy/algorithms/utils/act.py:41-162,
+ *                                                                                  onpolicy/algorithms/utils/distributions.py:14-68
+ *             R_MAPPO.ppo_update losses and cal_value_loss                         onpolicy/algorithms/r_mappo/r_mappo.py:52-136
+ *             huber_loss / mse_loss                                                onpolicy/utils/util.py:23-29
+ *    Parameters of one network live in ONE flat float32 buffer in this order (the reference's
+ *    nn.Module.parameters() order, minus the never-executed `fc_h` template, mlp.py:20-27):
+ *      [feature_norm.weight[in], feature_norm.bias[in]]            if use_feature_norm
+ *      fc1: W[H][in], b[H], ln_w[H], ln_b[H]
+ *      fc2[l], l < layer_N: W[H][H], b[H], ln_w[H], ln_b[H]
+ *      [rnn: W_ih[3H][H], W_hh[3H][H], b_ih[3H], b_hh[3H], norm_w[H], norm_b[H]]   if recurrent
+ *      heads h < n_heads: W[head_dim[h]][H], b[head_dim[h]]        (critic: one head of dim 1 = v_out)
+ *    Gradients use the same layout.
+ * ---------------------------------------------------------------------------------------------- */
+#define MAPPO_MAX_HEADS 4
+typedef struct {
+  int32_t in_dim;              /* obs dim D (actor) or share-obs dim S (critic) */
+  int32_t hidden;              /* H; this build: 64 */
+  int32_t layer_N;             /* this build: 1 */
+  int32_t use_relu;            /* 0 = Tanh, 1 = ReLU (mlp.py:11) */
+  int32_t use_feature_norm;    /* LayerNorm on the input (mlp.py:44-45) */
+  int32_t recurrent;           /* 0 = MLP, 1 = one GRU layer + LayerNorm (rnn.py) */
+  int32_t n_heads;             /* categorical heads (Discrete: 1, MultiDiscrete: 2); critic: 1 */
+  int32_t head_dim[MAPPO_MAX_HEADS];
+  int32_t is_critic;
+} mappo_net_config;
+
+long long mappo_net_param_count(const mappo_net_config* cfg);
+
+/* Actor forward for the rollout (R_Actor.forward): rows = N*M observations.
+ *   obs [rows][obs_ld] float32 (row stride obs_ld >= in_dim: rows may be slices of a wider share_obs row)
+ *   available_actions [rows][head_dim[0]] or NULL; deterministic != 0 -> mode() else sample()
+ *   sampling: inverse CDF on the softmax with u = Philox(counter = (row_offset + row, step, head, 0), key = (seed, 'SAMP'))
+ *   actions_out, logp_out: float32 [rows][n_heads]  (act.py:65-81: per-head, concatenated)
+ * Evaluate mode (R_Actor.evaluate_actions without the backward, act.py:107-162): if `given_actions`
+ * (float32 [rows][n_heads]) is not NULL nothing is sampled; logp_out receives log_prob(given action) and
+ * entropy_out (float32 [rows], may be NULL) the mean over heads of each row's entropy; actions_out may be NULL. */
+int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
+                        long long rows, const float* available_actions, int deterministic, uint64_t seed,
+                        uint64_t step, long long row_offset, const float* given_actions, float* actions_out,
+                        float* logp_out, float* entropy_out, void* stream);
+
+/* Critic forward (R_Critic.forward / get_values): `rows` unique share-obs rows, each value written `group`
+ * times: values_out float32 [rows][group] (group = M when the M agents of an env share one share_obs row). */
+int mappo_critic_forward(const mappo_net_config* cfg, const float* params, const float* share_obs, int obs_ld,
+                         long long rows, int group, float* values_out, void* stream);
+
+typedef struct {
+  float clip_param;            /* args.clip_param */
+  float entropy_coef;          /* args.entropy_coef */
+  float value_loss_coef;       /* args.value_loss_coef */
+  float huber_delta;           /* args.huber_delta */
+  int32_t use_huber_loss;
+  int32_t use_clipped_value_loss;
+  int32_t use_value_norm;      /* normalize(return) with vn_stats (ValueNorm or PopArt statistics) */
+  int32_t use_policy_active_masks;
+  int32_t use_value_active_masks;
+  int32_t reserved;
+} mappo_loss_config;
+
+/* number of thread blocks (= partial rows) the update kernels use for `rows` rows on the current device */
+int mappo_update_num_blocks(long long rows);
+
+/* Actor: forward + clipped-surrogate/entropy loss + backward over one minibatch (r_mappo.py:115-141).
+ *   index: int64 [rows] row gather into the flat buffers (the minibatch permutation,
+ *          shared_buffer.py:246-247), or NULL for the identity (num_mini_batch == 1: the loss is a mean,
+ *          so the order only changes the summation order).
+ *   actions, old_logp [*][n_heads]; adv [*]; active_masks [*] or NULL.
+ * Outputs, one row per block b < mappo_update_num_blocks(rows), UNNORMALISED sums (the 1/sum(active) factor,
+ * the LayerNorm-affine chain rule and the global sum over blocks and ranks are applied by
+ * mappo_grad_reduce / mappo_adam_step):
+ *   grad_partials float32 [blocks][P];
+ *   loss_partials double [blocks][4] = {sum -min(surr1,surr2)*active, sum entropy*active (mean over heads),
+ *                                       sum ratio (all heads), sum active} */
+int mappo_actor_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                       const float* obs, int obs_ld, long long rows, const int64_t* index, const float* actions,
+                       const float* old_logp, const float* adv, const float* active_masks,
+                       const float* available_actions, float* grad_partials, double* loss_partials, void* stream);
+
+/* Critic: forward + (clipped, huber/mse, value-normalised) value loss + backward (r_mappo.py:52-89,151-156).
+ *   `rows` unique share-obs rows; each carries `group` loss terms: value_preds, returns, active_masks
+ *   [rows][group] (group = M for the shared buffer with num_mini_batch == 1, else 1 with `index`).
+ *   share_rows_div: with `index`, sample i reads share_obs row index[i] / share_rows_div (= M when the
+ *   storage keeps ONE share_obs row per env and the reference's M replicated rows are a view of it), while
+ *   its value_preds / returns / active_masks entries are read at index[i].  1 otherwise.
+ *   vn_stats float32[3] AFTER this minibatch's ValueNorm.update (r_mappo.py:65-67) or NULL.
+ *   loss_partials double [blocks][4] = {sum value_loss*active, sum active, 0, 0} */
+int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                        const float* share_obs, int obs_ld, long long rows, int group, const int64_t* index,
+                        int share_rows_div,
+                        const float* value_preds, const float* returns, const float* active_masks,
+                        const float* vn_stats, float* grad_partials, double* loss_partials, void* stream);
+
+/* Sum the per-block partials in a fixed order: grad_sum float32 [P], loss_sum double [4].  In a multi-GPU job
+ * the caller all-reduces both (sum) before mappo_adam_step. */
+int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
+                      float* grad_sum, double* loss_sum, void* stream);
+
+typedef struct {
+  float lr, beta1, beta2, eps, weight_decay;
+  float max_grad_norm;         /* args.max_grad_norm */
+  int32_t use_max_grad_norm;
+  float bias_correction1;      /* 1 - beta1^t  (t = this step, computed on the host in double) */
+  float bias_correction2_sqrt; /* sqrt(1 - beta2^t) */
+  float loss_scale;            /* entropy/value coefficients are already inside the gradients: 1.0 */
+} mappo_adam_config;
+
+/* From the reduced sums: finish the chain rule through the folded LayerNorm affines, divide by the loss
+ * denominator (loss_sum[denominator_slot], or `rows_total` if use_mean != 0), clip the global L2 norm
+ * (nn.utils.clip_grad_norm_, r_mappo.py:143-146) and apply torch.optim.Adam's update in place
+ * (rMAPPOPolicy.py:31-37).  grad_out (float32 [P], may be NULL) receives the final (unclipped) gradient;
+ * info_out (float32 [4], may be NULL) is ACCUMULATED with {loss, grad_norm, aux (entropy | 0), ratio mean | 0}. */
+int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params, float* exp_avg,
+                    float* exp_avg_sq, const float* grad_sum, const double* loss_sum, int denominator_slot,
+                    long long rows_total, int apply_update, float* grad_out, float* info_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 4. Minibatch gather (the generator API; the update kernels take `index` and gather in place).
+ *    Replaces the fancy-index gathers of SharedReplayBuffer.feed_forward_generator / recurrent_generator /
+ *    naive_recurrent_generator   onpolicy/utils/shared_buffer.py:262-282,330-345,440-455
+ *    dst[i][0:width] = src[(index[i] / row_div) * row_stride + 0:width],  i < n;  index is the int64 permutation
+ *    (torch.randperm on the CPU generator, shared_buffer.py:246,301,397) copied to the device.
+ * ---------------------------------------------------------------------------------------------- */
+int mappo_gather_rows(const float* src, long long row_stride, int row_div, int width, const int64_t* index,
+                      long long n, float* dst, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,225 @@
+"""R_Actor / R_Critic mirrors (onpolicy/algorithms/r_mappo/algorithm/r_actor_critic.py:12-165).
+
+Same constructor arguments, method names, return order and `state_dict()` keys as the reference, so
+`actor.pt` / `critic.pt` checkpoints are interchangeable.  All trainable parameters of a network are
+views into ONE flat float32 CUDA buffer (`.flat`, layout in include/mappo_b200.h section 3) which the
+fused kernels read; there is no PyTorch forward path."""
+import copy
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .... import ops
+from ....envs.spaces import head_sizes
+
+
+def check(x, device):
+    """algorithms/utils/util.py:15-17 plus the move to the device."""
+    if x is None:
+        return None
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(x)
+    return x.to(device=device, dtype=torch.float32)
+
+
+class _Node(nn.Module):
+    """Anonymous container used to reproduce the reference's module tree (and therefore its key names)."""
+
+
+def _attach(root, dotted, param):
+    parts = dotted.split(".")
+    node = root
+    for p in parts[:-1]:
+        if p not in node._modules:
+            node.add_module(p, _Node())
+        node = node._modules[p]
+    node.register_parameter(parts[-1], param)
+
+
+def _reference_init(args, in_dim, head_dims, is_critic):
+    """Initial values, drawn exactly as the reference draws them (same torch CPU RNG consumption order):
+    MLPLayer.__init__ mlp.py:6-22 (fc1, then the fc_h template, fc2 = deep copies of fc_h),
+    RNNLayer.__init__ rnn.py:7-22, Categorical.__init__ distributions.py:56-62 / v_out r_actor_critic.py:134-140.
+    Returns an ordered {reference key: CPU tensor}."""
+    H = args.hidden_size
+    use_relu, orth = bool(args.use_ReLU), bool(args.use_orthogonal)
+    w_init = nn.init.orthogonal_ if orth else nn.init.xavier_uniform_
+    gain = nn.init.calculate_gain("relu" if use_relu else "tanh")
+    out = {}
+
+    def linear(i, o, g):
+        lin = nn.Linear(i, o)
+        w_init(lin.weight.data, gain=g)
+        nn.init.constant_(lin.bias.data, 0)
+        return lin
+
+    if args.use_feature_normalization:
+        out["base.feature_norm.weight"] = torch.ones(in_dim)
+        out["base.feature_norm.bias"] = torch.zeros(in_dim)
+    fc1 = linear(in_dim, H, gain)
+    fc_h = linear(H, H, gain)
+    out["base.mlp.fc1.0.weight"], out["base.mlp.fc1.0.bias"] = fc1.weight.data, fc1.bias.data
+    out["base.mlp.fc1.2.weight"], out["base.mlp.fc1.2.bias"] = torch.ones(H), torch.zeros(H)
+    out["base.mlp.fc_h.0.weight"], out["base.mlp.fc_h.0.bias"] = fc_h.weight.data, fc_h.bias.data
+    out["base.mlp.fc_h.2.weight"], out["base.mlp.fc_h.2.bias"] = torch.ones(H), torch.zeros(H)
+    for l in range(args.layer_N):
+        out["base.mlp.fc2.%d.0.weight" % l] = fc_h.weight.data.clone()
+        out["base.mlp.fc2.%d.0.bias" % l] = fc_h.bias.data.clone()
+        out["base.mlp.fc2.%d.2.weight" % l], out["base.mlp.fc2.%d.2.bias" % l] = torch.ones(H), torch.zeros(H)
+    if args.use_recurrent_policy or args.use_naive_recurrent_policy:
+        gru = nn.GRU(H, H, num_layers=args.recurrent_N)
+        for name, prm in gru.named_parameters():
+            if "bias" in name:
+                nn.init.constant_(prm, 0)
+            elif orth:
+                nn.init.orthogonal_(prm)
+            else:
+                nn.init.xavier_uniform_(prm)
+        for name, prm in gru.named_parameters():
+            out["rnn.rnn." + name] = prm.data
+        out["rnn.norm.weight"], out["rnn.norm.bias"] = torch.ones(H), torch.zeros(H)
+    if is_critic:
+        v = linear(H, 1, 1)
+        out["v_out.weight"], out["v_out.bias"] = v.weight.data, v.bias.data
+    elif len(head_dims) == 1:
+        a = linear(H, head_dims[0], args.gain)
+        out["act.action_out.linear.weight"], out["act.action_out.linear.bias"] = a.weight.data, a.bias.data
+    else:
+        for i, d in enumerate(head_dims):
+            a = linear(H, d, args.gain)
+            out["act.action_outs.%d.linear.weight" % i] = a.weight.data
+            out["act.action_outs.%d.linear.bias" % i] = a.bias.data
+    return out
+
+
+class _FlatNet(nn.Module):
+    def _build(self, args, in_dim, head_dims, is_critic, device):
+        self.hidden_size = args.hidden_size
+        self._recurrent = bool(args.use_recurrent_policy or args.use_naive_recurrent_policy)
+        self._recurrent_N = args.recurrent_N
+        self.device_ = torch.device(device)
+        if args.use_popart:
+            raise NotImplementedError("PopArt head is not built yet (SURVEY.md §8f)")
+        if self._recurrent and args.recurrent_N != 1:
+            raise NotImplementedError("recurrent_N > 1")
+        self.cfg = ops.net_config(in_dim, args.hidden_size, args.layer_N, args.use_ReLU,
+                                  args.use_feature_normalization, self._recurrent, head_dims, is_critic)
+        init = _reference_init(args, in_dim, head_dims, is_critic)
+        live = [k for k in init if "fc_h" not in k]
+        total = sum(init[k].numel() for k in live)
+        assert total == ops.net_param_count(self.cfg), (total, ops.net_param_count(self.cfg))
+        flat = torch.empty(total, dtype=torch.float32, device=self.device_)
+        self.register_buffer("flat", flat, persistent=False)
+        off = 0
+        self._slices = {}
+        for k, v in init.items():
+            if "fc_h" in k:      # registered-but-never-executed template (mlp.py:20-27): kept for checkpoints
+                p = nn.Parameter(v.to(self.device_), requires_grad=False)
+            else:
+                n = v.numel()
+                flat[off:off + n].copy_(v.reshape(-1))
+                p = nn.Parameter(flat[off:off + n].view(v.shape), requires_grad=False)
+                self._slices[k] = (off, off + n)
+                off += n
+            _attach(self, k, p)
+        assert off == total
+
+    def flat_view(self, key):
+        a, b = self._slices[key]
+        return self.flat[a:b]
+
+    def unflatten(self, vec):
+        """{reference key: view} of a flat vector laid out like `.flat` (gradients, Adam moments)."""
+        return {k: vec[a:b].view(dict(self.named_parameters())[k].shape) for k, (a, b) in self._slices.items()}
+
+    def load_state_dict(self, state_dict, strict=True):
+        own = dict(self.named_parameters())
+        missing = [k for k in own if k not in state_dict]
+        unexpected = [k for k in state_dict if k not in own]
+        if strict and (missing or unexpected):
+            raise RuntimeError("load_state_dict: missing %s unexpected %s" % (missing, unexpected))
+        with torch.no_grad():
+            for k, v in state_dict.items():
+                if k in own:
+                    own[k].copy_(torch.as_tensor(v).to(own[k]))
+
+
+class R_Actor(_FlatNet):
+    def __init__(self, args, obs_space, action_space, device=torch.device("cuda")):
+        super().__init__()
+        self._use_policy_active_masks = args.use_policy_active_masks
+        obs_shape = obs_space.shape
+        if len(obs_shape) == 3:
+            raise NotImplementedError("CNN base: MPE observations are vectors (r_actor_critic.py:33)")
+        self.head_dims = head_sizes(action_space)
+        self.discrete = action_space.__class__.__name__ == "Discrete"
+        self._build(args, obs_shape[0], self.head_dims, False, device)
+        self.sample_seed = int(getattr(args, "seed", 1))
+        self._calls = 0
+
+    def forward(self, obs, rnn_states, masks, available_actions=None, deterministic=False):
+        """-> (actions int64 [B, heads], action_log_probs [B, heads], rnn_states)   r_actor_critic.py:43-70"""
+        obs = check(obs, self.device_)
+        B = obs.shape[0]
+        nh = len(self.head_dims)
+        actions = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
+        logp = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
+        rnn_states = check(rnn_states, self.device_)
+        self.forward_into(obs, actions, logp, available_actions=check(available_actions, self.device_),
+                          deterministic=deterministic)
+        return actions.long(), logp, rnn_states
+
+    def forward_into(self, obs, actions_out, logp_out, available_actions=None, deterministic=False, step=None,
+                     row_offset=0):
+        """Hot-path entry: writes float32 action ids and log-probs straight into buffer slots."""
+        if self._recurrent:
+            raise NotImplementedError("recurrent (GRU) actor is not built yet")
+        if step is None:
+            step = self._calls
+        self._calls += 1
+        if not self.discrete:
+            available_actions = None
+        ops.actor_forward(self.cfg, self.flat, obs, actions_out, logp_out,
+                          available_actions=None if available_actions is None else available_actions.contiguous(),
+                          deterministic=deterministic, seed=self.sample_seed, step=step, row_offset=row_offset)
+
+    def evaluate_actions(self, obs, rnn_states, action, masks, available_actions=None, active_masks=None):
+        """-> (action_log_probs [B, heads], dist_entropy scalar)   r_actor_critic.py:72-107, act.py:107-162"""
+        if self._recurrent:
+            raise NotImplementedError("recurrent (GRU) actor is not built yet")
+        obs = check(obs, self.device_)
+        B, nh = obs.shape[0], len(self.head_dims)
+        action = check(action, self.device_).reshape(B, nh).contiguous()
+        logp = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
+        ent = torch.empty(B, dtype=torch.float32, device=self.device_)
+        avail = check(available_actions, self.device_) if self.discrete else None
+        ops.actor_forward(self.cfg, self.flat, obs, None, logp, available_actions=None if avail is None else avail.contiguous(),
+                          given_actions=action, entropy_out=ent)
+        if active_masks is not None and self._use_policy_active_masks:
+            am = check(active_masks, self.device_).reshape(B)
+            dist_entropy = (ent * am).sum() / am.sum()
+        else:
+            dist_entropy = ent.mean()
+        return logp, dist_entropy
+
+
+class R_Critic(_FlatNet):
+    def __init__(self, args, cent_obs_space, device=torch.device("cuda")):
+        super().__init__()
+        shape = cent_obs_space.shape
+        if len(shape) == 3:
+            raise NotImplementedError("CNN base: MPE observations are vectors")
+        self._build(args, shape[0], [1], True, device)
+
+    def forward(self, cent_obs, rnn_states, masks):
+        """-> (values [B, 1], rnn_states)   r_actor_critic.py:146-165"""
+        cent_obs = check(cent_obs, self.device_)
+        values = torch.empty(cent_obs.shape[0], 1, dtype=torch.float32, device=self.device_)
+        self.forward_into(cent_obs, values)
+        return values, check(rnn_states, self.device_)
+
+    def forward_into(self, cent_obs, values_out, group=1):
+        if self._recurrent:
+            raise NotImplementedError("recurrent (GRU) critic is not built yet")
+        ops.critic_forward(self.cfg, self.flat, cent_obs, values_out, group=group)

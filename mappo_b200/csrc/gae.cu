@@ -155,6 +155,29 @@ moments_kernel(const float* __restrict__ x, long long count, double* __restrict_
   }
 }
 
+// r_mappo.py:174-177 from the buffer contents, with the moments over active entries
+__global__ void __launch_bounds__(kRedThreads)
+advantages_kernel(const float* __restrict__ returns, const float* __restrict__ value_preds,
+                  const float* __restrict__ active, const float* __restrict__ vn_stats, long long count,
+                  float* __restrict__ adv_raw, double* __restrict__ partials) {
+  float mean = 0.f, sd = 1.f;
+  if (vn_stats) vn_mean_std(vn_stats, mean, sd);
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float v = value_preds[i];
+    const float dn = vn_stats ? (v * sd + mean) : v;
+    const float adv = returns[i] - dn;
+    adv_raw[i] = adv;
+    if (!active || active[i] != 0.0f) { a += (double)adv; b += (double)adv * (double)adv; c += 1.0; }
+  }
+  block_sum3(a, b, c);
+  if (threadIdx.x == 0) {
+    partials[(size_t)blockIdx.x * 3 + 0] = a; partials[(size_t)blockIdx.x * 3 + 1] = b;
+    partials[(size_t)blockIdx.x * 3 + 2] = c;
+  }
+}
+
 // ValueNorm.update (valuenorm.py:38-54), per_element_update=False: weight = beta
 __global__ void valuenorm_apply_kernel(float* st, const double* __restrict__ stats3, float w, float omw) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
@@ -224,6 +247,16 @@ extern "C" int mappo_moments(const float* x, long long count, double* partials, 
   MAPPO_REQUIRE(x && partials && count > 0, "moments: bad arguments");
   moments_kernel<<<mappo_moments_num_partials(count), kRedThreads, 0, (cudaStream_t)stream>>>(x, count, partials);
   MAPPO_CHECK_LAUNCH("moments_kernel");
+  return 0;
+}
+
+extern "C" int mappo_advantages(const float* returns, const float* value_preds, const float* active_masks,
+                                const float* vn_stats, long long count, float* advantages_raw, double* partials,
+                                void* stream) {
+  MAPPO_REQUIRE(returns && value_preds && advantages_raw && partials && count > 0, "advantages: bad arguments");
+  advantages_kernel<<<mappo_moments_num_partials(count), kRedThreads, 0, (cudaStream_t)stream>>>(
+      returns, value_preds, active_masks, vn_stats, count, advantages_raw, partials);
+  MAPPO_CHECK_LAUNCH("advantages_kernel");
   return 0;
 }
 

@@ -1,0 +1,654 @@
+// Fused MLP actor / critic kernels (fp32 FMA path): one persistent CTA per SM walks tiles of BM rows.
+//   rollout : LayerNorm(obs) -> fc1 -> act -> LN -> fc2 -> act -> LN -> head -> {sample, log-prob | value}
+//   update  : the same forward, the PPO loss per row, and the whole backward, all inside the tile, so
+//             activations never touch HBM; weight gradients accumulate in registers across the CTA's tiles
+//             and leave the kernel once, as one partial row per CTA (summed in a fixed order by optim.cu).
+// Reference: mlp.py:6-59, act.py:41-162, distributions.py:14-68, r_actor_critic.py:43-107,146-165,
+//            r_mappo.py:52-136 (losses), utils/util.py:23-29 (huber/mse).
+// See net.cuh for the LayerNorm-affine folding used here.
+#include "net.cuh"
+#include "philox.cuh"
+
+namespace mappo {
+
+constexpr int kLD = 68;            // tile row stride in floats: 64 + 4 (rows 16 B aligned, banks rotate by 4)
+constexpr int kDL = 17;            // dlogits row stride
+constexpr int kMaxA = 16;          // max total action logits
+constexpr uint32_t kStreamSample = 0x53414D50u;   // 'SAMP' (oracle/policy.py STREAM_SAMPLE)
+constexpr float kLnEps = 1e-5f;
+
+struct MlpArgs {
+  NetLayout L;
+  const float* params;
+  const float* x; int ld; long long rows; const int64_t* index; int x_div;
+  int Kp;                          // in_dim rounded up to a multiple of 4
+  long long ntiles;
+  // rollout, actor
+  const float* avail; int deterministic; uint32_t k0; uint32_t step; long long row_offset;
+  float* actions_out; float* logp_out; const float* given_actions; float* entropy_out;
+  // rollout, critic
+  float* values_out; int group;
+  // update
+  const float* actions; const float* old_logp; const float* adv; const float* active;
+  const float* value_preds; const float* returns; const float* vn_stats;
+  mappo_loss_config loss;
+  float* grad_partials; double* loss_partials;
+};
+
+// ---- shared memory map (floats) --------------------------------------------------------------------
+template <int BM>
+struct Smem {
+  static constexpr int W1t = 0;                       // [64][64]  W1t[k][j] = W1[j][k] g0[k]   (k < Kp)
+  static constexpr int W2t = W1t + 64 * 64;           // [64][64]  W2t[k][j] = W2[j][k] g1[k]
+  static constexpr int W2f = W2t + 64 * 64;           // [64][64]  W2f[j][k] = W2[j][k] g1[k]
+  static constexpr int Whf = W2f + 64 * 64;           // [16][64]  Whf[a][k] = Wh[a][k] g2[k]
+  static constexpr int b1f = Whf + kMaxA * 64;        // [64]
+  static constexpr int b2f = b1f + 64;                // [64]
+  static constexpr int bhf = b2f + 64;                // [16]
+  static constexpr int T0 = bhf + kMaxA;              // [BM][kLD] n0
+  static constexpr int T1 = T0 + BM * kLD;            // [BM][kLD] n1, later dz1
+  static constexpr int T2 = T1 + BM * kLD;            // [BM][kLD] n2, later dz2
+  static constexpr int mean1 = T2 + BM * kLD;         // [BM]
+  static constexpr int rstd1 = mean1 + BM;
+  static constexpr int mean2 = rstd1 + BM;
+  static constexpr int rstd2 = mean2 + BM;
+  static constexpr int dlog = rstd2 + BM;             // [BM][kDL]
+  static constexpr int total = dlog + BM * kDL;
+  static constexpr size_t bytes = sizeof(float) * (size_t)total;
+};
+
+__device__ __forceinline__ float act_fwd(float z, int relu) { return relu ? fmaxf(z, 0.0f) : tanhf(z); }
+
+// sum over the 16 lanes that share a row (half-warp: lanes differ in tx only)
+__device__ __forceinline__ float hw_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+// acc[i][c] += sum_k A[row(i)][k] * B[k][4tx + c],  row(i) = ty + NTY*i,  k < 4*K4
+template <int RPT, int NTY>
+__device__ __forceinline__ void gemm_tile(const float* __restrict__ A, int lda, int K4, const float* __restrict__ B,
+                                          float (&acc)[RPT][4], int ty, int tx) {
+#pragma unroll 2
+  for (int k4 = 0; k4 < K4; ++k4) {
+    const float4 b0 = *reinterpret_cast<const float4*>(B + (4 * k4 + 0) * 64 + 4 * tx);
+    const float4 b1 = *reinterpret_cast<const float4*>(B + (4 * k4 + 1) * 64 + 4 * tx);
+    const float4 b2 = *reinterpret_cast<const float4*>(B + (4 * k4 + 2) * 64 + 4 * tx);
+    const float4 b3 = *reinterpret_cast<const float4*>(B + (4 * k4 + 3) * 64 + 4 * tx);
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const float4 a = *reinterpret_cast<const float4*>(A + (ty + NTY * i) * lda + 4 * k4);
+      acc[i][0] = fmaf(a.x, b0.x, acc[i][0]); acc[i][1] = fmaf(a.x, b0.y, acc[i][1]);
+      acc[i][2] = fmaf(a.x, b0.z, acc[i][2]); acc[i][3] = fmaf(a.x, b0.w, acc[i][3]);
+      acc[i][0] = fmaf(a.y, b1.x, acc[i][0]); acc[i][1] = fmaf(a.y, b1.y, acc[i][1]);
+      acc[i][2] = fmaf(a.y, b1.z, acc[i][2]); acc[i][3] = fmaf(a.y, b1.w, acc[i][3]);
+      acc[i][0] = fmaf(a.z, b2.x, acc[i][0]); acc[i][1] = fmaf(a.z, b2.y, acc[i][1]);
+      acc[i][2] = fmaf(a.z, b2.z, acc[i][2]); acc[i][3] = fmaf(a.z, b2.w, acc[i][3]);
+      acc[i][0] = fmaf(a.w, b3.x, acc[i][0]); acc[i][1] = fmaf(a.w, b3.y, acc[i][1]);
+      acc[i][2] = fmaf(a.w, b3.z, acc[i][2]); acc[i][3] = fmaf(a.w, b3.w, acc[i][3]);
+    }
+  }
+}
+
+// z = acc + bias -> t = act(z) -> n = LayerNorm(t) (no affine); writes n to dst and (mean, rstd) per row.
+template <int RPT, int NTY>
+__device__ __forceinline__ void act_ln_store(float (&acc)[RPT][4], const float* __restrict__ bias, int relu,
+                                             float* __restrict__ dst, float* __restrict__ mean_out,
+                                             float* __restrict__ rstd_out, int ty, int tx) {
+  const float4 b = *reinterpret_cast<const float4*>(bias + 4 * tx);
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    const int r = ty + NTY * i;
+    float t0 = act_fwd(acc[i][0] + b.x, relu), t1 = act_fwd(acc[i][1] + b.y, relu);
+    float t2 = act_fwd(acc[i][2] + b.z, relu), t3 = act_fwd(acc[i][3] + b.w, relu);
+    const float mean = hw_sum((t0 + t1) + (t2 + t3)) * (1.0f / 64.0f);
+    t0 -= mean; t1 -= mean; t2 -= mean; t3 -= mean;
+    const float var = hw_sum((t0 * t0 + t1 * t1) + (t2 * t2 + t3 * t3)) * (1.0f / 64.0f);
+    const float rstd = 1.0f / sqrtf(var + kLnEps);
+    *reinterpret_cast<float4*>(dst + r * kLD + 4 * tx) = make_float4(t0 * rstd, t1 * rstd, t2 * rstd, t3 * rstd);
+    if (tx == 0) { mean_out[r] = mean; rstd_out[r] = rstd; }
+  }
+}
+
+// dn (in acc) -> dz, through LayerNorm (no affine) and the activation; overwrites the n tile with dz.
+// Caller guarantees nobody else still reads `tile` (sync before) and syncs after.
+template <int RPT, int NTY>
+__device__ __forceinline__ void ln_act_bwd_store(float (&acc)[RPT][4], int relu, float* __restrict__ tile,
+                                                 const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                                                 int ty, int tx) {
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    const int r = ty + NTY * i;
+    const float4 n = *reinterpret_cast<const float4*>(tile + r * kLD + 4 * tx);
+    const float s1 = hw_sum((acc[i][0] + acc[i][1]) + (acc[i][2] + acc[i][3])) * (1.0f / 64.0f);
+    const float s2 = hw_sum((acc[i][0] * n.x + acc[i][1] * n.y) + (acc[i][2] * n.z + acc[i][3] * n.w)) * (1.0f / 64.0f);
+    const float mean = mean_in[r], rstd = rstd_in[r];
+    const float sd = 1.0f / rstd;
+    // activation derivative from the activation output t = n*sd + mean.  ReLU needs "t == 0" exactly: the
+    // forward wrote n = (t - mean) * rstd, so t == 0 <=> n == (0 - mean) * rstd bit for bit.
+    const float nz = (0.0f - mean) * rstd;
+    float4 da;
+    if (relu) {
+      da.x = n.x != nz ? 1.0f : 0.0f; da.y = n.y != nz ? 1.0f : 0.0f;
+      da.z = n.z != nz ? 1.0f : 0.0f; da.w = n.w != nz ? 1.0f : 0.0f;
+    } else {
+      const float t0 = fmaf(n.x, sd, mean), t1 = fmaf(n.y, sd, mean), t2 = fmaf(n.z, sd, mean), t3 = fmaf(n.w, sd, mean);
+      da.x = 1.0f - t0 * t0; da.y = 1.0f - t1 * t1; da.z = 1.0f - t2 * t2; da.w = 1.0f - t3 * t3;
+    }
+    float4 dz;
+    dz.x = rstd * (acc[i][0] - s1 - n.x * s2) * da.x;
+    dz.y = rstd * (acc[i][1] - s1 - n.y * s2) * da.y;
+    dz.z = rstd * (acc[i][2] - s1 - n.z * s2) * da.z;
+    dz.w = rstd * (acc[i][3] - s1 - n.w * s2) * da.w;
+    *reinterpret_cast<float4*>(tile + r * kLD + 4 * tx) = dz;
+  }
+}
+
+// G[jj][c] += sum_r dz[r][j0 + jj] * n[r][4 tk + c];  db[jj] += sum_r dz[r][j0 + jj] (kept by tk == 0)
+template <int BM, int JT>
+__device__ __forceinline__ void wgrad_tile(const float* __restrict__ dz, const float* __restrict__ n,
+                                           float (&G)[JT][4], float (&db)[JT], int j0, int tk, bool k_active) {
+  if (!k_active) return;
+#pragma unroll 4
+  for (int r = 0; r < BM; ++r) {
+    const float4 nv = *reinterpret_cast<const float4*>(n + r * kLD + 4 * tk);
+    float d[JT];
+#pragma unroll
+    for (int q = 0; q < JT / 4; ++q) {
+      const float4 v = *reinterpret_cast<const float4*>(dz + r * kLD + j0 + 4 * q);
+      d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
+    }
+#pragma unroll
+    for (int jj = 0; jj < JT; ++jj) {
+      G[jj][0] = fmaf(d[jj], nv.x, G[jj][0]); G[jj][1] = fmaf(d[jj], nv.y, G[jj][1]);
+      G[jj][2] = fmaf(d[jj], nv.z, G[jj][2]); G[jj][3] = fmaf(d[jj], nv.w, G[jj][3]);
+      if (tk == 0) db[jj] += d[jj];
+    }
+  }
+}
+
+// ---- prologue: fold the LayerNorm affines into the following Linear and stage weights in shared memory
+template <int BM, bool UPDATE>
+__device__ __forceinline__ void stage_weights(float* sm, const MlpArgs& a) {
+  using S = Smem<BM>;
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  const int D = L.in_dim, Kp = a.Kp, nt = blockDim.x, tid = threadIdx.x;
+  for (int e = tid; e < 64 * 64; e += nt) {
+    const int j = e & 63, k = e >> 6;
+    float v = 0.0f;
+    if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+    if (k < Kp) sm[S::W1t + k * 64 + j] = v;
+    const float w2 = P[L.w2 + j * 64 + k] * P[L.g1 + k];
+    sm[S::W2t + k * 64 + j] = w2;
+    if (UPDATE) sm[S::W2f + j * 64 + k] = w2;
+  }
+  for (int e = tid; e < kMaxA * 64; e += nt) {
+    const int aidx = e >> 6, k = e & 63;
+    float v = 0.0f;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    if (h < L.n_heads) v = P[L.wh[h] + (aidx - off) * 64 + k] * P[L.g2 + k];
+    sm[S::Whf + aidx * 64 + k] = v;
+  }
+  if (tid < 64) {
+    const int j = tid;
+    float s1 = P[L.b1 + j];
+    if (L.use_fn) for (int k = 0; k < D; ++k) s1 = fmaf(P[L.w1 + j * D + k], P[L.fn_b + k], s1);
+    sm[S::b1f + j] = s1;
+    float s2 = P[L.b2 + j];
+    for (int k = 0; k < 64; ++k) s2 = fmaf(P[L.w2 + j * 64 + k], P[L.be1 + k], s2);
+    sm[S::b2f + j] = s2;
+  } else if (tid < 64 + kMaxA) {
+    const int aidx = tid - 64;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    float s = 0.0f;
+    if (h < L.n_heads) {
+      s = P[L.bh[h] + (aidx - off)];
+      for (int k = 0; k < 64; ++k) s = fmaf(P[L.wh[h] + (aidx - off) * 64 + k], P[L.be2 + k], s);
+    }
+    sm[S::bhf + aidx] = s;
+  }
+}
+
+// ---- tile input: gather rows, LayerNorm over the in_dim features (mlp.py:44-45,56-57), zero padding to Kp
+template <int BM>
+__device__ __forceinline__ void load_input_tile(float* __restrict__ T0, const MlpArgs& a, long long tile) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int D = a.L.in_dim, Kp = a.Kp;
+  for (int r = warp; r < BM; r += nw) {
+    const long long g = tile * BM + r;
+    float v0 = 0.0f, v1 = 0.0f;
+    if (g < a.rows) {
+      const long long src = a.index ? a.index[g] / a.x_div : g;
+      const float* __restrict__ row = a.x + src * (long long)a.ld;
+      if (lane < D) v0 = row[lane];
+      if (lane + 32 < D) v1 = row[lane + 32];
+    }
+    if (a.L.use_fn) {
+      float s = v0 + v1;
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      const float mean = s / (float)D;
+      const float d0 = lane < D ? v0 - mean : 0.0f, d1 = lane + 32 < D ? v1 - mean : 0.0f;
+      float q = d0 * d0 + d1 * d1;
+      for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      const float rstd = 1.0f / sqrtf(q / (float)D + kLnEps);
+      v0 = d0 * rstd; v1 = d1 * rstd;
+    }
+    if (lane < Kp) T0[r * kLD + lane] = v0;
+    if (lane + 32 < Kp) T0[r * kLD + lane + 32] = v1;
+  }
+}
+
+// logits of one row from the n2 tile: l[a] = bhf[a] + sum_k n2[r][k] Whf[a][k]
+__device__ __forceinline__ void row_logits(const float* __restrict__ n2row, const float* __restrict__ Whf,
+                                           const float* __restrict__ bhf, int A, float* l) {
+  for (int q = 0; q < A; ++q) l[q] = bhf[q];
+#pragma unroll 4
+  for (int k4 = 0; k4 < 16; ++k4) {
+    const float4 n = *reinterpret_cast<const float4*>(n2row + 4 * k4);
+    for (int q = 0; q < A; ++q) {
+      const float4 w = *reinterpret_cast<const float4*>(Whf + q * 64 + 4 * k4);
+      l[q] = fmaf(n.x, w.x, fmaf(n.y, w.y, fmaf(n.z, w.z, fmaf(n.w, w.w, l[q]))));
+    }
+  }
+}
+
+// log-softmax over l[0..n): returns logsumexp, writes logp in place
+__device__ __forceinline__ void log_softmax(float* l, int n) {
+  float m = l[0];
+  for (int q = 1; q < n; ++q) m = fmaxf(m, l[q]);
+  float s = 0.0f;
+  for (int q = 0; q < n; ++q) s += expf(l[q] - m);
+  const float lse = m + logf(s);
+  for (int q = 0; q < n; ++q) l[q] -= lse;
+}
+
+// Rollout: sample / mode + log-prob for each head (act.py:41-81, distributions.py:14-28)
+__device__ __forceinline__ void actor_rollout_row(const MlpArgs& a, long long g, float* l) {
+  const NetLayout& L = a.L;
+  int off = 0;
+  float ent_sum = 0.0f;
+  for (int h = 0; h < L.n_heads; ++h) {
+    const int n = L.head_dim[h];
+    float* lh = l + off;
+    if (a.avail && h == 0)
+      for (int q = 0; q < n; ++q) if (a.avail[g * n + q] == 0.0f) lh[q] = -1e10f;     // distributions.py:66-67
+    log_softmax(lh, n);
+    int pick = 0;
+    if (a.given_actions) {
+      pick = (int)a.given_actions[g * L.n_heads + h];
+      float ent = 0.0f;
+      for (int q = 0; q < n; ++q) ent -= expf(lh[q]) * lh[q];
+      ent_sum += ent;
+    } else if (a.deterministic) {
+      float best = lh[0];
+      for (int q = 1; q < n; ++q) if (lh[q] > best) { best = lh[q]; pick = q; }
+    } else {
+      const u32x4 rnd = philox4x32_10((uint32_t)(a.row_offset + g), a.step, (uint32_t)h, 0u, a.k0, kStreamSample);
+      const float u = u32_to_unit_f32(rnd.x);
+      float cum = 0.0f;
+      pick = n - 1;
+      for (int q = 0; q < n; ++q) { cum += expf(lh[q]); if (u < cum) { pick = q; break; } }
+    }
+    if (a.actions_out) a.actions_out[g * L.n_heads + h] = (float)pick;
+    a.logp_out[g * L.n_heads + h] = lh[pick];
+    off += n;
+  }
+  if (a.entropy_out) a.entropy_out[g] = ent_sum / (float)L.n_heads;
+}
+
+// Update, actor: PPO clipped surrogate + entropy for one row; writes dlogits (unnormalised) and loss sums.
+// r_mappo.py:115-141, act.py:107-162.
+__device__ __forceinline__ void actor_loss_row(const MlpArgs& a, long long src, float* l, float* __restrict__ dl,
+                                               double* acc4) {
+  const NetLayout& L = a.L;
+  const float active = (a.loss.use_policy_active_masks && a.active) ? a.active[src] : 1.0f;
+  const float adv = a.adv[src];
+  const float lo = 1.0f - a.loss.clip_param, hi = 1.0f + a.loss.clip_param;
+  const float ecoef = a.loss.entropy_coef / (float)L.n_heads;
+  int off = 0;
+  float obj_sum = 0.0f, ent_sum = 0.0f, ratio_sum = 0.0f;
+  for (int h = 0; h < L.n_heads; ++h) {
+    const int n = L.head_dim[h];
+    float* lh = l + off;
+    if (a.avail && h == 0)
+      for (int q = 0; q < n; ++q) if (a.avail[src * n + q] == 0.0f) lh[q] = -1e10f;
+    log_softmax(lh, n);
+    const int act = (int)a.actions[src * L.n_heads + h];
+    const float ratio = expf(lh[act] - a.old_logp[src * L.n_heads + h]);
+    const float s1 = ratio * adv, s2 = fminf(fmaxf(ratio, lo), hi) * adv;
+    obj_sum += fminf(s1, s2);
+    ratio_sum += ratio;
+    float ent = 0.0f;
+    for (int q = 0; q < n; ++q) ent -= expf(lh[q]) * lh[q];
+    ent_sum += ent;
+    // d(-obj)/dlogp_act: torch.min ties split evenly and clamp passes the gradient on its closed range
+    const bool inside = (ratio >= lo) && (ratio <= hi);
+    const float gcoef = (inside || s1 < s2) ? ratio * adv : 0.0f;
+    for (int q = 0; q < n; ++q) {
+      const float p = expf(lh[q]);
+      const float d_obj = -gcoef * ((q == act ? 1.0f : 0.0f) - p);
+      const float d_ent = ecoef * p * (lh[q] + ent);        // d(-c H)/dl = c p (logp + H)
+      dl[off + q] = active * (d_obj + d_ent);
+    }
+    off += n;
+  }
+  for (int q = off; q < kMaxA; ++q) dl[q] = 0.0f;
+  acc4[0] += (double)(-obj_sum * active);
+  acc4[1] += (double)(ent_sum / (float)L.n_heads * active);
+  acc4[2] += (double)ratio_sum;
+  acc4[3] += (double)active;
+}
+
+__device__ __forceinline__ float huber(float e, float d) { return fabsf(e) <= d ? 0.5f * e * e : d * (fabsf(e) - 0.5f * d); }
+__device__ __forceinline__ float huber_d(float e, float d) { return fabsf(e) <= d ? e : (e > 0.0f ? d : -d); }
+
+// Update, critic: value loss of the `group` terms that share this row's value (r_mappo.py:52-89).
+__device__ __forceinline__ float critic_loss_row(const MlpArgs& a, long long src, float v, double* acc4) {
+  const mappo_loss_config& c = a.loss;
+  float mean = 0.0f, sd = 1.0f;
+  if (c.use_value_norm) {                                   // ValueNorm.normalize, valuenorm.py:31-35,56-65
+    const float db = fmaxf(a.vn_stats[2], 1e-5f);
+    mean = a.vn_stats[0] / db;
+    sd = sqrtf(fmaxf(a.vn_stats[1] / db - mean * mean, 1e-2f));
+  }
+  float dv = 0.0f;
+  for (int m = 0; m < a.group; ++m) {
+    const long long o = src * a.group + m;
+    const float active = (c.use_value_active_masks && a.active) ? a.active[o] : 1.0f;
+    const float vp = a.value_preds[o];
+    const float target = c.use_value_norm ? (a.returns[o] - mean) / sd : a.returns[o];
+    const float diff = v - vp;
+    const float vclip = vp + fminf(fmaxf(diff, -c.clip_param), c.clip_param);
+    const float e_c = target - vclip, e_o = target - v;
+    const float l_c = c.use_huber_loss ? huber(e_c, c.huber_delta) : 0.5f * e_c * e_c;
+    const float l_o = c.use_huber_loss ? huber(e_o, c.huber_delta) : 0.5f * e_o * e_o;
+    const float g_o = -(c.use_huber_loss ? huber_d(e_o, c.huber_delta) : e_o);
+    const bool in_clip = (diff >= -c.clip_param) && (diff <= c.clip_param);
+    const float g_c = in_clip ? -(c.use_huber_loss ? huber_d(e_c, c.huber_delta) : e_c) : 0.0f;
+    float loss, g;
+    if (!c.use_clipped_value_loss) { loss = l_o; g = g_o; }
+    else if (l_o > l_c) { loss = l_o; g = g_o; }
+    else if (l_o < l_c) { loss = l_c; g = g_c; }
+    else { loss = l_o; g = 0.5f * (g_o + g_c); }            // torch.max ties split evenly
+    dv += active * g * c.value_loss_coef;
+    acc4[0] += (double)(loss * active);
+    acc4[1] += (double)active;
+  }
+  return dv;
+}
+
+// ---- the kernel ------------------------------------------------------------------------------------
+// BM rows per tile, NT threads.  Thread (ty, tx): tx = tid % 16 owns 4 output columns, ty = tid / 16 owns rows
+// ty + NTY*i.  MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic.
+template <int BM, int NT, int MODE>
+__global__ void __launch_bounds__(NT, 1) mlp_kernel(const MlpArgs a) {
+  constexpr bool UPDATE = (MODE >= 2);
+  constexpr bool CRITIC = (MODE == 1 || MODE == 3);
+  constexpr int NTY = NT / 16, RPT = BM / NTY, JT = 64 / NTY, NQ = (kMaxA * 64 + NT - 1) / NT;
+  static_assert(RPT * NTY == BM && JT * NTY == 64 && JT % 4 == 0, "tile shape");
+  using S = Smem<BM>;
+  extern __shared__ __align__(16) float sm[];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const NetLayout& L = a.L;
+  const int A = L.a_total, relu = L.use_relu, K4 = a.Kp >> 2;
+
+  stage_weights<BM, UPDATE>(sm, a);
+
+  // persistent gradient accumulators (UPDATE): this thread's 4(j) x 4(k) (or 8 x 4) blocks of G1, G2, its head
+  // outputs o = tid + NT*q of G_h[a][k], and the bias sums (kept by tk == 0 / k == 0 threads).
+  float G1[JT][4], G2[JT][4], db1[JT], db2[JT], gh[NQ], dbh[NQ];
+  double lacc[4] = {0.0, 0.0, 0.0, 0.0};
+  if (UPDATE) {
+#pragma unroll
+    for (int j = 0; j < JT; ++j) {
+      db1[j] = db2[j] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) G1[j][c] = G2[j][c] = 0.0f;
+    }
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) gh[q] = dbh[q] = 0.0f;
+  }
+  const int j0 = ty * JT, tk = tx;                       // wgrad block of this thread
+  const bool k1_active = (4 * tk < a.Kp);
+
+  for (long long tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+    __syncthreads();                                     // previous tile's readers of T0/T1/T2 are done (and weights staged)
+    load_input_tile<BM>(sm + S::T0, a, tile);
+    __syncthreads();
+    float acc[RPT][4];
+    // fc1
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    gemm_tile<RPT, NTY>(sm + S::T0, kLD, K4, sm + S::W1t, acc, ty, tx);
+    act_ln_store<RPT, NTY>(acc, sm + S::b1f, relu, sm + S::T1, sm + S::mean1, sm + S::rstd1, ty, tx);
+    __syncthreads();
+    // fc2
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    gemm_tile<RPT, NTY>(sm + S::T1, kLD, 16, sm + S::W2t, acc, ty, tx);
+    act_ln_store<RPT, NTY>(acc, sm + S::b2f, relu, sm + S::T2, sm + S::mean2, sm + S::rstd2, ty, tx);
+    __syncthreads();
+    // head + per-row loss / sampling: one thread per row
+    if (tid < BM) {
+      const long long g = tile * BM + tid;
+      float l[kMaxA];
+      if (g < a.rows) {
+        row_logits(sm + S::T2 + tid * kLD, sm + S::Whf, sm + S::bhf, A, l);
+        const long long src = a.index ? a.index[g] : g;
+        if (MODE == 0) actor_rollout_row(a, g, l);
+        if (MODE == 1) for (int m = 0; m < a.group; ++m) a.values_out[g * a.group + m] = l[0];
+        if (MODE == 2) actor_loss_row(a, src, l, sm + S::dlog + tid * kDL, lacc);
+        if (MODE == 3) {
+          const float dv = critic_loss_row(a, src, l[0], lacc);
+          float* dl = sm + S::dlog + tid * kDL;
+          dl[0] = dv;
+          for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+        }
+      } else if (UPDATE) {
+        float* dl = sm + S::dlog + tid * kDL;
+        for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+      }
+    }
+    if (!UPDATE) continue;
+    __syncthreads();
+    // head weight gradient: G_h[a][k] += sum_r dlog[r][a] n2[r][k]; output o = a*64 + k
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const int o = tid + NT * q;
+      if (o < A * 64) {
+        const int aa = o >> 6, k = o & 63;
+        float s = 0.0f, sb = 0.0f;
+        for (int r = 0; r < BM; ++r) {
+          const float d = sm[S::dlog + r * kDL + aa];
+          s = fmaf(d, sm[S::T2 + r * kLD + k], s);
+          sb += d;
+        }
+        gh[q] += s;
+        if (k == 0) dbh[q] += sb;
+      }
+    }
+    // dn2 = dlog . Whf
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    for (int aa = 0; aa < A; ++aa) {
+      const float4 w = *reinterpret_cast<const float4*>(sm + S::Whf + aa * 64 + 4 * tx);
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        const float d = sm[S::dlog + (ty + NTY * i) * kDL + aa];
+        acc[i][0] = fmaf(d, w.x, acc[i][0]); acc[i][1] = fmaf(d, w.y, acc[i][1]);
+        acc[i][2] = fmaf(d, w.z, acc[i][2]); acc[i][3] = fmaf(d, w.w, acc[i][3]);
+      }
+    }
+    __syncthreads();                                     // head wgrad finished reading n2
+    ln_act_bwd_store<RPT, NTY>(acc, relu, sm + S::T2, sm + S::mean2, sm + S::rstd2, ty, tx);   // T2 := dz2
+    __syncthreads();
+    // fc2 weight gradient and dgrad
+    wgrad_tile<BM, JT>(sm + S::T2, sm + S::T1, G2, db2, j0, tk, true);
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    gemm_tile<RPT, NTY>(sm + S::T2, kLD, 16, sm + S::W2f, acc, ty, tx);                      // dn1 = dz2 . W2'
+    __syncthreads();                                     // wgrad2 finished reading n1
+    ln_act_bwd_store<RPT, NTY>(acc, relu, sm + S::T1, sm + S::mean1, sm + S::rstd1, ty, tx);   // T1 := dz1
+    __syncthreads();
+    // fc1 weight gradient (no dgrad into the observations)
+    wgrad_tile<BM, JT>(sm + S::T1, sm + S::T0, G1, db1, j0, tk, k1_active);
+  }
+
+  if (!UPDATE) return;
+  // ---- epilogue: one partial row per CTA, in the flat parameter layout (G in the W slots, db in the b slots)
+  float* __restrict__ gp = a.grad_partials + (size_t)blockIdx.x * L.total;
+  for (int e = tid; e < L.total; e += NT) gp[e] = 0.0f;   // LayerNorm-affine slots stay zero (filled by optim.cu)
+  __syncthreads();
+  const int D = L.in_dim;
+#pragma unroll
+  for (int jj = 0; jj < JT; ++jj) {
+    const int j = j0 + jj;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int k = 4 * tk + c;
+      if (k < D) gp[L.w1 + j * D + k] = G1[jj][c];
+      gp[L.w2 + j * 64 + k] = G2[jj][c];
+    }
+    if (tk == 0) { gp[L.b1 + j] = db1[jj]; gp[L.b2 + j] = db2[jj]; }
+  }
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const int o = tid + NT * q;
+    if (o < A * 64) {
+      const int aa = o >> 6, k = o & 63;
+      int h = 0, off = 0;
+      while (aa >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+      gp[L.wh[h] + (aa - off) * 64 + k] = gh[q];
+      if (k == 0) gp[L.bh[h] + (aa - off)] = dbh[q];
+    }
+  }
+  // loss sums: block reduction in double
+  __shared__ double red[4][32];
+  for (int q = 0; q < 4; ++q) {
+    double v = lacc[q];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) red[q][tid >> 5] = v;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double v = 0.0;
+    for (int w = 0; w < NT / 32; ++w) v += red[tid][w];
+    a.loss_partials[(size_t)blockIdx.x * 4 + tid] = v;
+  }
+  (void)CRITIC;
+}
+
+// ---- host side -------------------------------------------------------------------------------------
+constexpr int kBM = 128, kNT = 256;
+
+static int device_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+static int blocks_for(long long rows) {
+  const long long ntiles = (rows + kBM - 1) / kBM;
+  const int sms = device_sm_count();
+  return (int)(ntiles < sms ? (ntiles < 1 ? 1 : ntiles) : sms);
+}
+
+template <int MODE>
+static int launch_mlp(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
+  if (int rc = check_net(cfg, who)) return rc;
+  if (cfg->recurrent) MAPPO_UNSUPPORTED("%s: recurrent (GRU) networks are not built yet", who);
+  if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d not built yet", who, cfg->in_dim, kMaxIn);
+  MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim, "%s: bad input arguments", who);
+  a.L = make_layout(*cfg);
+  if (a.x_div < 1) a.x_div = 1;
+  a.Kp = (cfg->in_dim + 3) & ~3;
+  a.ntiles = (a.rows + kBM - 1) / kBM;
+  const int grid = blocks_for(a.rows);
+  auto kern = mlp_kernel<kBM, kNT, MODE>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Smem<kBM>::bytes));
+    attr_set = true;
+  }
+  kern<<<grid, kNT, Smem<kBM>::bytes, stream>>>(a);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+}  // namespace mappo
+
+using namespace mappo;
+
+extern "C" long long mappo_net_param_count(const mappo_net_config* cfg) {
+  if (!cfg) return -1;
+  return make_layout(*cfg).total;
+}
+
+extern "C" int mappo_update_num_blocks(long long rows) { return blocks_for(rows); }
+
+extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
+                                   long long rows, const float* available_actions, int deterministic, uint64_t seed,
+                                   uint64_t step, long long row_offset, const float* given_actions,
+                                   float* actions_out, float* logp_out, float* entropy_out, void* stream) {
+  MAPPO_REQUIRE(logp_out && (actions_out || given_actions), "actor_forward: null outputs");
+  MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_forward: critic config");
+  MlpArgs a{};
+  a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.avail = available_actions;
+  a.deterministic = deterministic; a.k0 = (uint32_t)(seed & 0xFFFFFFFFull); a.step = (uint32_t)step;
+  a.row_offset = row_offset; a.actions_out = actions_out; a.logp_out = logp_out;
+  a.given_actions = given_actions; a.entropy_out = entropy_out;
+  return launch_mlp<0>(a, cfg, (cudaStream_t)stream, "actor_forward");
+}
+
+extern "C" int mappo_critic_forward(const mappo_net_config* cfg, const float* params, const float* share_obs,
+                                    int obs_ld, long long rows, int group, float* values_out, void* stream) {
+  MAPPO_REQUIRE(values_out && group >= 1, "critic_forward: bad outputs");
+  MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_forward: actor config");
+  MlpArgs a{};
+  a.params = params; a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.group = group; a.values_out = values_out;
+  return launch_mlp<1>(a, cfg, (cudaStream_t)stream, "critic_forward");
+}
+
+extern "C" int mappo_actor_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                                  const float* obs, int obs_ld, long long rows, const int64_t* index,
+                                  const float* actions, const float* old_logp, const float* adv,
+                                  const float* active_masks, const float* available_actions, float* grad_partials,
+                                  double* loss_partials, void* stream) {
+  MAPPO_REQUIRE(loss && actions && old_logp && adv && grad_partials && loss_partials, "actor_update: null pointer");
+  MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_update: critic config");
+  MlpArgs a{};
+  a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.index = index; a.actions = actions;
+  a.old_logp = old_logp; a.adv = adv; a.active = active_masks; a.avail = available_actions; a.loss = *loss;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials;
+  return launch_mlp<2>(a, cfg, (cudaStream_t)stream, "actor_update");
+}
+
+extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                                   const float* share_obs, int obs_ld, long long rows, int group,
+                                   const int64_t* index, int share_rows_div, const float* value_preds,
+                                   const float* returns,
+                                   const float* active_masks, const float* vn_stats, float* grad_partials,
+                                   double* loss_partials, void* stream) {
+  MAPPO_REQUIRE(loss && value_preds && returns && grad_partials && loss_partials && group >= 1,
+                "critic_update: null pointer");
+  MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_update: actor config");
+  MAPPO_REQUIRE(!(index && group != 1), "critic_update: a row gather needs group == 1");
+  MAPPO_REQUIRE(share_rows_div >= 1, "critic_update: share_rows_div");
+  MAPPO_REQUIRE(!loss->use_value_norm || vn_stats, "critic_update: use_value_norm without statistics");
+  MlpArgs a{};
+  a.params = params; a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.group = group; a.index = index;
+  a.x_div = share_rows_div;
+  a.value_preds = value_preds; a.returns = returns; a.active = active_masks; a.vn_stats = vn_stats; a.loss = *loss;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials;
+  return launch_mlp<3>(a, cfg, (cudaStream_t)stream, "critic_update");
+}

@@ -1,0 +1,141 @@
+// Gradient reduction, LayerNorm-affine chain rule, global-norm clipping and Adam.
+//   nn.utils.clip_grad_norm_(params, max_grad_norm)     onpolicy/algorithms/r_mappo/r_mappo.py:143-146,157-160
+//   torch.optim.Adam(lr, eps=opti_eps, weight_decay)    onpolicy/algorithms/r_mappo/algorithm/rMAPPOPolicy.py:31-37
+//   train_info accumulation                              r_mappo.py:187-219
+#include "net.cuh"
+
+namespace mappo {
+
+// column sums over the per-CTA partial rows, fixed order (deterministic)
+__global__ void __launch_bounds__(256)
+grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, int blocks, long long P,
+                   float* __restrict__ gsum, double* __restrict__ lsum) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e < P) {
+    float s = 0.0f;
+    for (int b = 0; b < blocks; ++b) s += gp[(size_t)b * P + e];
+    gsum[e] = s;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 4) {
+    double s = 0.0;
+    for (int b = 0; b < blocks; ++b) s += lp[(size_t)b * 4 + threadIdx.x];
+    lsum[threadIdx.x] = s;
+  }
+}
+
+constexpr int kOptThreads = 1024;
+
+// one Linear's slots: dW[j][k] = g[k] G[j][k] + be[k] db[j];  dg[k] = sum_j W[j][k] G[j][k];  dbe[k] = sum_j W[j][k] db[j]
+__device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const float* __restrict__ G, float* __restrict__ out,
+                                              int w_off, int b_off, int rows, int cols, int g_off, int be_off,
+                                              bool accumulate_affine) {
+  const int tid = threadIdx.x;
+  for (int e = tid; e < rows * cols; e += kOptThreads) {
+    const int j = e / cols, k = e - j * cols;
+    out[w_off + e] = (g_off >= 0) ? fmaf(P[g_off + k], G[w_off + e], P[be_off + k] * G[b_off + j]) : G[w_off + e];
+  }
+  for (int j = tid; j < rows; j += kOptThreads) out[b_off + j] = G[b_off + j];
+  if (g_off >= 0) {
+    for (int k = tid; k < cols; k += kOptThreads) {
+      float dg = 0.0f, dbe = 0.0f;
+      for (int j = 0; j < rows; ++j) {
+        const float w = P[w_off + j * cols + k];
+        dg = fmaf(w, G[w_off + j * cols + k], dg);
+        dbe = fmaf(w, G[b_off + j], dbe);
+      }
+      if (accumulate_affine) { out[g_off + k] += dg; out[be_off + k] += dbe; }
+      else { out[g_off + k] = dg; out[be_off + k] = dbe; }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kOptThreads)
+adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restrict__ params, float* __restrict__ m,
+                 float* __restrict__ v, const float* __restrict__ gsum, const double* __restrict__ lsum,
+                 int denom_slot, long long rows_total, int apply_update, float* __restrict__ g, float* info) {
+  const int tid = threadIdx.x;
+  const int D = L.in_dim, H = L.H;
+  // 1. chain rule through the folded affines (net.cuh)
+  unfold_linear(params, gsum, g, L.w1, L.b1, H, D, L.use_fn ? L.fn_g : -1, L.fn_b, false);
+  unfold_linear(params, gsum, g, L.w2, L.b2, H, H, L.g1, L.be1, false);
+  for (int h = 0; h < L.n_heads; ++h) {
+    unfold_linear(params, gsum, g, L.wh[h], L.bh[h], L.head_dim[h], H, L.g2, L.be2, h > 0);
+    __syncthreads();                                    // heads accumulate into the same g2/be2 slots
+  }
+  __syncthreads();
+  // 2. loss denominator, global L2 norm
+  const double denom = lsum[denom_slot];
+  const float inv = (float)(1.0 / denom);
+  double sq = 0.0;
+  for (int e = tid; e < L.total; e += kOptThreads) {
+    const float x = g[e] * inv;
+    g[e] = x;
+    sq += (double)x * (double)x;
+  }
+  __shared__ double red[32];
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_down_sync(0xffffffffu, sq, o);
+  if ((tid & 31) == 0) red[tid >> 5] = sq;
+  __syncthreads();
+  if (tid < 32) {
+    double t = red[tid];
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if (tid == 0) red[0] = t;
+  }
+  __syncthreads();
+  const float norm = (float)sqrt(red[0]);
+  float clip = 1.0f;
+  if (ad.use_max_grad_norm) clip = fminf(ad.max_grad_norm / (norm + 1e-6f), 1.0f);   // clip_grad_norm_: clamp(coef, max=1)
+  // 3. Adam (torch.optim.Adam, no amsgrad)
+  if (apply_update) {
+    const float step_size = ad.lr / ad.bias_correction1;
+    for (int e = tid; e < L.total; e += kOptThreads) {
+      float grad = g[e] * clip;
+      const float p = params[e];
+      if (ad.weight_decay != 0.0f) grad = fmaf(ad.weight_decay, p, grad);
+      const float mm = m[e] + (grad - m[e]) * (1.0f - ad.beta1);                   // exp_avg.lerp_(grad, 1 - beta1)
+      const float vv = v[e] * ad.beta2 + (1.0f - ad.beta2) * grad * grad;          // mul_(beta2).addcmul_(g, g, 1 - beta2)
+      m[e] = mm; v[e] = vv;
+      const float den = sqrtf(vv) / ad.bias_correction2_sqrt + ad.eps;
+      params[e] = p - step_size * (mm / den);
+    }
+  }
+  // 4. train_info accumulation: {loss, grad_norm, entropy, ratio}
+  if (info && tid == 0) {
+    info[0] += (float)(lsum[0] / denom);
+    info[1] += norm;
+    if (!L.is_critic) {
+      info[2] += (float)(lsum[1] / denom);
+      info[3] += (float)(lsum[2] / ((double)rows_total * (double)L.n_heads));
+    }
+  }
+}
+
+}  // namespace mappo
+
+using namespace mappo;
+
+extern "C" int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
+                                 float* grad_sum, double* loss_sum, void* stream) {
+  MAPPO_REQUIRE(grad_partials && loss_partials && grad_sum && loss_sum && blocks > 0 && P > 0, "grad_reduce: bad arguments");
+  grad_reduce_kernel<<<ceil_div(P, 256), 256, 0, (cudaStream_t)stream>>>(grad_partials, loss_partials, blocks, P,
+                                                                       grad_sum, loss_sum);
+  MAPPO_CHECK_LAUNCH("grad_reduce_kernel");
+  return 0;
+}
+
+extern "C" int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params,
+                               float* exp_avg, float* exp_avg_sq, const float* grad_sum, const double* loss_sum,
+                               int denominator_slot, long long rows_total, int apply_update, float* grad_out,
+                               float* info_out, void* stream) {
+  if (int rc = check_net(cfg, "adam_step")) return rc;
+  if (cfg->recurrent) MAPPO_UNSUPPORTED("adam_step: recurrent (GRU) networks are not built yet");
+  MAPPO_REQUIRE(adam && params && grad_sum && loss_sum && grad_out, "adam_step: null pointer (grad_out is required)");
+  MAPPO_REQUIRE(!apply_update || (exp_avg && exp_avg_sq), "adam_step: null optimiser state");
+  MAPPO_REQUIRE(denominator_slot >= 0 && denominator_slot < 4 && rows_total > 0, "adam_step: bad denominator");
+  const NetLayout L = make_layout(*cfg);
+  adam_step_kernel<<<1, kOptThreads, 0, (cudaStream_t)stream>>>(L, *adam, params, exp_avg, exp_avg_sq, grad_sum,
+                                                               loss_sum, denominator_slot, rows_total, apply_update,
+                                                               grad_out, info_out);
+  MAPPO_CHECK_LAUNCH("adam_step_kernel");
+  return 0;
+}

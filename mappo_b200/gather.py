@@ -1,0 +1,57 @@
+"""Row gather for the generator API (mappo_gather_rows)."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+_lib._EXTRA_SIGS["mappo_gather_rows"] = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_longlong,
+                                         C.c_void_p, C.c_void_p]
+
+
+def gather_rows(src, lead_dims, index):
+    """src: float32 CUDA tensor whose first `lead_dims` dims enumerate rows (row-major) and whose remaining dims
+    are a contiguous row; may be a broadcast (stride-0) view over trailing lead dims.  -> [len(index), width]."""
+    assert src.dtype == torch.float32 and src.is_cuda
+    shape, stride = src.shape, src.stride()
+    if all(st == 0 or sh == 1 for st, sh in zip(stride, shape)):          # a constant (fully broadcast) tensor
+        w = 1
+        for d in shape[lead_dims:]:
+            w *= d
+        return torch.empty(index.numel(), w, dtype=torch.float32, device=src.device).fill_(src[(0,) * src.dim()])
+    width = 1
+    for d in shape[lead_dims:]:
+        width *= d
+    tail_contig = True
+    exp = 1
+    for d in range(src.dim() - 1, lead_dims - 1, -1):
+        if shape[d] != 1 and stride[d] != exp:
+            tail_contig = False
+        exp *= shape[d]
+    row_div, row_stride, ok = 1, width, tail_contig
+    if ok:
+        # lead dims: allow "contiguous" or "trailing lead dims broadcast with stride 0"
+        div, exp_stride = 1, None
+        d = lead_dims - 1
+        while d >= 0 and (stride[d] == 0 or shape[d] == 1):
+            div *= shape[d]
+            d -= 1
+        if d < 0:
+            row_div, row_stride = 1, 0            # every row is the same row
+        else:
+            rs = stride[d]
+            e = rs
+            for dd in range(d, -1, -1):
+                if shape[dd] != 1 and stride[dd] != e:
+                    ok = False
+                e *= shape[dd]
+            row_div, row_stride = div, rs
+    if not ok:
+        src = src.contiguous()
+        row_div, row_stride = 1, width
+    index = index.to(device=src.device, dtype=torch.int64).contiguous()
+    out = torch.empty(index.numel(), width, dtype=torch.float32, device=src.device)
+    check(_lib.lib().mappo_gather_rows(C.c_void_p(src.data_ptr()), int(row_stride), int(row_div), int(width),
+                                       ptr(index), index.numel(), ptr(out), stream_ptr()), "gather_rows")
+    return out

@@ -1,0 +1,223 @@
+"""Thin Python wrappers over the C ABI (include/mappo_b200.h): argument checking and pointer plumbing only.
+Every function launches CUDA kernels on torch's current stream; none synchronises."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+
+class GaeConfig(C.Structure):
+    _fields_ = [("T", C.c_int32), ("R", C.c_int32), ("gamma", C.c_float), ("gamma_lambda", C.c_float),
+                ("use_gae", C.c_int32), ("use_proper_time_limits", C.c_int32), ("use_value_norm", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+_P = C.c_void_p
+_lib._EXTRA_SIGS.update({
+    "mappo_gae_returns": [C.POINTER(GaeConfig), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_adv_stats_reduce": [_P, C.c_int, _P, _P],
+    "mappo_adv_normalize": [_P, _P, C.c_longlong, _P, _P],
+    "mappo_moments": [_P, C.c_longlong, _P, _P],
+    "mappo_valuenorm_apply": [_P, _P, C.c_double, _P],
+    "mappo_valuenorm_transform": [_P, _P, _P, C.c_longlong, C.c_int, _P],
+})
+
+
+def _f32c(t, name):
+    assert t.dtype == torch.float32 and t.is_cuda and t.is_contiguous(), "%s must be contiguous float32 CUDA" % name
+    return t
+
+
+def gae_returns(rewards, value_preds, returns, masks, next_value, gamma, gae_lambda, use_gae=True,
+                use_proper_time_limits=False, bad_masks=None, active_masks=None, vn_stats=None,
+                advantages_raw=None, stats3=None, all_reduce=None):
+    """compute_returns + raw advantages + advantage moments.  Arrays [T(+1), ...] with any trailing shape.
+    Returns (advantages_raw [T,...], stats3 double[3] = {sum, sumsq, count})."""
+    L = _lib.lib()
+    T = rewards.shape[0]
+    R = rewards[0].numel()
+    assert value_preds.shape[0] == T + 1 and returns.shape[0] == T + 1 and masks.shape[0] == T + 1
+    dev = rewards.device
+    if advantages_raw is None:
+        advantages_raw = torch.empty_like(rewards)
+    nparts = L.mappo_gae_num_partials(R)
+    partials = torch.empty(nparts, 3, dtype=torch.float64, device=dev)
+    if stats3 is None:
+        stats3 = torch.empty(3, dtype=torch.float64, device=dev)
+    cfg = GaeConfig(T, R, float(gamma), float(gamma * gae_lambda), int(use_gae), int(use_proper_time_limits),
+                    int(vn_stats is not None), 0)
+    check(L.mappo_gae_returns(C.byref(cfg), ptr(_f32c(rewards, "rewards")), ptr(_f32c(value_preds, "value_preds")),
+                              ptr(_f32c(returns, "returns")), ptr(_f32c(masks, "masks")),
+                              ptr(bad_masks), ptr(active_masks), ptr(next_value), ptr(vn_stats),
+                              ptr(advantages_raw), ptr(partials), stream_ptr()), "gae_returns")
+    check(L.mappo_adv_stats_reduce(ptr(partials), nparts, ptr(stats3), stream_ptr()), "adv_stats_reduce")
+    if all_reduce is not None:
+        all_reduce(stats3)
+    return advantages_raw, stats3
+
+
+def adv_normalize(advantages_raw, stats3, out=None):
+    if out is None:
+        out = torch.empty_like(advantages_raw)
+    check(_lib.lib().mappo_adv_normalize(ptr(advantages_raw), ptr(out), advantages_raw.numel(), ptr(stats3),
+                                         stream_ptr()), "adv_normalize")
+    return out
+
+
+def moments(x, stats3=None, all_reduce=None):
+    """double[3] = {sum x, sum x^2 (x^2 rounded to f32 first), n} over a contiguous float32 tensor."""
+    L = _lib.lib()
+    n = x.numel()
+    nparts = L.mappo_moments_num_partials(n)
+    partials = torch.empty(nparts, 3, dtype=torch.float64, device=x.device)
+    if stats3 is None:
+        stats3 = torch.empty(3, dtype=torch.float64, device=x.device)
+    check(L.mappo_moments(ptr(_f32c(x, "x")), n, ptr(partials), stream_ptr()), "moments")
+    check(L.mappo_adv_stats_reduce(ptr(partials), nparts, ptr(stats3), stream_ptr()), "stats_reduce")
+    if all_reduce is not None:
+        all_reduce(stats3)
+    return stats3
+
+
+def valuenorm_apply(vn_stats, stats3, beta):
+    check(_lib.lib().mappo_valuenorm_apply(ptr(vn_stats), ptr(stats3), float(beta), stream_ptr()), "valuenorm_apply")
+
+
+def valuenorm_transform(vn_stats, x, denormalize, out=None):
+    if out is None:
+        out = torch.empty_like(x)
+    check(_lib.lib().mappo_valuenorm_transform(ptr(vn_stats), ptr(_f32c(x, "x")), ptr(out), x.numel(),
+                                               int(denormalize), stream_ptr()), "valuenorm_transform")
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# networks
+class NetConfig(C.Structure):
+    _fields_ = [("in_dim", C.c_int32), ("hidden", C.c_int32), ("layer_N", C.c_int32), ("use_relu", C.c_int32),
+                ("use_feature_norm", C.c_int32), ("recurrent", C.c_int32), ("n_heads", C.c_int32),
+                ("head_dim", C.c_int32 * 4), ("is_critic", C.c_int32)]
+
+
+class LossConfig(C.Structure):
+    _fields_ = [("clip_param", C.c_float), ("entropy_coef", C.c_float), ("value_loss_coef", C.c_float),
+                ("huber_delta", C.c_float), ("use_huber_loss", C.c_int32), ("use_clipped_value_loss", C.c_int32),
+                ("use_value_norm", C.c_int32), ("use_policy_active_masks", C.c_int32),
+                ("use_value_active_masks", C.c_int32), ("reserved", C.c_int32)]
+
+
+class AdamConfig(C.Structure):
+    _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+                ("weight_decay", C.c_float), ("max_grad_norm", C.c_float), ("use_max_grad_norm", C.c_int32),
+                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("loss_scale", C.c_float)]
+
+
+_NC, _LC, _AC = C.POINTER(NetConfig), C.POINTER(LossConfig), C.POINTER(AdamConfig)
+_lib._EXTRA_SIGS.update({
+    "mappo_actor_forward": [_NC, _P, _P, C.c_int, C.c_longlong, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_longlong,
+                            _P, _P, _P, _P, _P],
+    "mappo_advantages": [_P, _P, _P, _P, C.c_longlong, _P, _P, _P],
+    "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P],
+    "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_grad_reduce": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
+    "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
+})
+
+
+def net_config(in_dim, hidden, layer_N, use_relu, use_feature_norm, recurrent, head_dims, is_critic):
+    hd = (C.c_int32 * 4)(*(list(head_dims) + [0] * (4 - len(head_dims))))
+    return NetConfig(int(in_dim), int(hidden), int(layer_N), int(bool(use_relu)), int(bool(use_feature_norm)),
+                     int(bool(recurrent)), len(head_dims), hd, int(bool(is_critic)))
+
+
+def net_param_count(cfg):
+    L = _lib.lib()
+    L.mappo_net_param_count.restype = C.c_longlong
+    L.mappo_net_param_count.argtypes = [_NC]
+    n = L.mappo_net_param_count(C.byref(cfg))
+    assert n > 0
+    return int(n)
+
+
+def _rows_view(x):
+    """2-D float32 CUDA view [rows, width] with unit inner stride -> (tensor, row stride in floats)."""
+    assert x.dtype == torch.float32 and x.is_cuda and x.dim() == 2 and x.stride(1) == 1, \
+        "expected a float32 CUDA matrix with contiguous rows"
+    return x, int(x.stride(0))
+
+
+def _vp(t):
+    """pointer of a possibly strided view (base pointer of its first element); None -> NULL"""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def actor_forward(cfg, params, obs, actions_out, logp_out, available_actions=None, deterministic=False, seed=0,
+                  step=0, row_offset=0, given_actions=None, entropy_out=None):
+    obs, ld = _rows_view(obs)
+    check(_lib.lib().mappo_actor_forward(C.byref(cfg), ptr(params), _vp(obs), ld, obs.shape[0],
+                                         ptr(available_actions), int(deterministic), int(seed) & (2 ** 64 - 1),
+                                         int(step), int(row_offset), ptr(given_actions), ptr(actions_out),
+                                         ptr(logp_out), ptr(entropy_out), stream_ptr()), "actor_forward")
+
+
+def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=None, all_reduce=None):
+    """returns/value_preds: the [T, ...] slices (contiguous).  -> (advantages_raw, stats3)"""
+    L = _lib.lib()
+    n = returns.numel()
+    if out is None:
+        out = torch.empty_like(returns)
+    nparts = L.mappo_moments_num_partials(n)
+    partials = torch.empty(nparts, 3, dtype=torch.float64, device=returns.device)
+    if stats3 is None:
+        stats3 = torch.empty(3, dtype=torch.float64, device=returns.device)
+    check(L.mappo_advantages(ptr(_f32c(returns, "returns")), ptr(_f32c(value_preds, "value_preds")), ptr(active_masks),
+                             ptr(vn_stats), n, ptr(out), ptr(partials), stream_ptr()), "advantages")
+    check(L.mappo_adv_stats_reduce(ptr(partials), nparts, ptr(stats3), stream_ptr()), "adv_stats_reduce")
+    if all_reduce is not None:
+        all_reduce(stats3)
+    return out, stats3
+
+
+def critic_forward(cfg, params, share_obs, values_out, group=1):
+    x, ld = _rows_view(share_obs)
+    assert values_out.numel() == x.shape[0] * group
+    check(_lib.lib().mappo_critic_forward(C.byref(cfg), ptr(params), _vp(x), ld, x.shape[0], int(group),
+                                          ptr(values_out), stream_ptr()), "critic_forward")
+
+
+def update_num_blocks(rows):
+    return int(_lib.lib().mappo_update_num_blocks(C.c_longlong(int(rows))))
+
+
+def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, available_actions, grad_partials,
+                 loss_partials, index=None):
+    obs, ld = _rows_view(obs)
+    rows = obs.shape[0] if index is None else index.numel()
+    check(_lib.lib().mappo_actor_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(obs), ld, rows, ptr(index),
+                                        ptr(actions), ptr(old_logp), ptr(adv), ptr(active_masks),
+                                        ptr(available_actions), ptr(grad_partials), ptr(loss_partials), stream_ptr()),
+          "actor_update")
+
+
+def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_masks, vn_stats, grad_partials,
+                  loss_partials, group=1, index=None, share_rows_div=1):
+    x, ld = _rows_view(share_obs)
+    rows = x.shape[0] if index is None else index.numel()
+    check(_lib.lib().mappo_critic_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, rows, int(group),
+                                         ptr(index), int(share_rows_div), ptr(value_preds), ptr(returns), ptr(active_masks), ptr(vn_stats),
+                                         ptr(grad_partials), ptr(loss_partials), stream_ptr()), "critic_update")
+
+
+def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):
+    check(_lib.lib().mappo_grad_reduce(ptr(grad_partials), ptr(loss_partials), int(blocks), grad_sum.numel(),
+                                       ptr(grad_sum), ptr(loss_sum), stream_ptr()), "grad_reduce")
+
+
+def adam_step(cfg, adam, params, exp_avg, exp_avg_sq, grad_sum, loss_sum, denominator_slot, rows_total, grad_out,
+              info_out=None, apply_update=True):
+    check(_lib.lib().mappo_adam_step(C.byref(cfg), C.byref(adam), ptr(params), ptr(exp_avg), ptr(exp_avg_sq),
+                                     ptr(grad_sum), ptr(loss_sum), int(denominator_slot), int(rows_total),
+                                     int(apply_update), ptr(grad_out), ptr(info_out), stream_ptr()), "adam_step")

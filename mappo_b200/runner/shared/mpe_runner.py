@@ -1,0 +1,107 @@
+"""MPERunner mirror (onpolicy/runner/shared/mpe_runner.py:11-183), device-resident.
+
+The reference's loop moves every step's tensors host->device->host (mpe_runner.py:95-123); here `collect` writes
+actions / log-probs / values straight into the buffer slots, `envs.step` reads the action slot and writes the next
+obs / reward / mask slots, so `insert` only advances the step counter.  One rollout step = 3 kernel launches."""
+import time
+
+import numpy as np
+import torch
+
+from .base_runner import Runner
+
+
+class MPERunner(Runner):
+    def __init__(self, config):
+        super(MPERunner, self).__init__(config)
+        self._last_infos = None
+
+    def run(self):
+        self.warmup()
+        start = time.time()
+        episodes = int(self.num_env_steps) // self.episode_length // self.n_rollout_threads
+        train_infos = {}
+        for episode in range(episodes):
+            train_infos = self.run_episode(episode, episodes)
+            total_num_steps = (episode + 1) * self.episode_length * self.n_rollout_threads
+            if episode % self.save_interval == 0 or episode == episodes - 1:
+                self.save()
+            if episode % self.log_interval == 0:
+                end = time.time()
+                print("\n Scenario {} Algo {} Exp {} updates {}/{} episodes, total num timesteps {}/{}, FPS {}.\n".format(
+                    self.all_args.scenario_name, self.algorithm_name, self.experiment_name, episode, episodes,
+                    total_num_steps, self.num_env_steps, int(total_num_steps / (end - start))))
+                env_infos = {}
+                indiv = self.envs._indiv.mean(dim=0).cpu().numpy()          # last step's individual rewards
+                for agent_id in range(self.num_agents):
+                    env_infos["agent%i/individual_rewards" % agent_id] = [float(indiv[agent_id])]
+                train_infos["average_episode_rewards"] = float(self.buffer.rewards.mean().item()) * self.episode_length
+                print("average episode rewards is {}".format(train_infos["average_episode_rewards"]))
+                self.log_train(train_infos, total_num_steps)
+                self.log_env(env_infos, total_num_steps)
+            if episode % self.eval_interval == 0 and self.use_eval:
+                self.eval(total_num_steps)
+        return train_infos
+
+    def run_episode(self, episode=0, episodes=1):
+        """One iteration: episode_length x (collect, step, insert), compute, train (mpe_runner.py:24-40)."""
+        if self.use_linear_lr_decay:
+            self.trainer.policy.lr_decay(episode, episodes)
+        for step in range(self.episode_length):
+            values, actions, action_log_probs, rnn_states, rnn_states_critic, actions_env = self.collect(step)
+            obs, rewards, masks = self.envs.step_ids(actions_env, out_obs=self.buffer.obs[step + 1],
+                                                     out_rewards=self.buffer.rewards[step],
+                                                     out_masks=self.buffer.masks[step + 1])
+            data = obs, rewards, masks, None, values, actions, action_log_probs, rnn_states, rnn_states_critic
+            self.insert(data)
+        self.compute()
+        return self.train()
+
+    def warmup(self):
+        """mpe_runner.py:81-93: reset; obs[0] (and through the view share_obs[0]) receive the first observation."""
+        b = self.buffer
+        if b.share_obs_unique() is None and self.use_centralized_V:
+            raise NotImplementedError("shared runner needs homogeneous agents (use the separated runner)")
+        self.envs.reset(out_obs=b.obs[0])
+
+    @torch.no_grad()
+    def collect(self, step):
+        """mpe_runner.py:95-123 with outputs written in place.  `actions_env` is the action-id slot itself: the env
+        kernel decodes ids, so the one-hot conversion (:110-121) disappears."""
+        b = self.buffer
+        N, M = b.n_rollout_threads, b.num_agents
+        pol = self.trainer.policy
+        self.trainer.prep_rollout()
+        pol.actor.forward_into(b.obs[step].view(N * M, -1), b.actions[step], b.action_log_probs[step],
+                               row_offset=self.envs._cfg.env_id_offset * M)
+        if self.use_centralized_V:
+            pol.critic.forward_into(b.share_obs_unique()[step], b.value_preds[step], group=M)
+        else:
+            pol.critic.forward_into(b.obs[step].view(N * M, -1), b.value_preds[step], group=1)
+        return (b.value_preds[step], b.actions[step], b.action_log_probs[step], b.rnn_states[step + 1],
+                b.rnn_states_critic[step + 1], b.actions[step])
+
+    def insert(self, data):
+        """mpe_runner.py:125-139: everything already sits in its slot (masks = 1 - done written by the env kernel;
+        MLP policies carry no rnn state), so this validates the slot identity and advances `buffer.step`."""
+        obs, rewards, masks, infos, values, actions, action_log_probs, rnn_states, rnn_states_critic = data
+        b = self.buffer
+        b.insert(b.share_obs[b.step + 1], obs, None, None, actions, action_log_probs, values, rewards, masks)
+
+    @torch.no_grad()
+    def eval(self, total_num_steps):
+        """mpe_runner.py:141-183: deterministic rollout on eval_envs."""
+        envs = self.eval_envs
+        N, M = envs.num_envs, self.num_agents
+        obs = envs.reset()
+        acts = torch.empty(N, M, envs.act_width, dtype=torch.float32, device=self.device)
+        lps = torch.empty_like(acts)
+        total = torch.zeros(N, M, 1, dtype=torch.float32, device=self.device)
+        for _ in range(self.episode_length):
+            self.trainer.policy.actor.forward_into(envs._obs.view(N * M, -1), acts, lps, deterministic=True)
+            _, rew, _ = envs.step_ids(acts)
+            total += rew
+        r = float(total.mean().item())
+        print("eval average episode rewards of agent: " + str(r))
+        self.log_env({"eval_average_episode_rewards": [r]}, total_num_steps)
+        return r

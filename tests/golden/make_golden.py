@@ -271,7 +271,152 @@ def gen_gen():
     print("wrote", path, os.path.getsize(path))
 
 
-PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen}
+# ------------------------------------------------------------------ PPO update fixtures
+def _sd_np(module, prefix):
+    return {prefix + k: v.detach().cpu().numpy().copy() for k, v in module.state_dict().items()
+            if "fc_h" not in k or prefix.endswith("0.")}
+
+
+def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_updates=2):
+    """Run the reference's R_MAPPO.ppo_update `n_updates` times on one crafted minibatch and record everything:
+    initial weights, the sample, the six return values, PRE-clip gradients, post-step weights and Adam state."""
+    from onpolicy.envs.mpe.MPE_env import MPEEnv
+    from onpolicy.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    from onpolicy.algorithms.r_mappo.r_mappo import R_MAPPO
+    args = ref_args(scenario, M, L, algo, extra)
+    env = MPEEnv(args)
+    agent = 0 if scenario != "simple_speaker_listener" else 1
+    obs_sp, sh_sp, act_sp = env.observation_space[agent], env.share_observation_space[agent], env.action_space[agent]
+    torch.manual_seed(seed)
+    policy = R_MAPPOPolicy(args, obs_sp, sh_sp, act_sp)
+    trainer = R_MAPPO(args, policy)
+    # make LayerNorm affines and biases non-trivial so the folded-affine chain rule is exercised
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        for net in (policy.actor, policy.critic):
+            for name, prm in net.named_parameters():
+                if "fc_h" in name:
+                    continue
+                if prm.dim() == 1:
+                    prm.add_(torch.randn(prm.shape, generator=g) * 0.2)
+                elif "action_out" in name or "v_out" in name:
+                    prm.add_(torch.randn(prm.shape, generator=g) * 0.3)
+    D, S, H = obs_sp.shape[0], sh_sp.shape[0], args.hidden_size
+    rng = np.random.RandomState(seed)
+    recurrent = bool(args.use_recurrent_policy)
+    Lc = args.data_chunk_length
+    Nc = B // Lc if recurrent else B
+    obs = rng.standard_normal((B, D)).astype(np.float32) * 0.7
+    share_obs = rng.standard_normal((B, S)).astype(np.float32) * 0.7
+    rnn_a = (rng.standard_normal((Nc, 1, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
+    rnn_c = (rng.standard_normal((Nc, 1, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
+    masks = (rng.uniform(size=(B, 1)) > 0.08).astype(np.float32)
+    active = (rng.uniform(size=(B, 1)) > 0.1).astype(np.float32)
+    avail = None
+    if act_sp.__class__.__name__ == "Discrete":
+        avail = np.ones((B, act_sp.n), np.float32)
+        if zero_avail:
+            avail[rng.uniform(size=avail.shape) < 0.15] = 0.0
+            avail[:, 0] = 1.0
+    with torch.no_grad():
+        policy.actor.eval(); policy.critic.eval()
+        if recurrent:   # evaluate on the chunked layout to get consistent log-probs
+            feats_a = policy.actor.base(torch.from_numpy(obs))
+            feats_a, _ = policy.actor.rnn(feats_a, torch.from_numpy(rnn_a), torch.from_numpy(masks))
+            if act_sp.__class__.__name__ == "Discrete":
+                dist = [policy.actor.act.action_out(feats_a, torch.from_numpy(avail))]
+            else:
+                dist = [ao(feats_a) for ao in policy.actor.act.action_outs]
+            actions = torch.cat([d.sample() for d in dist], -1)
+            logp = torch.cat([d.log_probs(actions[:, i:i + 1]) for i, d in enumerate(dist)], -1)
+            values, _ = policy.critic(share_obs, rnn_c, masks)
+        else:
+            values, actions, logp, _, _ = policy.get_actions(share_obs, obs, rnn_a, rnn_c, masks, avail)
+    actions = actions.numpy().astype(np.float32)
+    old_logp = (logp.numpy() + rng.normal(0, 0.15, logp.shape)).astype(np.float32)
+    adv = rng.standard_normal((B, 1)).astype(np.float32)
+    value_preds = (values.numpy() + rng.normal(0, 0.25, (B, 1))).astype(np.float32)
+    if args.use_valuenorm:
+        returns = rng.normal(-5, 3, (B, 1)).astype(np.float32)
+        trainer.value_normalizer.update(torch.from_numpy(rng.normal(-4, 2, (300, 1)).astype(np.float32)))
+    else:
+        returns = (values.numpy() + rng.normal(0, 1.0, (B, 1))).astype(np.float32)
+    sample = (share_obs, obs, rnn_a, rnn_c, actions, value_preds, returns, masks, active, old_logp, adv, avail)
+    out = dict(B=B, D=D, S=S, recurrent=int(recurrent), chunk=Lc)
+    out.update({"args_" + k: np.asarray(getattr(args, k)) for k in (
+        "use_ReLU", "use_feature_normalization", "use_valuenorm", "use_huber_loss", "use_clipped_value_loss",
+        "use_policy_active_masks", "use_value_active_masks", "use_max_grad_norm", "max_grad_norm", "clip_param",
+        "entropy_coef", "value_loss_coef", "huber_delta", "lr", "critic_lr", "opti_eps", "weight_decay", "hidden_size",
+        "layer_N", "gain")})
+    out["act_heads"] = np.array([act_sp.n] if act_sp.__class__.__name__ == "Discrete"
+                                else list((act_sp.high - act_sp.low + 1).astype(int)))
+    for name, arr in zip(FIELDS, sample):
+        if arr is not None and (recurrent or not name.startswith("rnn_states")):
+            out["sample_" + name] = arr
+    out.update(_sd_np(policy.actor, "actor0."))
+    out.update(_sd_np(policy.critic, "critic0."))
+    if args.use_valuenorm:
+        out["vn0"] = vn_stats(trainer.value_normalizer)
+    trainer.prep_training()
+    import torch.nn.utils as U
+    real_clip = U.clip_grad_norm_
+    for u in range(n_updates):
+        pre = []
+
+        def spy(params, max_norm, *a, **k):
+            params = list(params)
+            pre.append([None if p.grad is None else p.grad.detach().clone() for p in params])
+            return real_clip(params, max_norm, *a, **k)
+        U.clip_grad_norm_ = spy
+        try:
+            vl, cgn, pl, ent, agn, ratio = trainer.ppo_update(sample)
+        finally:
+            U.clip_grad_norm_ = real_clip
+        tag = "u%d_" % u
+        out[tag + "value_loss"] = vl.item(); out[tag + "critic_grad_norm"] = float(cgn)
+        out[tag + "policy_loss"] = pl.item(); out[tag + "dist_entropy"] = ent.item()
+        out[tag + "actor_grad_norm"] = float(agn); out[tag + "ratio_mean"] = ratio.mean().item()
+        for net, nm, grads in ((policy.actor, "actor", pre[0]), (policy.critic, "critic", pre[1])):
+            for (pname, _), gr in zip(net.named_parameters(), grads):
+                if gr is not None:
+                    out[tag + nm + "_grad." + pname] = gr.numpy()
+            out.update(_sd_np(net, tag + nm + "."))
+        for opt, nm, net in ((policy.actor_optimizer, "actor", policy.actor), (policy.critic_optimizer, "critic", policy.critic)):
+            for (pname, prm) in net.named_parameters():
+                st = opt.state.get(prm, None)
+                if st:
+                    out[tag + nm + "_exp_avg." + pname] = st["exp_avg"].numpy().copy()
+                    out[tag + nm + "_exp_avg_sq." + pname] = st["exp_avg_sq"].numpy().copy()
+        if args.use_valuenorm:
+            out[tag + "vn"] = vn_stats(trainer.value_normalizer)
+    return out
+
+
+PPO_CASES = {
+    # C1/C2: spread, shared MLP, Tanh (the reference script passes --use_ReLU, a store_false flag), defaults
+    "mlp_tanh": dict(scenario="simple_spread", M=3, L=3, algo="mappo", extra="--use_ReLU --lr 7e-4 --critic_lr 7e-4",
+                     B=700, seed=3),
+    # option coverage: ReLU, no ValueNorm, MSE, no active masks, tight grad clip, masked available actions
+    "mlp_relu_opts": dict(scenario="simple_spread", M=3, L=3, algo="mappo",
+                          extra="--use_valuenorm --use_huber_loss --use_policy_active_masks --use_value_active_masks "
+                                "--max_grad_norm 0.05 --entropy_coef 0.03 --weight_decay 0.01",
+                          B=300, seed=5, zero_avail=True),
+    # unclipped value loss, no feature norm, listener of speaker_listener (D=11, S=14)
+    "mlp_listener": dict(scenario="simple_speaker_listener", M=2, L=3, algo="mappo",
+                         extra="--use_clipped_value_loss --use_feature_normalization --share_policy", B=257, seed=7),
+}
+
+
+def gen_ppo():
+    for tag, kw in PPO_CASES.items():
+        fx = make_ppo_fixture(**kw)
+        path = os.path.join(HERE, "ppo_%s.npz" % tag)
+        np.savez_compressed(path, **fx)
+        print("wrote", path, os.path.getsize(path), "policy_loss", fx["u0_policy_loss"], "agn", fx["u0_actor_grad_norm"],
+              "cgn", fx["u0_critic_grad_norm"])
+
+
+PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen, "ppo": gen_ppo}
 
 if __name__ == "__main__":
     todo = sys.argv[1:] or list(PARTS)

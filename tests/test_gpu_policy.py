@@ -1,0 +1,185 @@
+"""GPU: fused actor/critic kernels, PPO update, clipping and Adam against (a) fixtures recorded from the
+reference's own R_MAPPO.ppo_update and (b) the oracle.  Tolerances are north_star's: losses and gradients 1e-4."""
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from ppo_common import fx_args, sd_from
+
+pytestmark = pytest.mark.gpu
+CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener"]
+
+
+def make_space(n):
+    from mappo_b200.envs.spaces import Box
+    return Box(-np.inf, np.inf, (n,), np.float32)
+
+
+def build(fx, seed=1):
+    from mappo_b200.envs.spaces import Discrete, MultiDiscrete
+    from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    from mappo_b200.algorithms.r_mappo.r_mappo import R_MAPPO
+    a = fx_args(fx)
+    args = types.SimpleNamespace(**a)
+    args.use_recurrent_policy = bool(fx["recurrent"]); args.use_naive_recurrent_policy = False
+    args.recurrent_N = 1; args.use_popart = False; args.use_orthogonal = True; args.seed = seed
+    args.ppo_epoch = 1; args.num_mini_batch = 1; args.data_chunk_length = int(fx["chunk"])
+    heads = [int(h) for h in fx["act_heads"]]
+    act = Discrete(heads[0]) if len(heads) == 1 else MultiDiscrete([[0, h - 1] for h in heads])
+    pol = R_MAPPOPolicy(args, make_space(int(fx["D"])), make_space(int(fx["S"])), act, device="cuda")
+    pol.actor.load_state_dict(sd_from(fx, "actor0."))
+    pol.critic.load_state_dict(sd_from(fx, "critic0."))
+    tr = R_MAPPO(args, pol, device="cuda")
+    if "vn0" in fx.files:
+        tr.value_normalizer.stats.copy_(torch.as_tensor(fx["vn0"]))
+    return args, pol, tr
+
+
+def sample_of(fx):
+    s = {k[7:]: fx[k] for k in fx.files if k.startswith("sample_")}
+    B = int(fx["B"])
+    z = np.zeros((B, 1, 64), np.float32)
+    return (s["share_obs"], s["obs"], s.get("rnn_states", z), s.get("rnn_states_critic", z), s["actions"],
+            s["value_preds"], s["returns"], s["masks"], s["active_masks"], s["old_action_log_probs"], s["adv_targ"],
+            s.get("available_actions"))
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_state_dict_keys_and_forward_vs_oracle(tag, golden_dir):
+    from oracle import policy as op
+    fx = np.load(os.path.join(golden_dir, "ppo_%s.npz" % tag))
+    args, pol, tr = build(fx)
+    want_keys = [k[7:] for k in fx.files if k.startswith("actor0.")]
+    assert list(pol.actor.state_dict().keys()) == want_keys
+    assert list(pol.critic.state_dict().keys()) == [k[8:] for k in fx.files if k.startswith("critic0.")]
+    s = sample_of(fx)
+    share_obs, obs, avail = s[0], s[1], s[11]
+    asd, csd = sd_from(fx, "actor0."), sd_from(fx, "critic0.")
+    feats, _ = op.actor_features(asd, obs, s[2], s[7], args.use_ReLU, args.use_feature_normalization, False)
+    logits = op.actor_logits(asd, feats, avail)
+    v_ref, _ = op.critic_values(csd, share_obs, s[3], s[7], args.use_ReLU, args.use_feature_normalization, False)
+    # critic values
+    values = pol.get_values(share_obs, s[3], s[7])
+    np.testing.assert_allclose(values.cpu().numpy(), v_ref.numpy(), rtol=1e-4, atol=2e-5)
+    # deterministic actions = argmax, log-probs
+    a_ref, lp_ref, _ = op.act_forward(logits, True)
+    act, lp, _ = pol.actor(obs, s[2], s[7], avail, deterministic=True)
+    assert (act.cpu().numpy() == a_ref.numpy()).mean() > 0.995
+    same = act.cpu().numpy() == a_ref.numpy()
+    np.testing.assert_allclose(lp.cpu().numpy()[same], lp_ref.numpy()[same], rtol=1e-4, atol=2e-5)
+    # sampling: same Philox stream and inverse CDF as the oracle; ties at a CDF boundary may differ
+    pol.actor.sample_seed = 99
+    acts = torch.empty(obs.shape[0], len(logits), device="cuda"); lps = torch.empty_like(acts)
+    pol.actor.forward_into(torch.as_tensor(obs).cuda(), acts, lps,
+                           available_actions=None if avail is None else torch.as_tensor(avail).cuda(), step=5, row_offset=1000)
+    a_s, lp_s, margin = op.act_forward(logits, False, seed=99, step=5, row_offset=1000)
+    diff = acts.cpu().numpy() != a_s.numpy()
+    assert not (diff & (margin.numpy() > 1e-5)).any(), "sampled action differs away from a CDF boundary"
+    np.testing.assert_allclose(lps.cpu().numpy()[~diff], lp_s.numpy()[~diff], rtol=1e-4, atol=2e-5)
+    counts = np.bincount(acts.cpu().numpy()[:, 0].astype(int), minlength=logits[0].shape[1])
+    assert (counts > 0).sum() >= 2
+    # evaluate_actions
+    vals, elp, ent = pol.evaluate_actions(share_obs, obs, s[2], s[3], s[4], s[7], avail, s[8])
+    lp_e, ent_e = op.evaluate_actions(logits, s[4], s[8] if args.use_policy_active_masks else None)
+    np.testing.assert_allclose(elp.cpu().numpy(), lp_e.numpy(), rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(ent.item(), ent_e.item(), rtol=1e-5)
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_ppo_update_matches_reference(tag, golden_dir):
+    """Two consecutive ppo_updates on the reference's own minibatch: losses, PRE-clip gradients, post-step
+    parameters, Adam moments, ValueNorm statistics."""
+    fx = np.load(os.path.join(golden_dir, "ppo_%s.npz" % tag))
+    args, pol, tr = build(fx)
+    s = sample_of(fx)
+    Pa = pol.actor.flat.numel()
+    for u in range(2):
+        vl, cgn, pl, ent, agn, ratio = tr.ppo_update(s)
+        t = "u%d_" % u
+        got = dict(value_loss=vl, critic_grad_norm=cgn, policy_loss=pl, dist_entropy=ent, actor_grad_norm=agn,
+                   ratio_mean=ratio)
+        for k, v in got.items():
+            np.testing.assert_allclose(v.item(), fx[t + k].item(), rtol=1e-4, atol=1e-6, err_msg=k)
+        ws = next(iter(tr._ws.values()))
+        for net, name, g in ((pol.actor, "actor", ws["grad"][:Pa]), (pol.critic, "critic", ws["grad"][Pa:])):
+            for k, gv in net.unflatten(g).items():
+                want = fx[t + name + "_grad." + k]
+                np.testing.assert_allclose(gv.cpu().numpy(), want, rtol=1e-4, atol=1e-4 * np.abs(want).max() + 1e-9,
+                                           err_msg="%s grad %s (update %d)" % (name, k, u))
+            for k, p in net.state_dict().items():
+                if "fc_h" in k:
+                    continue
+                np.testing.assert_allclose(p.cpu().numpy(), fx[t + name + "." + k], rtol=1e-5, atol=3e-6, err_msg=k)
+            opt = pol.actor_optimizer if name == "actor" else pol.critic_optimizer
+            for k, m in net.unflatten(opt.exp_avg).items():
+                want = fx[t + name + "_exp_avg." + k]
+                np.testing.assert_allclose(m.cpu().numpy(), want, rtol=1e-4, atol=1e-4 * np.abs(want).max() + 1e-10)
+            for k, m in net.unflatten(opt.exp_avg_sq).items():
+                want = fx[t + name + "_exp_avg_sq." + k]
+                np.testing.assert_allclose(m.cpu().numpy(), want, rtol=2e-4, atol=2e-4 * np.abs(want).max() + 1e-12)
+        if "vn0" in fx.files:
+            np.testing.assert_allclose(tr.value_normalizer.stats.cpu().numpy(), fx[t + "vn"], rtol=1e-6)
+
+
+def test_reference_init_is_bit_identical(golden_dir):
+    """Same torch seed -> same initial weights as the reference constructors (the fixture was built after
+    torch.manual_seed(3); its LayerNorm/bias perturbation does not touch the matrices of fc1/fc2)."""
+    from mappo_b200.envs.spaces import Discrete
+    from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    fx = np.load(os.path.join(golden_dir, "ppo_mlp_tanh.npz"))
+    a = fx_args(fx)
+    args = types.SimpleNamespace(**a)
+    args.use_recurrent_policy = args.use_naive_recurrent_policy = False
+    args.recurrent_N = 1; args.use_popart = False; args.use_orthogonal = True; args.seed = 1
+    torch.manual_seed(3)
+    pol = R_MAPPOPolicy(args, make_space(18), make_space(54), Discrete(5), device="cuda")
+    for net, pre in ((pol.actor, "actor0."), (pol.critic, "critic0.")):
+        sd = net.state_dict()
+        for k in ("base.mlp.fc1.0.weight", "base.mlp.fc2.0.0.weight", "base.mlp.fc_h.0.weight"):
+            np.testing.assert_array_equal(sd[k].cpu().numpy(), fx[pre + k])
+
+
+def test_gradient_is_sum_over_shards_and_tiles():
+    """Size-independent property at a large batch: the unnormalised gradient sums of two half batches add up to
+    the full batch's (what the multi-GPU all-reduce relies on), and a row gather by a permutation leaves the
+    reduced sums unchanged up to summation order."""
+    from mappo_b200 import ops
+    from mappo_b200.envs.spaces import Discrete
+    from mappo_b200.algorithms.r_mappo.algorithm.r_actor_critic import R_Actor
+    args = types.SimpleNamespace(hidden_size=64, layer_N=1, use_ReLU=False, use_feature_normalization=True,
+                                 use_orthogonal=True, use_recurrent_policy=False, use_naive_recurrent_policy=False,
+                                 recurrent_N=1, use_popart=False, gain=0.01, use_policy_active_masks=True, seed=1)
+    torch.manual_seed(0)
+    actor = R_Actor(args, make_space(18), Discrete(5), "cuda")
+    B = 200_000
+    g = torch.Generator(device="cuda").manual_seed(1)
+    obs = torch.randn(B, 18, device="cuda", generator=g)
+    acts = torch.randint(0, 5, (B, 1), device="cuda", generator=g).float()
+    old = torch.full((B, 1), -1.6, device="cuda") + 0.1 * torch.randn(B, 1, device="cuda", generator=g)
+    adv = torch.randn(B, device="cuda", generator=g)
+    loss = ops.LossConfig(0.2, 0.01, 1.0, 10.0, 1, 1, 0, 1, 1, 0)
+    P = actor.flat.numel()
+
+    def run(sl, index=None):
+        rows = (sl.stop - sl.start) if index is None else index.numel()
+        nb = ops.update_num_blocks(rows)
+        gp = torch.empty(nb, P, device="cuda"); lp = torch.empty(nb, 4, dtype=torch.float64, device="cuda")
+        if index is None:
+            ops.actor_update(actor.cfg, loss, actor.flat, obs[sl], acts[sl], old[sl], adv[sl], None, None, gp, lp)
+        else:
+            ops.actor_update(actor.cfg, loss, actor.flat, obs, acts, old, adv, None, None, gp, lp, index=index)
+        gs = torch.empty(P, device="cuda"); ls = torch.empty(4, dtype=torch.float64, device="cuda")
+        ops.grad_reduce(gp, lp, nb, gs, ls)
+        return gs.double(), ls
+    g_all, l_all = run(slice(0, B))
+    g_a, l_a = run(slice(0, B // 2 + 37)); g_b, l_b = run(slice(B // 2 + 37, B))
+    scale = g_all.abs().max().item()
+    assert (g_all - (g_a + g_b)).abs().max().item() < 2e-5 * scale
+    np.testing.assert_allclose((l_a + l_b).cpu().numpy(), l_all.cpu().numpy(), rtol=1e-9)
+    perm = torch.randperm(B, device="cuda")
+    g_p, l_p = run(None, index=perm)
+    assert (g_all - g_p).abs().max().item() < 2e-5 * scale
+    np.testing.assert_allclose(l_p.cpu().numpy(), l_all.cpu().numpy(), rtol=1e-9)
