@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py -- agent-steps/s of full MAPPO iterations (rollout + GAE + PPO update) on MPE simple_spread.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--envs E]
+
+A "step" is ONE MAPPO iteration: episode_length x (policy forward, env step, insert), bootstrap value + GAE with
+ValueNorm, then ppo_epoch x (actor update, critic update, clip, Adam).  One iteration produces N*T*M agent-steps.
+Workload = BASELINE.json configs[1] (C2): simple_spread, 3 agents, 3 landmarks, 65,536 envs per GPU, T = 25,
+shared MLP policy (Tanh), ppo_epoch = 10, num_mini_batch = 1, GAE + ValueNorm; weak scaling (envs per GPU fixed).
+
+Prints ONE JSON line (rank 0).  `value`: device-resident runner.  `e2e`: the same iteration driven through the
+reference-facing vec-env / policy / buffer calls with HOST (pinned) buffers at the boundary, copies in the timed
+region.  `roofline`: the dominant kernel (fused actor forward+loss+backward), timed with CUDA events inside the
+timed region.  `cpu_baseline`: the CPU restatement of the reference path (oracle/iteration.py) timed on this
+box's host cores on a bounded sample.  `--impl reference` times that CPU path alone.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "agent-steps/sec (rollout+GAE+PPO update), MPE simple_spread"
+UNIT = "agent-steps/s"
+M_AGENTS, N_LANDMARKS, T_EP, PPO_EPOCH = 3, 3, 25, 10
+D_OBS, S_OBS, N_ACT, H = 18, 54, 5, 64
+
+
+def flags(n_envs):
+    return ("--env_name MPE --algorithm_name mappo --scenario_name simple_spread --num_agents %d --num_landmarks %d "
+            "--n_rollout_threads %d --episode_length %d --ppo_epoch %d --num_mini_batch 1 --use_ReLU --gain 0.01 "
+            "--lr 7e-4 --critic_lr 7e-4 --seed 1" % (M_AGENTS, N_LANDMARKS, n_envs, T_EP, PPO_EPOCH)).split()
+
+
+def workload_name(n_envs, n_gpus):
+    return ("C2: MPE simple_spread M=3 L=3, %d envs/GPU x %d GPU, T=25, shared MLP (Tanh, H=64), ppo_epoch=10, "
+            "num_mini_batch=1, GAE+ValueNorm" % (n_envs, n_gpus))
+
+
+# ---------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------- CPU path
+def cpu_iteration_rate(n_envs, steps, warmup, threads):
+    """agent-steps/s of oracle/iteration.py (the CPU port of the reference path) on `threads` host threads."""
+    import torch
+    from mappo_b200.config import parse_args
+    from mappo_b200.algorithms.r_mappo.algorithm.r_actor_critic import _reference_init
+    from oracle.iteration import OracleMAPPO
+    torch.set_num_threads(threads)
+    a = parse_args(flags(n_envs))
+    torch.manual_seed(1)
+    asd = _reference_init(a, D_OBS, [N_ACT], False)
+    csd = _reference_init(a, S_OBS, [1], True)
+    o = OracleMAPPO(a, asd, csd)
+    o.warmup()
+    for _ in range(warmup):
+        o.iteration()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        o.iteration()
+    dt = time.perf_counter() - t0
+    return n_envs * T_EP * M_AGENTS * steps / dt, dt / steps
+
+
+def run_reference(ns):
+    """--impl reference: the CPU path alone, rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    n_envs = ns.cpu_envs
+    val, sec = cpu_iteration_rate(n_envs, ns.steps, ns.warmup, cores)
+    sample = "%d envs x %d iterations (each a full rollout+GAE+%d-epoch update) of the same workload" % (
+        n_envs, ns.steps, PPO_EPOCH)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": ns.gpus, "steps": ns.steps,
+        "warmup": ns.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(ns.envs, ns.gpus), "cpu_sample_envs": n_envs},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------------------------- GPU path
+def build_runner(n_envs, device, rank, world, host_io=False):
+    import torch
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    from mappo_b200.runner.shared.mpe_runner import MPERunner
+    a = parse_args(flags(n_envs))
+    torch.manual_seed(1)                                 # same initial weights on every rank (replicated parameters)
+    envs = MPEVecEnv(a, device=device, env_id_offset=rank * n_envs, host_io=host_io)
+    runner = MPERunner({"all_args": a, "envs": envs, "eval_envs": None, "device": device, "num_agents": M_AGENTS,
+                        "run_dir": None})
+    if world > 1:
+        import torch.distributed as dist
+        runner.trainer.set_all_reduce(lambda t: dist.all_reduce(t), world)
+    return a, envs, runner
+
+
+def host_boundary_iteration(runner, envs, hb):
+    """One iteration driven like the reference's MPERunner.run body (runner/shared/mpe_runner.py:24-40,95-139) with
+    HOST arrays crossing every reference-facing call: policy outputs come back to the host (`_t2n`), one-hot
+    `actions_env` goes in through envs.step, obs / rewards / dones come back as host arrays, and buffer.insert
+    receives host arrays.  Returns (h2d_bytes, d2h_bytes)."""
+    import numpy as np
+    import torch
+    b, pol = runner.buffer, runner.trainer.policy
+    N, M = b.n_rollout_threads, b.num_agents
+    h2d = d2h = 0
+    eye = np.eye(N_ACT, dtype=np.float32)
+    for step in range(b.episode_length):
+        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step].reshape(N * M, -1),
+                                                         b.obs[step].view(N * M, -1), None, None, None)
+        hb["values"].copy_(values.view(N, M, 1), non_blocking=True)
+        hb["actions"].copy_(actions.view(N, M, 1), non_blocking=True)
+        hb["logp"].copy_(logp.view(N, M, 1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        d2h += hb["values"].numel() * 4 + hb["actions"].numel() * 8 + hb["logp"].numel() * 4
+        actions_env = eye[hb["actions"].numpy()[..., 0]]                  # mpe_runner.py:110-121
+        obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
+        h2d += actions_env.nbytes
+        d2h += obs.nbytes + rewards.nbytes + dones.nbytes
+        masks = np.ones((N, M, 1), dtype=np.float32)
+        masks[dones] = 0.0                                               # mpe_runner.py:128-131
+        share_obs = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))   # :133-137 (a view)
+        b.insert(share_obs, obs, None, None, hb["actions"].numpy(), hb["logp"].numpy(), hb["values"].numpy(), rewards,
+                 masks)
+        h2d += obs.nbytes + hb["actions"].numel() * 8 + hb["logp"].numel() * 4 + hb["values"].numel() * 4 + \
+            rewards.nbytes + masks.nbytes
+    runner.compute()
+    info = runner.train()                                                # six scalars come back to the host
+    d2h += 8 * 4
+    return h2d, d2h, info
+
+
+def run_ours(ns):
+    import torch
+    from mappo_b200 import _lib, ops
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU path); use --impl reference for the CPU arm")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    n_envs = ns.envs
+    a, envs, runner = build_runner(n_envs, device, rank, world)
+    agent_steps = n_envs * T_EP * M_AGENTS
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    runner.warmup()
+    for _ in range(ns.warmup):
+        runner.run_episode()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ops.TIMERS.reset(); ops.TIMERS.enabled = True
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(ns.steps):
+        info = runner.run_episode()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = _lib.launch_count() - launches0
+    ops.TIMERS.enabled = False
+    kt = ops.TIMERS.summary()
+    clocks = sampler.stop() if rank == 0 else None
+    value = agent_steps * world * ns.steps / (ms * 1e-3)
+
+    # ---- e2e: host buffers at the reference-facing boundary
+    envs.set_host_io(True)
+    pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
+    hb = {"values": pin(n_envs, M_AGENTS, 1), "actions": pin(n_envs, M_AGENTS, 1, dt=torch.int64),
+          "logp": pin(n_envs, M_AGENTS, 1)}
+    host_boundary_iteration(runner, envs, hb)               # warm-up of the host path
+    barrier()
+    e_steps = max(1, min(ns.steps, ns.e2e_steps))
+    t0 = time.perf_counter()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    for _ in range(e_steps):
+        h2d, d2h, _ = host_boundary_iteration(runner, envs, hb)
+    g1.record()
+    barrier()
+    e_ms = torch.tensor([max(g0.elapsed_time(g1), 0.0)], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = agent_steps * world * e_steps / (float(e_ms.item()) * 1e-3)
+    envs.set_host_io(False)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (see DESIGN.md "Kernels" for the per-row work)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    rows = agent_steps                                        # one actor_update launch covers the whole batch
+    flop_row = actor_update_flops_per_row()
+    n, tot = kt.get("actor_update", (0, 0.0))
+    per_launch_ms = tot / max(n, 1)
+    achieved = rows * flop_row / (per_launch_ms * 1e-3) / 1e12 if n else None
+    peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    roofline = {"kernel": "mlp_kernel<MODE=2> (actor forward+PPO loss+backward, fused)", "bound": "tensor",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
+                "peak_source": "measured bf16 sustained (MEASURED_PEAKS.json)" if peaks else "fallback",
+                "traffic": None, "launches": n, "ms_per_launch": per_launch_ms,
+                "flop_per_row": flop_row, "rows_per_launch": rows,
+                "note": "fp32 FMA kernel this round: its own pipe peak is 148 SM x 128 lanes x 2 x sm clock"}
+    share = {k: {"launches": v[0], "ms_per_step": v[1] / ns.steps} for k, v in kt.items()}
+
+    # ---- CPU baseline beside it (N = 1 only)
+    cpu = None
+    if world == 1 and not ns.no_cpu:
+        cores = len(os.sched_getaffinity(0))
+        v, sec = cpu_iteration_rate(ns.cpu_envs, 1, 0, cores)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d envs x 1 full iteration (%.1f s) of the same workload, oracle/iteration.py, torch %d threads"
+                         % (ns.cpu_envs, sec, cores)}
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": ns.steps, "warmup": ns.warmup,
+           "ms_per_step": ms / ns.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32 (policy, buffer), f64 (env physics)", "data": "synthetic",
+           "config": {"workload": workload_name(n_envs, world), "agent_steps_per_step": agent_steps * world,
+                      "l2": "inputs larger than L2 (rollout buffer 0.4 GB per GPU)"},
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                   "steps": e_steps, "wall_s": time.perf_counter() - t0},
+           "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "kernel_ms_per_step": share,
+           "clocks": clocks, "train_info": info}
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def actor_update_flops_per_row():
+    """Algorithmic FLOP of forward + dgrad + wgrad per sample for the actor (MACs x 2 x 3 minus the
+    first-layer dgrad)."""
+    macs = D_OBS * H + H * H + H * N_ACT
+    return 2 * macs * 3 - 2 * D_OBS * H
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
+    ap.add_argument("--cpu-envs", dest="cpu_envs", type=int, default=1024, help="envs of the bounded CPU sample")
+    ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
+    ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
+    ns = ap.parse_args()
+    ns.warmup = max(ns.warmup, 0)
+    if ns.impl == "reference":
+        run_reference(ns)
+    else:
+        run_ours(ns)
+
+
+if __name__ == "__main__":
+    main()

@@ -58,9 +58,21 @@ def _declare(L):
         fn.restype = C.c_int
 
 
-# filled by the modules that bind further entry points (kept in one table so the CPU test that
-# checks "every symbol in the header is exported" can iterate over it)
-_EXTRA_SIGS = {}
+class _Sigs(dict):
+    """Table of further entry points, filled by the modules that bind them (kept in one place so the CPU test that
+    checks "every symbol in the header is exported" can iterate over it).  Entries added after the library was
+    loaded are applied immediately."""
+
+    def update(self, other):
+        dict.update(self, other)
+        if _lib is not None:
+            for name, sig in other.items():
+                fn = getattr(_lib, name)
+                fn.argtypes = sig
+                fn.restype = C.c_int
+
+
+_EXTRA_SIGS = _Sigs()
 
 
 def check(rc, what=""):

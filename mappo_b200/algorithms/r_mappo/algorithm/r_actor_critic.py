@@ -20,7 +20,7 @@ def check(x, device):
         return None
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(x)
-    return x.to(device=device, dtype=torch.float32)
+    return x.to(device=device, dtype=torch.float32, non_blocking=True)
 
 
 class _Node(nn.Module):

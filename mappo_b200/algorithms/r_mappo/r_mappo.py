@@ -46,8 +46,10 @@ class R_MAPPO:
         self._info = torch.zeros(8, **self.tpdv)       # actor {loss, gnorm, entropy, ratio}, critic {loss, gnorm, -, -}
         self._info_total = torch.zeros(8, **self.tpdv)
 
-    def set_all_reduce(self, fn):
+    def set_all_reduce(self, fn, world_size):
+        """Data-parallel update: `fn(tensor)` sums a CUDA tensor in place over the ranks (NCCL all-reduce)."""
         self.all_reduce = fn
+        self.world_size = int(world_size)
         if self.value_normalizer is not None:
             self.value_normalizer.all_reduce = fn
 

@@ -46,7 +46,7 @@ class MPEVecEnv:
     """`envs` object of the runners: reset() / step(actions) / step_async / step_wait / close, attributes
     num_envs, observation_space, share_observation_space, action_space (lists of length M)."""
 
-    def __init__(self, args, num_envs=None, device="cuda", seed=None, env_id_offset=0):
+    def __init__(self, args, num_envs=None, device="cuda", seed=None, env_id_offset=0, host_io=False):
         name = args.scenario_name
         if name not in SCENARIOS:
             raise NotImplementedError("Can not support the %s scenario on the device env" % name)
@@ -97,6 +97,30 @@ class MPEVecEnv:
         self._indiv = torch.empty(N, M, dtype=torch.float32, device=dev)
         self._pending = None
         self.closed = False
+        self._host = None
+        self.set_host_io(host_io)
+
+    def set_host_io(self, on):
+        """host_io=True: `reset` / `step` return HOST numpy arrays like the reference's vec envs
+        (env_wrappers.py:257-272) -- views of pinned staging buffers, valid until the next call -- instead of
+        device tensors.  Inputs may be host arrays in either mode."""
+        self.host_io = bool(on)
+        if self.host_io and self._host is None:
+            N, M = self.num_envs, self.num_agents
+            pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
+            self._host = dict(obs=pin(N, self.obs_width), rew=pin(N, M, 1), dones=pin(N, M, dt=torch.uint8),
+                              indiv=pin(N, M))
+
+    def _to_host(self, obs_dev, with_step_outputs):
+        h = self._host
+        h["obs"].copy_(obs_dev.view(self.num_envs, self.obs_width), non_blocking=True)
+        if with_step_outputs:
+            h["rew"].copy_(self._rew_last.view(self.num_envs, self.num_agents, 1), non_blocking=True)
+            h["dones"].copy_(self._dones, non_blocking=True)
+            h["indiv"].copy_(self._indiv, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        obs = self._shape_obs(h["obs"])
+        return obs.numpy() if torch.is_tensor(obs) else [o.numpy() for o in obs]
 
     @staticmethod
     def _state_struct(o):
@@ -159,6 +183,8 @@ class MPEVecEnv:
         assert obs.is_contiguous() and obs.numel() == self.num_envs * self.obs_width
         _lib.check(_lib.lib().mappo_env_reset(C.byref(self._cfg), C.byref(self._st), _lib.ptr(obs),
                                               1 if use_given_state else 0, _lib.stream_ptr()), "env_reset")
+        if self.host_io:
+            return self._to_host(obs, False)
         return self._shape_obs(obs.view(self.num_envs, self.obs_width))
 
     def set_state(self, p_pos=None, p_vel=None, lm_pos=None, goal=None, comm=None, step_count=None):
@@ -195,10 +221,13 @@ class MPEVecEnv:
             o.p_vel, o.comm, o.step_count, o.episode = o.p_pos, o.goal, o.goal, o.goal
             self._rs_keep = o
             rs = C.byref(self._state_struct(o))
-        _lib.check(_lib.lib().mappo_env_step(
-            C.byref(self._cfg), C.byref(self._st), _lib.ptr(action_ids), int(action_ids.shape[-1]),
-            _lib.ptr(obs), _lib.ptr(rew), _lib.ptr(masks), _lib.ptr(self._dones), _lib.ptr(self._indiv),
-            rs, _lib.stream_ptr()), "env_step")
+        from ... import ops
+        with ops.TIMERS.span("env_step"):
+            _lib.check(_lib.lib().mappo_env_step(
+                C.byref(self._cfg), C.byref(self._st), _lib.ptr(action_ids), int(action_ids.shape[-1]),
+                _lib.ptr(obs), _lib.ptr(rew), _lib.ptr(masks), _lib.ptr(self._dones), _lib.ptr(self._indiv),
+                rs, _lib.stream_ptr()), "env_step")
+        self._rew_last = rew
         return obs, rew, masks
 
     def step_async(self, actions):
@@ -207,6 +236,10 @@ class MPEVecEnv:
     def step_wait(self):
         obs, rew, _ = self.step_ids(self._pending)
         self._pending = None
+        if self.host_io:
+            o = self._to_host(obs, True)
+            h = self._host
+            return o, h["rew"].numpy(), h["dones"].numpy().astype(bool), _Infos(h["indiv"])
         return (self._shape_obs(obs.view(self.num_envs, self.obs_width)), rew.view(self.num_envs, self.num_agents, 1),
                 self._dones.bool(), _Infos(self._indiv))
 

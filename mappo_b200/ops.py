@@ -14,6 +14,45 @@ class GaeConfig(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class KernelTimers:
+    """Per-kernel CUDA-event timing on the launching stream (bench.py's roofline figures).  Disabled by default:
+    `span` then costs one attribute test."""
+
+    def __init__(self):
+        self.enabled = False
+        self._ev = {}
+
+    class _Span:
+        def __init__(self, owner, name):
+            self.o, self.n = owner, name
+
+        def __enter__(self):
+            if self.o.enabled:
+                self.a = torch.cuda.Event(enable_timing=True)
+                self.b = torch.cuda.Event(enable_timing=True)
+                self.a.record()
+            return self
+
+        def __exit__(self, *exc):
+            if self.o.enabled:
+                self.b.record()
+                self.o._ev.setdefault(self.n, []).append((self.a, self.b))
+            return False
+
+    def span(self, name):
+        return KernelTimers._Span(self, name)
+
+    def reset(self):
+        self._ev = {}
+
+    def summary(self):
+        """{name: (launches, total_ms)}; synchronises."""
+        torch.cuda.synchronize()
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self._ev.items()}
+
+
+TIMERS = KernelTimers()
+
 _P = C.c_void_p
 _lib._EXTRA_SIGS.update({
     "mappo_gae_returns": [C.POINTER(GaeConfig), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
@@ -48,10 +87,11 @@ def gae_returns(rewards, value_preds, returns, masks, next_value, gamma, gae_lam
         stats3 = torch.empty(3, dtype=torch.float64, device=dev)
     cfg = GaeConfig(T, R, float(gamma), float(gamma * gae_lambda), int(use_gae), int(use_proper_time_limits),
                     int(vn_stats is not None), 0)
-    check(L.mappo_gae_returns(C.byref(cfg), ptr(_f32c(rewards, "rewards")), ptr(_f32c(value_preds, "value_preds")),
-                              ptr(_f32c(returns, "returns")), ptr(_f32c(masks, "masks")),
-                              ptr(bad_masks), ptr(active_masks), ptr(next_value), ptr(vn_stats),
-                              ptr(advantages_raw), ptr(partials), stream_ptr()), "gae_returns")
+    with TIMERS.span("gae_returns"):
+        check(L.mappo_gae_returns(C.byref(cfg), ptr(_f32c(rewards, "rewards")), ptr(_f32c(value_preds, "value_preds")),
+                                  ptr(_f32c(returns, "returns")), ptr(_f32c(masks, "masks")),
+                                  ptr(bad_masks), ptr(active_masks), ptr(next_value), ptr(vn_stats),
+                                  ptr(advantages_raw), ptr(partials), stream_ptr()), "gae_returns")
     check(L.mappo_adv_stats_reduce(ptr(partials), nparts, ptr(stats3), stream_ptr()), "adv_stats_reduce")
     if all_reduce is not None:
         all_reduce(stats3)
@@ -157,10 +197,11 @@ def _vp(t):
 def actor_forward(cfg, params, obs, actions_out, logp_out, available_actions=None, deterministic=False, seed=0,
                   step=0, row_offset=0, given_actions=None, entropy_out=None):
     obs, ld = _rows_view(obs)
-    check(_lib.lib().mappo_actor_forward(C.byref(cfg), ptr(params), _vp(obs), ld, obs.shape[0],
-                                         ptr(available_actions), int(deterministic), int(seed) & (2 ** 64 - 1),
-                                         int(step), int(row_offset), ptr(given_actions), ptr(actions_out),
-                                         ptr(logp_out), ptr(entropy_out), stream_ptr()), "actor_forward")
+    with TIMERS.span("actor_forward"):
+        check(_lib.lib().mappo_actor_forward(C.byref(cfg), ptr(params), _vp(obs), ld, obs.shape[0],
+                                             ptr(available_actions), int(deterministic), int(seed) & (2 ** 64 - 1),
+                                             int(step), int(row_offset), ptr(given_actions), ptr(actions_out),
+                                             ptr(logp_out), ptr(entropy_out), stream_ptr()), "actor_forward")
 
 
 def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=None, all_reduce=None):
@@ -184,8 +225,9 @@ def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=No
 def critic_forward(cfg, params, share_obs, values_out, group=1):
     x, ld = _rows_view(share_obs)
     assert values_out.numel() == x.shape[0] * group
-    check(_lib.lib().mappo_critic_forward(C.byref(cfg), ptr(params), _vp(x), ld, x.shape[0], int(group),
-                                          ptr(values_out), stream_ptr()), "critic_forward")
+    with TIMERS.span("critic_forward"):
+        check(_lib.lib().mappo_critic_forward(C.byref(cfg), ptr(params), _vp(x), ld, x.shape[0], int(group),
+                                              ptr(values_out), stream_ptr()), "critic_forward")
 
 
 def update_num_blocks(rows):
@@ -196,19 +238,22 @@ def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, a
                  loss_partials, index=None):
     obs, ld = _rows_view(obs)
     rows = obs.shape[0] if index is None else index.numel()
-    check(_lib.lib().mappo_actor_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(obs), ld, rows, ptr(index),
-                                        ptr(actions), ptr(old_logp), ptr(adv), ptr(active_masks),
-                                        ptr(available_actions), ptr(grad_partials), ptr(loss_partials), stream_ptr()),
-          "actor_update")
+    with TIMERS.span("actor_update"):
+        check(_lib.lib().mappo_actor_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(obs), ld, rows, ptr(index),
+                                            ptr(actions), ptr(old_logp), ptr(adv), ptr(active_masks),
+                                            ptr(available_actions), ptr(grad_partials), ptr(loss_partials),
+                                            stream_ptr()), "actor_update")
 
 
 def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_masks, vn_stats, grad_partials,
                   loss_partials, group=1, index=None, share_rows_div=1):
     x, ld = _rows_view(share_obs)
     rows = x.shape[0] if index is None else index.numel()
-    check(_lib.lib().mappo_critic_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, rows, int(group),
-                                         ptr(index), int(share_rows_div), ptr(value_preds), ptr(returns), ptr(active_masks), ptr(vn_stats),
-                                         ptr(grad_partials), ptr(loss_partials), stream_ptr()), "critic_update")
+    with TIMERS.span("critic_update"):
+        check(_lib.lib().mappo_critic_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, rows, int(group),
+                                             ptr(index), int(share_rows_div), ptr(value_preds), ptr(returns),
+                                             ptr(active_masks), ptr(vn_stats), ptr(grad_partials), ptr(loss_partials),
+                                             stream_ptr()), "critic_update")
 
 
 def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):

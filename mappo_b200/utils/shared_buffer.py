@@ -36,7 +36,7 @@ def _act_shape(space):
 def _dev(x, device):
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(x)
-    return x.to(device=device, dtype=torch.float32)
+    return x.to(device=device, dtype=torch.float32, non_blocking=True)
 
 
 class SharedReplayBuffer(object):

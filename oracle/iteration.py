@@ -1,0 +1,187 @@
+"""ORACLE (test infrastructure, not product code): one whole MAPPO iteration on the CPU, assembled from the
+oracle pieces -- the reference's driver loop restated over the batched oracle env:
+
+  MPERunner.run / warmup / collect / insert     onpolicy/runner/shared/mpe_runner.py:16-139
+  Runner.compute / train                        onpolicy/runner/shared/base_runner.py:110-125
+  R_MAPPO.train / ppo_update                    onpolicy/algorithms/r_mappo/r_mappo.py:91-219
+  SharedReplayBuffer.insert / after_update      onpolicy/utils/shared_buffer.py:79-159
+
+Shared MLP policy (BASELINE configs C1 / C2 / C5).  Env maths: oracle/mpe.py (numpy f64); networks, losses, clipping
+and Adam: oracle/policy.py (torch CPU f32 + autograd); returns / advantages / ValueNorm: oracle/buffer.py.
+Used by tests/ (trajectory-level parity of the CUDA path) and by bench.py's `cpu_baseline` / `--impl reference`
+legs, where it is the thing timed on the host cores ("port" of the reference's CPU path).  Never imported by
+the product package.
+"""
+import numpy as np
+import torch
+
+from . import buffer as ob
+from . import policy as op
+from .mpe import OracleMPE
+
+
+class OracleMAPPO:
+    def __init__(self, args, actor_sd, critic_sd, num_envs=None, seed=None, env_id_offset=0, sample_seed=None):
+        """args: the reference's flag namespace.  actor_sd / critic_sd: reference-keyed state dicts (CPU tensors);
+        they are cloned and trained in place of nn.Modules."""
+        self.a = args
+        self.N = int(num_envs if num_envs is not None else args.n_rollout_threads)
+        self.M, self.L, self.T = args.num_agents, args.num_landmarks, args.episode_length
+        seed = int(args.seed if seed is None else seed)
+        self.sample_seed = int(seed if sample_seed is None else sample_seed)
+        self.env = OracleMPE(args.scenario_name, self.N, self.M, self.L, self.T, seed=seed,
+                             env_id_offset=env_id_offset)
+        self.row_offset = env_id_offset * self.M
+        self.actor = {k: v.detach().clone().float() for k, v in actor_sd.items()}
+        self.critic = {k: v.detach().clone().float() for k, v in critic_sd.items()}
+        self.akeys = [k for k in self.actor if "fc_h" not in k]
+        self.ckeys = [k for k in self.critic if "fc_h" not in k]
+        self.adam = {"actor": {}, "critic": {}}
+        self.adam_step = {"actor": 0, "critic": 0}
+        self.vn = ob.OracleValueNorm() if args.use_valuenorm else None
+        N, M, T = self.N, self.M, self.T
+        D = self.env.spec.obs_dims[0]
+        self.D, self.S = D, D * M
+        f = np.float32
+        self.obs = np.zeros((T + 1, N, M, D), f)
+        self.value_preds = np.zeros((T + 1, N, M, 1), f)
+        self.returns = np.zeros((T + 1, N, M, 1), f)
+        self.masks = np.ones((T + 1, N, M, 1), f)
+        self.active_masks = np.ones((T + 1, N, M, 1), f)
+        self.actions = np.zeros((T, N, M, 1), f)
+        self.action_log_probs = np.zeros((T, N, M, 1), f)
+        self.rewards = np.zeros((T, N, M, 1), f)
+        self.calls = 0
+
+    # ------------------------------------------------------------------ rollout
+    def _stack_obs(self, obs_list):
+        return np.stack(obs_list, axis=1).astype(np.float32)            # [N, M, D]
+
+    def share_obs_of(self, obs):
+        """mpe_runner.py:133-137: concat of all agents' obs, repeated for every agent -> [N, M, S]"""
+        N, M = obs.shape[0], obs.shape[1]
+        return np.repeat(obs.reshape(N, 1, -1), M, axis=1)
+
+    def warmup(self, state=None):
+        self.obs[0] = self._stack_obs(self.env.reset(state))
+
+    @torch.no_grad()
+    def collect(self, step):
+        a = self.a
+        N, M = self.N, self.M
+        obs = self.obs[step].reshape(N * M, -1)
+        sh = self.share_obs_of(self.obs[step]).reshape(N * M, -1)
+        z = np.zeros((N * M, 1, a.hidden_size), np.float32)
+        ones = np.ones((N * M, 1), np.float32)
+        feats, _ = op.actor_features(self.actor, obs, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        logits = op.actor_logits(self.actor, feats, None)
+        acts, lps, _ = op.act_forward(logits, False, seed=self.sample_seed, step=self.calls,
+                                      row_offset=self.row_offset)
+        self.calls += 1
+        values, _ = op.critic_values(self.critic, sh, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, 1), lps.numpy().reshape(N, M, 1)
+
+    def rollout(self):
+        for step in range(self.T):
+            values, actions, logp = self.collect(step)
+            obs, rewards, dones, _ = self.env.step(actions)
+            self.obs[step + 1] = self._stack_obs(obs)
+            self.actions[step] = actions
+            self.action_log_probs[step] = logp
+            self.value_preds[step] = values
+            self.rewards[step] = rewards
+            m = np.ones((self.N, self.M, 1), np.float32)
+            m[dones] = 0.0
+            self.masks[step + 1] = m
+
+    # ------------------------------------------------------------------ compute + train
+    @torch.no_grad()
+    def compute(self):
+        a = self.a
+        N, M = self.N, self.M
+        sh = self.share_obs_of(self.obs[-1]).reshape(N * M, -1)
+        z = np.zeros((N * M, 1, a.hidden_size), np.float32)
+        nv, _ = op.critic_values(self.critic, sh, z, np.ones((N * M, 1), np.float32), a.use_ReLU,
+                                 a.use_feature_normalization, False)
+        vp, ret = ob.compute_returns(self.rewards, self.value_preds, self.masks, nv.numpy().reshape(N, M, 1), a.gamma,
+                                     a.gae_lambda, a.use_gae, a.use_proper_time_limits, None, self.vn)
+        self.value_preds, self.returns = vp, ret
+
+    def _step_net(self, name, sd, keys, grads, lr):
+        a = self.a
+        if a.use_max_grad_norm:
+            norm, grads = op.clip_grad_norm(grads, a.max_grad_norm)
+        else:
+            norm = torch.sqrt(sum((g ** 2).sum() for g in grads))
+        self.adam_step[name] += 1
+        st = self.adam[name]
+        for k, g in zip(keys, grads):
+            m, v = st.get(k, (torch.zeros_like(g), torch.zeros_like(g)))
+            p, m, v = op.adam_step(sd[k].detach(), g, m, v, self.adam_step[name], lr, a.opti_eps,
+                                   weight_decay=a.weight_decay)
+            sd[k] = p
+            st[k] = (m, v)
+        return float(norm)
+
+    def ppo_update(self, rows, adv):
+        """r_mappo.py:91-164 on the flat rows `rows` (None = all, in storage order)."""
+        a = self.a
+        T, N, M = self.T, self.N, self.M
+        B = T * N * M
+        take = (lambda x: x) if rows is None else (lambda x: x[rows])
+        obs = take(self.obs[:-1].reshape(B, -1))
+        sh = take(np.stack([self.share_obs_of(o) for o in self.obs[:-1]]).reshape(B, -1))
+        actions = take(self.actions.reshape(B, -1))
+        old_lp = take(self.action_log_probs.reshape(B, -1))
+        advb = take(adv.reshape(B, 1))
+        vp = take(self.value_preds[:-1].reshape(B, 1))
+        ret = take(self.returns[:-1].reshape(B, 1))
+        am = take(self.active_masks[:-1].reshape(B, 1))
+        nb = obs.shape[0]
+        z = np.zeros((nb, 1, a.hidden_size), np.float32)
+        ones = np.ones((nb, 1), np.float32)
+        asd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.actor.items()}
+        csd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.critic.items()}
+        feats, _ = op.actor_features(asd, obs, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        logits = op.actor_logits(asd, feats, None)
+        logp, ent = op.evaluate_actions(logits, actions, am if a.use_policy_active_masks else None)
+        values, _ = op.critic_values(csd, sh, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        pl, ratio = op.policy_loss(logp, old_lp, advb, am, a.clip_param, a.use_policy_active_masks)
+        agrads = torch.autograd.grad(pl - ent * a.entropy_coef, [asd[k] for k in self.akeys])
+        an = self._step_net("actor", self.actor, self.akeys, agrads, a.lr)
+        vl = op.value_loss(values, vp, ret, am, a.clip_param, self.vn, a.use_huber_loss, a.huber_delta,
+                           a.use_clipped_value_loss, a.use_value_active_masks)
+        cgrads = torch.autograd.grad(vl * a.value_loss_coef, [csd[k] for k in self.ckeys])
+        cn = self._step_net("critic", self.critic, self.ckeys, cgrads, a.critic_lr)
+        self.actor = {k: v.detach() for k, v in self.actor.items()}
+        self.critic = {k: v.detach() for k, v in self.critic.items()}
+        return dict(value_loss=vl.item(), critic_grad_norm=cn, policy_loss=pl.item(), dist_entropy=ent.item(),
+                    actor_grad_norm=an, ratio=ratio.mean().item())
+
+    def train(self, permute=False):
+        """r_mappo.py:166-219.  permute=False: num_mini_batch == 1 in storage order (the loss is a mean; the
+        reference's randperm only reorders it); permute=True draws torch.randperm like the reference."""
+        a = self.a
+        _, adv = ob.advantages(self.returns, self.value_preds, self.active_masks, self.vn)
+        B = self.T * self.N * self.M
+        info = None
+        n = 0
+        for _ in range(a.ppo_epoch):
+            if a.num_mini_batch == 1 and not permute:
+                batches = [None]
+            else:
+                batches = ob.feed_forward_rows(self.T, self.N, self.M, torch.randperm(B).numpy(), a.num_mini_batch)
+            for rows in batches:
+                r = self.ppo_update(rows, adv)
+                info = r if info is None else {k: info[k] + r[k] for k in r}
+                n += 1
+        # after_update, shared_buffer.py:149-159
+        self.obs[0] = self.obs[-1]
+        self.masks[0] = self.masks[-1]
+        self.active_masks[0] = self.active_masks[-1]
+        return {k: v / n for k, v in info.items()}
+
+    def iteration(self):
+        self.rollout()
+        self.compute()
+        return self.train()
