@@ -294,6 +294,17 @@ int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, 
 int mappo_gather_rows(const float* src, long long row_stride, int row_div, int width, const int64_t* index,
                       long long n, float* dst, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 5. Hardware self-test of the tcgen05 (5th-gen tensor core) operand layouts the policy kernels rely on: stages
+ *    tiles A [a_rows][a_cols] and B [b_rows][b_cols] (fp32, tf32-representable values) in the library's
+ *    shared-memory layout, issues `tcgen05.mma` instructions (M = 128; kind::tf32 with K = 8 per instruction, or kind::f16 on bf16 with
+ *    K = 16 when use_bf16 != 0) with the given descriptor
+ *    strides and writes the fp32 accumulator D [128][N] back.  No reference counterpart (test infrastructure).
+ * ---------------------------------------------------------------------------------------------- */
+int mappo_selftest_umma(const float* A, int a_rows, int a_cols, const float* B, int b_rows, int b_cols, int M, int N,
+                        int K, int a_mn_major, int b_mn_major, uint32_t a_lbo, uint32_t a_sbo, uint32_t a_kstep,
+                        uint32_t b_lbo, uint32_t b_sbo, uint32_t b_kstep, float* D, int use_bf16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
