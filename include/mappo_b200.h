@@ -228,15 +228,15 @@ typedef struct {
   int32_t reserved;
 } mappo_loss_config;
 
-/* number of thread blocks (= partial rows) the update kernels use for `rows` rows on the current device */
-int mappo_update_num_blocks(long long rows);
+/* number of partial rows the update kernels write for `rows` rows of network `cfg` on the current device */
+int mappo_update_num_blocks(const mappo_net_config* cfg, long long rows);
 
 /* Actor: forward + clipped-surrogate/entropy loss + backward over one minibatch (r_mappo.py:115-141).
  *   index: int64 [rows] row gather into the flat buffers (the minibatch permutation,
  *          shared_buffer.py:246-247), or NULL for the identity (num_mini_batch == 1: the loss is a mean,
  *          so the order only changes the summation order).
  *   actions, old_logp [*][n_heads]; adv [*]; active_masks [*] or NULL.
- * Outputs, one row per block b < mappo_update_num_blocks(rows), UNNORMALISED sums (the 1/sum(active) factor,
+ * Outputs, one row per partial b < mappo_update_num_blocks(cfg, rows), UNNORMALISED sums (the 1/sum(active) factor,
  * the LayerNorm-affine chain rule and the global sum over blocks and ranks are applied by
  * mappo_grad_reduce / mappo_adam_step):
  *   grad_partials float32 [blocks][P];

@@ -63,7 +63,8 @@ class R_MAPPO:
         ws = self._ws.get(key)
         if ws is None:
             Pa, Pc = self.policy.actor.flat.numel(), self.policy.critic.flat.numel()
-            nba, nbc = ops.update_num_blocks(rows_a), ops.update_num_blocks(rows_c)
+            nba = ops.update_num_blocks(self.policy.actor.cfg, rows_a)
+            nbc = ops.update_num_blocks(self.policy.critic.cfg, rows_c)
             dev = self.device
             ws = dict(nba=nba, nbc=nbc,
                       gpa=torch.empty(nba, Pa, dtype=torch.float32, device=dev),

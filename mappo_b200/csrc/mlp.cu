@@ -7,6 +7,16 @@
 //            r_mappo.py:52-136 (losses), utils/util.py:23-29 (huber/mse).
 // See net.cuh for the LayerNorm-affine folding used here.
 #include "mlp_rows.cuh"
+#include <stdlib.h>
+#include <string.h>
+
+namespace mappo {
+namespace tc {   // mlp_tc.cu: the tcgen05 tensor-core tiles
+bool supports(const mappo_net_config* cfg);
+int grid_for(long long rows);
+template <int MODE> int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who);
+}  // namespace tc
+}  // namespace mappo
 
 namespace mappo {
 
@@ -413,12 +423,23 @@ static int blocks_for(long long rows) {
   return (int)(ntiles < sms ? (ntiles < 1 ? 1 : ntiles) : sms);
 }
 
+// MAPPO_MLP_IMPL=fma selects the fp32 FMA tiles of this file (kept for A/B measurements); default: tensor cores
+static bool use_tc(const mappo_net_config* cfg) {
+  static int forced_fma = -1;
+  if (forced_fma < 0) {
+    const char* e = getenv("MAPPO_MLP_IMPL");
+    forced_fma = (e && strcmp(e, "fma") == 0) ? 1 : 0;
+  }
+  return !forced_fma && tc::supports(cfg);
+}
+
 template <int MODE>
 static int launch_mlp(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
   if (int rc = check_net(cfg, who)) return rc;
   if (cfg->recurrent) MAPPO_UNSUPPORTED("%s: recurrent (GRU) networks are not built yet", who);
   if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d not built yet", who, cfg->in_dim, kMaxIn);
   MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim, "%s: bad input arguments", who);
+  if (use_tc(cfg)) return tc::launch<MODE>(a, cfg, stream, who);
   a.L = make_layout(*cfg);
   if (a.x_div < 1) a.x_div = 1;
   a.Kp = (cfg->in_dim + 3) & ~3;
@@ -444,7 +465,10 @@ extern "C" long long mappo_net_param_count(const mappo_net_config* cfg) {
   return make_layout(*cfg).total;
 }
 
-extern "C" int mappo_update_num_blocks(long long rows) { return blocks_for(rows); }
+extern "C" int mappo_update_num_blocks(const mappo_net_config* cfg, long long rows) {
+  if (use_tc(cfg)) return 2 * tc::grid_for(rows);          // two partial rows per CTA (hi / lo operand halves)
+  return blocks_for(rows);
+}
 
 extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
                                    long long rows, const float* available_actions, int deterministic, uint64_t seed,

@@ -1,0 +1,596 @@
+// Fused MLP actor / critic kernels on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a only.
+//
+// One persistent CTA per SM (512 threads) walks tiles of 128 rows.  Every dense contraction of the tile -- fc1, fc2,
+// the data gradient through fc2, and the three weight gradients -- is a `tcgen05.mma.kind::f16` on fp16 operand
+// PAIRS: each fp32 operand x is carried as hi = fp16(x) and lo = fp16((x - hi) * 2^12) -- 22 significant bits, and
+// an absolute resolution of 2^-36 below the fp16 normal range; valid for |x| < 65504, which LayerNorm outputs
+// (|n| <= sqrt(63)), folded weights and per-sample gradients satisfy -- and the products hi*hi and
+// (hi*lo + lo*hi) accumulate in fp32 in two tensor-memory accumulators that the epilogue combines as
+// acc0 + 2^-12 acc1 (the weight gradients keep all four products in separate accumulator blocks).
+// Operands live in shared memory in the chunk-major layout of umma.cuh, where the same bytes serve as the K-major
+// operand of the forward / data-gradient GEMMs and as the MN-major operand of the weight-gradient GEMMs, so every
+// activation is written to shared memory exactly once.  Everything between the GEMMs (bias, tanh / ReLU,
+// LayerNorm and their derivatives, the categorical head, the PPO losses) runs in fp32 registers: thread
+// (row r, column quarter c) owns 16 of the 64 hidden columns of its row and reads them straight out of TMEM.
+// Weight gradients accumulate in TMEM across all tiles of the CTA and leave the kernel once.
+//
+// Reference: mlp.py:6-59, act.py:41-162, distributions.py:14-68, r_actor_critic.py:43-107,146-165,
+//            r_mappo.py:52-136, utils/util.py:23-29.  LayerNorm-affine folding: net.cuh.
+#include "mlp_rows.cuh"
+#include "umma.cuh"
+#include <cuda_fp16.h>
+
+namespace mappo {
+namespace tc {
+
+constexpr int kThreads = 512, kBM = 128, kNP = 2;
+constexpr int kTmemCols = 512;
+constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 256, kColGh = 384;   // TMEM column map
+constexpr float kLoScale = 4096.0f, kLoInv = 1.0f / 4096.0f;            // the lo halves are stored times 2^12
+constexpr uint32_t kRowChunk = kBM * 16;                                 // bytes of one 8-column chunk of a 128-row tile
+constexpr uint32_t kWChunk = 64 * 16;                                    // ... of a 64-row weight tile
+
+// shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
+struct Map {
+  uint32_t X, N1, BS, W1, W2, DL, Whf, b1f, b2f, bhf, dlog, dbh, xch, xlog, red, bars, total;
+  uint32_t x_piece, w1_piece;
+};
+__host__ __device__ inline Map make_map(int Kp, int AS) {
+  Map m;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.x_piece = (uint32_t)(Kp / 8) * kRowChunk;
+  m.w1_piece = (uint32_t)(Kp / 8) * kWChunk;
+  m.X = take(kNP * m.x_piece);
+  m.N1 = take(kNP * 8 * kRowChunk);
+  m.BS = take(kNP * 8 * kRowChunk);
+  m.W1 = take(kNP * m.w1_piece);
+  m.W2 = take(kNP * 8 * kWChunk);
+  m.DL = take(kNP * 2 * kRowChunk);
+  m.Whf = take(kMaxA * 64 * 4);
+  m.b1f = take(64 * 4);
+  m.b2f = take(64 * 4);
+  m.bhf = take(kMaxA * 4);
+  m.dlog = take(kBM * kDL * 4);
+  m.dbh = take(kBM * kDL * 4);
+  m.xch = take(2 * 4 * kBM * 8);
+  m.xlog = take(4 * kBM * AS * 4);
+  m.red = take(16 * 16 * 4 * 2);
+  m.bars = take(64);
+  m.total = o;
+  return m;
+}
+
+// ---- small device helpers -----------------------------------------------------------------------------
+__device__ __forceinline__ void bar_named(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+// tanh in fp32: 1 - 2 / (exp(2|x|) + 1) with ex2.approx / rcp.approx (absolute error ~1.5e-7)
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float ax = fabsf(x);
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * 2.885390081777927f));   // 2 * log2(e)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+  return copysignf(fmaf(-2.0f, r, 1.0f), x);
+}
+__device__ __forceinline__ float act_tc(float z, int relu) { return relu ? fmaxf(z, 0.0f) : tanh_fast(z); }
+
+// 8 consecutive fp32 -> one 16-byte chunk of fp16 `hi` and one of (scaled) `lo`
+__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    const float2 hf = __half22float2(hh);
+    const __half2 ll = __floats2half2_rn((v[2 * i] - hf.x) * kLoScale, (v[2 * i + 1] - hf.y) * kLoScale);
+    h[i] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[i] = *reinterpret_cast<const uint32_t*>(&ll);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// store this thread's 16 columns [16*cq, 16*cq+16) of row r into a 128-row, 64-column operand tile (both pieces)
+__device__ __forceinline__ void store_cols16(unsigned char* tile, int r, int cq, const float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint4 hi, lo;
+    split8(v + 8 * h, hi, lo);
+    const uint32_t off = (uint32_t)(2 * cq + h) * kRowChunk + (uint32_t)r * 16;
+    *reinterpret_cast<uint4*>(tile + off) = hi;
+    *reinterpret_cast<uint4*>(tile + 8 * kRowChunk + off) = lo;
+  }
+}
+
+// sum (a, b) over the 4 threads that share a row; `slot` alternates between two exchange buffers
+__device__ __forceinline__ float2 row_sum2(float a, float b, float2* xch, int& slot, int cq, int r, int q4) {
+  float2* buf = xch + slot * (4 * kBM);
+  buf[cq * kBM + r] = make_float2(a, b);
+  bar_named(1 + q4, 128);
+  const float2 p0 = buf[r], p1 = buf[kBM + r], p2 = buf[2 * kBM + r], p3 = buf[3 * kBM + r];
+  slot ^= 1;
+  return make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+}
+
+// ---- prologue: fold the LayerNorm affines into the following Linear (net.cuh), split into fp16 pairs, stage
+__device__ __forceinline__ void put_pair(unsigned char* tile, uint32_t piece, int R, int r, int c, float v) {
+  const __half hi = __float2half_rn(v);
+  const __half lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
+  const uint32_t off = umma::tile_off16(R, r, c);
+  *reinterpret_cast<__half*>(tile + off) = hi;
+  *reinterpret_cast<__half*>(tile + piece + off) = lo;
+}
+
+__device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a) {
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  const int D = L.in_dim, Kp = a.Kp, tid = threadIdx.x;
+  for (int e = tid; e < 64 * Kp; e += kThreads) {
+    const int j = e / Kp, k = e - j * Kp;
+    float v = 0.0f;
+    if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+    put_pair(sm + m.W1, m.w1_piece, 64, j, k, v);
+  }
+  for (int e = tid; e < 64 * 64; e += kThreads) {
+    const int j = e >> 6, k = e & 63;
+    put_pair(sm + m.W2, 8 * kWChunk, 64, j, k, P[L.w2 + j * 64 + k] * P[L.g1 + k]);
+  }
+  float* Whf = reinterpret_cast<float*>(sm + m.Whf);
+  for (int e = tid; e < kMaxA * 64; e += kThreads) {
+    const int aidx = e >> 6, k = e & 63;
+    float v = 0.0f;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    if (h < L.n_heads) v = P[L.wh[h] + (aidx - off) * 64 + k] * P[L.g2 + k];
+    Whf[aidx * 64 + k] = v;
+  }
+  if (tid < 64) {
+    const int j = tid;
+    float s1 = P[L.b1 + j];
+    if (L.use_fn) for (int k = 0; k < D; ++k) s1 = fmaf(P[L.w1 + j * D + k], P[L.fn_b + k], s1);
+    reinterpret_cast<float*>(sm + m.b1f)[j] = s1;
+    float s2 = P[L.b2 + j];
+    for (int k = 0; k < 64; ++k) s2 = fmaf(P[L.w2 + j * 64 + k], P[L.be1 + k], s2);
+    reinterpret_cast<float*>(sm + m.b2f)[j] = s2;
+  } else if (tid < 64 + kMaxA) {
+    const int aidx = tid - 64;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    float s = 0.0f;
+    if (h < L.n_heads) {
+      s = P[L.bh[h] + (aidx - off)];
+      for (int k = 0; k < 64; ++k) s = fmaf(P[L.wh[h] + (aidx - off) * 64 + k], P[L.be2 + k], s);
+    }
+    reinterpret_cast<float*>(sm + m.bhf)[aidx] = s;
+  }
+  float* dbh = reinterpret_cast<float*>(sm + m.dbh);
+  for (int e = tid; e < kBM * kDL; e += kThreads) dbh[e] = 0.0f;
+}
+
+// ---- MMA issue (one thread) ------------------------------------------------------------------------------
+// forward-type GEMM: ACC0[128][64] = A_hi . B_hi^T, ACC1 = A_hi . B_lo^T + A_lo . B_hi^T; A K-major 128-row tile
+__device__ __forceinline__ void issue_rowgemm(uint32_t acc0, uint32_t acc1, uint32_t a_base, uint32_t a_piece,
+                                              uint32_t b_base, uint32_t b_piece, uint32_t b_lbo, uint32_t b_sbo,
+                                              uint32_t b_kstep, int ksteps, uint32_t idesc) {
+  for (int ks = 0; ks < ksteps; ++ks) {
+    const uint32_t ao = a_base + (uint32_t)ks * 2 * kRowChunk, bo = b_base + (uint32_t)ks * b_kstep;
+    const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + a_piece, kRowChunk, 128);
+    const uint64_t bh = umma::smem_desc(bo, b_lbo, b_sbo), bl = umma::smem_desc(bo + b_piece, b_lbo, b_sbo);
+    umma::mma_f16(acc0, ah, bh, idesc, ks > 0);
+    umma::mma_f16(acc1, ah, bl, idesc, ks > 0);
+    umma::mma_f16(acc1, al, bh, idesc, true);
+  }
+}
+// weight-gradient GEMM: G[128 = (hi cols | lo cols) of A][N] += A^T . B over the 128 tile rows; both MN-major
+__device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a_base, uint32_t b_base, uint32_t idesc, bool accum) {
+#pragma unroll
+  for (int ks = 0; ks < kBM / 16; ++ks) {
+    const uint64_t da = umma::smem_desc(a_base + (uint32_t)ks * 256, 128, kRowChunk);
+    const uint64_t db = umma::smem_desc(b_base + (uint32_t)ks * 256, 128, kRowChunk);
+    umma::mma_f16(g, da, db, idesc, accum || ks > 0);
+  }
+}
+
+// this thread's 16 accumulator columns: acc0 + 2^-12 acc1
+__device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16]) {
+  float w[16];
+  umma::tmem_ld16(lane_addr + kColAcc + 16 * cq, v);
+  umma::tmem_ld16(lane_addr + kColAcc1 + 16 * cq, w);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
+}
+
+// activation -> LayerNorm (no affine) of this thread's 16 columns; returns n in t[], (mean, rstd) of the row
+__device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict__ bias, int relu, float2* xch, int& slot,
+                                         int cq, int r, int q4, float& mean, float& rstd) {
+  float s = 0.0f, q = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    t[i] = act_tc(t[i] + bias[i], relu);
+    s += t[i];
+    q = fmaf(t[i], t[i], q);
+  }
+  const float2 tot = row_sum2(s, q, xch, slot, cq, r, q4);
+  mean = tot.x * (1.0f / 64.0f);
+  const float var = fmaxf(fmaf(-mean, mean, tot.y * (1.0f / 64.0f)), 0.0f);
+  rstd = 1.0f / sqrtf(var + kLnEps);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) t[i] = (t[i] - mean) * rstd;
+}
+
+// dn (gradient w.r.t. the LayerNorm output n) -> dz (gradient w.r.t. the pre-activation), in place
+__device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[16], float mean, float rstd, int relu,
+                                             float2* xch, int& slot, int cq, int r, int q4) {
+  float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { s1 += dn[i]; s2 = fmaf(dn[i], n[i], s2); }
+  const float2 tot = row_sum2(s1, s2, xch, slot, cq, r, q4);
+  s1 = tot.x * (1.0f / 64.0f); s2 = tot.y * (1.0f / 64.0f);
+  const float sd = 1.0f / rstd, nz = (0.0f - mean) * rstd;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float da;
+    if (relu) da = (n[i] != nz) ? 1.0f : 0.0f;            // t == 0  <=>  n == (0 - mean) * rstd, bit for bit
+    else { const float t = fmaf(n[i], sd, mean); da = fmaf(-t, t, 1.0f); }
+    dn[i] = rstd * (dn[i] - s1 - n[i] * s2) * da;
+  }
+}
+
+// ---- the kernel ------------------------------------------------------------------------------------------
+// MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic.  KP: padded input width (32 | 64).
+template <int MODE, int KP>
+__global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
+  constexpr bool UPDATE = (MODE >= 2);
+  constexpr int XC = KP / 4;                         // input columns per thread
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ double lred[4][kThreads / 32];
+  const NetLayout& L = a.L;
+  const int A = L.a_total, relu = L.use_relu, D = L.in_dim, AS = A | 1;
+  const Map m = make_map(KP, AS);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + m.bars);          // [0] ACC ready, [1] head wgrad done, [2] wgrad1 done
+  if (tid == 0) {
+    umma::mbar_init(&bars[0], 1); umma::mbar_init(&bars[1], 1); umma::mbar_init(&bars[2], 1);
+    umma::fence_mbar_init();
+  }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
+  stage_weights_tc(sm, m, a);
+  umma::fence_async_smem();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+  const uint32_t sX = umma::smem_u32(sm + m.X), sN1 = umma::smem_u32(sm + m.N1), sBS = umma::smem_u32(sm + m.BS);
+  const uint32_t sW1 = umma::smem_u32(sm + m.W1), sW2 = umma::smem_u32(sm + m.W2), sDL = umma::smem_u32(sm + m.DL);
+  float2* xch = reinterpret_cast<float2*>(sm + m.xch);
+  float* xlog = reinterpret_cast<float*>(sm + m.xlog);
+  float* dlog = reinterpret_cast<float*>(sm + m.dlog);
+  const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
+  const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
+  const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
+  const float* bhf = reinterpret_cast<const float*>(sm + m.bhf);
+  constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
+  constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
+  constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
+
+  int slot = 0;
+  uint32_t ph_acc = 0, ph_gh = 0, ph_x = 0;
+  bool first = true;
+  float db1[16], db2[16];
+  double lacc[4] = {0.0, 0.0, 0.0, 0.0};
+  if (UPDATE) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) db1[i] = db2[i] = 0.0f;
+  }
+
+  for (long long tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+    const long long g = tile * kBM + r;
+    const bool valid = g < a.rows;
+    // ---- input rows: gather, LayerNorm over in_dim (mlp.py:44-45), fp16 pairs -> X
+    {
+      float xv[XC];
+      const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+      const float* __restrict__ row = a.x + srow * (long long)a.ld;
+#pragma unroll
+      for (int i = 0; i < XC; ++i) {
+        const int c = XC * cq + i;
+        xv[i] = (valid && c < D) ? __ldg(row + c) : 0.0f;
+      }
+      if (L.use_fn) {
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < XC; ++i) s += xv[i];
+        const float mean = row_sum2(s, 0.0f, xch, slot, cq, r, q4).x / (float)D;
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < XC; ++i) {
+          xv[i] = (XC * cq + i < D) ? xv[i] - mean : 0.0f;
+          q = fmaf(xv[i], xv[i], q);
+        }
+        const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
+#pragma unroll
+        for (int i = 0; i < XC; ++i) xv[i] *= rstd;
+      }
+      if (UPDATE && !first) { umma::mbar_wait(&bars[2], ph_x); ph_x ^= 1; }      // wgrad1 of the previous tile read X
+#pragma unroll
+      for (int h = 0; h < XC / 8; ++h) {
+        uint4 hi, lo;
+        split8(xv + 8 * h, hi, lo);
+        const uint32_t off = (uint32_t)(XC / 8 * cq + h) * kRowChunk + (uint32_t)r * 16;
+        *reinterpret_cast<uint4*>(sm + m.X + off) = hi;
+        *reinterpret_cast<uint4*>(sm + m.X + m.x_piece + off) = lo;
+      }
+    }
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX, m.x_piece, sW1, m.w1_piece, kWChunk, 128, 2 * kWChunk, KP / 16, kIdFwd);
+      umma::mma_commit(&bars[0]);
+    }
+    // ---- layer 1 epilogue
+    float n1[16], mean1, rstd1;
+    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::tc_fence_after();
+    load_acc16(lane_addr, cq, n1);
+    act_ln16(n1, b1f, relu, xch, slot, cq, r, q4, mean1, rstd1);
+    store_cols16(sm + m.N1, r, cq, n1);
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk, sW2, 8 * kWChunk, kWChunk, 128, 2 * kWChunk, 4, kIdFwd);
+      umma::mma_commit(&bars[0]);
+    }
+    // ---- layer 2 epilogue + head
+    float n2[16], mean2, rstd2;
+    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::tc_fence_after();
+    load_acc16(lane_addr, cq, n2);
+    act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
+    if (UPDATE) store_cols16(sm + m.BS, r, cq, n2);
+    {
+      float* mine = xlog + (size_t)(cq * kBM + r) * AS;
+#pragma unroll
+      for (int q = 0; q < kMaxA; ++q) {
+        if (q < A) {
+          const float* w = Whf + q * 64 + 16 * cq;
+          float s = 0.0f;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) s = fmaf(n2[i], w[i], s);
+          mine[q] = s;
+        }
+      }
+    }
+    bar_named(1 + q4, 128);
+    if (cq == 0) {
+      float l[kMaxA];
+#pragma unroll
+      for (int q = 0; q < kMaxA; ++q) {
+        l[q] = 0.0f;
+        if (q < A) {
+          const float* p = xlog + (size_t)r * AS + q;
+          l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
+        }
+      }
+      const long long src = (valid && a.index) ? a.index[g] : g;
+      if (MODE == 0 && valid) actor_rollout_row(a, g, l);
+      if (MODE == 1 && valid) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
+      if (UPDATE) {
+        float* dl = dlog + r * kDL;
+        if (valid) {
+          if (MODE == 2) actor_loss_row(a, src, l, dl, lacc);
+          if (MODE == 3) {
+            dl[0] = critic_loss_row(a, src, l[0], lacc);
+#pragma unroll
+            for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+        }
+        float d16[16];
+        float* dbh = reinterpret_cast<float*>(sm + m.dbh) + r * kDL;
+#pragma unroll
+        for (int q = 0; q < kMaxA; ++q) { d16[q] = dl[q]; dbh[q] += dl[q]; }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint4 hi, lo;
+          split8(d16 + 8 * h, hi, lo);
+          const uint32_t off = (uint32_t)h * kRowChunk + (uint32_t)r * 16;
+          *reinterpret_cast<uint4*>(sm + m.DL + off) = hi;
+          *reinterpret_cast<uint4*>(sm + m.DL + 2 * kRowChunk + off) = lo;
+        }
+      }
+    }
+    if (!UPDATE) continue;
+    // ---- head weight gradient (tensor cores) while the threads push dlogits back through the head
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+      issue_wgrad(tb + kColGh, sBS, sDL, kIdGh, !first);
+      umma::mma_commit(&bars[1]);
+    }
+    float dz[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dz[i] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < kMaxA; ++q) {
+      if (q < A) {
+        const float d = dlog[r * kDL + q];
+        const float* w = Whf + q * 64 + 16 * cq;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) dz[i] = fmaf(d, w[i], dz[i]);
+      }
+    }
+    ln_act_bwd16(dz, n2, mean2, rstd2, relu, xch, slot, cq, r, q4);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) db2[i] += dz[i];
+    umma::mbar_wait(&bars[1], ph_gh); ph_gh ^= 1;                       // the head wgrad has finished reading n2
+    store_cols16(sm + m.BS, r, cq, dz);
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
+      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);   // dn1 = dz2 W2'
+      umma::mma_commit(&bars[0]);
+    }
+    // ---- layer 1 backward
+    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::tc_fence_after();
+    load_acc16(lane_addr, cq, dz);
+    ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) db1[i] += dz[i];
+    store_cols16(sm + m.BS, r, cq, dz);
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+      issue_wgrad(tb + kColG1, sBS, sX, kIdG1, !first);                                        // G1 += dz1^T x
+      umma::mma_commit(&bars[2]);
+    }
+    first = false;
+  }
+  // ---- epilogue: weight gradients TMEM -> two partial rows per CTA (the hi-half and the lo-half lanes of the stacked A operand), in the flat
+  // parameter layout (G in the W slots, db in the b slots; LayerNorm-affine slots stay zero, optim.cu fills them)
+  if (UPDATE) {
+    if (!first) { umma::mbar_wait(&bars[2], ph_x); ph_x ^= 1; }
+    umma::tc_fence_after();
+    float* __restrict__ gp0 = a.grad_partials + (size_t)(2 * blockIdx.x) * L.total;
+    for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;
+    float* red = reinterpret_cast<float*>(sm + m.red);                    // [2][16 warps][16]
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float v1 = db1[i], v2 = db2[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { v1 += __shfl_xor_sync(0xffffffffu, v1, o); v2 += __shfl_xor_sync(0xffffffffu, v2, o); }
+      if (lane == 0) { red[warp * 16 + i] = v1; red[256 + warp * 16 + i] = v2; }
+    }
+    __syncthreads();                                                      // zero fill + red visible
+    float* __restrict__ gp = gp0 + (size_t)(q4 >> 1) * L.total;
+    const int mrow = r & 63;
+    const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;                  // lanes 64..127 hold the (scaled) lo halves of A
+    {
+      float u[16], w[16];
+      umma::tmem_ld16(lane_addr + kColG2 + 16 * cq, u);
+      umma::tmem_ld16(lane_addr + kColG2 + 64 + 16 * cq, w);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) gp[L.w2 + mrow * 64 + 16 * cq + i] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+      if (cq < KP / 16) {
+        umma::tmem_ld16(lane_addr + kColG1 + 16 * cq, u);
+        umma::tmem_ld16(lane_addr + kColG1 + KP + 16 * cq, w);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int k = 16 * cq + i;
+          if (k < D) gp[L.w1 + mrow * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+        }
+      }
+      if (cq == 3) {                                                      // warps 12..15: head gradient, lanes = hidden unit
+        umma::tmem_ld16(lane_addr + kColGh, u);
+        umma::tmem_ld16(lane_addr + kColGh + 16, w);
+        int h = 0, off = 0;
+#pragma unroll
+        for (int q = 0; q < kMaxA; ++q) {
+          if (q < A) {
+            while (q >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+            gp[L.wh[h] + (q - off) * 64 + mrow] = fmaf(w[q], kLoInv, u[q]) * lane_scale;
+          }
+        }
+      }
+    }
+    if (tid < 64) {
+      const int c = tid >> 4, i = tid & 15;
+      float s1 = 0.0f, s2 = 0.0f;
+      for (int q = 0; q < 4; ++q) { s1 += red[(4 * c + q) * 16 + i]; s2 += red[256 + (4 * c + q) * 16 + i]; }
+      gp0[L.b1 + tid] = s1; gp0[L.b2 + tid] = s2;
+    } else if (tid < 64 + A) {
+      const int q = tid - 64;
+      const float* dbh = reinterpret_cast<const float*>(sm + m.dbh);
+      float s = 0.0f;
+      for (int rr = 0; rr < kBM; ++rr) s += dbh[rr * kDL + q];
+      int h = 0, off = 0;
+      while (q >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+      gp0[L.bh[h] + (q - off)] = s;
+    }
+    // loss sums: block reduction in double
+    for (int q = 0; q < 4; ++q) {
+      double v = lacc[q];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+      if (lane == 0) lred[q][warp] = v;
+    }
+    __syncthreads();
+    if (tid < 4) {
+      double v = 0.0;
+      for (int w = 0; w < kThreads / 32; ++w) v += lred[tid][w];
+      a.loss_partials[(size_t)(2 * blockIdx.x) * 4 + tid] = v;
+      a.loss_partials[(size_t)(2 * blockIdx.x + 1) * 4 + tid] = 0.0;
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, UPDATE ? kTmemCols : 128);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+static int sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+int grid_for(long long rows) {
+  const long long ntiles = (rows + kBM - 1) / kBM;
+  const int sms = sm_count();
+  return (int)(ntiles < sms ? (ntiles < 1 ? 1 : ntiles) : sms);
+}
+
+bool supports(const mappo_net_config* cfg) {
+  return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim <= 64;
+}
+
+template <int MODE, int KP>
+static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
+  const Map m = make_map(KP, a.L.a_total | 1);
+  auto kern = mlp_tc_kernel<MODE, KP>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  MAPPO_REQUIRE(m.total <= 200 * 1024, "%s: shared-memory map too large (%u B)", who, m.total);
+  kern<<<grid_for(a.rows), kThreads, m.total, stream>>>(a);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+template <int MODE>
+int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
+  a.L = make_layout(*cfg);
+  if (a.x_div < 1) a.x_div = 1;
+  a.Kp = cfg->in_dim <= 32 ? 32 : 64;
+  a.ntiles = (a.rows + kBM - 1) / kBM;
+  if (a.Kp == 32) return launch_one<MODE, 32>(a, stream, who);
+  return launch_one<MODE, 64>(a, stream, who);
+}
+
+template int launch<0>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+template int launch<1>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+template int launch<2>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+template int launch<3>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+
+}  // namespace tc
+}  // namespace mappo

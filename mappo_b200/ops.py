@@ -230,8 +230,11 @@ def critic_forward(cfg, params, share_obs, values_out, group=1):
                                               ptr(values_out), stream_ptr()), "critic_forward")
 
 
-def update_num_blocks(rows):
-    return int(_lib.lib().mappo_update_num_blocks(C.c_longlong(int(rows))))
+def update_num_blocks(cfg, rows):
+    L = _lib.lib()
+    L.mappo_update_num_blocks.argtypes = [_NC, C.c_longlong]
+    L.mappo_update_num_blocks.restype = C.c_int
+    return int(L.mappo_update_num_blocks(C.byref(cfg), int(rows)))
 
 
 def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, available_actions, grad_partials,

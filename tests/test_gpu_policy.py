@@ -165,7 +165,7 @@ def test_gradient_is_sum_over_shards_and_tiles():
 
     def run(sl, index=None):
         rows = (sl.stop - sl.start) if index is None else index.numel()
-        nb = ops.update_num_blocks(rows)
+        nb = ops.update_num_blocks(actor.cfg, rows)
         gp = torch.empty(nb, P, device="cuda"); lp = torch.empty(nb, 4, dtype=torch.float64, device="cuda")
         if index is None:
             ops.actor_update(actor.cfg, loss, actor.flat, obs[sl], acts[sl], old[sl], adv[sl], None, None, gp, lp)
