@@ -32,7 +32,7 @@ constexpr uint32_t kWChunk = 64 * 16;                                    // ... 
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
-  uint32_t X, N1, BS, W1, W2, DL, Whf, b1f, b2f, bhf, dlog, dbh, xch, xlog, red, bars, total;
+  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, bhf, dbh, xch, xlog, red, bars, total;
   uint32_t x_piece, w1_piece;
 };
 __host__ __device__ inline Map make_map(int Kp, int AS) {
@@ -41,9 +41,10 @@ __host__ __device__ inline Map make_map(int Kp, int AS) {
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
   m.x_piece = (uint32_t)(Kp / 8) * kRowChunk;
   m.w1_piece = (uint32_t)(Kp / 8) * kWChunk;
-  m.X = take(kNP * m.x_piece);
+  m.X = take(2 * kNP * m.x_piece);                 // two buffers: this tile's rows and the next tile's
   m.N1 = take(kNP * 8 * kRowChunk);
-  m.BS = take(kNP * 8 * kRowChunk);
+  m.BS = take(kNP * 8 * kRowChunk);                 // dz2, then dz1
+  m.BS2 = take(kNP * 8 * kRowChunk);                // n2 (operand of the head weight gradient)
   m.W1 = take(kNP * m.w1_piece);
   m.W2 = take(kNP * 8 * kWChunk);
   m.DL = take(kNP * 2 * kRowChunk);
@@ -51,8 +52,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS) {
   m.b1f = take(64 * 4);
   m.b2f = take(64 * 4);
   m.bhf = take(kMaxA * 4);
-  m.dlog = take(kBM * kDL * 4);
-  m.dbh = take(kBM * kDL * 4);
+  m.dbh = take(kBM * AS * 4);
   m.xch = take(2 * 4 * kBM * 8);
   m.xlog = take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 2);
@@ -163,7 +163,7 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     reinterpret_cast<float*>(sm + m.bhf)[aidx] = s;
   }
   float* dbh = reinterpret_cast<float*>(sm + m.dbh);
-  for (int e = tid; e < kBM * kDL; e += kThreads) dbh[e] = 0.0f;
+  for (int e = tid; e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
 }
 
 // ---- MMA issue (one thread) ------------------------------------------------------------------------------
@@ -235,12 +235,97 @@ __device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[1
   }
 }
 
+// ---- input rows: gather, LayerNorm over in_dim (mlp.py:44-45,56-57), fp16 pairs -> X operand tile
+template <int KP>
+__device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsigned char* xs, uint32_t x_piece, float2* xch,
+                                        int& slot, int cq, int r, int q4) {
+  constexpr int XC = KP / 4;                         // input columns per thread
+  const int D = a.L.in_dim;
+  const long long g = tile * kBM + r;
+  const bool valid = g < a.rows;
+  float xv[XC];
+  const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+  const float* __restrict__ row = a.x + srow * (long long)a.ld;
+#pragma unroll
+  for (int i = 0; i < XC; ++i) {
+    const int c = XC * cq + i;
+    xv[i] = (valid && c < D) ? __ldg(row + c) : 0.0f;
+  }
+  if (a.L.use_fn) {
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < XC; ++i) s += xv[i];
+    const float mean = row_sum2(s, 0.0f, xch, slot, cq, r, q4).x / (float)D;
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < XC; ++i) {
+      xv[i] = (XC * cq + i < D) ? xv[i] - mean : 0.0f;
+      q = fmaf(xv[i], xv[i], q);
+    }
+    const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
+#pragma unroll
+    for (int i = 0; i < XC; ++i) xv[i] *= rstd;
+  }
+#pragma unroll
+  for (int h = 0; h < XC / 8; ++h) {
+    uint4 hi, lo;
+    split8(xv + 8 * h, hi, lo);
+    const uint32_t off = (uint32_t)(XC / 8 * cq + h) * kRowChunk + (uint32_t)r * 16;
+    *reinterpret_cast<uint4*>(xs + off) = hi;
+    *reinterpret_cast<uint4*>(xs + x_piece + off) = lo;
+  }
+}
+
+// single categorical head, A <= AMAX logits in registers: PPO clipped surrogate + entropy (r_mappo.py:115-141,
+// act.py:107-162).  Same arithmetic as actor_loss_row (mlp_rows.cuh) with exp() taken once per logit.
+template <int AMAX>
+__device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int A, const float (&l)[AMAX], int act, float old_lp,
+                                                float adv, float active, float (&dl)[AMAX], float (&sums)[4]) {
+  float m = l[0];
+#pragma unroll
+  for (int q = 1; q < AMAX; ++q) if (q < A) m = fmaxf(m, l[q]);
+  float e[AMAX], s = 0.0f;
+#pragma unroll
+  for (int q = 0; q < AMAX; ++q) { e[q] = (q < A) ? __expf(l[q] - m) : 0.0f; s += e[q]; }
+  const float inv = 1.0f / s, ls = m + logf(s);
+  float ent = 0.0f, lp_act = 0.0f;
+#pragma unroll
+  for (int q = 0; q < AMAX; ++q) {
+    if (q < A) {
+      const float lp = l[q] - ls;
+      e[q] *= inv;                                       // p
+      ent = fmaf(-e[q], lp, ent);
+      if (q == act) lp_act = lp;
+    }
+  }
+  const float lo = 1.0f - c.clip_param, hi = 1.0f + c.clip_param;
+  const float ratio = __expf(lp_act - old_lp);
+  const float s1 = ratio * adv, s2 = fminf(fmaxf(ratio, lo), hi) * adv;
+  const bool inside = (ratio >= lo) && (ratio <= hi);
+  const float gcoef = (inside || s1 < s2) ? s1 : 0.0f;   // torch.min / clamp gradient conventions, see actor_loss_row
+#pragma unroll
+  for (int q = 0; q < AMAX; ++q) {
+    dl[q] = 0.0f;
+    if (q < A) {
+      const float lp = l[q] - ls;
+      const float d_obj = -gcoef * ((q == act ? 1.0f : 0.0f) - e[q]);
+      const float d_ent = c.entropy_coef * e[q] * (lp + ent);
+      dl[q] = active * (d_obj + d_ent);
+    }
+  }
+  sums[0] = -fminf(s1, s2) * active; sums[1] = ent * active; sums[2] = ratio; sums[3] = active;
+}
+
 // ---- the kernel ------------------------------------------------------------------------------------------
 // MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic.  KP: padded input width (32 | 64).
-template <int MODE, int KP>
+// AMAX: register width of the head (1 critic; 8 = single categorical head with <= 8 logits and no availability
+// mask, losses evaluated in registers; 16 = generic heads through the row functions of mlp_rows.cuh).
+// Per tile the update issues three groups of MMAs -- {fc2}, {head wgrad, fc2 wgrad, fc2 dgrad}, {fc1 wgrad, fc1 of
+// the NEXT tile} -- so there are three CTA-wide synchronisations per tile; the next tile's input rows are staged
+// into the second X buffer while the second group runs on the tensor cores.
+template <int MODE, int KP, int AMAX>
 __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE >= 2);
-  constexpr int XC = KP / 4;                         // input columns per thread
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
@@ -249,24 +334,25 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   const Map m = make_map(KP, AS);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + m.bars);          // [0] ACC ready, [1] head wgrad done, [2] wgrad1 done
-  if (tid == 0) {
-    umma::mbar_init(&bars[0], 1); umma::mbar_init(&bars[1], 1); umma::mbar_init(&bars[2], 1);
-    umma::fence_mbar_init();
-  }
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   stage_weights_tc(sm, m, a);
+  int slot = 0;
+  float2* xch = reinterpret_cast<float2*>(sm + m.xch);
+  long long tile = blockIdx.x;
+  stage_x<KP>(a, tile, sm + m.X, m.x_piece, xch, slot, cq, r, q4);
   umma::fence_async_smem();
   umma::tc_fence_before();
   __syncthreads();
   umma::tc_fence_after();
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+  const uint32_t x_bytes = kNP * m.x_piece;
   const uint32_t sX = umma::smem_u32(sm + m.X), sN1 = umma::smem_u32(sm + m.N1), sBS = umma::smem_u32(sm + m.BS);
-  const uint32_t sW1 = umma::smem_u32(sm + m.W1), sW2 = umma::smem_u32(sm + m.W2), sDL = umma::smem_u32(sm + m.DL);
-  float2* xch = reinterpret_cast<float2*>(sm + m.xch);
+  const uint32_t sB2 = umma::smem_u32(sm + m.BS2), sW1 = umma::smem_u32(sm + m.W1), sW2 = umma::smem_u32(sm + m.W2);
+  const uint32_t sDL = umma::smem_u32(sm + m.DL);
   float* xlog = reinterpret_cast<float*>(sm + m.xlog);
-  float* dlog = reinterpret_cast<float*>(sm + m.dlog);
   const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
   const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
   const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
@@ -274,9 +360,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
-
-  int slot = 0;
-  uint32_t ph_acc = 0, ph_gh = 0, ph_x = 0;
+  if (tid == 0) {
+    issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX, m.x_piece, sW1, m.w1_piece, kWChunk, 128, 2 * kWChunk, KP / 16, kIdFwd);
+    umma::mma_commit(bar);
+  }
+  uint32_t ph = 0;
+  int buf = 0;
   bool first = true;
   float db1[16], db2[16];
   double lacc[4] = {0.0, 0.0, 0.0, 0.0};
@@ -285,55 +374,23 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     for (int i = 0; i < 16; ++i) db1[i] = db2[i] = 0.0f;
   }
 
-  for (long long tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+  for (; tile < a.ntiles; tile += gridDim.x) {
     const long long g = tile * kBM + r;
     const bool valid = g < a.rows;
-    // ---- input rows: gather, LayerNorm over in_dim (mlp.py:44-45), fp16 pairs -> X
-    {
-      float xv[XC];
-      const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
-      const float* __restrict__ row = a.x + srow * (long long)a.ld;
-#pragma unroll
-      for (int i = 0; i < XC; ++i) {
-        const int c = XC * cq + i;
-        xv[i] = (valid && c < D) ? __ldg(row + c) : 0.0f;
-      }
-      if (L.use_fn) {
-        float s = 0.0f;
-#pragma unroll
-        for (int i = 0; i < XC; ++i) s += xv[i];
-        const float mean = row_sum2(s, 0.0f, xch, slot, cq, r, q4).x / (float)D;
-        float q = 0.0f;
-#pragma unroll
-        for (int i = 0; i < XC; ++i) {
-          xv[i] = (XC * cq + i < D) ? xv[i] - mean : 0.0f;
-          q = fmaf(xv[i], xv[i], q);
-        }
-        const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
-#pragma unroll
-        for (int i = 0; i < XC; ++i) xv[i] *= rstd;
-      }
-      if (UPDATE && !first) { umma::mbar_wait(&bars[2], ph_x); ph_x ^= 1; }      // wgrad1 of the previous tile read X
-#pragma unroll
-      for (int h = 0; h < XC / 8; ++h) {
-        uint4 hi, lo;
-        split8(xv + 8 * h, hi, lo);
-        const uint32_t off = (uint32_t)(XC / 8 * cq + h) * kRowChunk + (uint32_t)r * 16;
-        *reinterpret_cast<uint4*>(sm + m.X + off) = hi;
-        *reinterpret_cast<uint4*>(sm + m.X + m.x_piece + off) = lo;
-      }
-    }
-    umma::fence_async_smem();
-    umma::tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      umma::tc_fence_after();
-      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX, m.x_piece, sW1, m.w1_piece, kWChunk, 128, 2 * kWChunk, KP / 16, kIdFwd);
-      umma::mma_commit(&bars[0]);
+    const bool has_next = tile + gridDim.x < a.ntiles;
+    const long long src = (valid && a.index) ? a.index[g] : (valid ? g : 0);
+    // per-row scalars of the register loss path, requested now and consumed after the second layer
+    int p_act = 0;
+    float p_old = 0.0f, p_adv = 0.0f, p_active = 1.0f;
+    if (MODE == 2 && AMAX == 8 && valid) {
+      p_act = (int)__ldg(a.actions + src);
+      p_old = __ldg(a.old_logp + src);
+      p_adv = __ldg(a.adv + src);
+      if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
     }
     // ---- layer 1 epilogue
     float n1[16], mean1, rstd1;
-    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
     load_acc16(lane_addr, cq, n1);
     act_ln16(n1, b1f, relu, xch, slot, cq, r, q4, mean1, rstd1);
@@ -344,59 +401,95 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     if (tid == 0) {
       umma::tc_fence_after();
       issue_rowgemm(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk, sW2, 8 * kWChunk, kWChunk, 128, 2 * kWChunk, 4, kIdFwd);
-      umma::mma_commit(&bars[0]);
+      umma::mma_commit(bar);
     }
     // ---- layer 2 epilogue + head
     float n2[16], mean2, rstd2;
-    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
     load_acc16(lane_addr, cq, n2);
     act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
-    if (UPDATE) store_cols16(sm + m.BS, r, cq, n2);
+    if (UPDATE) store_cols16(sm + m.BS2, r, cq, n2);
     {
       float* mine = xlog + (size_t)(cq * kBM + r) * AS;
 #pragma unroll
-      for (int q = 0; q < kMaxA; ++q) {
+      for (int q = 0; q < AMAX; ++q) {
         if (q < A) {
-          const float* w = Whf + q * 64 + 16 * cq;
+          const float4* w4 = reinterpret_cast<const float4*>(Whf + q * 64 + 16 * cq);
           float s = 0.0f;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) s = fmaf(n2[i], w[i], s);
+          for (int i = 0; i < 4; ++i) {
+            const float4 w = w4[i];
+            s = fmaf(n2[4 * i], w.x, fmaf(n2[4 * i + 1], w.y, fmaf(n2[4 * i + 2], w.z, fmaf(n2[4 * i + 3], w.w, s))));
+          }
           mine[q] = s;
         }
       }
     }
     bar_named(1 + q4, 128);
-    if (cq == 0) {
-      float l[kMaxA];
+    float l[AMAX];
 #pragma unroll
-      for (int q = 0; q < kMaxA; ++q) {
-        l[q] = 0.0f;
-        if (q < A) {
-          const float* p = xlog + (size_t)r * AS + q;
-          l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
-        }
+    for (int q = 0; q < AMAX; ++q) {
+      l[q] = 0.0f;
+      if (q < A) {
+        const float* p = xlog + (size_t)r * AS + q;
+        l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
       }
-      const long long src = (valid && a.index) ? a.index[g] : g;
-      if (MODE == 0 && valid) actor_rollout_row(a, g, l);
-      if (MODE == 1 && valid) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
-      if (UPDATE) {
-        float* dl = dlog + r * kDL;
-        if (valid) {
-          if (MODE == 2) actor_loss_row(a, src, l, dl, lacc);
-          if (MODE == 3) {
-            dl[0] = critic_loss_row(a, src, l[0], lacc);
+    }
+    if (!UPDATE) {
+      if (cq == 0 && valid) {
+        if (MODE == 0) actor_rollout_row(a, g, l);
+        if (MODE == 1) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
+      }
+      if (has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (tid == 0 && has_next) {
+        umma::tc_fence_after();
+        issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
+                      2 * kWChunk, KP / 16, kIdFwd);
+        umma::mma_commit(bar);
+      }
+      buf ^= 1;
+      continue;
+    }
+    // ---- losses: every thread of a row evaluates them (no idle warps, no shared-memory round trip for dlogits);
+    // the column-quarter-0 thread keeps the sums and writes the dlogits operand of the head weight gradient
+    float dl[AMAX];
+    {
+      double mine[4] = {0.0, 0.0, 0.0, 0.0};
+      if (MODE == 2 && AMAX == 8) {
+        float sums[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (valid) actor_loss_regs<AMAX>(a.loss, A, l, p_act, p_old, p_adv, p_active, dl, sums);
+        else {
 #pragma unroll
-            for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
-          }
-        } else {
-#pragma unroll
-          for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+          for (int q = 0; q < AMAX; ++q) dl[q] = 0.0f;
         }
-        float d16[16];
-        float* dbh = reinterpret_cast<float*>(sm + m.dbh) + r * kDL;
 #pragma unroll
-        for (int q = 0; q < kMaxA; ++q) { d16[q] = dl[q]; dbh[q] += dl[q]; }
+        for (int q = 0; q < 4; ++q) mine[q] = (double)sums[q];
+      } else if (MODE == 2) {
+        float lt[kMaxA], dt[kMaxA];
+#pragma unroll
+        for (int q = 0; q < kMaxA; ++q) { lt[q] = (q < AMAX) ? l[q < AMAX ? q : 0] : 0.0f; dt[q] = 0.0f; }
+        if (valid) actor_loss_row(a, src, lt, dt, mine);
+#pragma unroll
+        for (int q = 0; q < AMAX; ++q) dl[q] = dt[q];
+      } else {
+        dl[0] = valid ? critic_loss_row(a, src, l[0], mine) : 0.0f;
+#pragma unroll
+        for (int q = 1; q < AMAX; ++q) dl[q] = 0.0f;
+      }
+      if (cq == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) lacc[q] += mine[q];
+        float d16[16];
+        float* dbh = reinterpret_cast<float*>(sm + m.dbh) + r * AS;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          d16[q] = (q < AMAX) ? dl[q < AMAX ? q : 0] : 0.0f;
+          if (q < AMAX && q < A) dbh[q] += d16[q];
+        }
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint4 hi, lo;
@@ -407,44 +500,40 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         }
       }
     }
-    if (!UPDATE) continue;
-    // ---- head weight gradient (tensor cores) while the threads push dlogits back through the head
-    umma::fence_async_smem();
-    umma::tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      umma::tc_fence_after();
-      issue_wgrad(tb + kColGh, sBS, sDL, kIdGh, !first);
-      umma::mma_commit(&bars[1]);
-    }
+    // ---- back through the head and layer 2
     float dz[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) dz[i] = 0.0f;
 #pragma unroll
-    for (int q = 0; q < kMaxA; ++q) {
+    for (int q = 0; q < AMAX; ++q) {
       if (q < A) {
-        const float d = dlog[r * kDL + q];
-        const float* w = Whf + q * 64 + 16 * cq;
+        const float4* w4 = reinterpret_cast<const float4*>(Whf + q * 64 + 16 * cq);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) dz[i] = fmaf(d, w[i], dz[i]);
+        for (int i = 0; i < 4; ++i) {
+          const float4 w = w4[i];
+          dz[4 * i] = fmaf(dl[q], w.x, dz[4 * i]); dz[4 * i + 1] = fmaf(dl[q], w.y, dz[4 * i + 1]);
+          dz[4 * i + 2] = fmaf(dl[q], w.z, dz[4 * i + 2]); dz[4 * i + 3] = fmaf(dl[q], w.w, dz[4 * i + 3]);
+        }
       }
     }
     ln_act_bwd16(dz, n2, mean2, rstd2, relu, xch, slot, cq, r, q4);
 #pragma unroll
     for (int i = 0; i < 16; ++i) db2[i] += dz[i];
-    umma::mbar_wait(&bars[1], ph_gh); ph_gh ^= 1;                       // the head wgrad has finished reading n2
     store_cols16(sm + m.BS, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
     if (tid == 0) {
       umma::tc_fence_after();
+      issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                                       // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
-      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);   // dn1 = dz2 W2'
-      umma::mma_commit(&bars[0]);
+      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);
+      umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
     }
+    // ---- next tile's input rows, staged while the tensor cores work
+    if (has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
     // ---- layer 1 backward
-    umma::mbar_wait(&bars[0], ph_acc); ph_acc ^= 1;
+    umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
     load_acc16(lane_addr, cq, dz);
     ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
@@ -456,15 +545,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (tid == 0) {
       umma::tc_fence_after();
-      issue_wgrad(tb + kColG1, sBS, sX, kIdG1, !first);                                        // G1 += dz1^T x
-      umma::mma_commit(&bars[2]);
+      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes, kIdG1, !first);                        // G1 += dz1^T x
+      if (has_next)
+        issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
+                      2 * kWChunk, KP / 16, kIdFwd);
+      umma::mma_commit(bar);
     }
+    buf ^= 1;
     first = false;
   }
   // ---- epilogue: weight gradients TMEM -> two partial rows per CTA (the hi-half and the lo-half lanes of the stacked A operand), in the flat
   // parameter layout (G in the W slots, db in the b slots; LayerNorm-affine slots stay zero, optim.cu fills them)
   if (UPDATE) {
-    if (!first) { umma::mbar_wait(&bars[2], ph_x); ph_x ^= 1; }
+    umma::mbar_wait(bar, ph); ph ^= 1;                                  // the last tile's fc1 weight gradient
     umma::tc_fence_after();
     float* __restrict__ gp0 = a.grad_partials + (size_t)(2 * blockIdx.x) * L.total;
     for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;
@@ -500,7 +593,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         umma::tmem_ld16(lane_addr + kColGh + 16, w);
         int h = 0, off = 0;
 #pragma unroll
-        for (int q = 0; q < kMaxA; ++q) {
+        for (int q = 0; q < AMAX; ++q) {
           if (q < A) {
             while (q >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
             gp[L.wh[h] + (q - off) * 64 + mrow] = fmaf(w[q], kLoInv, u[q]) * lane_scale;
@@ -517,7 +610,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       const int q = tid - 64;
       const float* dbh = reinterpret_cast<const float*>(sm + m.dbh);
       float s = 0.0f;
-      for (int rr = 0; rr < kBM; ++rr) s += dbh[rr * kDL + q];
+      for (int rr = 0; rr < kBM; ++rr) s += dbh[rr * AS + q];
       int h = 0, off = 0;
       while (q >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
       gp0[L.bh[h] + (q - off)] = s;
@@ -542,6 +635,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------
+constexpr int kMaxDynSmem = 232448 - 2048;          // 227 KB per CTA minus this kernel's static shared memory
+
 static int sm_count() {
   static int sms = 0;
   if (sms == 0) {
@@ -562,16 +657,16 @@ bool supports(const mappo_net_config* cfg) {
   return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim <= 64;
 }
 
-template <int MODE, int KP>
+template <int MODE, int KP, int AMAX>
 static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
   const Map m = make_map(KP, a.L.a_total | 1);
-  auto kern = mlp_tc_kernel<MODE, KP>;
+  auto kern = mlp_tc_kernel<MODE, KP, AMAX>;
   static bool attr_set = false;
   if (!attr_set) {
-    MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
     attr_set = true;
   }
-  MAPPO_REQUIRE(m.total <= 200 * 1024, "%s: shared-memory map too large (%u B)", who, m.total);
+  MAPPO_REQUIRE(m.total <= kMaxDynSmem, "%s: shared-memory map too large (%u B)", who, m.total);
   kern<<<grid_for(a.rows), kThreads, m.total, stream>>>(a);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
@@ -583,8 +678,19 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
   if (a.x_div < 1) a.x_div = 1;
   a.Kp = cfg->in_dim <= 32 ? 32 : 64;
   a.ntiles = (a.rows + kBM - 1) / kBM;
-  if (a.Kp == 32) return launch_one<MODE, 32>(a, stream, who);
-  return launch_one<MODE, 64>(a, stream, who);
+  constexpr bool kCritic = (MODE == 1 || MODE == 3);
+  if constexpr (kCritic) {
+    if (a.Kp == 32) return launch_one<MODE, 32, 1>(a, stream, who);
+    return launch_one<MODE, 64, 1>(a, stream, who);
+  } else {
+  const bool small_head = cfg->n_heads == 1 && a.L.a_total <= 8 && a.avail == nullptr;
+  if (small_head) {
+    if (a.Kp == 32) return launch_one<MODE, 32, 8>(a, stream, who);
+    return launch_one<MODE, 64, 8>(a, stream, who);
+  }
+  if (a.Kp == 32) return launch_one<MODE, 32, 16>(a, stream, who);
+  return launch_one<MODE, 64, 16>(a, stream, who);
+  }
 }
 
 template int launch<0>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
