@@ -144,12 +144,12 @@ def build_runner(n_envs, device, rank, world, host_io=False):
     from mappo_b200.runner.shared.mpe_runner import MPERunner
     a = parse_args(flags(n_envs))
     torch.manual_seed(1)                                 # same initial weights on every rank (replicated parameters)
-    envs = MPEVecEnv(a, device=device, env_id_offset=rank * n_envs, host_io=host_io)
+    from mappo_b200 import parallel as _par
+    envs = MPEVecEnv(a, device=device, env_id_offset=_par.env_shard(n_envs, rank), host_io=host_io)
     runner = MPERunner({"all_args": a, "envs": envs, "eval_envs": None, "device": device, "num_agents": M_AGENTS,
                         "run_dir": None})
-    if world > 1:
-        import torch.distributed as dist
-        runner.trainer.set_all_reduce(lambda t: dist.all_reduce(t), world)
+    from mappo_b200 import parallel
+    parallel.attach(runner.trainer, world)
     return a, envs, runner
 
 
@@ -202,7 +202,8 @@ def run_ours(ns):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=device)
+        from mappo_b200 import parallel
+        parallel.init_distributed("nccl", device)
     n_envs = ns.envs
     a, envs, runner = build_runner(n_envs, device, rank, world)
     agent_steps = n_envs * T_EP * M_AGENTS

@@ -287,7 +287,7 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
   float e[AMAX], s = 0.0f;
 #pragma unroll
   for (int q = 0; q < AMAX; ++q) { e[q] = (q < A) ? __expf(l[q] - m) : 0.0f; s += e[q]; }
-  const float inv = 1.0f / s, ls = m + logf(s);
+  const float inv = __frcp_rn(s), ls = m + __logf(s);
   float ent = 0.0f, lp_act = 0.0f;
 #pragma unroll
   for (int q = 0; q < AMAX; ++q) {
@@ -466,8 +466,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
 #pragma unroll
           for (int q = 0; q < AMAX; ++q) dl[q] = 0.0f;
         }
+        if (cq == 0) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) mine[q] = (double)sums[q];
+          for (int q = 0; q < 4; ++q) lacc[q] += (double)sums[q];
+        }
       } else if (MODE == 2) {
         float lt[kMaxA], dt[kMaxA];
 #pragma unroll
