@@ -277,12 +277,13 @@ def run_ours(ns):
     per_launch_ms = tot / max(n, 1)
     achieved = rows * flop_row / (per_launch_ms * 1e-3) / 1e12 if n else None
     peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    roofline = {"kernel": "mlp_kernel<MODE=2> (actor forward+PPO loss+backward, fused)", "bound": "tensor",
+    roofline = {"kernel": "mlp_tc_kernel<MODE=2> (actor forward + PPO loss + backward, tcgen05 fp16-pair GEMMs)", "bound": "tensor",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
                 "peak_source": "measured bf16 sustained (MEASURED_PEAKS.json)" if peaks else "fallback",
                 "traffic": None, "launches": n, "ms_per_launch": per_launch_ms,
                 "flop_per_row": flop_row, "rows_per_launch": rows,
-                "note": "fp32 FMA kernel this round: its own pipe peak is 148 SM x 128 lanes x 2 x sm clock"}
+                "note": "algorithmic fp32-equivalent FLOP; the kernel issues 3-4 fp16 MMAs per product and is bound by "
+                        "the fp32 epilogues between the GEMMs (see DESIGN.md 4.1, profiles/)"}
     share = {k: {"launches": v[0], "ms_per_step": v[1] / ns.steps} for k, v in kt.items()}
 
     # ---- CPU baseline beside it (N = 1 only)
