@@ -172,28 +172,17 @@ class R_MAPPO:
                                  all_reduce=self.all_reduce)
         advantages = ops.adv_normalize(raw, s3, out=buffer._adv_scratch())
         self._info_total.zero_()
-        B = advantages.numel()
-        M = buffer.num_agents
-        obs_flat = buffer.obs[:-1].reshape(B, -1)
-        acts = buffer.actions.view(B, -1)
-        logp = buffer.action_log_probs.view(B, -1)
+        v = buffer.flat_views()
+        B, M = v["B"], v["M"]
+        obs_flat, sh, acts, logp, avail = v["obs"], v["share"], v["actions"], v["logp"], v["avail"]
+        vp, ret, act_m = v["value_preds"], v["returns"], v["active"]
         adv = advantages.view(B)
-        vp = buffer.value_preds[:-1].reshape(B)
-        ret = buffer.returns[:-1].reshape(B)
-        act_m = buffer.active_masks[:-1].reshape(B)
-        avail = None
-        if buffer.available_actions is not None and not buffer._avail_all_ones:
-            avail = buffer.available_actions[:-1].reshape(B, -1)
-        unique = buffer.share_obs_unique()              # [T+1, N, S] when share_obs is a broadcast view, else None
+        rep = M if v["share_is_unique"] else 1          # samples served by one share_obs row
         n_updates = 0
         for _ in range(self.ppo_epoch):
             if self.num_mini_batch == 1 and not buffer.force_permutation:
                 # the loss is a mean over the whole batch: the permutation only reorders the sum
-                if unique is not None:
-                    sh, group = unique[:-1].reshape(-1, unique.shape[-1]), M
-                else:
-                    sh, group = buffer.share_obs[:-1].reshape(B, -1), 1
-                self._update(obs_flat, sh, group, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor)
+                self._update(obs_flat, sh, rep, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor)
                 n_updates += 1
             else:
                 mbs = B // self.num_mini_batch
@@ -201,13 +190,9 @@ class R_MAPPO:
                 rand_dev = rand.to(self.device, non_blocking=True)
                 for k in range(self.num_mini_batch):
                     idx = rand_dev[k * mbs:(k + 1) * mbs].contiguous()
-                    if unique is not None:
-                        sh, div = unique[:-1].reshape(-1, unique.shape[-1]), M
-                    else:
-                        sh, div = buffer.share_obs[:-1].reshape(B, -1), 1
                     vn_batch = ret.index_select(0, idx) if self.value_normalizer is not None else None
                     self._update(obs_flat, sh, 1, acts, logp, adv, vp, ret, act_m, avail, mbs, index=idx,
-                                 share_rows_div=div, update_actor=update_actor, vn_batch=vn_batch)
+                                 share_rows_div=rep, update_actor=update_actor, vn_batch=vn_batch)
                     n_updates += 1
         info = (self._info_total / float(n_updates)).cpu().numpy()      # the only host sync of train()
         return {"value_loss": float(info[4]), "policy_loss": float(info[0]), "dist_entropy": float(info[2]),

@@ -103,6 +103,21 @@ class SharedReplayBuffer(object):
             self._adv = torch.empty_like(self.rewards)
         return self._adv
 
+    def flat_views(self):
+        """2-D row views for the update kernels.  share_is_unique: `share` holds one row per (t, env) serving all M
+        agents of that env (the stride-0 view above), else one row per sample."""
+        T, N, M = self.rewards.shape[0:3]
+        B = T * N * M
+        avail = None
+        if self.available_actions is not None and not self._avail_all_ones:
+            avail = self.available_actions[:-1].reshape(B, -1)
+        u = self._share_unique
+        share = u[:-1].view(T * N, -1) if u is not None else self.share_obs[:-1].view(B, -1)
+        return dict(B=B, M=M, obs=self.obs[:-1].view(B, -1), share=share, share_is_unique=u is not None,
+                    actions=self.actions.view(B, -1), logp=self.action_log_probs.view(B, -1),
+                    value_preds=self.value_preds[:-1].view(B), returns=self.returns[:-1].view(B),
+                    active=self.active_masks[:-1].view(B), avail=avail)
+
     def _put(self, dst, src):
         """Copy unless `src` already IS the destination slot (the kernels wrote in place)."""
         if src is None:

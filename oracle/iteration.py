@@ -62,6 +62,14 @@ class OracleMAPPO:
         N, M = obs.shape[0], obs.shape[1]
         return np.repeat(obs.reshape(N, 1, -1), M, axis=1)
 
+    def share_at(self, t):
+        """share_obs slot t as [N, M, S]"""
+        return self.share_obs_of(self.obs[t])
+
+    def share_rows(self):
+        """share_obs[:-1] flattened to [T*N*M, S]"""
+        return np.stack([self.share_at(t) for t in range(self.T)]).reshape(self.T * self.N * self.M, -1)
+
     def warmup(self, state=None):
         self.obs[0] = self._stack_obs(self.env.reset(state))
 
@@ -70,7 +78,7 @@ class OracleMAPPO:
         a = self.a
         N, M = self.N, self.M
         obs = self.obs[step].reshape(N * M, -1)
-        sh = self.share_obs_of(self.obs[step]).reshape(N * M, -1)
+        sh = self.share_at(step).reshape(N * M, -1)
         z = np.zeros((N * M, 1, a.hidden_size), np.float32)
         ones = np.ones((N * M, 1), np.float32)
         feats, _ = op.actor_features(self.actor, obs, z, ones, a.use_ReLU, a.use_feature_normalization, False)
@@ -79,7 +87,7 @@ class OracleMAPPO:
                                       row_offset=self.row_offset)
         self.calls += 1
         values, _ = op.critic_values(self.critic, sh, z, ones, a.use_ReLU, a.use_feature_normalization, False)
-        return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, 1), lps.numpy().reshape(N, M, 1)
+        return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, -1), lps.numpy().reshape(N, M, -1)
 
     def rollout(self):
         for step in range(self.T):
@@ -99,7 +107,7 @@ class OracleMAPPO:
     def compute(self):
         a = self.a
         N, M = self.N, self.M
-        sh = self.share_obs_of(self.obs[-1]).reshape(N * M, -1)
+        sh = self.share_at(-1).reshape(N * M, -1)
         z = np.zeros((N * M, 1, a.hidden_size), np.float32)
         nv, _ = op.critic_values(self.critic, sh, z, np.ones((N * M, 1), np.float32), a.use_ReLU,
                                  a.use_feature_normalization, False)
@@ -130,7 +138,7 @@ class OracleMAPPO:
         B = T * N * M
         take = (lambda x: x) if rows is None else (lambda x: x[rows])
         obs = take(self.obs[:-1].reshape(B, -1))
-        sh = take(np.stack([self.share_obs_of(o) for o in self.obs[:-1]]).reshape(B, -1))
+        sh = take(self.share_rows())
         actions = take(self.actions.reshape(B, -1))
         old_lp = take(self.action_log_probs.reshape(B, -1))
         advb = take(adv.reshape(B, 1))
@@ -175,11 +183,119 @@ class OracleMAPPO:
                 r = self.ppo_update(rows, adv)
                 info = r if info is None else {k: info[k] + r[k] for k in r}
                 n += 1
-        # after_update, shared_buffer.py:149-159
+        self.after_update()
+        return {k: v / n for k, v in info.items()}
+
+    def after_update(self):
+        """shared_buffer.py:149-159"""
         self.obs[0] = self.obs[-1]
         self.masks[0] = self.masks[-1]
         self.active_masks[0] = self.active_masks[-1]
-        return {k: v / n for k, v in info.items()}
+
+    def iteration(self):
+        self.rollout()
+        self.compute()
+        return self.train()
+
+
+class _AgentLearner(OracleMAPPO):
+    """One agent of the separated setting: its own networks, Adam / ValueNorm state and [T+1, N, 1, ...] storage
+    (separated_buffer.py:13-70 with the agent axis kept at size 1 so the shared maths above applies unchanged)."""
+
+    def __init__(self, args, actor_sd, critic_sd, N, D, S, heads, sample_seed, row_offset):
+        self.a = args
+        self.N, self.M, self.T = N, 1, args.episode_length
+        self.sample_seed, self.row_offset = int(sample_seed), int(row_offset)
+        self.actor = {k: v.detach().clone().float() for k, v in actor_sd.items()}
+        self.critic = {k: v.detach().clone().float() for k, v in critic_sd.items()}
+        self.akeys = [k for k in self.actor if "fc_h" not in k]
+        self.ckeys = [k for k in self.critic if "fc_h" not in k]
+        self.adam = {"actor": {}, "critic": {}}
+        self.adam_step = {"actor": 0, "critic": 0}
+        self.vn = ob.OracleValueNorm() if args.use_valuenorm else None
+        T = self.T
+        f = np.float32
+        self.D, self.S = D, S
+        self.obs = np.zeros((T + 1, N, 1, D), f)
+        self.share = np.zeros((T + 1, N, 1, S), f)
+        self.value_preds = np.zeros((T + 1, N, 1, 1), f)
+        self.returns = np.zeros((T + 1, N, 1, 1), f)
+        self.masks = np.ones((T + 1, N, 1, 1), f)
+        self.active_masks = np.ones((T + 1, N, 1, 1), f)
+        self.actions = np.zeros((T, N, 1, heads), f)
+        self.action_log_probs = np.zeros((T, N, 1, heads), f)
+        self.rewards = np.zeros((T, N, 1, 1), f)
+        self.calls = 0
+
+    def share_at(self, t):
+        return self.share[t]
+
+    def share_rows(self):
+        return self.share[:-1].reshape(self.T * self.N, -1)
+
+    def after_update(self):
+        """separated_buffer.py:101-110"""
+        OracleMAPPO.after_update(self)
+        self.share[0] = self.share[-1]
+
+
+class OracleSeparatedMAPPO:
+    """Separated policies (BASELINE config C3): onpolicy/runner/separated/mpe_runner.py:16-176 and
+    runner/separated/base_runner.py:110-130 restated over the batched oracle env, one _AgentLearner per agent."""
+
+    def __init__(self, args, actor_sds, critic_sds, num_envs=None, seed=None, env_id_offset=0, sample_seeds=None):
+        self.a = args
+        self.N = int(num_envs if num_envs is not None else args.n_rollout_threads)
+        self.M, self.T = args.num_agents, args.episode_length
+        seed = int(args.seed if seed is None else seed)
+        self.env = OracleMPE(args.scenario_name, self.N, self.M, args.num_landmarks, self.T, seed=seed,
+                             env_id_offset=env_id_offset)
+        dims = self.env.spec.obs_dims
+        W = int(sum(dims))
+        self.agents = []
+        for m in range(self.M):
+            S = W if args.use_centralized_V else dims[m]
+            heads = sum(1 for k in actor_sds[m] if k.endswith("linear.weight"))
+            ss = seed if sample_seeds is None else sample_seeds[m]
+            self.agents.append(_AgentLearner(args, actor_sds[m], critic_sds[m], self.N, dims[m], S, heads, ss,
+                                             env_id_offset))
+        self.heads = max(ag.actions.shape[-1] for ag in self.agents)
+
+    def _store_obs(self, t, obs_list):
+        """mpe_runner.py:86-96,160-176: agent m sees its own obs and (centralised) the concatenation of all."""
+        joint = np.concatenate([np.asarray(o, np.float32) for o in obs_list], axis=1)
+        for m, ag in enumerate(self.agents):
+            ag.obs[t, :, 0] = obs_list[m]
+            ag.share[t, :, 0] = joint if self.a.use_centralized_V else obs_list[m]
+
+    def warmup(self, state=None):
+        self._store_obs(0, self.env.reset(state))
+
+    def rollout(self):
+        N, M = self.N, self.M
+        for step in range(self.T):
+            acts_env = np.zeros((N, M, self.heads), np.int64)
+            outs = []
+            for m, ag in enumerate(self.agents):
+                v, a, lp = ag.collect(step)
+                outs.append((v, a, lp))
+                acts_env[:, m, :a.shape[-1]] = a[:, 0]
+            obs, rewards, dones, _ = self.env.step(acts_env)
+            self._store_obs(step + 1, obs)
+            for m, ag in enumerate(self.agents):
+                v, a, lp = outs[m]
+                ag.actions[step], ag.action_log_probs[step], ag.value_preds[step] = a, lp, v
+                ag.rewards[step, :, 0] = rewards[:, m]
+                mk = np.ones((N, 1), np.float32)
+                mk[dones[:, m]] = 0.0
+                ag.masks[step + 1, :, 0] = mk
+
+    def compute(self):
+        for ag in self.agents:
+            ag.compute()
+
+    def train(self, permute=False):
+        return [ag.train(permute) for ag in self.agents]
 
     def iteration(self):
         self.rollout()
