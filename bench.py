@@ -38,9 +38,18 @@ def flags(n_envs):
             "--lr 7e-4 --critic_lr 7e-4 --seed 1" % (M_AGENTS, N_LANDMARKS, n_envs, T_EP, PPO_EPOCH)).split()
 
 
+def set_workload(num_agents):
+    """Default M = 3 is C2 (the configuration the metric is quoted on); --agents 10 selects the C5 shape."""
+    global M_AGENTS, D_OBS, S_OBS
+    M_AGENTS = int(num_agents)
+    D_OBS = 4 + 2 * N_LANDMARKS + 4 * (M_AGENTS - 1)       # simple_spread.py:93-103
+    S_OBS = D_OBS * M_AGENTS
+
+
 def workload_name(n_envs, n_gpus):
-    return ("C2: MPE simple_spread M=3 L=3, %d envs/GPU x %d GPU, T=25, shared MLP (Tanh, H=64), ppo_epoch=10, "
-            "num_mini_batch=1, GAE+ValueNorm" % (n_envs, n_gpus))
+    return ("%s: MPE simple_spread M=%d L=3, %d envs/GPU x %d GPU, T=25, shared MLP (Tanh, H=64), ppo_epoch=10, "
+            "num_mini_batch=1, GAE+ValueNorm" % ("C2" if M_AGENTS == 3 else "C5" if M_AGENTS == 10 else "custom",
+                                                 M_AGENTS, n_envs, n_gpus))
 
 
 # ---------------------------------------------------------------------------------------------- clocks
@@ -323,10 +332,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
+    ap.add_argument("--agents", type=int, default=3, help="agents per env (3 = C2, the headline; 10 = C5 shape)")
     ap.add_argument("--cpu-envs", dest="cpu_envs", type=int, default=1024, help="envs of the bounded CPU sample")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
     ns = ap.parse_args()
+    set_workload(ns.agents)
     ns.warmup = max(ns.warmup, 0)
     if ns.impl == "reference":
         run_reference(ns)

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define MAPPO_B200_ABI_VERSION 1
+#define MAPPO_B200_ABI_VERSION 2
 
 typedef enum {
   MAPPO_OK = 0,
@@ -213,7 +213,12 @@ int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const 
 /* Critic forward (R_Critic.forward / get_values): `rows` unique share-obs rows, each value written `group`
  * times: values_out float32 [rows][group] (group = M when the M agents of an env share one share_obs row). */
 int mappo_critic_forward(const mappo_net_config* cfg, const float* params, const float* share_obs, int obs_ld,
-                         long long rows, int group, float* values_out, void* stream);
+                         long long rows, int group, float* values_out, void* workspace, void* stream);
+
+/* Scratch bytes a critic call over `rows` rows needs in `workspace` (device memory, 16-byte aligned): 0 for
+ * in_dim <= 64 (pass NULL); for a wide centralised critic (in_dim > 64, e.g. 460 = 10 agents x 46) the first layer runs
+ * as separate streaming GEMMs and its [rows][64] activations / gradients plus [rows][2] row statistics live there. */
+long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long long rows);
 
 typedef struct {
   float clip_param;            /* args.clip_param */
@@ -259,7 +264,8 @@ int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss_config* lo
                         const float* share_obs, int obs_ld, long long rows, int group, const int64_t* index,
                         int share_rows_div,
                         const float* value_preds, const float* returns, const float* active_masks,
-                        const float* vn_stats, float* grad_partials, double* loss_partials, void* stream);
+                        const float* vn_stats, float* grad_partials, double* loss_partials, void* workspace,
+                        void* stream);
 
 /* Sum the per-block partials in a fixed order: grad_sum float32 [P], loss_sum double [4].  In a multi-GPU job
  * the caller all-reduces both (sum) before mappo_adam_step. */

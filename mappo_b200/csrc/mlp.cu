@@ -14,6 +14,7 @@ namespace mappo {
 namespace tc {   // mlp_tc.cu: the tcgen05 tensor-core tiles
 bool supports(const mappo_net_config* cfg);
 int grid_for(long long rows);
+long long wide_workspace_bytes(long long rows);      // mlp_wide.cu
 template <int MODE> int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who);
 }  // namespace tc
 }  // namespace mappo
@@ -437,9 +438,9 @@ template <int MODE>
 static int launch_mlp(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
   if (int rc = check_net(cfg, who)) return rc;
   if (cfg->recurrent) MAPPO_UNSUPPORTED("%s: recurrent (GRU) networks are not built yet", who);
-  if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d not built yet", who, cfg->in_dim, kMaxIn);
   MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim, "%s: bad input arguments", who);
   if (use_tc(cfg)) return tc::launch<MODE>(a, cfg, stream, who);
+  if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d is built for critics on the tensor-core path only", who, cfg->in_dim, kMaxIn);
   a.L = make_layout(*cfg);
   if (a.x_div < 1) a.x_div = 1;
   a.Kp = (cfg->in_dim + 3) & ~3;
@@ -470,6 +471,11 @@ extern "C" int mappo_update_num_blocks(const mappo_net_config* cfg, long long ro
   return blocks_for(rows);
 }
 
+extern "C" long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long long rows) {
+  if (!cfg || rows < 0) return -1;
+  return (cfg->in_dim > kMaxIn && use_tc(cfg)) ? tc::wide_workspace_bytes(rows) : 0;
+}
+
 extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
                                    long long rows, const float* available_actions, int deterministic, uint64_t seed,
                                    uint64_t step, long long row_offset, const float* given_actions,
@@ -485,11 +491,13 @@ extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* par
 }
 
 extern "C" int mappo_critic_forward(const mappo_net_config* cfg, const float* params, const float* share_obs,
-                                    int obs_ld, long long rows, int group, float* values_out, void* stream) {
+                                    int obs_ld, long long rows, int group, float* values_out, void* workspace,
+                                    void* stream) {
   MAPPO_REQUIRE(values_out && group >= 1, "critic_forward: bad outputs");
   MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_forward: actor config");
   MlpArgs a{};
   a.params = params; a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.group = group; a.values_out = values_out;
+  a.workspace = workspace;
   return launch_mlp<1>(a, cfg, (cudaStream_t)stream, "critic_forward");
 }
 
@@ -512,7 +520,7 @@ extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss
                                    const int64_t* index, int share_rows_div, const float* value_preds,
                                    const float* returns,
                                    const float* active_masks, const float* vn_stats, float* grad_partials,
-                                   double* loss_partials, void* stream) {
+                                   double* loss_partials, void* workspace, void* stream) {
   MAPPO_REQUIRE(loss && value_preds && returns && grad_partials && loss_partials && group >= 1,
                 "critic_update: null pointer");
   MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_update: actor config");
@@ -523,6 +531,6 @@ extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss
   a.params = params; a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.group = group; a.index = index;
   a.x_div = share_rows_div;
   a.value_preds = value_preds; a.returns = returns; a.active = active_masks; a.vn_stats = vn_stats; a.loss = *loss;
-  a.grad_partials = grad_partials; a.loss_partials = loss_partials;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
   return launch_mlp<3>(a, cfg, (cudaStream_t)stream, "critic_update");
 }

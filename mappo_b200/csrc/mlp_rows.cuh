@@ -30,6 +30,8 @@ struct MlpArgs {
   const float* value_preds; const float* returns; const float* vn_stats;
   mappo_loss_config loss;
   float* grad_partials; double* loss_partials;
+  // wide first layer (mlp_wide.cu): caller scratch; z1 = its [rows][64] part (activations in, gradient out)
+  void* workspace; float* z1;
 };
 
 // log-softmax over l[0..n): returns logsumexp, writes logp in place

@@ -16,26 +16,26 @@
 //
 // Reference: mlp.py:6-59, act.py:41-162, distributions.py:14-68, r_actor_critic.py:43-107,146-165,
 //            r_mappo.py:52-136, utils/util.py:23-29.  LayerNorm-affine folding: net.cuh.
-#include "mlp_rows.cuh"
-#include "umma.cuh"
-#include <cuda_fp16.h>
+#include "mlp_tc_common.cuh"
 
 namespace mappo {
 namespace tc {
 
-constexpr int kThreads = 512, kBM = 128, kNP = 2;
 constexpr int kTmemCols = 512;
 constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 256, kColGh = 384;   // TMEM column map
-constexpr float kLoScale = 4096.0f, kLoInv = 1.0f / 4096.0f;            // the lo halves are stored times 2^12
-constexpr uint32_t kRowChunk = kBM * 16;                                 // bytes of one 8-column chunk of a 128-row tile
-constexpr uint32_t kWChunk = 64 * 16;                                    // ... of a 64-row weight tile
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
   uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, bhf, dbh, xch, xlog, red, bars, total;
   uint32_t x_piece, w1_piece;
+  int xlog_in_x;                 // 1: the head's partial logits live in the idle X buffer (see below), `xlog` unused
 };
-__host__ __device__ inline Map make_map(int Kp, int AS) {
+// The partial logits [4 column quarters][128 rows][AS] are written after the second layer and read before the
+// weight-gradient group is issued; in the update kernels the OTHER X buffer is idle over exactly that span (the previous
+// tile's fc1 weight gradient has completed, the next tile's rows are staged only after the block-wide barrier that
+// follows the last read), so they borrow it whenever they fit.  The rollout kernels have no BS / BS2 / DL / dbh regions
+// and keep a private one.
+__host__ __device__ inline Map make_map(int Kp, int AS, bool update) {
   Map m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
@@ -43,88 +43,31 @@ __host__ __device__ inline Map make_map(int Kp, int AS) {
   m.w1_piece = (uint32_t)(Kp / 8) * kWChunk;
   m.X = take(2 * kNP * m.x_piece);                 // two buffers: this tile's rows and the next tile's
   m.N1 = take(kNP * 8 * kRowChunk);
-  m.BS = take(kNP * 8 * kRowChunk);                 // dz2, then dz1
-  m.BS2 = take(kNP * 8 * kRowChunk);                // n2 (operand of the head weight gradient)
+  m.BS = take(update ? kNP * 8 * kRowChunk : 0);    // dz2, then dz1
+  m.BS2 = take(update ? kNP * 8 * kRowChunk : 0);   // n2 (operand of the head weight gradient)
   m.W1 = take(kNP * m.w1_piece);
   m.W2 = take(kNP * 8 * kWChunk);
-  m.DL = take(kNP * 2 * kRowChunk);
+  m.DL = take(update ? kNP * 2 * kRowChunk : 0);
   m.Whf = take(kMaxA * 64 * 4);
   m.b1f = take(64 * 4);
   m.b2f = take(64 * 4);
   m.bhf = take(kMaxA * 4);
-  m.dbh = take(kBM * AS * 4);
+  m.dbh = take(update ? kBM * AS * 4 : 0);
   m.xch = take(2 * 4 * kBM * 8);
-  m.xlog = take(4 * kBM * AS * 4);
+  m.xlog_in_x = (update && (uint32_t)(4 * kBM * AS * 4) <= kNP * m.x_piece) ? 1 : 0;
+  m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 2);
   m.bars = take(64);
   m.total = o;
   return m;
 }
 
-// ---- small device helpers -----------------------------------------------------------------------------
-__device__ __forceinline__ void bar_named(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
-
-// tanh in fp32: 1 - 2 / (exp(2|x|) + 1) with ex2.approx / rcp.approx (absolute error ~1.5e-7)
-__device__ __forceinline__ float tanh_fast(float x) {
-  const float ax = fabsf(x);
-  float e, r;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * 2.885390081777927f));   // 2 * log2(e)
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
-  return copysignf(fmaf(-2.0f, r, 1.0f), x);
-}
-__device__ __forceinline__ float act_tc(float z, int relu) { return relu ? fmaxf(z, 0.0f) : tanh_fast(z); }
-
-// 8 consecutive fp32 -> one 16-byte chunk of fp16 `hi` and one of (scaled) `lo`
-__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
-  uint32_t h[4], l[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-    const float2 hf = __half22float2(hh);
-    const __half2 ll = __floats2half2_rn((v[2 * i] - hf.x) * kLoScale, (v[2 * i + 1] - hf.y) * kLoScale);
-    h[i] = *reinterpret_cast<const uint32_t*>(&hh);
-    l[i] = *reinterpret_cast<const uint32_t*>(&ll);
-  }
-  hi = make_uint4(h[0], h[1], h[2], h[3]);
-  lo = make_uint4(l[0], l[1], l[2], l[3]);
-}
-
-// store this thread's 16 columns [16*cq, 16*cq+16) of row r into a 128-row, 64-column operand tile (both pieces)
-__device__ __forceinline__ void store_cols16(unsigned char* tile, int r, int cq, const float* v) {
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint4 hi, lo;
-    split8(v + 8 * h, hi, lo);
-    const uint32_t off = (uint32_t)(2 * cq + h) * kRowChunk + (uint32_t)r * 16;
-    *reinterpret_cast<uint4*>(tile + off) = hi;
-    *reinterpret_cast<uint4*>(tile + 8 * kRowChunk + off) = lo;
-  }
-}
-
-// sum (a, b) over the 4 threads that share a row; `slot` alternates between two exchange buffers
-__device__ __forceinline__ float2 row_sum2(float a, float b, float2* xch, int& slot, int cq, int r, int q4) {
-  float2* buf = xch + slot * (4 * kBM);
-  buf[cq * kBM + r] = make_float2(a, b);
-  bar_named(1 + q4, 128);
-  const float2 p0 = buf[r], p1 = buf[kBM + r], p2 = buf[2 * kBM + r], p3 = buf[3 * kBM + r];
-  slot ^= 1;
-  return make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
-}
-
 // ---- prologue: fold the LayerNorm affines into the following Linear (net.cuh), split into fp16 pairs, stage
-__device__ __forceinline__ void put_pair(unsigned char* tile, uint32_t piece, int R, int r, int c, float v) {
-  const __half hi = __float2half_rn(v);
-  const __half lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
-  const uint32_t off = umma::tile_off16(R, r, c);
-  *reinterpret_cast<__half*>(tile + off) = hi;
-  *reinterpret_cast<__half*>(tile + piece + off) = lo;
-}
-
-__device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a) {
+__device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a, bool with_w1, bool update) {
   const NetLayout& L = a.L;
   const float* __restrict__ P = a.params;
   const int D = L.in_dim, Kp = a.Kp, tid = threadIdx.x;
-  for (int e = tid; e < 64 * Kp; e += kThreads) {
+  for (int e = tid; with_w1 && e < 64 * Kp; e += kThreads) {
     const int j = e / Kp, k = e - j * Kp;
     float v = 0.0f;
     if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
@@ -163,7 +106,7 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     reinterpret_cast<float*>(sm + m.bhf)[aidx] = s;
   }
   float* dbh = reinterpret_cast<float*>(sm + m.dbh);
-  for (int e = tid; e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
+  for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
 }
 
 // ---- MMA issue (one thread) ------------------------------------------------------------------------------
@@ -323,7 +266,8 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
 // Per tile the update issues three groups of MMAs -- {fc2}, {head wgrad, fc2 wgrad, fc2 dgrad}, {fc1 wgrad, fc1 of
 // the NEXT tile} -- so there are three CTA-wide synchronisations per tile; the next tile's input rows are staged
 // into the second X buffer while the second group runs on the tensor cores.
-template <int MODE, int KP, int AMAX>
+// WIDE: the first layer lives outside (mlp_wide.cu): z1 rows come from a.z1 and dLoss/dz1 goes back in place.
+template <int MODE, int KP, int AMAX, bool WIDE>
 __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE >= 2);
   extern __shared__ __align__(1024) unsigned char sm[];
@@ -331,17 +275,17 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __shared__ double lred[4][kThreads / 32];
   const NetLayout& L = a.L;
   const int A = L.a_total, relu = L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS);
+  const Map m = make_map(KP, AS, UPDATE);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
   if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
-  stage_weights_tc(sm, m, a);
+  stage_weights_tc(sm, m, a, !WIDE, UPDATE);
   int slot = 0;
   float2* xch = reinterpret_cast<float2*>(sm + m.xch);
   long long tile = blockIdx.x;
-  stage_x<KP>(a, tile, sm + m.X, m.x_piece, xch, slot, cq, r, q4);
+  if (!WIDE) stage_x<KP>(a, tile, sm + m.X, m.x_piece, xch, slot, cq, r, q4);
   umma::fence_async_smem();
   umma::tc_fence_before();
   __syncthreads();
@@ -352,7 +296,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   const uint32_t sX = umma::smem_u32(sm + m.X), sN1 = umma::smem_u32(sm + m.N1), sBS = umma::smem_u32(sm + m.BS);
   const uint32_t sB2 = umma::smem_u32(sm + m.BS2), sW1 = umma::smem_u32(sm + m.W1), sW2 = umma::smem_u32(sm + m.W2);
   const uint32_t sDL = umma::smem_u32(sm + m.DL);
-  float* xlog = reinterpret_cast<float*>(sm + m.xlog);
   const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
   const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
   const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
@@ -360,7 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
-  if (tid == 0) {
+  if (tid == 0 && !WIDE) {
     issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX, m.x_piece, sW1, m.w1_piece, kWChunk, 128, 2 * kWChunk, KP / 16, kIdFwd);
     umma::mma_commit(bar);
   }
@@ -390,9 +333,18 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     }
     // ---- layer 1 epilogue
     float n1[16], mean1, rstd1;
-    umma::mbar_wait(bar, ph); ph ^= 1;
-    umma::tc_fence_after();
-    load_acc16(lane_addr, cq, n1);
+    if (WIDE) {
+      const float4* zp = reinterpret_cast<const float4*>(a.z1 + g * 64 + 16 * cq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 z = valid ? zp[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        n1[4 * i] = z.x; n1[4 * i + 1] = z.y; n1[4 * i + 2] = z.z; n1[4 * i + 3] = z.w;
+      }
+    } else {
+      umma::mbar_wait(bar, ph); ph ^= 1;
+      umma::tc_fence_after();
+      load_acc16(lane_addr, cq, n1);
+    }
     act_ln16(n1, b1f, relu, xch, slot, cq, r, q4, mean1, rstd1);
     store_cols16(sm + m.N1, r, cq, n1);
     umma::fence_async_smem();
@@ -410,6 +362,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     load_acc16(lane_addr, cq, n2);
     act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
     if (UPDATE) store_cols16(sm + m.BS2, r, cq, n2);
+    float* xlog = reinterpret_cast<float*>(sm + (m.xlog_in_x ? m.X + (buf ^ 1) * x_bytes : m.xlog));
     {
       float* mine = xlog + (size_t)(cq * kBM + r) * AS;
 #pragma unroll
@@ -441,6 +394,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         if (MODE == 0) actor_rollout_row(a, g, l);
         if (MODE == 1) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
       }
+      if (WIDE) continue;
       if (has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
       umma::fence_async_smem();
       umma::tc_fence_before();
@@ -533,7 +487,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
     }
     // ---- next tile's input rows, staged while the tensor cores work
-    if (has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
+    if (!WIDE && has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
@@ -541,6 +495,15 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
 #pragma unroll
     for (int i = 0; i < 16; ++i) db1[i] += dz[i];
+    if (WIDE) {                                                          // dLoss/dz1 leaves for wgrad1_wide_kernel
+      if (valid) {
+        float4* zp = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) zp[i] = make_float4(dz[4 * i], dz[4 * i + 1], dz[4 * i + 2], dz[4 * i + 3]);
+      }
+      first = false;
+      continue;
+    }
     store_cols16(sm + m.BS, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
@@ -559,7 +522,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   // ---- epilogue: weight gradients TMEM -> two partial rows per CTA (the hi-half and the lo-half lanes of the stacked A operand), in the flat
   // parameter layout (G in the W slots, db in the b slots; LayerNorm-affine slots stay zero, optim.cu fills them)
   if (UPDATE) {
-    umma::mbar_wait(bar, ph); ph ^= 1;                                  // the last tile's fc1 weight gradient
+    if (!WIDE) { umma::mbar_wait(bar, ph); ph ^= 1; }                   // the last tile's fc1 weight gradient
     umma::tc_fence_after();
     float* __restrict__ gp0 = a.grad_partials + (size_t)(2 * blockIdx.x) * L.total;
     for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;
@@ -581,7 +544,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::tmem_ld16(lane_addr + kColG2 + 64 + 16 * cq, w);
 #pragma unroll
       for (int i = 0; i < 16; ++i) gp[L.w2 + mrow * 64 + 16 * cq + i] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
-      if (cq < KP / 16) {
+      if (!WIDE && cq < KP / 16) {
         umma::tmem_ld16(lane_addr + kColG1 + 16 * cq, u);
         umma::tmem_ld16(lane_addr + kColG1 + KP + 16 * cq, w);
 #pragma unroll
@@ -655,14 +618,25 @@ int grid_for(long long rows) {
   return (int)(ntiles < sms ? (ntiles < 1 ? 1 : ntiles) : sms);
 }
 
+bool wide_supports(const mappo_net_config* cfg);                                      // mlp_wide.cu
+long long wide_workspace_bytes(long long rows);
+int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
+int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
+
 bool supports(const mappo_net_config* cfg) {
-  return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim <= 64;
+  if (wide_supports(cfg)) return true;
+  if (!(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim <= 64)) return false;
+  int A = 0;
+  for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
+  if (cfg->is_critic) A = 1;
+  const int Kp = cfg->in_dim <= 32 ? 32 : 64;
+  return make_map(Kp, A | 1, true).total <= (uint32_t)kMaxDynSmem && make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
-template <int MODE, int KP, int AMAX>
+template <int MODE, int KP, int AMAX, bool WIDE = false>
 static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
-  const Map m = make_map(KP, a.L.a_total | 1);
-  auto kern = mlp_tc_kernel<MODE, KP, AMAX>;
+  const Map m = make_map(KP, a.L.a_total | 1, MODE >= 2);
+  auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE>;
   static bool attr_set = false;
   if (!attr_set) {
     MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
@@ -682,6 +656,15 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
   a.ntiles = (a.rows + kBM - 1) / kBM;
   constexpr bool kCritic = (MODE == 1 || MODE == 3);
   if constexpr (kCritic) {
+    if (cfg->in_dim > 64) {                     // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
+      MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
+      a.Kp = 32;
+      a.z1 = static_cast<float*>(a.workspace);
+      if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
+      if (int rc = launch_one<MODE, 32, 1, true>(a, stream, who)) return rc;
+      if (MODE == 3) return launch_wide_wgrad1(a, a.workspace, stream, who);
+      return 0;
+    }
     if (a.Kp == 32) return launch_one<MODE, 32, 1>(a, stream, who);
     return launch_one<MODE, 64, 1>(a, stream, who);
   } else {

@@ -1,0 +1,77 @@
+// Pieces shared by the tensor-core policy kernels (mlp_tc.cu: the fused 64-wide network; mlp_wide.cu: the first layer
+// of a wide-input network as two streaming GEMMs): tile constants, the fp16-pair split, operand-tile stores in the
+// chunk-major layout of umma.cuh, and the 4-thread row exchange.
+#pragma once
+#include "mlp_rows.cuh"
+#include "umma.cuh"
+#include <cuda_fp16.h>
+
+namespace mappo {
+namespace tc {
+
+constexpr int kThreads = 512, kBM = 128, kNP = 2;
+constexpr float kLoScale = 4096.0f, kLoInv = 1.0f / 4096.0f;            // the lo halves are stored times 2^12
+constexpr uint32_t kRowChunk = kBM * 16;                                 // bytes of one 8-column chunk of a 128-row tile
+constexpr uint32_t kWChunk = 64 * 16;                                    // ... of a 64-row weight tile
+
+// ---- small device helpers -----------------------------------------------------------------------------
+__device__ __forceinline__ void bar_named(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+// tanh in fp32: 1 - 2 / (exp(2|x|) + 1) with ex2.approx / rcp.approx (absolute error ~1.5e-7)
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float ax = fabsf(x);
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * 2.885390081777927f));   // 2 * log2(e)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+  return copysignf(fmaf(-2.0f, r, 1.0f), x);
+}
+__device__ __forceinline__ float act_tc(float z, int relu) { return relu ? fmaxf(z, 0.0f) : tanh_fast(z); }
+
+// 8 consecutive fp32 -> one 16-byte chunk of fp16 `hi` and one of (scaled) `lo`
+__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    const float2 hf = __half22float2(hh);
+    const __half2 ll = __floats2half2_rn((v[2 * i] - hf.x) * kLoScale, (v[2 * i + 1] - hf.y) * kLoScale);
+    h[i] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[i] = *reinterpret_cast<const uint32_t*>(&ll);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// store this thread's 16 columns [16*cq, 16*cq+16) of row r into a 128-row, 64-column operand tile (both pieces)
+__device__ __forceinline__ void store_cols16(unsigned char* tile, int r, int cq, const float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint4 hi, lo;
+    split8(v + 8 * h, hi, lo);
+    const uint32_t off = (uint32_t)(2 * cq + h) * kRowChunk + (uint32_t)r * 16;
+    *reinterpret_cast<uint4*>(tile + off) = hi;
+    *reinterpret_cast<uint4*>(tile + 8 * kRowChunk + off) = lo;
+  }
+}
+
+// sum (a, b) over the 4 threads that share a row; `slot` alternates between two exchange buffers
+__device__ __forceinline__ float2 row_sum2(float a, float b, float2* xch, int& slot, int cq, int r, int q4) {
+  float2* buf = xch + slot * (4 * kBM);
+  buf[cq * kBM + r] = make_float2(a, b);
+  bar_named(1 + q4, 128);
+  const float2 p0 = buf[r], p1 = buf[kBM + r], p2 = buf[2 * kBM + r], p3 = buf[3 * kBM + r];
+  slot ^= 1;
+  return make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+}
+
+// one fp32 value -> (hi, lo) fp16 at (r, c) of an R-row chunk-major tile
+__device__ __forceinline__ void put_pair(unsigned char* tile, uint32_t piece, int R, int r, int c, float v) {
+  const __half hi = __float2half_rn(v);
+  const __half lo = __float2half_rn((v - __half2float(hi)) * kLoScale);
+  const uint32_t off = umma::tile_off16(R, r, c);
+  *reinterpret_cast<__half*>(tile + off) = hi;
+  *reinterpret_cast<__half*>(tile + piece + off) = lo;
+}
+
+}  // namespace tc
+}  // namespace mappo

@@ -1,0 +1,386 @@
+// First layer of a WIDE-input network (in_dim > 64: the centralised critic of many-agent scenarios, share_obs =
+// M * obs_dim = 460 for simple_spread with 10 agents) as two streaming tensor-core GEMMs around the fused 64-wide kernel
+// of mlp_tc.cu:
+//
+//   fc1_wide_kernel     z1[rows][64]  = LayerNorm_feat(x)[rows][D] . W1'^T          (forward; also writes the row
+//                                                                                     statistics mean, rstd)
+//   mlp_tc_kernel<WIDE> reads z1 where it would read its own fc1 accumulator, and writes dz1 = dLoss/dz1 in place
+//   wgrad1_wide_kernel  G1[64][D]     = sum_rows dz1[row][:]^T x^[row][:]           (weight gradient, split over rows and
+//                                                                                     column groups; partial rows of the
+//                                                                                     CTAs go to the W1 slots of the
+//                                                                                     main kernel's gradient partials)
+//
+// Both kernels are bound by reading x once from HBM (D * 4 bytes per row); the products use the fp16-pair scheme of
+// mlp_tc.cu (hi*hi + 2^-12 (hi*lo + lo*hi), fp32 accumulation in TMEM).  x rows are normalised without the affine,
+// which is folded into W1' (net.cuh), so G1 / db1 are gradients with respect to the folded weights as everywhere else.
+//
+// Reference: mlp.py:44-59 (feature_norm, fc1), r_actor_critic.py:146-165, r_mappo.py:52-89,151-156.
+#include "mlp_tc_common.cuh"
+
+namespace mappo {
+namespace tc {
+
+struct WideArgs {
+  NetLayout L;
+  const float* params;
+  const float* x; int ld; long long rows; const int64_t* index; int x_div;
+  int vec;                       // 1: x rows are 16-byte aligned (float4 loads)
+  float* z1;                     // [rows][64]   forward: out
+  float* xstats;                 // [rows][2]    forward: out, weight gradient: in
+  const float* dz1;              // [rows][64]   weight gradient: in
+  float* grad_partials;          // weight gradient: partial rows [2 * nsplit][L.total] (W1 slot written)
+  int nsplit, ncg, colw;         // weight gradient: row splits, column groups, columns per group (multiple of 16, <= 240)
+};
+
+// 8 consecutive floats of a row, columns [c, c + 8), zero beyond D
+__device__ __forceinline__ void load8(const float* __restrict__ row, int c, int D, bool ok, int vec, float (&v)[8]) {
+  if (ok && vec && c + 8 <= D) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(row + c));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(row + c + 4));
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (ok && c + i < D) ? __ldg(row + c + i) : 0.0f;
+  }
+}
+
+// ---- forward ---------------------------------------------------------------------------------------------
+// Shared memory: W1' as the K-major B operand (both fp16 pieces, K padded to a multiple of 16), two X buffers of
+// one 64-column K-chunk each (128 rows, both pieces), the row-exchange buffers, two mbarriers (one per X buffer).
+struct FwdMap { uint32_t W, w_piece, X, xch, bars, total; int K16; };
+__host__ __device__ inline FwdMap make_fwd_map(int D) {
+  FwdMap m;
+  m.K16 = (D + 15) / 16;
+  m.w_piece = (uint32_t)(2 * m.K16) * kWChunk;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.W = take(2 * m.w_piece);
+  m.X = take(2 * 2 * 8 * kRowChunk);
+  m.xch = take(2 * 4 * kBM * 8);
+  m.bars = take(64);
+  m.total = o;
+  return m;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const NetLayout& L = a.L;
+  const int D = L.in_dim;
+  const FwdMap m = make_fwd_map(D);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + m.bars);          // bars[b]: MMAs that read X buffer b
+  if (tid == 0) { umma::mbar_init(bars, 1); umma::mbar_init(bars + 1, 1); umma::fence_mbar_init(); }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 128);
+  {
+    const float* __restrict__ P = a.params;
+    const int Kp = 16 * m.K16;
+    for (int e = tid; e < 64 * Kp; e += kThreads) {
+      const int j = e / Kp, k = e - j * Kp;
+      float v = 0.0f;
+      if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+      put_pair(sm + m.W, m.w_piece, 64, j, k, v);
+    }
+  }
+  umma::fence_async_smem();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+  const uint32_t sX = umma::smem_u32(sm + m.X), sW = umma::smem_u32(sm + m.W);
+  constexpr uint32_t kXBuf = 2 * 8 * kRowChunk;
+  constexpr uint32_t kId = umma::idesc_f16(128, 64, 0, 0);
+  float2* xch = reinterpret_cast<float2*>(sm + m.xch);
+  int slot = 0;
+  const int nkc = (m.K16 + 3) / 4;                                     // 64-column K-chunks per tile
+  uint32_t n = 0;                                                      // MMA groups committed so far
+  long long prev_g = -1;                                               // row whose accumulators are still in TMEM
+
+  auto wait_commit = [&](uint32_t c) { umma::mbar_wait(bars + (c & 1), (c >> 1) & 1); };
+  auto drain = [&](long long g) {                                      // accumulators -> z1 row g
+    wait_commit(n - 1);
+    umma::tc_fence_after();
+    float u[16], w[16];
+    umma::tmem_ld16(lane_addr + 16 * cq, u);
+    umma::tmem_ld16(lane_addr + 64 + 16 * cq, w);
+    if (g < a.rows) {
+      float4* out = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        out[i] = make_float4(fmaf(w[4 * i], kLoInv, u[4 * i]), fmaf(w[4 * i + 1], kLoInv, u[4 * i + 1]),
+                             fmaf(w[4 * i + 2], kLoInv, u[4 * i + 2]), fmaf(w[4 * i + 3], kLoInv, u[4 * i + 3]));
+    }
+    umma::tc_fence_before();
+    __syncthreads();
+  };
+
+  for (long long tile = blockIdx.x; tile < (a.rows + kBM - 1) / kBM; tile += gridDim.x) {
+    const long long g = tile * kBM + r;
+    const bool valid = g < a.rows;
+    const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+    const float* __restrict__ row = a.x + srow * (long long)a.ld;
+    // row statistics over in_dim, shifted by the first element (mlp.py:44-45: LayerNorm, eps 1e-5)
+    float mean = 0.0f, rstd = 1.0f;
+    if (L.use_fn) {
+      const float x0 = valid ? __ldg(row) : 0.0f;
+      float s = 0.0f, q = 0.0f;
+      for (int ch = cq; ch < (D + 7) / 8; ch += 4) {
+        float v[8];
+        load8(row, 8 * ch, D, valid, a.vec, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float d = (8 * ch + i < D) ? v[i] - x0 : 0.0f;
+          s += d;
+          q = fmaf(d, d, q);
+        }
+      }
+      const float2 tot = row_sum2(s, q, xch, slot, cq, r, q4);
+      const float ms = tot.x / (float)D;
+      const float var = fmaxf(tot.y / (float)D - ms * ms, 0.0f);
+      mean = x0 + ms;
+      rstd = 1.0f / sqrtf(var + kLnEps);
+    }
+    if (cq == 0 && valid && a.xstats) { a.xstats[2 * g] = mean; a.xstats[2 * g + 1] = rstd; }
+    for (int kc = 0; kc < nkc; ++kc) {
+      const uint32_t b = n & 1;
+      const int ksteps = min(4, m.K16 - 4 * kc);
+      if (n >= 2) wait_commit(n - 2);                                  // X buffer b is free again
+      if (cq < ksteps) {
+        float v[16];
+        const int c0 = 64 * kc + 16 * cq;
+        load8(row, c0, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v));
+        load8(row, c0 + 8, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v + 8));
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = (valid && c0 + i < D) ? (v[i] - mean) * rstd : 0.0f;
+        store_cols16(sm + m.X + b * kXBuf, r, cq, v);
+      }
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (kc == 0 && prev_g >= 0) drain(prev_g);                      // previous tile leaves TMEM before fc1 restarts
+      if (tid == 0) {
+        umma::tc_fence_after();
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint32_t ao = sX + b * kXBuf + (uint32_t)ks * 2 * kRowChunk;
+          const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * kWChunk;
+          const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
+          const uint64_t bh = umma::smem_desc(bo, kWChunk, 128), bl = umma::smem_desc(bo + m.w_piece, kWChunk, 128);
+          const bool acc = kc > 0 || ks > 0;
+          umma::mma_f16(tb, ah, bh, kId, acc);
+          umma::mma_f16(tb + 64, ah, bl, kId, acc);
+          umma::mma_f16(tb + 64, al, bh, kId, true);
+        }
+        umma::mma_commit(bars + b);
+      }
+      ++n;
+    }
+    prev_g = g;
+  }
+  if (prev_g >= 0) drain(prev_g);
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 128);
+}
+
+// ---- weight gradient ---------------------------------------------------------------------------------------
+// CTA (column group cg, row split sp) accumulates G[128 = dz1 hi | dz1 lo][colw] over its 64-row half tiles in two TMEM
+// blocks (x^ hi at column 0, x^ lo at column 256).  Operands are MN-major (the contraction runs over the rows): A =
+// dz1 [64 rows][128], B = x^ [64 rows][colw] per piece.  One operand buffer; the next half tile's values are
+// prefetched into registers while the tensor cores read the current one.
+constexpr int kHR = 64;                                    // rows per half tile
+constexpr uint32_t kHChunk = kHR * 16;                     // bytes of one 8-column chunk of a 64-row operand tile
+constexpr int kMaxColw = 240;
+constexpr int kXChunksPerThread = 4;                       // ceil(30 chunks / 8 column subsets)
+
+struct WgMap { uint32_t A, B, b_piece, bars, total; };
+__host__ __device__ inline WgMap make_wg_map(int colw) {
+  WgMap m;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.A = take(16 * kHChunk);
+  m.b_piece = (uint32_t)(colw / 8) * kHChunk;
+  m.B = take(2 * m.b_piece);
+  m.bars = take(64);
+  m.total = o;
+  return m;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs a) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const NetLayout& L = a.L;
+  const int D = L.in_dim, colw = a.colw;
+  const WgMap m = make_wg_map(colw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int cg = blockIdx.x % a.ncg, sp = blockIdx.x / a.ncg;
+  const int col0 = cg * colw;
+  const int hr = 32 * (warp & 1) + lane;                  // row of the half tile this thread stages
+  const int cs = warp >> 1;                               // column subset: chunks cs, cs + 8, ...
+  const int nchx = colw / 8;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 512);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const uint32_t sA = umma::smem_u32(sm + m.A), sB = umma::smem_u32(sm + m.B);
+  const uint32_t idesc = umma::idesc_f16(128, colw, 1, 1);
+  const long long nht = (a.rows + kHR - 1) / kHR;
+
+  float xr[kXChunksPerThread][8], dr[8], mean = 0.0f, rstd = 1.0f;
+  bool valid = false;
+  auto prefetch = [&](long long ht) {
+    const long long g = ht * kHR + hr;
+    valid = g < a.rows;
+    const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+    const float* __restrict__ row = a.x + srow * (long long)a.ld;
+    if (L.use_fn && valid) { mean = __ldg(a.xstats + 2 * g); rstd = __ldg(a.xstats + 2 * g + 1); }
+    else { mean = 0.0f; rstd = 1.0f; }
+#pragma unroll
+    for (int i = 0; i < kXChunksPerThread; ++i) {
+      const int ch = cs + 8 * i;
+      if (ch < nchx) load8(row, col0 + 8 * ch, D, valid, a.vec, xr[i]);
+    }
+    if (valid) {
+      const float4 p = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * 64 + 8 * cs));
+      const float4 q = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * 64 + 8 * cs + 4));
+      dr[0] = p.x; dr[1] = p.y; dr[2] = p.z; dr[3] = p.w; dr[4] = q.x; dr[5] = q.y; dr[6] = q.z; dr[7] = q.w;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dr[i] = 0.0f;
+    }
+  };
+
+  uint32_t n = 0;
+  long long ht = sp;
+  if (ht < nht) prefetch(ht);
+  for (; ht < nht; ht += a.nsplit) {
+    if (n > 0) umma::mbar_wait(bar, (n - 1) & 1);                       // the operand buffer is free again
+    {
+      uint4 hi, lo;
+#pragma unroll
+      for (int i = 0; i < kXChunksPerThread; ++i) {
+        const int ch = cs + 8 * i;
+        if (ch < nchx) {
+          float v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] = (valid && col0 + 8 * ch + e < D) ? (xr[i][e] - mean) * rstd : 0.0f;
+          split8(v, hi, lo);
+          const uint32_t off = (uint32_t)ch * kHChunk + (uint32_t)hr * 16;
+          *reinterpret_cast<uint4*>(sm + m.B + off) = hi;
+          *reinterpret_cast<uint4*>(sm + m.B + m.b_piece + off) = lo;
+        }
+      }
+      split8(dr, hi, lo);
+      const uint32_t off = (uint32_t)cs * kHChunk + (uint32_t)hr * 16;
+      *reinterpret_cast<uint4*>(sm + m.A + off) = hi;
+      *reinterpret_cast<uint4*>(sm + m.A + 8 * kHChunk + off) = lo;
+    }
+    umma::fence_async_smem();
+    umma::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      umma::tc_fence_after();
+#pragma unroll
+      for (int ks = 0; ks < kHR / 16; ++ks) {
+        const uint64_t da = umma::smem_desc(sA + (uint32_t)ks * 256, 128, kHChunk);
+        const uint64_t dh = umma::smem_desc(sB + (uint32_t)ks * 256, 128, kHChunk);
+        const uint64_t dl = umma::smem_desc(sB + m.b_piece + (uint32_t)ks * 256, 128, kHChunk);
+        umma::mma_f16(tb, da, dh, idesc, n > 0 || ks > 0);
+        umma::mma_f16(tb + 256, da, dl, idesc, n > 0 || ks > 0);
+      }
+      umma::mma_commit(bar);
+    }
+    ++n;
+    if (ht + a.nsplit < nht) prefetch(ht + a.nsplit);
+  }
+  // ---- G -> the W1 slots of partial rows 2 sp (lanes 0..63: dz1 hi) and 2 sp + 1 (lanes 64..127: dz1 lo, scaled)
+  if (n > 0) {
+    umma::mbar_wait(bar, (n - 1) & 1);
+    umma::tc_fence_after();
+    const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+    const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+    float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * L.total + L.w1 + (size_t)(r & 63) * D;
+    const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;
+    for (int blk = cq; blk < colw / 16; blk += 4) {
+      float u[16], w[16];
+      umma::tmem_ld16(lane_addr + 16 * blk, u);
+      umma::tmem_ld16(lane_addr + 256 + 16 * blk, w);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int k = col0 + 16 * blk + i;
+        if (k < D) gp[k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+      }
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 512);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+constexpr int kWideMaxSmem = 232448 - 1024;
+
+int grid_for(long long rows);                                             // mlp_tc.cu
+
+bool wide_supports(const mappo_net_config* cfg) {
+  return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->is_critic && cfg->in_dim > 64 &&
+         make_fwd_map(cfg->in_dim).total <= (uint32_t)kWideMaxSmem;
+}
+
+// bytes of the caller-provided scratch: z1 / dz1 [rows][64] (the gradient overwrites the activations in place) and the
+// row statistics [rows][2]
+long long wide_workspace_bytes(long long rows) { return rows * 64 * 4 + rows * 2 * 4; }
+
+static void fill(WideArgs& w, const MlpArgs& a, void* workspace) {
+  w.L = a.L; w.params = a.params; w.x = a.x; w.ld = a.ld; w.rows = a.rows; w.index = a.index;
+  w.x_div = a.x_div < 1 ? 1 : a.x_div;
+  w.vec = ((reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 && (a.ld & 3) == 0) ? 1 : 0;
+  w.z1 = static_cast<float*>(workspace);
+  w.xstats = w.z1 + a.rows * 64;
+  w.dz1 = w.z1;
+}
+
+int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
+  WideArgs w{};
+  fill(w, a, workspace);
+  const FwdMap m = make_fwd_map(a.L.in_dim);
+  MAPPO_REQUIRE(m.total <= (uint32_t)kWideMaxSmem, "%s: in_dim %d too wide for the staged first layer", who, a.L.in_dim);
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(fc1_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideMaxSmem));
+    attr_set = true;
+  }
+  fc1_wide_kernel<<<grid_for(a.rows), kThreads, m.total, stream>>>(w);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
+  WideArgs w{};
+  fill(w, a, workspace);
+  const int D = a.L.in_dim;
+  w.ncg = (D + kMaxColw - 1) / kMaxColw;
+  w.colw = (((D + w.ncg - 1) / w.ncg) + 15) & ~15;
+  const long long nht = (a.rows + kHR - 1) / kHR;
+  long long ns = grid_for(a.rows) / w.ncg;                               // <= the main kernel's CTAs (2 partial rows each)
+  if (ns < 1) ns = 1;
+  if (ns > nht) ns = nht;
+  w.nsplit = (int)ns;
+  w.grad_partials = a.grad_partials;
+  const WgMap m = make_wg_map(w.colw);
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideMaxSmem));
+    attr_set = true;
+  }
+  wgrad1_wide_kernel<<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+}  // namespace tc
+}  // namespace mappo

@@ -159,9 +159,9 @@ _lib._EXTRA_SIGS.update({
     "mappo_actor_forward": [_NC, _P, _P, C.c_int, C.c_longlong, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_longlong,
                             _P, _P, _P, _P, _P],
     "mappo_advantages": [_P, _P, _P, _P, C.c_longlong, _P, _P, _P],
-    "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P],
+    "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
     "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P],
-    "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P],
     "mappo_grad_reduce": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
     "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
 })
@@ -222,12 +222,31 @@ def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=No
     return out, stats3
 
 
+_WORKSPACES = {}
+
+
+def mlp_workspace(cfg, rows, device):
+    """Scratch for a wide (in_dim > 64) critic call, grown on demand and kept per device; None when not needed."""
+    L = _lib.lib()
+    L.mappo_mlp_workspace_bytes.argtypes = [_NC, C.c_longlong]
+    L.mappo_mlp_workspace_bytes.restype = C.c_longlong
+    need = int(L.mappo_mlp_workspace_bytes(C.byref(cfg), int(rows)))
+    if need <= 0:
+        return None
+    ws = _WORKSPACES.get(device)
+    if ws is None or ws.numel() * 4 < need:
+        ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=device)
+        _WORKSPACES[device] = ws
+    return ws
+
+
 def critic_forward(cfg, params, share_obs, values_out, group=1):
     x, ld = _rows_view(share_obs)
     assert values_out.numel() == x.shape[0] * group
+    ws = mlp_workspace(cfg, x.shape[0], x.device)
     with TIMERS.span("critic_forward"):
         check(_lib.lib().mappo_critic_forward(C.byref(cfg), ptr(params), _vp(x), ld, x.shape[0], int(group),
-                                              ptr(values_out), stream_ptr()), "critic_forward")
+                                              ptr(values_out), ptr(ws), stream_ptr()), "critic_forward")
 
 
 def update_num_blocks(cfg, rows):
@@ -252,11 +271,12 @@ def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_mas
                   loss_partials, group=1, index=None, share_rows_div=1):
     x, ld = _rows_view(share_obs)
     rows = x.shape[0] if index is None else index.numel()
+    ws = mlp_workspace(cfg, rows, x.device)
     with TIMERS.span("critic_update"):
         check(_lib.lib().mappo_critic_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, rows, int(group),
                                              ptr(index), int(share_rows_div), ptr(value_preds), ptr(returns),
                                              ptr(active_masks), ptr(vn_stats), ptr(grad_partials), ptr(loss_partials),
-                                             stream_ptr()), "critic_update")
+                                             ptr(ws), stream_ptr()), "critic_update")
 
 
 def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):

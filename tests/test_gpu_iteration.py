@@ -8,3 +8,9 @@ pytestmark = pytest.mark.gpu
 def test_full_iteration_matches_oracle():
     import __graft_entry__ as g
     g._smoke_iteration()
+
+
+def test_full_iteration_ten_agents_wide_critic():
+    """BASELINE config C5 shape: M = 10 (obs 46, share_obs 460 -> the critic's wide first layer)."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=10, N=48)

@@ -1,0 +1,99 @@
+"""GPU: the wide-input centralised critic (BASELINE config C5: share_obs = 10 agents x 46 = 460 columns) -- the first
+layer runs as two streaming tensor-core GEMMs (csrc/mlp_wide.cu) around the fused 64-wide kernel.  Values, value
+loss and PRE-clip gradients against the oracle (oracle/policy.py, torch CPU fp32 + autograd) on the same inputs."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(S, B, flags="", seed=0):
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.spaces import Box, Discrete
+    from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    from mappo_b200.algorithms.r_mappo.r_mappo import R_MAPPO
+    a = parse_args(("--scenario_name simple_spread --num_agents 10 --ppo_epoch 1 " + flags).split())
+    torch.manual_seed(seed)
+    box = lambda n: Box(-np.inf, np.inf, (n,), np.float32)
+    pol = R_MAPPOPolicy(a, box(46), box(S), Discrete(5), device="cuda")
+    g = torch.Generator(device="cuda").manual_seed(seed + 1)
+    for net in (pol.actor, pol.critic):                     # LayerNorm affines and biases away from (1, 0)
+        net.flat.add_(0.05 * torch.randn(net.flat.shape, device="cuda", generator=g))
+    tr = R_MAPPO(a, pol, device="cuda")
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    share = r(B, S) * (0.5 + r(1, S).abs()) + 0.3 * r(1, S)
+    sample = (share, r(B, 46), None, None, torch.randint(0, 5, (B, 1), device="cuda", generator=g).float(),
+              0.5 * r(B, 1), 0.5 * r(B, 1) + 0.2, torch.ones(B, 1, device="cuda"),
+              (torch.rand(B, 1, device="cuda", generator=g) > 0.1).float(), -1.6 + 0.1 * r(B, 1), r(B, 1), None)
+    return a, pol, tr, sample
+
+
+def _oracle_critic(a, pol, tr, sample):
+    from oracle import policy as op
+    from oracle.buffer import OracleValueNorm
+    sd = {k: v.detach().cpu().clone().requires_grad_("fc_h" not in k) for k, v in pol.critic.state_dict().items()}
+    share, vp, ret, am = (sample[i].cpu().numpy() for i in (0, 5, 6, 8))
+    B = share.shape[0]
+    z = np.zeros((B, 1, 64), np.float32)
+    values, _ = op.critic_values(sd, share, z, np.ones((B, 1), np.float32), a.use_ReLU, a.use_feature_normalization, False)
+    vn = None
+    if tr.value_normalizer is not None:
+        vn = OracleValueNorm(); vn.load(tr.value_normalizer.stats.cpu().numpy())
+    vl = op.value_loss(values, vp, ret, am, a.clip_param, vn, a.use_huber_loss, a.huber_delta, a.use_clipped_value_loss,
+                       a.use_value_active_masks)
+    keys = [k for k in sd if "fc_h" not in k]
+    grads = torch.autograd.grad(vl * a.value_loss_coef, [sd[k] for k in keys])
+    return values.detach().numpy(), vl.item(), dict(zip(keys, grads))
+
+
+@pytest.mark.parametrize("S,B,flags", [(460, 1000, ""), (460, 333, "--use_ReLU --use_valuenorm"), (600, 700, ""),
+                                       (100, 129, "--use_feature_normalization")])
+def test_wide_critic_values_loss_and_gradients(S, B, flags):
+    a, pol, tr, sample = _setup(S, B, flags)
+    want_v, want_vl, want_g = _oracle_critic(a, pol, tr, sample)
+    got_v, _ = pol.critic(sample[0], None, None)
+    np.testing.assert_allclose(got_v.cpu().numpy(), want_v, rtol=1e-4, atol=2e-5)
+    vl, cgn, pl, ent, agn, ratio = tr.ppo_update(sample)
+    np.testing.assert_allclose(vl.item(), want_vl, rtol=1e-4, atol=1e-6)
+    ws = next(iter(tr._ws.values()))
+    Pa = pol.actor.flat.numel()
+    for k, gv in pol.critic.unflatten(ws["grad"][Pa:]).items():
+        w = want_g[k].numpy()
+        np.testing.assert_allclose(gv.cpu().numpy(), w, rtol=1e-4, atol=1e-4 * np.abs(w).max() + 1e-9, err_msg=k)
+
+
+def test_wide_critic_strided_rows_and_row_gather():
+    """Rows addressed through an index (minibatch gather, several samples per share_obs row) and rows that are column
+    slices of a wider storage (unaligned: scalar loads) give the same sums as the plain layout."""
+    from mappo_b200 import ops
+    a, pol, tr, sample = _setup(460, 900, "")
+    cfg, flat = pol.critic.cfg, pol.critic.flat
+    share, vp, ret, am = sample[0], sample[5].reshape(-1), sample[6].reshape(-1), sample[8].reshape(-1)
+    loss = tr._loss_config()
+    vn = tr.value_normalizer.stats
+    P = flat.numel()
+
+    def run(x, rows, **kw):
+        nb = ops.update_num_blocks(cfg, rows)
+        gp = torch.empty(nb, P, device="cuda"); lp = torch.empty(nb, 4, dtype=torch.float64, device="cuda")
+        ops.critic_update(cfg, loss, flat, x, kw.pop("vp", vp), kw.pop("ret", ret), kw.pop("am", am), vn, gp, lp, **kw)
+        gs = torch.empty(P, device="cuda"); ls = torch.empty(4, dtype=torch.float64, device="cuda")
+        ops.grad_reduce(gp, lp, nb, gs, ls)
+        return gs.double(), ls
+    g0, l0 = run(share, 900)
+    scale = g0.abs().max().item()
+    wide = torch.zeros(900, 460 + 7, device="cuda")
+    wide[:, 3:463] = share
+    g1, l1 = run(wide[:, 3:463], 900)
+    assert (g0 - g1).abs().max().item() < 2e-5 * scale
+    np.testing.assert_allclose(l1.cpu().numpy(), l0.cpu().numpy(), rtol=1e-9)
+    # 3 samples per share row, visited through a permutation
+    rep = lambda t: t.repeat_interleave(3)
+    perm = torch.randperm(2700, device="cuda")
+    g2, l2 = run(share, 2700, vp=rep(vp), ret=rep(ret), am=rep(am), index=perm, share_rows_div=3)
+    assert (3 * g0 - g2).abs().max().item() < 6e-5 * scale
+    np.testing.assert_allclose(l2.cpu().numpy(), 3 * l0.cpu().numpy(), rtol=1e-9)
+    # group = 3: the same thing without an index
+    g3, l3 = run(share, 900, vp=rep(vp), ret=rep(ret), am=rep(am), group=3)
+    assert (3 * g0 - g3).abs().max().item() < 6e-5 * scale
