@@ -267,6 +267,45 @@ int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss_config* lo
                         const float* vn_stats, float* grad_partials, double* loss_partials, void* workspace,
                         void* stream);
 
+/* ---- recurrent (GRU) networks: cfg->recurrent = 1 ---------------------------------------------------------
+ *    Replaces RNNLayer.forward (rollout branch and the chunked training branch)   onpolicy/algorithms/utils/rnn.py:24-77
+ *             inside R_Actor / R_Critic                                            r_actor_critic.py:43-107,146-165
+ *             and the recurrent ppo_update (evaluate_actions on chunks)            r_mappo.py:91-164
+ * rnn_states: float32 [rows][H] (recurrent_N = 1); masks: float32 [rows]; the hidden state is multiplied by the mask
+ * before the step (rnn.py:26,60).  `workspace`: mappo_rnn_workspace_bytes(cfg, positions, update) bytes, 16-byte
+ * aligned; positions = rows (forward) or n_chunks * chunk_len (update). */
+long long mappo_rnn_workspace_bytes(const mappo_net_config* cfg, long long positions, int update);
+
+int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
+                            long long rows, const float* rnn_states_in, const float* masks,
+                            const float* available_actions, int deterministic, uint64_t seed, uint64_t step,
+                            long long row_offset, const float* given_actions, float* rnn_states_out,
+                            float* actions_out, float* logp_out, float* entropy_out, void* workspace, void* stream);
+
+/* share_obs row of sample i is share_obs[i / share_rows_div] (several agents' samples may share one row). */
+int mappo_critic_forward_rnn(const mappo_net_config* cfg, const float* params, const float* share_obs, int obs_ld,
+                             long long rows, int share_rows_div, const float* rnn_states_in, const float* masks,
+                             float* rnn_states_out, float* values_out, void* workspace, void* stream);
+
+/* One recurrent PPO minibatch: n_chunks sequences of chunk_len steps (recurrent_generator, shared_buffer.py:385-494;
+ * naive_recurrent_generator :288-383 with chunk_len = episode_length).  index int64 [chunk_len][n_chunks]: the
+ * flat sample row of step s of chunk c; obs / actions / old_logp / adv / masks / active_masks / rnn_states are the
+ * flat per-sample arrays of the buffer and are read at those rows; the initial hidden state of chunk c is
+ * rnn_states[index[0][c]].  Back-propagation through time covers the whole chunk.  grad_partials
+ * float32 [n_partials][P] with n_partials = mappo_update_num_blocks(cfg, n_chunks * chunk_len) (zeroed here). */
+int mappo_actor_update_rnn(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                           const float* obs, int obs_ld, long long n_chunks, int chunk_len, const int64_t* index,
+                           const float* rnn_states, const float* masks, const float* actions, const float* old_logp,
+                           const float* adv, const float* active_masks, const float* available_actions,
+                           float* grad_partials, int n_partials, double* loss_partials, void* workspace, void* stream);
+
+int mappo_critic_update_rnn(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                            const float* share_obs, int obs_ld, long long n_chunks, int chunk_len,
+                            const int64_t* index, int share_rows_div, const float* rnn_states, const float* masks,
+                            const float* value_preds, const float* returns, const float* active_masks,
+                            const float* vn_stats, float* grad_partials, int n_partials, double* loss_partials,
+                            void* workspace, void* stream);
+
 /* Sum the per-block partials in a fixed order: grad_sum float32 [P], loss_sum double [4].  In a multi-GPU job
  * the caller all-reduces both (sum) before mappo_adam_step. */
 int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,

@@ -166,30 +166,41 @@ class R_Actor(_FlatNet):
         actions = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
         logp = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
         rnn_states = check(rnn_states, self.device_)
+        if self._recurrent:
+            rnn_in = rnn_states.to(torch.float32).contiguous()
+            rnn_out = torch.empty_like(rnn_in)
+            self.forward_into(obs, actions, logp, available_actions=check(available_actions, self.device_),
+                              deterministic=deterministic, rnn_in=rnn_in,
+                              masks=check(masks, self.device_).to(torch.float32).contiguous(), rnn_out=rnn_out)
+            return actions.long(), logp, rnn_out
         self.forward_into(obs, actions, logp, available_actions=check(available_actions, self.device_),
                           deterministic=deterministic)
         return actions.long(), logp, rnn_states
 
     def forward_into(self, obs, actions_out, logp_out, available_actions=None, deterministic=False, step=None,
-                     row_offset=0):
-        """Hot-path entry: writes float32 action ids and log-probs straight into buffer slots."""
-        if self._recurrent:
-            raise NotImplementedError("recurrent (GRU) actor is not built yet")
+                     row_offset=0, rnn_in=None, masks=None, rnn_out=None):
+        """Hot-path entry: writes float32 action ids and log-probs (and, recurrent, the next rnn state) straight into
+        buffer slots."""
         if step is None:
             step = self._calls
         self._calls += 1
         if not self.discrete:
             available_actions = None
+        if self._recurrent:
+            ops.actor_forward_rnn(self.cfg, self.flat, obs, rnn_in, masks, rnn_out, actions_out, logp_out,
+                                  available_actions=None if available_actions is None else available_actions.contiguous(),
+                                  deterministic=deterministic, seed=self.sample_seed, step=step, row_offset=row_offset)
+            return
         ops.actor_forward(self.cfg, self.flat, obs, actions_out, logp_out,
                           available_actions=None if available_actions is None else available_actions.contiguous(),
                           deterministic=deterministic, seed=self.sample_seed, step=step, row_offset=row_offset)
 
     def evaluate_actions(self, obs, rnn_states, action, masks, available_actions=None, active_masks=None):
         """-> (action_log_probs [B, heads], dist_entropy scalar)   r_actor_critic.py:72-107, act.py:107-162"""
-        if self._recurrent:
-            raise NotImplementedError("recurrent (GRU) actor is not built yet")
         obs = check(obs, self.device_)
         B, nh = obs.shape[0], len(self.head_dims)
+        if self._recurrent:
+            return self._evaluate_actions_rnn(obs, rnn_states, action, masks, available_actions, active_masks)
         action = check(action, self.device_).reshape(B, nh).contiguous()
         logp = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
         ent = torch.empty(B, dtype=torch.float32, device=self.device_)
@@ -204,6 +215,31 @@ class R_Actor(_FlatNet):
         return logp, dist_entropy
 
 
+    def _evaluate_actions_rnn(self, obs, rnn_states, action, masks, available_actions, active_masks):
+        """rnn.py:30-77 (training branch): obs [L*N, D] step-major, rnn_states [N, 1, H] -- L sequential single-step
+        evaluations with the hidden state carried on the device."""
+        B, nh = obs.shape[0], len(self.head_dims)
+        h = check(rnn_states, self.device_).to(torch.float32).reshape(-1, self.hidden_size).contiguous()
+        N = h.shape[0]
+        Lc = B // N
+        action = check(action, self.device_).reshape(B, nh).to(torch.float32).contiguous()
+        masks = check(masks, self.device_).to(torch.float32).reshape(B).contiguous()
+        logp = torch.empty(B, nh, dtype=torch.float32, device=self.device_)
+        ent = torch.empty(B, dtype=torch.float32, device=self.device_)
+        avail = check(available_actions, self.device_) if self.discrete else None
+        for s in range(Lc):
+            sl = slice(s * N, (s + 1) * N)
+            h_next = torch.empty_like(h)
+            ops.actor_forward_rnn(self.cfg, self.flat, obs[sl], h, masks[sl], h_next, None, logp[sl],
+                                  available_actions=None if avail is None else avail[sl].contiguous(),
+                                  given_actions=action[sl], entropy_out=ent[sl])
+            h = h_next
+        if active_masks is not None and self._use_policy_active_masks:
+            am = check(active_masks, self.device_).reshape(B)
+            return logp, (ent * am).sum() / am.sum()
+        return logp, ent.mean()
+
+
 class R_Critic(_FlatNet):
     def __init__(self, args, cent_obs_space, device=torch.device("cuda")):
         super().__init__()
@@ -216,10 +252,19 @@ class R_Critic(_FlatNet):
         """-> (values [B, 1], rnn_states)   r_actor_critic.py:146-165"""
         cent_obs = check(cent_obs, self.device_)
         values = torch.empty(cent_obs.shape[0], 1, dtype=torch.float32, device=self.device_)
+        if self._recurrent:
+            rnn_in = check(rnn_states, self.device_).to(torch.float32).contiguous()
+            rnn_out = torch.empty_like(rnn_in)
+            self.forward_into(cent_obs, values, rnn_in=rnn_in,
+                              masks=check(masks, self.device_).to(torch.float32).contiguous(), rnn_out=rnn_out)
+            return values, rnn_out
         self.forward_into(cent_obs, values)
         return values, check(rnn_states, self.device_)
 
-    def forward_into(self, cent_obs, values_out, group=1):
+    def forward_into(self, cent_obs, values_out, group=1, rnn_in=None, masks=None, rnn_out=None, share_rows_div=1):
+        """Recurrent: one value per (env, agent) sample; sample i reads share-obs row i // share_rows_div."""
         if self._recurrent:
-            raise NotImplementedError("recurrent (GRU) critic is not built yet")
+            ops.critic_forward_rnn(self.cfg, self.flat, cent_obs, rnn_in, masks, rnn_out, values_out,
+                                   share_rows_div=share_rows_div)
+            return
         ops.critic_forward(self.cfg, self.flat, cent_obs, values_out, group=group)

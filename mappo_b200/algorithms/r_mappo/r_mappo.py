@@ -118,6 +118,44 @@ class R_MAPPO:
         self._info_total += self._info
         return ws
 
+    def _update_rnn(self, v, idx, n_chunks, L, update_actor=True):
+        """One recurrent minibatch: idx int64 [L * n_chunks] (step-major) flat sample rows of the chunks
+        (shared_buffer.py:385-494 / :288-383); back-propagation through time inside the kernels (csrc/mlp_gru.cu)."""
+        pol = self.policy
+        rows = n_chunks * L
+        ws = self._workspace(rows, rows)
+        Pa = pol.actor.flat.numel()
+        loss = self._loss_config()
+        gsa, gsc = ws["gsum"][:Pa], ws["gsum"][Pa:]
+        lsa, lsc = ws["lsum"][:4], ws["lsum"][4:]
+        ops.actor_update_rnn(pol.actor.cfg, loss, pol.actor.flat, v["obs"], n_chunks, L, idx, v["rnn"], v["masks"],
+                             v["actions"], v["logp"], v["adv"], v["active"], v["avail"], ws["gpa"], ws["lpa"])
+        ops.grad_reduce(ws["gpa"], ws["lpa"], ws["nba"], gsa, lsa)
+        if self.value_normalizer is not None:
+            self.value_normalizer.update(v["returns"].index_select(0, idx))
+        ops.critic_update_rnn(pol.critic.cfg, loss, pol.critic.flat, v["share"], n_chunks, L, idx, v["rnn_critic"],
+                              v["masks"], v["value_preds"], v["returns"], v["active"],
+                              None if self.value_normalizer is None else self.value_normalizer.stats,
+                              ws["gpc"], ws["lpc"], share_rows_div=v["M"] if v["share_is_unique"] else 1)
+        ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
+        rows_global = rows
+        if self.all_reduce is not None:
+            self.all_reduce(ws["gsum"]); self.all_reduce(ws["lsum"])
+            rows_global = rows * self.world_size
+        self._info.zero_()
+        aopt, copt = pol.actor_optimizer, pol.critic_optimizer
+        ops.adam_step(pol.actor.cfg, aopt.config(self.max_grad_norm, self._use_max_grad_norm), pol.actor.flat,
+                      aopt.exp_avg, aopt.exp_avg_sq, gsa, lsa, 3, rows_global, ws["grad"][:Pa], self._info[:4],
+                      apply_update=update_actor)
+        if update_actor:
+            aopt.step_count += 1
+        ops.adam_step(pol.critic.cfg, copt.config(self.max_grad_norm, self._use_max_grad_norm), pol.critic.flat,
+                      copt.exp_avg, copt.exp_avg_sq, gsc, lsc, 1, rows_global, ws["grad"][Pa:], self._info[4:],
+                      apply_update=True)
+        copt.step_count += 1
+        self._info_total += self._info
+        return ws
+
     world_size = 1
 
     # ------------------------------------------------------------------ reference API
@@ -150,7 +188,7 @@ class R_MAPPO:
         tensors; `imp_weights` is the MEAN importance weight (the reference returns the per-sample tensor and
         only ever takes its mean, r_mappo.py:212)."""
         if self._use_recurrent_policy or self._use_naive_recurrent:
-            raise NotImplementedError("recurrent ppo_update is not built yet")
+            return self._ppo_update_rnn(sample, update_actor)
         (share_obs, obs, _rs, _rsc, actions, value_preds, returns, masks, active, old_logp, adv, avail) = sample
         dev = self.device
         c = lambda x: None if x is None else check(x, dev).contiguous()
@@ -162,10 +200,32 @@ class R_MAPPO:
         i = self._info.clone()
         return i[4], i[5], i[0], i[2], i[1], i[3]
 
+    def _ppo_update_rnn(self, sample, update_actor=True):
+        """Recurrent sample of the generators: arrays [L*N, ...] step-major, rnn states [N, 1, H]."""
+        (share_obs, obs, rs, rsc, actions, value_preds, returns, masks, active, old_logp, adv, avail) = sample
+        dev = self.device
+        c = lambda x: None if x is None else check(x, dev).to(torch.float32).contiguous()
+        obs, share_obs = c(obs), c(share_obs)
+        B = obs.shape[0]
+        N = c(rs).reshape(-1, 64).shape[0]
+        L = B // N
+        H = 64
+        # rnn states exist per chunk only: place them at the rows of step 0 (the only rows the kernels read them at)
+        def spread(x):
+            full = torch.zeros(B, H, dtype=torch.float32, device=dev)
+            full[:N] = c(x).reshape(N, H)
+            return full
+        v = dict(obs=obs, share=share_obs, M=1, share_is_unique=False, rnn=spread(rs), rnn_critic=spread(rsc),
+                 masks=c(masks).reshape(-1), actions=c(actions), logp=c(old_logp), adv=c(adv).reshape(-1),
+                 active=c(active).reshape(-1), avail=c(avail) if self.policy.actor.discrete else None,
+                 value_preds=c(value_preds).reshape(-1), returns=c(returns).reshape(-1))
+        idx = torch.arange(B, device=dev, dtype=torch.int64)
+        self._update_rnn(v, idx, N, L, update_actor=update_actor)
+        i = self._info.clone()
+        return i[4], i[5], i[0], i[2], i[1], i[3]
+
     def train(self, buffer, update_actor=True):
         """r_mappo.py:166-219 on the device-resident buffer."""
-        if self._use_recurrent_policy or self._use_naive_recurrent:
-            raise NotImplementedError("recurrent training is not built yet")
         vn = None if self.value_normalizer is None else self.value_normalizer.stats
         T = buffer.episode_length
         raw, s3 = ops.advantages(buffer.returns[:-1], buffer.value_preds[:-1], buffer.active_masks[:-1], vn,
@@ -179,8 +239,17 @@ class R_MAPPO:
         adv = advantages.view(B)
         rep = M if v["share_is_unique"] else 1          # samples served by one share_obs row
         n_updates = 0
+        v["adv"] = adv
         for _ in range(self.ppo_epoch):
-            if self.num_mini_batch == 1 and not buffer.force_permutation:
+            if self._use_recurrent_policy or self._use_naive_recurrent:
+                if self._use_recurrent_policy:
+                    batches = buffer.recurrent_rows(self.num_mini_batch, self.data_chunk_length)
+                else:
+                    batches = buffer.naive_recurrent_rows(self.num_mini_batch)
+                for rows_idx, n_chunks, L in batches:
+                    self._update_rnn(v, rows_idx, n_chunks, L, update_actor=update_actor)
+                    n_updates += 1
+            elif self.num_mini_batch == 1 and not buffer.force_permutation:
                 # the loss is a mean over the whole batch: the permutation only reorders the sum
                 self._update(obs_flat, sh, rep, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor)
                 n_updates += 1

@@ -1,0 +1,674 @@
+// Recurrent (GRU) networks: RNNLayer (onpolicy/algorithms/utils/rnn.py:7-77) between the MLP base and the head of
+// R_Actor / R_Critic (r_actor_critic.py:43-107,146-165), as a chain of streaming kernels around the fused 64-wide
+// kernel of mlp_tc.cu.  Positions p = s * nc + c: step s of chunk (sequence) c; rollout = one step, nc = rows.
+//
+//   mlp_tc_kernel<MODE 4>   n2[p]   = base(obs[src(p)])                      (features, all positions at once)
+//   gru_fwd_kernel          h[p]    = GRU(n2[p], h[p - nc] * mask[p])          (sequential over s inside the CTA; tensor
+//                                                                             cores for n2.Wih' and hm.Whh; stores the
+//                                                                             gates and the masked previous hidden)
+//   gru_head_kernel         y = LN(h[p]) -> head -> sample | value | loss;    dh[p] = dLoss/dh[p] through head and LN
+//   gru_bwd_kernel          s = L-1 .. 0: gate derivatives, dn2[p] = dgi.Wih', carry = (dgh.Whh + z dh) * mask[p]
+//   wgrad1_wide_kernel      dW_ih = dgi^T n2, dW_hh = dgh^T hm, bias sums     (mlp_wide.cu, generic form)
+//   mlp_tc_kernel<MODE 5>   base backward from dn2[p]
+//
+// GRU (torch.nn.GRU, gate order r, z, n):  r = s(Wir x + bir + Whr h + bhr), z likewise,
+// n = tanh(Win x + bin + r (Whn h + bhn)),  h' = (1 - z) n + z h;  x = LN-affine(n2) is folded into Wih' / bih'
+// (net.cuh), the LayerNorm after the GRU into the head.  The reference's training branch (rnn.py:30-77) runs cuDNN
+// over the mask-free segments of a chunk and multiplies the hidden state by the mask at segment starts: identical to
+// multiplying by mask[p] at every step.
+#include "mlp_tc_common.cuh"
+
+namespace mappo {
+namespace tc {
+
+struct GruArgs {
+  NetLayout L;
+  const float* params;
+  long long nc; int len;
+  const int64_t* index;          // [len * nc] sample rows (step-major) or NULL (src = p)
+  const float* n2;               // [len * nc][64]
+  const float* h0;               // rnn states at sample rows [*][64]; step 0 reads row src(0, c)
+  const float* masks;            // [*] at sample rows
+  float* hs;                     // [len * nc][64]  hidden after each step (rollout: the next rnn-state slot)
+  float* hm;                     // [len * nc][64]  masked previous hidden, or NULL
+  float* gates;                  // [len * nc][256] r | z | n | (Whn h + bhn) -> backward: dgi_n | P_r | P_z | dgh_n
+  float* dh;                     // backward: [len * nc][64] dLoss/dh direct (in), dLoss/dn2 (out, in place)
+};
+
+constexpr uint32_t kGChunk = 192 * 16;                   // bytes of one 8-column chunk of a 192-row weight tile
+constexpr uint32_t kGPiece = 8 * kGChunk;                // one fp16 piece of a [192][64] weight
+constexpr uint32_t kTile = 2 * 8 * kRowChunk;            // a [128][64] operand tile, both pieces
+
+struct GruMap { uint32_t Wih, Whh, T0, T1, T2, bias, bars, total; };
+__host__ __device__ inline GruMap make_gru_map(bool bwd) {
+  GruMap m;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.Wih = take(2 * kGPiece);
+  m.Whh = take(2 * kGPiece);
+  m.T0 = take(kTile);
+  m.T1 = take(kTile);
+  m.T2 = take(bwd ? kTile : 0);
+  m.bias = take(4 * 64 * 4);
+  m.bars = take(64);
+  m.total = o;
+  return m;
+}
+
+__device__ __forceinline__ float sigmoid_f(float x) { return __frcp_rn(1.0f + __expf(-x)); }
+
+__device__ __forceinline__ void stage_gru_weights(unsigned char* sm, const GruMap& m, const GruArgs& a) {
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  for (int e = threadIdx.x; e < 192 * 64; e += kThreads) {
+    const int j = e >> 6, k = e & 63;
+    put_pair(sm + m.Wih, kGPiece, 192, j, k, P[L.wih + e] * P[L.g2 + k]);
+    put_pair(sm + m.Whh, kGPiece, 192, j, k, P[L.whh + e]);
+  }
+  float* b = reinterpret_cast<float*>(sm + m.bias);       // [0,128): r, z (input + hidden bias); [128,192): b_in; [192,256): b_hn
+  if (threadIdx.x < 192) {
+    const int j = threadIdx.x;
+    float s = P[L.bih + j];
+    for (int k = 0; k < 64; ++k) s = fmaf(P[L.wih + j * 64 + k], P[L.be2 + k], s);
+    if (j < 128) b[j] = s + P[L.bhh + j];
+    else { b[j] = s; b[j + 64] = P[L.bhh + j]; }
+  }
+}
+
+__device__ __forceinline__ void load16(const float* __restrict__ p, float (&v)[16]) {
+  const float4* q = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float4 t = __ldg(q + i); v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w; }
+}
+__device__ __forceinline__ void store16(float* __restrict__ p, const float (&v)[16]) {
+  float4* q = reinterpret_cast<float4*>(p);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) q[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+// acc0 + 2^-12 acc1 of this thread's 16 columns
+__device__ __forceinline__ void tmem_pair16(uint32_t a0, uint32_t a1, float (&v)[16]) {
+  float w[16];
+  umma::tmem_ld16(a0, v);
+  umma::tmem_ld16(a1, w);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
+}
+
+// ---- forward sweep ---------------------------------------------------------------------------------------
+// TMEM: D1 = n2.Wih'^T (+ hm.Whh^T on the r, z columns): acc0 at column 0, acc1 at 192 (192 columns each);
+//       D2 = hm.Whn^T: acc0 at 384, acc1 at 448.
+__global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const GruMap m = make_gru_map(false);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 512);
+  stage_gru_weights(sm, m, a);
+  umma::fence_async_smem();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const uint32_t la = tb + ((uint32_t)(32 * q4) << 16) + 16 * cq;
+  const uint32_t sIh = umma::smem_u32(sm + m.Wih), sHh = umma::smem_u32(sm + m.Whh);
+  const uint32_t sN2 = umma::smem_u32(sm + m.T0), sHm = umma::smem_u32(sm + m.T1);
+  const float* bias = reinterpret_cast<const float*>(sm + m.bias) + 16 * cq;
+  constexpr uint32_t id192 = umma::idesc_f16(128, 192, 0, 0), id128 = umma::idesc_f16(128, 128, 0, 0),
+                     id64 = umma::idesc_f16(128, 64, 0, 0);
+  uint32_t ph = 0;
+  const long long ntiles = (a.nc + kBM - 1) / kBM;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long c = tile * kBM + r;
+    const bool valid = c < a.nc;
+    float h[16], x[16], mask;
+    {
+      const long long src = valid ? (a.index ? a.index[c] : c) : 0;
+      if (valid) { load16(a.h0 + src * 64 + 16 * cq, h); load16(a.n2 + c * 64 + 16 * cq, x); mask = __ldg(a.masks + src); }
+      else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) h[i] = x[i] = 0.0f;
+        mask = 0.0f;
+      }
+    }
+    for (int s = 0; s < a.len; ++s) {
+      const long long p = (long long)s * a.nc + c;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) h[i] *= mask;                          // hm = h_prev * mask[p]
+      store_cols16(sm + m.T0, r, cq, x);
+      store_cols16(sm + m.T1, r, cq, h);
+      if (valid && a.hm) store16(a.hm + p * 64 + 16 * cq, h);
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        umma::tc_fence_after();
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint32_t ao = (uint32_t)ks * 2 * kRowChunk, bo = (uint32_t)ks * 2 * kGChunk;
+          const uint64_t xh = umma::smem_desc(sN2 + ao, kRowChunk, 128), xl = umma::smem_desc(sN2 + 8 * kRowChunk + ao, kRowChunk, 128);
+          const uint64_t hh = umma::smem_desc(sHm + ao, kRowChunk, 128), hl = umma::smem_desc(sHm + 8 * kRowChunk + ao, kRowChunk, 128);
+          const uint64_t ih = umma::smem_desc(sIh + bo, kGChunk, 128), il = umma::smem_desc(sIh + kGPiece + bo, kGChunk, 128);
+          const uint64_t wh = umma::smem_desc(sHh + bo, kGChunk, 128), wl = umma::smem_desc(sHh + kGPiece + bo, kGChunk, 128);
+          const uint64_t nh = umma::smem_desc(sHh + bo + 128 * 16, kGChunk, 128), nl = umma::smem_desc(sHh + kGPiece + bo + 128 * 16, kGChunk, 128);
+          umma::mma_f16(tb, xh, ih, id192, ks > 0);
+          umma::mma_f16(tb + 192, xh, il, id192, ks > 0);
+          umma::mma_f16(tb + 192, xl, ih, id192, true);
+          umma::mma_f16(tb, hh, wh, id128, true);
+          umma::mma_f16(tb + 192, hh, wl, id128, true);
+          umma::mma_f16(tb + 192, hl, wh, id128, true);
+          umma::mma_f16(tb + 384, hh, nh, id64, ks > 0);
+          umma::mma_f16(tb + 448, hh, nl, id64, ks > 0);
+          umma::mma_f16(tb + 448, hl, nh, id64, true);
+        }
+        umma::mma_commit(bar);
+      }
+      // next step's inputs travel while the tensor cores work
+      float xn[16], mask_n = 0.0f;
+      if (s + 1 < a.len && valid) {
+        const long long pn = p + a.nc;
+        load16(a.n2 + pn * 64 + 16 * cq, xn);
+        mask_n = __ldg(a.masks + (a.index ? a.index[pn] : pn));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) xn[i] = 0.0f;
+      }
+      umma::mbar_wait(bar, ph); ph ^= 1;
+      umma::tc_fence_after();
+      float g[16], t[16];
+      float* gp = (valid && a.gates) ? a.gates + p * 256 + 16 * cq : nullptr;
+      tmem_pair16(la, la + 192, g);                                      // r
+#pragma unroll
+      for (int i = 0; i < 16; ++i) g[i] = sigmoid_f(g[i] + bias[i]);
+      if (gp) store16(gp, g);
+      tmem_pair16(la + 384, la + 448, t);                                // Whn h + bhn
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t[i] += bias[192 + i];
+      if (gp) store16(gp + 192, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t[i] *= g[i];
+      tmem_pair16(la + 128, la + 192 + 128, g);                          // n
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t[i] = tanh_fast(g[i] + bias[128 + i] + t[i]);
+      if (gp) store16(gp + 128, t);
+      tmem_pair16(la + 64, la + 192 + 64, g);                            // z
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        g[i] = sigmoid_f(g[i] + bias[64 + i]);
+        h[i] = fmaf(g[i], h[i] - t[i], t[i]);                            // (1 - z) n + z hm
+      }
+      if (gp) store16(gp + 64, g);
+      if (valid) store16(a.hs + p * 64 + 16 * cq, h);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) x[i] = xn[i];
+      mask = mask_n;
+      umma::tc_fence_before();                                           // TMEM reads done before the next step's MMAs
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 512);
+}
+
+// ---- backward sweep ----------------------------------------------------------------------------------------
+// Per step (descending): dt = dh[p] + carry;  dz~ = dt (hm - n) z (1 - z);  dn~ = dt (1 - z)(1 - n^2);
+// dr~ = dn~ ghn r (1 - r);  dgi = (dr~, dz~, dn~), dgh = (dr~, dz~, dn~ r);  dn2 = dgi . Wih',
+// carry = (dgh . Whh + dt z) * mask[p].  The gate slots of `gates` are overwritten with dgi_n | dr~ | dz~ | dgh_n.
+// TMEM: dn2 acc0 / acc1 at columns 0 / 64, dhm at 128 / 192.
+__global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const GruMap m = make_gru_map(true);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 256);
+  stage_gru_weights(sm, m, a);
+  umma::fence_async_smem();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const uint32_t la = tb + ((uint32_t)(32 * q4) << 16) + 16 * cq;
+  const uint32_t sIh = umma::smem_u32(sm + m.Wih), sHh = umma::smem_u32(sm + m.Whh);
+  const uint32_t sT0 = umma::smem_u32(sm + m.T0), sT1 = umma::smem_u32(sm + m.T1), sT2 = umma::smem_u32(sm + m.T2);
+  constexpr uint32_t idD = umma::idesc_f16(128, 64, 0, 1);
+  // acc += A (K-major [128][64] tile) . W[gate rows][:]   (W read MN-major: contraction over its 64 rows)
+  auto dgrad = [&](uint32_t acc0, uint32_t acc1, uint32_t a_tile, uint32_t w_base, int gate, bool accum) {
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      const uint32_t ao = a_tile + (uint32_t)ks * 2 * kRowChunk, bo = w_base + (uint32_t)gate * 1024 + (uint32_t)ks * 256;
+      const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
+      const uint64_t bh = umma::smem_desc(bo, 128, kGChunk), bl = umma::smem_desc(bo + kGPiece, 128, kGChunk);
+      umma::mma_f16(acc0, ah, bh, idD, accum || ks > 0);
+      umma::mma_f16(acc1, ah, bl, idD, accum || ks > 0);
+      umma::mma_f16(acc1, al, bh, idD, true);
+    }
+  };
+  uint32_t ph = 0;
+  const long long ntiles = (a.nc + kBM - 1) / kBM;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long c = tile * kBM + r;
+    const bool valid = c < a.nc;
+    float carry[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) carry[i] = 0.0f;
+    for (int s = a.len - 1; s >= 0; --s) {
+      const long long p = (long long)s * a.nc + c;
+      float dt[16], u[16], v[16], w[16], dd[16];
+      float mask = 0.0f;
+      float* gp = a.gates + p * 256 + 16 * cq;
+      if (valid) {
+        load16(a.dh + p * 64 + 16 * cq, dt);
+        load16(gp + 64, u);                                             // z
+        load16(gp + 128, v);                                            // n
+        load16(a.hm + p * 64 + 16 * cq, w);                             // hm
+        mask = __ldg(a.masks + (a.index ? a.index[p] : p));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) dt[i] = u[i] = v[i] = w[i] = 0.0f;
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        dt[i] += carry[i];
+        dd[i] = dt[i] * u[i];                                           // dt z
+        w[i] = dt[i] * (w[i] - v[i]) * u[i] * (1.0f - u[i]);            // dz~
+        v[i] = dt[i] * (1.0f - u[i]) * fmaf(-v[i], v[i], 1.0f);         // dn~
+      }
+      store_cols16(sm + m.T1, r, cq, w);
+      store_cols16(sm + m.T2, r, cq, v);
+      if (valid) {
+        load16(gp, u);                                                  // r
+        load16(gp + 192, dt);                                           // ghn
+        store16(gp + 128, w);                                           // P_z
+        store16(gp, v);                                                 // dgi_n
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) u[i] = dt[i] = 0.0f;
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        w[i] = v[i] * dt[i] * u[i] * (1.0f - u[i]);                     // dr~
+        v[i] *= u[i];                                                   // dgh_n = dn~ r
+      }
+      store_cols16(sm + m.T0, r, cq, w);
+      if (valid) { store16(gp + 64, w); store16(gp + 192, v); }
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        umma::tc_fence_after();
+        dgrad(tb, tb + 64, sT0, sIh, 0, false);
+        dgrad(tb, tb + 64, sT1, sIh, 1, true);
+        dgrad(tb, tb + 64, sT2, sIh, 2, true);
+        dgrad(tb + 128, tb + 192, sT0, sHh, 0, false);
+        dgrad(tb + 128, tb + 192, sT1, sHh, 1, true);
+        umma::mma_commit(bar);
+      }
+      umma::mbar_wait(bar, ph); ph ^= 1;
+      store_cols16(sm + m.T0, r, cq, v);                                // dgh_n
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        umma::tc_fence_after();
+        dgrad(tb + 128, tb + 192, sT0, sHh, 2, true);
+        umma::mma_commit(bar);
+      }
+      umma::mbar_wait(bar, ph); ph ^= 1;
+      umma::tc_fence_after();
+      tmem_pair16(la, la + 64, u);                                      // dn2
+      if (valid) store16(a.dh + p * 64 + 16 * cq, u);
+      tmem_pair16(la + 128, la + 192, u);                               // dgh . Whh
+#pragma unroll
+      for (int i = 0; i < 16; ++i) carry[i] = (u[i] + dd[i]) * mask;
+      umma::tc_fence_before();
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 256);
+}
+
+}  // namespace tc
+}  // namespace mappo
+
+// ---- head on the hidden state (fp32 CUDA cores: the head is 64 x A, A <= 16) -------------------------------------
+#include "mlp_fma.cuh"
+
+namespace mappo {
+namespace tc {
+
+struct HeadSmem {
+  static constexpr int BM = 128;
+  static constexpr int Whf = 0;                          // [16][64] Wh[a][k] gr[k]
+  static constexpr int bhf = Whf + kMaxA * 64;           // [16]     bh + Wh ber
+  static constexpr int TY = bhf + kMaxA;                 // [BM][kLD] y = LN(h) without the affine
+  static constexpr int rstd = TY + BM * kLD;             // [BM]
+  static constexpr int dlog = rstd + BM;                 // [BM][kDL]
+  static constexpr int total = dlog + BM * kDL;
+  static constexpr size_t bytes = sizeof(float) * (size_t)total;
+};
+
+// MODE 0 actor rollout (sample / evaluate), 1 critic rollout, 2 actor update, 3 critic update.
+// Row g of this launch is position p = g; its sample row is index[g] (update) or g.  h: [rows][64] hidden states.
+template <int MODE>
+__global__ void __launch_bounds__(256, 1) gru_head_kernel(const MlpArgs a, const float* __restrict__ h, float* __restrict__ dh) {
+  constexpr bool UPDATE = (MODE >= 2);
+  constexpr int BM = HeadSmem::BM, NT = 256, NTY = NT / 16, RPT = BM / NTY, NQ = (kMaxA * 64 + NT - 1) / NT;
+  using S = HeadSmem;
+  extern __shared__ __align__(16) float smf[];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  const int A = L.a_total;
+  for (int e = tid; e < kMaxA * 64; e += NT) {
+    const int aidx = e >> 6, k = e & 63;
+    float v = 0.0f;
+    int hh = 0, off = 0;
+    while (hh < L.n_heads && aidx >= off + L.head_dim[hh]) { off += L.head_dim[hh]; ++hh; }
+    if (hh < L.n_heads) v = P[L.wh[hh] + (aidx - off) * 64 + k] * P[L.gr + k];
+    smf[S::Whf + e] = v;
+  }
+  if (tid < kMaxA) {
+    int hh = 0, off = 0;
+    while (hh < L.n_heads && tid >= off + L.head_dim[hh]) { off += L.head_dim[hh]; ++hh; }
+    float s = 0.0f;
+    if (hh < L.n_heads) {
+      s = P[L.bh[hh] + (tid - off)];
+      for (int k = 0; k < 64; ++k) s = fmaf(P[L.wh[hh] + (tid - off) * 64 + k], P[L.ber + k], s);
+    }
+    smf[S::bhf + tid] = s;
+  }
+  float gh[NQ], dbh[NQ];
+  double lacc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) gh[q] = dbh[q] = 0.0f;
+  const long long ntiles = (a.rows + BM - 1) / BM;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    __syncthreads();
+    for (int r = warp; r < BM; r += NT / 32) {                            // y = LN(h), one warp per row
+      const long long g = tile * BM + r;
+      float v0 = 0.0f, v1 = 0.0f;
+      if (g < a.rows) { v0 = h[g * 64 + lane]; v1 = h[g * 64 + lane + 32]; }
+      float s = v0 + v1;
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      const float mean = s * (1.0f / 64.0f);
+      v0 -= mean; v1 -= mean;
+      float q = v0 * v0 + v1 * v1;
+      for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      const float rstd = 1.0f / sqrtf(q * (1.0f / 64.0f) + kLnEps);
+      smf[S::TY + r * kLD + lane] = v0 * rstd;
+      smf[S::TY + r * kLD + lane + 32] = v1 * rstd;
+      if (lane == 0) smf[S::rstd + r] = rstd;
+    }
+    __syncthreads();
+    if (tid < BM) {
+      const long long g = tile * BM + tid;
+      float l[kMaxA];
+      float* dl = smf + S::dlog + tid * kDL;
+      if (g < a.rows) {
+        row_logits(smf + S::TY + tid * kLD, smf + S::Whf, smf + S::bhf, A, l);
+        const long long src = a.index ? a.index[g] : g;
+        if (MODE == 0) actor_rollout_row(a, g, l);
+        if (MODE == 1) a.values_out[g] = l[0];
+        if (MODE == 2) actor_loss_row(a, src, l, dl, lacc);
+        if (MODE == 3) {
+          dl[0] = critic_loss_row(a, src, l[0], lacc);
+          for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+        }
+      } else if (UPDATE) {
+        for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+      }
+    }
+    if (!UPDATE) continue;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {                                        // G_h[a][k] += sum_r dlog[r][a] y[r][k]
+      const int o = tid + NT * q;
+      if (o < A * 64) {
+        const int aa = o >> 6, k = o & 63;
+        float s = 0.0f, sb = 0.0f;
+        for (int r = 0; r < BM; ++r) {
+          const float d = smf[S::dlog + r * kDL + aa];
+          s = fmaf(d, smf[S::TY + r * kLD + k], s);
+          sb += d;
+        }
+        gh[q] += s;
+        if (k == 0) dbh[q] += sb;
+      }
+    }
+    float acc[RPT][4];                                                    // dy = dlog . Wh'
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    for (int aa = 0; aa < A; ++aa) {
+      const float4 w = *reinterpret_cast<const float4*>(smf + S::Whf + aa * 64 + 4 * tx);
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        const float d = smf[S::dlog + (ty + NTY * i) * kDL + aa];
+        acc[i][0] = fmaf(d, w.x, acc[i][0]); acc[i][1] = fmaf(d, w.y, acc[i][1]);
+        acc[i][2] = fmaf(d, w.z, acc[i][2]); acc[i][3] = fmaf(d, w.w, acc[i][3]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {                                       // through the LayerNorm: dh = rstd (dy - mean(dy) - y mean(dy y))
+      const int r = ty + NTY * i;
+      const long long g = tile * BM + r;
+      const float4 y = *reinterpret_cast<const float4*>(smf + S::TY + r * kLD + 4 * tx);
+      const float s1 = hw_sum((acc[i][0] + acc[i][1]) + (acc[i][2] + acc[i][3])) * (1.0f / 64.0f);
+      const float s2 = hw_sum((acc[i][0] * y.x + acc[i][1] * y.y) + (acc[i][2] * y.z + acc[i][3] * y.w)) * (1.0f / 64.0f);
+      const float rstd = smf[S::rstd + r];
+      if (g < a.rows)
+        *reinterpret_cast<float4*>(dh + g * 64 + 4 * tx) =
+            make_float4(rstd * (acc[i][0] - s1 - y.x * s2), rstd * (acc[i][1] - s1 - y.y * s2),
+                        rstd * (acc[i][2] - s1 - y.z * s2), rstd * (acc[i][3] - s1 - y.w * s2));
+    }
+  }
+  if (!UPDATE) return;
+  // head slots of partial row blockIdx.x (the buffer was zeroed by the caller), loss sums
+  float* __restrict__ gp = a.grad_partials + (size_t)blockIdx.x * L.total;
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const int o = tid + NT * q;
+    if (o < A * 64) {
+      const int aa = o >> 6, k = o & 63;
+      int hh = 0, off = 0;
+      while (aa >= off + L.head_dim[hh]) { off += L.head_dim[hh]; ++hh; }
+      gp[L.wh[hh] + (aa - off) * 64 + k] = gh[q];
+      if (k == 0) gp[L.bh[hh] + (aa - off)] = dbh[q];
+    }
+  }
+  __shared__ double red[4][8];
+  for (int q = 0; q < 4; ++q) {
+    double v = lacc[q];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) red[q][warp] = v;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double v = 0.0;
+    for (int w = 0; w < NT / 32; ++w) v += red[tid][w];
+    a.loss_partials[(size_t)blockIdx.x * 4 + tid] = v;
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+int grid_for(long long rows);                                                        // mlp_tc.cu
+template <int MODE> int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who);
+}  // namespace tc
+}  // namespace mappo
+
+#include "mlp_wide.cuh"
+
+namespace mappo {
+namespace tc {
+
+constexpr int kGruMaxSmem = 232448 - 1024;
+
+static int check_rnn(const mappo_net_config* cfg, const char* who) {
+  if (int rc = check_net(cfg, who)) return rc;
+  MAPPO_REQUIRE(cfg->recurrent, "%s: not a recurrent network", who);
+  if (cfg->in_dim > 64) MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d > 64 are not built", who, cfg->in_dim);
+  return 0;
+}
+
+static int set_attrs() {
+  static bool done = false;
+  if (done) return 0;
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGruMaxSmem));
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGruMaxSmem));
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_head_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HeadSmem::bytes));
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_head_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HeadSmem::bytes));
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_head_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HeadSmem::bytes));
+  MAPPO_CUDA(cudaFuncSetAttribute(gru_head_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HeadSmem::bytes));
+  done = true;
+  return 0;
+}
+
+static int head_grid(long long rows) {
+  const long long nt = (rows + HeadSmem::BM - 1) / HeadSmem::BM;
+  const int g = grid_for(rows);
+  return (int)(nt < g ? nt : g);
+}
+
+// floats of workspace per position: rollout keeps the base features only
+long long rnn_workspace_floats(long long positions, int update) { return positions * (update ? 512 : 64); }
+
+// One forward step for `rows` rows (rollout / evaluation): base -> GRU -> head.
+template <int MODE>
+int rnn_forward(MlpArgs& a, const mappo_net_config* cfg, const float* h_in, const float* masks, float* h_out,
+                cudaStream_t stream, const char* who) {
+  if (int rc = check_rnn(cfg, who)) return rc;
+  MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim && h_in && masks && h_out && a.workspace,
+                "%s: bad arguments", who);
+  if (int rc = set_attrs()) return rc;
+  float* n2 = static_cast<float*>(a.workspace);
+  a.feat = n2;
+  if (int rc = launch<4>(a, cfg, stream, who)) return rc;
+  GruArgs g{};
+  g.L = a.L; g.params = a.params; g.nc = a.rows; g.len = 1; g.index = nullptr; g.n2 = n2; g.h0 = h_in; g.masks = masks;
+  g.hs = h_out;
+  gru_fwd_kernel<<<grid_for(a.rows), kThreads, make_gru_map(false).total, stream>>>(g);
+  MAPPO_CHECK_LAUNCH(who);
+  gru_head_kernel<MODE><<<head_grid(a.rows), 256, HeadSmem::bytes, stream>>>(a, h_out, nullptr);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+// One PPO minibatch of n_chunks sequences of chunk_len steps: positions p = s * n_chunks + c, sample row index[p].
+template <int MODE>
+int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int chunk_len, const float* rnn_states,
+               const float* masks, int n_partials, cudaStream_t stream, const char* who) {
+  if (int rc = check_rnn(cfg, who)) return rc;
+  const long long B = n_chunks * chunk_len;
+  MAPPO_REQUIRE(a.params && a.x && n_chunks > 0 && chunk_len > 0 && a.ld >= cfg->in_dim && rnn_states && masks &&
+                a.index && a.workspace && a.grad_partials && a.loss_partials, "%s: bad arguments", who);
+  MAPPO_REQUIRE(n_partials >= 2 * grid_for(B), "%s: %d partial rows, need %d", who, n_partials, 2 * grid_for(B));
+  if (int rc = set_attrs()) return rc;
+  a.rows = B;
+  a.L = make_layout(*cfg);
+  const size_t P = (size_t)a.L.total;
+  MAPPO_CUDA(cudaMemsetAsync(a.grad_partials, 0, sizeof(float) * P * (size_t)n_partials, stream));
+  MAPPO_CUDA(cudaMemsetAsync(a.loss_partials, 0, sizeof(double) * 4 * (size_t)n_partials, stream));
+  float* ws = static_cast<float*>(a.workspace);
+  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256;
+  a.feat = n2;
+  if (int rc = launch<4>(a, cfg, stream, who)) return rc;
+  GruArgs g{};
+  g.L = a.L; g.params = a.params; g.nc = n_chunks; g.len = chunk_len; g.index = a.index; g.n2 = n2; g.h0 = rnn_states;
+  g.masks = masks; g.hs = hs; g.hm = hm; g.gates = gates; g.dh = dh;
+  gru_fwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(false).total, stream>>>(g);
+  MAPPO_CHECK_LAUNCH(who);
+  gru_head_kernel<MODE><<<head_grid(B), 256, HeadSmem::bytes, stream>>>(a, hs, dh);
+  MAPPO_CHECK_LAUNCH(who);
+  gru_bwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(true).total, stream>>>(g);
+  MAPPO_CHECK_LAUNCH(who);
+  WideArgs w{};
+  w.rows = B; w.index = nullptr; w.x_div = 1; w.vec = 1; w.ld = 256; w.D = 192; w.dz_ld = 64; w.norm = 0;
+  w.total = a.L.total; w.transposed = 1; w.grad_partials = a.grad_partials;
+  w.x = gates; w.dz1 = n2; w.rot = 128; w.out_w = a.L.wih; w.out_b = a.L.bih;
+  if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
+  w.x = gates + 64; w.dz1 = hm; w.rot = 0; w.out_w = a.L.whh; w.out_b = a.L.bhh;
+  if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
+  a.feat = dh;
+  return launch<5>(a, cfg, stream, who);
+}
+
+template int rnn_forward<0>(MlpArgs&, const mappo_net_config*, const float*, const float*, float*, cudaStream_t, const char*);
+template int rnn_forward<1>(MlpArgs&, const mappo_net_config*, const float*, const float*, float*, cudaStream_t, const char*);
+template int rnn_update<2>(MlpArgs&, const mappo_net_config*, long long, int, const float*, const float*, int, cudaStream_t, const char*);
+template int rnn_update<3>(MlpArgs&, const mappo_net_config*, long long, int, const float*, const float*, int, cudaStream_t, const char*);
+
+}  // namespace tc
+}  // namespace mappo
+
+using namespace mappo;
+
+extern "C" long long mappo_rnn_workspace_bytes(const mappo_net_config* cfg, long long positions, int update) {
+  if (!cfg || positions < 0) return -1;
+  return cfg->recurrent ? 4 * tc::rnn_workspace_floats(positions, update) : 0;
+}
+
+extern "C" int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
+                                       long long rows, const float* rnn_states_in, const float* masks,
+                                       const float* available_actions, int deterministic, uint64_t seed, uint64_t step,
+                                       long long row_offset, const float* given_actions, float* rnn_states_out,
+                                       float* actions_out, float* logp_out, float* entropy_out, void* workspace,
+                                       void* stream) {
+  MAPPO_REQUIRE(logp_out && (actions_out || given_actions), "actor_forward_rnn: null outputs");
+  MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_forward_rnn: critic config");
+  MlpArgs a{};
+  a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.avail = available_actions;
+  a.deterministic = deterministic; a.k0 = (uint32_t)(seed & 0xFFFFFFFFull); a.step = (uint32_t)step;
+  a.row_offset = row_offset; a.actions_out = actions_out; a.logp_out = logp_out;
+  a.given_actions = given_actions; a.entropy_out = entropy_out; a.workspace = workspace;
+  return tc::rnn_forward<0>(a, cfg, rnn_states_in, masks, rnn_states_out, (cudaStream_t)stream, "actor_forward_rnn");
+}
+
+extern "C" int mappo_critic_forward_rnn(const mappo_net_config* cfg, const float* params, const float* share_obs,
+                                        int obs_ld, long long rows, int share_rows_div, const float* rnn_states_in,
+                                        const float* masks, float* rnn_states_out, float* values_out, void* workspace,
+                                        void* stream) {
+  MAPPO_REQUIRE(values_out && share_rows_div >= 1, "critic_forward_rnn: bad outputs");
+  MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_forward_rnn: actor config");
+  MlpArgs a{};
+  a.params = params; a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.group = 1; a.values_out = values_out;
+  a.x_div = share_rows_div; a.workspace = workspace;
+  return tc::rnn_forward<1>(a, cfg, rnn_states_in, masks, rnn_states_out, (cudaStream_t)stream, "critic_forward_rnn");
+}
+
+extern "C" int mappo_actor_update_rnn(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                                      const float* obs, int obs_ld, long long n_chunks, int chunk_len,
+                                      const int64_t* index, const float* rnn_states, const float* masks,
+                                      const float* actions, const float* old_logp, const float* adv,
+                                      const float* active_masks, const float* available_actions, float* grad_partials,
+                                      int n_partials, double* loss_partials, void* workspace, void* stream) {
+  MAPPO_REQUIRE(loss && actions && old_logp && adv, "actor_update_rnn: null pointer");
+  MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_update_rnn: critic config");
+  MlpArgs a{};
+  a.params = params; a.x = obs; a.ld = obs_ld; a.index = index; a.x_div = 1; a.actions = actions;
+  a.old_logp = old_logp; a.adv = adv; a.active = active_masks; a.avail = available_actions; a.loss = *loss;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
+  return tc::rnn_update<2>(a, cfg, n_chunks, chunk_len, rnn_states, masks, n_partials, (cudaStream_t)stream,
+                           "actor_update_rnn");
+}
+
+extern "C" int mappo_critic_update_rnn(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
+                                       const float* share_obs, int obs_ld, long long n_chunks, int chunk_len,
+                                       const int64_t* index, int share_rows_div, const float* rnn_states,
+                                       const float* masks, const float* value_preds, const float* returns,
+                                       const float* active_masks, const float* vn_stats, float* grad_partials,
+                                       int n_partials, double* loss_partials, void* workspace, void* stream) {
+  MAPPO_REQUIRE(loss && value_preds && returns && share_rows_div >= 1, "critic_update_rnn: null pointer");
+  MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_update_rnn: actor config");
+  MAPPO_REQUIRE(!loss->use_value_norm || vn_stats, "critic_update_rnn: use_value_norm without statistics");
+  MlpArgs a{};
+  a.params = params; a.x = share_obs; a.ld = obs_ld; a.index = index; a.x_div = share_rows_div; a.group = 1;
+  a.value_preds = value_preds; a.returns = returns; a.active = active_masks; a.vn_stats = vn_stats; a.loss = *loss;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
+  return tc::rnn_update<3>(a, cfg, n_chunks, chunk_len, rnn_states, masks, n_partials, (cudaStream_t)stream,
+                           "critic_update_rnn");
+}

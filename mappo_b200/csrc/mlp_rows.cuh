@@ -32,6 +32,8 @@ struct MlpArgs {
   float* grad_partials; double* loss_partials;
   // wide first layer (mlp_wide.cu): caller scratch; z1 = its [rows][64] part (activations in, gradient out)
   void* workspace; float* z1;
+  // recurrent networks (mlp_gru.cu): n2 rows out (base features) / dLoss/dn2 rows in (base backward), [rows][64]
+  float* feat;
 };
 
 // log-softmax over l[0..n): returns logsumexp, writes logp in place

@@ -187,7 +187,7 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
   const long long g = tile * kBM + r;
   const bool valid = g < a.rows;
   float xv[XC];
-  const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+  const long long srow = valid ? ((a.index ? a.index[g] : g) / a.x_div) : 0;
   const float* __restrict__ row = a.x + srow * (long long)a.ld;
 #pragma unroll
   for (int i = 0; i < XC; ++i) {
@@ -260,7 +260,9 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
 }
 
 // ---- the kernel ------------------------------------------------------------------------------------------
-// MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic.  KP: padded input width (32 | 64).
+// MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic; recurrent networks (mlp_gru.cu) use
+// 4 = base features only (n2 rows written to a.feat) and 5 = base backward from dLoss/dn2 rows read from a.feat.
+// KP: padded input width (32 | 64).
 // AMAX: register width of the head (1 critic; 8 = single categorical head with <= 8 logits and no availability
 // mask, losses evaluated in registers; 16 = generic heads through the row functions of mlp_rows.cuh).
 // Per tile the update issues three groups of MMAs -- {fc2}, {head wgrad, fc2 wgrad, fc2 dgrad}, {fc1 wgrad, fc1 of
@@ -269,7 +271,8 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
 // WIDE: the first layer lives outside (mlp_wide.cu): z1 rows come from a.z1 and dLoss/dz1 goes back in place.
 template <int MODE, int KP, int AMAX, bool WIDE>
 __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
-  constexpr bool UPDATE = (MODE >= 2);
+  constexpr bool UPDATE = (MODE == 2 || MODE == 3 || MODE == 5);
+  constexpr bool HEAD = (MODE < 4);
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
@@ -361,9 +364,14 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::tc_fence_after();
     load_acc16(lane_addr, cq, n2);
     act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
-    if (UPDATE) store_cols16(sm + m.BS2, r, cq, n2);
+    if (UPDATE && HEAD) store_cols16(sm + m.BS2, r, cq, n2);
+    if (MODE == 4 && valid) {
+      float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) fo[i] = make_float4(n2[4 * i], n2[4 * i + 1], n2[4 * i + 2], n2[4 * i + 3]);
+    }
     float* xlog = reinterpret_cast<float*>(sm + (m.xlog_in_x ? m.X + (buf ^ 1) * x_bytes : m.xlog));
-    {
+    if (HEAD) {
       float* mine = xlog + (size_t)(cq * kBM + r) * AS;
 #pragma unroll
       for (int q = 0; q < AMAX; ++q) {
@@ -379,12 +387,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         }
       }
     }
-    bar_named(1 + q4, 128);
+    if (HEAD) bar_named(1 + q4, 128);
     float l[AMAX];
 #pragma unroll
     for (int q = 0; q < AMAX; ++q) {
       l[q] = 0.0f;
-      if (q < A) {
+      if (HEAD && q < A) {
         const float* p = xlog + (size_t)r * AS + q;
         l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
       }
@@ -411,7 +419,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- losses: every thread of a row evaluates them (no idle warps, no shared-memory round trip for dlogits);
     // the column-quarter-0 thread keeps the sums and writes the dlogits operand of the head weight gradient
     float dl[AMAX];
-    {
+#pragma unroll
+    for (int q = 0; q < AMAX; ++q) dl[q] = 0.0f;
+    if (HEAD) {
       double mine[4] = {0.0, 0.0, 0.0, 0.0};
       if (MODE == 2 && AMAX == 8) {
         float sums[4] = {0.0f, 0.0f, 0.0f, 0.0f};
@@ -460,9 +470,14 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     float dz[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) dz[i] = 0.0f;
+    if (MODE == 5 && valid) {                                             // dLoss/dn2 from the recurrent layer
+      const float4* fi = reinterpret_cast<const float4*>(a.feat + g * 64 + 16 * cq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { const float4 t = fi[i]; dz[4 * i] = t.x; dz[4 * i + 1] = t.y; dz[4 * i + 2] = t.z; dz[4 * i + 3] = t.w; }
+    }
 #pragma unroll
     for (int q = 0; q < AMAX; ++q) {
-      if (q < A) {
+      if (HEAD && q < A) {
         const float4* w4 = reinterpret_cast<const float4*>(Whf + q * 64 + 16 * cq);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -481,7 +496,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (tid == 0) {
       umma::tc_fence_after();
-      issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                                       // Gh += n2^T dlogits
+      if (HEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
       issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
@@ -525,7 +540,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     if (!WIDE) { umma::mbar_wait(bar, ph); ph ^= 1; }                   // the last tile's fc1 weight gradient
     umma::tc_fence_after();
     float* __restrict__ gp0 = a.grad_partials + (size_t)(2 * blockIdx.x) * L.total;
-    for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;
+    if (HEAD) for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;   // MODE 5: the caller zeroed the buffer
     float* red = reinterpret_cast<float*>(sm + m.red);                    // [2][16 warps][16]
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -553,7 +568,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
           if (k < D) gp[L.w1 + mrow * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
         }
       }
-      if (cq == 3) {                                                      // warps 12..15: head gradient, lanes = hidden unit
+      if (HEAD && cq == 3) {                                              // warps 12..15: head gradient, lanes = hidden unit
         umma::tmem_ld16(lane_addr + kColGh, u);
         umma::tmem_ld16(lane_addr + kColGh + 16, w);
         int h = 0, off = 0;
@@ -571,7 +586,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       float s1 = 0.0f, s2 = 0.0f;
       for (int q = 0; q < 4; ++q) { s1 += red[(4 * c + q) * 16 + i]; s2 += red[256 + (4 * c + q) * 16 + i]; }
       gp0[L.b1 + tid] = s1; gp0[L.b2 + tid] = s2;
-    } else if (tid < 64 + A) {
+    } else if (HEAD && tid < 64 + A) {
       const int q = tid - 64;
       const float* dbh = reinterpret_cast<const float*>(sm + m.dbh);
       float s = 0.0f;
@@ -587,7 +602,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (lane == 0) lred[q][warp] = v;
     }
     __syncthreads();
-    if (tid < 4) {
+    if (HEAD && tid < 4) {
       double v = 0.0;
       for (int w = 0; w < kThreads / 32; ++w) v += lred[tid][w];
       a.loss_partials[(size_t)(2 * blockIdx.x) * 4 + tid] = v;
@@ -635,7 +650,7 @@ bool supports(const mappo_net_config* cfg) {
 
 template <int MODE, int KP, int AMAX, bool WIDE = false>
 static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
-  const Map m = make_map(KP, a.L.a_total | 1, MODE >= 2);
+  const Map m = make_map(KP, a.L.a_total | 1, MODE == 2 || MODE == 3 || MODE == 5);
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -654,9 +669,9 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
   if (a.x_div < 1) a.x_div = 1;
   a.Kp = cfg->in_dim <= 32 ? 32 : 64;
   a.ntiles = (a.rows + kBM - 1) / kBM;
-  constexpr bool kCritic = (MODE == 1 || MODE == 3);
+  constexpr bool kCritic = (MODE == 1 || MODE == 3 || MODE >= 4);        // one register column for the head
   if constexpr (kCritic) {
-    if (cfg->in_dim > 64) {                     // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
+    if (MODE < 4 && cfg->in_dim > 64) {         // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
       MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
       a.Kp = 32;
       a.z1 = static_cast<float*>(a.workspace);
@@ -682,6 +697,8 @@ template int launch<0>(MlpArgs&, const mappo_net_config*, cudaStream_t, const ch
 template int launch<1>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
 template int launch<2>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
 template int launch<3>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+template int launch<4>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
+template int launch<5>(MlpArgs&, const mappo_net_config*, cudaStream_t, const char*);
 
 }  // namespace tc
 }  // namespace mappo

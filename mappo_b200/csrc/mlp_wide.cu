@@ -16,21 +16,10 @@
 //
 // Reference: mlp.py:44-59 (feature_norm, fc1), r_actor_critic.py:146-165, r_mappo.py:52-89,151-156.
 #include "mlp_tc_common.cuh"
+#include "mlp_wide.cuh"
 
 namespace mappo {
 namespace tc {
-
-struct WideArgs {
-  NetLayout L;
-  const float* params;
-  const float* x; int ld; long long rows; const int64_t* index; int x_div;
-  int vec;                       // 1: x rows are 16-byte aligned (float4 loads)
-  float* z1;                     // [rows][64]   forward: out
-  float* xstats;                 // [rows][2]    forward: out, weight gradient: in
-  const float* dz1;              // [rows][64]   weight gradient: in
-  float* grad_partials;          // weight gradient: partial rows [2 * nsplit][L.total] (W1 slot written)
-  int nsplit, ncg, colw;         // weight gradient: row splits, column groups, columns per group (multiple of 16, <= 240)
-};
 
 // 8 consecutive floats of a row, columns [c, c + 8), zero beyond D
 __device__ __forceinline__ void load8(const float* __restrict__ row, int c, int D, bool ok, int vec, float (&v)[8]) {
@@ -207,11 +196,12 @@ __host__ __device__ inline WgMap make_wg_map(int colw) {
   return m;
 }
 
+template <bool COLSUM>
 __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs a) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
-  const NetLayout& L = a.L;
-  const int D = L.in_dim, colw = a.colw;
+  __shared__ float csred[2][8][kXChunksPerThread * 8];
+  const int D = a.D, colw = a.colw;
   const WgMap m = make_wg_map(colw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cg = blockIdx.x % a.ncg, sp = blockIdx.x / a.ncg;
@@ -237,7 +227,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     valid = g < a.rows;
     const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
     const float* __restrict__ row = a.x + srow * (long long)a.ld;
-    if (L.use_fn && valid) { mean = __ldg(a.xstats + 2 * g); rstd = __ldg(a.xstats + 2 * g + 1); }
+    if (a.norm && valid) { mean = __ldg(a.xstats + 2 * g); rstd = __ldg(a.xstats + 2 * g + 1); }
     else { mean = 0.0f; rstd = 1.0f; }
 #pragma unroll
     for (int i = 0; i < kXChunksPerThread; ++i) {
@@ -245,8 +235,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       if (ch < nchx) load8(row, col0 + 8 * ch, D, valid, a.vec, xr[i]);
     }
     if (valid) {
-      const float4 p = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * 64 + 8 * cs));
-      const float4 q = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * 64 + 8 * cs + 4));
+      const float4 p = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * a.dz_ld + 8 * cs));
+      const float4 q = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * a.dz_ld + 8 * cs + 4));
       dr[0] = p.x; dr[1] = p.y; dr[2] = p.z; dr[3] = p.w; dr[4] = q.x; dr[5] = q.y; dr[6] = q.z; dr[7] = q.w;
     } else {
 #pragma unroll
@@ -254,6 +244,11 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     }
   };
 
+  float csum[kXChunksPerThread][8];
+#pragma unroll
+  for (int i = 0; i < kXChunksPerThread; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) csum[i][e] = 0.0f;
   uint32_t n = 0;
   long long ht = sp;
   if (ht < nht) prefetch(ht);
@@ -267,7 +262,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
         if (ch < nchx) {
           float v[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = (valid && col0 + 8 * ch + e < D) ? (xr[i][e] - mean) * rstd : 0.0f;
+          for (int e = 0; e < 8; ++e) {
+            v[e] = (valid && col0 + 8 * ch + e < D) ? (xr[i][e] - mean) * rstd : 0.0f;
+            if (COLSUM) csum[i][e] += v[e];
+          }
           split8(v, hi, lo);
           const uint32_t off = (uint32_t)ch * kHChunk + (uint32_t)hr * 16;
           *reinterpret_cast<uint4*>(sm + m.B + off) = hi;
@@ -303,7 +301,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     umma::tc_fence_after();
     const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
     const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
-    float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * L.total + L.w1 + (size_t)(r & 63) * D;
+    float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * a.total + a.out_w;
+    const int j = r & 63;
     const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;
     for (int blk = cq; blk < colw / 16; blk += 4) {
       float u[16], w[16];
@@ -312,8 +311,30 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int k = col0 + 16 * blk + i;
-        if (k < D) gp[k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+        if (k < D) {
+          const float val = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+          if (a.transposed) gp[(size_t)((k + a.rot) % D) * 64 + j] = val;
+          else gp[(size_t)j * D + k] = val;
+        }
       }
+    }
+  }
+  if (COLSUM && a.out_b >= 0) {                            // column sums of x over this CTA's rows -> partial row 2 sp
+#pragma unroll
+    for (int i = 0; i < kXChunksPerThread; ++i)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float v = csum[i][e];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) csred[warp & 1][cs][i * 8 + e] = v;
+      }
+    __syncthreads();
+    if (tid < 8 * kXChunksPerThread * 8) {
+      const int c8 = tid / (kXChunksPerThread * 8), ie = tid % (kXChunksPerThread * 8);
+      const int ch = c8 + 8 * (ie >> 3), k = col0 + 8 * ch + (ie & 7);
+      if (ch < nchx && k < D)
+        a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b + (k + a.rot) % D] = csred[0][c8][ie] + csred[1][c8][ie];
     }
   }
   umma::tc_fence_before();
@@ -342,6 +363,8 @@ static void fill(WideArgs& w, const MlpArgs& a, void* workspace) {
   w.z1 = static_cast<float*>(workspace);
   w.xstats = w.z1 + a.rows * 64;
   w.dz1 = w.z1;
+  w.D = a.L.in_dim; w.dz_ld = 64; w.norm = a.L.use_fn; w.total = a.L.total; w.out_w = a.L.w1;
+  w.transposed = 0; w.rot = 0; w.out_b = -1;
 }
 
 int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
@@ -359,27 +382,35 @@ int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, cons
   return 0;
 }
 
-int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
-  WideArgs w{};
-  fill(w, a, workspace);
-  const int D = a.L.in_dim;
+// G[j][k] = sum_rows dz[row][j] x[row][k] into the partial rows, split over rows (nsplit <= grid_for(rows)) and
+// column groups of at most 240 columns
+int launch_wgrad_generic(WideArgs& w, cudaStream_t stream, const char* who) {
+  const int D = w.D;
   w.ncg = (D + kMaxColw - 1) / kMaxColw;
   w.colw = (((D + w.ncg - 1) / w.ncg) + 15) & ~15;
-  const long long nht = (a.rows + kHR - 1) / kHR;
-  long long ns = grid_for(a.rows) / w.ncg;                               // <= the main kernel's CTAs (2 partial rows each)
+  const long long nht = (w.rows + kHR - 1) / kHR;
+  long long ns = grid_for(w.rows) / w.ncg;                               // <= the main kernel's CTAs (2 partial rows each)
   if (ns < 1) ns = 1;
   if (ns > nht) ns = nht;
   w.nsplit = (int)ns;
-  w.grad_partials = a.grad_partials;
   const WgMap m = make_wg_map(w.colw);
   static bool attr_set = false;
   if (!attr_set) {
-    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideMaxSmem));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
     attr_set = true;
   }
-  wgrad1_wide_kernel<<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  if (w.out_b >= 0) wgrad1_wide_kernel<true><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  else wgrad1_wide_kernel<false><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
+}
+
+int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
+  WideArgs w{};
+  fill(w, a, workspace);
+  w.grad_partials = a.grad_partials;
+  return launch_wgrad_generic(w, stream, who);
 }
 
 }  // namespace tc

@@ -58,9 +58,17 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
   // 1. chain rule through the folded affines (net.cuh)
   unfold_linear(params, gsum, g, L.w1, L.b1, H, D, L.use_fn ? L.fn_g : -1, L.fn_b, false);
   unfold_linear(params, gsum, g, L.w2, L.b2, H, H, L.g1, L.be1, false);
+  // what follows fc2's LayerNorm: the heads, or (recurrent) the GRU input weights; the GRU's own LayerNorm then
+  // precedes the heads, and W_hh sees the raw hidden state (no affine)
+  int hg = L.g2, hbe = L.be2;
+  if (L.recurrent) {
+    unfold_linear(params, gsum, g, L.wih, L.bih, 3 * H, H, L.g2, L.be2, false);
+    unfold_linear(params, gsum, g, L.whh, L.bhh, 3 * H, H, -1, -1, false);
+    hg = L.gr; hbe = L.ber;
+  }
   for (int h = 0; h < L.n_heads; ++h) {
-    unfold_linear(params, gsum, g, L.wh[h], L.bh[h], L.head_dim[h], H, L.g2, L.be2, h > 0);
-    __syncthreads();                                    // heads accumulate into the same g2/be2 slots
+    unfold_linear(params, gsum, g, L.wh[h], L.bh[h], L.head_dim[h], H, hg, hbe, h > 0);
+    __syncthreads();                                    // heads accumulate into the same affine slots
   }
   __syncthreads();
   // 2. loss denominator, global L2 norm
@@ -128,7 +136,6 @@ extern "C" int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_con
                                int denominator_slot, long long rows_total, int apply_update, float* grad_out,
                                float* info_out, void* stream) {
   if (int rc = check_net(cfg, "adam_step")) return rc;
-  if (cfg->recurrent) MAPPO_UNSUPPORTED("adam_step: recurrent (GRU) networks are not built yet");
   MAPPO_REQUIRE(adam && params && grad_sum && loss_sum && grad_out, "adam_step: null pointer (grad_out is required)");
   MAPPO_REQUIRE(!apply_update || (exp_avg && exp_avg_sq), "adam_step: null optimiser state");
   MAPPO_REQUIRE(denominator_slot >= 0 && denominator_slot < 4 && rows_total > 0, "adam_step: bad denominator");

@@ -249,6 +249,86 @@ def critic_forward(cfg, params, share_obs, values_out, group=1):
                                               ptr(values_out), ptr(ws), stream_ptr()), "critic_forward")
 
 
+def rnn_workspace(cfg, positions, update, device):
+    L = _lib.lib()
+    L.mappo_rnn_workspace_bytes.argtypes = [_NC, C.c_longlong, C.c_int]
+    L.mappo_rnn_workspace_bytes.restype = C.c_longlong
+    need = int(L.mappo_rnn_workspace_bytes(C.byref(cfg), int(positions), int(update)))
+    key = (device, "rnn")
+    ws = _WORKSPACES.get(key)
+    if ws is None or ws.numel() * 4 < need:
+        ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=device)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+def _h2(x, rows):
+    """rnn states [rows, recurrent_N = 1, H] (or [rows, H]) -> contiguous float32 [rows, H] view"""
+    x = x.reshape(rows, -1)
+    assert x.dtype == torch.float32 and x.is_cuda and x.is_contiguous() and x.shape[1] == 64, "rnn states must be contiguous [rows, 64]"
+    return x
+
+
+def actor_forward_rnn(cfg, params, obs, rnn_in, masks, rnn_out, actions_out, logp_out, available_actions=None,
+                      deterministic=False, seed=0, step=0, row_offset=0, given_actions=None, entropy_out=None):
+    obs, ld = _rows_view(obs)
+    rows = obs.shape[0]
+    ws = rnn_workspace(cfg, rows, 0, obs.device)
+    L = _lib.lib()
+    L.mappo_actor_forward_rnn.argtypes = [_NC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, C.c_int, C.c_uint64, C.c_uint64,
+                                          C.c_longlong, _P, _P, _P, _P, _P, _P, _P]
+    with TIMERS.span("actor_forward"):
+        check(L.mappo_actor_forward_rnn(C.byref(cfg), ptr(params), _vp(obs), ld, rows, ptr(_h2(rnn_in, rows)),
+                                        ptr(_f32c(masks.reshape(rows), "masks")), ptr(available_actions),
+                                        int(deterministic), int(seed) & (2 ** 64 - 1), int(step), int(row_offset),
+                                        ptr(given_actions), ptr(_h2(rnn_out, rows)), ptr(actions_out), ptr(logp_out),
+                                        ptr(entropy_out), ptr(ws), stream_ptr()), "actor_forward_rnn")
+
+
+def critic_forward_rnn(cfg, params, share_obs, rnn_in, masks, rnn_out, values_out, share_rows_div=1):
+    x, ld = _rows_view(share_obs)
+    rows = values_out.numel()
+    ws = rnn_workspace(cfg, rows, 0, x.device)
+    L = _lib.lib()
+    L.mappo_critic_forward_rnn.argtypes = [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P, _P, _P]
+    with TIMERS.span("critic_forward"):
+        check(L.mappo_critic_forward_rnn(C.byref(cfg), ptr(params), _vp(x), ld, rows, int(share_rows_div),
+                                         ptr(_h2(rnn_in, rows)), ptr(_f32c(masks.reshape(rows), "masks")),
+                                         ptr(_h2(rnn_out, rows)), ptr(values_out), ptr(ws), stream_ptr()),
+              "critic_forward_rnn")
+
+
+def actor_update_rnn(cfg, loss, params, obs, n_chunks, chunk_len, index, rnn_states, masks, actions, old_logp, adv,
+                     active_masks, available_actions, grad_partials, loss_partials):
+    obs, ld = _rows_view(obs)
+    ws = rnn_workspace(cfg, n_chunks * chunk_len, 1, obs.device)
+    L = _lib.lib()
+    L.mappo_actor_update_rnn.argtypes = [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P, _P, _P, _P,
+                                         _P, _P, C.c_int, _P, _P, _P]
+    assert index.dtype == torch.int64 and index.numel() == n_chunks * chunk_len
+    with TIMERS.span("actor_update"):
+        check(L.mappo_actor_update_rnn(C.byref(cfg), C.byref(loss), ptr(params), _vp(obs), ld, int(n_chunks),
+                                       int(chunk_len), ptr(index), ptr(rnn_states), ptr(masks), ptr(actions),
+                                       ptr(old_logp), ptr(adv), ptr(active_masks), ptr(available_actions),
+                                       ptr(grad_partials), int(grad_partials.shape[0]), ptr(loss_partials), ptr(ws),
+                                       stream_ptr()), "actor_update_rnn")
+
+
+def critic_update_rnn(cfg, loss, params, share_obs, n_chunks, chunk_len, index, rnn_states, masks, value_preds, returns,
+                      active_masks, vn_stats, grad_partials, loss_partials, share_rows_div=1):
+    x, ld = _rows_view(share_obs)
+    ws = rnn_workspace(cfg, n_chunks * chunk_len, 1, x.device)
+    L = _lib.lib()
+    L.mappo_critic_update_rnn.argtypes = [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P,
+                                          _P, _P, _P, C.c_int, _P, _P, _P]
+    with TIMERS.span("critic_update"):
+        check(L.mappo_critic_update_rnn(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, int(n_chunks),
+                                        int(chunk_len), ptr(index), int(share_rows_div), ptr(rnn_states), ptr(masks),
+                                        ptr(value_preds), ptr(returns), ptr(active_masks), ptr(vn_stats),
+                                        ptr(grad_partials), int(grad_partials.shape[0]), ptr(loss_partials), ptr(ws),
+                                        stream_ptr()), "critic_update_rnn")
+
+
 def update_num_blocks(cfg, rows):
     L = _lib.lib()
     L.mappo_update_num_blocks.argtypes = [_NC, C.c_longlong]

@@ -74,7 +74,17 @@ class Runner(object):
         b = self.buffer
         nv = torch.empty(b.n_rollout_threads, b.num_agents, 1, dtype=torch.float32, device=b.device)
         uniq = b.share_obs_unique()
-        if uniq is not None:
+        if b._recurrent:
+            M = b.num_agents
+            scratch = torch.empty_like(b.rnn_states_critic[-1])
+            if uniq is not None and self.use_centralized_V:
+                self.policy.critic.forward_into(uniq[-1], nv, rnn_in=b.rnn_states_critic[-1], masks=b.masks[-1],
+                                                rnn_out=scratch, share_rows_div=M)
+            else:
+                x = b.share_obs[-1] if self.use_centralized_V else b.obs[-1]
+                self.policy.critic.forward_into(x.reshape(-1, x.shape[-1]), nv, rnn_in=b.rnn_states_critic[-1],
+                                                masks=b.masks[-1], rnn_out=scratch)
+        elif uniq is not None:
             self.policy.critic.forward_into(uniq[-1], nv, group=b.num_agents)
         else:
             self.policy.critic.forward_into(b.share_obs[-1].reshape(-1, b.share_obs.shape[-1]), nv, group=1)

@@ -72,6 +72,21 @@ class MPERunner(Runner):
         N, M = b.n_rollout_threads, b.num_agents
         pol = self.trainer.policy
         self.trainer.prep_rollout()
+        if b._recurrent:
+            # rnn.py:24-28: h = GRU(x, h * mask); the new states go straight into slot step + 1
+            pol.actor.forward_into(b.obs[step].view(N * M, -1), b.actions[step], b.action_log_probs[step],
+                                   row_offset=self.envs._cfg.env_id_offset * M, rnn_in=b.rnn_states[step],
+                                   masks=b.masks[step], rnn_out=b.rnn_states[step + 1])
+            uniq = b.share_obs_unique()
+            if self.use_centralized_V and uniq is not None:
+                pol.critic.forward_into(uniq[step], b.value_preds[step], rnn_in=b.rnn_states_critic[step],
+                                        masks=b.masks[step], rnn_out=b.rnn_states_critic[step + 1], share_rows_div=M)
+            else:
+                x = b.share_obs[step] if self.use_centralized_V else b.obs[step]
+                pol.critic.forward_into(x.reshape(N * M, -1), b.value_preds[step], rnn_in=b.rnn_states_critic[step],
+                                        masks=b.masks[step], rnn_out=b.rnn_states_critic[step + 1])
+            return (b.value_preds[step], b.actions[step], b.action_log_probs[step], b.rnn_states[step + 1],
+                    b.rnn_states_critic[step + 1], b.actions[step])
         pol.actor.forward_into(b.obs[step].view(N * M, -1), b.actions[step], b.action_log_probs[step],
                                row_offset=self.envs._cfg.env_id_offset * M)
         if self.use_centralized_V:
@@ -86,7 +101,13 @@ class MPERunner(Runner):
         MLP policies carry no rnn state), so this validates the slot identity and advances `buffer.step`."""
         obs, rewards, masks, infos, values, actions, action_log_probs, rnn_states, rnn_states_critic = data
         b = self.buffer
-        b.insert(b.share_obs[b.step + 1], obs, None, None, actions, action_log_probs, values, rewards, masks)
+        if b._recurrent:
+            # mpe_runner.py:128-129: states of finished episodes are zeroed (masks = 1 - done, written by the env kernel)
+            s1 = b.step + 1
+            b.rnn_states[s1].mul_(b.masks[s1].unsqueeze(-1))
+            b.rnn_states_critic[s1].mul_(b.masks[s1].unsqueeze(-1))
+        b.insert(b.share_obs[b.step + 1], obs, rnn_states, rnn_states_critic, actions, action_log_probs, values,
+                 rewards, masks)
 
     @torch.no_grad()
     def eval(self, total_num_steps):

@@ -116,7 +116,37 @@ class SharedReplayBuffer(object):
         return dict(B=B, M=M, obs=self.obs[:-1].view(B, -1), share=share, share_is_unique=u is not None,
                     actions=self.actions.view(B, -1), logp=self.action_log_probs.view(B, -1),
                     value_preds=self.value_preds[:-1].view(B), returns=self.returns[:-1].view(B),
-                    active=self.active_masks[:-1].view(B), avail=avail)
+                    active=self.active_masks[:-1].view(B), avail=avail, masks=self.masks[:-1].view(B),
+                    rnn=self.rnn_states[:-1].reshape(B, -1) if self._recurrent else None,
+                    rnn_critic=self.rnn_states_critic[:-1].reshape(B, -1) if self._recurrent else None)
+
+    def recurrent_rows(self, num_mini_batch, data_chunk_length):
+        """Index form of recurrent_generator (shared_buffer.py:385-494): per minibatch (rows int64 [L * Nc] step-major
+        into the flat [T*N*M] sample arrays, Nc, L)."""
+        T, N, M = self.rewards.shape[0:3]
+        L = data_chunk_length
+        data_chunks = (N * T * M) // L
+        mini_batch_size = data_chunks // num_mini_batch
+        rand = torch.randperm(data_chunks).to(self.device)
+        dev = self.device
+        for i in range(num_mini_batch):
+            idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size]
+            pos = idx[None, :] * L + torch.arange(L, device=dev)[:, None]            # stream positions, [N, M, T] order
+            nm, t = pos // T, pos % T
+            yield (t * (N * M) + nm).reshape(-1).contiguous(), int(idx.numel()), L
+
+    def naive_recurrent_rows(self, num_mini_batch):
+        """Index form of naive_recurrent_generator (shared_buffer.py:288-383): whole trajectories."""
+        T, N, M = self.rewards.shape[0:3]
+        batch_size = N * M
+        per = batch_size // num_mini_batch
+        perm = torch.randperm(batch_size).to(self.device)
+        tt = torch.arange(T, device=self.device)
+        for start in range(0, batch_size, per):
+            idx = perm[start:start + per]
+            if idx.numel() < per:
+                break
+            yield (tt[:, None] * batch_size + idx[None, :]).reshape(-1).contiguous(), int(idx.numel()), T
 
     def _put(self, dst, src):
         """Copy unless `src` already IS the destination slot (the kernels wrote in place)."""

@@ -43,14 +43,18 @@ class OracleMAPPO:
         D = self.env.spec.obs_dims[0]
         self.D, self.S = D, D * M
         f = np.float32
+        A = len(op.head_keys(self.actor))
+        self.rec = bool(args.use_recurrent_policy or args.use_naive_recurrent_policy)
         self.obs = np.zeros((T + 1, N, M, D), f)
         self.value_preds = np.zeros((T + 1, N, M, 1), f)
         self.returns = np.zeros((T + 1, N, M, 1), f)
         self.masks = np.ones((T + 1, N, M, 1), f)
         self.active_masks = np.ones((T + 1, N, M, 1), f)
-        self.actions = np.zeros((T, N, M, 1), f)
-        self.action_log_probs = np.zeros((T, N, M, 1), f)
+        self.actions = np.zeros((T, N, M, A), f)
+        self.action_log_probs = np.zeros((T, N, M, A), f)
         self.rewards = np.zeros((T, N, M, 1), f)
+        self.rnn_states = np.zeros((T + 1, N, M, 1, args.hidden_size), f)
+        self.rnn_states_critic = np.zeros((T + 1, N, M, 1, args.hidden_size), f)
         self.calls = 0
 
     # ------------------------------------------------------------------ rollout
@@ -79,14 +83,16 @@ class OracleMAPPO:
         N, M = self.N, self.M
         obs = self.obs[step].reshape(N * M, -1)
         sh = self.share_at(step).reshape(N * M, -1)
-        z = np.zeros((N * M, 1, a.hidden_size), np.float32)
-        ones = np.ones((N * M, 1), np.float32)
-        feats, _ = op.actor_features(self.actor, obs, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        z = self.rnn_states[step].reshape(N * M, 1, -1)
+        zc = self.rnn_states_critic[step].reshape(N * M, 1, -1)
+        mk = self.masks[step].reshape(N * M, 1)
+        feats, h = op.actor_features(self.actor, obs, z, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
         logits = op.actor_logits(self.actor, feats, None)
         acts, lps, _ = op.act_forward(logits, False, seed=self.sample_seed, step=self.calls,
                                       row_offset=self.row_offset)
         self.calls += 1
-        values, _ = op.critic_values(self.critic, sh, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        values, hc = op.critic_values(self.critic, sh, zc, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
+        self._h = (h.numpy().reshape(N, M, 1, -1), hc.numpy().reshape(N, M, 1, -1))
         return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, -1), lps.numpy().reshape(N, M, -1)
 
     def rollout(self):
@@ -101,6 +107,11 @@ class OracleMAPPO:
             m = np.ones((self.N, self.M, 1), np.float32)
             m[dones] = 0.0
             self.masks[step + 1] = m
+            if self.rec:                                                 # mpe_runner.py:128-129
+                h, hc = self._h
+                h = h.copy(); hc = hc.copy()
+                h[dones] = 0.0; hc[dones] = 0.0
+                self.rnn_states[step + 1], self.rnn_states_critic[step + 1] = h, hc
 
     # ------------------------------------------------------------------ compute + train
     @torch.no_grad()
@@ -108,9 +119,9 @@ class OracleMAPPO:
         a = self.a
         N, M = self.N, self.M
         sh = self.share_at(-1).reshape(N * M, -1)
-        z = np.zeros((N * M, 1, a.hidden_size), np.float32)
-        nv, _ = op.critic_values(self.critic, sh, z, np.ones((N * M, 1), np.float32), a.use_ReLU,
-                                 a.use_feature_normalization, False)
+        z = self.rnn_states_critic[-1].reshape(N * M, 1, -1)
+        nv, _ = op.critic_values(self.critic, sh, z, self.masks[-1].reshape(N * M, 1), a.use_ReLU,
+                                 a.use_feature_normalization, self.rec)
         vp, ret = ob.compute_returns(self.rewards, self.value_preds, self.masks, nv.numpy().reshape(N, M, 1), a.gamma,
                                      a.gae_lambda, a.use_gae, a.use_proper_time_limits, None, self.vn)
         self.value_preds, self.returns = vp, ret
@@ -131,8 +142,9 @@ class OracleMAPPO:
             st[k] = (m, v)
         return float(norm)
 
-    def ppo_update(self, rows, adv):
-        """r_mappo.py:91-164 on the flat rows `rows` (None = all, in storage order)."""
+    def ppo_update(self, rows, adv, rnn_rows=None):
+        """r_mappo.py:91-164 on the flat rows `rows` (None = all, in storage order).  Recurrent: rows are the
+        step-major [L * Nc] rows of a chunked minibatch and rnn_rows [Nc] the rows that seed each chunk."""
         a = self.a
         T, N, M = self.T, self.N, self.M
         B = T * N * M
@@ -146,14 +158,18 @@ class OracleMAPPO:
         ret = take(self.returns[:-1].reshape(B, 1))
         am = take(self.active_masks[:-1].reshape(B, 1))
         nb = obs.shape[0]
-        z = np.zeros((nb, 1, a.hidden_size), np.float32)
+        z = zc = np.zeros((nb, 1, a.hidden_size), np.float32)
         ones = np.ones((nb, 1), np.float32)
+        if self.rec:
+            z = self.rnn_states[:-1].reshape(B, 1, -1)[rnn_rows]
+            zc = self.rnn_states_critic[:-1].reshape(B, 1, -1)[rnn_rows]
+            ones = take(self.masks[:-1].reshape(B, 1))
         asd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.actor.items()}
         csd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.critic.items()}
-        feats, _ = op.actor_features(asd, obs, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        feats, _ = op.actor_features(asd, obs, z, ones, a.use_ReLU, a.use_feature_normalization, self.rec)
         logits = op.actor_logits(asd, feats, None)
         logp, ent = op.evaluate_actions(logits, actions, am if a.use_policy_active_masks else None)
-        values, _ = op.critic_values(csd, sh, z, ones, a.use_ReLU, a.use_feature_normalization, False)
+        values, _ = op.critic_values(csd, sh, zc, ones, a.use_ReLU, a.use_feature_normalization, self.rec)
         pl, ratio = op.policy_loss(logp, old_lp, advb, am, a.clip_param, a.use_policy_active_masks)
         agrads = torch.autograd.grad(pl - ent * a.entropy_coef, [asd[k] for k in self.akeys])
         an = self._step_net("actor", self.actor, self.akeys, agrads, a.lr)
@@ -175,12 +191,21 @@ class OracleMAPPO:
         info = None
         n = 0
         for _ in range(a.ppo_epoch):
-            if a.num_mini_batch == 1 and not permute:
+            if a.use_recurrent_policy:
+                L = a.data_chunk_length
+                batches = ob.recurrent_rows(self.T, self.N, self.M, torch.randperm(B // L).numpy(), a.num_mini_batch, L)
+            elif a.use_naive_recurrent_policy:
+                batches = ob.naive_recurrent_rows(self.T, self.N * self.M, torch.randperm(self.N * self.M).numpy(),
+                                                  a.num_mini_batch)
+            elif a.num_mini_batch == 1 and not permute:
                 batches = [None]
             else:
                 batches = ob.feed_forward_rows(self.T, self.N, self.M, torch.randperm(B).numpy(), a.num_mini_batch)
             for rows in batches:
-                r = self.ppo_update(rows, adv)
+                rnn_rows = None
+                if isinstance(rows, tuple):
+                    rows, rnn_rows = rows
+                r = self.ppo_update(rows, adv, rnn_rows)
                 info = r if info is None else {k: info[k] + r[k] for k in r}
                 n += 1
         self.after_update()
@@ -191,6 +216,8 @@ class OracleMAPPO:
         self.obs[0] = self.obs[-1]
         self.masks[0] = self.masks[-1]
         self.active_masks[0] = self.active_masks[-1]
+        self.rnn_states[0] = self.rnn_states[-1]
+        self.rnn_states_critic[0] = self.rnn_states_critic[-1]
 
     def iteration(self):
         self.rollout()
@@ -225,6 +252,9 @@ class _AgentLearner(OracleMAPPO):
         self.actions = np.zeros((T, N, 1, heads), f)
         self.action_log_probs = np.zeros((T, N, 1, heads), f)
         self.rewards = np.zeros((T, N, 1, 1), f)
+        self.rec = False                                   # separated + recurrent is not restated
+        self.rnn_states = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
+        self.rnn_states_critic = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
         self.calls = 0
 
     def share_at(self, t):

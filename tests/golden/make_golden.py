@@ -404,6 +404,9 @@ PPO_CASES = {
     # unclipped value loss, no feature norm, listener of speaker_listener (D=11, S=14)
     "mlp_listener": dict(scenario="simple_speaker_listener", M=2, L=3, algo="mappo",
                          extra="--use_clipped_value_loss --use_feature_normalization --share_policy", B=257, seed=7),
+    # C4: simple_reference, shared GRU policy (rmappo), MultiDiscrete heads (5, 10), chunks of 10 steps
+    "gru_reference": dict(scenario="simple_reference", M=2, L=3, algo="rmappo",
+                          extra="--use_ReLU --lr 7e-4 --critic_lr 7e-4 --data_chunk_length 10", B=370, seed=9),
 }
 
 

@@ -88,7 +88,7 @@ def test_state_dict_keys_and_forward_vs_oracle(tag, golden_dir):
     np.testing.assert_allclose(ent.item(), ent_e.item(), rtol=1e-5)
 
 
-@pytest.mark.parametrize("tag", CASES)
+@pytest.mark.parametrize("tag", CASES + ["gru_reference"])
 def test_ppo_update_matches_reference(tag, golden_dir):
     """Two consecutive ppo_updates on the reference's own minibatch: losses, PRE-clip gradients, post-step
     parameters, Adam moments, ValueNorm statistics."""
@@ -183,3 +183,34 @@ def test_gradient_is_sum_over_shards_and_tiles():
     g_p, l_p = run(None, index=perm)
     assert (g_all - g_p).abs().max().item() < 2e-5 * scale
     np.testing.assert_allclose(l_p.cpu().numpy(), l_all.cpu().numpy(), rtol=1e-9)
+
+
+def test_recurrent_forward_and_evaluate_vs_oracle(golden_dir):
+    """GRU networks (rnn.py:24-77): one rollout step (values, argmax actions, log-probs, next rnn states) and the chunked
+    evaluate_actions against the oracle on the reference fixture's weights and minibatch."""
+    from oracle import policy as op
+    fx = np.load(os.path.join(golden_dir, "ppo_gru_reference.npz"))
+    args, pol, tr = build(fx)
+    assert list(pol.actor.state_dict().keys()) == [k[7:] for k in fx.files if k.startswith("actor0.")]
+    s = sample_of(fx)
+    share_obs, obs, rnn_a, rnn_c, actions, masks, active = s[0], s[1], s[2], s[3], s[4], s[7], s[8]
+    asd, csd = sd_from(fx, "actor0."), sd_from(fx, "critic0.")
+    N = rnn_a.shape[0]
+    # one step on the first N rows
+    feats, h1 = op.actor_features(asd, obs[:N], rnn_a, masks[:N], args.use_ReLU, args.use_feature_normalization, True)
+    a_ref, lp_ref, _ = op.act_forward(op.actor_logits(asd, feats, None), True)
+    act, lp, h_new = pol.actor(obs[:N], rnn_a, masks[:N], None, deterministic=True)
+    np.testing.assert_allclose(h_new.cpu().numpy(), h1.numpy(), rtol=1e-4, atol=2e-5)
+    same = act.cpu().numpy() == a_ref.numpy()
+    assert same.mean() > 0.99
+    np.testing.assert_allclose(lp.cpu().numpy()[same], lp_ref.numpy()[same], rtol=1e-4, atol=2e-5)
+    v_ref, hc1 = op.critic_values(csd, share_obs[:N], rnn_c, masks[:N], args.use_ReLU, args.use_feature_normalization, True)
+    v, hc = pol.critic(share_obs[:N], rnn_c, masks[:N])
+    np.testing.assert_allclose(v.cpu().numpy(), v_ref.numpy(), rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(hc.cpu().numpy(), hc1.numpy(), rtol=1e-4, atol=2e-5)
+    # the whole chunked minibatch
+    feats, _ = op.actor_features(asd, obs, rnn_a, masks, args.use_ReLU, args.use_feature_normalization, True)
+    lp_e, ent_e = op.evaluate_actions(op.actor_logits(asd, feats, None), actions, active if args.use_policy_active_masks else None)
+    elp, ent = pol.actor.evaluate_actions(obs, rnn_a, actions, masks, None, active)
+    np.testing.assert_allclose(elp.cpu().numpy(), lp_e.numpy(), rtol=1e-4, atol=3e-5)
+    np.testing.assert_allclose(ent.item(), ent_e.item(), rtol=1e-5)

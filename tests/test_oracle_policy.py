@@ -8,7 +8,7 @@ import torch
 
 from ppo_common import oracle_update, sd_from
 
-CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener"]
+CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener", "gru_reference"]
 
 
 @pytest.mark.parametrize("tag", CASES)
