@@ -32,24 +32,38 @@ M_AGENTS, N_LANDMARKS, T_EP, PPO_EPOCH = 3, 3, 25, 10
 D_OBS, S_OBS, N_ACT, H = 18, 54, 5, 64
 
 
+SCENARIO, ALGO, SEPARATED, CONFIG = "simple_spread", "mappo", False, "C2"
+
+
 def flags(n_envs):
-    return ("--env_name MPE --algorithm_name mappo --scenario_name simple_spread --num_agents %d --num_landmarks %d "
+    return ("--env_name MPE --algorithm_name %s --scenario_name %s --num_agents %d --num_landmarks %d "
             "--n_rollout_threads %d --episode_length %d --ppo_epoch %d --num_mini_batch 1 --use_ReLU --gain 0.01 "
-            "--lr 7e-4 --critic_lr 7e-4 --seed 1" % (M_AGENTS, N_LANDMARKS, n_envs, T_EP, PPO_EPOCH)).split()
+            "--lr 7e-4 --critic_lr 7e-4 --seed 1 %s" % (ALGO, SCENARIO, M_AGENTS, N_LANDMARKS, n_envs, T_EP, PPO_EPOCH,
+                                                        "--share_policy" if SEPARATED else "")).split()
 
 
-def set_workload(num_agents):
-    """Default M = 3 is C2 (the configuration the metric is quoted on); --agents 10 selects the C5 shape."""
-    global M_AGENTS, D_OBS, S_OBS
+def set_workload(num_agents, config=None):
+    """Default M = 3 is C2 (the configuration the metric is quoted on).  --agents 10 / --config c5: the C5 shape;
+    --config c3: speaker_listener with separated policies (15 epochs); --config c4: simple_reference with the
+    shared GRU policy (rmappo, chunks of 10, 15 epochs).  Only the default is the contract line; the others are
+    supplementary measurements of the remaining BASELINE configs."""
+    global M_AGENTS, D_OBS, S_OBS, SCENARIO, ALGO, SEPARATED, PPO_EPOCH, CONFIG
     M_AGENTS = int(num_agents)
+    if config == "c5":
+        M_AGENTS = 10
+    if config == "c3":
+        SCENARIO, SEPARATED, M_AGENTS, PPO_EPOCH = "simple_speaker_listener", True, 2, 15
+    if config == "c4":
+        SCENARIO, ALGO, M_AGENTS, PPO_EPOCH = "simple_reference", "rmappo", 2, 15
     D_OBS = 4 + 2 * N_LANDMARKS + 4 * (M_AGENTS - 1)       # simple_spread.py:93-103
     S_OBS = D_OBS * M_AGENTS
+    CONFIG = {"c3": "C3", "c4": "C4"}.get(config, "C2" if M_AGENTS == 3 else "C5" if M_AGENTS == 10 else "custom")
 
 
 def workload_name(n_envs, n_gpus):
-    return ("%s: MPE simple_spread M=%d L=3, %d envs/GPU x %d GPU, T=25, shared MLP (Tanh, H=64), ppo_epoch=10, "
-            "num_mini_batch=1, GAE+ValueNorm" % ("C2" if M_AGENTS == 3 else "C5" if M_AGENTS == 10 else "custom",
-                                                 M_AGENTS, n_envs, n_gpus))
+    kind = "separated MLP policies" if SEPARATED else ("shared GRU policy, chunks of 10" if ALGO == "rmappo" else "shared MLP")
+    return ("%s: MPE %s M=%d L=3, %d envs/GPU x %d GPU, T=25, %s (Tanh, H=64), ppo_epoch=%d, "
+            "num_mini_batch=1, GAE+ValueNorm" % (CONFIG, SCENARIO, M_AGENTS, n_envs, n_gpus, kind, PPO_EPOCH))
 
 
 # ---------------------------------------------------------------------------------------------- clocks
@@ -150,7 +164,10 @@ def build_runner(n_envs, device, rank, world, host_io=False):
     import torch
     from mappo_b200.config import parse_args
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
-    from mappo_b200.runner.shared.mpe_runner import MPERunner
+    if SEPARATED:
+        from mappo_b200.runner.separated.mpe_runner import MPERunner
+    else:
+        from mappo_b200.runner.shared.mpe_runner import MPERunner
     a = parse_args(flags(n_envs))
     torch.manual_seed(1)                                 # same initial weights on every rank (replicated parameters)
     from mappo_b200 import parallel as _par
@@ -158,7 +175,8 @@ def build_runner(n_envs, device, rank, world, host_io=False):
     runner = MPERunner({"all_args": a, "envs": envs, "eval_envs": None, "device": device, "num_agents": M_AGENTS,
                         "run_dir": None})
     from mappo_b200 import parallel
-    parallel.attach(runner.trainer, world)
+    for tr in (runner.trainer if SEPARATED else [runner.trainer]):
+        parallel.attach(tr, world)
     return a, envs, runner
 
 
@@ -248,6 +266,20 @@ def run_ours(ns):
     clocks = sampler.stop() if rank == 0 else None
     value = agent_steps * world * ns.steps / (ms * 1e-3)
 
+    if CONFIG not in ("C2", "C5", "custom"):
+        # supplementary configs: device-resident figure and kernel split only
+        if rank == 0:
+            print(json.dumps({"metric": METRIC.replace("simple_spread", SCENARIO), "value": value, "unit": UNIT,
+                              "n_gpus": world, "steps": ns.steps, "warmup": ns.warmup, "ms_per_step": ms / ns.steps,
+                              "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "data": "synthetic",
+                              "dtype": "f32 (policy, buffer), f64 (env physics)",
+                              "config": {"workload": workload_name(n_envs, world)}, "gpu_launches": int(launches),
+                              "kernel_ms_per_step": {k: {"launches": v[0], "ms_per_step": v[1] / ns.steps}
+                                                     for k, v in kt.items()},
+                              "clocks": clocks, "train_info": info, "supplementary": True}))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     # ---- e2e: host buffers at the reference-facing boundary
     envs.set_host_io(True)
     pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
@@ -333,11 +365,14 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
     ap.add_argument("--agents", type=int, default=3, help="agents per env (3 = C2, the headline; 10 = C5 shape)")
+    ap.add_argument("--config", default=None, choices=["c3", "c4", "c5"], help="supplementary BASELINE configs")
     ap.add_argument("--cpu-envs", dest="cpu_envs", type=int, default=1024, help="envs of the bounded CPU sample")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
     ns = ap.parse_args()
-    set_workload(ns.agents)
+    set_workload(ns.agents, ns.config)
+    if ns.config in ("c3", "c4") and ns.envs == 65536:
+        ns.envs = 32768
     ns.warmup = max(ns.warmup, 0)
     if ns.impl == "reference":
         run_reference(ns)
