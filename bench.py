@@ -190,7 +190,6 @@ def host_boundary_iteration(runner, envs, hb):
     b, pol = runner.buffer, runner.trainer.policy
     N, M = b.n_rollout_threads, b.num_agents
     h2d = d2h = 0
-    eye = np.eye(N_ACT, dtype=np.float32)
     for step in range(b.episode_length):
         values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step].reshape(N * M, -1),
                                                          b.obs[step].view(N * M, -1), None, None, None)
@@ -199,7 +198,9 @@ def host_boundary_iteration(runner, envs, hb):
         hb["logp"].copy_(logp.view(N, M, 1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         d2h += hb["values"].numel() * 4 + hb["actions"].numel() * 8 + hb["logp"].numel() * 4
-        actions_env = eye[hb["actions"].numpy()[..., 0]]                  # mpe_runner.py:110-121
+        oh = hb["onehot"]                                                # mpe_runner.py:110-121 (np.eye(n)[actions]), as a
+        oh.zero_().scatter_(2, hb["actions"], 1.0)                       # multi-threaded scatter into a pinned array
+        actions_env = oh.numpy()
         obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
         h2d += actions_env.nbytes
         d2h += obs.nbytes + rewards.nbytes + dones.nbytes
@@ -284,7 +285,7 @@ def run_ours(ns):
     envs.set_host_io(True)
     pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
     hb = {"values": pin(n_envs, M_AGENTS, 1), "actions": pin(n_envs, M_AGENTS, 1, dt=torch.int64),
-          "logp": pin(n_envs, M_AGENTS, 1)}
+          "logp": pin(n_envs, M_AGENTS, 1), "onehot": pin(n_envs, M_AGENTS, N_ACT)}
     host_boundary_iteration(runner, envs, hb)               # warm-up of the host path
     barrier()
     e_steps = max(1, min(ns.steps, ns.e2e_steps))

@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""Where the host-boundary iteration (bench.py `e2e`) spends its wall time: per-section host timers with a device
+synchronise at each boundary (diagnostic only; not a bench number)."""
+import os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+import bench
+
+
+def main():
+    n_envs = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+    dev = torch.device("cuda", 0)
+    a, envs, runner = bench.build_runner(n_envs, dev, 0, 1)
+    runner.warmup()
+    runner.run_episode()
+    envs.set_host_io(True)
+    M = bench.M_AGENTS
+    pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
+    hb = {"values": pin(n_envs, M, 1), "actions": pin(n_envs, M, 1, dt=torch.int64), "logp": pin(n_envs, M, 1),
+          "onehot": pin(n_envs, M, bench.N_ACT)}
+    bench.host_boundary_iteration(runner, envs, hb)
+    b, pol = runner.buffer, runner.trainer.policy
+    N = n_envs
+    T = {}
+    def tick(name, t0):
+        torch.cuda.synchronize()
+        T[name] = T.get(name, 0.0) + time.perf_counter() - t0
+    eye = np.eye(bench.N_ACT, dtype=np.float32)
+    t_all = time.perf_counter()
+    for step in range(b.episode_length):
+        t0 = time.perf_counter()
+        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step].reshape(N * M, -1), b.obs[step].view(N * M, -1), None, None, None)
+        tick("policy", t0); t0 = time.perf_counter()
+        hb["values"].copy_(values.view(N, M, 1), non_blocking=True)
+        hb["actions"].copy_(actions.view(N, M, 1), non_blocking=True)
+        hb["logp"].copy_(logp.view(N, M, 1), non_blocking=True)
+        tick("d2h policy outputs", t0); t0 = time.perf_counter()
+        actions_env = hb["onehot"].zero_().scatter_(2, hb["actions"], 1.0).numpy()
+        tick("host one-hot", t0); t0 = time.perf_counter()
+        obs, rewards, dones, infos = envs.step(actions_env)
+        tick("envs.step (h2d + kernel + d2h)", t0); t0 = time.perf_counter()
+        masks = np.ones((N, M, 1), dtype=np.float32); masks[dones] = 0.0
+        share_obs = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))
+        tick("host masks", t0); t0 = time.perf_counter()
+        b.insert(share_obs, obs, None, None, hb["actions"].numpy(), hb["logp"].numpy(), hb["values"].numpy(), rewards, masks)
+        tick("buffer.insert (h2d)", t0)
+    t0 = time.perf_counter()
+    runner.compute(); runner.train()
+    tick("compute + train", t0)
+    total = time.perf_counter() - t_all
+    for k, v in T.items():
+        print("%-34s %8.2f ms  %5.1f%%" % (k, v * 1e3, 100 * v / total))
+    print("total %.2f ms" % (total * 1e3))
+
+
+if __name__ == "__main__":
+    main()
