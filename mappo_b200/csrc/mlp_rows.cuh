@@ -34,6 +34,7 @@ struct MlpArgs {
   void* workspace; float* z1;
   // recurrent networks (mlp_gru.cu): n2 rows out (base features) / dLoss/dn2 rows in (base backward), [rows][64]
   float* feat;
+  int raw_ok;                      // mlp_tc.cu: input tiles are contiguous and arrive by bulk copy
 };
 
 // log-softmax over l[0..n): returns logsumexp, writes logp in place

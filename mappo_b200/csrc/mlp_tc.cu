@@ -26,7 +26,7 @@ constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 256, kColG
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
-  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, bhf, dbh, xch, xlog, red, bars, total;
+  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, bhf, dbh, xch, xlog, red, bars, raw, total;
   uint32_t x_piece, w1_piece;
   int xlog_in_x;                 // 1: the head's partial logits live in the idle X buffer (see below), `xlog` unused
 };
@@ -35,7 +35,9 @@ struct Map {
 // tile's fc1 weight gradient has completed, the next tile's rows are staged only after the block-wide barrier that
 // follows the last read), so they borrow it whenever they fit.  The rollout kernels have no BS / BS2 / DL / dbh regions
 // and keep a private one.
-__host__ __device__ inline Map make_map(int Kp, int AS, bool update) {
+// raw_floats > 0: a landing buffer for the NEXT tile's input rows as one bulk (TMA) copy -- used when the rows of a tile
+// are contiguous in global memory (no gather, row stride = in_dim), so that no thread issues row-divergent loads.
+__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0) {
   Map m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
@@ -58,6 +60,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update) {
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 2);
   m.bars = take(64);
+  m.raw = take((uint32_t)raw_floats * 4);
   m.total = o;
   return m;
 }
@@ -181,18 +184,27 @@ __device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[1
 // ---- input rows: gather, LayerNorm over in_dim (mlp.py:44-45,56-57), fp16 pairs -> X operand tile
 template <int KP>
 __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsigned char* xs, uint32_t x_piece, float2* xch,
-                                        int& slot, int cq, int r, int q4) {
+                                        int& slot, int cq, int r, int q4, const float* raw = nullptr) {
   constexpr int XC = KP / 4;                         // input columns per thread
   const int D = a.L.in_dim;
   const long long g = tile * kBM + r;
   const bool valid = g < a.rows;
   float xv[XC];
   const long long srow = valid ? ((a.index ? a.index[g] : g) / a.x_div) : 0;
-  const float* __restrict__ row = a.x + srow * (long long)a.ld;
+  if (raw) {                                          // the tile's rows already sit in shared memory
+    const float* row = raw + r * D;
 #pragma unroll
-  for (int i = 0; i < XC; ++i) {
-    const int c = XC * cq + i;
-    xv[i] = (valid && c < D) ? __ldg(row + c) : 0.0f;
+    for (int i = 0; i < XC; ++i) {
+      const int c = XC * cq + i;
+      xv[i] = (c < D) ? row[c] : 0.0f;
+    }
+  } else {
+    const float* __restrict__ row = a.x + srow * (long long)a.ld;
+#pragma unroll
+    for (int i = 0; i < XC; ++i) {
+      const int c = XC * cq + i;
+      xv[i] = (valid && c < D) ? __ldg(row + c) : 0.0f;
+    }
   }
   if (a.L.use_fn) {
     float s = 0.0f;
@@ -278,11 +290,32 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __shared__ double lred[4][kThreads / 32];
   const NetLayout& L = a.L;
   const int A = L.a_total, relu = L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS, UPDATE);
+  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
-  if (tid == 0) { umma::mbar_init(bar, 1); umma::fence_mbar_init(); }
+  uint64_t* tbar = bar + 1;                                           // arrival of a bulk-copied input tile
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::fence_mbar_init(); }
+  const float* raw = reinterpret_cast<const float*>(sm + m.raw);
+  const uint32_t raw_bytes = (uint32_t)(kBM * D) * 4u;
+  uint32_t tph = 0;
+  // tile t arrives by bulk copy iff it is a full tile, not this CTA's first, and the layout allows it
+  auto bulk_tile = [&](long long t) { return a.raw_ok && !WIDE && t < a.ntiles && (t + 1) * kBM <= a.rows; };
+  auto issue_bulk = [&](long long t) {                                // one thread
+    if (!bulk_tile(t)) return;
+    const uint32_t dst = umma::smem_u32(sm + m.raw), mb = umma::smem_u32(tbar);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(raw_bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(a.x + t * (long long)(kBM * D)), "r"(raw_bytes), "r"(mb) : "memory");
+  };
+  auto stage_next = [&](long long t, unsigned char* xs, int& slot_ref) {
+    if (bulk_tile(t)) {
+      umma::mbar_wait(tbar, tph); tph ^= 1;
+      stage_x<KP>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4, raw);
+    } else {
+      stage_x<KP>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4);
+    }
+  };
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   stage_weights_tc(sm, m, a, !WIDE, UPDATE);
   int slot = 0;
@@ -293,6 +326,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   umma::tc_fence_before();
   __syncthreads();
   umma::tc_fence_after();
+  if (tid == 0) issue_bulk(tile + gridDim.x);
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
   const uint32_t x_bytes = kNP * m.x_piece;
@@ -403,11 +437,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         if (MODE == 1) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
       }
       if (WIDE) continue;
-      if (has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
+      if (has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
       umma::fence_async_smem();
       umma::tc_fence_before();
       __syncthreads();
       if (tid == 0 && has_next) {
+        issue_bulk(tile + 2 * (long long)gridDim.x);
         umma::tc_fence_after();
         issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
                       2 * kWChunk, KP / 16, kIdFwd);
@@ -502,7 +537,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
     }
     // ---- next tile's input rows, staged while the tensor cores work
-    if (!WIDE && has_next) stage_x<KP>(a, tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, m.x_piece, xch, slot, cq, r, q4);
+    if (!WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
@@ -525,6 +560,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (tid == 0) {
       umma::tc_fence_after();
+      if (has_next) issue_bulk(tile + 2 * (long long)gridDim.x);
       issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes, kIdG1, !first);                        // G1 += dz1^T x
       if (has_next)
         issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
@@ -650,7 +686,13 @@ bool supports(const mappo_net_config* cfg) {
 
 template <int MODE, int KP, int AMAX, bool WIDE = false>
 static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
-  const Map m = make_map(KP, a.L.a_total | 1, MODE == 2 || MODE == 3 || MODE == 5);
+  constexpr bool kUpd = (MODE == 2 || MODE == 3 || MODE == 5);
+  // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
+  a.raw_ok = 0;
+  if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && (reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 &&
+      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim).total <= (uint32_t)kMaxDynSmem)
+    a.raw_ok = 1;
+  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0);
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE>;
   static bool attr_set = false;
   if (!attr_set) {

@@ -51,9 +51,15 @@ __host__ __device__ inline FwdMap make_fwd_map(int D) {
   return m;
 }
 
+// One pass over x: the staged operand is d = x - x[row][0] (exactly representable differences keep the fp16 pairs
+// accurate); the LayerNorm is applied algebraically when the accumulators leave TMEM,
+//   LN(x) . W'^T = rstd (d . W'^T - (mean - x0) colsum(W')),
+// with the row sums of d and d^2 gathered while staging.  The next 64-column chunk travels in registers while the
+// current one is converted and multiplied.
 __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
+  __shared__ float cs[64];                                              // colsum_k W'[j][k]
   const NetLayout& L = a.L;
   const int D = L.in_dim;
   const FwdMap m = make_fwd_map(D);
@@ -71,6 +77,13 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
       if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
       put_pair(sm + m.W, m.w_piece, 64, j, k, v);
     }
+    for (int j = warp; j < 64; j += kThreads / 32) {                   // one warp per output row, fixed lane order
+      float t = 0.0f;
+      for (int k = lane; k < D; k += 32) t += P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+      if (lane == 0) cs[j] = t;
+    }
   }
   umma::fence_async_smem();
   umma::tc_fence_before();
@@ -84,11 +97,28 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   float2* xch = reinterpret_cast<float2*>(sm + m.xch);
   int slot = 0;
   const int nkc = (m.K16 + 3) / 4;                                     // 64-column K-chunks per tile
+  const long long ntiles = (a.rows + kBM - 1) / kBM;
   uint32_t n = 0;                                                      // MMA groups committed so far
-  long long prev_g = -1;                                               // row whose accumulators are still in TMEM
 
+  struct RowInfo { const float* row; long long g; float x0; bool valid; };
+  auto row_info = [&](long long tile) {
+    RowInfo ri;
+    ri.g = tile * kBM + r;
+    ri.valid = ri.g < a.rows;
+    const long long srow = ri.valid ? (a.index ? a.index[ri.g] / a.x_div : ri.g) : 0;
+    ri.row = a.x + srow * (long long)a.ld;
+    ri.x0 = (ri.valid && L.use_fn) ? __ldg(ri.row) : 0.0f;
+    return ri;
+  };
+  auto load_chunk = [&](const RowInfo& ri, int kc, float (&v)[16]) {
+    const int c0 = 64 * kc + 16 * cq;
+    if (16 * cq < 16 * min(4, m.K16 - 4 * kc)) {
+      load8(ri.row, c0, D, ri.valid, a.vec, *reinterpret_cast<float(*)[8]>(v));
+      load8(ri.row, c0 + 8, D, ri.valid, a.vec, *reinterpret_cast<float(*)[8]>(v + 8));
+    }
+  };
   auto wait_commit = [&](uint32_t c) { umma::mbar_wait(bars + (c & 1), (c >> 1) & 1); };
-  auto drain = [&](long long g) {                                      // accumulators -> z1 row g
+  auto drain = [&](long long g, float ms, float rstd) {                 // accumulators -> z1 row g
     wait_commit(n - 1);
     umma::tc_fence_after();
     float u[16], w[16];
@@ -96,78 +126,83 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
     umma::tmem_ld16(lane_addr + 64 + 16 * cq, w);
     if (g < a.rows) {
       float4* out = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
+      const float* c16 = cs + 16 * cq;
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        out[i] = make_float4(fmaf(w[4 * i], kLoInv, u[4 * i]), fmaf(w[4 * i + 1], kLoInv, u[4 * i + 1]),
-                             fmaf(w[4 * i + 2], kLoInv, u[4 * i + 2]), fmaf(w[4 * i + 3], kLoInv, u[4 * i + 3]));
+        out[i] = make_float4(rstd * (fmaf(w[4 * i], kLoInv, u[4 * i]) - ms * c16[4 * i]),
+                             rstd * (fmaf(w[4 * i + 1], kLoInv, u[4 * i + 1]) - ms * c16[4 * i + 1]),
+                             rstd * (fmaf(w[4 * i + 2], kLoInv, u[4 * i + 2]) - ms * c16[4 * i + 2]),
+                             rstd * (fmaf(w[4 * i + 3], kLoInv, u[4 * i + 3]) - ms * c16[4 * i + 3]));
     }
     umma::tc_fence_before();
     __syncthreads();
   };
 
-  for (long long tile = blockIdx.x; tile < (a.rows + kBM - 1) / kBM; tile += gridDim.x) {
-    const long long g = tile * kBM + r;
-    const bool valid = g < a.rows;
-    const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
-    const float* __restrict__ row = a.x + srow * (long long)a.ld;
-    // row statistics over in_dim, shifted by the first element (mlp.py:44-45: LayerNorm, eps 1e-5)
-    float mean = 0.0f, rstd = 1.0f;
-    if (L.use_fn) {
-      const float x0 = valid ? __ldg(row) : 0.0f;
+  long long tile = blockIdx.x;
+  long long prev_g = -1;
+  float prev_ms = 0.0f, prev_rstd = 1.0f;
+  if (tile < ntiles) {
+    RowInfo cur = row_info(tile);
+    float pre[16];
+    load_chunk(cur, 0, pre);
+    while (tile < ntiles) {
       float s = 0.0f, q = 0.0f;
-      for (int ch = cq; ch < (D + 7) / 8; ch += 4) {
-        float v[8];
-        load8(row, 8 * ch, D, valid, a.vec, v);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float d = (8 * ch + i < D) ? v[i] - x0 : 0.0f;
-          s += d;
-          q = fmaf(d, d, q);
-        }
-      }
-      const float2 tot = row_sum2(s, q, xch, slot, cq, r, q4);
-      const float ms = tot.x / (float)D;
-      const float var = fmaxf(tot.y / (float)D - ms * ms, 0.0f);
-      mean = x0 + ms;
-      rstd = 1.0f / sqrtf(var + kLnEps);
-    }
-    if (cq == 0 && valid && a.xstats) { a.xstats[2 * g] = mean; a.xstats[2 * g + 1] = rstd; }
-    for (int kc = 0; kc < nkc; ++kc) {
-      const uint32_t b = n & 1;
-      const int ksteps = min(4, m.K16 - 4 * kc);
-      if (n >= 2) wait_commit(n - 2);                                  // X buffer b is free again
-      if (cq < ksteps) {
+      RowInfo nxt = cur;
+      const long long ntile = tile + gridDim.x;
+      for (int kc = 0; kc < nkc; ++kc) {
         float v[16];
-        const int c0 = 64 * kc + 16 * cq;
-        load8(row, c0, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v));
-        load8(row, c0 + 8, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v + 8));
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = (valid && c0 + i < D) ? (v[i] - mean) * rstd : 0.0f;
-        store_cols16(sm + m.X + b * kXBuf, r, cq, v);
-      }
-      umma::fence_async_smem();
-      umma::tc_fence_before();
-      __syncthreads();
-      if (kc == 0 && prev_g >= 0) drain(prev_g);                      // previous tile leaves TMEM before fc1 restarts
-      if (tid == 0) {
-        umma::tc_fence_after();
-        for (int ks = 0; ks < ksteps; ++ks) {
-          const uint32_t ao = sX + b * kXBuf + (uint32_t)ks * 2 * kRowChunk;
-          const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * kWChunk;
-          const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
-          const uint64_t bh = umma::smem_desc(bo, kWChunk, 128), bl = umma::smem_desc(bo + m.w_piece, kWChunk, 128);
-          const bool acc = kc > 0 || ks > 0;
-          umma::mma_f16(tb, ah, bh, kId, acc);
-          umma::mma_f16(tb + 64, ah, bl, kId, acc);
-          umma::mma_f16(tb + 64, al, bh, kId, true);
+        for (int i = 0; i < 16; ++i) v[i] = pre[i];
+        if (kc + 1 < nkc) load_chunk(cur, kc + 1, pre);                 // next chunk of this tile ...
+        else if (ntile < ntiles) { nxt = row_info(ntile); load_chunk(nxt, 0, pre); }   // ... or the first of the next
+        const uint32_t b = n & 1;
+        const int ksteps = min(4, m.K16 - 4 * kc);
+        if (n >= 2) wait_commit(n - 2);                                // X buffer b is free again
+        if (cq < ksteps) {
+          const int c0 = 64 * kc + 16 * cq;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[i] = (cur.valid && c0 + i < D) ? v[i] - cur.x0 : 0.0f;
+            s += v[i];
+            q = fmaf(v[i], v[i], q);
+          }
+          store_cols16(sm + m.X + b * kXBuf, r, cq, v);
         }
-        umma::mma_commit(bars + b);
+        umma::fence_async_smem();
+        umma::tc_fence_before();
+        __syncthreads();
+        if (kc == 0 && prev_g >= 0) drain(prev_g, prev_ms, prev_rstd);  // previous tile leaves TMEM before fc1 restarts
+        if (tid == 0) {
+          umma::tc_fence_after();
+          for (int ks = 0; ks < ksteps; ++ks) {
+            const uint32_t ao = sX + b * kXBuf + (uint32_t)ks * 2 * kRowChunk;
+            const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * kWChunk;
+            const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
+            const uint64_t bh = umma::smem_desc(bo, kWChunk, 128), bl = umma::smem_desc(bo + m.w_piece, kWChunk, 128);
+            const bool acc = kc > 0 || ks > 0;
+            umma::mma_f16(tb, ah, bh, kId, acc);
+            umma::mma_f16(tb + 64, ah, bl, kId, acc);
+            umma::mma_f16(tb + 64, al, bh, kId, true);
+          }
+          umma::mma_commit(bars + b);
+        }
+        ++n;
       }
-      ++n;
+      // row statistics (mlp.py:44-45: LayerNorm over in_dim, eps 1e-5) from the sums of d and d^2
+      float ms = 0.0f, rstd = 1.0f;
+      if (L.use_fn) {
+        const float2 tot = row_sum2(s, q, xch, slot, cq, r, q4);
+        ms = tot.x / (float)D;
+        const float var = fmaxf(tot.y / (float)D - ms * ms, 0.0f);
+        rstd = 1.0f / sqrtf(var + kLnEps);
+      }
+      if (cq == 0 && cur.valid && a.xstats) { a.xstats[2 * cur.g] = cur.x0 + ms; a.xstats[2 * cur.g + 1] = rstd; }
+      prev_g = cur.g; prev_ms = ms; prev_rstd = rstd;
+      cur = nxt;
+      tile = ntile;
     }
-    prev_g = g;
+    drain(prev_g, prev_ms, prev_rstd);
   }
-  if (prev_g >= 0) drain(prev_g);
   umma::tc_fence_before();
   __syncthreads();
   if (warp == 0) umma::tmem_dealloc(tb, 128);
@@ -183,7 +218,8 @@ constexpr uint32_t kHChunk = kHR * 16;                     // bytes of one 8-col
 constexpr int kMaxColw = 240;
 constexpr int kXChunksPerThread = 4;                       // ceil(30 chunks / 8 column subsets)
 
-struct WgMap { uint32_t A, B, b_piece, bars, total; };
+constexpr int kStageUnits = 2 * kXChunksPerThread + 2;   // 16-byte units per thread: its x chunks and its dz chunk
+struct WgMap { uint32_t A, B, b_piece, stage, bars, total; };
 __host__ __device__ inline WgMap make_wg_map(int colw) {
   WgMap m;
   uint32_t o = 0;
@@ -191,9 +227,15 @@ __host__ __device__ inline WgMap make_wg_map(int colw) {
   m.A = take(16 * kHChunk);
   m.b_piece = (uint32_t)(colw / 8) * kHChunk;
   m.B = take(2 * m.b_piece);
+  m.stage = take(kStageUnits * kThreads * 16);             // thread-private landing slots of the asynchronous row loads
   m.bars = take(64);
   m.total = o;
   return m;
+}
+
+// 16-byte asynchronous global -> shared copy of `bytes` (0..16) valid bytes, zero-filling the rest
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, int bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(umma::smem_u32(dst)), "l"(src), "r"(bytes) : "memory");
 }
 
 template <bool COLSUM>
@@ -222,6 +264,50 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
 
   float xr[kXChunksPerThread][8], dr[8], mean = 0.0f, rstd = 1.0f;
   bool valid = false;
+  // 16-byte aligned rows: the next half tile's values are copied asynchronously into thread-private shared-memory
+  // slots (unit j of thread t at (j * 512 + t) * 16: conflict-free) the moment the current ones have been read out,
+  // so a whole half tile (80 KB per SM) is in flight behind the conversion and the MMAs.
+  float mean_n = 0.0f, rstd_n = 1.0f;
+  bool valid_n = false;
+  uint4* stage = reinterpret_cast<uint4*>(sm + m.stage) + tid;
+  auto issue_async = [&](long long ht) {
+    const long long g = ht * kHR + hr;
+    valid_n = g < a.rows;
+    const long long srow = valid_n ? (a.index ? a.index[g] / a.x_div : g) : 0;
+    const float* __restrict__ row = a.x + srow * (long long)a.ld;
+    if (a.norm && valid_n) { mean_n = __ldg(a.xstats + 2 * g); rstd_n = __ldg(a.xstats + 2 * g + 1); }
+    else { mean_n = 0.0f; rstd_n = 1.0f; }
+#pragma unroll
+    for (int i = 0; i < kXChunksPerThread; ++i) {
+      const int ch = cs + 8 * i;
+      if (ch < nchx) {
+        const int c = col0 + 8 * ch;
+        const int b0 = valid_n ? max(0, min(4, D - c)) * 4 : 0, b1 = valid_n ? max(0, min(4, D - c - 4)) * 4 : 0;
+        cp_async16(stage + (2 * i) * kThreads, b0 ? row + c : a.x, b0);
+        cp_async16(stage + (2 * i + 1) * kThreads, b1 ? row + c + 4 : a.x, b1);
+      }
+    }
+    const float* dz = a.dz1 + (valid_n ? g : 0) * a.dz_ld + 8 * cs;
+    cp_async16(stage + (2 * kXChunksPerThread) * kThreads, dz, valid_n ? 16 : 0);
+    cp_async16(stage + (2 * kXChunksPerThread + 1) * kThreads, dz + 4, valid_n ? 16 : 0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto take_async = [&]() {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < kXChunksPerThread; ++i) {
+      if (cs + 8 * i < nchx) {
+        const uint4 u0 = stage[(2 * i) * kThreads], u1 = stage[(2 * i + 1) * kThreads];
+        xr[i][0] = __uint_as_float(u0.x); xr[i][1] = __uint_as_float(u0.y); xr[i][2] = __uint_as_float(u0.z); xr[i][3] = __uint_as_float(u0.w);
+        xr[i][4] = __uint_as_float(u1.x); xr[i][5] = __uint_as_float(u1.y); xr[i][6] = __uint_as_float(u1.z); xr[i][7] = __uint_as_float(u1.w);
+      }
+    }
+    const uint4 d0 = stage[(2 * kXChunksPerThread) * kThreads], d1 = stage[(2 * kXChunksPerThread + 1) * kThreads];
+    dr[0] = __uint_as_float(d0.x); dr[1] = __uint_as_float(d0.y); dr[2] = __uint_as_float(d0.z); dr[3] = __uint_as_float(d0.w);
+    dr[4] = __uint_as_float(d1.x); dr[5] = __uint_as_float(d1.y); dr[6] = __uint_as_float(d1.z); dr[7] = __uint_as_float(d1.w);
+    valid = valid_n; mean = mean_n; rstd = rstd_n;
+  };
+  const bool use_async = a.vec && (a.dz_ld & 3) == 0;
   auto prefetch = [&](long long ht) {
     const long long g = ht * kHR + hr;
     valid = g < a.rows;
@@ -251,8 +337,12 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     for (int e = 0; e < 8; ++e) csum[i][e] = 0.0f;
   uint32_t n = 0;
   long long ht = sp;
-  if (ht < nht) prefetch(ht);
+  if (ht < nht) { if (use_async) issue_async(ht); else prefetch(ht); }
   for (; ht < nht; ht += a.nsplit) {
+    if (use_async) {
+      take_async();
+      if (ht + a.nsplit < nht) issue_async(ht + a.nsplit);
+    }
     if (n > 0) umma::mbar_wait(bar, (n - 1) & 1);                       // the operand buffer is free again
     {
       uint4 hi, lo;
@@ -293,7 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       umma::mma_commit(bar);
     }
     ++n;
-    if (ht + a.nsplit < nht) prefetch(ht + a.nsplit);
+    if (!use_async && ht + a.nsplit < nht) prefetch(ht + a.nsplit);
   }
   // ---- G -> the W1 slots of partial rows 2 sp (lanes 0..63: dz1 hi) and 2 sp + 1 (lanes 64..127: dz1 lo, scaled)
   if (n > 0) {
@@ -396,8 +486,8 @@ int launch_wgrad_generic(WideArgs& w, cudaStream_t stream, const char* who) {
   const WgMap m = make_wg_map(w.colw);
   static bool attr_set = false;
   if (!attr_set) {
-    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
-    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set = true;
   }
   if (w.out_b >= 0) wgrad1_wide_kernel<true><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);

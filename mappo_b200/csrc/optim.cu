@@ -6,20 +6,30 @@
 
 namespace mappo {
 
-// column sums over the per-CTA partial rows, fixed order (deterministic)
-__global__ void __launch_bounds__(256)
+// column sums over the per-CTA partial rows, fixed order (deterministic): 8 row slices per column are summed
+// independently (rows s, s + 8, ...) and combined in slice order
+constexpr int kRedSlices = 8, kRedCols = 32;
+__global__ void __launch_bounds__(kRedSlices * kRedCols)
 grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, int blocks, long long P,
                    float* __restrict__ gsum, double* __restrict__ lsum) {
-  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (e < P) {
-    float s = 0.0f;
-    for (int b = 0; b < blocks; ++b) s += gp[(size_t)b * P + e];
-    gsum[e] = s;
+  __shared__ float part[kRedSlices][kRedCols];
+  const int c = threadIdx.x % kRedCols, sl = threadIdx.x / kRedCols;
+  const long long e = blockIdx.x * (long long)kRedCols + c;
+  float s = 0.0f;
+  if (e < P)
+    for (int b = sl; b < blocks; b += kRedSlices) s += gp[(size_t)b * P + e];
+  part[sl][c] = s;
+  __syncthreads();
+  if (sl == 0 && e < P) {
+    float t = part[0][c];
+#pragma unroll
+    for (int q = 1; q < kRedSlices; ++q) t += part[q][c];
+    gsum[e] = t;
   }
   if (blockIdx.x == 0 && threadIdx.x < 4) {
-    double s = 0.0;
-    for (int b = 0; b < blocks; ++b) s += lp[(size_t)b * 4 + threadIdx.x];
-    lsum[threadIdx.x] = s;
+    double t = 0.0;
+    for (int b = 0; b < blocks; ++b) t += lp[(size_t)b * 4 + threadIdx.x];
+    lsum[threadIdx.x] = t;
   }
 }
 
@@ -125,8 +135,8 @@ using namespace mappo;
 extern "C" int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
                                  float* grad_sum, double* loss_sum, void* stream) {
   MAPPO_REQUIRE(grad_partials && loss_partials && grad_sum && loss_sum && blocks > 0 && P > 0, "grad_reduce: bad arguments");
-  grad_reduce_kernel<<<ceil_div(P, 256), 256, 0, (cudaStream_t)stream>>>(grad_partials, loss_partials, blocks, P,
-                                                                       grad_sum, loss_sum);
+  grad_reduce_kernel<<<ceil_div(P, kRedCols), kRedSlices * kRedCols, 0, (cudaStream_t)stream>>>(
+      grad_partials, loss_partials, blocks, P, grad_sum, loss_sum);
   MAPPO_CHECK_LAUNCH("grad_reduce_kernel");
   return 0;
 }
