@@ -356,7 +356,7 @@ struct HeadSmem {
 // MODE 0 actor rollout (sample / evaluate), 1 critic rollout, 2 actor update, 3 critic update.
 // Row g of this launch is position p = g; its sample row is index[g] (update) or g.  h: [rows][64] hidden states.
 template <int MODE>
-__global__ void __launch_bounds__(256, 1) gru_head_kernel(const MlpArgs a, const float* __restrict__ h, float* __restrict__ dh) {
+__global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const float* __restrict__ h, float* __restrict__ dh) {
   constexpr bool UPDATE = (MODE >= 2);
   constexpr int BM = HeadSmem::BM, NT = 256, NTY = NT / 16, RPT = BM / NTY, NQ = (kMaxA * 64 + NT - 1) / NT;
   using S = HeadSmem;
@@ -530,7 +530,7 @@ static int set_attrs() {
 
 static int head_grid(long long rows) {
   const long long nt = (rows + HeadSmem::BM - 1) / HeadSmem::BM;
-  const int g = grid_for(rows);
+  const int g = 2 * grid_for(rows);                       // two CTAs per SM; <= the partial rows of an update
   return (int)(nt < g ? nt : g);
 }
 

@@ -218,8 +218,8 @@ constexpr uint32_t kHChunk = kHR * 16;                     // bytes of one 8-col
 constexpr int kMaxColw = 240;
 constexpr int kXChunksPerThread = 4;                       // ceil(30 chunks / 8 column subsets)
 
-constexpr int kStageUnits = 2 * kXChunksPerThread + 2;   // 16-byte units per thread: its x chunks and its dz chunk
-struct WgMap { uint32_t A, B, b_piece, stage, bars, total; };
+constexpr int kDzStride = 68;                              // floats per staged dz row (64 + 4: conflict-free float4 reads)
+struct WgMap { uint32_t A, B, b_piece, stage, stage_dz, xs_stride, bars, total; };
 __host__ __device__ inline WgMap make_wg_map(int colw) {
   WgMap m;
   uint32_t o = 0;
@@ -227,7 +227,9 @@ __host__ __device__ inline WgMap make_wg_map(int colw) {
   m.A = take(16 * kHChunk);
   m.b_piece = (uint32_t)(colw / 8) * kHChunk;
   m.B = take(2 * m.b_piece);
-  m.stage = take(kStageUnits * kThreads * 16);             // thread-private landing slots of the asynchronous row loads
+  m.xs_stride = (uint32_t)colw + 4;                        // floats per staged x row
+  m.stage = take(kHR * m.xs_stride * 4);                   // landing tiles of the asynchronous, row-coalesced loads: x ...
+  m.stage_dz = take(kHR * kDzStride * 4);                  // ... and dz
   m.bars = take(64);
   m.total = o;
   return m;
@@ -264,48 +266,60 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
 
   float xr[kXChunksPerThread][8], dr[8], mean = 0.0f, rstd = 1.0f;
   bool valid = false;
-  // 16-byte aligned rows: the next half tile's values are copied asynchronously into thread-private shared-memory
-  // slots (unit j of thread t at (j * 512 + t) * 16: conflict-free) the moment the current ones have been read out,
-  // so a whole half tile (80 KB per SM) is in flight behind the conversion and the MMAs.
+  // 16-byte aligned rows: the next half tile is copied asynchronously into shared-memory landing tiles, consecutive
+  // threads fetching consecutive 16-byte units of a row (coalesced: a warp touches 4 lines, not 32), the moment the
+  // current tile has been read out; each thread then picks up its (row, chunk) values from the landing tile.
   float mean_n = 0.0f, rstd_n = 1.0f;
   bool valid_n = false;
-  uint4* stage = reinterpret_cast<uint4*>(sm + m.stage) + tid;
+  float* xs = reinterpret_cast<float*>(sm + m.stage);
+  float* dzs = reinterpret_cast<float*>(sm + m.stage_dz);
+  const int xs_stride = (int)m.xs_stride, upr = colw / 4;     // 16-byte units per staged x row
+  (void)upr;
   auto issue_async = [&](long long ht) {
-    const long long g = ht * kHR + hr;
-    valid_n = g < a.rows;
-    const long long srow = valid_n ? (a.index ? a.index[g] / a.x_div : g) : 0;
-    const float* __restrict__ row = a.x + srow * (long long)a.ld;
-    if (a.norm && valid_n) { mean_n = __ldg(a.xstats + 2 * g); rstd_n = __ldg(a.xstats + 2 * g + 1); }
-    else { mean_n = 0.0f; rstd_n = 1.0f; }
-#pragma unroll
-    for (int i = 0; i < kXChunksPerThread; ++i) {
-      const int ch = cs + 8 * i;
-      if (ch < nchx) {
-        const int c = col0 + 8 * ch;
-        const int b0 = valid_n ? max(0, min(4, D - c)) * 4 : 0, b1 = valid_n ? max(0, min(4, D - c - 4)) * 4 : 0;
-        cp_async16(stage + (2 * i) * kThreads, b0 ? row + c : a.x, b0);
-        cp_async16(stage + (2 * i + 1) * kThreads, b1 ? row + c + 4 : a.x, b1);
+    {
+      const long long g = ht * kHR + hr;
+      valid_n = g < a.rows;
+      if (a.norm && valid_n) { mean_n = __ldg(a.xstats + 2 * g); rstd_n = __ldg(a.xstats + 2 * g + 1); }
+      else { mean_n = 0.0f; rstd_n = 1.0f; }
+    }
+    // warp w fetches rows w, w + 16, ...: the row quantities are warp-uniform, lanes walk the 16-byte units of the row
+    for (int rr = warp; rr < kHR; rr += kThreads / 32) {
+      const long long g = ht * kHR + rr;
+      const bool ok = g < a.rows;
+      const long long srow = ok ? (a.index ? a.index[g] / a.x_div : g) : 0;
+      const float* __restrict__ src = a.x + srow * (long long)a.ld + col0;
+      float* dst = xs + rr * xs_stride;
+      const int lim = ok ? D - col0 : 0;                                // valid floats of this row from col0 on
+      for (int q = lane; q < upr; q += 32) {
+        const int bytes = max(0, min(4, lim - 4 * q)) * 4;
+        cp_async16(dst + 4 * q, bytes ? src + 4 * q : a.x, bytes);
       }
     }
-    const float* dz = a.dz1 + (valid_n ? g : 0) * a.dz_ld + 8 * cs;
-    cp_async16(stage + (2 * kXChunksPerThread) * kThreads, dz, valid_n ? 16 : 0);
-    cp_async16(stage + (2 * kXChunksPerThread + 1) * kThreads, dz + 4, valid_n ? 16 : 0);
+    for (int rr = 2 * warp + (lane >> 4); rr < kHR; rr += 2 * (kThreads / 32)) {
+      const long long g = ht * kHR + rr;
+      const bool ok = g < a.rows;
+      const int q = lane & 15;
+      cp_async16(dzs + rr * kDzStride + 4 * q, a.dz1 + (ok ? g : 0) * a.dz_ld + 4 * q, ok ? 16 : 0);
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   auto take_async = [&]() {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                                                    // everybody's copies have landed
 #pragma unroll
     for (int i = 0; i < kXChunksPerThread; ++i) {
       if (cs + 8 * i < nchx) {
-        const uint4 u0 = stage[(2 * i) * kThreads], u1 = stage[(2 * i + 1) * kThreads];
-        xr[i][0] = __uint_as_float(u0.x); xr[i][1] = __uint_as_float(u0.y); xr[i][2] = __uint_as_float(u0.z); xr[i][3] = __uint_as_float(u0.w);
-        xr[i][4] = __uint_as_float(u1.x); xr[i][5] = __uint_as_float(u1.y); xr[i][6] = __uint_as_float(u1.z); xr[i][7] = __uint_as_float(u1.w);
+        const float4* p = reinterpret_cast<const float4*>(xs + hr * xs_stride + 8 * (cs + 8 * i));
+        const float4 u0 = p[0], u1 = p[1];
+        xr[i][0] = u0.x; xr[i][1] = u0.y; xr[i][2] = u0.z; xr[i][3] = u0.w;
+        xr[i][4] = u1.x; xr[i][5] = u1.y; xr[i][6] = u1.z; xr[i][7] = u1.w;
       }
     }
-    const uint4 d0 = stage[(2 * kXChunksPerThread) * kThreads], d1 = stage[(2 * kXChunksPerThread + 1) * kThreads];
-    dr[0] = __uint_as_float(d0.x); dr[1] = __uint_as_float(d0.y); dr[2] = __uint_as_float(d0.z); dr[3] = __uint_as_float(d0.w);
-    dr[4] = __uint_as_float(d1.x); dr[5] = __uint_as_float(d1.y); dr[6] = __uint_as_float(d1.z); dr[7] = __uint_as_float(d1.w);
+    const float4* p = reinterpret_cast<const float4*>(dzs + hr * kDzStride + 8 * cs);
+    const float4 d0 = p[0], d1 = p[1];
+    dr[0] = d0.x; dr[1] = d0.y; dr[2] = d0.z; dr[3] = d0.w; dr[4] = d1.x; dr[5] = d1.y; dr[6] = d1.z; dr[7] = d1.w;
     valid = valid_n; mean = mean_n; rstd = rstd_n;
+    __syncthreads();                                                    // landing tiles free for the next half tile
   };
   const bool use_async = a.vec && (a.dz_ld & 3) == 0;
   auto prefetch = [&](long long ht) {
