@@ -37,7 +37,8 @@ struct Map {
 // and keep a private one.
 // raw_floats > 0: a landing buffer for the NEXT tile's input rows as one bulk (TMA) copy -- used when the rows of a tile
 // are contiguous in global memory (no gather, row stride = in_dim), so that no thread issues row-divergent loads.
-__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0) {
+// vhead: scalar (value) head whose weight gradient accumulates in registers: no n2 / dlogits operand tiles.
+__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0, bool vhead = false) {
   Map m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
@@ -46,10 +47,10 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.X = take(2 * kNP * m.x_piece);                 // two buffers: this tile's rows and the next tile's
   m.N1 = take(kNP * 8 * kRowChunk);
   m.BS = take(update ? kNP * 8 * kRowChunk : 0);    // dz2, then dz1
-  m.BS2 = take(update ? kNP * 8 * kRowChunk : 0);   // n2 (operand of the head weight gradient)
+  m.BS2 = take(update && !vhead ? kNP * 8 * kRowChunk : 0);   // n2 (operand of the head weight gradient)
   m.W1 = take(kNP * m.w1_piece);
   m.W2 = take(kNP * 8 * kWChunk);
-  m.DL = take(update ? kNP * 2 * kRowChunk : 0);
+  m.DL = take(update && !vhead ? kNP * 2 * kRowChunk : 0);
   m.Whf = take(kMaxA * 64 * 4);
   m.b1f = take(64 * 4);
   m.b2f = take(64 * 4);
@@ -58,7 +59,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.xch = take(2 * 4 * kBM * 8);
   m.xlog_in_x = (update && (uint32_t)(4 * kBM * AS * 4) <= kNP * m.x_piece) ? 1 : 0;
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
-  m.red = take(16 * 16 * 4 * 2);
+  m.red = take(16 * 16 * 4 * 3);
   m.bars = take(64);
   m.raw = take((uint32_t)raw_floats * 4);
   m.total = o;
@@ -285,12 +286,13 @@ template <int MODE, int KP, int AMAX, bool WIDE>
 __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE == 2 || MODE == 3 || MODE == 5);
   constexpr bool HEAD = (MODE < 4);
+  constexpr bool VHEAD = (MODE == 3);                                  // critic update: head gradient in registers
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
   const NetLayout& L = a.L;
   const int A = L.a_total, relu = L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0);
+  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
@@ -347,11 +349,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   uint32_t ph = 0;
   int buf = 0;
   bool first = true;
-  float db1[16], db2[16];
+  float db1[16], db2[16], ghv[VHEAD ? 16 : 1];
   double lacc[4] = {0.0, 0.0, 0.0, 0.0};
   if (UPDATE) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) db1[i] = db2[i] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < (VHEAD ? 16 : 1); ++i) ghv[i] = 0.0f;
   }
 
   for (; tile < a.ntiles; tile += gridDim.x) {
@@ -398,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::tc_fence_after();
     load_acc16(lane_addr, cq, n2);
     act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
-    if (UPDATE && HEAD) store_cols16(sm + m.BS2, r, cq, n2);
+    if (UPDATE && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
     if (MODE == 4 && valid) {
       float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
 #pragma unroll
@@ -491,15 +495,21 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
           d16[q] = (q < AMAX) ? dl[q < AMAX ? q : 0] : 0.0f;
           if (q < AMAX && q < A) dbh[q] += d16[q];
         }
+        if (!VHEAD) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint4 hi, lo;
-          split8(d16 + 8 * h, hi, lo);
-          const uint32_t off = (uint32_t)h * kRowChunk + (uint32_t)r * 16;
-          *reinterpret_cast<uint4*>(sm + m.DL + off) = hi;
-          *reinterpret_cast<uint4*>(sm + m.DL + 2 * kRowChunk + off) = lo;
+          for (int h = 0; h < 2; ++h) {
+            uint4 hi, lo;
+            split8(d16 + 8 * h, hi, lo);
+            const uint32_t off = (uint32_t)h * kRowChunk + (uint32_t)r * 16;
+            *reinterpret_cast<uint4*>(sm + m.DL + off) = hi;
+            *reinterpret_cast<uint4*>(sm + m.DL + 2 * kRowChunk + off) = lo;
+          }
         }
       }
+    }
+    if (VHEAD) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) ghv[i] = fmaf(dl[0], n2[i], ghv[i]);      // G_v[k] += dv n2[k]
     }
     // ---- back through the head and layer 2
     float dz[16];
@@ -531,7 +541,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (tid == 0) {
       umma::tc_fence_after();
-      if (HEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
+      if (HEAD && !VHEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
       issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
@@ -584,6 +594,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) { v1 += __shfl_xor_sync(0xffffffffu, v1, o); v2 += __shfl_xor_sync(0xffffffffu, v2, o); }
       if (lane == 0) { red[warp * 16 + i] = v1; red[256 + warp * 16 + i] = v2; }
+      if (VHEAD) {
+        float v3 = ghv[VHEAD ? i : 0];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v3 += __shfl_xor_sync(0xffffffffu, v3, o);
+        if (lane == 0) red[512 + warp * 16 + i] = v3;
+      }
     }
     __syncthreads();                                                      // zero fill + red visible
     float* __restrict__ gp = gp0 + (size_t)(q4 >> 1) * L.total;
@@ -604,7 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
           if (k < D) gp[L.w1 + mrow * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
         }
       }
-      if (HEAD && cq == 3) {                                              // warps 12..15: head gradient, lanes = hidden unit
+      if (HEAD && !VHEAD && cq == 3) {                                    // warps 12..15: head gradient, lanes = hidden unit
         umma::tmem_ld16(lane_addr + kColGh, u);
         umma::tmem_ld16(lane_addr + kColGh + 16, w);
         int h = 0, off = 0;
@@ -622,6 +638,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       float s1 = 0.0f, s2 = 0.0f;
       for (int q = 0; q < 4; ++q) { s1 += red[(4 * c + q) * 16 + i]; s2 += red[256 + (4 * c + q) * 16 + i]; }
       gp0[L.b1 + tid] = s1; gp0[L.b2 + tid] = s2;
+      if (VHEAD) {
+        float s3 = 0.0f;
+        for (int q = 0; q < 4; ++q) s3 += red[512 + (4 * c + q) * 16 + i];
+        gp0[L.wh[0] + tid] = s3;
+      }
     } else if (HEAD && tid < 64 + A) {
       const int q = tid - 64;
       const float* dbh = reinterpret_cast<const float*>(sm + m.dbh);
@@ -690,9 +711,9 @@ static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
   // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
   a.raw_ok = 0;
   if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && (reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 &&
-      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim).total <= (uint32_t)kMaxDynSmem)
+      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3).total <= (uint32_t)kMaxDynSmem)
     a.raw_ok = 1;
-  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0);
+  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3);
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE>;
   static bool attr_set = false;
   if (!attr_set) {
