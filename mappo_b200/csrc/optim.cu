@@ -46,15 +46,29 @@ __device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const
   }
   for (int j = tid; j < rows; j += kOptThreads) out[b_off + j] = G[b_off + j];
   if (g_off >= 0) {
-    for (int k = tid; k < cols; k += kOptThreads) {
+    // 64 columns at a time, 16 row slices per column (rows s, s + 16, ...), combined in slice order
+    __shared__ float pdg[16][64], pdbe[16][64];
+    const int kk = tid & 63, sl = tid >> 6;
+    for (int k0 = 0; k0 < cols; k0 += 64) {
+      const int k = k0 + kk;
       float dg = 0.0f, dbe = 0.0f;
-      for (int j = 0; j < rows; ++j) {
-        const float w = P[w_off + j * cols + k];
-        dg = fmaf(w, G[w_off + j * cols + k], dg);
-        dbe = fmaf(w, G[b_off + j], dbe);
+      if (k < cols) {
+        for (int j = sl; j < rows; j += 16) {
+          const float w = P[w_off + j * cols + k];
+          dg = fmaf(w, G[w_off + j * cols + k], dg);
+          dbe = fmaf(w, G[b_off + j], dbe);
+        }
       }
-      if (accumulate_affine) { out[g_off + k] += dg; out[be_off + k] += dbe; }
-      else { out[g_off + k] = dg; out[be_off + k] = dbe; }
+      pdg[sl][kk] = dg; pdbe[sl][kk] = dbe;
+      __syncthreads();
+      if (sl == 0 && k < cols) {
+        float a = pdg[0][kk], b = pdbe[0][kk];
+#pragma unroll
+        for (int q = 1; q < 16; ++q) { a += pdg[q][kk]; b += pdbe[q][kk]; }
+        if (accumulate_affine) { out[g_off + k] += a; out[be_off + k] += b; }
+        else { out[g_off + k] = a; out[be_off + k] = b; }
+      }
+      __syncthreads();
     }
   }
 }
