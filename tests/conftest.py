@@ -9,6 +9,13 @@ if ROOT not in sys.path:
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+# The oracle (torch CPU fp32) is the checker: keep it single-threaded.  With the intra-op pool of the B200 box's host
+# (16 threads) one worker's ~32-row slice of a 700-row batch came out ~1e-4 off in about one process in eight
+# (tools/flake_probe.py: the GPU output hash is identical in every process, the oracle's is not).
+import torch  # noqa: E402
+
+torch.set_num_threads(1)
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
