@@ -14,6 +14,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 # (tools/flake_probe.py: the GPU output hash is identical in every process, the oracle's is not).
 import torch  # noqa: E402
 
+DEFAULT_TORCH_THREADS = torch.get_num_threads()
 torch.set_num_threads(1)
 
 

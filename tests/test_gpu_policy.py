@@ -134,8 +134,15 @@ def test_reference_init_is_bit_identical(golden_dir):
     args = types.SimpleNamespace(**a)
     args.use_recurrent_policy = args.use_naive_recurrent_policy = False
     args.recurrent_N = 1; args.use_popart = False; args.use_orthogonal = True; args.seed = 1
-    torch.manual_seed(3)
-    pol = R_MAPPOPolicy(args, make_space(18), make_space(54), Discrete(5), device="cuda")
+    # orthogonal_ runs LAPACK's QR, whose blocking (and so the last bits) follows the intra-op thread count: use the
+    # multi-threaded default the fixture was recorded with, not the single thread the oracle checks run on
+    from conftest import DEFAULT_TORCH_THREADS
+    torch.set_num_threads(max(2, DEFAULT_TORCH_THREADS))
+    try:
+        torch.manual_seed(3)
+        pol = R_MAPPOPolicy(args, make_space(18), make_space(54), Discrete(5), device="cuda")
+    finally:
+        torch.set_num_threads(1)
     for net, pre in ((pol.actor, "actor0."), (pol.critic, "critic0.")):
         sd = net.state_dict()
         for k in ("base.mlp.fc1.0.weight", "base.mlp.fc2.0.0.weight", "base.mlp.fc_h.0.weight"):
