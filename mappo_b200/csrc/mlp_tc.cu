@@ -113,35 +113,45 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
   for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
 }
 
-// ---- MMA issue (one thread) ------------------------------------------------------------------------------
+// ---- MMA issue (one elected thread) ---------------------------------------------------------------------
+// Operand addresses and strides arrive in 16-BYTE UNITS (shared-memory base >> 4 plus compile-time offsets), so a
+// descriptor costs one uniform add (umma::smem_desc16).
+constexpr uint32_t kRowChunk16 = kRowChunk >> 4, kWChunk16 = kWChunk >> 4;
 // forward-type GEMM: ACC0[128][64] = A_hi . B_hi^T, ACC1 = A_hi . B_lo^T + A_lo . B_hi^T; A K-major 128-row tile
-__device__ __forceinline__ void issue_rowgemm(uint32_t acc0, uint32_t acc1, uint32_t a_base, uint32_t a_piece,
-                                              uint32_t b_base, uint32_t b_piece, uint32_t b_lbo, uint32_t b_sbo,
-                                              uint32_t b_kstep, int ksteps, uint32_t idesc) {
-  for (int ks = 0; ks < ksteps; ++ks) {
-    const uint32_t ao = a_base + (uint32_t)ks * 2 * kRowChunk, bo = b_base + (uint32_t)ks * b_kstep;
-    const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + a_piece, kRowChunk, 128);
-    const uint64_t bh = umma::smem_desc(bo, b_lbo, b_sbo), bl = umma::smem_desc(bo + b_piece, b_lbo, b_sbo);
+template <int KSTEPS>
+__device__ __forceinline__ void issue_rowgemm(uint32_t acc0, uint32_t acc1, uint32_t a16, uint32_t a_piece16,
+                                              uint32_t b16, uint32_t b_piece16, uint32_t b_lbo, uint32_t b_sbo,
+                                              uint32_t b_kstep16, uint32_t idesc) {
+#pragma unroll
+  for (int ks = 0; ks < KSTEPS; ++ks) {
+    const uint32_t ao = a16 + (uint32_t)ks * 2 * kRowChunk16, bo = b16 + (uint32_t)ks * b_kstep16;
+    const uint64_t ah = umma::smem_desc16(ao, kRowChunk, 128), al = umma::smem_desc16(ao + a_piece16, kRowChunk, 128);
+    const uint64_t bh = umma::smem_desc16(bo, b_lbo, b_sbo), bl = umma::smem_desc16(bo + b_piece16, b_lbo, b_sbo);
     umma::mma_f16(acc0, ah, bh, idesc, ks > 0);
     umma::mma_f16(acc1, ah, bl, idesc, ks > 0);
     umma::mma_f16(acc1, al, bh, idesc, true);
   }
 }
 // weight-gradient GEMM: G[128 = (hi cols | lo cols) of A][N] += A^T . B over the 128 tile rows; both MN-major
-__device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a_base, uint32_t b_base, uint32_t idesc, bool accum) {
+__device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a16, uint32_t b16, uint32_t idesc, bool accum) {
 #pragma unroll
   for (int ks = 0; ks < kBM / 16; ++ks) {
-    const uint64_t da = umma::smem_desc(a_base + (uint32_t)ks * 256, 128, kRowChunk);
-    const uint64_t db = umma::smem_desc(b_base + (uint32_t)ks * 256, 128, kRowChunk);
+    const uint64_t da = umma::smem_desc16(a16 + (uint32_t)ks * 16, 128, kRowChunk);
+    const uint64_t db = umma::smem_desc16(b16 + (uint32_t)ks * 16, 128, kRowChunk);
     umma::mma_f16(g, da, db, idesc, accum || ks > 0);
   }
 }
 
 // this thread's 16 accumulator columns: acc0 + 2^-12 acc1
+// DUAL: both blocks in flight under one wait (16 more live registers for the duration of the load)
+template <bool DUAL>
 __device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16]) {
   float w[16];
-  umma::tmem_ld16(lane_addr + kColAcc + 16 * cq, v);
-  umma::tmem_ld16(lane_addr + kColAcc1 + 16 * cq, w);
+  if (DUAL) umma::tmem_ld16x2(lane_addr + kColAcc + 16 * cq, lane_addr + kColAcc1 + 16 * cq, v, w);
+  else {
+    umma::tmem_ld16(lane_addr + kColAcc + 16 * cq, v);
+    umma::tmem_ld16(lane_addr + kColAcc1 + 16 * cq, w);
+  }
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
 }
@@ -328,13 +338,16 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   umma::tc_fence_before();
   __syncthreads();
   umma::tc_fence_after();
-  if (tid == 0) issue_bulk(tile + gridDim.x);
+  // MMA groups are issued by one elected lane of warps 0 / 1 / 2 (three different schedulers) in turn
+  const bool issuer_fc2 = (warp == 0), issuer_bwd = (warp == 1), issuer_next = (warp == 2);
+  if (issuer_next && umma::elect_one()) issue_bulk(tile + gridDim.x);
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
   const uint32_t x_bytes = kNP * m.x_piece;
-  const uint32_t sX = umma::smem_u32(sm + m.X), sN1 = umma::smem_u32(sm + m.N1), sBS = umma::smem_u32(sm + m.BS);
-  const uint32_t sB2 = umma::smem_u32(sm + m.BS2), sW1 = umma::smem_u32(sm + m.W1), sW2 = umma::smem_u32(sm + m.W2);
-  const uint32_t sDL = umma::smem_u32(sm + m.DL);
+  const uint32_t b16 = umma::smem_u32(sm) >> 4;                         // operand addresses in 16-byte units
+  const uint32_t sX = b16 + (m.X >> 4), sN1 = b16 + (m.N1 >> 4), sBS = b16 + (m.BS >> 4), sB2 = b16 + (m.BS2 >> 4);
+  const uint32_t sW1 = b16 + (m.W1 >> 4), sW2 = b16 + (m.W2 >> 4), sDL = b16 + (m.DL >> 4);
+  const uint32_t x_piece16 = m.x_piece >> 4, w1_piece16 = m.w1_piece >> 4, x_bytes16 = x_bytes >> 4;
   const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
   const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
   const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
@@ -342,8 +355,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
-  if (tid == 0 && !WIDE) {
-    issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX, m.x_piece, sW1, m.w1_piece, kWChunk, 128, 2 * kWChunk, KP / 16, kIdFwd);
+  if (!WIDE && issuer_next && umma::elect_one()) {
+    issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
     umma::mma_commit(bar);
   }
   uint32_t ph = 0;
@@ -364,10 +377,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     const bool has_next = tile + gridDim.x < a.ntiles;
     const long long src = (valid && a.index) ? a.index[g] : (valid ? g : 0);
     // per-row scalars of the register loss path, requested now and consumed after the second layer
-    int p_act = 0;
+    float p_actf = 0.0f;                              // converted at its use: no wait on the load up here
     float p_old = 0.0f, p_adv = 0.0f, p_active = 1.0f;
     if (MODE == 2 && AMAX == 8 && valid) {
-      p_act = (int)__ldg(a.actions + src);
+      p_actf = __ldg(a.actions + src);
       p_old = __ldg(a.old_logp + src);
       p_adv = __ldg(a.adv + src);
       if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
@@ -384,23 +397,23 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     } else {
       umma::mbar_wait(bar, ph); ph ^= 1;
       umma::tc_fence_after();
-      load_acc16(lane_addr, cq, n1);
+      load_acc16<!VHEAD>(lane_addr, cq, n1);
     }
     act_ln16(n1, b1f, relu, xch, slot, cq, r, q4, mean1, rstd1);
     store_cols16(sm + m.N1, r, cq, n1);
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (issuer_fc2 && umma::elect_one()) {
       umma::tc_fence_after();
-      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk, sW2, 8 * kWChunk, kWChunk, 128, 2 * kWChunk, 4, kIdFwd);
+      issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk16, sW2, 8 * kWChunk16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
       umma::mma_commit(bar);
     }
     // ---- layer 2 epilogue + head
     float n2[16], mean2, rstd2;
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
-    load_acc16(lane_addr, cq, n2);
+    load_acc16<!VHEAD>(lane_addr, cq, n2);
     act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
     if (UPDATE && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
     if (MODE == 4 && valid) {
@@ -445,11 +458,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::fence_async_smem();
       umma::tc_fence_before();
       __syncthreads();
-      if (tid == 0 && has_next) {
+      if (has_next && issuer_next && umma::elect_one()) {
         issue_bulk(tile + 2 * (long long)gridDim.x);
         umma::tc_fence_after();
-        issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
-                      2 * kWChunk, KP / 16, kIdFwd);
+        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+                               128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(bar);
       }
       buf ^= 1;
@@ -464,7 +477,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       double mine[4] = {0.0, 0.0, 0.0, 0.0};
       if (MODE == 2 && AMAX == 8) {
         float sums[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-        if (valid) actor_loss_regs<AMAX>(a.loss, A, l, p_act, p_old, p_adv, p_active, dl, sums);
+        if (valid) actor_loss_regs<AMAX>(a.loss, A, l, (int)p_actf, p_old, p_adv, p_active, dl, sums);
         else {
 #pragma unroll
           for (int q = 0; q < AMAX; ++q) dl[q] = 0.0f;
@@ -539,11 +552,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (issuer_bwd && umma::elect_one()) {
       umma::tc_fence_after();
       if (HEAD && !VHEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
-      issue_rowgemm(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk, sW2, 8 * kWChunk, 128, kWChunk, 256, 4, kIdDgrad);
+      issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
     }
     // ---- next tile's input rows, staged while the tensor cores work
@@ -551,7 +564,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
-    load_acc16(lane_addr, cq, dz);
+    load_acc16<!VHEAD>(lane_addr, cq, dz);
     ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
 #pragma unroll
     for (int i = 0; i < 16; ++i) db1[i] += dz[i];
@@ -568,13 +581,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (issuer_next && umma::elect_one()) {
       umma::tc_fence_after();
       if (has_next) issue_bulk(tile + 2 * (long long)gridDim.x);
-      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes, kIdG1, !first);                        // G1 += dz1^T x
+      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);                      // G1 += dz1^T x
       if (has_next)
-        issue_rowgemm(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes, m.x_piece, sW1, m.w1_piece, kWChunk, 128,
-                      2 * kWChunk, KP / 16, kIdFwd);
+        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+                               128, 2 * kWChunk16, kIdFwd);
       umma::mma_commit(bar);
     }
     buf ^= 1;

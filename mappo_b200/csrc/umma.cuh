@@ -59,9 +59,22 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 // ---- descriptors ---------------------------------------------------------------------------------------
 // shared-memory matrix descriptor, no swizzle (cute::UMMA::SmemDescriptor: start[0,14) LBO[16,30) SBO[32,46)
 // version[46,48) = 1, layout_type[61,64) = 0), all byte quantities >> 4
+// (no field masks: shared-memory addresses are < 256 KB and the strides < 256 KB, so every field fits its 14 bits;
+// without the masks the compiler folds a descriptor into one or two uniform-datapath instructions)
 __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
-         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46);
+  return (uint64_t)((saddr >> 4) + ((lbo_bytes >> 4) << 16)) | ((uint64_t)((sbo_bytes >> 4) | (1u << 14)) << 32);
+}
+// same, from an address that is already in 16-byte units (base >> 4 computed once, offsets added as constants)
+__device__ __forceinline__ uint64_t smem_desc16(uint32_t addr16, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)(addr16 + ((lbo_bytes >> 4) << 16)) | ((uint64_t)((sbo_bytes >> 4) | (1u << 14)) << 32);
+}
+// one elected lane of a CONVERGED warp (call under a warp-uniform condition).  Issuing tcgen05.mma / commit / bulk
+// copies under `warp == w && elect_one()` instead of `tid == 0` lets the compiler emit them straight on the uniform
+// datapath; under a per-thread condition it wraps every one of them in an ELECT / BRA.U.ANY serialisation loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 // instruction descriptor for kind::tf32, fp32 accumulate (cute::UMMA::InstrDescriptor)
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
@@ -111,17 +124,31 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
 }
 
 // ---- TMEM -> registers: this warp's 32 lanes (lane field of taddr = 32 * (warp % 4)), 16 consecutive columns
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-  uint32_t r[16];
+// asynchronous form: the registers are valid only after tmem_ld_wait()
+__device__ __forceinline__ void tmem_ld16_async(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr)
       : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  tmem_ld16_async(taddr, r);
+  tmem_ld_wait();
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+// two 16-column blocks in flight under one wait
+__device__ __forceinline__ void tmem_ld16x2(uint32_t taddr0, uint32_t taddr1, float (&v)[16], float (&w)[16]) {
+  uint32_t r0[16], r1[16];
+  tmem_ld16_async(taddr0, r0);
+  tmem_ld16_async(taddr1, r1);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { v[i] = __uint_as_float(r0[i]); w[i] = __uint_as_float(r1[i]); }
 }
 
 // ---- operand tiles ---------------------------------------------------------------------------------------
