@@ -26,7 +26,7 @@ constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 256, kColG
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
-  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, bhf, dbh, xch, xlog, red, bars, raw, total;
+  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, b1s, b2s, bhf, dbh, xch, xlog, red, bars, raw, total;
   uint32_t x_piece, w1_piece;
   int xlog_in_x;                 // 1: the head's partial logits live in the idle X buffer (see below), `xlog` unused
 };
@@ -54,6 +54,8 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.Whf = take(kMaxA * 64 * 4);
   m.b1f = take(64 * 4);
   m.b2f = take(64 * 4);
+  m.b1s = take(64 * 4);                             // biases times 2 log2(e): tanh straight from the accumulator
+  m.b2s = take(64 * 4);
   m.bhf = take(kMaxA * 4);
   m.dbh = take(update ? kBM * AS * 4 : 0);
   m.xch = take(2 * 4 * kBM * 8);
@@ -95,9 +97,11 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     float s1 = P[L.b1 + j];
     if (L.use_fn) for (int k = 0; k < D; ++k) s1 = fmaf(P[L.w1 + j * D + k], P[L.fn_b + k], s1);
     reinterpret_cast<float*>(sm + m.b1f)[j] = s1;
+    reinterpret_cast<float*>(sm + m.b1s)[j] = s1 * kTanhScale;
     float s2 = P[L.b2 + j];
     for (int k = 0; k < 64; ++k) s2 = fmaf(P[L.w2 + j * 64 + k], P[L.be1 + k], s2);
     reinterpret_cast<float*>(sm + m.b2f)[j] = s2;
+    reinterpret_cast<float*>(sm + m.b2s)[j] = s2 * kTanhScale;
   } else if (tid < 64 + kMaxA) {
     const int aidx = tid - 64;
     int h = 0, off = 0;
@@ -156,13 +160,15 @@ __device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v
   for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
 }
 
-// activation -> LayerNorm (no affine) of this thread's 16 columns; returns n in t[], (mean, rstd) of the row
-__device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict__ bias, int relu, float2* xch, int& slot,
-                                         int cq, int r, int q4, float& mean, float& rstd) {
+// activation -> LayerNorm (no affine) of this thread's 16 columns; returns n in t[], (mean, rstd) of the row.
+// tanh takes its argument pre-scaled: 2 log2(e) (z + b) = fma(z, 2 log2(e), bias_s) with bias_s = 2 log2(e) b, so the
+// bias add and the scaling are one FFMA; the normalisation is one FFMA per element, n = fma(t, rstd, -mean rstd).
+__device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict__ bias, const float* __restrict__ bias_s,
+                                         int relu, float2* xch, int& slot, int cq, int r, int q4, float& mean, float& rstd) {
   float s = 0.0f, q = 0.0f;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    t[i] = act_tc(t[i] + bias[i], relu);
+    t[i] = relu ? fmaxf(t[i] + bias[i], 0.0f) : tanh_scaled(fmaf(t[i], kTanhScale, bias_s[i]));
     s += t[i];
     q = fmaf(t[i], t[i], q);
   }
@@ -170,25 +176,27 @@ __device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict
   mean = tot.x * (1.0f / 64.0f);
   const float var = fmaxf(fmaf(-mean, mean, tot.y * (1.0f / 64.0f)), 0.0f);
   rstd = 1.0f / sqrtf(var + kLnEps);
+  const float nmr = -(mean * rstd);
 #pragma unroll
-  for (int i = 0; i < 16; ++i) t[i] = (t[i] - mean) * rstd;
+  for (int i = 0; i < 16; ++i) t[i] = fmaf(t[i], rstd, nmr);
 }
 
-// dn (gradient w.r.t. the LayerNorm output n) -> dz (gradient w.r.t. the pre-activation), in place
+// dn (gradient w.r.t. the LayerNorm output n) -> dz (gradient w.r.t. the pre-activation), in place:
+// dz = rstd (dn - mean(dn) - n mean(dn n)) act'(z), with rstd folded into the two FFMAs
 __device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[16], float mean, float rstd, int relu,
                                              float2* xch, int& slot, int cq, int r, int q4) {
   float s1 = 0.0f, s2 = 0.0f;
 #pragma unroll
   for (int i = 0; i < 16; ++i) { s1 += dn[i]; s2 = fmaf(dn[i], n[i], s2); }
   const float2 tot = row_sum2(s1, s2, xch, slot, cq, r, q4);
-  s1 = tot.x * (1.0f / 64.0f); s2 = tot.y * (1.0f / 64.0f);
-  const float sd = 1.0f / rstd, nz = (0.0f - mean) * rstd;
+  const float rs1 = -(tot.x * (1.0f / 64.0f)) * rstd, rs2 = -(tot.y * (1.0f / 64.0f)) * rstd;
+  const float sd = 1.0f / rstd, nz = -(mean * rstd);
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
     float da;
-    if (relu) da = (n[i] != nz) ? 1.0f : 0.0f;            // t == 0  <=>  n == (0 - mean) * rstd, bit for bit
+    if (relu) da = (n[i] != nz) ? 1.0f : 0.0f;            // t == 0  <=>  n == fma(0, rstd, -mean rstd), bit for bit
     else { const float t = fmaf(n[i], sd, mean); da = fmaf(-t, t, 1.0f); }
-    dn[i] = rstd * (dn[i] - s1 - n[i] * s2) * da;
+    dn[i] = fmaf(n[i], rs2, fmaf(dn[i], rstd, rs1)) * da;
   }
 }
 
@@ -292,7 +300,8 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
 // the NEXT tile} -- so there are three CTA-wide synchronisations per tile; the next tile's input rows are staged
 // into the second X buffer while the second group runs on the tensor cores.
 // WIDE: the first layer lives outside (mlp_wide.cu): z1 rows come from a.z1 and dLoss/dz1 goes back in place.
-template <int MODE, int KP, int AMAX, bool WIDE>
+// AFIX > 0: the head has exactly AFIX logits (compile-time loop bounds); ACT: 0 tanh, 1 ReLU, -1 read it from the layout.
+template <int MODE, int KP, int AMAX, bool WIDE, int AFIX, int ACT>
 __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE == 2 || MODE == 3 || MODE == 5);
   constexpr bool HEAD = (MODE < 4);
@@ -301,7 +310,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
   const NetLayout& L = a.L;
-  const int A = L.a_total, relu = L.use_relu, D = L.in_dim, AS = A | 1;
+  const int A = AFIX > 0 ? AFIX : L.a_total, relu = ACT >= 0 ? ACT : L.use_relu, D = L.in_dim, AS = A | 1;
   const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
@@ -351,6 +360,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
   const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
   const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
+  const float* b1s = reinterpret_cast<const float*>(sm + m.b1s) + 16 * cq;
+  const float* b2s = reinterpret_cast<const float*>(sm + m.b2s) + 16 * cq;
   const float* bhf = reinterpret_cast<const float*>(sm + m.bhf);
   constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
@@ -399,7 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::tc_fence_after();
       load_acc16<!VHEAD>(lane_addr, cq, n1);
     }
-    act_ln16(n1, b1f, relu, xch, slot, cq, r, q4, mean1, rstd1);
+    act_ln16(n1, b1f, b1s, relu, xch, slot, cq, r, q4, mean1, rstd1);
     store_cols16(sm + m.N1, r, cq, n1);
     umma::fence_async_smem();
     umma::tc_fence_before();
@@ -414,7 +425,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
     load_acc16<!VHEAD>(lane_addr, cq, n2);
-    act_ln16(n2, b2f, relu, xch, slot, cq, r, q4, mean2, rstd2);
+    act_ln16(n2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
     if (UPDATE && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
     if (MODE == 4 && valid) {
       float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
@@ -718,8 +729,8 @@ bool supports(const mappo_net_config* cfg) {
   return make_map(Kp, A | 1, true).total <= (uint32_t)kMaxDynSmem && make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
-template <int MODE, int KP, int AMAX, bool WIDE = false>
-static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
+template <int MODE, int KP, int AMAX, bool WIDE, int AFIX, int ACT>
+static int launch_inst(MlpArgs& a, cudaStream_t stream, const char* who) {
   constexpr bool kUpd = (MODE == 2 || MODE == 3 || MODE == 5);
   // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
   a.raw_ok = 0;
@@ -727,7 +738,7 @@ static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
       make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3).total <= (uint32_t)kMaxDynSmem)
     a.raw_ok = 1;
   const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3);
-  auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE>;
+  auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE, AFIX, ACT>;
   static bool attr_set = false;
   if (!attr_set) {
     MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
@@ -737,6 +748,19 @@ static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
   kern<<<grid_for(a.rows), kThreads, m.total, stream>>>(a);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
+}
+
+// the common shapes get compile-time loop bounds and activation: tanh (the reference scripts' setting)
+// and, for a single categorical head, exactly 5 logits (every moving MPE agent); everything else takes the generic build
+template <int MODE, int KP, int AMAX, bool WIDE = false>
+static int launch_one(MlpArgs& a, cudaStream_t stream, const char* who) {
+  if constexpr (AMAX == 8) {
+    if (!a.L.use_relu && a.L.a_total == 5) return launch_inst<MODE, KP, AMAX, WIDE, 5, 0>(a, stream, who);
+  }
+  if constexpr (AMAX == 1) {
+    if (!a.L.use_relu) return launch_inst<MODE, KP, AMAX, WIDE, 0, 0>(a, stream, who);
+  }
+  return launch_inst<MODE, KP, AMAX, WIDE, 0, -1>(a, stream, who);
 }
 
 template <int MODE>

@@ -25,6 +25,14 @@ __device__ __forceinline__ float tanh_fast(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
   return copysignf(fmaf(-2.0f, r, 1.0f), x);
 }
+// the same from a pre-scaled argument y = 2 log2(e) x
+constexpr float kTanhScale = 2.885390081777927f;
+__device__ __forceinline__ float tanh_scaled(float y) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fabsf(y)));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+  return copysignf(fmaf(-2.0f, r, 1.0f), y);
+}
 __device__ __forceinline__ float act_tc(float z, int relu) { return relu ? fmaxf(z, 0.0f) : tanh_fast(z); }
 
 // 8 consecutive fp32 -> one 16-byte chunk of fp16 `hi` and one of (scaled) `lo`
