@@ -296,9 +296,11 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
 // KP: padded input width (32 | 64).
 // AMAX: register width of the head (1 critic; 8 = single categorical head with <= 8 logits and no availability
 // mask, losses evaluated in registers; 16 = generic heads through the row functions of mlp_rows.cuh).
-// Per tile the update issues three groups of MMAs -- {fc2}, {head wgrad, fc2 wgrad, fc2 dgrad}, {fc1 wgrad, fc1 of
-// the NEXT tile} -- so there are three CTA-wide synchronisations per tile; the next tile's input rows are staged
-// into the second X buffer while the second group runs on the tensor cores.
+// Per tile the update issues three groups of MMAs -- {fc2}, {fc2 dgrad | head wgrad, fc2 wgrad}, {fc1 of the NEXT
+// tile | fc1 wgrad} -- so there are three CTA-wide synchronisations per tile.  Inside a group the MMAs whose result
+// the threads wait for come first and commit to `bar`; the weight gradients behind them commit to `gbar`, which is
+// only waited for where one of their operand buffers is about to be overwritten (they run in the background).  The
+// next tile's input rows are staged into the second X buffer while the second group runs on the tensor cores.
 // WIDE: the first layer lives outside (mlp_wide.cu): z1 rows come from a.z1 and dLoss/dz1 goes back in place.
 // AFIX > 0: the head has exactly AFIX logits (compile-time loop bounds); ACT: 0 tanh, 1 ReLU, -1 read it from the layout.
 template <int MODE, int KP, int AMAX, bool WIDE, int AFIX, int ACT>
@@ -316,7 +318,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
   uint64_t* tbar = bar + 1;                                           // arrival of a bulk-copied input tile
-  if (tid == 0) { umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::fence_mbar_init(); }
+  uint64_t* gbar = bar + 2;                                           // completion of the weight-gradient MMAs (background)
+  if (tid == 0) { umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::mbar_init(gbar, 1); umma::fence_mbar_init(); }
   const float* raw = reinterpret_cast<const float*>(sm + m.raw);
   const uint32_t raw_bytes = (uint32_t)(kBM * D) * 4u;
   uint32_t tph = 0;
@@ -370,7 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
     umma::mma_commit(bar);
   }
-  uint32_t ph = 0;
+  uint32_t ph = 0, gph = 0;
   int buf = 0;
   bool first = true;
   float db1[16], db2[16], ghv[VHEAD ? 16 : 1];
@@ -399,6 +402,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- layer 1 epilogue
     float n1[16], mean1, rstd1;
     if (WIDE) {
+      if (UPDATE && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }     // previous tile's G2 still reads N1 / BS
       const float4* zp = reinterpret_cast<const float4*>(a.z1 + g * 64 + 16 * cq);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -423,6 +427,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- layer 2 epilogue + head
     float n2[16], mean2, rstd2;
     umma::mbar_wait(bar, ph); ph ^= 1;
+    if (UPDATE && !WIDE && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }   // previous tile's G1: frees the other X buffer and BS
     umma::tc_fence_after();
     load_acc16<!VHEAD>(lane_addr, cq, n2);
     act_ln16(n2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
@@ -565,10 +570,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (issuer_bwd && umma::elect_one()) {
       umma::tc_fence_after();
-      if (HEAD && !VHEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
-      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
       issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
+      if (HEAD && !VHEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
+      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
+      umma::mma_commit(gbar);
     }
     // ---- next tile's input rows, staged while the tensor cores work
     if (!WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
@@ -588,6 +594,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       first = false;
       continue;
     }
+    umma::mbar_wait(gbar, gph); gph ^= 1;                                 // this tile's G2 has read dz2 out of BS
     store_cols16(sm + m.BS, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
@@ -595,11 +602,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     if (issuer_next && umma::elect_one()) {
       umma::tc_fence_after();
       if (has_next) issue_bulk(tile + 2 * (long long)gridDim.x);
-      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);                      // G1 += dz1^T x
-      if (has_next)
+      if (has_next) {
         issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
-      umma::mma_commit(bar);
+        umma::mma_commit(bar);
+      }
+      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);                      // G1 += dz1^T x
+      umma::mma_commit(gbar);
     }
     buf ^= 1;
     first = false;
@@ -607,7 +616,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   // ---- epilogue: weight gradients TMEM -> two partial rows per CTA (the hi-half and the lo-half lanes of the stacked A operand), in the flat
   // parameter layout (G in the W slots, db in the b slots; LayerNorm-affine slots stay zero, optim.cu fills them)
   if (UPDATE) {
-    if (!WIDE) { umma::mbar_wait(bar, ph); ph ^= 1; }                   // the last tile's fc1 weight gradient
+    if (!first) { umma::mbar_wait(gbar, gph); gph ^= 1; }               // the last tile's weight gradients
     umma::tc_fence_after();
     float* __restrict__ gp0 = a.grad_partials + (size_t)(2 * blockIdx.x) * L.total;
     if (HEAD) for (int e = tid; e < 2 * L.total; e += kThreads) gp0[e] = 0.0f;   // MODE 5: the caller zeroed the buffer
