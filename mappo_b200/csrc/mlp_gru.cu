@@ -511,7 +511,7 @@ constexpr int kGruMaxSmem = 232448 - 1024;
 static int check_rnn(const mappo_net_config* cfg, const char* who) {
   if (int rc = check_net(cfg, who)) return rc;
   MAPPO_REQUIRE(cfg->recurrent, "%s: not a recurrent network", who);
-  if (cfg->in_dim > 64) MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d > 64 are not built", who, cfg->in_dim);
+  if (cfg->in_dim >= 64) MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d >= 64 are not built", who, cfg->in_dim);
   return 0;
 }
 

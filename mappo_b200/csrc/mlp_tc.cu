@@ -22,12 +22,15 @@ namespace mappo {
 namespace tc {
 
 constexpr int kTmemCols = 512;
-constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 256, kColGh = 384;   // TMEM column map
+// TMEM column map.  The BIAS gradients sum_rows dz come off the tensor cores too: the n1 operand tile ends in a constant
+// chunk whose first column is 1 (column 128 of G2), and the input tile carries a 1 in its first padding column
+// (column in_dim of G1; W1' is zero there, so the forward pass does not see it).
+constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 288, kColGh = 448;
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
   uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, b1s, b2s, bhf, dbh, xch, xlog, red, bars, raw, total;
-  uint32_t x_piece, w1_piece;
+  uint32_t x_piece, w1_piece, x_buf;
   int xlog_in_x;                 // 1: the head's partial logits live in the idle X buffer (see below), `xlog` unused
 };
 // The partial logits [4 column quarters][128 rows][AS] are written after the second layer and read before the
@@ -44,8 +47,10 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
   m.x_piece = (uint32_t)(Kp / 8) * kRowChunk;
   m.w1_piece = (uint32_t)(Kp / 8) * kWChunk;
-  m.X = take(2 * kNP * m.x_piece);                 // two buffers: this tile's rows and the next tile's
-  m.N1 = take(kNP * 8 * kRowChunk);
+  const uint32_t ones = update ? 2 * kRowChunk : 0;  // the constant [1 0 .. 0] columns behind the n1 tile (bias gradient)
+  m.x_buf = kNP * m.x_piece;
+  m.X = take(2 * m.x_buf);                         // two buffers: this tile's rows and the next tile's
+  m.N1 = take(kNP * 8 * kRowChunk + ones);
   m.BS = take(update ? kNP * 8 * kRowChunk : 0);    // dz2, then dz1
   m.BS2 = take(update && !vhead ? kNP * 8 * kRowChunk : 0);   // n2 (operand of the head weight gradient)
   m.W1 = take(kNP * m.w1_piece);
@@ -201,7 +206,8 @@ __device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[1
 }
 
 // ---- input rows: gather, LayerNorm over in_dim (mlp.py:44-45,56-57), fp16 pairs -> X operand tile
-template <int KP>
+// ONES: column in_dim (the first padding column; in_dim < KP) is set to 1 -- see the TMEM column map
+template <int KP, bool ONES>
 __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsigned char* xs, uint32_t x_piece, float2* xch,
                                         int& slot, int cq, int r, int q4, const float* raw = nullptr) {
   constexpr int XC = KP / 4;                         // input columns per thread
@@ -239,6 +245,10 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
     const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
 #pragma unroll
     for (int i = 0; i < XC; ++i) xv[i] *= rstd;
+  }
+  if (ONES) {
+#pragma unroll
+    for (int i = 0; i < XC; ++i) if (XC * cq + i == D) xv[i] = 1.0f;
   }
 #pragma unroll
   for (int h = 0; h < XC / 8; ++h) {
@@ -335,17 +345,25 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   auto stage_next = [&](long long t, unsigned char* xs, int& slot_ref) {
     if (bulk_tile(t)) {
       umma::mbar_wait(tbar, tph); tph ^= 1;
-      stage_x<KP>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4, raw);
+      stage_x<KP, UPDATE>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4, raw);
     } else {
-      stage_x<KP>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4);
+      stage_x<KP, UPDATE>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4);
     }
   };
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   stage_weights_tc(sm, m, a, !WIDE, UPDATE);
+  if (UPDATE && tid < kBM) {                                            // the ones columns (written once)
+    const uint4 one = make_uint4(0x00003C00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
+    auto put = [&](unsigned char* base) {
+      *reinterpret_cast<uint4*>(base + tid * 16) = one;
+      *reinterpret_cast<uint4*>(base + kRowChunk + tid * 16) = zero;
+    };
+    put(sm + m.N1 + kNP * 8 * kRowChunk);
+  }
   int slot = 0;
   float2* xch = reinterpret_cast<float2*>(sm + m.xch);
   long long tile = blockIdx.x;
-  if (!WIDE) stage_x<KP>(a, tile, sm + m.X, m.x_piece, xch, slot, cq, r, q4);
+  if (!WIDE) stage_x<KP, UPDATE>(a, tile, sm + m.X, m.x_piece, xch, slot, cq, r, q4);
   umma::fence_async_smem();
   umma::tc_fence_before();
   __syncthreads();
@@ -355,7 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   if (issuer_next && umma::elect_one()) issue_bulk(tile + gridDim.x);
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
-  const uint32_t x_bytes = kNP * m.x_piece;
+  const uint32_t x_bytes = m.x_buf;
   const uint32_t b16 = umma::smem_u32(sm) >> 4;                         // operand addresses in 16-byte units
   const uint32_t sX = b16 + (m.X >> 4), sN1 = b16 + (m.N1 >> 4), sBS = b16 + (m.BS >> 4), sB2 = b16 + (m.BS2 >> 4);
   const uint32_t sW1 = b16 + (m.W1 >> 4), sW2 = b16 + (m.W2 >> 4), sDL = b16 + (m.DL >> 4);
@@ -367,7 +385,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   const float* b2s = reinterpret_cast<const float*>(sm + m.b2s) + 16 * cq;
   const float* bhf = reinterpret_cast<const float*>(sm + m.bhf);
   constexpr uint32_t kIdFwd = umma::idesc_f16(128, 64, 0, 0), kIdDgrad = umma::idesc_f16(128, 64, 0, 1);
-  constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
+  constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128 + 16, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
   if (!WIDE && issuer_next && umma::elect_one()) {
     issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
@@ -376,11 +394,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   uint32_t ph = 0, gph = 0;
   int buf = 0;
   bool first = true;
-  float db1[16], db2[16], ghv[VHEAD ? 16 : 1];
+  float db1[WIDE ? 16 : 1], ghv[VHEAD ? 16 : 1];      // WIDE: the fc1 weight gradient (and its ones column) lives outside
   double lacc[4] = {0.0, 0.0, 0.0, 0.0};
   if (UPDATE) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) db1[i] = db2[i] = 0.0f;
+    for (int i = 0; i < (WIDE ? 16 : 1); ++i) db1[i] = 0.0f;
 #pragma unroll
     for (int i = 0; i < (VHEAD ? 16 : 1); ++i) ghv[i] = 0.0f;
   }
@@ -562,8 +580,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       }
     }
     ln_act_bwd16(dz, n2, mean2, rstd2, relu, xch, slot, cq, r, q4);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) db2[i] += dz[i];
     store_cols16(sm + m.BS, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
@@ -583,8 +599,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::tc_fence_after();
     load_acc16<!VHEAD>(lane_addr, cq, dz);
     ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
+    if (WIDE) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) db1[i] += dz[i];
+      for (int i = 0; i < 16; ++i) db1[WIDE ? i : 0] += dz[i];
+    }
     if (WIDE) {                                                          // dLoss/dz1 leaves for wgrad1_wide_kernel
       if (valid) {
         float4* zp = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
@@ -623,10 +641,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     float* red = reinterpret_cast<float*>(sm + m.red);                    // [2][16 warps][16]
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      float v1 = db1[i], v2 = db2[i];
+      if (WIDE) {
+        float v1 = db1[WIDE ? i : 0];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) { v1 += __shfl_xor_sync(0xffffffffu, v1, o); v2 += __shfl_xor_sync(0xffffffffu, v2, o); }
-      if (lane == 0) { red[warp * 16 + i] = v1; red[256 + warp * 16 + i] = v2; }
+        for (int o = 16; o > 0; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        if (lane == 0) red[warp * 16 + i] = v1;
+      }
       if (VHEAD) {
         float v3 = ghv[VHEAD ? i : 0];
 #pragma unroll
@@ -651,7 +671,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         for (int i = 0; i < 16; ++i) {
           const int k = 16 * cq + i;
           if (k < D) gp[L.w1 + mrow * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+          if (k == D) gp[L.b1 + mrow] = u[i] * lane_scale;             // the ones column of the input tile
         }
+      }
+      if (cq == 0) {                                                      // bias gradients: the ones columns
+        umma::tmem_ld16(lane_addr + kColG2 + 128, u);
+        gp[L.b2 + mrow] = u[0] * lane_scale;
       }
       if (HEAD && !VHEAD && cq == 3) {                                    // warps 12..15: head gradient, lanes = hidden unit
         umma::tmem_ld16(lane_addr + kColGh, u);
@@ -668,9 +693,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     }
     if (tid < 64) {
       const int c = tid >> 4, i = tid & 15;
-      float s1 = 0.0f, s2 = 0.0f;
-      for (int q = 0; q < 4; ++q) { s1 += red[(4 * c + q) * 16 + i]; s2 += red[256 + (4 * c + q) * 16 + i]; }
-      gp0[L.b1 + tid] = s1; gp0[L.b2 + tid] = s2;
+      if (WIDE) {
+        float s1 = 0.0f;
+        for (int q = 0; q < 4; ++q) s1 += red[(4 * c + q) * 16 + i];
+        gp0[L.b1 + tid] = s1;
+      }
       if (VHEAD) {
         float s3 = 0.0f;
         for (int q = 0; q < 4; ++q) s3 += red[512 + (4 * c + q) * 16 + i];
@@ -730,11 +757,11 @@ int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, c
 
 bool supports(const mappo_net_config* cfg) {
   if (wide_supports(cfg)) return true;
-  if (!(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim <= 64)) return false;
+  if (!(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim < 64)) return false;
   int A = 0;
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
-  const int Kp = cfg->in_dim <= 32 ? 32 : 64;
+  const int Kp = cfg->in_dim < 32 ? 32 : 64;
   return make_map(Kp, A | 1, true).total <= (uint32_t)kMaxDynSmem && make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
@@ -776,7 +803,7 @@ template <int MODE>
 int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
   a.L = make_layout(*cfg);
   if (a.x_div < 1) a.x_div = 1;
-  a.Kp = cfg->in_dim <= 32 ? 32 : 64;
+  a.Kp = cfg->in_dim < 32 ? 32 : 64;               // strictly: the update kernels need one padding column
   a.ntiles = (a.rows + kBM - 1) / kBM;
   constexpr bool kCritic = (MODE == 1 || MODE == 3 || MODE >= 4);        // one register column for the head
   if constexpr (kCritic) {
