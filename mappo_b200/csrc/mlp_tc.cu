@@ -430,7 +430,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     } else {
       umma::mbar_wait(bar, ph); ph ^= 1;
       umma::tc_fence_after();
-      load_acc16<!VHEAD>(lane_addr, cq, n1);
+      load_acc16<true>(lane_addr, cq, n1);
     }
     act_ln16(n1, b1f, b1s, relu, xch, slot, cq, r, q4, mean1, rstd1);
     store_cols16(sm + m.N1, r, cq, n1);
@@ -442,12 +442,27 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk16, sW2, 8 * kWChunk16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
       umma::mma_commit(bar);
     }
+    // rollout: the next tile's input rows are staged while fc2 runs, and its fc1 is issued as soon as every warp has
+    // its fc2 accumulators in registers, so both GEMMs hide under epilogue work
+    if (!UPDATE && !WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
     // ---- layer 2 epilogue + head
     float n2[16], mean2, rstd2;
     umma::mbar_wait(bar, ph); ph ^= 1;
     if (UPDATE && !WIDE && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }   // previous tile's G1: frees the other X buffer and BS
     umma::tc_fence_after();
-    load_acc16<!VHEAD>(lane_addr, cq, n2);
+    load_acc16<true>(lane_addr, cq, n2);
+    if (!UPDATE && !WIDE) {
+      umma::fence_async_smem();
+      umma::tc_fence_before();
+      __syncthreads();
+      if (has_next && issuer_next && umma::elect_one()) {
+        issue_bulk(tile + 2 * (long long)gridDim.x);
+        umma::tc_fence_after();
+        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+                               128, 2 * kWChunk16, kIdFwd);
+        umma::mma_commit(bar);
+      }
+    }
     act_ln16(n2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
     if (UPDATE && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
     if (MODE == 4 && valid) {
@@ -488,17 +503,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         if (MODE == 1) for (int mm = 0; mm < a.group; ++mm) a.values_out[g * a.group + mm] = l[0];
       }
       if (WIDE) continue;
-      if (has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
-      umma::fence_async_smem();
-      umma::tc_fence_before();
-      __syncthreads();
-      if (has_next && issuer_next && umma::elect_one()) {
-        issue_bulk(tile + 2 * (long long)gridDim.x);
-        umma::tc_fence_after();
-        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
-                               128, 2 * kWChunk16, kIdFwd);
-        umma::mma_commit(bar);
-      }
       buf ^= 1;
       continue;
     }
@@ -597,7 +601,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
-    load_acc16<!VHEAD>(lane_addr, cq, dz);
+    load_acc16<true>(lane_addr, cq, dz);
     ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
     if (WIDE) {
 #pragma unroll
