@@ -1,5 +1,6 @@
 """ORACLE (test infrastructure, not product code): CPU restatement of the reference's MPE step for the
-three target scenarios, batched over envs in float64 numpy.
+three target scenarios (plus simple_adversary / simple_push / simple_tag), batched over envs in
+float64 numpy.
 
 Follows, operation for operation (so results agree with the reference to the last f64 bit wherever
 numpy/libm agree):
@@ -9,6 +10,9 @@ numpy/libm agree):
   * simple_spread   make_world/reset_world/reward/observation   scenarios/simple_spread.py:7-45,72-103
   * simple_speaker_listener                                       scenarios/simple_speaker_listener.py:7-98
   * simple_reference                                              scenarios/simple_reference.py:7-97
+  * simple_adversary / simple_push / simple_tag                   scenarios/simple_adversary.py:9-137,
+                                                                  simple_push.py:8-104, simple_tag.py:7-144
+    (per-agent size / accel / max_speed, agent-landmark contacts, individual rewards: core.py:229-278,290-321)
   * auto-reset on done (obs replaced by reset obs, reward/done kept)  onpolicy/envs/env_wrappers.py:140-157,676-682
 
 Reset states come from Philox (oracle/philox.py) instead of the reference's process-global MT19937
@@ -59,7 +63,7 @@ def np_sum_small(vals):
 class ScenarioSpec:
     """Static description of a scenario (what make_world sets)."""
 
-    def __init__(self, name, M, L):
+    def __init__(self, name, M, L, num_adversaries=None):
         self.name, self.M, self.L = name, M, L
         if name == "simple_spread":
             self.dim_c = 2
@@ -93,15 +97,63 @@ class ScenarioSpec:
             self.n_goals = 2
             self.obs_dims = [2 + 2 * L + 3 + 10] * M
             self.act_heads = [[5, 10]] * M        # MultiDiscrete([[0,4],[0,9]])
+        elif name == "simple_adversary":                                # simple_adversary.py:9-36
+            assert L == M - 1, "simple_adversary: num_landmarks = num_agents - 1"
+            self.n_adv = 1
+            self.collide = False
+            self.agent_size = 0.15
+            self.landmark_scale = 1.0
+            self.n_goals = 1
+            self.shared_goal = True
+            self.collaborative = False
+            self.obs_dims = [2 * L + 2 * (M - 1)] + [2 + 2 * L + 2 * (M - 1)] * (M - 1)
+        elif name == "simple_push":                                     # simple_push.py:8-36
+            assert L <= 2, "simple_push: landmark.color[i + 1] limits it to 2 landmarks"
+            self.n_adv = 1
+            self.collide = True
+            self.agent_size = 0.05                                      # Entity default, core.py:38
+            self.landmark_scale = 0.8
+            self.n_goals = 1
+            self.shared_goal = True
+            self.collaborative = False
+            self.obs_dims = [2 + 2 * L + 2 * (M - 1)] + [2 + 2 + 3 + 2 * L + 3 * L + 2 * (M - 1)] * (M - 1)
+        elif name == "simple_tag":                                      # simple_tag.py:7-38
+            self.n_adv = n_adv = int(num_adversaries if num_adversaries else 3)
+            assert 0 < n_adv < M
+            self.collide = True
+            self.sizes = [0.075] * n_adv + [0.05] * (M - n_adv)
+            self.accel = [3.0] * n_adv + [4.0] * (M - n_adv)
+            self.max_speed = [1.0] * n_adv + [1.3] * (M - n_adv)
+            self.landmark_collide, self.landmark_size = True, 0.2
+            self.agent_size = None
+            self.landmark_scale = 0.8
+            self.n_goals = 0
+            self.collaborative = False
+            n_good = M - n_adv
+            self.obs_dims = [4 + 2 * L + 2 * (M - 1) + 2 * n_good] * n_adv + \
+                            [4 + 2 * L + 2 * (M - 1) + 2 * (n_good - 1)] * n_good
         else:
             raise NotImplementedError(name)
+        if name in ("simple_adversary", "simple_push", "simple_tag"):
+            self.dim_c = 2
+            self.movable = [True] * M
+            self.silent = [True] * M
+            self.act_heads = [[5]] * M
+        if not hasattr(self, "sizes"):
+            self.sizes = [self.agent_size] * M
+            self.accel = [None] * M
+            self.max_speed = [None] * M
+            self.landmark_collide, self.landmark_size = False, 0.05
+        self.shared_goal = getattr(self, "shared_goal", False)
+        self.collaborative = getattr(self, "collaborative", True)
+        self.n_adv = getattr(self, "n_adv", 0)
         self.n_draws = self.n_goals + 2 * M + 2 * L
 
 
 class OracleMPE:
     def __init__(self, scenario, num_envs, num_agents, num_landmarks, episode_length,
-                 seed=0, env_id_offset=0):
-        self.spec = ScenarioSpec(scenario, num_agents, num_landmarks)
+                 seed=0, env_id_offset=0, num_adversaries=None):
+        self.spec = ScenarioSpec(scenario, num_agents, num_landmarks, num_adversaries)
         self.N, self.M, self.L = num_envs, num_agents, num_landmarks
         self.world_length = episode_length
         self.seed = seed
@@ -126,6 +178,8 @@ class OracleMPE:
             # uniform landmark id: floor(u32 * L / 2**32)
             goal[:, g] = (d[:, k].astype(np.uint64) * np.uint64(self.L)) >> np.uint64(32)
             k += 1
+        if sp.shared_goal:                                              # agent.goal_a = goal for every agent
+            goal[:, :] = goal[:, :1]
         u = philox.u32_to_sym(d[:, k:])
         p_pos = u[:, :2 * self.M].reshape(-1, self.M, 2).copy()
         lm = u[:, 2 * self.M:].reshape(-1, self.L, 2)
@@ -171,7 +225,7 @@ class OracleMPE:
                 onehot = np.eye(5)[a]
                 u[:, i, 0] += onehot[:, 1] - onehot[:, 2]
                 u[:, i, 1] += onehot[:, 3] - onehot[:, 4]
-                u[:, i] *= SENSITIVITY
+                u[:, i] *= SENSITIVITY if sp.accel[i] is None else sp.accel[i]   # environment.py:243-246
                 head += 1
             if not sp.silent[i]:
                 c_act[:, i] = np.eye(sp.dim_c)[actions[:, i, head]]
@@ -179,11 +233,11 @@ class OracleMPE:
         force = [None] * M
         for i in range(M):                                              # apply_action_force core.py:229-238
             if sp.movable[i]:
-                force[i] = 1.0 * u[:, i] + 0.0
+                force[i] = (1.0 if sp.accel[i] is None else 1.0 * sp.accel[i]) * u[:, i] + 0.0
         if sp.collide:                                                  # apply_environment_force core.py:241-263
-            dist_min = sp.agent_size + sp.agent_size
             for a in range(M):
                 for b in range(a + 1, M):
+                    dist_min = sp.sizes[a] + sp.sizes[b]
                     delta = self.p_pos[:, a] - self.p_pos[:, b]
                     dist = np.sqrt(np.sum(np.square(delta), axis=-1))
                     k = CONTACT_MARGIN
@@ -193,19 +247,38 @@ class OracleMPE:
                     fb = -(1 / 1.0) * f
                     force[a] = fa + force[a]
                     force[b] = fb + force[b]
+                if sp.landmark_collide:                                 # entities = agents + landmarks: (agent a, landmark l)
+                    for l in range(self.L):
+                        dist_min = sp.sizes[a] + sp.landmark_size
+                        delta = self.p_pos[:, a] - self.lm_pos[:, l]
+                        dist = np.sqrt(np.sum(np.square(delta), axis=-1))
+                        k = CONTACT_MARGIN
+                        pen = np.logaddexp(0, -(dist - dist_min) / k) * k
+                        f = CONTACT_FORCE * delta / dist[:, None] * pen[:, None]
+                        force[a] = +f + force[a]                        # core.py:318-320 (landmark not movable)
         for i in range(M):                                              # integrate_state core.py:265-278
             if not sp.movable[i]:
                 continue
             self.p_vel[:, i] = self.p_vel[:, i] * (1 - DAMPING)
             if force[i] is not None:
                 self.p_vel[:, i] += (force[i] / 1.0) * DT
+            if sp.max_speed[i] is not None:                             # core.py:272-277
+                v = self.p_vel[:, i]
+                speed = np.sqrt(np.square(v[:, 0]) + np.square(v[:, 1]))
+                fast = speed > sp.max_speed[i]
+                with np.errstate(invalid="ignore", divide="ignore"):
+                    clamped = v / np.sqrt(np.square(v[:, 0]) + np.square(v[:, 1]))[:, None] * sp.max_speed[i]
+                self.p_vel[:, i] = np.where(fast[:, None], clamped, v)
             self.p_pos[:, i] += self.p_vel[:, i] * DT
         for i in range(M):                                              # update_agent_state core.py:280-287
             self.comm[:, i] = 0.0 if sp.silent[i] else c_act[:, i] + 0.0
         obs = self.observations()
         indiv = self.rewards()                                          # [N, M]
-        total = np_sum_small([indiv[:, i] for i in range(M)])           # environment.py:141-143 (collaborative)
-        rewards = np.repeat(total[:, None, None], M, axis=1)
+        if sp.collaborative:
+            total = np_sum_small([indiv[:, i] for i in range(M)])       # environment.py:141-143 (collaborative)
+            rewards = np.repeat(total[:, None, None], M, axis=1)
+        else:
+            rewards = indiv[:, :, None].copy()
         done_env = self.step_count >= self.world_length                 # environment.py:179-185
         dones = np.repeat(done_env[:, None], M, axis=1)
         idx = np.nonzero(done_env)[0]
@@ -233,9 +306,32 @@ class OracleMPE:
                     o = COLORS_SPEAKER_LISTENER[self.goal[:, 0]].copy()
                 else:
                     o = np.concatenate([self.p_vel[:, 1]] + ent + [self.comm[:, 0]], axis=-1)
-            else:                                                       # simple_reference.py:69-97
+            elif sp.name == "simple_reference":                         # simple_reference.py:69-97
                 color = COLORS_REFERENCE[self.goal[:, i]]
                 o = np.concatenate([self.p_vel[:, i]] + ent + [color, self.comm[:, 1 - i]], axis=-1)
+            elif sp.name == "simple_adversary":                         # simple_adversary.py:116-137
+                other = [self.p_pos[:, j] - pos_i for j in range(M) if j != i]
+                goal_pos = self.lm_pos[np.arange(N), self.goal[:, i]]
+                o = np.concatenate(([goal_pos - pos_i] if i >= sp.n_adv else []) + ent + other, axis=-1)
+            elif sp.name == "simple_push":                              # simple_push.py:81-104
+                other = [self.p_pos[:, j] - pos_i for j in range(M) if j != i]
+                if i < sp.n_adv:
+                    o = np.concatenate([self.p_vel[:, i]] + ent + other, axis=-1)
+                else:
+                    g = self.goal[:, i]
+                    goal_pos = self.lm_pos[np.arange(N), g]
+                    color = np.full((N, 3), 0.25)                       # simple_push.py:48-54
+                    color[np.arange(N), g + 1] += 0.5
+                    lm_colors = []
+                    for l in range(L):                                  # simple_push.py:41-44
+                        c = np.full((N, 3), 0.1)
+                        c[:, l + 1] += 0.8
+                        lm_colors.append(c)
+                    o = np.concatenate([self.p_vel[:, i], goal_pos - pos_i, color] + ent + lm_colors + other, axis=-1)
+            else:                                                       # simple_tag.py:125-144
+                other = [self.p_pos[:, j] - pos_i for j in range(M) if j != i]
+                other_vel = [self.p_vel[:, j] for j in range(M) if j != i and j >= sp.n_adv]
+                o = np.concatenate([self.p_vel[:, i], pos_i] + ent + other + other_vel, axis=-1)
             out.append(o)
         return out
 
@@ -261,8 +357,48 @@ class OracleMPE:
         elif sp.name == "simple_speaker_listener":                      # simple_speaker_listener.py:69-73
             d = self.p_pos[:, 1] - self.lm_pos[ar, self.goal[:, 0]]
             r[:] = -np.sum(np.square(d), axis=-1)[:, None]
-        else:                                                           # simple_reference.py:62-67
+        elif sp.name == "simple_reference":                             # simple_reference.py:62-67
             for i in range(M):
                 d = self.p_pos[:, 1 - i] - self.lm_pos[ar, self.goal[:, i]]
                 r[:, i] = -np.sum(np.square(d), axis=-1)
+        elif sp.name in ("simple_adversary", "simple_push"):
+            goal_pos = self.lm_pos[ar, self.goal[:, 0]]
+            dist = [np.sqrt(np.sum(np.square(self.p_pos[:, a] - goal_pos), axis=-1)) for a in range(M)]
+            good_min = np.stack(dist[sp.n_adv:], axis=0).min(axis=0)
+            for i in range(M):
+                if sp.name == "simple_adversary":                       # simple_adversary.py:69-113
+                    if i < sp.n_adv:
+                        r[:, i] = -np.sum(np.square(self.p_pos[:, i] - goal_pos), axis=-1)
+                    else:
+                        adv_rew = 0
+                        for a in range(sp.n_adv):
+                            adv_rew = adv_rew + dist[a]
+                        r[:, i] = -good_min + adv_rew
+                else:                                                   # simple_push.py:62-78
+                    if i < sp.n_adv:
+                        neg = np.sqrt(np.sum(np.square(goal_pos - self.p_pos[:, i]), axis=-1))
+                        r[:, i] = good_min - neg
+                    else:
+                        r[:, i] = -dist[i]
+        else:                                                           # simple_tag.py:73-123
+            def hit(a, b):
+                d = np.sqrt(np.sum(np.square(self.p_pos[:, a] - self.p_pos[:, b]), axis=-1))
+                return d < sp.sizes[a] + sp.sizes[b]
+            adv_total = np.zeros(N)
+            for ag in range(sp.n_adv, M):
+                for adv in range(sp.n_adv):
+                    adv_total = adv_total + 10.0 * hit(ag, adv)
+            for i in range(M):
+                if i < sp.n_adv:
+                    r[:, i] = adv_total
+                else:
+                    ri = np.zeros(N)
+                    for a in range(sp.n_adv):
+                        ri = ri - 10.0 * hit(a, i)
+                    for p in range(2):
+                        x = np.abs(self.p_pos[:, i, p])
+                        with np.errstate(over="ignore"):
+                            b = np.where(x < 0.9, 0.0, np.where(x < 1.0, (x - 0.9) * 10, np.minimum(np.exp(2 * x - 2), 10)))
+                        ri = ri - b
+                    r[:, i] = ri
         return r

@@ -35,8 +35,13 @@ def world_state(env):
     p_vel = np.array([a.state.p_vel for a in w.agents])
     lm = np.array([l.state.p_pos for l in w.landmarks])
     comm = np.array([a.state.c for a in w.agents])
-    goal = np.array([w.landmarks.index(a.goal_b) if getattr(a, "goal_b", None) is not None else -1
-                     for a in w.agents])
+    def goal_of(a):
+        for name in ("goal_b", "goal_a"):      # goal_b: speaker_listener / reference; goal_a (a landmark): adversary / push
+            g = getattr(a, name, None)
+            if g is not None and g in w.landmarks:
+                return w.landmarks.index(g)
+        return -1
+    goal = np.array([goal_of(a) for a in w.agents])
     return p_pos, p_vel, lm, comm, goal
 
 
@@ -52,6 +57,9 @@ def one_hot_action(space, ids):
 def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
     from onpolicy.envs.mpe.MPE_env import MPEEnv
     args = ref_args(scenario, M, L, "mappo")
+    if scenario == "simple_tag":
+        # simple_tag.py:11-12 reads two flags that train_mpe.py's parser (train_mpe.py:52-61) does not define
+        args.num_adversaries, args.num_good_agents = M - 1, 1
     rng = np.random.RandomState(seed)
     # one reference env per slot; they share the process-global np.random like DummyVecEnv
     np.random.seed(seed)
@@ -61,6 +69,13 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
         heads.append([sp.n] if sp.__class__.__name__ == "Discrete" else list((sp.high - sp.low + 1).astype(int)))
     H = max(len(h) for h in heads)
     obs0 = [e.reset() for e in envs]
+    if scenario in ("simple_push", "simple_tag"):
+        # crowd the upper half of the envs around a landmark: agent-agent and agent-landmark contacts, tag rewards
+        for n in range(N // 2, N):
+            c = envs[n].world.landmarks[0].state.p_pos
+            for a in envs[n].world.agents:
+                a.state.p_pos = c + rng.uniform(-0.3, 0.3, 2)
+            obs0[n] = [envs[n]._get_obs(a) for a in envs[n].agents]
     if scenario == "simple_spread":
         # crowd the agents of the upper half of the envs so the soft-contact force (core.py:290-321)
         # and the collision penalty (simple_spread.py:80-83) are exercised from the first step
@@ -114,10 +129,15 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
     return out
 
 
-def gen_env():
-    for scen, M, L, tag in (("simple_spread", 3, 3, "spread_m3"), ("simple_spread", 10, 3, "spread_m10"),
-                            ("simple_speaker_listener", 2, 3, "speaker_listener"),
-                            ("simple_reference", 2, 3, "reference")):
+ENV_FIXTURES = (("simple_spread", 3, 3, "spread_m3"), ("simple_spread", 10, 3, "spread_m10"),
+                ("simple_speaker_listener", 2, 3, "speaker_listener"), ("simple_reference", 2, 3, "reference"),
+                ("simple_adversary", 3, 2, "adversary"), ("simple_push", 2, 2, "push"), ("simple_tag", 4, 2, "tag"))
+
+
+def gen_env(only=None):
+    for scen, M, L, tag in ENV_FIXTURES:
+        if only and tag not in only:
+            continue
         fx = make_env_fixture(scen, M, L, N=4 if M == 10 else 6)
         path = os.path.join(HERE, "env_%s.npz" % tag)
         np.savez_compressed(path, scenario=scen, **fx)

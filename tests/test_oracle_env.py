@@ -7,13 +7,14 @@ import pytest
 
 from oracle.mpe import OracleMPE, np_sum_small
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag"]
 
 
 def replay(fx, make_env):
     """Replay a fixture through an env implementation; yields per-step comparisons."""
     N, M, L = int(fx["N"]), int(fx["M"]), int(fx["L"])
-    env = make_env(str(fx["scenario"]), N, M, L, int(fx["episode_length"]))
+    kw = dict(num_adversaries=M - 1) if str(fx["scenario"]) == "simple_tag" else {}
+    env = make_env(str(fx["scenario"]), N, M, L, int(fx["episode_length"]), **kw)
     env.reset(state=dict(p_pos=fx["init_p_pos"], lm_pos=fx["init_lm_pos"], goal=fx["init_goal"]))
     obs = env.observations()
     for i in range(M):
@@ -33,7 +34,7 @@ def test_oracle_env_matches_reference(tag, golden_dir):
     fx = np.load(os.path.join(golden_dir, "env_%s.npz" % tag))
     M = int(fx["M"])
     worst = 0.0
-    for s, env, (obs, rew, done, indiv) in replay(fx, lambda *a: OracleMPE(*a)):
+    for s, env, (obs, rew, done, indiv) in replay(fx, lambda *a, **k: OracleMPE(*a, **k)):
         for i in range(M):
             np.testing.assert_allclose(obs[i], fx["obs_%d" % i][s], rtol=1e-13, atol=1e-15,
                                        err_msg="obs step %d agent %d" % (s, i))
