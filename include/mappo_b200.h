@@ -57,7 +57,12 @@ uint64_t mappo_launch_count(void);
 typedef enum {
   MAPPO_SCN_SIMPLE_SPREAD = 0,
   MAPPO_SCN_SIMPLE_SPEAKER_LISTENER = 1,
-  MAPPO_SCN_SIMPLE_REFERENCE = 2
+  MAPPO_SCN_SIMPLE_REFERENCE = 2,
+  /* scenarios/simple_adversary.py:9-137, simple_push.py:8-104, simple_tag.py:7-144
+   * (individual rewards; simple_tag adds per-agent size / accel / max_speed and obstacle landmarks) */
+  MAPPO_SCN_SIMPLE_ADVERSARY = 3,
+  MAPPO_SCN_SIMPLE_PUSH = 4,
+  MAPPO_SCN_SIMPLE_TAG = 5
 } mappo_scenario;
 
 typedef struct {
@@ -66,7 +71,8 @@ typedef struct {
   int32_t num_agents;      /* M */
   int32_t num_landmarks;   /* L */
   int32_t episode_length;  /* world_length: done when step count reaches it (environment.py:179-185) */
-  int32_t reserved;
+  int32_t num_adversaries; /* simple_tag: args.num_adversaries (0 = the scenario's default 3); the agents listed first.
+                            * Occupies the word that was `reserved` (= 0) in ABI v2. */
   uint64_t seed;           /* Philox key word 0 for reset draws */
   int64_t env_id_offset;   /* global id of local env 0: reset streams do not depend on the sharding */
 } mappo_env_config;
@@ -87,6 +93,9 @@ typedef struct {
 int mappo_env_obs_width(int scenario, int num_agents, int num_landmarks);
 /* obs dim of one agent */
 int mappo_env_obs_dim(int scenario, int num_agents, int num_landmarks, int agent);
+/* the same from a config (needed where the width depends on num_adversaries: simple_tag) */
+int mappo_env_obs_dim_cfg(const mappo_env_config* cfg, int agent);
+int mappo_env_obs_width_cfg(const mappo_env_config* cfg);
 
 /* envs.reset(): draw every env's initial state (Philox, counter = (env id, episode, block, 0)),
  * zero step counts, and write the observations.  obs_out: float32 [N][obs_width], agent-major inside

@@ -18,7 +18,7 @@ class MappoError(RuntimeError):
 
 class EnvConfig(C.Structure):
     _fields_ = [("scenario", C.c_int32), ("num_envs", C.c_int32), ("num_agents", C.c_int32),
-                ("num_landmarks", C.c_int32), ("episode_length", C.c_int32), ("reserved", C.c_int32),
+                ("num_landmarks", C.c_int32), ("episode_length", C.c_int32), ("num_adversaries", C.c_int32),
                 ("seed", C.c_uint64), ("env_id_offset", C.c_int64)]
 
 
@@ -49,6 +49,8 @@ def _declare(L):
     L.mappo_launch_count.restype = C.c_uint64
     L.mappo_env_obs_width.argtypes = [C.c_int, C.c_int, C.c_int]
     L.mappo_env_obs_dim.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+    L.mappo_env_obs_dim_cfg.argtypes = [C.POINTER(EnvConfig), C.c_int]
+    L.mappo_env_obs_width_cfg.argtypes = [C.POINTER(EnvConfig)]
     L.mappo_env_reset.argtypes = [C.POINTER(EnvConfig), C.POINTER(EnvState), C.c_void_p, C.c_int, C.c_void_p]
     L.mappo_env_step.argtypes = [C.POINTER(EnvConfig), C.POINTER(EnvState), C.c_void_p, C.c_int, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(EnvState), C.c_void_p]

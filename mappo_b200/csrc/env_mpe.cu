@@ -12,6 +12,9 @@
 //                                 simple_reference.py:62-97; collaborative sum environment.py:141-143
 //   _get_done + auto-reset        environment.py:179-185, envs/env_wrappers.py:145-154
 //   reset_world                   simple_spread.py:32-45, simple_speaker_listener.py:38-63, simple_reference.py:34-60
+// plus simple_adversary.py:9-137, simple_push.py:8-104, simple_tag.py:7-144: per-agent size /
+// accel / max_speed (core.py:229-238,265-278, environment.py:243-246), agent-landmark contacts (core.py:290-321),
+// individual (non-collaborative) rewards.
 #include "common.cuh"
 #include "philox.cuh"
 
@@ -25,25 +28,58 @@ __constant__ double c_colors_ref[9] = {0.75, 0.25, 0.25, 0.25, 0.75, 0.25, 0.25,
 
 struct ScnInfo {
   int dim_c, n_goals, collide;
-  double agent_size, landmark_scale;
+  int shared_goal;          // one goal landmark, the same for every agent (agent.goal_a = goal)
+  int collaborative;        // world.collaborative: every agent receives the sum (environment.py:141-143)
+  int landmark_collide;     // landmarks are obstacles (simple_tag.py:32-34)
+  double agent_size, landmark_scale, landmark_size;
 };
 
 __host__ __device__ inline ScnInfo scn_info(int scn) {
   ScnInfo s;
+  s.shared_goal = 0; s.collaborative = 1; s.landmark_collide = 0; s.landmark_size = 0.05;
   if (scn == MAPPO_SCN_SIMPLE_SPREAD) { s.dim_c = 2; s.n_goals = 0; s.collide = 1; s.agent_size = 0.15; s.landmark_scale = 0.8; }
   else if (scn == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) { s.dim_c = 3; s.n_goals = 1; s.collide = 0; s.agent_size = 0.075; s.landmark_scale = 1.0; }
-  else { s.dim_c = 10; s.n_goals = 2; s.collide = 0; s.agent_size = 0.05; s.landmark_scale = 0.8; }
+  else if (scn == MAPPO_SCN_SIMPLE_REFERENCE) { s.dim_c = 10; s.n_goals = 2; s.collide = 0; s.agent_size = 0.05; s.landmark_scale = 0.8; }
+  else if (scn == MAPPO_SCN_SIMPLE_ADVERSARY) {
+    s.dim_c = 2; s.n_goals = 1; s.collide = 0; s.agent_size = 0.15; s.landmark_scale = 1.0; s.shared_goal = 1; s.collaborative = 0;
+  } else if (scn == MAPPO_SCN_SIMPLE_PUSH) {
+    s.dim_c = 2; s.n_goals = 1; s.collide = 1; s.agent_size = 0.05; s.landmark_scale = 0.8; s.shared_goal = 1; s.collaborative = 0;
+  } else {  // simple_tag: sizes / accel / max_speed depend on the agent's side, see agent_* below
+    s.dim_c = 2; s.n_goals = 0; s.collide = 1; s.agent_size = 0.05; s.landmark_scale = 0.8; s.collaborative = 0;
+    s.landmark_collide = 1; s.landmark_size = 0.2;
+  }
   return s;
 }
+// adversaries come first (agent i is one iff i < nadv); simple_adversary / simple_push have exactly one
+__host__ __device__ inline int n_adversaries(int scn, int cfg_nadv) {
+  if (scn == MAPPO_SCN_SIMPLE_ADVERSARY || scn == MAPPO_SCN_SIMPLE_PUSH) return 1;
+  if (scn == MAPPO_SCN_SIMPLE_TAG) return cfg_nadv > 0 ? cfg_nadv : 3;              // simple_tag.py:12 default
+  return 0;
+}
+__host__ __device__ inline double agent_size_of(int scn, int i, int nadv) {
+  if (scn == MAPPO_SCN_SIMPLE_TAG) return i < nadv ? 0.075 : 0.05;                   // simple_tag.py:22
+  return scn_info(scn).agent_size;
+}
+__host__ __device__ inline double agent_accel_of(int scn, int i, int nadv) {         // 0: accel None
+  return scn == MAPPO_SCN_SIMPLE_TAG ? (i < nadv ? 3.0 : 4.0) : 0.0;                 // simple_tag.py:23
+}
+__host__ __device__ inline double agent_max_speed_of(int scn, int i, int nadv) {     // 0: max_speed None
+  return scn == MAPPO_SCN_SIMPLE_TAG ? (i < nadv ? 1.0 : 1.3) : 0.0;                 // simple_tag.py:24
+}
 
-__host__ __device__ inline int obs_dim_of(int scn, int M, int L, int agent) {
+__host__ __device__ inline int obs_dim_of(int scn, int M, int L, int agent, int nadv = 0) {
+  nadv = n_adversaries(scn, nadv);
   if (scn == MAPPO_SCN_SIMPLE_SPREAD) return 4 + 2 * L + 4 * (M - 1);
   if (scn == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) return agent == 0 ? 3 : 2 + 2 * L + 3;
-  return 2 + 2 * L + 3 + 10;
+  if (scn == MAPPO_SCN_SIMPLE_REFERENCE) return 2 + 2 * L + 3 + 10;
+  if (scn == MAPPO_SCN_SIMPLE_ADVERSARY) return (agent < nadv ? 0 : 2) + 2 * L + 2 * (M - 1);
+  if (scn == MAPPO_SCN_SIMPLE_PUSH) return agent < nadv ? 2 + 2 * L + 2 * (M - 1) : 2 + 2 + 3 + 2 * L + 3 * L + 2 * (M - 1);
+  const int good_others = (M - nadv) - (agent < nadv ? 0 : 1);
+  return 4 + 2 * L + 2 * (M - 1) + 2 * good_others;
 }
-__host__ __device__ inline int obs_off_of(int scn, int M, int L, int agent) {
+__host__ __device__ inline int obs_off_of(int scn, int M, int L, int agent, int nadv = 0) {
   int o = 0;
-  for (int i = 0; i < agent; ++i) o += obs_dim_of(scn, M, L, i);
+  for (int i = 0; i < agent; ++i) o += obs_dim_of(scn, M, L, i, nadv);
   return o;
 }
 __host__ __device__ inline bool is_movable(int scn, int agent) {
@@ -84,6 +120,7 @@ __device__ __forceinline__ double np_sum_small(const double* v, int stride, int 
 // Shared-memory carve-up for one block of EPB envs (all agent-major so a warp has consecutive envs).
 struct EnvSmem {
   double* pos;    // [2][M][EPB]   agent positions (old, then new, then reset)
+  double* vel;    // [2][M][EPB]   agent velocities after the step / reset (simple_tag observes the others')
   double* lm;     // [2][L][EPB]
   double* aux;    // [L*M + M][EPB]  landmark distances, then individual rewards
   int* comm;      // [M][EPB]
@@ -94,7 +131,8 @@ struct EnvSmem {
 __device__ __forceinline__ EnvSmem carve(unsigned char* base, int M, int L, int EPB, int tile_ld) {
   EnvSmem s;
   s.pos = reinterpret_cast<double*>(base);
-  s.lm = s.pos + 2 * M * EPB;
+  s.vel = s.pos + 2 * M * EPB;
+  s.lm = s.vel + 2 * M * EPB;
   s.aux = s.lm + 2 * L * EPB;
   const int aux_rows = L * M + M;
   s.comm = reinterpret_cast<int*>(s.aux + aux_rows * EPB);
@@ -107,7 +145,7 @@ __device__ __forceinline__ EnvSmem carve(unsigned char* base, int M, int L, int 
 static inline int tile_ld_of(int W) { return (W % 2 == 0) ? W + 1 : W; }   // odd row stride: conflict-free columns
 static size_t env_smem_bytes(int M, int L, int EPB, int W) {
   const int aux_rows = L * M + M;
-  return sizeof(double) * (size_t)EPB * (2 * M + 2 * L + aux_rows) + sizeof(int) * (size_t)EPB * 2 * M +
+  return sizeof(double) * (size_t)EPB * (4 * M + 2 * L + aux_rows) + sizeof(int) * (size_t)EPB * 2 * M +
          sizeof(float) * (size_t)EPB * tile_ld_of(W) + sizeof(int) * (size_t)EPB;
 }
 
@@ -115,8 +153,8 @@ static size_t env_smem_bytes(int M, int L, int EPB, int W) {
 // the buffer's float32 assignment does, utils/shared_buffer.py:96-97).
 template <int SCN>
 __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EPB, int ld, int e, int i,
-                                          double vx, double vy) {
-  float* o = s.tile + (size_t)e * ld + obs_off_of(SCN, M, L, i);
+                                          double vx, double vy, int nadv) {
+  float* o = s.tile + (size_t)e * ld + obs_off_of(SCN, M, L, i, nadv);
   const double px = s.pos[(0 * M + i) * EPB + e], py = s.pos[(1 * M + i) * EPB + e];
   int k = 0;
   if (SCN == MAPPO_SCN_SIMPLE_SPREAD) {
@@ -144,7 +182,7 @@ __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EP
       const int cid = s.comm[0 * EPB + e];
       for (int c = 0; c < 3; ++c) o[k++] = (c == cid) ? 1.0f : 0.0f;
     }
-  } else {
+  } else if (SCN == MAPPO_SCN_SIMPLE_REFERENCE) {
     o[k++] = (float)vx; o[k++] = (float)vy;
     for (int l = 0; l < L; ++l) {
       o[k++] = (float)(s.lm[(0 * L + l) * EPB + e] - px);
@@ -154,6 +192,36 @@ __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EP
     for (int c = 0; c < 3; ++c) o[k++] = (float)c_colors_ref[g * 3 + c];
     const int cid = s.comm[(1 - i) * EPB + e];
     for (int c = 0; c < 10; ++c) o[k++] = (c == cid) ? 1.0f : 0.0f;
+  } else {
+    // simple_adversary.py:116-137, simple_push.py:81-104, simple_tag.py:125-144
+    const bool adv = i < nadv;
+    const int g = s.goal[i * EPB + e];
+    if (SCN != MAPPO_SCN_SIMPLE_ADVERSARY) { o[k++] = (float)vx; o[k++] = (float)vy; }
+    if (SCN == MAPPO_SCN_SIMPLE_TAG) { o[k++] = (float)px; o[k++] = (float)py; }
+    if (SCN != MAPPO_SCN_SIMPLE_TAG && !adv) {
+      o[k++] = (float)(s.lm[(0 * L + g) * EPB + e] - px);
+      o[k++] = (float)(s.lm[(1 * L + g) * EPB + e] - py);
+      if (SCN == MAPPO_SCN_SIMPLE_PUSH)                                  // agent.color: 0.25, goal channel + 0.5
+        for (int c = 0; c < 3; ++c) o[k++] = (float)(c == g + 1 ? 0.25 + 0.5 : 0.25);
+    }
+    for (int l = 0; l < L; ++l) {
+      o[k++] = (float)(s.lm[(0 * L + l) * EPB + e] - px);
+      o[k++] = (float)(s.lm[(1 * L + l) * EPB + e] - py);
+    }
+    if (SCN == MAPPO_SCN_SIMPLE_PUSH && !adv)
+      for (int l = 0; l < L; ++l)                                        // landmark.color: 0.1, channel l + 1 + 0.8
+        for (int c = 0; c < 3; ++c) o[k++] = (float)(c == l + 1 ? 0.1 + 0.8 : 0.1);
+    for (int j = 0; j < M; ++j) {
+      if (j == i) continue;
+      o[k++] = (float)(s.pos[(0 * M + j) * EPB + e] - px);
+      o[k++] = (float)(s.pos[(1 * M + j) * EPB + e] - py);
+    }
+    if (SCN == MAPPO_SCN_SIMPLE_TAG)
+      for (int j = nadv; j < M; ++j) {                                   // velocities of the other GOOD agents
+        if (j == i) continue;
+        o[k++] = (float)s.vel[(0 * M + j) * EPB + e];
+        o[k++] = (float)s.vel[(1 * M + j) * EPB + e];
+      }
   }
 }
 
@@ -178,7 +246,7 @@ __device__ __forceinline__ void draw_landmark(uint32_t env_lo, uint32_t ep, uint
   const int base = scn_info(SCN).n_goals + 2 * M + 2 * l;
   x = u32_to_sym(philox_draw(env_lo, ep, base, k0, kStreamReset));
   y = u32_to_sym(philox_draw(env_lo, ep, base + 1, k0, kStreamReset));
-  if (SCN != MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) { x = x * 0.8; y = y * 0.8; }
+  if (scn_info(SCN).landmark_scale != 1.0) { x = x * 0.8; y = y * 0.8; }
 }
 __device__ __forceinline__ int draw_goal(uint32_t env_lo, uint32_t ep, uint32_t k0, int g, int L) {
   const uint32_t d = philox_draw(env_lo, ep, g, k0, kStreamReset);
@@ -186,7 +254,7 @@ __device__ __forceinline__ int draw_goal(uint32_t env_lo, uint32_t ep, uint32_t 
 }
 
 struct StepArgs {
-  int N, M, L, T, EPB, W, ld;
+  int N, M, L, T, EPB, W, ld, nadv;
   uint32_t k0;
   long long env_id_offset;
   mappo_env_state st;
@@ -225,6 +293,7 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
     px = a.st.p_pos[(size_t)(0 * M + i) * N + n]; py = a.st.p_pos[(size_t)(1 * M + i) * N + n];
     vx = a.st.p_vel[(size_t)(0 * M + i) * N + n]; vy = a.st.p_vel[(size_t)(1 * M + i) * N + n];
     s.pos[(0 * M + i) * EPB + e] = px; s.pos[(1 * M + i) * EPB + e] = py;
+    s.vel[(0 * M + i) * EPB + e] = vx; s.vel[(1 * M + i) * EPB + e] = vy;
     s.goal[i * EPB + e] = a.st.goal[(size_t)i * N + n];
     s.comm[i * EPB + e] = a.st.comm[(size_t)i * N + n];
     step = a.st.step_count[n] + (stepping ? 1 : 0);                   // environment.py:118
@@ -253,14 +322,21 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
         double ux = 0.0, uy = 0.0;
         ux += (act == 1 ? 1.0 : 0.0) - (act == 2 ? 1.0 : 0.0);          // environment.py:224-225
         uy += (act == 3 ? 1.0 : 0.0) - (act == 4 ? 1.0 : 0.0);
-        ux *= kSensitivity; uy *= kSensitivity;                          // environment.py:243-246
-        fx = 1.0 * ux + 0.0; fy = 1.0 * uy + 0.0;                        // core.py:237-238 (mass 1, no noise)
+        const double accel = agent_accel_of(SCN, i, a.nadv);
+        if (accel != 0.0) {
+          ux *= accel; uy *= accel;                                      // sensitivity = agent.accel
+          fx = (1.0 * accel) * ux + 0.0; fy = (1.0 * accel) * uy + 0.0;  // (mass * accel) * u + noise
+        } else {
+          ux *= kSensitivity; uy *= kSensitivity;                        // environment.py:243-246
+          fx = 1.0 * ux + 0.0; fy = 1.0 * uy + 0.0;                      // core.py:237-238 (mass 1, no noise)
+        }
       }
       if (!silent) new_comm = (int)arow[head];
-      if (SCN == MAPPO_SCN_SIMPLE_SPREAD) {
-        const double dist_min = si.agent_size + si.agent_size;
+      if (si.collide) {
+        const double my_size = agent_size_of(SCN, i, a.nadv);
         for (int j = 0; j < M; ++j) {                                    // core.py:241-263, pair order = j ascending
           if (j == i) continue;
+          const double dist_min = (i < j) ? my_size + agent_size_of(SCN, j, a.nadv) : agent_size_of(SCN, j, a.nadv) + my_size;
           const double qx = s.pos[(0 * M + j) * EPB + e], qy = s.pos[(1 * M + j) * EPB + e];
           // the reference evaluates the pair once as (a,b) with a<b: delta = p_a - p_b
           const double dx = (i < j) ? (px - qx) : (qx - px), dy = (i < j) ? (py - qy) : (qy - py);
@@ -270,16 +346,31 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
           if (i > j) { gx = -gx; gy = -gy; }                             // force_b = -(1/ratio) * force
           fx = gx + fx; fy = gy + fy;
         }
+        if (si.landmark_collide)
+          for (int l = 0; l < L; ++l) {                                  // (agent, landmark) pairs follow the agent pairs
+            const double dist_min = my_size + si.landmark_size;
+            const double dx = px - s.lm[(0 * L + l) * EPB + e], dy = py - s.lm[(1 * L + l) * EPB + e];
+            const double dist = sqrt(dx * dx + dy * dy);
+            const double pen = logaddexp0(-(dist - dist_min) / kContactMargin) * kContactMargin;
+            const double gx = kContactForce * dx / dist * pen, gy = kContactForce * dy / dist * pen;
+            fx = gx + fx; fy = gy + fy;                                  // core.py:318-320: force_a = +force
+          }
       }
       if (movable) {                                                     // core.py:265-278
         vx = vx * (1 - kDamp); vy = vy * (1 - kDamp);
         vx += (fx / 1.0) * kDt; vy += (fy / 1.0) * kDt;
+        const double vmax = agent_max_speed_of(SCN, i, a.nadv);
+        if (vmax != 0.0) {                                               // core.py:272-277
+          const double speed = sqrt(vx * vx + vy * vy);
+          if (speed > vmax) { vx = vx / speed * vmax; vy = vy / speed * vmax; }
+        }
         px += vx * kDt; py += vy * kDt;
       }
     }
     __syncthreads();                                                     // all reads of old positions done
     if (valid) {
       s.pos[(0 * M + i) * EPB + e] = px; s.pos[(1 * M + i) * EPB + e] = py;
+      s.vel[(0 * M + i) * EPB + e] = vx; s.vel[(1 * M + i) * EPB + e] = vy;
       s.comm[i * EPB + e] = new_comm;                                    // core.py:280-287
     }
     __syncthreads();
@@ -306,6 +397,55 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
         }
         indiv = rew;
       }
+    } else if (SCN == MAPPO_SCN_SIMPLE_ADVERSARY || SCN == MAPPO_SCN_SIMPLE_PUSH) {
+      const int g = valid ? s.goal[0 * EPB + e] : 0;
+      const double gx = s.lm[(0 * L + g) * EPB + e], gy = s.lm[(1 * L + g) * EPB + e];
+      if (valid) {                                                       // every agent's distance to the goal landmark
+        const double dx = px - gx, dy = py - gy;
+        s.aux[(size_t)i * EPB + e] = sqrt(dx * dx + dy * dy);
+      }
+      __syncthreads();
+      if (valid) {
+        double good_min = s.aux[(size_t)a.nadv * EPB + e];
+        for (int k = a.nadv + 1; k < M; ++k) { const double d = s.aux[(size_t)k * EPB + e]; good_min = d < good_min ? d : good_min; }
+        if (SCN == MAPPO_SCN_SIMPLE_ADVERSARY) {                         // simple_adversary.py:69-113
+          if (i < a.nadv) { const double dx = px - gx, dy = py - gy; indiv = -(dx * dx + dy * dy); }
+          else {
+            double adv_rew = 0.0;
+            for (int k = 0; k < a.nadv; ++k) adv_rew = adv_rew + s.aux[(size_t)k * EPB + e];
+            indiv = -good_min + adv_rew;
+          }
+        } else {                                                         // simple_push.py:62-78
+          if (i < a.nadv) { const double dx = gx - px, dy = gy - py; indiv = good_min - sqrt(dx * dx + dy * dy); }
+          else indiv = -s.aux[(size_t)i * EPB + e];
+        }
+      }
+    } else if (SCN == MAPPO_SCN_SIMPLE_TAG) {                            // simple_tag.py:73-123
+      if (valid) {
+        double rew = 0.0;
+        if (i < a.nadv) {
+          for (int ag = a.nadv; ag < M; ++ag)
+            for (int adv = 0; adv < a.nadv; ++adv) {
+              const double dx = s.pos[(0 * M + ag) * EPB + e] - s.pos[(0 * M + adv) * EPB + e];
+              const double dy = s.pos[(1 * M + ag) * EPB + e] - s.pos[(1 * M + adv) * EPB + e];
+              if (sqrt(dx * dx + dy * dy) < agent_size_of(SCN, ag, a.nadv) + agent_size_of(SCN, adv, a.nadv)) rew += 10;
+            }
+        } else {
+          for (int adv = 0; adv < a.nadv; ++adv) {
+            const double dx = s.pos[(0 * M + adv) * EPB + e] - px, dy = s.pos[(1 * M + adv) * EPB + e] - py;
+            if (sqrt(dx * dx + dy * dy) < agent_size_of(SCN, adv, a.nadv) + agent_size_of(SCN, i, a.nadv)) rew -= 10;
+          }
+          for (int p = 0; p < 2; ++p) {                                  // bound(), simple_tag.py:95-104
+            const double x = fabs(p == 0 ? px : py);
+            double b;
+            if (x < 0.9) b = 0.0;
+            else if (x < 1.0) b = (x - 0.9) * 10;
+            else { const double ex = exp(2 * x - 2); b = ex < 10.0 ? ex : 10.0; }
+            rew -= b;
+          }
+        }
+        indiv = rew;
+      }
     } else if (valid) {
       const int who = (SCN == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) ? 1 : 1 - i;   // goal_a
       const int g = s.goal[((SCN == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) ? 0 : i) * EPB + e];
@@ -315,7 +455,7 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
     }
     if (valid) ind[i * EPB + e] = indiv;
     __syncthreads();
-    if (valid) total = np_sum_small(ind + e, EPB, M);                    // environment.py:141-143
+    if (valid) total = si.collaborative ? np_sum_small(ind + e, EPB, M) : indiv;   // environment.py:141-143
   }
 
   // ---- phase 4: reset finished envs (env_wrappers.py:145-154) / all envs (mode 1)
@@ -328,10 +468,12 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
       s.goal[i * EPB + e] = a.rs.goal[(size_t)i * N + n];
     } else {
       draw_agent<SCN>(env_lo, ep, a.k0, i, px, py);
-      s.goal[i * EPB + e] = (i < si.n_goals) ? draw_goal(env_lo, ep, a.k0, i, L) : -1;
+      if (si.shared_goal) s.goal[i * EPB + e] = draw_goal(env_lo, ep, a.k0, 0, L);
+      else s.goal[i * EPB + e] = (i < si.n_goals) ? draw_goal(env_lo, ep, a.k0, i, L) : -1;
     }
     vx = 0.0; vy = 0.0;
     s.pos[(0 * M + i) * EPB + e] = px; s.pos[(1 * M + i) * EPB + e] = py;
+    s.vel[(0 * M + i) * EPB + e] = 0.0; s.vel[(1 * M + i) * EPB + e] = 0.0;
     s.comm[i * EPB + e] = -1;
   }
   for (int idx = tid; idx < EPB * L; idx += blockDim.x) {
@@ -347,7 +489,7 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
   __syncthreads();
 
   // ---- phase 5: observations -> staged tile -> coalesced store
-  if (valid) write_obs<SCN>(s, M, L, EPB, ld, e, i, vx, vy);
+  if (valid) write_obs<SCN>(s, M, L, EPB, ld, e, i, vx, vy, a.nadv);
   __syncthreads();
   store_tile(s.tile, ld, a.W, cnt, a.obs_out + (size_t)n0 * a.W);
 
@@ -373,13 +515,22 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
 
 static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
   MAPPO_REQUIRE(cfg && st, "env: null config/state");
-  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= 2, "env: unknown scenario %d", cfg->scenario);
+  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= MAPPO_SCN_SIMPLE_TAG, "env: unknown scenario %d", cfg->scenario);
   MAPPO_REQUIRE(cfg->num_envs > 0 && cfg->num_agents > 0 && cfg->num_landmarks > 0 && cfg->episode_length > 0,
                 "env: non-positive size");
   MAPPO_REQUIRE(cfg->num_agents <= 16 && cfg->num_landmarks <= 16, "env: at most 16 agents and 16 landmarks");
-  if (cfg->scenario != MAPPO_SCN_SIMPLE_SPREAD)
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER || cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE)
     MAPPO_REQUIRE(cfg->num_agents == 2 && cfg->num_landmarks == 3,
                   "env: only 2 agents is supported (3 landmarks), check the config");  // scenario asserts
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_ADVERSARY)
+    MAPPO_REQUIRE(cfg->num_agents >= 2 && cfg->num_landmarks == cfg->num_agents - 1,
+                  "env: simple_adversary has num_agents - 1 landmarks");               // simple_adversary.py:17
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_PUSH)
+    MAPPO_REQUIRE(cfg->num_agents >= 2 && cfg->num_landmarks <= 2, "env: simple_push has at most 2 landmarks");  // simple_push.py:42
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_TAG) {
+    const int nadv = n_adversaries(cfg->scenario, cfg->num_adversaries);
+    MAPPO_REQUIRE(nadv > 0 && nadv < cfg->num_agents, "env: simple_tag needs 0 < num_adversaries (%d) < num_agents", nadv);
+  }
   MAPPO_REQUIRE(st->p_pos && st->p_vel && st->lm_pos && st->comm && st->goal && st->step_count && st->episode,
                 "env: null state array");
   return 0;
@@ -388,7 +539,8 @@ static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
 static int launch_env(const mappo_env_config* cfg, StepArgs& a, cudaStream_t stream) {
   const int M = cfg->num_agents, L = cfg->num_landmarks;
   a.N = cfg->num_envs; a.M = M; a.L = L; a.T = cfg->episode_length;
-  a.W = mappo_env_obs_width(cfg->scenario, M, L);
+  a.nadv = n_adversaries(cfg->scenario, cfg->num_adversaries);
+  a.W = obs_off_of(cfg->scenario, M, L, M, a.nadv);
   a.ld = tile_ld_of(a.W);
   a.k0 = (uint32_t)(cfg->seed & 0xFFFFFFFFull);
   a.env_id_offset = cfg->env_id_offset;
@@ -407,7 +559,10 @@ static int launch_env(const mappo_env_config* cfg, StepArgs& a, cudaStream_t str
   } while (0)
   if (cfg->scenario == MAPPO_SCN_SIMPLE_SPREAD) LAUNCH_SCN(MAPPO_SCN_SIMPLE_SPREAD);
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) LAUNCH_SCN(MAPPO_SCN_SIMPLE_SPEAKER_LISTENER);
-  else LAUNCH_SCN(MAPPO_SCN_SIMPLE_REFERENCE);
+  else if (cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE) LAUNCH_SCN(MAPPO_SCN_SIMPLE_REFERENCE);
+  else if (cfg->scenario == MAPPO_SCN_SIMPLE_ADVERSARY) LAUNCH_SCN(MAPPO_SCN_SIMPLE_ADVERSARY);
+  else if (cfg->scenario == MAPPO_SCN_SIMPLE_PUSH) LAUNCH_SCN(MAPPO_SCN_SIMPLE_PUSH);
+  else LAUNCH_SCN(MAPPO_SCN_SIMPLE_TAG);
 #undef LAUNCH_SCN
   MAPPO_CHECK_LAUNCH("env_kernel");
   return 0;
@@ -419,6 +574,12 @@ using namespace mappo;
 
 extern "C" int mappo_env_obs_dim(int scenario, int M, int L, int agent) { return obs_dim_of(scenario, M, L, agent); }
 extern "C" int mappo_env_obs_width(int scenario, int M, int L) { return obs_off_of(scenario, M, L, M); }
+extern "C" int mappo_env_obs_dim_cfg(const mappo_env_config* c, int agent) {
+  return c ? obs_dim_of(c->scenario, c->num_agents, c->num_landmarks, agent, c->num_adversaries) : -1;
+}
+extern "C" int mappo_env_obs_width_cfg(const mappo_env_config* c) {
+  return c ? obs_off_of(c->scenario, c->num_agents, c->num_landmarks, c->num_agents, c->num_adversaries) : -1;
+}
 
 extern "C" int mappo_env_reset(const mappo_env_config* cfg, const mappo_env_state* st, float* obs_out,
                                int use_given_state, void* stream) {

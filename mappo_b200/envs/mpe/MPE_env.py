@@ -12,7 +12,8 @@ import torch
 from ... import _lib
 from ..spaces import Box, Discrete, MultiDiscrete, head_sizes
 
-SCENARIOS = {"simple_spread": 0, "simple_speaker_listener": 1, "simple_reference": 2}
+SCENARIOS = {"simple_spread": 0, "simple_speaker_listener": 1, "simple_reference": 2,
+             "simple_adversary": 3, "simple_push": 4, "simple_tag": 5}
 
 
 class _Infos:
@@ -56,16 +57,32 @@ class MPEVecEnv:
         self.n = self.num_agents = int(args.num_agents)
         self.num_landmarks = int(args.num_landmarks)
         self.episode_length = int(args.episode_length)
-        if name != "simple_spread":
+        self.num_adversaries = 0
+        if name in ("simple_speaker_listener", "simple_reference"):
             assert self.num_agents == 2, "only 2 agents is supported, check the config.py."
+        elif name in ("simple_adversary", "simple_push"):
+            self.num_adversaries = 1                                   # simple_adversary.py:16, simple_push.py:14
+            if name == "simple_adversary":
+                self.num_landmarks = self.num_agents - 1               # simple_adversary.py:17 (not args.num_landmarks)
+            else:
+                assert self.num_landmarks <= 2, "simple_push colours at most 2 landmarks (simple_push.py:42)"
+        elif name == "simple_tag":                                     # simple_tag.py:10-13: adversaries first
+            self.num_adversaries = int(getattr(args, "num_adversaries", 0) or 3)
+            good = getattr(args, "num_good_agents", None)
+            if good is not None:
+                self.n = self.num_agents = self.num_adversaries + int(good)
+            assert 0 < self.num_adversaries < self.num_agents
         self.device = torch.device(device)
         L = _lib.lib()
         M, NL, N = self.num_agents, self.num_landmarks, self.num_envs
-        self.obs_dims = [L.mappo_env_obs_dim(self.scenario, M, NL, i) for i in range(M)]
-        self.obs_width = L.mappo_env_obs_width(self.scenario, M, NL)
+        self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length, self.num_adversaries,
+                                   int(seed if seed is not None else getattr(args, "seed", 1)) & (2 ** 64 - 1),
+                                   int(env_id_offset))
+        self.obs_dims = [L.mappo_env_obs_dim_cfg(C.byref(self._cfg), i) for i in range(M)]
+        self.obs_width = L.mappo_env_obs_width_cfg(C.byref(self._cfg))
         self.homogeneous = len(set(self.obs_dims)) == 1
         # spaces (environment.py:54-100)
-        if name == "simple_spread":
+        if name in ("simple_spread", "simple_adversary", "simple_push", "simple_tag"):
             acts = [Discrete(5) for _ in range(M)]
         elif name == "simple_speaker_listener":
             acts = [Discrete(3), Discrete(5)]
@@ -85,9 +102,6 @@ class MPEVecEnv:
         self.goal = torch.full((M, N), -1, dtype=torch.int32, device=dev)
         self.step_count = torch.zeros(N, dtype=torch.int32, device=dev)
         self.episode = torch.zeros(N, dtype=torch.int32, device=dev)
-        self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length, 0,
-                                   int(seed if seed is not None else getattr(args, "seed", 1)) & (2 ** 64 - 1),
-                                   int(env_id_offset))
         self._st = self._state_struct(self)
         # default outputs (callers may pass buffer slots instead)
         self._obs = torch.empty(N, self.obs_width, dtype=torch.float32, device=dev)

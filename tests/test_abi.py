@@ -31,3 +31,16 @@ def test_obs_widths_match_reference_shapes():
     assert L.mappo_env_obs_width(0, 10, 3) == 460 and L.mappo_env_obs_width(0, 10, 10) == 600
     assert L.mappo_env_obs_width(1, 2, 3) == 14 and L.mappo_env_obs_dim(1, 2, 3, 0) == 3
     assert L.mappo_env_obs_width(2, 2, 3) == 42
+
+
+def test_obs_widths_of_the_adversarial_scenarios():
+    """simple_adversary.py:116-137, simple_push.py:81-104, simple_tag.py:125-144 (widths probed on the reference when the
+    env fixtures were recorded: tests/golden/env_{adversary,push,tag}.npz)."""
+    import ctypes as C
+    from mappo_b200 import _lib
+    L = _lib.lib()
+    cfg = lambda scn, M, NL, nadv=0: C.byref(_lib.EnvConfig(scn, 4, M, NL, 25, nadv, 0, 0))
+    assert [L.mappo_env_obs_dim_cfg(cfg(3, 3, 2), i) for i in range(3)] == [8, 10, 10]
+    assert [L.mappo_env_obs_dim_cfg(cfg(4, 2, 2), i) for i in range(2)] == [8, 19]
+    assert [L.mappo_env_obs_dim_cfg(cfg(5, 4, 2, 3), i) for i in range(4)] == [16, 16, 16, 14]
+    assert L.mappo_env_obs_width_cfg(cfg(5, 4, 2, 3)) == 62

@@ -9,12 +9,12 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag"]
 
 
-def make_args(scenario, M, L, T=25, N=4, seed=1):
+def make_args(scenario, M, L, T=25, N=4, seed=1, **kw):
     return types.SimpleNamespace(scenario_name=scenario, num_agents=M, num_landmarks=L, episode_length=T,
-                                 n_rollout_threads=N, seed=seed)
+                                 n_rollout_threads=N, seed=seed, **kw)
 
 
 def f32(x):
@@ -26,7 +26,8 @@ def test_env_matches_reference_fixture(tag, golden_dir):
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
     fx = np.load(os.path.join(golden_dir, "env_%s.npz" % tag))
     N, M, L = int(fx["N"]), int(fx["M"]), int(fx["L"])
-    env = MPEVecEnv(make_args(str(fx["scenario"]), M, L, int(fx["episode_length"]), N), device="cuda")
+    kw = dict(num_adversaries=M - 1, num_good_agents=1) if str(fx["scenario"]) == "simple_tag" else {}
+    env = MPEVecEnv(make_args(str(fx["scenario"]), M, L, int(fx["episode_length"]), N, **kw), device="cuda")
     env.set_state(p_pos=fx["init_p_pos"], p_vel=np.zeros_like(fx["init_p_pos"]), lm_pos=fx["init_lm_pos"],
                   goal=fx["init_goal"])
     obs = env.reset(use_given_state=True)
@@ -63,15 +64,19 @@ def test_env_matches_reference_fixture(tag, golden_dir):
     print(tag, "worst abs obs diff", worst)
 
 
-@pytest.mark.parametrize("scenario,M,L", [("simple_spread", 3, 3), ("simple_spread", 10, 3),
-                                          ("simple_speaker_listener", 2, 3), ("simple_reference", 2, 3)])
-def test_env_matches_oracle_with_philox_resets(scenario, M, L):
+@pytest.mark.parametrize("scenario,M,L,nadv", [("simple_spread", 3, 3, None), ("simple_spread", 10, 3, None),
+                                               ("simple_speaker_listener", 2, 3, None), ("simple_reference", 2, 3, None),
+                                               ("simple_adversary", 3, 2, None), ("simple_adversary", 5, 4, None),
+                                               ("simple_push", 2, 2, None), ("simple_push", 4, 2, None),
+                                               ("simple_tag", 4, 2, 3), ("simple_tag", 6, 3, 2)])
+def test_env_matches_oracle_with_philox_resets(scenario, M, L, nadv):
     """Free-running 60 steps (two auto-resets) at N=1000 with an env-id offset: states equal the oracle's."""
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
     from oracle.mpe import OracleMPE
     N, T, off = 1000, 25, 12345
-    env = MPEVecEnv(make_args(scenario, M, L, T, N, seed=7), device="cuda", env_id_offset=off)
-    orc = OracleMPE(scenario, N, M, L, T, seed=7, env_id_offset=off)
+    kw = dict(num_adversaries=nadv) if nadv else {}
+    env = MPEVecEnv(make_args(scenario, M, L, T, N, seed=7, **kw), device="cuda", env_id_offset=off)
+    orc = OracleMPE(scenario, N, M, L, T, seed=7, env_id_offset=off, **kw)
     o_dev = env.reset()
     o_ref = orc.reset()
     st = env.get_state()
@@ -88,7 +93,7 @@ def test_env_matches_oracle_with_philox_resets(scenario, M, L):
         obs, rew, done, indiv = orc.step(ids)
         want = np.concatenate(obs, axis=-1).astype(np.float32)
         np.testing.assert_allclose(o.view(N, -1).cpu().numpy(), want, rtol=1e-6, atol=1e-7, err_msg="step %d" % s)
-        np.testing.assert_allclose(r.view(N, M).cpu().numpy(), rew[..., 0].astype(np.float32), rtol=1e-6)
+        np.testing.assert_allclose(r.view(N, M).cpu().numpy(), rew[..., 0].astype(np.float32), rtol=1e-6, atol=1e-7)
         st = env.get_state()
         np.testing.assert_allclose(st["p_pos"], orc.p_pos, rtol=1e-11, atol=1e-13)
         assert (st["step_count"] == orc.step_count).all()
@@ -98,6 +103,6 @@ def test_env_matches_oracle_with_philox_resets(scenario, M, L):
 def test_env_rejects_bad_config():
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
     with pytest.raises(NotImplementedError):
-        MPEVecEnv(make_args("simple_tag", 3, 3))
+        MPEVecEnv(make_args("simple_world_comm", 3, 3))
     with pytest.raises(AssertionError):
         MPEVecEnv(make_args("simple_reference", 3, 3))
