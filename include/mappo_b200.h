@@ -119,6 +119,31 @@ int mappo_env_step(const mappo_env_config* cfg, const mappo_env_state* st, const
                    int act_width, float* obs_out, float* rewards_out, float* masks_out,
                    uint8_t* dones_out, float* indiv_out, const mappo_env_state* reset_src, void* stream);
 
+/* envs.render('rgb_array'): headless rasteriser.
+ *    Replaces MultiAgentEnv.render                      onpolicy/envs/mpe/environment.py:263-412
+ *             Viewer.render / FilledPolygon / make_circle onpolicy/envs/mpe/rendering.py:44-112,223-250
+ *    (pyglet window + fixed-function OpenGL in the reference: unavailable on this box; this is a CUDA
+ *    restatement of that raster -- white clear, one 30-gon per entity blended SRC_ALPHA / ONE_MINUS_SRC_ALPHA,
+ *    half-intensity outline of width `line_width`, communication circles last -- into a device buffer.) */
+typedef struct {
+  int32_t width, height;   /* rendering.Viewer(700, 700), environment.py:297; width % 4 == 0 */
+  int32_t num_images;      /* envs to draw */
+  int32_t num_entities;    /* E = M + L: world.entities = agents then landmarks (core.py:142-144) */
+  int32_t res;             /* vertices per circle: 30 (rendering.make_circle) */
+  int32_t reserved;
+  double cam_range;        /* 2 (environment.py:8); shared viewer centred on the origin (environment.py:383-388) */
+  double line_width;       /* glLineWidth(2.0), rendering.py:59 */
+} mappo_render_config;
+/*   env_ids      int32 [num_images] local env index of each image (NULL: image i = env i)
+ *   entity_size  float32 [E]                 entity.size
+ *   entity_rgba  float32 [num_images][E][4]  entity.color + alpha (agents 0.5, landmarks 1; environment.py:315,338)
+ *   comm_dim     int32 [E] or NULL           world.dim_c for non-silent agents (communication circles), else 0
+ *   unit_circle  float64 [res][2]            (cos, sin)(2 pi k / res), computed by the caller (math.cos / math.sin)
+ *   rgb_out      uint8 [num_images][height][width][3], row 0 = top (rendering.py:103 flips the GL buffer) */
+int mappo_env_render(const mappo_env_config* cfg, const mappo_env_state* st, const mappo_render_config* rc,
+                     const int32_t* env_ids, const float* entity_size, const float* entity_rgba,
+                     const int32_t* comm_dim, const double* unit_circle, uint8_t* rgb_out, void* stream);
+
 
 /* ------------------------------------------------------------------------------------------------
  * 2. Returns / GAE / ValueNorm / advantages.

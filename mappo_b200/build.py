@@ -17,8 +17,8 @@ BUILD = os.path.join(CSRC, "build")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 # Sources whose arithmetic must round like numpy's separately-rounded ops (no FMA contraction):
-# the f64 physics and the f32 GAE scan / ValueNorm.
-NO_FMA = {"env_mpe.cu", "gae.cu"}
+# the f64 physics, the f32 GAE scan / ValueNorm and the f64 rasteriser (bit-exact vs oracle/render.py).
+NO_FMA = {"env_mpe.cu", "gae.cu", "render.cu"}
 
 
 def sources():

@@ -264,8 +264,22 @@ class MPEVecEnv:
     def close(self):
         self.closed = True
 
-    def render(self, mode="rgb_array"):
-        raise NotImplementedError("rendering (pyglet/OpenGL in the reference) is unavailable on this box")
+    def render(self, mode="rgb_array", env_ids=None, width=None, height=None, as_numpy=True):
+        """env_wrappers.py:292-297,695-702: `rgb_array` returns the frames of all envs stacked, each env contributing
+        its list of one shared-viewer image -> uint8 [n, 1, 700, 700, 3] (the runner reads `[0][0]`,
+        shared/mpe_runner.py:195).  Rasterised on the device (csrc/render.cu); `env_ids` restricts the envs drawn
+        (default: all, refused above 1 GiB of pixels), `as_numpy=False` keeps the frames in HBM.  `human` needs a
+        window: unavailable on this box."""
+        if mode != "rgb_array":
+            raise NotImplementedError("render(mode=%r): only 'rgb_array' exists without a display" % (mode,))
+        from . import rendering
+        w = rendering.WIDTH if width is None else int(width)
+        h = rendering.HEIGHT if height is None else int(height)
+        n = self.num_envs if env_ids is None else len(env_ids)
+        if n * w * h * 3 > (1 << 30):
+            raise ValueError("render: %d frames of %dx%d exceed 1 GiB; pass env_ids" % (n, w, h))
+        frames = rendering.render_rgb(self, env_ids, w, h).unsqueeze(1)
+        return frames.cpu().numpy() if as_numpy else frames
 
 
 def MPEEnv(args, **kw):
