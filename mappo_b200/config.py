@@ -55,6 +55,12 @@ def get_config():
     p.add_argument("--eval_interval", type=int, default=25)
     p.add_argument("--eval_episodes", type=int, default=32)
     p.add_argument("--model_dir", type=str, default=None)
+    # render parameters (config.py:174,278-282)
+    p.add_argument("--n_render_rollout_threads", type=int, default=1)
+    p.add_argument("--save_gifs", action="store_true", default=False)
+    p.add_argument("--use_render", action="store_true", default=False)
+    p.add_argument("--render_episodes", type=int, default=5)
+    p.add_argument("--ifi", type=float, default=0.1)
     # train_mpe.py:52-61
     p.add_argument("--scenario_name", type=str, default="simple_spread")
     p.add_argument("--num_landmarks", type=int, default=3)

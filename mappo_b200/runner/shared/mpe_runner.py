@@ -126,3 +126,52 @@ class MPERunner(Runner):
         print("eval average episode rewards of agent: " + str(r))
         self.log_env({"eval_average_episode_rewards": [r]}, total_num_steps)
         return r
+
+    @torch.no_grad()
+    def render(self):
+        """mpe_runner.py:185-248: deterministic episodes on `self.envs`, one frame of env 0 after the reset and after
+        every step (`envs.render('rgb_array')[0][0]`), rasterised on the device (csrc/render.cu) and kept in HBM until
+        the episode ends.  With `save_gifs` the frames go to `<run_dir>/gifs/render.gif` (PIL on the host; the
+        reference uses imageio, which is not installed).  `human` mode needs a window: unavailable on this box, so
+        frames are always produced.  Returns (frames uint8 [F, 700, 700, 3] on the host, average episode reward)."""
+        a = self.all_args
+        envs = self.envs
+        N, M = envs.num_envs, self.num_agents
+        pol = self.trainer.policy
+        recurrent = bool(self.buffer._recurrent)
+        frames, ep_rewards = [], []
+        acts = torch.empty(N, M, envs.act_width, dtype=torch.float32, device=self.device)
+        lps = torch.empty_like(acts)
+        for _ in range(int(getattr(a, "render_episodes", 1))):
+            envs.reset()
+            frames.append(envs.render("rgb_array", env_ids=[0], as_numpy=False)[0, 0])
+            rnn = torch.zeros(N, M, self.recurrent_N, self.hidden_size, dtype=torch.float32, device=self.device)
+            rnn_next = torch.zeros_like(rnn)
+            masks = torch.ones(N, M, 1, dtype=torch.float32, device=self.device)
+            total = torch.zeros(N, M, 1, dtype=torch.float32, device=self.device)
+            for _step in range(self.episode_length):
+                if recurrent:
+                    pol.actor.forward_into(envs._obs.view(N * M, -1), acts, lps, deterministic=True, rnn_in=rnn,
+                                           masks=masks, rnn_out=rnn_next)
+                    rnn, rnn_next = rnn_next, rnn
+                else:
+                    pol.actor.forward_into(envs._obs.view(N * M, -1), acts, lps, deterministic=True)
+                _, rew, masks = envs.step_ids(acts)
+                masks = masks.clone()
+                if recurrent:
+                    rnn.mul_(masks.unsqueeze(-1))                              # mpe_runner.py:232
+                total += rew
+                frames.append(envs.render("rgb_array", env_ids=[0], as_numpy=False)[0, 0])
+            ep_rewards.append(total)
+        avg = float(torch.stack(ep_rewards).mean().item())
+        print("average episode rewards is: " + str(avg))
+        out = torch.stack(frames).cpu().numpy()
+        if getattr(a, "save_gifs", False) and self.run_dir is not None:
+            import os
+            from PIL import Image
+            gif_dir = os.path.join(str(self.run_dir), "gifs")
+            os.makedirs(gif_dir, exist_ok=True)
+            imgs = [Image.fromarray(f) for f in out]
+            imgs[0].save(os.path.join(gif_dir, "render.gif"), save_all=True, append_images=imgs[1:],
+                         duration=int(1000 * float(getattr(a, "ifi", 0.1))), loop=0)
+        return out, avg

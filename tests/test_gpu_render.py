@@ -87,3 +87,26 @@ def test_render_rejects_human_mode_and_oversize():
         env.render("human")
     with pytest.raises(AssertionError):
         env.render("rgb_array", width=230, height=64)                   # width must be a multiple of 4
+
+
+@pytest.mark.parametrize("algo,scenario", [("mappo", "simple_spread"), ("rmappo", "simple_reference")])
+def test_runner_render_episode_frames_and_gif(tmp_path, algo, scenario):
+    """runner.render (shared/mpe_runner.py:185-248): one frame after the reset and one per step, env 0; GIF on request."""
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    from mappo_b200.runner.shared.mpe_runner import MPERunner
+    M = 3 if scenario == "simple_spread" else 2
+    a = parse_args(("--algorithm_name %s --scenario_name %s --num_agents %d --num_landmarks 3 --n_rollout_threads 1 "
+                    "--episode_length 6 --render_episodes 2 --save_gifs --use_render --ifi 0.05 --seed 3"
+                    % (algo, scenario, M)).split())
+    envs = MPEVecEnv(a, device="cuda")
+    runner = MPERunner({"all_args": a, "envs": envs, "device": torch.device("cuda"), "num_agents": M,
+                        "run_dir": str(tmp_path)})
+    frames, avg = runner.render()
+    assert frames.shape == (2 * 7, 700, 700, 3) and frames.dtype == np.uint8 and np.isfinite(avg)
+    assert (frames[0] != frames[7]).any(), "the second episode starts from a new reset state"
+    # the last frame is the state the env holds now
+    np.testing.assert_array_equal(frames[-1], envs.render("rgb_array", env_ids=[0])[0, 0])
+    from PIL import Image
+    gif = Image.open(str(tmp_path / "gifs" / "render.gif"))
+    assert gif.n_frames == 14 and gif.size == (700, 700)
