@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define MAPPO_B200_ABI_VERSION 2
+#define MAPPO_B200_ABI_VERSION 3
 
 typedef enum {
   MAPPO_OK = 0,
@@ -238,11 +238,13 @@ long long mappo_net_param_count(const mappo_net_config* cfg);
  *   actions_out, logp_out: float32 [rows][n_heads]  (act.py:65-81: per-head, concatenated)
  * Evaluate mode (R_Actor.evaluate_actions without the backward, act.py:107-162): if `given_actions`
  * (float32 [rows][n_heads]) is not NULL nothing is sampled; logp_out receives log_prob(given action) and
- * entropy_out (float32 [rows], may be NULL) the mean over heads of each row's entropy; actions_out may be NULL. */
+ * entropy_out (float32 [rows], may be NULL) the mean over heads of each row's entropy; actions_out may be NULL.
+ * step_offset (int64 on the device, may be NULL) is added to `step` inside the kernel: a captured CUDA graph of the
+ * rollout keeps its sampling counter in HBM and advances it between launches.  (ABI v3.) */
 int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
                         long long rows, const float* available_actions, int deterministic, uint64_t seed,
                         uint64_t step, long long row_offset, const float* given_actions, float* actions_out,
-                        float* logp_out, float* entropy_out, void* stream);
+                        float* logp_out, float* entropy_out, const int64_t* step_offset, void* stream);
 
 /* Critic forward (R_Critic.forward / get_values): `rows` unique share-obs rows, each value written `group`
  * times: values_out float32 [rows][group] (group = M when the M agents of an env share one share_obs row). */
@@ -352,16 +354,24 @@ typedef struct {
   float bias_correction1;      /* 1 - beta1^t  (t = this step, computed on the host in double) */
   float bias_correction2_sqrt; /* sqrt(1 - beta2^t) */
   float loss_scale;            /* entropy/value coefficients are already inside the gradients: 1.0 */
+  int32_t reserved;
+  double beta1_exact;          /* the betas in double: only read when the step count lives on the device (below) */
+  double beta2_exact;
 } mappo_adam_config;
 
 /* From the reduced sums: finish the chain rule through the folded LayerNorm affines, divide by the loss
  * denominator (loss_sum[denominator_slot], or `rows_total` if use_mean != 0), clip the global L2 norm
  * (nn.utils.clip_grad_norm_, r_mappo.py:143-146) and apply torch.optim.Adam's update in place
  * (rMAPPOPolicy.py:31-37).  grad_out (float32 [P], may be NULL) receives the final (unclipped) gradient;
- * info_out (float32 [4], may be NULL) is ACCUMULATED with {loss, grad_norm, aux (entropy | 0), ratio mean | 0}. */
+ * info_out (float32 [4], may be NULL) is ACCUMULATED with {loss, grad_norm, aux (entropy | 0), ratio mean | 0}.
+ * step_dev (int64 on the device, may be NULL): optimiser step count kept in HBM so that a captured CUDA graph of the
+ * whole iteration replays correctly -- when given, the bias corrections are computed in the kernel from
+ * t = *step_dev + 1 (the host-computed fields of `adam` are ignored) and *step_dev is incremented when
+ * apply_update != 0.  (ABI v3.) */
 int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params, float* exp_avg,
                     float* exp_avg_sq, const float* grad_sum, const double* loss_sum, int denominator_slot,
-                    long long rows_total, int apply_update, float* grad_out, float* info_out, void* stream);
+                    long long rows_total, int apply_update, float* grad_out, float* info_out, long long* step_dev,
+                    void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 4. Minibatch gather (the generator API; the update kernels take `index` and gather in place).

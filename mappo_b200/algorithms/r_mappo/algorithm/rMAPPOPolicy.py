@@ -19,6 +19,11 @@ class FusedAdam:
         self.exp_avg = torch.zeros_like(net.flat)
         self.exp_avg_sq = torch.zeros_like(net.flat)
         self.step_count = 0
+        self.step_dev = None            # int64 device scalar mirroring step_count (CUDA-graph replays)
+
+    def use_device_step(self, on=True):
+        """Keep the step count in HBM: mappo_adam_step then derives the bias corrections from it and increments it."""
+        self.step_dev = torch.tensor(self.step_count, dtype=torch.int64, device=self.exp_avg.device) if on else None
 
     def zero_grad(self):
         pass
@@ -28,7 +33,8 @@ class FusedAdam:
         b1, b2 = g["betas"]
         t = self.step_count + 1
         return ops.AdamConfig(g["lr"], b1, b2, g["eps"], g["weight_decay"], float(max_grad_norm),
-                              int(bool(use_max_grad_norm)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), 1.0)
+                              int(bool(use_max_grad_norm)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), 1.0, 0,
+                              float(b1), float(b2))
 
     def state_dict(self):
         return dict(exp_avg=self.exp_avg.clone(), exp_avg_sq=self.exp_avg_sq.clone(), step=self.step_count,
@@ -36,6 +42,8 @@ class FusedAdam:
 
     def load_state_dict(self, sd):
         self.exp_avg.copy_(sd["exp_avg"]); self.exp_avg_sq.copy_(sd["exp_avg_sq"]); self.step_count = int(sd["step"])
+        if self.step_dev is not None:
+            self.step_dev.fill_(self.step_count)
         self.param_groups = [dict(g) for g in sd["param_groups"]]
 
 

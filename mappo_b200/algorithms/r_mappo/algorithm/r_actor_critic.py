@@ -157,6 +157,13 @@ class R_Actor(_FlatNet):
         self._build(args, obs_shape[0], self.head_dims, False, device)
         self.sample_seed = int(getattr(args, "seed", 1))
         self._calls = 0
+        self.step_dev = None            # int64 device scalar: the sampling counter when a CUDA graph replays the rollout
+
+    def use_device_step(self, on=True):
+        """Keep the sampling counter (Philox counter word 1) in HBM, advanced on the stream after every forward, so
+        a captured rollout draws fresh numbers on every replay.  The stream of draws is the same as with the host
+        counter."""
+        self.step_dev = torch.tensor(self._calls, dtype=torch.int64, device=self.device_) if on else None
 
     def forward(self, obs, rnn_states, masks, available_actions=None, deterministic=False):
         """-> (actions int64 [B, heads], action_log_probs [B, heads], rnn_states)   r_actor_critic.py:43-70"""
@@ -181,11 +188,19 @@ class R_Actor(_FlatNet):
                      row_offset=0, rnn_in=None, masks=None, rnn_out=None):
         """Hot-path entry: writes float32 action ids and log-probs (and, recurrent, the next rnn state) straight into
         buffer slots."""
+        dev_step = self.step_dev if (step is None and not self._recurrent) else None
         if step is None:
             step = self._calls
         self._calls += 1
         if not self.discrete:
             available_actions = None
+        if dev_step is not None:
+            ops.actor_forward(self.cfg, self.flat, obs, actions_out, logp_out,
+                              available_actions=None if available_actions is None else available_actions.contiguous(),
+                              deterministic=deterministic, seed=self.sample_seed, step=0, row_offset=row_offset,
+                              step_offset=dev_step)
+            dev_step.add_(1)
+            return
         if self._recurrent:
             ops.actor_forward_rnn(self.cfg, self.flat, obs, rnn_in, masks, rnn_out, actions_out, logp_out,
                                   available_actions=None if available_actions is None else available_actions.contiguous(),

@@ -108,12 +108,12 @@ class R_MAPPO:
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer
         ops.adam_step(pol.actor.cfg, aopt.config(self.max_grad_norm, self._use_max_grad_norm), pol.actor.flat,
                       aopt.exp_avg, aopt.exp_avg_sq, gsa, lsa, 3, rows_global, ws["grad"][:Pa], self._info[:4],
-                      apply_update=update_actor)
+                      apply_update=update_actor, step_dev=aopt.step_dev)
         if update_actor:
             aopt.step_count += 1
         ops.adam_step(pol.critic.cfg, copt.config(self.max_grad_norm, self._use_max_grad_norm), pol.critic.flat,
                       copt.exp_avg, copt.exp_avg_sq, gsc, lsc, 1, rows_global, ws["grad"][Pa:], self._info[4:],
-                      apply_update=True)
+                      apply_update=True, step_dev=copt.step_dev)
         copt.step_count += 1
         self._info_total += self._info
         return ws
@@ -146,12 +146,12 @@ class R_MAPPO:
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer
         ops.adam_step(pol.actor.cfg, aopt.config(self.max_grad_norm, self._use_max_grad_norm), pol.actor.flat,
                       aopt.exp_avg, aopt.exp_avg_sq, gsa, lsa, 3, rows_global, ws["grad"][:Pa], self._info[:4],
-                      apply_update=update_actor)
+                      apply_update=update_actor, step_dev=aopt.step_dev)
         if update_actor:
             aopt.step_count += 1
         ops.adam_step(pol.critic.cfg, copt.config(self.max_grad_norm, self._use_max_grad_norm), pol.critic.flat,
                       copt.exp_avg, copt.exp_avg_sq, gsc, lsc, 1, rows_global, ws["grad"][Pa:], self._info[4:],
-                      apply_update=True)
+                      apply_update=True, step_dev=copt.step_dev)
         copt.step_count += 1
         self._info_total += self._info
         return ws
@@ -226,6 +226,17 @@ class R_MAPPO:
 
     def train(self, buffer, update_actor=True):
         """r_mappo.py:166-219 on the device-resident buffer."""
+        return self.train_finish(self.train_enqueue(buffer, update_actor))
+
+    def train_finish(self, n_updates):
+        """The only host synchronisation of train(): the six averaged scalars (r_mappo.py:207-219)."""
+        info = (self._info_total / float(n_updates)).cpu().numpy()
+        return {"value_loss": float(info[4]), "policy_loss": float(info[0]), "dist_entropy": float(info[2]),
+                "actor_grad_norm": float(info[1]), "critic_grad_norm": float(info[5]), "ratio": float(info[3])}
+
+    def train_enqueue(self, buffer, update_actor=True):
+        """Everything of train() that runs on the stream (capturable in a CUDA graph when no host permutation is
+        drawn); returns the number of ppo_update calls whose scalars were accumulated in `_info_total`."""
         vn = None if self.value_normalizer is None else self.value_normalizer.stats
         T = buffer.episode_length
         raw, s3 = ops.advantages(buffer.returns[:-1], buffer.value_preds[:-1], buffer.active_masks[:-1], vn,
@@ -263,9 +274,7 @@ class R_MAPPO:
                     self._update(obs_flat, sh, 1, acts, logp, adv, vp, ret, act_m, avail, mbs, index=idx,
                                  share_rows_div=rep, update_actor=update_actor, vn_batch=vn_batch)
                     n_updates += 1
-        info = (self._info_total / float(n_updates)).cpu().numpy()      # the only host sync of train()
-        return {"value_loss": float(info[4]), "policy_loss": float(info[0]), "dist_entropy": float(info[2]),
-                "actor_grad_norm": float(info[1]), "critic_grad_norm": float(info[5]), "ratio": float(info[3])}
+        return n_updates
 
     def prep_training(self):
         pass

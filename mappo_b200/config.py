@@ -55,6 +55,8 @@ def get_config():
     p.add_argument("--eval_interval", type=int, default=25)
     p.add_argument("--eval_episodes", type=int, default=32)
     p.add_argument("--model_dir", type=str, default=None)
+    # not in the reference: replay the whole iteration as one captured CUDA graph (runner/shared/mpe_runner.py)
+    p.add_argument("--use_cuda_graph", action="store_true", default=False)
     # render parameters (config.py:174,278-282)
     p.add_argument("--n_render_rollout_threads", type=int, default=1)
     p.add_argument("--save_gifs", action="store_true", default=False)

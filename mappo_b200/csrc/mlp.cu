@@ -352,12 +352,14 @@ extern "C" long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long
 extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
                                    long long rows, const float* available_actions, int deterministic, uint64_t seed,
                                    uint64_t step, long long row_offset, const float* given_actions,
-                                   float* actions_out, float* logp_out, float* entropy_out, void* stream) {
+                                   float* actions_out, float* logp_out, float* entropy_out,
+                                   const int64_t* step_offset, void* stream) {
   MAPPO_REQUIRE(logp_out && (actions_out || given_actions), "actor_forward: null outputs");
   MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_forward: critic config");
   MlpArgs a{};
   a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.avail = available_actions;
   a.deterministic = deterministic; a.k0 = (uint32_t)(seed & 0xFFFFFFFFull); a.step = (uint32_t)step;
+  a.step_dev = step_offset;
   a.row_offset = row_offset; a.actions_out = actions_out; a.logp_out = logp_out;
   a.given_actions = given_actions; a.entropy_out = entropy_out;
   return launch_mlp<0>(a, cfg, (cudaStream_t)stream, "actor_forward");

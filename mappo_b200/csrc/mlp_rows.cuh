@@ -22,6 +22,7 @@ struct MlpArgs {
   long long ntiles;
   // rollout, actor
   const float* avail; int deterministic; uint32_t k0; uint32_t step; long long row_offset;
+  const int64_t* step_dev;         // device-resident offset added to `step` (CUDA-graph replays), or NULL
   float* actions_out; float* logp_out; const float* given_actions; float* entropy_out;
   // rollout, critic
   float* values_out; int group;
@@ -68,7 +69,8 @@ __device__ __forceinline__ void actor_rollout_row(const MlpArgs& a, long long g,
       float best = lh[0];
       for (int q = 1; q < n; ++q) if (lh[q] > best) { best = lh[q]; pick = q; }
     } else {
-      const u32x4 rnd = philox4x32_10((uint32_t)(a.row_offset + g), a.step, (uint32_t)h, 0u, a.k0, kStreamSample);
+      const uint32_t stp = a.step + (a.step_dev ? (uint32_t)__ldg(a.step_dev) : 0u);
+      const u32x4 rnd = philox4x32_10((uint32_t)(a.row_offset + g), stp, (uint32_t)h, 0u, a.k0, kStreamSample);
       const float u = u32_to_unit_f32(rnd.x);
       float cum = 0.0f;
       pick = n - 1;

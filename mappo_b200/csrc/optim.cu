@@ -76,7 +76,8 @@ __device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const
 __global__ void __launch_bounds__(kOptThreads)
 adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restrict__ params, float* __restrict__ m,
                  float* __restrict__ v, const float* __restrict__ gsum, const double* __restrict__ lsum,
-                 int denom_slot, long long rows_total, int apply_update, float* __restrict__ g, float* info) {
+                 int denom_slot, long long rows_total, int apply_update, float* __restrict__ g, float* info,
+                 long long* step_dev) {
   const int tid = threadIdx.x;
   const int D = L.in_dim, H = L.H;
   // 1. chain rule through the folded affines (net.cuh)
@@ -119,7 +120,13 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
   if (ad.use_max_grad_norm) clip = fminf(ad.max_grad_norm / (norm + 1e-6f), 1.0f);   // clip_grad_norm_: clamp(coef, max=1)
   // 3. Adam (torch.optim.Adam, no amsgrad)
   if (apply_update) {
-    const float step_size = ad.lr / ad.bias_correction1;
+    float bc1 = ad.bias_correction1, bc2s = ad.bias_correction2_sqrt;
+    if (step_dev) {                                     // device-resident step count (CUDA-graph replays): t = *step_dev + 1
+      const double t = (double)(*step_dev + 1);
+      bc1 = (float)(1.0 - pow(ad.beta1_exact, t));
+      bc2s = (float)sqrt(1.0 - pow(ad.beta2_exact, t));
+    }
+    const float step_size = ad.lr / bc1;
     for (int e = tid; e < L.total; e += kOptThreads) {
       float grad = g[e] * clip;
       const float p = params[e];
@@ -127,9 +134,13 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
       const float mm = m[e] + (grad - m[e]) * (1.0f - ad.beta1);                   // exp_avg.lerp_(grad, 1 - beta1)
       const float vv = v[e] * ad.beta2 + (1.0f - ad.beta2) * grad * grad;          // mul_(beta2).addcmul_(g, g, 1 - beta2)
       m[e] = mm; v[e] = vv;
-      const float den = sqrtf(vv) / ad.bias_correction2_sqrt + ad.eps;
+      const float den = sqrtf(vv) / bc2s + ad.eps;
       params[e] = p - step_size * (mm / den);
     }
+  }
+  if (step_dev && apply_update) {
+    __syncthreads();                                    // every thread has read the count
+    if (tid == 0) *step_dev += 1;
   }
   // 4. train_info accumulation: {loss, grad_norm, entropy, ratio}
   if (info && tid == 0) {
@@ -158,7 +169,7 @@ extern "C" int mappo_grad_reduce(const float* grad_partials, const double* loss_
 extern "C" int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params,
                                float* exp_avg, float* exp_avg_sq, const float* grad_sum, const double* loss_sum,
                                int denominator_slot, long long rows_total, int apply_update, float* grad_out,
-                               float* info_out, void* stream) {
+                               float* info_out, long long* step_dev, void* stream) {
   if (int rc = check_net(cfg, "adam_step")) return rc;
   MAPPO_REQUIRE(adam && params && grad_sum && loss_sum && grad_out, "adam_step: null pointer (grad_out is required)");
   MAPPO_REQUIRE(!apply_update || (exp_avg && exp_avg_sq), "adam_step: null optimiser state");
@@ -166,7 +177,7 @@ extern "C" int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_con
   const NetLayout L = make_layout(*cfg);
   adam_step_kernel<<<1, kOptThreads, 0, (cudaStream_t)stream>>>(L, *adam, params, exp_avg, exp_avg_sq, grad_sum,
                                                                loss_sum, denominator_slot, rows_total, apply_update,
-                                                               grad_out, info_out);
+                                                               grad_out, info_out, step_dev);
   MAPPO_CHECK_LAUNCH("adam_step_kernel");
   return 0;
 }

@@ -151,19 +151,20 @@ class LossConfig(C.Structure):
 class AdamConfig(C.Structure):
     _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
                 ("weight_decay", C.c_float), ("max_grad_norm", C.c_float), ("use_max_grad_norm", C.c_int32),
-                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("loss_scale", C.c_float)]
+                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("loss_scale", C.c_float),
+                ("reserved", C.c_int32), ("beta1_exact", C.c_double), ("beta2_exact", C.c_double)]
 
 
 _NC, _LC, _AC = C.POINTER(NetConfig), C.POINTER(LossConfig), C.POINTER(AdamConfig)
 _lib._EXTRA_SIGS.update({
     "mappo_actor_forward": [_NC, _P, _P, C.c_int, C.c_longlong, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_longlong,
-                            _P, _P, _P, _P, _P],
+                            _P, _P, _P, _P, _P, _P],
     "mappo_advantages": [_P, _P, _P, _P, C.c_longlong, _P, _P, _P],
     "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
     "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P],
     "mappo_grad_reduce": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
-    "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
+    "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P],
 })
 
 
@@ -195,13 +196,15 @@ def _vp(t):
 
 
 def actor_forward(cfg, params, obs, actions_out, logp_out, available_actions=None, deterministic=False, seed=0,
-                  step=0, row_offset=0, given_actions=None, entropy_out=None):
+                  step=0, row_offset=0, given_actions=None, entropy_out=None, step_offset=None):
+    """step_offset: int64 device scalar added to `step` in the kernel (CUDA-graph replays), or None."""
     obs, ld = _rows_view(obs)
     with TIMERS.span("actor_forward"):
         check(_lib.lib().mappo_actor_forward(C.byref(cfg), ptr(params), _vp(obs), ld, obs.shape[0],
                                              ptr(available_actions), int(deterministic), int(seed) & (2 ** 64 - 1),
                                              int(step), int(row_offset), ptr(given_actions), ptr(actions_out),
-                                             ptr(logp_out), ptr(entropy_out), stream_ptr()), "actor_forward")
+                                             ptr(logp_out), ptr(entropy_out), ptr(step_offset), stream_ptr()),
+              "actor_forward")
 
 
 def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=None, all_reduce=None):
@@ -365,7 +368,10 @@ def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):
 
 
 def adam_step(cfg, adam, params, exp_avg, exp_avg_sq, grad_sum, loss_sum, denominator_slot, rows_total, grad_out,
-              info_out=None, apply_update=True):
+              info_out=None, apply_update=True, step_dev=None):
+    """step_dev: int64 device scalar holding the optimiser step count (read for the bias corrections and incremented
+    by the kernel), or None for the host-computed corrections in `adam`."""
     check(_lib.lib().mappo_adam_step(C.byref(cfg), C.byref(adam), ptr(params), ptr(exp_avg), ptr(exp_avg_sq),
                                      ptr(grad_sum), ptr(loss_sum), int(denominator_slot), int(rows_total),
-                                     int(apply_update), ptr(grad_out), ptr(info_out), stream_ptr()), "adam_step")
+                                     int(apply_update), ptr(grad_out), ptr(info_out), ptr(step_dev), stream_ptr()),
+          "adam_step")

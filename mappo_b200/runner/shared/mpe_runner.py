@@ -15,6 +15,12 @@ class MPERunner(Runner):
     def __init__(self, config):
         super(MPERunner, self).__init__(config)
         self._last_infos = None
+        # --use_cuda_graph: the whole iteration (T x {actor, critic, env step}, bootstrap value, GAE, every ppo_update,
+        # after_update) is captured once and replayed as ONE graph launch per iteration
+        self.use_cuda_graph = bool(getattr(self.all_args, "use_cuda_graph", False))
+        self._graph = None
+        self._graph_state = 0            # 0: counters still on the host; 1: one eager iteration done; 2: captured
+        self._graph_updates = 0
 
     def run(self):
         self.warmup()
@@ -47,6 +53,54 @@ class MPERunner(Runner):
         """One iteration: episode_length x (collect, step, insert), compute, train (mpe_runner.py:24-40)."""
         if self.use_linear_lr_decay:
             self.trainer.policy.lr_decay(episode, episodes)
+        if self._graph_eligible():
+            return self._run_episode_graph()
+        self._rollout()
+        self.compute()
+        return self.train()
+
+    def _graph_eligible(self):
+        """A graph replays fixed launches: nothing on the path may depend on host state that changes between
+        iterations.  That rules out host-drawn permutations (num_mini_batch > 1, the recurrent generators), a learning
+        rate schedule, the NCCL hooks and per-kernel event timing; the sampling counter and the Adam step counts move
+        into HBM (R_Actor.use_device_step, FusedAdam.use_device_step)."""
+        from ... import ops
+        t, b = self.trainer, self.buffer
+        return (self.use_cuda_graph and not b._recurrent and t.num_mini_batch == 1 and not b.force_permutation
+                and not self.use_linear_lr_decay and t.all_reduce is None and not ops.TIMERS.enabled)
+
+    def _iteration_on_stream(self):
+        self._rollout()
+        self.compute()
+        self.trainer.prep_training()
+        n = self.trainer.train_enqueue(self.buffer)
+        self.buffer.after_update()
+        return n
+
+    def _run_episode_graph(self):
+        pol = self.trainer.policy
+        if self._graph_state == 0:
+            # iteration 1 runs eagerly with the device counters: every lazily created workspace and kernel attribute
+            # exists before the capture
+            pol.actor.use_device_step(); pol.actor_optimizer.use_device_step(); pol.critic_optimizer.use_device_step()
+            self._graph_state = 1
+            n = self._iteration_on_stream()
+            return self.trainer.train_finish(n)
+        if self._graph_state == 1:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._graph_updates = self._iteration_on_stream()     # records the launches; host counters advance once
+            self._graph, self._graph_state = g, 2
+        else:
+            # host mirrors of the counters the graph advances on the device
+            pol.actor._calls += self.episode_length
+            pol.actor_optimizer.step_count += self._graph_updates
+            pol.critic_optimizer.step_count += self._graph_updates
+        self._graph.replay()
+        return self.trainer.train_finish(self._graph_updates)
+
+    def _rollout(self):
         for step in range(self.episode_length):
             values, actions, action_log_probs, rnn_states, rnn_states_critic, actions_env = self.collect(step)
             obs, rewards, masks = self.envs.step_ids(actions_env, out_obs=self.buffer.obs[step + 1],
@@ -54,8 +108,6 @@ class MPERunner(Runner):
                                                      out_masks=self.buffer.masks[step + 1])
             data = obs, rewards, masks, None, values, actions, action_log_probs, rnn_states, rnn_states_critic
             self.insert(data)
-        self.compute()
-        return self.train()
 
     def warmup(self):
         """mpe_runner.py:81-93: reset; obs[0] (and through the view share_obs[0]) receive the first observation."""

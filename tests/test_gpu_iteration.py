@@ -26,3 +26,51 @@ def test_full_iteration_recurrent_gru_reference_scenario():
 def test_full_iteration_naive_recurrent():
     import __graft_entry__ as g
     g._smoke_iteration(M=3, N=32, extra="--use_naive_recurrent_policy --num_mini_batch 2")
+
+
+def _make_runner(extra, N=192, M=3):
+    import torch
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    from mappo_b200.runner.shared.mpe_runner import MPERunner
+    a = parse_args(("--scenario_name simple_spread --num_agents %d --num_landmarks 3 --n_rollout_threads %d "
+                    "--episode_length 25 --ppo_epoch 3 --lr 7e-4 --critic_lr 7e-4 --seed 5 %s" % (M, N, extra)).split())
+    torch.manual_seed(11)
+    envs = MPEVecEnv(a, device="cuda:0")
+    r = MPERunner({"all_args": a, "envs": envs, "device": torch.device("cuda:0"), "num_agents": M, "run_dir": None})
+    r.warmup()
+    return r
+
+
+@pytest.mark.parametrize("M", [3, 10])
+def test_cuda_graph_iteration_equals_eager(M):
+    """--use_cuda_graph: iteration 1 eager with device-resident counters, iteration 2 captured,
+    iterations 3+ replayed.  Same Philox streams and the same kernels as the eager runner, so the sampled actions are
+    identical; the Adam bias corrections come from pow() on the device instead of the host (<= 1 ulp of float32 apart),
+    hence a tolerance on the parameters instead of equality."""
+    import numpy as np
+    import torch
+    eager, graph = _make_runner("", M=M), _make_runner("--use_cuda_graph", M=M)
+    assert graph._graph_eligible() and not eager._graph_eligible()
+    for it in range(5):
+        ie, ig = eager.run_episode(), graph.run_episode()
+        same = (eager.buffer.actions == graph.buffer.actions).float().mean().item()
+        assert same > 0.999, "iteration %d: sampled actions diverge (%.5f)" % (it, same)
+        for k in ie:
+            np.testing.assert_allclose(ig[k], ie[k], rtol=2e-4, atol=1e-6, err_msg="iteration %d %s" % (it, k))
+    assert graph._graph_state == 2 and graph._graph is not None
+    pe, pg = eager.policy, graph.policy
+    torch.testing.assert_close(pg.actor.flat, pe.actor.flat, rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(pg.critic.flat, pe.critic.flat, rtol=1e-4, atol=1e-6)
+    # host mirrors of the device counters stay in step
+    assert pg.actor._calls == pe.actor._calls == int(pg.actor.step_dev.item())
+    assert pg.actor_optimizer.step_count == pe.actor_optimizer.step_count == int(pg.actor_optimizer.step_dev.item())
+    assert pg.critic_optimizer.step_count == int(pg.critic_optimizer.step_dev.item())
+    torch.testing.assert_close(graph.trainer.value_normalizer.stats, eager.trainer.value_normalizer.stats, rtol=1e-5, atol=0)
+
+
+def test_cuda_graph_not_used_where_the_host_draws_permutations():
+    r = _make_runner("--use_cuda_graph --num_mini_batch 2")
+    assert not r._graph_eligible()
+    r.run_episode()
+    assert r._graph_state == 0
