@@ -62,7 +62,10 @@ typedef enum {
    * (individual rewards; simple_tag adds per-agent size / accel / max_speed and obstacle landmarks) */
   MAPPO_SCN_SIMPLE_ADVERSARY = 3,
   MAPPO_SCN_SIMPLE_PUSH = 4,
-  MAPPO_SCN_SIMPLE_TAG = 5
+  MAPPO_SCN_SIMPLE_TAG = 5,
+  /* scenarios/simple_crypto.py:21-171 (= simple_crypto_display.py without its prints): three immobile agents
+   * (adversary, listener, speaker) exchanging 4-colour words; goal slot 0 = goal landmark, slot 1 = key landmark */
+  MAPPO_SCN_SIMPLE_CRYPTO = 6
 } mappo_scenario;
 
 typedef struct {

@@ -44,6 +44,8 @@ __host__ __device__ inline ScnInfo scn_info(int scn) {
     s.dim_c = 2; s.n_goals = 1; s.collide = 0; s.agent_size = 0.15; s.landmark_scale = 1.0; s.shared_goal = 1; s.collaborative = 0;
   } else if (scn == MAPPO_SCN_SIMPLE_PUSH) {
     s.dim_c = 2; s.n_goals = 1; s.collide = 1; s.agent_size = 0.05; s.landmark_scale = 0.8; s.shared_goal = 1; s.collaborative = 0;
+  } else if (scn == MAPPO_SCN_SIMPLE_CRYPTO) {  // simple_crypto.py:21-47: nobody moves, everybody speaks; goal + key landmark
+    s.dim_c = 4; s.n_goals = 2; s.collide = 0; s.agent_size = 0.05; s.landmark_scale = 1.0; s.collaborative = 0;
   } else {  // simple_tag: sizes / accel / max_speed depend on the agent's side, see agent_* below
     s.dim_c = 2; s.n_goals = 0; s.collide = 1; s.agent_size = 0.05; s.landmark_scale = 0.8; s.collaborative = 0;
     s.landmark_collide = 1; s.landmark_size = 0.2;
@@ -52,7 +54,7 @@ __host__ __device__ inline ScnInfo scn_info(int scn) {
 }
 // adversaries come first (agent i is one iff i < nadv); simple_adversary / simple_push have exactly one
 __host__ __device__ inline int n_adversaries(int scn, int cfg_nadv) {
-  if (scn == MAPPO_SCN_SIMPLE_ADVERSARY || scn == MAPPO_SCN_SIMPLE_PUSH) return 1;
+  if (scn == MAPPO_SCN_SIMPLE_ADVERSARY || scn == MAPPO_SCN_SIMPLE_PUSH || scn == MAPPO_SCN_SIMPLE_CRYPTO) return 1;
   if (scn == MAPPO_SCN_SIMPLE_TAG) return cfg_nadv > 0 ? cfg_nadv : 3;              // simple_tag.py:12 default
   return 0;
 }
@@ -74,6 +76,7 @@ __host__ __device__ inline int obs_dim_of(int scn, int M, int L, int agent, int 
   if (scn == MAPPO_SCN_SIMPLE_REFERENCE) return 2 + 2 * L + 3 + 10;
   if (scn == MAPPO_SCN_SIMPLE_ADVERSARY) return (agent < nadv ? 0 : 2) + 2 * L + 2 * (M - 1);
   if (scn == MAPPO_SCN_SIMPLE_PUSH) return agent < nadv ? 2 + 2 * L + 2 * (M - 1) : 2 + 2 + 3 + 2 * L + 3 * L + 2 * (M - 1);
+  if (scn == MAPPO_SCN_SIMPLE_CRYPTO) return agent == 0 ? 4 : 8;                      // simple_crypto.py:160-171
   const int good_others = (M - nadv) - (agent < nadv ? 0 : 1);
   return 4 + 2 * L + 2 * (M - 1) + 2 * good_others;
 }
@@ -83,12 +86,12 @@ __host__ __device__ inline int obs_off_of(int scn, int M, int L, int agent, int 
   return o;
 }
 __host__ __device__ inline bool is_movable(int scn, int agent) {
+  if (scn == MAPPO_SCN_SIMPLE_CRYPTO) return false;                                   // simple_crypto.py:33
   return !(scn == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER && agent == 0);
 }
 __host__ __device__ inline bool is_silent(int scn, int agent) {
-  if (scn == MAPPO_SCN_SIMPLE_SPREAD) return true;
   if (scn == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) return agent == 1;
-  return false;
+  return !(scn == MAPPO_SCN_SIMPLE_REFERENCE || scn == MAPPO_SCN_SIMPLE_CRYPTO);      // every other scenario: silent = True
 }
 
 // np.logaddexp(0, y)   (numpy npy_logaddexp with x = 0)
@@ -192,6 +195,13 @@ __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EP
     for (int c = 0; c < 3; ++c) o[k++] = (float)c_colors_ref[g * 3 + c];
     const int cid = s.comm[(1 - i) * EPB + e];
     for (int c = 0; c < 10; ++c) o[k++] = (c == cid) ? 1.0f : 0.0f;
+  } else if (SCN == MAPPO_SCN_SIMPLE_CRYPTO) {
+    // simple_crypto.py:127-171: landmark l's colour is the unit vector e_l of the 4 colour channels (:54-58);
+    // goal slot 0 = the goal landmark, slot 1 = the landmark whose colour is the speaker's key
+    const int g = s.goal[0 * EPB + e], key = s.goal[1 * EPB + e], said = s.comm[2 * EPB + e];
+    if (i == 2) for (int c = 0; c < 4; ++c) o[k++] = (c == g) ? 1.0f : 0.0f;           // speaker: goal colour, key
+    if (i >= 1) for (int c = 0; c < 4; ++c) o[k++] = (c == key) ? 1.0f : 0.0f;         // listener: key, utterance
+    if (i <= 1) for (int c = 0; c < 4; ++c) o[k++] = (c == said) ? 1.0f : 0.0f;        // adversary: utterance only
   } else {
     // simple_adversary.py:116-137, simple_push.py:81-104, simple_tag.py:125-144
     const bool adv = i < nadv;
@@ -446,6 +456,15 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
         }
         indiv = rew;
       }
+    } else if (SCN == MAPPO_SCN_SIMPLE_CRYPTO) {                         // simple_crypto.py:90-125
+      if (valid) {
+        // sum((c - goal_colour)^2) for one-hot c: 0 if the word is the goal's channel else 2; 0 while nothing was said
+        const int g = s.goal[0 * EPB + e];
+        const int c_adv = s.comm[0 * EPB + e], c_good = s.comm[1 * EPB + e];
+        const double adv_err = (c_adv < 0 || c_adv == g) ? 0.0 : 2.0;
+        const double good_err = (c_good < 0 || c_good == g) ? 0.0 : 2.0;
+        indiv = (i == 0) ? 0.0 - adv_err : adv_err + (0.0 - good_err);
+      }
     } else if (valid) {
       const int who = (SCN == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) ? 1 : 1 - i;   // goal_a
       const int g = s.goal[((SCN == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) ? 0 : i) * EPB + e];
@@ -515,7 +534,7 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
 
 static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
   MAPPO_REQUIRE(cfg && st, "env: null config/state");
-  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= MAPPO_SCN_SIMPLE_TAG, "env: unknown scenario %d", cfg->scenario);
+  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= MAPPO_SCN_SIMPLE_CRYPTO, "env: unknown scenario %d", cfg->scenario);
   MAPPO_REQUIRE(cfg->num_envs > 0 && cfg->num_agents > 0 && cfg->num_landmarks > 0 && cfg->episode_length > 0,
                 "env: non-positive size");
   MAPPO_REQUIRE(cfg->num_agents <= 16 && cfg->num_landmarks <= 16, "env: at most 16 agents and 16 landmarks");
@@ -527,6 +546,9 @@ static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
                   "env: simple_adversary has num_agents - 1 landmarks");               // simple_adversary.py:17
   if (cfg->scenario == MAPPO_SCN_SIMPLE_PUSH)
     MAPPO_REQUIRE(cfg->num_agents >= 2 && cfg->num_landmarks <= 2, "env: simple_push has at most 2 landmarks");  // simple_push.py:42
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_CRYPTO)
+    MAPPO_REQUIRE(cfg->num_agents == 3 && cfg->num_landmarks <= 4,
+                  "env: simple_crypto has 3 agents and at most 4 landmarks (dim_c colours)");  // simple_crypto.py:27-31,54-58
   if (cfg->scenario == MAPPO_SCN_SIMPLE_TAG) {
     const int nadv = n_adversaries(cfg->scenario, cfg->num_adversaries);
     MAPPO_REQUIRE(nadv > 0 && nadv < cfg->num_agents, "env: simple_tag needs 0 < num_adversaries (%d) < num_agents", nadv);
@@ -562,6 +584,7 @@ static int launch_env(const mappo_env_config* cfg, StepArgs& a, cudaStream_t str
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE) LAUNCH_SCN(MAPPO_SCN_SIMPLE_REFERENCE);
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_ADVERSARY) LAUNCH_SCN(MAPPO_SCN_SIMPLE_ADVERSARY);
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_PUSH) LAUNCH_SCN(MAPPO_SCN_SIMPLE_PUSH);
+  else if (cfg->scenario == MAPPO_SCN_SIMPLE_CRYPTO) LAUNCH_SCN(MAPPO_SCN_SIMPLE_CRYPTO);
   else LAUNCH_SCN(MAPPO_SCN_SIMPLE_TAG);
 #undef LAUNCH_SCN
   MAPPO_CHECK_LAUNCH("env_kernel");

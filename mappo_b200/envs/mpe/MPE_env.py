@@ -13,7 +13,8 @@ from ... import _lib
 from ..spaces import Box, Discrete, MultiDiscrete, head_sizes
 
 SCENARIOS = {"simple_spread": 0, "simple_speaker_listener": 1, "simple_reference": 2,
-             "simple_adversary": 3, "simple_push": 4, "simple_tag": 5}
+             "simple_adversary": 3, "simple_push": 4, "simple_tag": 5,
+             "simple_crypto": 6, "simple_crypto_display": 6}      # the display variant only adds prints
 
 
 class _Infos:
@@ -66,6 +67,9 @@ class MPEVecEnv:
                 self.num_landmarks = self.num_agents - 1               # simple_adversary.py:17 (not args.num_landmarks)
             else:
                 assert self.num_landmarks <= 2, "simple_push colours at most 2 landmarks (simple_push.py:42)"
+        elif name in ("simple_crypto", "simple_crypto_display"):       # simple_crypto.py:27-31
+            assert self.num_agents == 3, "simple_crypto: adversary, listener, speaker"
+            self.num_adversaries = 1
         elif name == "simple_tag":                                     # simple_tag.py:10-13: adversaries first
             self.num_adversaries = int(getattr(args, "num_adversaries", 0) or 3)
             good = getattr(args, "num_good_agents", None)
@@ -86,6 +90,8 @@ class MPEVecEnv:
             acts = [Discrete(5) for _ in range(M)]
         elif name == "simple_speaker_listener":
             acts = [Discrete(3), Discrete(5)]
+        elif name in ("simple_crypto", "simple_crypto_display"):
+            acts = [Discrete(4) for _ in range(M)]                     # immobile, not silent: the word (dim_c = 4)
         else:
             acts = [MultiDiscrete([[0, 4], [0, 9]]) for _ in range(M)]
         self.action_space = acts

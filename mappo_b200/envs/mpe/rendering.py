@@ -48,7 +48,7 @@ def entity_sizes(env):
     elif name == "simple_tag":
         a = [0.075 if i < nadv else 0.05 for i in range(M)]            # simple_tag.py:21,31
         l = [0.2] * L
-    else:                                                              # simple_reference, simple_push: defaults
+    else:                                                              # simple_reference, simple_push, simple_crypto
         a, l = [0.05] * M, [0.05] * L
     return np.asarray(a + l, dtype=np.float32)
 
@@ -61,6 +61,8 @@ def comm_dims(env):
         d[0] = 3                                                       # the speaker; the listener is silent (:26)
     elif name == "simple_reference":
         d[:M] = [10] * M
+    elif name in ("simple_crypto", "simple_crypto_display"):
+        d[:M] = [4] * M
     return np.asarray(d, dtype=np.int32)
 
 
@@ -99,6 +101,11 @@ def entity_rgba(env, env_ids):
             bump[j, j + 1] = 0.5
         for i in range(M):
             rgb[:, i] = t(_ADV) if i < nadv else t(_GREY) + bump[goal[:, i]]
+    elif name in ("simple_crypto", "simple_crypto_display"):           # simple_crypto.py:50-66
+        rgb[:, :M] = t([_ADV, _GREY, _GREY])
+        lm = torch.eye(4, dtype=torch.float32, device=dev)[:L, :3]     # colour e_l; only r, g, b reach the rasteriser
+        rgb[:, M:] = lm
+        rgb[:, 1] = lm[goal[:, 0]]                                     # world.agents[1].color = goal.color
     else:
         raise NotImplementedError(name)
     alpha = torch.ones(n, M + L, 1, dtype=torch.float32, device=dev)

@@ -132,6 +132,20 @@ class ScenarioSpec:
             n_good = M - n_adv
             self.obs_dims = [4 + 2 * L + 2 * (M - 1) + 2 * n_good] * n_adv + \
                             [4 + 2 * L + 2 * (M - 1) + 2 * (n_good - 1)] * n_good
+        elif name in ("simple_crypto", "simple_crypto_display"):         # simple_crypto.py:21-47 (display: same + prints)
+            assert M == 3 and 1 <= L <= 4, "simple_crypto: 3 agents (adversary, listener, speaker), dim_c = 4 colours"
+            self.name = "simple_crypto"
+            self.dim_c = 4
+            self.movable = [False] * M
+            self.silent = [False] * M
+            self.collide = False
+            self.agent_size = 0.05
+            self.landmark_scale = 1.0
+            self.n_goals = 2                                            # goal landmark, key landmark
+            self.n_adv = 1
+            self.collaborative = False
+            self.obs_dims = [4, 8, 8]
+            self.act_heads = [[4]] * M                                  # not movable, not silent: Discrete(dim_c)
         else:
             raise NotImplementedError(name)
         if name in ("simple_adversary", "simple_push", "simple_tag"):
@@ -328,6 +342,15 @@ class OracleMPE:
                         c[:, l + 1] += 0.8
                         lm_colors.append(c)
                     o = np.concatenate([self.p_vel[:, i], goal_pos - pos_i, color] + ent + lm_colors + other, axis=-1)
+            elif sp.name == "simple_crypto":                            # simple_crypto.py:127-171
+                goal_color = np.eye(4)[self.goal[:, 0]]                 # landmark i's colour is e_i (:54-58)
+                key = np.eye(4)[self.goal[:, 1]]
+                if i == 2:
+                    o = np.concatenate([goal_color, key], axis=-1)      # speaker
+                elif i == 1:
+                    o = np.concatenate([key, self.comm[:, 2]], axis=-1)  # good listener
+                else:
+                    o = self.comm[:, 2].copy()                          # adversary: the speaker's utterance only
             else:                                                       # simple_tag.py:125-144
                 other = [self.p_pos[:, j] - pos_i for j in range(M) if j != i]
                 other_vel = [self.p_vel[:, j] for j in range(M) if j != i and j >= sp.n_adv]
@@ -380,6 +403,15 @@ class OracleMPE:
                         r[:, i] = good_min - neg
                     else:
                         r[:, i] = -dist[i]
+        elif sp.name == "simple_crypto":                                # simple_crypto.py:90-125
+            goal_color = np.eye(4)[self.goal[:, 0]]
+            def sq_err(a):                                              # 0 while the agent has not spoken (:103,:122)
+                spoke = (self.comm[:, a] != 0).any(axis=-1)
+                return np.where(spoke, np.sum(np.square(self.comm[:, a] - goal_color), axis=-1), 0.0)
+            adv_err, good_err = sq_err(0), sq_err(1)
+            r[:, 0] = 0.0 - adv_err
+            r[:, 1] = adv_err + (0.0 - good_err)
+            r[:, 2] = adv_err + (0.0 - good_err)
         else:                                                           # simple_tag.py:73-123
             def hit(a, b):
                 d = np.sqrt(np.sum(np.square(self.p_pos[:, a] - self.p_pos[:, b]), axis=-1))

@@ -42,6 +42,11 @@ def world_state(env):
                 return w.landmarks.index(g)
         return -1
     goal = np.array([goal_of(a) for a in w.agents])
+    if hasattr(w.agents[0], "key"):
+        # simple_crypto.py:63-69: slot 0 = the goal landmark (goal_a of every agent), slot 1 = the landmark whose
+        # colour is the speaker's key, slot 2 unused
+        key = w.agents[2].key
+        goal = np.array([goal[0], -1 if key is None else int(np.argmax(key)), -1])
     return p_pos, p_vel, lm, comm, goal
 
 
@@ -131,7 +136,8 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
 
 ENV_FIXTURES = (("simple_spread", 3, 3, "spread_m3"), ("simple_spread", 10, 3, "spread_m10"),
                 ("simple_speaker_listener", 2, 3, "speaker_listener"), ("simple_reference", 2, 3, "reference"),
-                ("simple_adversary", 3, 2, "adversary"), ("simple_push", 2, 2, "push"), ("simple_tag", 4, 2, "tag"))
+                ("simple_adversary", 3, 2, "adversary"), ("simple_push", 2, 2, "push"), ("simple_tag", 4, 2, "tag"),
+                ("simple_crypto", 3, 2, "crypto"))
 
 
 def gen_env(only=None):

@@ -44,3 +44,5 @@ def test_obs_widths_of_the_adversarial_scenarios():
     assert [L.mappo_env_obs_dim_cfg(cfg(4, 2, 2), i) for i in range(2)] == [8, 19]
     assert [L.mappo_env_obs_dim_cfg(cfg(5, 4, 2, 3), i) for i in range(4)] == [16, 16, 16, 14]
     assert L.mappo_env_obs_width_cfg(cfg(5, 4, 2, 3)) == 62
+    # simple_crypto.py:160-171 (tests/golden/env_crypto.npz): adversary 4, listener 8, speaker 8
+    assert [L.mappo_env_obs_dim_cfg(cfg(6, 3, 2), i) for i in range(3)] == [4, 8, 8]

@@ -9,7 +9,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto"]
 
 
 def make_args(scenario, M, L, T=25, N=4, seed=1, **kw):
@@ -68,7 +68,8 @@ def test_env_matches_reference_fixture(tag, golden_dir):
                                                ("simple_speaker_listener", 2, 3, None), ("simple_reference", 2, 3, None),
                                                ("simple_adversary", 3, 2, None), ("simple_adversary", 5, 4, None),
                                                ("simple_push", 2, 2, None), ("simple_push", 4, 2, None),
-                                               ("simple_tag", 4, 2, 3), ("simple_tag", 6, 3, 2)])
+                                               ("simple_tag", 4, 2, 3), ("simple_tag", 6, 3, 2),
+                                               ("simple_crypto", 3, 2, None), ("simple_crypto_display", 3, 4, None)])
 def test_env_matches_oracle_with_philox_resets(scenario, M, L, nadv):
     """Free-running 60 steps (two auto-resets) at N=1000 with an env-id offset: states equal the oracle's."""
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 CASES = [("simple_spread", 3, 3, {}), ("simple_spread", 10, 3, {}), ("simple_speaker_listener", 2, 3, {}),
          ("simple_reference", 2, 3, {}), ("simple_adversary", 3, 2, {}), ("simple_push", 2, 2, {}),
-         ("simple_tag", 4, 2, dict(num_adversaries=3, num_good_agents=1))]
+         ("simple_tag", 4, 2, dict(num_adversaries=3, num_good_agents=1)), ("simple_crypto", 3, 2, {})]
 
 
 def make_env(scenario, M, L, N, **kw):

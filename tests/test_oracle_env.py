@@ -7,7 +7,7 @@ import pytest
 
 from oracle.mpe import OracleMPE, np_sum_small
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto"]
 
 
 def replay(fx, make_env):
