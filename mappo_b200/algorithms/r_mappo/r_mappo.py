@@ -79,7 +79,7 @@ class R_MAPPO:
 
     # ------------------------------------------------------------------ core: one minibatch on device tensors
     def _update(self, obs, share_obs, group, actions, old_logp, adv, value_preds, returns, active, avail,
-                rows_total_a, index=None, share_rows_div=1, update_actor=True, vn_batch=None):
+                rows_total_a, index=None, share_rows_div=1, update_actor=True, vn_batch=None, vn_moments=None):
         """obs [rows_a, D] (strided rows ok); share_obs [rows_c, S]; the per-sample arrays are flat and, with
         `index`, addressed through it.  rows_total_a: number of actor samples in this minibatch."""
         pol = self.policy
@@ -95,7 +95,7 @@ class R_MAPPO:
         ops.grad_reduce(ws["gpa"], ws["lpa"], ws["nba"], gsa, lsa)
         # ValueNorm.update(return_batch) happens inside the value loss, before normalize (r_mappo.py:65-67)
         if self.value_normalizer is not None:
-            self.value_normalizer.update(returns if vn_batch is None else vn_batch)
+            self.value_normalizer.update(returns if vn_batch is None else vn_batch, moments=vn_moments)
         ops.critic_update(pol.critic.cfg, loss, pol.critic.flat, share_obs, value_preds, returns, active,
                           None if self.value_normalizer is None else self.value_normalizer.stats,
                           ws["gpc"], ws["lpc"], group=group, index=index, share_rows_div=share_rows_div)
@@ -251,6 +251,13 @@ class R_MAPPO:
         rep = M if v["share_is_unique"] else 1          # samples served by one share_obs row
         n_updates = 0
         v["adv"] = adv
+        # num_mini_batch == 1: every epoch's return batch is the whole buffer, so its moments (and, multi-GPU, their
+        # all-reduce) are computed once per iteration; ValueNorm.update still runs every epoch
+        vn_once = None
+        whole_batch = not (self._use_recurrent_policy or self._use_naive_recurrent) and \
+            self.num_mini_batch == 1 and not buffer.force_permutation
+        if whole_batch and self.value_normalizer is not None:
+            vn_once = self.value_normalizer.batch_moments(ret)
         for _ in range(self.ppo_epoch):
             if self._use_recurrent_policy or self._use_naive_recurrent:
                 if self._use_recurrent_policy:
@@ -262,7 +269,8 @@ class R_MAPPO:
                     n_updates += 1
             elif self.num_mini_batch == 1 and not buffer.force_permutation:
                 # the loss is a mean over the whole batch: the permutation only reorders the sum
-                self._update(obs_flat, sh, rep, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor)
+                self._update(obs_flat, sh, rep, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor,
+                             vn_moments=vn_once)
                 n_updates += 1
             else:
                 mbs = B // self.num_mini_batch

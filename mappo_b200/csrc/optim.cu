@@ -6,9 +6,9 @@
 
 namespace mappo {
 
-// column sums over the per-CTA partial rows, fixed order (deterministic): 8 row slices per column are summed
-// independently (rows s, s + 8, ...) and combined in slice order
-constexpr int kRedSlices = 8, kRedCols = 32;
+// column sums over the per-CTA partial rows, fixed order (deterministic): 32 row slices per column are summed
+// independently (rows s, s + 32, ...: ~10 loads in flight per thread at 296 partial rows) and combined in slice order
+constexpr int kRedSlices = 32, kRedCols = 32;
 __global__ void __launch_bounds__(kRedSlices * kRedCols)
 grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, int blocks, long long P,
                    float* __restrict__ gsum, double* __restrict__ lsum) {

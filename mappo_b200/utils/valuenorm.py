@@ -49,9 +49,15 @@ class ValueNorm(nn.Module):
         return x.to(self.stats.device, torch.float32).contiguous()
 
     @torch.no_grad()
-    def update(self, input_vector):
-        s3 = ops.moments(self._dev(input_vector), all_reduce=self.all_reduce)
+    def update(self, input_vector, moments=None):
+        """`moments`: the double[3] batch moments of `input_vector` if the caller already has them (the trainer
+        computes them once per iteration when every epoch sees the same return batch)."""
+        s3 = moments if moments is not None else self.batch_moments(input_vector)
         ops.valuenorm_apply(self.stats, s3, self.beta)
+
+    @torch.no_grad()
+    def batch_moments(self, input_vector):
+        return ops.moments(self._dev(input_vector), all_reduce=self.all_reduce)
 
     def normalize(self, input_vector):
         return ops.valuenorm_transform(self.stats, self._dev(input_vector), False)
