@@ -65,7 +65,11 @@ typedef enum {
   MAPPO_SCN_SIMPLE_TAG = 5,
   /* scenarios/simple_crypto.py:21-171 (= simple_crypto_display.py without its prints): three immobile agents
    * (adversary, listener, speaker) exchanging 4-colour words; goal slot 0 = goal landmark, slot 1 = key landmark */
-  MAPPO_SCN_SIMPLE_CRYPTO = 6
+  MAPPO_SCN_SIMPLE_CRYPTO = 6,
+  /* scenarios/simple_world_comm.py:7-288: simple_tag's physics (per-side size / accel / max_speed, obstacle landmarks)
+   * plus 2 food and 2 forest landmarks stored behind the `num_landmarks` obstacles, forest-limited visibility, and a
+   * leader (agent 0) with a movement and a 4-word communication head */
+  MAPPO_SCN_SIMPLE_WORLD_COMM = 7
 } mappo_scenario;
 
 typedef struct {
@@ -85,7 +89,8 @@ typedef struct {
 typedef struct {
   double* p_pos;        /* [2][M][N] agent positions */
   double* p_vel;        /* [2][M][N] agent velocities */
-  double* lm_pos;       /* [2][L][N] landmark positions */
+  double* lm_pos;       /* [2][L][N] landmark positions; L = mappo_env_num_landmarks(cfg) (= num_landmarks except for
+                         * simple_world_comm: obstacles, then 2 food, then 2 forests) */
   int32_t* comm;        /* [M][N] id of the one-hot utterance state.c of agent i, -1 = all zeros */
   int32_t* goal;        /* [M][N] landmark id of agent i's goal_b, -1 = none */
   int32_t* step_count;  /* [N] MultiAgentEnv.current_step */
@@ -99,6 +104,8 @@ int mappo_env_obs_dim(int scenario, int num_agents, int num_landmarks, int agent
 /* the same from a config (needed where the width depends on num_adversaries: simple_tag) */
 int mappo_env_obs_dim_cfg(const mappo_env_config* cfg, int agent);
 int mappo_env_obs_width_cfg(const mappo_env_config* cfg);
+/* landmarks held in the state arrays: cfg->num_landmarks plus the scenario's own (simple_world_comm: + 4) */
+int mappo_env_num_landmarks(const mappo_env_config* cfg);
 
 /* envs.reset(): draw every env's initial state (Philox, counter = (env id, episode, block, 0)),
  * zero step counts, and write the observations.  obs_out: float32 [N][obs_width], agent-major inside

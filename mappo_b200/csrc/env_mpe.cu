@@ -44,6 +44,9 @@ __host__ __device__ inline ScnInfo scn_info(int scn) {
     s.dim_c = 2; s.n_goals = 1; s.collide = 0; s.agent_size = 0.15; s.landmark_scale = 1.0; s.shared_goal = 1; s.collaborative = 0;
   } else if (scn == MAPPO_SCN_SIMPLE_PUSH) {
     s.dim_c = 2; s.n_goals = 1; s.collide = 1; s.agent_size = 0.05; s.landmark_scale = 0.8; s.shared_goal = 1; s.collaborative = 0;
+  } else if (scn == MAPPO_SCN_SIMPLE_WORLD_COMM) {  // simple_world_comm.py:7-53: tag physics + food, forests, a speaking leader
+    s.dim_c = 4; s.n_goals = 0; s.collide = 1; s.agent_size = 0.045; s.landmark_scale = 0.8; s.collaborative = 0;
+    s.landmark_collide = 1; s.landmark_size = 0.2;
   } else if (scn == MAPPO_SCN_SIMPLE_CRYPTO) {  // simple_crypto.py:21-47: nobody moves, everybody speaks; goal + key landmark
     s.dim_c = 4; s.n_goals = 2; s.collide = 0; s.agent_size = 0.05; s.landmark_scale = 1.0; s.collaborative = 0;
   } else {  // simple_tag: sizes / accel / max_speed depend on the agent's side, see agent_* below
@@ -56,17 +59,23 @@ __host__ __device__ inline ScnInfo scn_info(int scn) {
 __host__ __device__ inline int n_adversaries(int scn, int cfg_nadv) {
   if (scn == MAPPO_SCN_SIMPLE_ADVERSARY || scn == MAPPO_SCN_SIMPLE_PUSH || scn == MAPPO_SCN_SIMPLE_CRYPTO) return 1;
   if (scn == MAPPO_SCN_SIMPLE_TAG) return cfg_nadv > 0 ? cfg_nadv : 3;              // simple_tag.py:12 default
+  if (scn == MAPPO_SCN_SIMPLE_WORLD_COMM) return cfg_nadv > 0 ? cfg_nadv : 4;       // simple_world_comm.py:12 default
   return 0;
 }
+// landmarks behind the `num_landmarks` obstacles the flag counts: simple_world_comm appends 2 food and 2 forests
+// (simple_world_comm.py:27-50); they are observed like landmarks but do not collide
+__host__ __device__ inline int n_extra_landmarks(int scn) { return scn == MAPPO_SCN_SIMPLE_WORLD_COMM ? 4 : 0; }
+constexpr double kFoodSize = 0.03, kForestSize = 0.3;
 __host__ __device__ inline double agent_size_of(int scn, int i, int nadv) {
   if (scn == MAPPO_SCN_SIMPLE_TAG) return i < nadv ? 0.075 : 0.05;                   // simple_tag.py:22
+  if (scn == MAPPO_SCN_SIMPLE_WORLD_COMM) return i < nadv ? 0.075 : 0.045;           // simple_world_comm.py:23
   return scn_info(scn).agent_size;
 }
 __host__ __device__ inline double agent_accel_of(int scn, int i, int nadv) {         // 0: accel None
-  return scn == MAPPO_SCN_SIMPLE_TAG ? (i < nadv ? 3.0 : 4.0) : 0.0;                 // simple_tag.py:23
+  return (scn == MAPPO_SCN_SIMPLE_TAG || scn == MAPPO_SCN_SIMPLE_WORLD_COMM) ? (i < nadv ? 3.0 : 4.0) : 0.0;   // simple_tag.py:23
 }
 __host__ __device__ inline double agent_max_speed_of(int scn, int i, int nadv) {     // 0: max_speed None
-  return scn == MAPPO_SCN_SIMPLE_TAG ? (i < nadv ? 1.0 : 1.3) : 0.0;                 // simple_tag.py:24
+  return (scn == MAPPO_SCN_SIMPLE_TAG || scn == MAPPO_SCN_SIMPLE_WORLD_COMM) ? (i < nadv ? 1.0 : 1.3) : 0.0;   // simple_tag.py:24
 }
 
 __host__ __device__ inline int obs_dim_of(int scn, int M, int L, int agent, int nadv = 0) {
@@ -77,6 +86,10 @@ __host__ __device__ inline int obs_dim_of(int scn, int M, int L, int agent, int 
   if (scn == MAPPO_SCN_SIMPLE_ADVERSARY) return (agent < nadv ? 0 : 2) + 2 * L + 2 * (M - 1);
   if (scn == MAPPO_SCN_SIMPLE_PUSH) return agent < nadv ? 2 + 2 * L + 2 * (M - 1) : 2 + 2 + 3 + 2 * L + 3 * L + 2 * (M - 1);
   if (scn == MAPPO_SCN_SIMPLE_CRYPTO) return agent == 0 ? 4 : 8;                      // simple_crypto.py:160-171
+  if (scn == MAPPO_SCN_SIMPLE_WORLD_COMM) {                                           // simple_world_comm.py:281-288
+    const int Lt = L + 4, good = M - nadv;
+    return agent < nadv ? 4 + 2 * Lt + 2 * (M - 1) + 2 * good + 2 + 4 : 4 + 2 * Lt + 2 * (M - 1) + 2 + 2 * (good - 1);
+  }
   const int good_others = (M - nadv) - (agent < nadv ? 0 : 1);
   return 4 + 2 * L + 2 * (M - 1) + 2 * good_others;
 }
@@ -91,6 +104,7 @@ __host__ __device__ inline bool is_movable(int scn, int agent) {
 }
 __host__ __device__ inline bool is_silent(int scn, int agent) {
   if (scn == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER) return agent == 1;
+  if (scn == MAPPO_SCN_SIMPLE_WORLD_COMM) return agent != 0;                          // only the leader speaks (:20)
   return !(scn == MAPPO_SCN_SIMPLE_REFERENCE || scn == MAPPO_SCN_SIMPLE_CRYPTO);      // every other scenario: silent = True
 }
 
@@ -157,7 +171,7 @@ static size_t env_smem_bytes(int M, int L, int EPB, int W) {
 template <int SCN>
 __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EPB, int ld, int e, int i,
                                           double vx, double vy, int nadv) {
-  float* o = s.tile + (size_t)e * ld + obs_off_of(SCN, M, L, i, nadv);
+  float* o = s.tile + (size_t)e * ld + obs_off_of(SCN, M, L - n_extra_landmarks(SCN), i, nadv);
   const double px = s.pos[(0 * M + i) * EPB + e], py = s.pos[(1 * M + i) * EPB + e];
   int k = 0;
   if (SCN == MAPPO_SCN_SIMPLE_SPREAD) {
@@ -195,6 +209,42 @@ __device__ __forceinline__ void write_obs(const EnvSmem& s, int M, int L, int EP
     for (int c = 0; c < 3; ++c) o[k++] = (float)c_colors_ref[g * 3 + c];
     const int cid = s.comm[(1 - i) * EPB + e];
     for (int c = 0; c < 10; ++c) o[k++] = (c == cid) ? 1.0f : 0.0f;
+  } else if (SCN == MAPPO_SCN_SIMPLE_WORLD_COMM) {
+    // simple_world_comm.py:214-288.  The last two landmarks are the forests: an agent is hidden in one when it overlaps it
+    // (is_collision); another agent is visible when both share a forest, when neither is in any forest, or to the leader.
+    const int f1 = L - 2, f2 = L - 1;
+    auto in_f = [&](int ag, int f) {
+      const double dx = s.pos[(0 * M + ag) * EPB + e] - s.lm[(0 * L + f) * EPB + e];
+      const double dy = s.pos[(1 * M + ag) * EPB + e] - s.lm[(1 * L + f) * EPB + e];
+      return sqrt(dx * dx + dy * dy) < agent_size_of(SCN, ag, nadv) + kForestSize;
+    };
+    const bool inf1 = in_f(i, f1), inf2 = in_f(i, f2), adv = i < nadv;
+    o[k++] = (float)vx; o[k++] = (float)vy; o[k++] = (float)px; o[k++] = (float)py;
+    for (int l = 0; l < L; ++l) {
+      o[k++] = (float)(s.lm[(0 * L + l) * EPB + e] - px);
+      o[k++] = (float)(s.lm[(1 * L + l) * EPB + e] - py);
+    }
+    unsigned vis = 0;
+    for (int j = 0; j < M; ++j) {
+      if (j == i) continue;
+      const bool o1 = in_f(j, f1), o2 = in_f(j, f2);
+      const bool v = (inf1 && o1) || (inf2 && o2) || (!inf1 && !o1 && !inf2 && !o2) || i == 0;
+      if (v) vis |= 1u << j;
+      o[k++] = v ? (float)(s.pos[(0 * M + j) * EPB + e] - px) : 0.0f;
+      o[k++] = v ? (float)(s.pos[(1 * M + j) * EPB + e] - py) : 0.0f;
+    }
+    if (!adv) { o[k++] = inf1 ? 1.0f : -1.0f; o[k++] = inf2 ? 1.0f : -1.0f; }          // good agents: in_forest first
+    for (int j = nadv; j < M; ++j) {                                                   // velocities of the other GOOD agents
+      if (j == i) continue;
+      const bool v = (vis >> j) & 1u;
+      o[k++] = v ? (float)s.vel[(0 * M + j) * EPB + e] : 0.0f;
+      o[k++] = v ? (float)s.vel[(1 * M + j) * EPB + e] : 0.0f;
+    }
+    if (adv) {
+      o[k++] = inf1 ? 1.0f : -1.0f; o[k++] = inf2 ? 1.0f : -1.0f;
+      const int said = s.comm[0 * EPB + e];                                            // the leader's word
+      for (int c = 0; c < 4; ++c) o[k++] = (c == said) ? 1.0f : 0.0f;
+    }
   } else if (SCN == MAPPO_SCN_SIMPLE_CRYPTO) {
     // simple_crypto.py:127-171: landmark l's colour is the unit vector e_l of the 4 colour channels (:54-58);
     // goal slot 0 = the goal landmark, slot 1 = the landmark whose colour is the speaker's key
@@ -265,6 +315,7 @@ __device__ __forceinline__ int draw_goal(uint32_t env_lo, uint32_t ep, uint32_t 
 
 struct StepArgs {
   int N, M, L, T, EPB, W, ld, nadv;
+  int Lc;               // colliding landmarks: the first Lc of the L (simple_world_comm: food and forests follow)
   uint32_t k0;
   long long env_id_offset;
   mappo_env_state st;
@@ -357,7 +408,7 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
           fx = gx + fx; fy = gy + fy;
         }
         if (si.landmark_collide)
-          for (int l = 0; l < L; ++l) {                                  // (agent, landmark) pairs follow the agent pairs
+          for (int l = 0; l < a.Lc; ++l) {                               // (agent, landmark) pairs follow the agent pairs
             const double dist_min = my_size + si.landmark_size;
             const double dx = px - s.lm[(0 * L + l) * EPB + e], dy = py - s.lm[(1 * L + l) * EPB + e];
             const double dist = sqrt(dx * dx + dy * dy);
@@ -456,6 +507,46 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
         }
         indiv = rew;
       }
+    } else if (SCN == MAPPO_SCN_SIMPLE_WORLD_COMM) {                     // simple_world_comm.py:135-190
+      if (valid) {
+        auto dist = [&](double ax, double ay, double bx, double by) {
+          const double dx = ax - bx, dy = ay - by;
+          return sqrt(dx * dx + dy * dy);
+        };
+        auto apos = [&](int ag, int c) { return s.pos[(c * M + ag) * EPB + e]; };
+        double rew;
+        if (i < a.nadv) {
+          double near = dist(apos(a.nadv, 0), apos(a.nadv, 1), px, py);
+          for (int g = a.nadv + 1; g < M; ++g) { const double d = dist(apos(g, 0), apos(g, 1), px, py); near = d < near ? d : near; }
+          rew = 0.0 - 0.1 * near;
+          for (int ag = a.nadv; ag < M; ++ag)
+            for (int adv = 0; adv < a.nadv; ++adv)
+              if (dist(apos(ag, 0), apos(ag, 1), apos(adv, 0), apos(adv, 1)) <
+                  agent_size_of(SCN, ag, a.nadv) + agent_size_of(SCN, adv, a.nadv)) rew += 5;
+        } else {
+          rew = 0.0;
+          for (int adv = 0; adv < a.nadv; ++adv)
+            if (dist(apos(adv, 0), apos(adv, 1), px, py) < agent_size_of(SCN, adv, a.nadv) + agent_size_of(SCN, i, a.nadv)) rew -= 5;
+          for (int p = 0; p < 2; ++p) {                                  // 2 * bound(|x|)
+            const double x = fabs(p == 0 ? px : py);
+            double b;
+            if (x < 0.9) b = 0.0;
+            else if (x < 1.0) b = (x - 0.9) * 10;
+            else { const double ex = exp(2 * x - 2); b = ex < 10.0 ? ex : 10.0; }
+            rew -= 2 * b;
+          }
+          const int food0 = L - 4;
+          double fmin_ = 0.0;
+          for (int f = 0; f < 2; ++f) {
+            const double fx = s.lm[(0 * L + food0 + f) * EPB + e], fy = s.lm[(1 * L + food0 + f) * EPB + e];
+            if (dist(px, py, fx, fy) < agent_size_of(SCN, i, a.nadv) + kFoodSize) rew += 2;
+            const double d = dist(fx, fy, px, py);
+            fmin_ = (f == 0 || d < fmin_) ? d : fmin_;
+          }
+          rew += 0.05 * fmin_;
+        }
+        indiv = rew;
+      }
     } else if (SCN == MAPPO_SCN_SIMPLE_CRYPTO) {                         // simple_crypto.py:90-125
       if (valid) {
         // sum((c - goal_colour)^2) for one-hot c: 0 if the word is the goal's channel else 2; 0 while nothing was said
@@ -534,10 +625,11 @@ __global__ void __launch_bounds__(512) env_kernel(const StepArgs a) {
 
 static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
   MAPPO_REQUIRE(cfg && st, "env: null config/state");
-  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= MAPPO_SCN_SIMPLE_CRYPTO, "env: unknown scenario %d", cfg->scenario);
+  MAPPO_REQUIRE(cfg->scenario >= 0 && cfg->scenario <= MAPPO_SCN_SIMPLE_WORLD_COMM, "env: unknown scenario %d", cfg->scenario);
   MAPPO_REQUIRE(cfg->num_envs > 0 && cfg->num_agents > 0 && cfg->num_landmarks > 0 && cfg->episode_length > 0,
                 "env: non-positive size");
-  MAPPO_REQUIRE(cfg->num_agents <= 16 && cfg->num_landmarks <= 16, "env: at most 16 agents and 16 landmarks");
+  MAPPO_REQUIRE(cfg->num_agents <= 16 && cfg->num_landmarks + n_extra_landmarks(cfg->scenario) <= 16,
+                "env: at most 16 agents and 16 landmarks");
   if (cfg->scenario == MAPPO_SCN_SIMPLE_SPEAKER_LISTENER || cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE)
     MAPPO_REQUIRE(cfg->num_agents == 2 && cfg->num_landmarks == 3,
                   "env: only 2 agents is supported (3 landmarks), check the config");  // scenario asserts
@@ -549,9 +641,9 @@ static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
   if (cfg->scenario == MAPPO_SCN_SIMPLE_CRYPTO)
     MAPPO_REQUIRE(cfg->num_agents == 3 && cfg->num_landmarks <= 4,
                   "env: simple_crypto has 3 agents and at most 4 landmarks (dim_c colours)");  // simple_crypto.py:27-31,54-58
-  if (cfg->scenario == MAPPO_SCN_SIMPLE_TAG) {
+  if (cfg->scenario == MAPPO_SCN_SIMPLE_TAG || cfg->scenario == MAPPO_SCN_SIMPLE_WORLD_COMM) {
     const int nadv = n_adversaries(cfg->scenario, cfg->num_adversaries);
-    MAPPO_REQUIRE(nadv > 0 && nadv < cfg->num_agents, "env: simple_tag needs 0 < num_adversaries (%d) < num_agents", nadv);
+    MAPPO_REQUIRE(nadv > 0 && nadv < cfg->num_agents, "env: simple_tag / simple_world_comm need 0 < num_adversaries (%d) < num_agents", nadv);
   }
   MAPPO_REQUIRE(st->p_pos && st->p_vel && st->lm_pos && st->comm && st->goal && st->step_count && st->episode,
                 "env: null state array");
@@ -559,10 +651,10 @@ static int check_cfg(const mappo_env_config* cfg, const mappo_env_state* st) {
 }
 
 static int launch_env(const mappo_env_config* cfg, StepArgs& a, cudaStream_t stream) {
-  const int M = cfg->num_agents, L = cfg->num_landmarks;
-  a.N = cfg->num_envs; a.M = M; a.L = L; a.T = cfg->episode_length;
+  const int M = cfg->num_agents, L = cfg->num_landmarks + n_extra_landmarks(cfg->scenario);
+  a.N = cfg->num_envs; a.M = M; a.L = L; a.Lc = cfg->num_landmarks; a.T = cfg->episode_length;
   a.nadv = n_adversaries(cfg->scenario, cfg->num_adversaries);
-  a.W = obs_off_of(cfg->scenario, M, L, M, a.nadv);
+  a.W = obs_off_of(cfg->scenario, M, cfg->num_landmarks, M, a.nadv);
   a.ld = tile_ld_of(a.W);
   a.k0 = (uint32_t)(cfg->seed & 0xFFFFFFFFull);
   a.env_id_offset = cfg->env_id_offset;
@@ -585,6 +677,7 @@ static int launch_env(const mappo_env_config* cfg, StepArgs& a, cudaStream_t str
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_ADVERSARY) LAUNCH_SCN(MAPPO_SCN_SIMPLE_ADVERSARY);
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_PUSH) LAUNCH_SCN(MAPPO_SCN_SIMPLE_PUSH);
   else if (cfg->scenario == MAPPO_SCN_SIMPLE_CRYPTO) LAUNCH_SCN(MAPPO_SCN_SIMPLE_CRYPTO);
+  else if (cfg->scenario == MAPPO_SCN_SIMPLE_WORLD_COMM) LAUNCH_SCN(MAPPO_SCN_SIMPLE_WORLD_COMM);
   else LAUNCH_SCN(MAPPO_SCN_SIMPLE_TAG);
 #undef LAUNCH_SCN
   MAPPO_CHECK_LAUNCH("env_kernel");
@@ -599,6 +692,9 @@ extern "C" int mappo_env_obs_dim(int scenario, int M, int L, int agent) { return
 extern "C" int mappo_env_obs_width(int scenario, int M, int L) { return obs_off_of(scenario, M, L, M); }
 extern "C" int mappo_env_obs_dim_cfg(const mappo_env_config* c, int agent) {
   return c ? obs_dim_of(c->scenario, c->num_agents, c->num_landmarks, agent, c->num_adversaries) : -1;
+}
+extern "C" int mappo_env_num_landmarks(const mappo_env_config* c) {
+  return c ? c->num_landmarks + n_extra_landmarks(c->scenario) : -1;
 }
 extern "C" int mappo_env_obs_width_cfg(const mappo_env_config* c) {
   return c ? obs_off_of(c->scenario, c->num_agents, c->num_landmarks, c->num_agents, c->num_adversaries) : -1;
@@ -619,7 +715,7 @@ extern "C" int mappo_env_step(const mappo_env_config* cfg, const mappo_env_state
                               void* stream) {
   if (int rc = check_cfg(cfg, st)) return rc;
   MAPPO_REQUIRE(actions && obs_out && rewards_out, "env_step: null actions/obs_out/rewards_out");
-  const int need = (cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE) ? 2 : 1;
+  const int need = (cfg->scenario == MAPPO_SCN_SIMPLE_REFERENCE || cfg->scenario == MAPPO_SCN_SIMPLE_WORLD_COMM) ? 2 : 1;
   MAPPO_REQUIRE(act_width >= need, "env_step: act_width %d < %d heads", act_width, need);
   StepArgs a{};
   a.st = *st; a.actions = actions; a.act_w = act_width; a.obs_out = obs_out; a.rewards_out = rewards_out;

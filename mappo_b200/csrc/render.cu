@@ -203,7 +203,8 @@ extern "C" int mappo_env_render(const mappo_env_config* cfg, const mappo_env_sta
   MAPPO_REQUIRE(rc->width > 0 && rc->height > 0 && rc->width % 4 == 0, "env_render: width must be a positive multiple of 4");
   MAPPO_REQUIRE(rc->num_images >= 0 && rc->num_images <= 65535, "env_render: num_images %d outside [0, 65535]", rc->num_images);
   MAPPO_REQUIRE(rc->res >= 3 && rc->res <= kMaxRes, "env_render: res %d outside [3, %d]", rc->res, kMaxRes);
-  MAPPO_REQUIRE(rc->num_entities == cfg->num_agents + cfg->num_landmarks, "env_render: num_entities must be M + L");
+  const int L_all = mappo_env_num_landmarks(cfg);
+  MAPPO_REQUIRE(rc->num_entities == cfg->num_agents + L_all, "env_render: num_entities must be M + L");
   MAPPO_REQUIRE(rc->num_entities <= kMaxPrim, "env_render: too many entities");
   MAPPO_REQUIRE(rc->cam_range > 0.0 && rc->line_width >= 0.0, "env_render: bad camera range / line width");
   MAPPO_REQUIRE((reinterpret_cast<uintptr_t>(rgb_out) & 3u) == 0, "env_render: rgb_out must be 4-byte aligned");
@@ -211,7 +212,7 @@ extern "C" int mappo_env_render(const mappo_env_config* cfg, const mappo_env_sta
   if (rc->num_images == 0) return MAPPO_OK;
   RenderArgs a;
   a.st = *st;
-  a.N = cfg->num_envs; a.M = cfg->num_agents; a.L = cfg->num_landmarks;
+  a.N = cfg->num_envs; a.M = cfg->num_agents; a.L = L_all;
   a.W = rc->width; a.H = rc->height; a.E = rc->num_entities; a.res = rc->res;
   a.cam = rc->cam_range; a.half_width = rc->line_width * 0.5;
   a.env_ids = env_ids; a.size = entity_size; a.rgba = entity_rgba; a.comm_dim = comm_dim; a.unit = unit_circle;

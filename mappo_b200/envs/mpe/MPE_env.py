@@ -14,7 +14,8 @@ from ..spaces import Box, Discrete, MultiDiscrete, head_sizes
 
 SCENARIOS = {"simple_spread": 0, "simple_speaker_listener": 1, "simple_reference": 2,
              "simple_adversary": 3, "simple_push": 4, "simple_tag": 5,
-             "simple_crypto": 6, "simple_crypto_display": 6}      # the display variant only adds prints
+             "simple_crypto": 6, "simple_crypto_display": 6,      # the display variant only adds prints
+             "simple_world_comm": 7}
 
 
 class _Infos:
@@ -70,8 +71,9 @@ class MPEVecEnv:
         elif name in ("simple_crypto", "simple_crypto_display"):       # simple_crypto.py:27-31
             assert self.num_agents == 3, "simple_crypto: adversary, listener, speaker"
             self.num_adversaries = 1
-        elif name == "simple_tag":                                     # simple_tag.py:10-13: adversaries first
-            self.num_adversaries = int(getattr(args, "num_adversaries", 0) or 3)
+        elif name in ("simple_tag", "simple_world_comm"):              # simple_tag.py:10-13, simple_world_comm.py:10-13:
+            default_adv = 3 if name == "simple_tag" else 4             # adversaries first
+            self.num_adversaries = int(getattr(args, "num_adversaries", 0) or default_adv)
             good = getattr(args, "num_good_agents", None)
             if good is not None:
                 self.n = self.num_agents = self.num_adversaries + int(good)
@@ -82,6 +84,9 @@ class MPEVecEnv:
         self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length, self.num_adversaries,
                                    int(seed if seed is not None else getattr(args, "seed", 1)) & (2 ** 64 - 1),
                                    int(env_id_offset))
+        L.mappo_env_num_landmarks.argtypes = [C.POINTER(_lib.EnvConfig)]
+        # landmarks held in the state arrays (simple_world_comm: obstacles + 2 food + 2 forests)
+        self.num_landmarks_total = NL = int(L.mappo_env_num_landmarks(C.byref(self._cfg)))
         self.obs_dims = [L.mappo_env_obs_dim_cfg(C.byref(self._cfg), i) for i in range(M)]
         self.obs_width = L.mappo_env_obs_width_cfg(C.byref(self._cfg))
         self.homogeneous = len(set(self.obs_dims)) == 1
@@ -92,6 +97,8 @@ class MPEVecEnv:
             acts = [Discrete(3), Discrete(5)]
         elif name in ("simple_crypto", "simple_crypto_display"):
             acts = [Discrete(4) for _ in range(M)]                     # immobile, not silent: the word (dim_c = 4)
+        elif name == "simple_world_comm":                              # the leader moves and speaks (environment.py:66-93)
+            acts = [MultiDiscrete([[0, 4], [0, 3]])] + [Discrete(5) for _ in range(M - 1)]
         else:
             acts = [MultiDiscrete([[0, 4], [0, 9]]) for _ in range(M)]
         self.action_space = acts

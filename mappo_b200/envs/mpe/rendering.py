@@ -38,7 +38,7 @@ def unit_circle(res=RES):
 
 def entity_sizes(env):
     """[E] entity.size: agents then landmarks (core.py:53 default 0.05 and the scenarios' make_world)."""
-    name, M, L, nadv = env.scenario_name, env.num_agents, env.num_landmarks, env.num_adversaries
+    name, M, L, nadv = env.scenario_name, env.num_agents, env.num_landmarks_total, env.num_adversaries
     if name == "simple_spread":
         a, l = [0.15] * M, [0.05] * L                                  # simple_spread.py:21
     elif name == "simple_speaker_listener":
@@ -48,6 +48,9 @@ def entity_sizes(env):
     elif name == "simple_tag":
         a = [0.075 if i < nadv else 0.05 for i in range(M)]            # simple_tag.py:21,31
         l = [0.2] * L
+    elif name == "simple_world_comm":                                  # simple_world_comm.py:23,31,38,45
+        a = [0.075 if i < nadv else 0.045 for i in range(M)]
+        l = [0.2] * (L - 4) + [0.03] * 2 + [0.3] * 2                   # obstacles, food, forests
     else:                                                              # simple_reference, simple_push, simple_crypto
         a, l = [0.05] * M, [0.05] * L
     return np.asarray(a + l, dtype=np.float32)
@@ -55,7 +58,7 @@ def entity_sizes(env):
 
 def comm_dims(env):
     """[E] world.dim_c for agents that are not silent (they get communication circles, environment.py:317-330)."""
-    name, M, L = env.scenario_name, env.num_agents, env.num_landmarks
+    name, M, L = env.scenario_name, env.num_agents, env.num_landmarks_total
     d = [0] * (M + L)
     if name == "simple_speaker_listener":
         d[0] = 3                                                       # the speaker; the listener is silent (:26)
@@ -63,13 +66,15 @@ def comm_dims(env):
         d[:M] = [10] * M
     elif name in ("simple_crypto", "simple_crypto_display"):
         d[:M] = [4] * M
+    elif name == "simple_world_comm":
+        d[0] = 4                                                       # the leader
     return np.asarray(d, dtype=np.int32)
 
 
 def entity_rgba(env, env_ids):
     """float32 [n, E, 4] on the device: entity.color as the scenarios' reset_world leaves it, alpha 0.5 for agents and
     1 for landmarks (environment.py:315,338)."""
-    name, M, L, nadv = env.scenario_name, env.num_agents, env.num_landmarks, env.num_adversaries
+    name, M, L, nadv = env.scenario_name, env.num_agents, env.num_landmarks_total, env.num_adversaries
     dev = env.device
     ids = torch.as_tensor(env_ids, dtype=torch.long, device=dev)
     n = ids.numel()
@@ -106,6 +111,12 @@ def entity_rgba(env, env_ids):
         lm = torch.eye(4, dtype=torch.float32, device=dev)[:L, :3]     # colour e_l; only r, g, b reach the rasteriser
         rgb[:, M:] = lm
         rgb[:, 1] = lm[goal[:, 0]]                                     # world.agents[1].color = goal.color
+    elif name == "simple_world_comm":                                  # simple_world_comm.py:79-89
+        rgb[:, :M] = t([(0.95, 0.45, 0.45) if i < nadv else (0.45, 0.95, 0.45) for i in range(M)])
+        rgb[:, 0] -= 0.3                                               # the leader
+        rgb[:, M:M + L - 4] = t(_GREY)
+        rgb[:, M + L - 4:M + L - 2] = t((0.15, 0.15, 0.65))            # food
+        rgb[:, M + L - 2:] = t((0.6, 0.9, 0.6))                        # forests
     else:
         raise NotImplementedError(name)
     alpha = torch.ones(n, M + L, 1, dtype=torch.float32, device=dev)
@@ -115,7 +126,7 @@ def entity_rgba(env, env_ids):
 
 def render_rgb(env, env_ids=None, width=WIDTH, height=HEIGHT, out=None):
     """uint8 device tensor [n, height, width, 3] of the envs `env_ids` (default: all)."""
-    N, M, L = env.num_envs, env.num_agents, env.num_landmarks
+    N, M, L = env.num_envs, env.num_agents, env.num_landmarks_total
     if env_ids is None:
         env_ids = np.arange(N)
     env_ids = np.asarray(env_ids, dtype=np.int32).reshape(-1)

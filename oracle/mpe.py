@@ -132,6 +132,28 @@ class ScenarioSpec:
             n_good = M - n_adv
             self.obs_dims = [4 + 2 * L + 2 * (M - 1) + 2 * n_good] * n_adv + \
                             [4 + 2 * L + 2 * (M - 1) + 2 * (n_good - 1)] * n_good
+        elif name == "simple_world_comm":                               # simple_world_comm.py:7-53
+            # world.landmarks = L obstacles (collide, 0.2) + 2 food (0.03) + 2 forests (0.3); agent 0 leads and speaks
+            self.n_adv = n_adv = int(num_adversaries if num_adversaries else 4)
+            assert 0 < n_adv < M
+            self.n_extra = 4
+            self.collide = True
+            self.sizes = [0.075] * n_adv + [0.045] * (M - n_adv)
+            self.accel = [3.0] * n_adv + [4.0] * (M - n_adv)
+            self.max_speed = [1.0] * n_adv + [1.3] * (M - n_adv)
+            self.landmark_collide, self.landmark_size = True, 0.2
+            self.food_size, self.forest_size = 0.03, 0.3
+            self.agent_size = None
+            self.landmark_scale = 0.8
+            self.n_goals = 0
+            self.collaborative = False
+            self.dim_c = 4
+            self.movable = [True] * M
+            self.silent = [False] + [True] * (M - 1)
+            self.act_heads = [[5, 4]] + [[5]] * (M - 1)                 # leader: MultiDiscrete([[0,4],[0,3]])
+            n_good, Lt = M - n_adv, L + 4
+            self.obs_dims = [4 + 2 * Lt + 2 * (M - 1) + 2 * n_good + 2 + 4] * n_adv + \
+                            [4 + 2 * Lt + 2 * (M - 1) + 2 + 2 * (n_good - 1)] * n_good
         elif name in ("simple_crypto", "simple_crypto_display"):         # simple_crypto.py:21-47 (display: same + prints)
             assert M == 3 and 1 <= L <= 4, "simple_crypto: 3 agents (adversary, listener, speaker), dim_c = 4 colours"
             self.name = "simple_crypto"
@@ -161,14 +183,16 @@ class ScenarioSpec:
         self.shared_goal = getattr(self, "shared_goal", False)
         self.collaborative = getattr(self, "collaborative", True)
         self.n_adv = getattr(self, "n_adv", 0)
-        self.n_draws = self.n_goals + 2 * M + 2 * L
+        self.n_extra = getattr(self, "n_extra", 0)                      # landmarks behind the L the flag counts
+        self.L_obst = L
+        self.n_draws = self.n_goals + 2 * M + 2 * (L + self.n_extra)
 
 
 class OracleMPE:
     def __init__(self, scenario, num_envs, num_agents, num_landmarks, episode_length,
                  seed=0, env_id_offset=0, num_adversaries=None):
         self.spec = ScenarioSpec(scenario, num_agents, num_landmarks, num_adversaries)
-        self.N, self.M, self.L = num_envs, num_agents, num_landmarks
+        self.N, self.M, self.L = num_envs, num_agents, num_landmarks + self.spec.n_extra   # L: all of world.landmarks
         self.world_length = episode_length
         self.seed = seed
         self.env_ids = np.arange(num_envs, dtype=np.uint64) + np.uint64(env_id_offset)
@@ -262,7 +286,7 @@ class OracleMPE:
                     force[a] = fa + force[a]
                     force[b] = fb + force[b]
                 if sp.landmark_collide:                                 # entities = agents + landmarks: (agent a, landmark l)
-                    for l in range(self.L):
+                    for l in range(sp.L_obst):                          # food and forests do not collide
                         dist_min = sp.sizes[a] + sp.landmark_size
                         delta = self.p_pos[:, a] - self.lm_pos[:, l]
                         dist = np.sqrt(np.sum(np.square(delta), axis=-1))
@@ -342,6 +366,27 @@ class OracleMPE:
                         c[:, l + 1] += 0.8
                         lm_colors.append(c)
                     o = np.concatenate([self.p_vel[:, i], goal_pos - pos_i, color] + ent + lm_colors + other, axis=-1)
+            elif sp.name == "simple_world_comm":                        # simple_world_comm.py:214-288
+                f1, f2 = L - 2, L - 1                                   # the two forests close world.landmarks
+                def in_f(a, f):
+                    d = np.sqrt(np.sum(np.square(self.p_pos[:, a] - self.lm_pos[:, f]), axis=-1))
+                    return d < sp.sizes[a] + sp.forest_size
+                inf1, inf2 = in_f(i, f1), in_f(i, f2)
+                in_forest = np.stack([np.where(inf1, 1.0, -1.0), np.where(inf2, 1.0, -1.0)], axis=-1)
+                other, other_vel = [], []
+                for j in range(M):
+                    if j == i:
+                        continue
+                    o1, o2 = in_f(j, f1), in_f(j, f2)
+                    vis = (inf1 & o1) | (inf2 & o2) | (~inf1 & ~o1 & ~inf2 & ~o2) | (i == 0)
+                    other.append(np.where(vis[:, None], self.p_pos[:, j] - pos_i, 0.0))
+                    if j >= sp.n_adv:
+                        other_vel.append(np.where(vis[:, None], self.p_vel[:, j], 0.0))
+                if i < sp.n_adv:
+                    o = np.concatenate([self.p_vel[:, i], pos_i] + ent + other + other_vel + [in_forest, self.comm[:, 0]],
+                                       axis=-1)
+                else:
+                    o = np.concatenate([self.p_vel[:, i], pos_i] + ent + other + [in_forest] + other_vel, axis=-1)
             elif sp.name == "simple_crypto":                            # simple_crypto.py:127-171
                 goal_color = np.eye(4)[self.goal[:, 0]]                 # landmark i's colour is e_i (:54-58)
                 key = np.eye(4)[self.goal[:, 1]]
@@ -403,6 +448,32 @@ class OracleMPE:
                         r[:, i] = good_min - neg
                     else:
                         r[:, i] = -dist[i]
+        elif sp.name == "simple_world_comm":                            # simple_world_comm.py:135-190
+            def dist(pa, pb):
+                return np.sqrt(np.sum(np.square(pa - pb), axis=-1))
+            food = [L - 4, L - 3]
+            for i in range(M):
+                if i < sp.n_adv:
+                    near = np.stack([dist(self.p_pos[:, a], self.p_pos[:, i]) for a in range(sp.n_adv, M)], 0).min(axis=0)
+                    ri = 0.0 - 0.1 * near
+                    for ag in range(sp.n_adv, M):                       # += 5 one pair at a time, in this order
+                        for adv in range(sp.n_adv):
+                            ri = ri + 5.0 * (dist(self.p_pos[:, ag], self.p_pos[:, adv]) < sp.sizes[ag] + sp.sizes[adv])
+                    r[:, i] = ri
+                else:
+                    ri = np.zeros(N)
+                    for a in range(sp.n_adv):
+                        ri = ri - 5.0 * (dist(self.p_pos[:, a], self.p_pos[:, i]) < sp.sizes[a] + sp.sizes[i])
+                    for p in range(2):
+                        x = np.abs(self.p_pos[:, i, p])
+                        with np.errstate(over="ignore"):
+                            b = np.where(x < 0.9, 0.0, np.where(x < 1.0, (x - 0.9) * 10, np.minimum(np.exp(2 * x - 2), 10)))
+                        ri = ri - 2 * b
+                    fd = [dist(self.lm_pos[:, f], self.p_pos[:, i]) for f in food]
+                    for k, f in enumerate(food):
+                        ri = ri + 2.0 * (dist(self.p_pos[:, i], self.lm_pos[:, f]) < sp.sizes[i] + sp.food_size)
+                    ri = ri + 0.05 * np.minimum(fd[0], fd[1])
+                    r[:, i] = ri
         elif sp.name == "simple_crypto":                                # simple_crypto.py:90-125
             goal_color = np.eye(4)[self.goal[:, 0]]
             def sq_err(a):                                              # 0 while the agent has not spoken (:103,:122)

@@ -65,6 +65,8 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
     if scenario == "simple_tag":
         # simple_tag.py:11-12 reads two flags that train_mpe.py's parser (train_mpe.py:52-61) does not define
         args.num_adversaries, args.num_good_agents = M - 1, 1
+    if scenario == "simple_world_comm":                                 # simple_world_comm.py:11-12, same two flags
+        args.num_adversaries, args.num_good_agents = M - 2, 2
     rng = np.random.RandomState(seed)
     # one reference env per slot; they share the process-global np.random like DummyVecEnv
     np.random.seed(seed)
@@ -74,10 +76,12 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
         heads.append([sp.n] if sp.__class__.__name__ == "Discrete" else list((sp.high - sp.low + 1).astype(int)))
     H = max(len(h) for h in heads)
     obs0 = [e.reset() for e in envs]
-    if scenario in ("simple_push", "simple_tag"):
+    if scenario in ("simple_push", "simple_tag", "simple_world_comm"):
         # crowd the upper half of the envs around a landmark: agent-agent and agent-landmark contacts, tag rewards
+        # (simple_world_comm: alternately the obstacle and the first forest, so the forest visibility masks switch)
         for n in range(N // 2, N):
-            c = envs[n].world.landmarks[0].state.p_pos
+            lm = envs[n].world.landmarks
+            c = lm[len(lm) - 2 if (scenario == "simple_world_comm" and n % 2) else 0].state.p_pos
             for a in envs[n].world.agents:
                 a.state.p_pos = c + rng.uniform(-0.3, 0.3, 2)
             obs0[n] = [envs[n]._get_obs(a) for a in envs[n].agents]
@@ -137,7 +141,7 @@ def make_env_fixture(scenario, M, L, N=6, steps=56, seed=11):
 ENV_FIXTURES = (("simple_spread", 3, 3, "spread_m3"), ("simple_spread", 10, 3, "spread_m10"),
                 ("simple_speaker_listener", 2, 3, "speaker_listener"), ("simple_reference", 2, 3, "reference"),
                 ("simple_adversary", 3, 2, "adversary"), ("simple_push", 2, 2, "push"), ("simple_tag", 4, 2, "tag"),
-                ("simple_crypto", 3, 2, "crypto"))
+                ("simple_crypto", 3, 2, "crypto"), ("simple_world_comm", 4, 1, "world_comm"))
 
 
 def gen_env(only=None):

@@ -46,3 +46,6 @@ def test_obs_widths_of_the_adversarial_scenarios():
     assert L.mappo_env_obs_width_cfg(cfg(5, 4, 2, 3)) == 62
     # simple_crypto.py:160-171 (tests/golden/env_crypto.npz): adversary 4, listener 8, speaker 8
     assert [L.mappo_env_obs_dim_cfg(cfg(6, 3, 2), i) for i in range(3)] == [4, 8, 8]
+    # simple_world_comm.py:281-288, probed on the reference (4 adversaries, 2 good agents, 1 obstacle): 34 / 28
+    assert [L.mappo_env_obs_dim_cfg(cfg(7, 6, 1, 4), i) for i in range(6)] == [34, 34, 34, 34, 28, 28]
+    assert L.mappo_env_num_landmarks(cfg(7, 6, 1, 4)) == 5 and L.mappo_env_num_landmarks(cfg(0, 3, 3)) == 3

@@ -9,7 +9,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto", "world_comm"]
 
 
 def make_args(scenario, M, L, T=25, N=4, seed=1, **kw):
@@ -27,6 +27,8 @@ def test_env_matches_reference_fixture(tag, golden_dir):
     fx = np.load(os.path.join(golden_dir, "env_%s.npz" % tag))
     N, M, L = int(fx["N"]), int(fx["M"]), int(fx["L"])
     kw = dict(num_adversaries=M - 1, num_good_agents=1) if str(fx["scenario"]) == "simple_tag" else {}
+    if str(fx["scenario"]) == "simple_world_comm":
+        kw = dict(num_adversaries=M - 2, num_good_agents=2)
     env = MPEVecEnv(make_args(str(fx["scenario"]), M, L, int(fx["episode_length"]), N, **kw), device="cuda")
     env.set_state(p_pos=fx["init_p_pos"], p_vel=np.zeros_like(fx["init_p_pos"]), lm_pos=fx["init_lm_pos"],
                   goal=fx["init_goal"])
@@ -69,7 +71,8 @@ def test_env_matches_reference_fixture(tag, golden_dir):
                                                ("simple_adversary", 3, 2, None), ("simple_adversary", 5, 4, None),
                                                ("simple_push", 2, 2, None), ("simple_push", 4, 2, None),
                                                ("simple_tag", 4, 2, 3), ("simple_tag", 6, 3, 2),
-                                               ("simple_crypto", 3, 2, None), ("simple_crypto_display", 3, 4, None)])
+                                               ("simple_crypto", 3, 2, None), ("simple_crypto_display", 3, 4, None),
+                                               ("simple_world_comm", 4, 1, 2), ("simple_world_comm", 6, 2, 4)])
 def test_env_matches_oracle_with_philox_resets(scenario, M, L, nadv):
     """Free-running 60 steps (two auto-resets) at N=1000 with an env-id offset: states equal the oracle's."""
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
@@ -104,6 +107,6 @@ def test_env_matches_oracle_with_philox_resets(scenario, M, L, nadv):
 def test_env_rejects_bad_config():
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
     with pytest.raises(NotImplementedError):
-        MPEVecEnv(make_args("simple_world_comm", 3, 3))
+        MPEVecEnv(make_args("simple_attack", 4, 4))     # broken in the reference itself (NameError: bound), not built
     with pytest.raises(AssertionError):
         MPEVecEnv(make_args("simple_reference", 3, 3))

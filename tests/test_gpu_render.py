@@ -10,7 +10,8 @@ pytestmark = pytest.mark.gpu
 
 CASES = [("simple_spread", 3, 3, {}), ("simple_spread", 10, 3, {}), ("simple_speaker_listener", 2, 3, {}),
          ("simple_reference", 2, 3, {}), ("simple_adversary", 3, 2, {}), ("simple_push", 2, 2, {}),
-         ("simple_tag", 4, 2, dict(num_adversaries=3, num_good_agents=1)), ("simple_crypto", 3, 2, {})]
+         ("simple_tag", 4, 2, dict(num_adversaries=3, num_good_agents=1)), ("simple_crypto", 3, 2, {}),
+         ("simple_world_comm", 4, 1, dict(num_adversaries=2, num_good_agents=2))]
 
 
 def make_env(scenario, M, L, N, **kw):
@@ -29,7 +30,7 @@ def oracle_frames(env, env_ids, w, h):
     out = []
     for k, n in enumerate(env_ids):
         pos = np.concatenate([st["p_pos"][n], st["lm_pos"][n]], 0)
-        comm = np.concatenate([st["comm"][n], -np.ones(env.num_landmarks, np.int64)])
+        comm = np.concatenate([st["comm"][n], -np.ones(env.num_landmarks_total, np.int64)])
         out.append(R.render_env(pos, size, rgba[k], cdim, comm, width=w, height=h))
     return np.stack(out)
 
@@ -44,7 +45,7 @@ def test_render_matches_oracle(scenario, M, L, kw):
         ids = np.stack([rng.randint(0, h[0], (N,)) for h in env.head_sizes], 1)[..., None].astype(np.float32)
         ids = np.repeat(ids, env.act_width, -1)
         if env.act_width == 2:
-            ids[..., 1] = rng.randint(0, 10, (N, env.num_agents))
+            ids[..., 1] = rng.randint(0, min(h[1] for h in env.head_sizes if len(h) > 1), (N, env.num_agents))
         env.step_ids(torch.as_tensor(ids, device="cuda").contiguous())
     sel = [4, 0, 5]
     w, h = 232, 200                                                     # ragged against the 128 x 8 tile

@@ -7,13 +7,15 @@ import pytest
 
 from oracle.mpe import OracleMPE, np_sum_small
 
-TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto"]
+TAGS = ["spread_m3", "spread_m10", "speaker_listener", "reference", "adversary", "push", "tag", "crypto", "world_comm"]
 
 
 def replay(fx, make_env):
     """Replay a fixture through an env implementation; yields per-step comparisons."""
     N, M, L = int(fx["N"]), int(fx["M"]), int(fx["L"])
     kw = dict(num_adversaries=M - 1) if str(fx["scenario"]) == "simple_tag" else {}
+    if str(fx["scenario"]) == "simple_world_comm":
+        kw = dict(num_adversaries=M - 2)
     env = make_env(str(fx["scenario"]), N, M, L, int(fx["episode_length"]), **kw)
     env.reset(state=dict(p_pos=fx["init_p_pos"], lm_pos=fx["init_lm_pos"], goal=fx["init_goal"]))
     obs = env.observations()
