@@ -100,7 +100,8 @@ class _FlatNet(nn.Module):
         self._recurrent_N = args.recurrent_N
         self.device_ = torch.device(device)
         if args.use_popart:
-            raise NotImplementedError("PopArt head is not built yet (SURVEY.md §8f)")
+            raise NotImplementedError("--use_popart raises TypeError inside the reference's PopArt.update "
+                                      "(popart.py:61); not built, see DESIGN.md section 7")
         if self._recurrent and args.recurrent_N != 1:
             raise NotImplementedError("recurrent_N > 1")
         self.cfg = ops.net_config(in_dim, args.hidden_size, args.layer_N, args.use_ReLU,

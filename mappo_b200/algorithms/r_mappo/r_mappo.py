@@ -38,7 +38,10 @@ class R_MAPPO:
         assert (self._use_popart and self._use_valuenorm) == False, \
             ("self._use_popart and self._use_valuenorm can not be set True simultaneously")
         if self._use_popart:
-            raise NotImplementedError("PopArt is not built yet (SURVEY.md §8f)")
+            # the reference's own PopArt cannot run: PopArt.update assigns plain tensors to registered nn.Parameters
+            # (popart.py:61,66-67) -> TypeError at the first cal_value_loss (probed on the unmodified reference)
+            raise NotImplementedError("--use_popart raises TypeError inside the reference's PopArt.update "
+                                      "(popart.py:61); not built, see DESIGN.md section 7")
         self.value_normalizer = ValueNorm(1, device=self.device) if self._use_valuenorm else None
         # multi-GPU hook: callable(tensor) summing it in place over ranks (torch.distributed.all_reduce); None on 1 GPU
         self.all_reduce = None
