@@ -33,7 +33,7 @@ D_OBS, S_OBS, N_ACT, H = 18, 54, 5, 64
 
 
 SCENARIO, ALGO, SEPARATED, CONFIG = "simple_spread", "mappo", False, "C2"
-ACTOR_UPDATE_DRAM_BYTES = 436786944      # 432,684,544 read + 4,102,400 written (profiles/r01_actor_update_tc_v3.md)
+ACTOR_UPDATE_DRAM_BYTES = 439284480      # 432,684,544 read + 4,102,400 written (profiles/r01_actor_update_tc_v3.md)
 
 
 def flags(n_envs):
@@ -325,7 +325,7 @@ def run_ours(ns):
                 "peak_source": "measured bf16 sustained (MEASURED_PEAKS.json)" if peaks else "fallback",
                 "traffic": ACTOR_UPDATE_DRAM_BYTES if (CONFIG == "C2" and n_envs == 65536) else None,
                 "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch "
-                                  "(profiles/r01_actor_update_tc_v3.md); algorithmic 88 B x 4,915,200 rows = 432.5 MB",
+                                  "(profiles/r01_update_tc_v5.md); algorithmic 88 B x 4,915,200 rows = 432.5 MB",
                 "launches": n, "ms_per_launch": per_launch_ms,
                 "flop_per_row": flop_row, "rows_per_launch": rows,
                 "note": "algorithmic fp32-equivalent FLOP; the kernel issues 3-4 fp16 MMAs per product and is bound by "
