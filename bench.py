@@ -33,7 +33,7 @@ D_OBS, S_OBS, N_ACT, H = 18, 54, 5, 64
 
 
 SCENARIO, ALGO, SEPARATED, CONFIG = "simple_spread", "mappo", False, "C2"
-ACTOR_UPDATE_DRAM_BYTES = 439284480      # 432,684,544 read + 4,102,400 written (profiles/r01_actor_update_tc_v3.md)
+ACTOR_UPDATE_DRAM_BYTES = 439284480      # 432,719,104 read + 6,565,376 written (profiles/r01_update_tc_v5.md)
 
 
 def flags(n_envs):
