@@ -192,8 +192,9 @@ def host_boundary_iteration(runner, envs, hb):
     N, M = b.n_rollout_threads, b.num_agents
     h2d = d2h = 0
     for step in range(b.episode_length):
-        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step].reshape(N * M, -1),
-                                                         b.obs[step].view(N * M, -1), None, None, None)
+        # cent_obs = the buffer's share_obs slot [N, M, S] (its M rows per env are one stored row: R_Critic.forward
+        # evaluates each env once); the reference passes np.concatenate of the same slot (mpe_runner.py:99)
+        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step], b.obs[step].view(N * M, -1), None, None, None)
         hb["values"].copy_(values.view(N, M, 1), non_blocking=True)
         hb["actions"].copy_(actions.view(N, M, 1), non_blocking=True)
         hb["logp"].copy_(logp.view(N, M, 1), non_blocking=True)

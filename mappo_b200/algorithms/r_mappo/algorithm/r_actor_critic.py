@@ -267,6 +267,17 @@ class R_Critic(_FlatNet):
     def forward(self, cent_obs, rnn_states, masks):
         """-> (values [B, 1], rnn_states)   r_actor_critic.py:146-165"""
         cent_obs = check(cent_obs, self.device_)
+        if (not self._recurrent and torch.is_tensor(cent_obs) and cent_obs.dim() == 3 and cent_obs.stride(1) == 0
+                and cent_obs.stride(2) == 1):
+            # [N, M, S] with the M agent rows of an env being ONE stored row (the buffer's share_obs view,
+            # utils/shared_buffer.py): evaluate each env once and write its value M times -- the same numbers as the
+            # reference's M replicated rows (shared/mpe_runner.py:133-137), a third of the work
+            N, M = cent_obs.shape[0], cent_obs.shape[1]
+            values = torch.empty(N * M, 1, dtype=torch.float32, device=self.device_)
+            self.forward_into(cent_obs[:, 0, :], values, group=M)
+            return values, check(rnn_states, self.device_)
+        if cent_obs.dim() == 3:
+            cent_obs = cent_obs.reshape(-1, cent_obs.shape[-1])
         values = torch.empty(cent_obs.shape[0], 1, dtype=torch.float32, device=self.device_)
         if self._recurrent:
             rnn_in = check(rnn_states, self.device_).to(torch.float32).contiguous()
