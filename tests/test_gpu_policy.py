@@ -221,3 +221,29 @@ def test_recurrent_forward_and_evaluate_vs_oracle(golden_dir):
     elp, ent = pol.actor.evaluate_actions(obs, rnn_a, actions, masks, None, active)
     np.testing.assert_allclose(elp.cpu().numpy(), lp_e.numpy(), rtol=1e-4, atol=3e-5)
     np.testing.assert_allclose(ent.item(), ent_e.item(), rtol=1e-5)
+
+
+def test_critic_on_the_buffers_replicated_share_obs_view(golden_dir):
+    """R_Critic.forward given the buffer's share_obs slot [N, M, S] (M stride-0 copies of one stored row per env,
+    utils/shared_buffer.py) evaluates each env once and repeats the value: identical to the reference's call on the
+    materialised [N*M, S] concatenation (shared/mpe_runner.py:99,133-137)."""
+    from mappo_b200.envs.spaces import Discrete
+    from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    fx = np.load(os.path.join(golden_dir, "ppo_mlp_tanh.npz"))
+    args = types.SimpleNamespace(**fx_args(fx))
+    args.use_recurrent_policy = args.use_naive_recurrent_policy = False
+    args.recurrent_N = 1; args.use_popart = False; args.use_orthogonal = True; args.seed = 1
+    torch.manual_seed(5)
+    pol = R_MAPPOPolicy(args, make_space(18), make_space(54), Discrete(5), device="cuda")
+    N, M, S = 333, 3, 54
+    uniq = torch.randn(N, S, device="cuda")
+    view = uniq.unsqueeze(1).expand(N, M, S)
+    assert view.stride(1) == 0
+    v_view = pol.get_values(view, None, None)
+    v_full = pol.get_values(view.reshape(N * M, S), None, None)
+    assert v_view.shape == (N * M, 1)
+    torch.testing.assert_close(v_view, v_full, rtol=0, atol=0)
+    # a genuinely different row per agent is not mistaken for the view
+    full3 = torch.randn(N, M, S, device="cuda")
+    torch.testing.assert_close(pol.get_values(full3, None, None), pol.get_values(full3.reshape(N * M, S), None, None),
+                               rtol=0, atol=0)
