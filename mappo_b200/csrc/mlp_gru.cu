@@ -344,21 +344,26 @@ namespace tc {
 
 struct HeadSmem {
   static constexpr int BM = 128;
+  static constexpr int DL = 20;                          // dlogits row stride: 16 logits + 4 (rows 16 B aligned)
   static constexpr int Whf = 0;                          // [16][64] Wh[a][k] gr[k]
   static constexpr int bhf = Whf + kMaxA * 64;           // [16]     bh + Wh ber
   static constexpr int TY = bhf + kMaxA;                 // [BM][kLD] y = LN(h) without the affine
   static constexpr int rstd = TY + BM * kLD;             // [BM]
-  static constexpr int dlog = rstd + BM;                 // [BM][kDL]
-  static constexpr int total = dlog + BM * kDL;
+  static constexpr int dlog = rstd + BM;                 // [BM][DL]
+  static constexpr int total = dlog + BM * DL;
   static constexpr size_t bytes = sizeof(float) * (size_t)total;
 };
 
 // MODE 0 actor rollout (sample / evaluate), 1 critic rollout, 2 actor update, 3 critic update.
 // Row g of this launch is position p = g; its sample row is index[g] (update) or g.  h: [rows][64] hidden states.
+// Per tile of 128 rows: (A) LayerNorm, one warp per row; (B) logits with two threads per row (32 columns each, combined
+// by one shuffle), the loss on the even thread; (C) head weight gradient G_h[a][k] += dlog[r][a] y[r][k] as a register
+// tile -- thread (row group of 32, 4 logits, 4 columns) does 16 FMAs per two 16-byte shared-memory loads and keeps its
+// 4 x 4 block in registers across all tiles; (D) dy = dlog . Wh' and (E) back through the LayerNorm.
 template <int MODE>
 __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const float* __restrict__ h, float* __restrict__ dh) {
   constexpr bool UPDATE = (MODE >= 2);
-  constexpr int BM = HeadSmem::BM, NT = 256, NTY = NT / 16, RPT = BM / NTY, NQ = (kMaxA * 64 + NT - 1) / NT;
+  constexpr int BM = HeadSmem::BM, NT = 256, NTY = NT / 16, RPT = BM / NTY, DL = HeadSmem::DL;
   using S = HeadSmem;
   extern __shared__ __align__(16) float smf[];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
@@ -383,14 +388,16 @@ __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const
     }
     smf[S::bhf + tid] = s;
   }
-  float gh[NQ], dbh[NQ];
+  // phase C mapping: row group (32 rows), logit block (4 logits), column block (4 columns)
+  const int c_k4 = tid & 15, c_ab = (tid >> 4) & 3, c_rg = tid >> 6;
+  float gacc[4][4], sb[4];
   double lacc[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-  for (int q = 0; q < NQ; ++q) gh[q] = dbh[q] = 0.0f;
+  for (int j = 0; j < 4; ++j) { sb[j] = 0.0f; gacc[j][0] = gacc[j][1] = gacc[j][2] = gacc[j][3] = 0.0f; }
   const long long ntiles = (a.rows + BM - 1) / BM;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     __syncthreads();
-    for (int r = warp; r < BM; r += NT / 32) {                            // y = LN(h), one warp per row
+    for (int r = warp; r < BM; r += NT / 32) {                            // (A) y = LN(h), one warp per row
       const long long g = tile * BM + r;
       float v0 = 0.0f, v1 = 0.0f;
       if (g < a.rows) { v0 = h[g * 64 + lane]; v1 = h[g * 64 + lane + 32]; }
@@ -406,55 +413,78 @@ __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const
       if (lane == 0) smf[S::rstd + r] = rstd;
     }
     __syncthreads();
-    if (tid < BM) {
-      const long long g = tile * BM + tid;
+    {                                                                     // (B) logits: two threads per row
+      const int row = tid >> 1, half = tid & 1;
+      const long long g = tile * BM + row;
       float l[kMaxA];
-      float* dl = smf + S::dlog + tid * kDL;
-      if (g < a.rows) {
-        row_logits(smf + S::TY + tid * kLD, smf + S::Whf, smf + S::bhf, A, l);
-        const long long src = a.index ? a.index[g] : g;
-        if (MODE == 0) actor_rollout_row(a, g, l);
-        if (MODE == 1) a.values_out[g] = l[0];
-        if (MODE == 2) actor_loss_row(a, src, l, dl, lacc);
-        if (MODE == 3) {
-          dl[0] = critic_loss_row(a, src, l[0], lacc);
-          for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+#pragma unroll
+      for (int q = 0; q < kMaxA; ++q) l[q] = 0.0f;
+      const float* yrow = smf + S::TY + row * kLD + 32 * half;
+      const float* wbase = smf + S::Whf + 32 * half;
+#pragma unroll 2
+      for (int k4 = 0; k4 < 8; ++k4) {
+        const float4 n = *reinterpret_cast<const float4*>(yrow + 4 * k4);
+#pragma unroll
+        for (int q = 0; q < kMaxA; ++q) {
+          if (q < A) {
+            const float4 w = *reinterpret_cast<const float4*>(wbase + q * 64 + 4 * k4);
+            l[q] = fmaf(n.x, w.x, fmaf(n.y, w.y, fmaf(n.z, w.z, fmaf(n.w, w.w, l[q]))));
+          }
         }
-      } else if (UPDATE) {
-        for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+      }
+#pragma unroll
+      for (int q = 0; q < kMaxA; ++q) {
+        const float other = __shfl_xor_sync(0xffffffffu, l[q], 1);
+        l[q] = smf[S::bhf + q] + (half ? other + l[q] : l[q] + other);    // the same sum on both threads of the row
+      }
+      if (half == 0) {
+        float* dl = smf + S::dlog + row * DL;
+        if (g < a.rows) {
+          const long long src = a.index ? a.index[g] : g;
+          if (MODE == 0) actor_rollout_row(a, g, l);
+          if (MODE == 1) a.values_out[g] = l[0];
+          if (MODE == 2) actor_loss_row(a, src, l, dl, lacc);
+          if (MODE == 3) {
+            dl[0] = critic_loss_row(a, src, l[0], lacc);
+            for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+          }
+        } else if (UPDATE) {
+          for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+        }
       }
     }
     if (!UPDATE) continue;
     __syncthreads();
+    {                                                                     // (C) G_h += dlog^T y over this thread's 32 rows
+      const float* yb = smf + S::TY + 4 * c_k4 + 32 * c_rg * kLD;
+      const float* db = smf + S::dlog + 4 * c_ab + 32 * c_rg * DL;
+#pragma unroll 4
+      for (int rr = 0; rr < 32; ++rr) {
+        const float4 y = *reinterpret_cast<const float4*>(yb + rr * kLD);
+        const float4 d = *reinterpret_cast<const float4*>(db + rr * DL);
+        const float dv[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
-    for (int q = 0; q < NQ; ++q) {                                        // G_h[a][k] += sum_r dlog[r][a] y[r][k]
-      const int o = tid + NT * q;
-      if (o < A * 64) {
-        const int aa = o >> 6, k = o & 63;
-        float s = 0.0f, sb = 0.0f;
-        for (int r = 0; r < BM; ++r) {
-          const float d = smf[S::dlog + r * kDL + aa];
-          s = fmaf(d, smf[S::TY + r * kLD + k], s);
-          sb += d;
+        for (int j = 0; j < 4; ++j) {
+          gacc[j][0] = fmaf(dv[j], y.x, gacc[j][0]); gacc[j][1] = fmaf(dv[j], y.y, gacc[j][1]);
+          gacc[j][2] = fmaf(dv[j], y.z, gacc[j][2]); gacc[j][3] = fmaf(dv[j], y.w, gacc[j][3]);
+          sb[j] += dv[j];
         }
-        gh[q] += s;
-        if (k == 0) dbh[q] += sb;
       }
     }
-    float acc[RPT][4];                                                    // dy = dlog . Wh'
+    float acc[RPT][4];                                                    // (D) dy = dlog . Wh'
 #pragma unroll
     for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
     for (int aa = 0; aa < A; ++aa) {
       const float4 w = *reinterpret_cast<const float4*>(smf + S::Whf + aa * 64 + 4 * tx);
 #pragma unroll
       for (int i = 0; i < RPT; ++i) {
-        const float d = smf[S::dlog + (ty + NTY * i) * kDL + aa];
+        const float d = smf[S::dlog + (ty + NTY * i) * DL + aa];
         acc[i][0] = fmaf(d, w.x, acc[i][0]); acc[i][1] = fmaf(d, w.y, acc[i][1]);
         acc[i][2] = fmaf(d, w.z, acc[i][2]); acc[i][3] = fmaf(d, w.w, acc[i][3]);
       }
     }
 #pragma unroll
-    for (int i = 0; i < RPT; ++i) {                                       // through the LayerNorm: dh = rstd (dy - mean(dy) - y mean(dy y))
+    for (int i = 0; i < RPT; ++i) {                                       // (E) through the LayerNorm: dh = rstd (dy - mean(dy) - y mean(dy y))
       const int r = ty + NTY * i;
       const long long g = tile * BM + r;
       const float4 y = *reinterpret_cast<const float4*>(smf + S::TY + r * kLD + 4 * tx);
@@ -468,29 +498,36 @@ __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const
     }
   }
   if (!UPDATE) return;
-  // head slots of partial row blockIdx.x (the buffer was zeroed by the caller), loss sums
-  float* __restrict__ gp = a.grad_partials + (size_t)blockIdx.x * L.total;
+  // head slots of partial row blockIdx.x (the buffer was zeroed by the caller): the four row groups' register blocks are
+  // summed in group order through shared memory (the y tile and the dlogits tile are free now)
+  __syncthreads();
+  float* red = smf + S::TY;                                               // [4 row groups][16][64]
+  float* redb = smf + S::dlog;                                            // [4 row groups][16]
 #pragma unroll
-  for (int q = 0; q < NQ; ++q) {
-    const int o = tid + NT * q;
-    if (o < A * 64) {
-      const int aa = o >> 6, k = o & 63;
-      int hh = 0, off = 0;
-      while (aa >= off + L.head_dim[hh]) { off += L.head_dim[hh]; ++hh; }
-      gp[L.wh[hh] + (aa - off) * 64 + k] = gh[q];
-      if (k == 0) gp[L.bh[hh] + (aa - off)] = dbh[q];
-    }
+  for (int j = 0; j < 4; ++j) {
+    *reinterpret_cast<float4*>(red + c_rg * (kMaxA * 64) + (4 * c_ab + j) * 64 + 4 * c_k4) =
+        make_float4(gacc[j][0], gacc[j][1], gacc[j][2], gacc[j][3]);
+    if (c_k4 == 0) redb[c_rg * kMaxA + 4 * c_ab + j] = sb[j];
   }
-  __shared__ double red[4][8];
+  __syncthreads();
+  float* __restrict__ gp = a.grad_partials + (size_t)blockIdx.x * L.total;
+  for (int o = tid; o < A * 64; o += NT) {
+    const int aa = o >> 6, k = o & 63;
+    int hh = 0, off = 0;
+    while (aa >= off + L.head_dim[hh]) { off += L.head_dim[hh]; ++hh; }
+    gp[L.wh[hh] + (aa - off) * 64 + k] = (red[o] + red[kMaxA * 64 + o]) + (red[2 * kMaxA * 64 + o] + red[3 * kMaxA * 64 + o]);
+    if (k == 0) gp[L.bh[hh] + (aa - off)] = (redb[aa] + redb[kMaxA + aa]) + (redb[2 * kMaxA + aa] + redb[3 * kMaxA + aa]);
+  }
+  __shared__ double lred[4][8];
   for (int q = 0; q < 4; ++q) {
     double v = lacc[q];
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-    if (lane == 0) red[q][warp] = v;
+    if (lane == 0) lred[q][warp] = v;
   }
   __syncthreads();
   if (tid < 4) {
     double v = 0.0;
-    for (int w = 0; w < NT / 32; ++w) v += red[tid][w];
+    for (int w = 0; w < NT / 32; ++w) v += lred[tid][w];
     a.loss_partials[(size_t)blockIdx.x * 4 + tid] = v;
   }
 }
