@@ -305,13 +305,26 @@ int mappo_actor_update(const mappo_net_config* cfg, const mappo_loss_config* los
  *   storage keeps ONE share_obs row per env and the reference's M replicated rows are a view of it), while
  *   its value_preds / returns / active_masks entries are read at index[i].  1 otherwise.
  *   vn_stats float32[3] AFTER this minibatch's ValueNorm.update (r_mappo.py:65-67) or NULL.
- *   loss_partials double [blocks][4] = {sum value_loss*active, sum active, 0, 0} */
+ *   loss_partials double [blocks][4] = {sum value_loss*active, sum active, 0, 0}
+ *   packed_inputs: NULL, or the buffer mappo_critic_pack_inputs filled from these same share_obs rows (wide first
+ *   layer, no row gather): the forward pass then streams the packed tiles instead of converting the rows again.
+ *   (ABI v3.) */
 int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
                         const float* share_obs, int obs_ld, long long rows, int group, const int64_t* index,
                         int share_rows_div,
                         const float* value_preds, const float* returns, const float* active_masks,
                         const float* vn_stats, float* grad_partials, double* loss_partials, void* workspace,
-                        void* stream);
+                        const void* packed_inputs, void* stream);
+
+/* Wide first layer (in_dim > 64), num_mini_batch == 1: every PPO epoch reads the same share_obs rows and their
+ * LayerNorm does not depend on the weights, so they can be converted ONCE per iteration into the fp16-pair operand
+ * tiles the tensor cores read (per 128 rows: [hi | lo][8-column chunk][row][8 fp16] of LN(x)).
+ *   mappo_critic_packed_bytes: bytes of that buffer for `rows` rows (0: this network does not pack)
+ *   mappo_critic_pack_inputs:  fill it (and the row statistics inside `workspace`, which must be the workspace later
+ *                              passed to mappo_critic_update) */
+long long mappo_critic_packed_bytes(const mappo_net_config* cfg, long long rows);
+int mappo_critic_pack_inputs(const mappo_net_config* cfg, const float* share_obs, int obs_ld, long long rows,
+                             void* packed, void* workspace, void* stream);
 
 /* ---- recurrent (GRU) networks: cfg->recurrent = 1 ---------------------------------------------------------
  *    Replaces RNNLayer.forward (rollout branch and the chunked training branch)   onpolicy/algorithms/utils/rnn.py:24-77

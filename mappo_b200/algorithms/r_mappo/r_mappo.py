@@ -5,6 +5,8 @@ One `ppo_update` is: fused actor forward+loss+backward kernel, fused critic kern
 the per-CTA partial gradients, (multi-GPU: one NCCL all-reduce of the two flat gradient buffers and the loss
 sums), and one kernel per network that finishes the chain rule, clips the global norm and applies Adam.
 Nothing synchronises with the host until `train` returns its six scalars."""
+import os
+
 import numpy as np
 import torch
 
@@ -45,6 +47,7 @@ class R_MAPPO:
         self.value_normalizer = ValueNorm(1, device=self.device) if self._use_valuenorm else None
         # multi-GPU hook: callable(tensor) summing it in place over ranks (torch.distributed.all_reduce); None on 1 GPU
         self.all_reduce = None
+        self.pack_wide_inputs = os.environ.get("MAPPO_PACK_WIDE", "1") != "0"   # A/B switch for the packed first layer
         self._ws = {}
         self._info = torch.zeros(8, **self.tpdv)       # actor {loss, gnorm, entropy, ratio}, critic {loss, gnorm, -, -}
         self._info_total = torch.zeros(8, **self.tpdv)
@@ -82,7 +85,8 @@ class R_MAPPO:
 
     # ------------------------------------------------------------------ core: one minibatch on device tensors
     def _update(self, obs, share_obs, group, actions, old_logp, adv, value_preds, returns, active, avail,
-                rows_total_a, index=None, share_rows_div=1, update_actor=True, vn_batch=None, vn_moments=None):
+                rows_total_a, index=None, share_rows_div=1, update_actor=True, vn_batch=None, vn_moments=None,
+                packed=None):
         """obs [rows_a, D] (strided rows ok); share_obs [rows_c, S]; the per-sample arrays are flat and, with
         `index`, addressed through it.  rows_total_a: number of actor samples in this minibatch."""
         pol = self.policy
@@ -101,7 +105,7 @@ class R_MAPPO:
             self.value_normalizer.update(returns if vn_batch is None else vn_batch, moments=vn_moments)
         ops.critic_update(pol.critic.cfg, loss, pol.critic.flat, share_obs, value_preds, returns, active,
                           None if self.value_normalizer is None else self.value_normalizer.stats,
-                          ws["gpc"], ws["lpc"], group=group, index=index, share_rows_div=share_rows_div)
+                          ws["gpc"], ws["lpc"], group=group, index=index, share_rows_div=share_rows_div, packed=packed)
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows_a
         if self.all_reduce is not None:
@@ -261,6 +265,10 @@ class R_MAPPO:
             self.num_mini_batch == 1 and not buffer.force_permutation
         if whole_batch and self.value_normalizer is not None:
             vn_once = self.value_normalizer.batch_moments(ret)
+        # wide centralised critic: the share_obs rows of the whole batch become packed operand tiles once per iteration
+        packed = None
+        if whole_batch and self.pack_wide_inputs and self.policy.critic.cfg.in_dim > 64:
+            packed = ops.critic_pack_inputs(self.policy.critic.cfg, sh)
         for _ in range(self.ppo_epoch):
             if self._use_recurrent_policy or self._use_naive_recurrent:
                 if self._use_recurrent_policy:
@@ -273,7 +281,7 @@ class R_MAPPO:
             elif self.num_mini_batch == 1 and not buffer.force_permutation:
                 # the loss is a mean over the whole batch: the permutation only reorders the sum
                 self._update(obs_flat, sh, rep, acts, logp, adv, vp, ret, act_m, avail, B, update_actor=update_actor,
-                             vn_moments=vn_once)
+                             vn_moments=vn_once, packed=packed)
                 n_updates += 1
             else:
                 mbs = B // self.num_mini_batch

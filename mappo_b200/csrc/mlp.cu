@@ -15,6 +15,9 @@ namespace tc {   // mlp_tc.cu: the tcgen05 tensor-core tiles
 bool supports(const mappo_net_config* cfg);
 int grid_for(long long rows);
 long long wide_workspace_bytes(long long rows);      // mlp_wide.cu
+long long wide_packed_bytes(int in_dim, long long rows);
+bool wide_pack_ok(const MlpArgs& a);
+int launch_wide_pack(const MlpArgs& a, void* workspace, void* packed, cudaStream_t stream, const char* who);
 template <int MODE> int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who);
 }  // namespace tc
 }  // namespace mappo
@@ -395,7 +398,7 @@ extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss
                                    const int64_t* index, int share_rows_div, const float* value_preds,
                                    const float* returns,
                                    const float* active_masks, const float* vn_stats, float* grad_partials,
-                                   double* loss_partials, void* workspace, void* stream) {
+                                   double* loss_partials, void* workspace, const void* packed_inputs, void* stream) {
   MAPPO_REQUIRE(loss && value_preds && returns && grad_partials && loss_partials && group >= 1,
                 "critic_update: null pointer");
   MAPPO_REQUIRE(!cfg || cfg->is_critic, "critic_update: actor config");
@@ -407,5 +410,26 @@ extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss
   a.x_div = share_rows_div;
   a.value_preds = value_preds; a.returns = returns; a.active = active_masks; a.vn_stats = vn_stats; a.loss = *loss;
   a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
+  a.packed = packed_inputs;
+  MAPPO_REQUIRE(!packed_inputs || (!index && share_rows_div == 1 && cfg->in_dim > kMaxIn && use_tc(cfg)),
+                "critic_update: packed inputs need the wide first layer and no row gather");
   return launch_mlp<3>(a, cfg, (cudaStream_t)stream, "critic_update");
+}
+
+extern "C" long long mappo_critic_packed_bytes(const mappo_net_config* cfg, long long rows) {
+  if (!cfg || rows < 0) return -1;
+  if (!(cfg->in_dim > kMaxIn && use_tc(cfg))) return 0;
+  MlpArgs a{};
+  a.L = make_layout(*cfg); a.x_div = 1;
+  return tc::wide_pack_ok(a) ? tc::wide_packed_bytes(cfg->in_dim, rows) : 0;
+}
+
+extern "C" int mappo_critic_pack_inputs(const mappo_net_config* cfg, const float* share_obs, int obs_ld, long long rows,
+                                        void* packed, void* workspace, void* stream) {
+  if (int rc = check_net(cfg, "critic_pack_inputs")) return rc;
+  MAPPO_REQUIRE(cfg->is_critic && cfg->in_dim > kMaxIn && use_tc(cfg), "critic_pack_inputs: only the wide first layer packs its inputs");
+  MAPPO_REQUIRE(share_obs && packed && workspace && rows > 0 && obs_ld >= cfg->in_dim, "critic_pack_inputs: bad arguments");
+  MlpArgs a{};
+  a.L = make_layout(*cfg); a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.x_div = 1;
+  return tc::launch_wide_pack(a, workspace, packed, (cudaStream_t)stream, "critic_pack_inputs");
 }

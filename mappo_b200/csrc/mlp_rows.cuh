@@ -33,6 +33,7 @@ struct MlpArgs {
   float* grad_partials; double* loss_partials;
   // wide first layer (mlp_wide.cu): caller scratch; z1 = its [rows][64] part (activations in, gradient out)
   void* workspace; float* z1;
+  const void* packed;              // mlp_wide.cu: the input rows as packed fp16-pair operand tiles (wide_pack_kernel), or NULL
   // recurrent networks (mlp_gru.cu): n2 rows out (base features) / dLoss/dn2 rows in (base backward), [rows][64]
   float* feat;
   int raw_ok;                      // mlp_tc.cu: input tiles are contiguous and arrive by bulk copy

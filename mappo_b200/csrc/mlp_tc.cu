@@ -758,6 +758,7 @@ bool wide_supports(const mappo_net_config* cfg);                                
 long long wide_workspace_bytes(long long rows);
 int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
 int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
+int launch_wide_fc1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who);
 
 bool supports(const mappo_net_config* cfg) {
   if (wide_supports(cfg)) return true;
@@ -815,7 +816,8 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
       MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
       a.Kp = 32;
       a.z1 = static_cast<float*>(a.workspace);
-      if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
+      if (a.packed) { if (int rc = launch_wide_fc1_packed(a, a.workspace, a.packed, stream, who)) return rc; }
+      else if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
       if (int rc = launch_one<MODE, 32, 1, true>(a, stream, who)) return rc;
       if (MODE == 3) return launch_wide_wgrad1(a, a.workspace, stream, who);
       return 0;

@@ -208,6 +208,211 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   if (warp == 0) umma::tmem_dealloc(tb, 128);
 }
 
+// ---- packed inputs -------------------------------------------------------------------------------------------
+// With num_mini_batch == 1 every PPO epoch reads the same share_obs rows, and their LayerNorm does not depend on the
+// weights (the affine is folded into W1').  wide_pack_kernel therefore converts them ONCE per iteration into the
+// operand image the tensor cores read -- per 128-row tile: [piece hi | lo][8-column chunk][row][8 fp16] of
+// x^ = LN(x), zero rows / columns as padding -- and fc1_packed_kernel streams those tiles with bulk copies
+// (cp.async.bulk + mbarrier transaction counts) through a 3-stage ring straight into tcgen05.mma: no thread touches an
+// input element.  Warp roles: warp 0 one producer lane, warp 1 one MMA-issuing lane, warps 2..5 drain the two
+// alternating TMEM accumulators to z1.
+__host__ __device__ inline long long packed_tile_bytes(int D) { return 2ll * (2 * ((D + 15) / 16)) * kRowChunk; }
+
+__global__ void __launch_bounds__(kThreads, 1) wide_pack_kernel(const WideArgs a, unsigned char* __restrict__ packed) {
+  __shared__ float2 xch_s[2 * 4 * kBM];
+  const NetLayout& L = a.L;
+  const int D = L.in_dim, K16 = (D + 15) / 16, C8 = 2 * K16, nkc = (K16 + 3) / 4;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
+  const long long ntiles = (a.rows + kBM - 1) / kBM;
+  const long long tile_bytes = packed_tile_bytes(D);
+  int slot = 0;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long g = tile * kBM + r;
+    const bool valid = g < a.rows;
+    const float* __restrict__ row = a.x + (valid ? g : 0) * (long long)a.ld;
+    float ms = 0.0f, rstd = 1.0f, x0 = 0.0f;
+    if (L.use_fn) {                                                     // mlp.py:44-45: LayerNorm over in_dim, eps 1e-5
+      x0 = valid ? __ldg(row) : 0.0f;
+      float s = 0.0f, q = 0.0f;
+      for (int kc = 0; kc < nkc; ++kc) {
+        const int c0 = 64 * kc + 16 * cq;
+        if (c0 < 16 * K16) {
+          float v[16];
+          load8(row, c0, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v));
+          load8(row, c0 + 8, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v + 8));
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float d = (valid && c0 + i < D) ? v[i] - x0 : 0.0f;
+            s += d;
+            q = fmaf(d, d, q);
+          }
+        }
+      }
+      const float2 tot = row_sum2(s, q, xch_s, slot, cq, r, q4);
+      ms = tot.x / (float)D;
+      rstd = 1.0f / sqrtf(fmaxf(tot.y / (float)D - ms * ms, 0.0f) + kLnEps);
+    }
+    if (cq == 0 && valid && a.xstats) { a.xstats[2 * g] = x0 + ms; a.xstats[2 * g + 1] = rstd; }
+    unsigned char* __restrict__ out = packed + tile * tile_bytes;
+    for (int kc = 0; kc < nkc; ++kc) {
+      const int c0 = 64 * kc + 16 * cq;
+      if (c0 >= 16 * K16) continue;
+      float v[16];
+      load8(row, c0, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v));
+      load8(row, c0 + 8, D, valid, a.vec, *reinterpret_cast<float(*)[8]>(v + 8));
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = (valid && c0 + i < D) ? ((v[i] - x0) - ms) * rstd : 0.0f;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint4 hi, lo;
+        split8(v + 8 * h, hi, lo);
+        const long long off = (long long)(8 * kc + 2 * cq + h) * kRowChunk + (long long)r * 16;
+        *reinterpret_cast<uint4*>(out + off) = hi;                      // a warp writes 512 contiguous bytes
+        *reinterpret_cast<uint4*>(out + (long long)C8 * kRowChunk + off) = lo;
+      }
+    }
+  }
+}
+
+constexpr int kPkThreads = 192, kPkStages = 3;
+constexpr uint32_t kPkStage = 2 * 8 * kRowChunk;                        // one 64-column K-chunk, both pieces: 32 KB
+struct PkMap { uint32_t W, w_piece, X, bars, total; int K16; };
+__host__ __device__ inline PkMap make_pk_map(int D) {
+  PkMap m;
+  m.K16 = (D + 15) / 16;
+  m.w_piece = (uint32_t)(2 * m.K16) * kWChunk;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.W = take(2 * m.w_piece);
+  m.X = take(kPkStages * kPkStage);
+  m.bars = take(128);
+  m.total = o;
+  return m;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(umma::smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(umma::smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(umma::smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kPkThreads, 1) fc1_packed_kernel(const WideArgs a, const unsigned char* __restrict__ packed) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const NetLayout& L = a.L;
+  const int D = L.in_dim;
+  const PkMap m = make_pk_map(D);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + m.bars);          // [3] stage landed (transaction bytes)
+  uint64_t* empty = full + kPkStages;                                  // [3] stage read by its MMAs (tcgen05.commit)
+  uint64_t* acc_full = empty + kPkStages;                              // [2] tile accumulated (tcgen05.commit)
+  uint64_t* acc_empty = acc_full + 2;                                  // [2] accumulator drained (4 epilogue warps)
+  if (tid == 0) {
+    for (int i = 0; i < kPkStages; ++i) { umma::mbar_init(full + i, 1); umma::mbar_init(empty + i, 1); }
+    for (int i = 0; i < 2; ++i) { umma::mbar_init(acc_full + i, 1); umma::mbar_init(acc_empty + i, 4); }
+    umma::fence_mbar_init();
+  }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 256);
+  {
+    const float* __restrict__ P = a.params;
+    const int Kp = 16 * m.K16;
+    for (int e = tid; e < 64 * Kp; e += kPkThreads) {
+      const int j = e / Kp, k = e - j * Kp;
+      float v = 0.0f;
+      if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+      put_pair(sm + m.W, m.w_piece, 64, j, k, v);
+    }
+  }
+  umma::fence_async_smem();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const int nkc = (m.K16 + 3) / 4, C8 = 2 * m.K16;
+  const long long ntiles = (a.rows + kBM - 1) / kBM;
+  const long long tile_bytes = packed_tile_bytes(D);
+  if (warp == 0) {
+    if (umma::elect_one()) {                                           // ---- producer
+      const uint32_t sX = umma::smem_u32(sm + m.X);
+      uint32_t it = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const unsigned char* src = packed + tile * tile_bytes;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const uint32_t s = it % kPkStages, ph = (it / kPkStages) & 1;
+          umma::mbar_wait(empty + s, ph ^ 1);
+          const uint32_t bytes = (uint32_t)min(8, C8 - 8 * kc) * kRowChunk;
+          mbar_expect_tx(full + s, 2 * bytes);
+          bulk_g2s(sX + s * kPkStage, src + (long long)(8 * kc) * kRowChunk, bytes, full + s);
+          bulk_g2s(sX + s * kPkStage + 8 * kRowChunk, src + (long long)(C8 + 8 * kc) * kRowChunk, bytes, full + s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (umma::elect_one()) {                                           // ---- MMA issue
+      const uint32_t sX = umma::smem_u32(sm + m.X), sW = umma::smem_u32(sm + m.W);
+      constexpr uint32_t kId = umma::idesc_f16(128, 64, 0, 0);
+      uint32_t it = 0, t = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+        const uint32_t b = t & 1, acc = tb + 128 * b;
+        umma::mbar_wait(acc_empty + b, ((t >> 1) & 1) ^ 1);
+        umma::tc_fence_after();
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const uint32_t s = it % kPkStages, ph = (it / kPkStages) & 1;
+          umma::mbar_wait(full + s, ph);
+          umma::tc_fence_after();
+          const int ksteps = min(4, m.K16 - 4 * kc);
+          for (int ks = 0; ks < ksteps; ++ks) {
+            const uint32_t ao = sX + s * kPkStage + (uint32_t)ks * 2 * kRowChunk;
+            const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * kWChunk;
+            const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
+            const uint64_t bh = umma::smem_desc(bo, kWChunk, 128), bl = umma::smem_desc(bo + m.w_piece, kWChunk, 128);
+            const bool accum = kc > 0 || ks > 0;
+            umma::mma_f16(acc, ah, bh, kId, accum);
+            umma::mma_f16(acc + 64, ah, bl, kId, accum);
+            umma::mma_f16(acc + 64, al, bh, kId, true);
+          }
+          umma::mma_commit(empty + s);
+        }
+        umma::mma_commit(acc_full + b);
+      }
+    }
+  } else {                                                             // ---- epilogue: warps 2..5, TMEM lanes 32 (warp % 4)
+    const int q4 = warp & 3, lane = tid & 31, r = 32 * q4 + lane;
+    const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+    uint32_t t = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+      const uint32_t b = t & 1;
+      umma::mbar_wait(acc_full + b, (t >> 1) & 1);
+      umma::tc_fence_after();
+      const long long g = tile * kBM + r;
+#pragma unroll
+      for (int cq = 0; cq < 4; ++cq) {
+        float u[16], w[16];
+        umma::tmem_ld16x2(lane_addr + 128 * b + 16 * cq, lane_addr + 128 * b + 64 + 16 * cq, u, w);
+        if (g < a.rows) {
+          float4* out = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            out[i] = make_float4(fmaf(w[4 * i], kLoInv, u[4 * i]), fmaf(w[4 * i + 1], kLoInv, u[4 * i + 1]),
+                                 fmaf(w[4 * i + 2], kLoInv, u[4 * i + 2]), fmaf(w[4 * i + 3], kLoInv, u[4 * i + 3]));
+        }
+      }
+      umma::tc_fence_before();
+      __syncwarp();
+      if (umma::elect_one()) mbar_arrive(acc_empty + b);
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 256);
+}
+
 // ---- weight gradient ---------------------------------------------------------------------------------------
 // CTA (column group cg, row split sp) accumulates G[128 = dz1 hi | dz1 lo][colw] over its 64-row half tiles in two TMEM
 // blocks (x^ hi at column 0, x^ lo at column 256).  Operands are MN-major (the contraction runs over the rows): A =
@@ -482,6 +687,38 @@ int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, cons
     attr_set = true;
   }
   fc1_wide_kernel<<<grid_for(a.rows), kThreads, m.total, stream>>>(w);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+// packed inputs (see wide_pack_kernel): bytes of the tile image for `rows` rows, the packing pass, the streamed forward
+long long wide_packed_bytes(int in_dim, long long rows) { return ((rows + kBM - 1) / kBM) * packed_tile_bytes(in_dim); }
+
+bool wide_pack_ok(const MlpArgs& a) {
+  return a.index == nullptr && a.x_div <= 1 && make_pk_map(a.L.in_dim).total <= (uint32_t)kWideMaxSmem;
+}
+
+int launch_wide_pack(const MlpArgs& a, void* workspace, void* packed, cudaStream_t stream, const char* who) {
+  MAPPO_REQUIRE(wide_pack_ok(a) && packed && (reinterpret_cast<uintptr_t>(packed) & 15u) == 0,
+                "%s: inputs cannot be packed (row gather, in_dim %d too wide, or unaligned buffer)", who, a.L.in_dim);
+  WideArgs w{};
+  fill(w, a, workspace);
+  wide_pack_kernel<<<grid_for(a.rows), kThreads, 0, stream>>>(w, static_cast<unsigned char*>(packed));
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+int launch_wide_fc1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who) {
+  WideArgs w{};
+  fill(w, a, workspace);
+  const PkMap m = make_pk_map(a.L.in_dim);
+  MAPPO_REQUIRE(wide_pack_ok(a), "%s: packed inputs do not apply to this call", who);
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(fc1_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideMaxSmem));
+    attr_set = true;
+  }
+  fc1_packed_kernel<<<grid_for(a.rows), kPkThreads, m.total, stream>>>(w, static_cast<const unsigned char*>(packed));
   MAPPO_CHECK_LAUNCH(who);
   return 0;
 }

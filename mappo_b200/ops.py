@@ -162,7 +162,9 @@ _lib._EXTRA_SIGS.update({
     "mappo_advantages": [_P, _P, _P, _P, C.c_longlong, _P, _P, _P],
     "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
     "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P],
-    "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P,
+                            _P],
+    "mappo_critic_pack_inputs": [_NC, _P, C.c_int, C.c_longlong, _P, _P, _P],
     "mappo_grad_reduce": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
     "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P],
 })
@@ -350,8 +352,30 @@ def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, a
                                             stream_ptr()), "actor_update")
 
 
+def critic_pack_inputs(cfg, share_obs):
+    """Wide first layer: convert the share_obs rows once into the packed fp16-pair operand tiles every epoch's forward
+    pass then streams (mappo_critic_pack_inputs).  Returns the packed buffer (kept per device), or None when this
+    network does not pack.  Pass it to critic_update(packed=...) with the SAME rows."""
+    x, ld = _rows_view(share_obs)
+    L = _lib.lib()
+    L.mappo_critic_packed_bytes.argtypes = [_NC, C.c_longlong]
+    L.mappo_critic_packed_bytes.restype = C.c_longlong
+    need = int(L.mappo_critic_packed_bytes(C.byref(cfg), int(x.shape[0])))
+    if need <= 0:
+        return None
+    key = (x.device, "packed")
+    buf = _WORKSPACES.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.uint8, device=x.device)
+        _WORKSPACES[key] = buf
+    ws = mlp_workspace(cfg, x.shape[0], x.device)
+    check(L.mappo_critic_pack_inputs(C.byref(cfg), _vp(x), ld, x.shape[0], ptr(buf), ptr(ws), stream_ptr()),
+          "critic_pack_inputs")
+    return buf
+
+
 def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_masks, vn_stats, grad_partials,
-                  loss_partials, group=1, index=None, share_rows_div=1):
+                  loss_partials, group=1, index=None, share_rows_div=1, packed=None):
     x, ld = _rows_view(share_obs)
     rows = x.shape[0] if index is None else index.numel()
     ws = mlp_workspace(cfg, rows, x.device)
@@ -359,7 +383,7 @@ def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_mas
         check(_lib.lib().mappo_critic_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(x), ld, rows, int(group),
                                              ptr(index), int(share_rows_div), ptr(value_preds), ptr(returns),
                                              ptr(active_masks), ptr(vn_stats), ptr(grad_partials), ptr(loss_partials),
-                                             ptr(ws), stream_ptr()), "critic_update")
+                                             ptr(ws), ptr(packed), stream_ptr()), "critic_update")
 
 
 def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):

@@ -97,3 +97,52 @@ def test_wide_critic_strided_rows_and_row_gather():
     # group = 3: the same thing without an index
     g3, l3 = run(share, 900, vp=rep(vp), ret=rep(ret), am=rep(am), group=3)
     assert (3 * g0 - g3).abs().max().item() < 6e-5 * scale
+
+
+@pytest.mark.parametrize("S,B,flags", [(460, 1000, ""), (460, 12800 + 77, "--use_ReLU"), (100, 129, "--use_feature_normalization"),
+                                       (96, 300, "")])
+def test_packed_inputs_give_the_same_update(S, B, flags):
+    """num_mini_batch == 1: the share_obs rows are packed once per iteration into fp16-pair operand tiles
+    (mappo_critic_pack_inputs) and every epoch's forward streams them (fc1_packed_kernel).  Loss sums and gradient sums
+    equal the unpacked path's to the precision of the operand pairs (2^-22 relative per product), over several tiles per
+    CTA, a ragged last tile and strided rows."""
+    from mappo_b200 import ops
+    a, pol, tr, sample = _setup(S, B, flags)
+    cfg, flat = pol.critic.cfg, pol.critic.flat
+    share, vp, ret, am = sample[0], sample[5].reshape(-1), sample[6].reshape(-1), sample[8].reshape(-1)
+    loss, vn, P = tr._loss_config(), tr.value_normalizer.stats, flat.numel()
+
+    def run(x, packed):
+        nb = ops.update_num_blocks(cfg, B)
+        gp = torch.empty(nb, P, device="cuda"); lp = torch.empty(nb, 4, dtype=torch.float64, device="cuda")
+        ops.critic_update(cfg, loss, flat, x, vp, ret, am, vn, gp, lp, packed=packed)
+        gs = torch.empty(P, device="cuda"); ls = torch.empty(4, dtype=torch.float64, device="cuda")
+        ops.grad_reduce(gp, lp, nb, gs, ls)
+        torch.cuda.synchronize()
+        return gs.double(), ls
+    g0, l0 = run(share, None)
+    packed = ops.critic_pack_inputs(cfg, share)
+    assert packed is not None and packed.dtype == torch.uint8
+    for _ in range(2):                                                   # the packed tiles survive an update (epochs)
+        g1, l1 = run(share, packed)
+        scale = g0.abs().max().item()
+        assert (g0 - g1).abs().max().item() < 2e-5 * scale, (g0 - g1).abs().max().item() / scale
+        np.testing.assert_allclose(l1.cpu().numpy(), l0.cpu().numpy(), rtol=1e-6)
+    wide = torch.zeros(B, S + 8, device="cuda")
+    wide[:, 4:4 + S] = share
+    packed = ops.critic_pack_inputs(cfg, wide[:, 4:4 + S])
+    g2, l2 = run(wide[:, 4:4 + S], packed)
+    assert (g0 - g2).abs().max().item() < 2e-5 * scale
+
+
+def test_packing_is_refused_with_a_row_gather():
+    from mappo_b200 import ops
+    a, pol, tr, sample = _setup(460, 600, "")
+    cfg, flat = pol.critic.cfg, pol.critic.flat
+    share, vp, ret, am = sample[0], sample[5].reshape(-1), sample[6].reshape(-1), sample[8].reshape(-1)
+    packed = ops.critic_pack_inputs(cfg, share)
+    nb, P = ops.update_num_blocks(cfg, 600), flat.numel()
+    gp = torch.empty(nb, P, device="cuda"); lp = torch.empty(nb, 4, dtype=torch.float64, device="cuda")
+    with pytest.raises(AssertionError):
+        ops.critic_update(cfg, tr._loss_config(), flat, share, vp, ret, am, tr.value_normalizer.stats, gp, lp,
+                          index=torch.randperm(600, device="cuda"), packed=packed)
