@@ -759,6 +759,7 @@ long long wide_workspace_bytes(long long rows);
 int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
 int launch_wide_wgrad1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who);
 int launch_wide_fc1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who);
+int launch_wide_wgrad1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who);
 
 bool supports(const mappo_net_config* cfg) {
   if (wide_supports(cfg)) return true;
@@ -819,6 +820,7 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
       if (a.packed) { if (int rc = launch_wide_fc1_packed(a, a.workspace, a.packed, stream, who)) return rc; }
       else if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
       if (int rc = launch_one<MODE, 32, 1, true>(a, stream, who)) return rc;
+      if (MODE == 3 && a.packed) return launch_wide_wgrad1_packed(a, a.workspace, a.packed, stream, who);
       if (MODE == 3) return launch_wide_wgrad1(a, a.workspace, stream, who);
       return 0;
     }

@@ -651,6 +651,135 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
   if (warp == 0) umma::tmem_dealloc(tb, 512);
 }
 
+// ---- weight gradient from packed inputs ------------------------------------------------------------------------
+// G1[64][D] = sum_rows dz1^T x^ with x^ read from the packed tiles: the bytes of a tile that served as the K-major A
+// operand of the forward are, unchanged, the MN-major B operand here (umma.cuh).  CTA (column group of up to 16
+// 8-column chunks, row split) walks its 128-row tiles through a 2-stage ring: warp 0's elected lane fetches the group's
+// hi and lo chunk ranges with two bulk copies per tile, warps 2..5 turn the tile's dz1 rows into the stacked fp16-pair A
+// operand ([hi columns | lo columns] = M 128), warp 1's elected lane issues 8 K-steps x 2 MMAs into two TMEM blocks.
+constexpr int kPgChunks = 16;                                           // 8-column chunks per column group (N <= 128)
+constexpr uint32_t kPgB = 2 * kPgChunks * kRowChunk;                    // one B stage: both pieces, 64 KB
+constexpr uint32_t kPgA = 16 * kRowChunk;                               // one A stage: dz1 hi | lo, 32 KB
+struct PgMap { uint32_t A, B, bars, total; };
+__host__ __device__ inline PgMap make_pg_map() {
+  PgMap m;
+  uint32_t o = 0;
+  auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
+  m.A = take(2 * kPgA);
+  m.B = take(2 * kPgB);
+  m.bars = take(128);
+  m.total = o;
+  return m;
+}
+
+__global__ void __launch_bounds__(kPkThreads, 1) wgrad1_packed_kernel(const WideArgs a, const unsigned char* __restrict__ packed) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_base_s;
+  const int D = a.D, K16 = (D + 15) / 16, C8 = 2 * K16;
+  const PgMap m = make_pg_map();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int cg = blockIdx.x % a.ncg, sp = blockIdx.x / a.ncg;
+  const int ch0 = cg * kPgChunks, nch = min(kPgChunks, C8 - ch0), N = 8 * nch;   // this group's chunks; N is a multiple of 16
+  uint64_t* b_full = reinterpret_cast<uint64_t*>(sm + m.bars);        // [2] B stage landed
+  uint64_t* a_full = b_full + 2;                                       // [2] A stage converted (4 warps)
+  uint64_t* st_empty = a_full + 2;                                     // [2] stage read by its MMAs
+  uint64_t* done = st_empty + 2;                                       // all MMAs of this CTA
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { umma::mbar_init(b_full + i, 1); umma::mbar_init(a_full + i, 4); umma::mbar_init(st_empty + i, 1); }
+    umma::mbar_init(done, 1);
+    umma::fence_mbar_init();
+  }
+  if (warp == 0) umma::tmem_alloc(&tmem_base_s, 256);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tb = tmem_base_s;
+  const long long ntiles = (a.rows + kBM - 1) / kBM;
+  const long long tile_bytes = packed_tile_bytes(D);
+  uint32_t my_tiles = 0;
+  for (long long t = sp; t < ntiles; t += a.nsplit) ++my_tiles;
+  if (warp == 0) {
+    if (umma::elect_one()) {                                           // ---- producer: x^ chunks [ch0, ch0 + nch), hi and lo
+      const uint32_t sB = umma::smem_u32(sm + m.B);
+      const uint32_t bytes = (uint32_t)nch * kRowChunk;
+      uint32_t it = 0;
+      for (long long t = sp; t < ntiles; t += a.nsplit, ++it) {
+        const uint32_t s = it & 1, ph = (it >> 1) & 1;
+        umma::mbar_wait(st_empty + s, ph ^ 1);
+        const unsigned char* src = packed + t * tile_bytes + (long long)ch0 * kRowChunk;
+        mbar_expect_tx(b_full + s, 2 * bytes);
+        bulk_g2s(sB + s * kPgB, src, bytes, b_full + s);
+        bulk_g2s(sB + s * kPgB + kPgChunks * kRowChunk, src + (long long)C8 * kRowChunk, bytes, b_full + s);
+      }
+    }
+  } else if (warp == 1) {
+    if (umma::elect_one()) {                                           // ---- MMA issue
+      const uint32_t sA = umma::smem_u32(sm + m.A), sB = umma::smem_u32(sm + m.B);
+      const uint32_t idesc = umma::idesc_f16(128, N, 1, 1);
+      for (uint32_t it = 0; it < my_tiles; ++it) {
+        const uint32_t s = it & 1, ph = (it >> 1) & 1;
+        umma::mbar_wait(a_full + s, ph);
+        umma::mbar_wait(b_full + s, ph);
+        umma::tc_fence_after();
+#pragma unroll
+        for (int ks = 0; ks < kBM / 16; ++ks) {
+          const uint64_t da = umma::smem_desc(sA + s * kPgA + (uint32_t)ks * 256, 128, kRowChunk);
+          const uint64_t dh = umma::smem_desc(sB + s * kPgB + (uint32_t)ks * 256, 128, kRowChunk);
+          const uint64_t dl = umma::smem_desc(sB + s * kPgB + kPgChunks * kRowChunk + (uint32_t)ks * 256, 128, kRowChunk);
+          umma::mma_f16(tb, da, dh, idesc, it > 0 || ks > 0);
+          umma::mma_f16(tb + 128, da, dl, idesc, it > 0 || ks > 0);
+        }
+        umma::mma_commit(st_empty + s);
+      }
+      umma::mma_commit(done);
+    }
+  } else {                                                             // ---- warps 2..5: dz1 rows -> A operand, then the epilogue
+    const int r = 32 * (warp - 2) + lane;                              // row of the tile this thread converts
+    uint32_t it = 0;
+    for (long long t = sp; t < ntiles; t += a.nsplit, ++it) {
+      const uint32_t s = it & 1, ph = (it >> 1) & 1;
+      const long long g = t * kBM + r;
+      float v[64];
+      if (g < a.rows) {
+        const float4* src = reinterpret_cast<const float4*>(a.dz1 + g * a.dz_ld);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { const float4 q = __ldg(src + i); v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w; }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) v[i] = 0.0f;
+      }
+      umma::mbar_wait(st_empty + s, ph ^ 1);
+#pragma unroll
+      for (int cq = 0; cq < 4; ++cq) store_cols16(sm + m.A + s * kPgA, r, cq, v + 16 * cq);
+      umma::fence_async_smem();
+      __syncwarp();
+      if (umma::elect_one()) mbar_arrive(a_full + s);
+    }
+    // G -> the W1 slots of partial rows 2 sp (lanes 0..63: dz1 hi) and 2 sp + 1 (lanes 64..127: dz1 lo, scaled)
+    if (my_tiles > 0) {
+      umma::mbar_wait(done, 0);
+      umma::tc_fence_after();
+      const int q4 = warp & 3, rr = 32 * q4 + lane;
+      const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
+      float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * a.total + a.out_w;
+      const int j = rr & 63;
+      const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;
+      for (int blk = 0; blk < N / 16; ++blk) {
+        float u[16], w[16];
+        umma::tmem_ld16x2(lane_addr + 16 * blk, lane_addr + 128 + 16 * blk, u, w);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int k = 8 * ch0 + 16 * blk + i;
+          if (k < D) gp[(size_t)j * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+        }
+      }
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tb, 256);
+}
+
 // ---- host side ---------------------------------------------------------------------------------------------
 constexpr int kWideMaxSmem = 232448 - 1024;
 
@@ -719,6 +848,29 @@ int launch_wide_fc1_packed(const MlpArgs& a, void* workspace, const void* packed
     attr_set = true;
   }
   fc1_packed_kernel<<<grid_for(a.rows), kPkThreads, m.total, stream>>>(w, static_cast<const unsigned char*>(packed));
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+int launch_wide_wgrad1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who) {
+  WideArgs w{};
+  fill(w, a, workspace);
+  w.grad_partials = a.grad_partials;
+  MAPPO_REQUIRE(wide_pack_ok(a) && (w.dz_ld & 3) == 0, "%s: packed inputs do not apply to this call", who);
+  const int C8 = 2 * ((w.D + 15) / 16);
+  w.ncg = (C8 + kPgChunks - 1) / kPgChunks;
+  const long long ntiles = (w.rows + kBM - 1) / kBM;
+  long long ns = grid_for(w.rows) / w.ncg;                               // <= the main kernel's CTAs (2 partial rows each)
+  if (ns < 1) ns = 1;
+  if (ns > ntiles) ns = ntiles;
+  w.nsplit = (int)ns;
+  const PgMap m = make_pg_map();
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m.total));
+    attr_set = true;
+  }
+  wgrad1_packed_kernel<<<w.ncg * w.nsplit, kPkThreads, m.total, stream>>>(w, static_cast<const unsigned char*>(packed));
   MAPPO_CHECK_LAUNCH(who);
   return 0;
 }

@@ -100,10 +100,11 @@ def test_wide_critic_strided_rows_and_row_gather():
 
 
 @pytest.mark.parametrize("S,B,flags", [(460, 1000, ""), (460, 12800 + 77, "--use_ReLU"), (100, 129, "--use_feature_normalization"),
-                                       (96, 300, "")])
+                                       (96, 300, ""), (460, 51205, ""), (300, 3000, "")])
 def test_packed_inputs_give_the_same_update(S, B, flags):
     """num_mini_batch == 1: the share_obs rows are packed once per iteration into fp16-pair operand tiles
-    (mappo_critic_pack_inputs) and every epoch's forward streams them (fc1_packed_kernel).  Loss sums and gradient sums
+    (mappo_critic_pack_inputs); every epoch's forward (fc1_packed_kernel) and first-layer weight gradient
+    (wgrad1_packed_kernel, 2-stage ring: 51205 rows give 11 tiles per CTA, in_dim 300 three column groups, the last 48 columns wide) stream them.  Loss sums and gradient sums
     equal the unpacked path's to the precision of the operand pairs (2^-22 relative per product), over several tiles per
     CTA, a ragged last tile and strided rows."""
     from mappo_b200 import ops
