@@ -45,7 +45,7 @@ def flags(n_envs):
 
 def set_workload(num_agents, config=None):
     """Default M = 3 is C2 (the configuration the metric is quoted on).  --agents 10 / --config c5: the C5 shape;
-    --config c3: speaker_listener with separated policies (15 epochs); --config c4: simple_reference with the
+    --config c3: speaker_listener with separated policies (15 epochs), c3r: the same with GRU policies; --config c4: simple_reference with the
     shared GRU policy (rmappo, chunks of 10, 15 epochs).  Only the default is the contract line; the others are
     supplementary measurements of the remaining BASELINE configs."""
     global M_AGENTS, D_OBS, S_OBS, SCENARIO, ALGO, SEPARATED, PPO_EPOCH, CONFIG
@@ -54,15 +54,17 @@ def set_workload(num_agents, config=None):
         M_AGENTS = 10
     if config == "c3":
         SCENARIO, SEPARATED, M_AGENTS, PPO_EPOCH = "simple_speaker_listener", True, 2, 15
+    if config == "c3r":                                    # the reference's train_mpe_comm.sh as is: separated + GRU
+        SCENARIO, SEPARATED, ALGO, M_AGENTS, PPO_EPOCH = "simple_speaker_listener", True, "rmappo", 2, 15
     if config == "c4":
         SCENARIO, ALGO, M_AGENTS, PPO_EPOCH = "simple_reference", "rmappo", 2, 15
     D_OBS = 4 + 2 * N_LANDMARKS + 4 * (M_AGENTS - 1)       # simple_spread.py:93-103
     S_OBS = D_OBS * M_AGENTS
-    CONFIG = {"c3": "C3", "c4": "C4"}.get(config, "C2" if M_AGENTS == 3 else "C5" if M_AGENTS == 10 else "custom")
+    CONFIG = {"c3": "C3", "c3r": "C3 (rmappo)", "c4": "C4"}.get(config, "C2" if M_AGENTS == 3 else "C5" if M_AGENTS == 10 else "custom")
 
 
 def workload_name(n_envs, n_gpus):
-    kind = "separated MLP policies" if SEPARATED else ("shared GRU policy, chunks of 10" if ALGO == "rmappo" else "shared MLP")
+    kind = ("separated GRU policies, chunks of 10" if ALGO == "rmappo" else "separated MLP policies") if SEPARATED else ("shared GRU policy, chunks of 10" if ALGO == "rmappo" else "shared MLP")
     return ("%s: MPE %s M=%d L=3, %d envs/GPU x %d GPU, T=25, %s (Tanh, H=64), ppo_epoch=%d, "
             "num_mini_batch=1, GAE+ValueNorm" % (CONFIG, SCENARIO, M_AGENTS, n_envs, n_gpus, kind, PPO_EPOCH))
 
@@ -371,13 +373,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
     ap.add_argument("--agents", type=int, default=3, help="agents per env (3 = C2, the headline; 10 = C5 shape)")
-    ap.add_argument("--config", default=None, choices=["c3", "c4", "c5"], help="supplementary BASELINE configs")
+    ap.add_argument("--config", default=None, choices=["c3", "c3r", "c4", "c5"], help="supplementary BASELINE configs")
     ap.add_argument("--cpu-envs", dest="cpu_envs", type=int, default=1024, help="envs of the bounded CPU sample")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
     ns = ap.parse_args()
     set_workload(ns.agents, ns.config)
-    if ns.config in ("c3", "c4") and ns.envs == 65536:
+    if ns.config in ("c3", "c3r", "c4") and ns.envs == 65536:
         ns.envs = 32768
     ns.warmup = max(ns.warmup, 0)
     if ns.impl == "reference":

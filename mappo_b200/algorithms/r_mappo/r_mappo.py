@@ -49,6 +49,7 @@ class R_MAPPO:
         self.all_reduce = None
         self.pack_wide_inputs = os.environ.get("MAPPO_PACK_WIDE", "1") != "0"   # A/B switch for the packed first layer
         self._ws = {}
+        self._seed_scratch = {}
         self._info = torch.zeros(8, **self.tpdv)       # actor {loss, gnorm, entropy, ratio}, critic {loss, gnorm, -, -}
         self._info_total = torch.zeros(8, **self.tpdv)
 
@@ -124,6 +125,19 @@ class R_MAPPO:
         copt.step_count += 1
         self._info_total += self._info
         return ws
+
+    def _seeded_states(self, v, first_rows, seed_rows):
+        """The kernels read the initial state of slot c at the sample row of its step 0 (`first_rows[c]`).  Where the
+        buffer keeps it elsewhere (SeparatedReplayBuffer.recurrent_rows), copy it there in a scratch array of the same
+        shape; only those Nc rows of the scratch are ever read."""
+        out = dict(v)
+        for k in ("rnn", "rnn_critic"):
+            sc = self._seed_scratch.get(k)
+            if sc is None or sc.shape != v[k].shape:
+                sc = self._seed_scratch[k] = torch.empty_like(v[k])
+            sc.index_copy_(0, first_rows, v[k].index_select(0, seed_rows))
+            out[k] = sc
+        return out
 
     def _update_rnn(self, v, idx, n_chunks, L, update_actor=True):
         """One recurrent minibatch: idx int64 [L * n_chunks] (step-major) flat sample rows of the chunks
@@ -275,8 +289,11 @@ class R_MAPPO:
                     batches = buffer.recurrent_rows(self.num_mini_batch, self.data_chunk_length)
                 else:
                     batches = buffer.naive_recurrent_rows(self.num_mini_batch)
-                for rows_idx, n_chunks, L in batches:
-                    self._update_rnn(v, rows_idx, n_chunks, L, update_actor=update_actor)
+                for batch in batches:
+                    rows_idx, n_chunks, L = batch[:3]
+                    seed = batch[3] if len(batch) > 3 else None
+                    vb = v if seed is None else self._seeded_states(v, rows_idx[:n_chunks], seed)
+                    self._update_rnn(vb, rows_idx, n_chunks, L, update_actor=update_actor)
                     n_updates += 1
             elif self.num_mini_batch == 1 and not buffer.force_permutation:
                 # the loss is a mean over the whole batch: the permutation only reorders the sum

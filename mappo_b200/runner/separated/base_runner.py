@@ -84,7 +84,12 @@ class Runner(object):
             self.trainer[agent_id].prep_rollout()
             b = self.buffer[agent_id]
             nv = torch.empty(b.n_rollout_threads, 1, dtype=torch.float32, device=b.device)
-            self.policy[agent_id].critic.forward_into(b.share_obs[-1], nv, group=1)
+            if b._recurrent:
+                self.policy[agent_id].critic.forward_into(b.share_obs[-1], nv, rnn_in=b.rnn_states_critic[-1],
+                                                          masks=b.masks[-1],
+                                                          rnn_out=torch.empty_like(b.rnn_states_critic[-1]))
+            else:
+                self.policy[agent_id].critic.forward_into(b.share_obs[-1], nv, group=1)
             b.compute_returns(nv, self.trainer[agent_id].value_normalizer)
 
     def train(self):

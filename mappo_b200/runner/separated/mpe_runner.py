@@ -72,8 +72,15 @@ class MPERunner(Runner):
         for agent_id in range(self.num_agents):
             self.trainer[agent_id].prep_rollout()
             b, pol = self.buffer[agent_id], self.trainer[agent_id].policy
-            pol.actor.forward_into(b.obs[step], b.actions[step], b.action_log_probs[step], row_offset=off)
-            pol.critic.forward_into(b.share_obs[step], b.value_preds[step], group=1)
+            if b._recurrent:
+                # rnn.py:24-28: h = GRU(x, h * mask); the new states go straight into slot step + 1
+                pol.actor.forward_into(b.obs[step], b.actions[step], b.action_log_probs[step], row_offset=off,
+                                       rnn_in=b.rnn_states[step], masks=b.masks[step], rnn_out=b.rnn_states[step + 1])
+                pol.critic.forward_into(b.share_obs[step], b.value_preds[step], rnn_in=b.rnn_states_critic[step],
+                                        masks=b.masks[step], rnn_out=b.rnn_states_critic[step + 1])
+            else:
+                pol.actor.forward_into(b.obs[step], b.actions[step], b.action_log_probs[step], row_offset=off)
+                pol.critic.forward_into(b.share_obs[step], b.value_preds[step], group=1)
             self._act_env[:, agent_id, :b.actions.shape[2]].copy_(b.actions[step])
             values.append(b.value_preds[step]); actions.append(b.actions[step]); logps.append(b.action_log_probs[step])
             rs.append(b.rnn_states[step + 1]); rsc.append(b.rnn_states_critic[step + 1])
@@ -84,6 +91,11 @@ class MPERunner(Runner):
         obs, rewards, masks, infos, values, actions, action_log_probs, rnn_states, rnn_states_critic = data
         for agent_id in range(self.num_agents):
             b = self.buffer[agent_id]
+            if b._recurrent:
+                # mpe_runner.py:145-146: states of finished episodes are zeroed (masks = 1 - done)
+                keep = masks[:, agent_id].unsqueeze(-1)
+                b.rnn_states[b.step + 1].mul_(keep)
+                b.rnn_states_critic[b.step + 1].mul_(keep)
             b.insert(b.share_obs[b.step + 1], b.obs[b.step + 1], None, None, actions[agent_id],
                      action_log_probs[agent_id], values[agent_id], rewards[:, agent_id], masks[:, agent_id])
 
@@ -96,15 +108,24 @@ class MPERunner(Runner):
         acts = torch.zeros(N, M, envs.act_width, dtype=torch.float32, device=self.device)
         total = torch.zeros(N, M, 1, dtype=torch.float32, device=self.device)
         views = envs._shape_obs(envs._obs)
+        recurrent = bool(self.buffer[0]._recurrent)
+        f = dict(dtype=torch.float32, device=self.device)
+        rnn = [torch.zeros(N, self.recurrent_N, self.hidden_size, **f) for _ in range(M)]
+        nxt = [torch.empty_like(x) for x in rnn]
+        masks = torch.ones(N, M, 1, **f)
         for _ in range(self.episode_length):
             for agent_id in range(M):
                 h = len(envs.head_sizes[agent_id])
-                a = torch.empty(N, h, dtype=torch.float32, device=self.device)
+                a = torch.empty(N, h, **f)
+                kw = dict(rnn_in=rnn[agent_id], masks=masks[:, agent_id].contiguous(), rnn_out=nxt[agent_id]) \
+                    if recurrent else {}
                 self.trainer[agent_id].policy.actor.forward_into(
                     views[:, agent_id] if torch.is_tensor(views) else views[agent_id], a, torch.empty_like(a),
-                    deterministic=True)
+                    deterministic=True, **kw)
                 acts[:, agent_id, :h].copy_(a)
-            _, rew, _ = envs.step_ids(acts)
+            _, rew, m = envs.step_ids(acts)
+            masks = m.view(N, M, 1).clone()                              # mpe_runner.py:213-216: h * mask at the next step
+            rnn, nxt = nxt, rnn
             total += rew
         out = []
         for agent_id in range(M):

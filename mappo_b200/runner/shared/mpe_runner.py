@@ -170,9 +170,16 @@ class MPERunner(Runner):
         acts = torch.empty(N, M, envs.act_width, dtype=torch.float32, device=self.device)
         lps = torch.empty_like(acts)
         total = torch.zeros(N, M, 1, dtype=torch.float32, device=self.device)
+        recurrent = bool(self.buffer._recurrent)
+        rnn = torch.zeros(N, M, self.recurrent_N, self.hidden_size, dtype=torch.float32, device=self.device)
+        nxt = torch.empty_like(rnn)
+        masks = torch.ones(N, M, 1, dtype=torch.float32, device=self.device)
         for _ in range(self.episode_length):
-            self.trainer.policy.actor.forward_into(envs._obs.view(N * M, -1), acts, lps, deterministic=True)
-            _, rew, _ = envs.step_ids(acts)
+            kw = dict(rnn_in=rnn, masks=masks, rnn_out=nxt) if recurrent else {}
+            self.trainer.policy.actor.forward_into(envs._obs.view(N * M, -1), acts, lps, deterministic=True, **kw)
+            _, rew, m = envs.step_ids(acts)
+            masks = m.view(N, M, 1).clone()                              # mpe_runner.py:166-169: h * mask at the next step
+            rnn, nxt = nxt, rnn
             total += rew
         r = float(total.mean().item())
         print("eval average episode rewards of agent: " + str(r))

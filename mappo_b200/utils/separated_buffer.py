@@ -104,7 +104,41 @@ class SeparatedReplayBuffer(object):
         return dict(B=B, M=1, obs=obs, share=share, share_is_unique=False,
                     actions=self.actions.view(B, -1), logp=self.action_log_probs.view(B, -1),
                     value_preds=self.value_preds[:-1].view(B), returns=self.returns[:-1].view(B),
-                    active=self.active_masks[:-1].view(B), avail=avail)
+                    active=self.active_masks[:-1].view(B), avail=avail, masks=self.masks[:-1].view(B),
+                    rnn=self.rnn_states[:-1].reshape(B, -1) if self._recurrent else None,
+                    rnn_critic=self.rnn_states_critic[:-1].reshape(B, -1) if self._recurrent else None)
+
+    def recurrent_rows(self, num_mini_batch, data_chunk_length):
+        """Index form of recurrent_generator (separated_buffer.py:289-393) for the fused kernels: per minibatch
+        (rows int64 [Nc * L], Nc, L, seed_rows int64 [Nc]).  The reference stacks a minibatch as (Nc, L) and flattens it
+        as if it were (L, Nc) (see recurrent_generator below), so the sample the network sees at step s of slot c is
+        flat element p = s * Nc + c of the (Nc, L) stack: chunk p // L, offset p % L -- `rows` is exactly that stack,
+        flattened.  The initial state of slot c is still the one stored at the first row of chunk c: `seed_rows`."""
+        T, N = self.rewards.shape[0:2]
+        L = data_chunk_length
+        data_chunks = (N * T) // L
+        mini_batch_size = data_chunks // num_mini_batch
+        rand = torch.randperm(data_chunks).to(self.device)
+        dev = self.device
+        ar = torch.arange(L, device=dev)
+        for i in range(num_mini_batch):
+            idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size]
+            pos = idx[:, None] * L + ar[None, :]                                   # [N, T]-ordered stream positions
+            rows = ((pos % T) * N + pos // T).reshape(-1).contiguous()              # -> rows of the [T, N] arrays
+            seed = ((idx * L) % T) * N + (idx * L) // T
+            yield rows, int(idx.numel()), L, seed
+
+    def naive_recurrent_rows(self, num_mini_batch):
+        """Index form of naive_recurrent_generator (separated_buffer.py:215-287): whole trajectories, step-major."""
+        T, N = self.rewards.shape[0:2]
+        per = N // num_mini_batch
+        perm = torch.randperm(N).to(self.device)
+        tt = torch.arange(T, device=self.device)
+        for start in range(0, N, per):
+            idx = perm[start:start + per]
+            if idx.numel() < per:
+                break
+            yield (tt[:, None] * N + idx[None, :]).reshape(-1).contiguous(), int(idx.numel()), T, None
 
     def _put(self, dst, src):
         if src is None:

@@ -62,6 +62,10 @@ class SharedReplayBuffer(object):
         if self._share_is_view:
             self._share_unique = self.obs.view(T + 1, N, S)
             self.share_obs = self._share_unique.unsqueeze(2).expand(T + 1, N, M, S)
+        elif S == D and not bool(getattr(args, "use_centralized_V", True)):
+            # decentralised critic (ippo): share_obs IS obs (mpe_runner.py:136-137), kept as the same storage
+            self._share_unique = None
+            self.share_obs = self.obs
         else:
             self._share_unique = None
             self.share_obs = torch.zeros(T + 1, N, M, S, **f)

@@ -62,8 +62,11 @@ class OracleMAPPO:
         return np.stack(obs_list, axis=1).astype(np.float32)            # [N, M, D]
 
     def share_obs_of(self, obs):
-        """mpe_runner.py:133-137: concat of all agents' obs, repeated for every agent -> [N, M, S]"""
+        """mpe_runner.py:133-137: concat of all agents' obs, repeated for every agent -> [N, M, S]; the agent's own
+        obs with a decentralised critic (ippo)"""
         N, M = obs.shape[0], obs.shape[1]
+        if not self.a.use_centralized_V:                                 # mpe_runner.py:136-137: share_obs = obs
+            return obs
         return np.repeat(obs.reshape(N, 1, -1), M, axis=1)
 
     def share_at(self, t):
@@ -182,6 +185,10 @@ class OracleMAPPO:
         return dict(value_loss=vl.item(), critic_grad_norm=cn, policy_loss=pl.item(), dist_entropy=ent.item(),
                     actor_grad_norm=an, ratio=ratio.mean().item())
 
+    def recurrent_batches(self, perm, L):
+        """shared_buffer.py:385-494: chunks cut from the [N, M, T]-ordered stream."""
+        return ob.recurrent_rows(self.T, self.N, self.M, perm, self.a.num_mini_batch, L)
+
     def train(self, permute=False):
         """r_mappo.py:166-219.  permute=False: num_mini_batch == 1 in storage order (the loss is a mean; the
         reference's randperm only reorders it); permute=True draws torch.randperm like the reference."""
@@ -193,7 +200,7 @@ class OracleMAPPO:
         for _ in range(a.ppo_epoch):
             if a.use_recurrent_policy:
                 L = a.data_chunk_length
-                batches = ob.recurrent_rows(self.T, self.N, self.M, torch.randperm(B // L).numpy(), a.num_mini_batch, L)
+                batches = self.recurrent_batches(torch.randperm(B // L).numpy(), L)
             elif a.use_naive_recurrent_policy:
                 batches = ob.naive_recurrent_rows(self.T, self.N * self.M, torch.randperm(self.N * self.M).numpy(),
                                                   a.num_mini_batch)
@@ -252,13 +259,17 @@ class _AgentLearner(OracleMAPPO):
         self.actions = np.zeros((T, N, 1, heads), f)
         self.action_log_probs = np.zeros((T, N, 1, heads), f)
         self.rewards = np.zeros((T, N, 1, 1), f)
-        self.rec = False                                   # separated + recurrent is not restated
+        self.rec = bool(args.use_recurrent_policy or args.use_naive_recurrent_policy)
         self.rnn_states = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
         self.rnn_states_critic = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
         self.calls = 0
 
     def share_at(self, t):
         return self.share[t]
+
+    def recurrent_batches(self, perm, L):
+        """separated_buffer.py:289-393, including the (Nc, L) stack flattened as (L, Nc)."""
+        return ob.separated_recurrent_rows(self.T, self.N, perm, self.a.num_mini_batch, L)
 
     def share_rows(self):
         return self.share[:-1].reshape(self.T * self.N, -1)
@@ -319,6 +330,11 @@ class OracleSeparatedMAPPO:
                 mk = np.ones((N, 1), np.float32)
                 mk[dones[:, m]] = 0.0
                 ag.masks[step + 1, :, 0] = mk
+                if ag.rec:                                               # separated/mpe_runner.py:145-146
+                    h, hc = ag._h
+                    h = h.copy(); hc = hc.copy()
+                    h[dones[:, m]] = 0.0; hc[dones[:, m]] = 0.0
+                    ag.rnn_states[step + 1], ag.rnn_states_critic[step + 1] = h, hc
 
     def compute(self):
         for ag in self.agents:

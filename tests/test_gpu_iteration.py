@@ -25,7 +25,14 @@ def test_full_iteration_recurrent_gru_reference_scenario():
 
 def test_full_iteration_naive_recurrent():
     import __graft_entry__ as g
-    g._smoke_iteration(M=3, N=32, extra="--use_naive_recurrent_policy --num_mini_batch 2")
+    g._smoke_iteration(M=3, N=32, extra="--algorithm_name ippo --use_recurrent_policy --use_naive_recurrent_policy --num_mini_batch 2")
+
+
+def test_full_iteration_ippo_decentralised_critic():
+    """ippo with a shared MLP policy: the critic reads each agent's own observation (share_obs is obs,
+    mpe_runner.py:136-137)."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=3, N=64, extra="--algorithm_name ippo --use_recurrent_policy")
 
 
 def _make_runner(extra, N=192, M=3):

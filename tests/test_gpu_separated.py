@@ -13,10 +13,10 @@ def _args(extra):
     return parse_args(extra.split())
 
 
-def _buffer(T=6, N=5, D=4, S=7, A=3):
+def _buffer(T=6, N=5, D=4, S=7, A=3, extra=""):
     from mappo_b200.envs.spaces import Box, Discrete
     from mappo_b200.utils.separated_buffer import SeparatedReplayBuffer
-    a = _args("--scenario_name simple_spread --episode_length %d --n_rollout_threads %d" % (T, N))
+    a = _args("--scenario_name simple_spread --episode_length %d --n_rollout_threads %d %s" % (T, N, extra))
     b = SeparatedReplayBuffer(a, Box(-np.inf, np.inf, (D,), np.float32), Box(-np.inf, np.inf, (S,), np.float32),
                               Discrete(A), device="cuda:0")
     g = torch.Generator().manual_seed(3)
@@ -56,6 +56,33 @@ def test_generators_follow_oracle_rows():
     torch.manual_seed(9); check(b.naive_recurrent_generator(adv, 2), ob.naive_recurrent_rows(T, N, perm, 2))
 
 
+def test_recurrent_rows_address_what_the_generators_yield():
+    """The index forms the fused kernels consume (recurrent_rows / naive_recurrent_rows) against the arrays the
+    reference-shaped generators yield under the same torch.randperm draw: every field row for row, and the initial
+    states at the seed rows -- including the (Nc, L)-stack-flattened-as-(L, Nc) order of separated_buffer.py:361-391."""
+    T, N = 6, 5
+    a, b = _buffer(T, N, extra="--algorithm_name rmappo")
+    assert b._recurrent
+    g = torch.Generator().manual_seed(5)
+    b.rnn_states.copy_(torch.randn(b.rnn_states.shape, generator=g))
+    b.rnn_states_critic.copy_(torch.randn(b.rnn_states_critic.shape, generator=g))
+    adv = torch.randn(T, N, 1, generator=g).cuda()
+    v = b.flat_views()
+    for gen, rows_fn in ((lambda: b.recurrent_generator(adv, 2, 3), lambda: b.recurrent_rows(2, 3)),
+                         (lambda: b.naive_recurrent_generator(adv, 2), lambda: b.naive_recurrent_rows(2))):
+        torch.manual_seed(9); samples = list(gen())
+        torch.manual_seed(9); batches = list(rows_fn())
+        assert len(samples) == len(batches) == 2
+        for sample, (rows, nc, L, seed) in zip(samples, batches):
+            assert rows.numel() == nc * L
+            seed = rows[:nc] if seed is None else seed
+            eq = lambda x, y: np.testing.assert_array_equal(x.cpu().numpy().reshape(y.shape[0], -1),
+                                                            y.cpu().numpy().reshape(y.shape[0], -1))
+            eq(sample[1], v["obs"][rows]); eq(sample[0], v["share"][rows]); eq(sample[4], v["actions"][rows])
+            eq(sample[7], v["masks"][rows]); eq(sample[6], v["returns"][rows]); eq(sample[10], adv.view(-1)[rows])
+            eq(sample[2], v["rnn"][seed]); eq(sample[3], v["rnn_critic"][seed])
+
+
 def test_insert_after_update_roundtrip():
     """separated_buffer.py:72-110"""
     a, b = _buffer()
@@ -75,6 +102,11 @@ def test_insert_after_update_roundtrip():
     ("simple_reference", ""),
     ("simple_speaker_listener", "--use_centralized_V"),      # store_false: decentralised critic
     ("simple_spread", "--num_mini_batch 2"),
+    # the reference's own train_mpe_comm.sh: rmappo with separated policies (GRU, chunks of 10)
+    ("simple_speaker_listener", "--algorithm_name rmappo --data_chunk_length 10"),
+    ("simple_reference", "--algorithm_name rmappo --data_chunk_length 5 --num_mini_batch 2"),
+    # whole-trajectory recurrent minibatches (ippo keeps the recurrent flags as given; decentralised critic)
+    ("simple_speaker_listener", "--algorithm_name ippo --use_recurrent_policy --use_naive_recurrent_policy --num_mini_batch 2"),
 ])
 def test_separated_iteration_matches_oracle(scenario, extra):
     from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
@@ -93,7 +125,8 @@ def test_separated_iteration_matches_oracle(scenario, extra):
                                [cpu(p.critic.state_dict()) for p in runner.policy],
                                sample_seeds=[p.actor.sample_seed for p in runner.policy])
     runner.warmup(); orc.warmup()
-    permute = a.num_mini_batch > 1
+    recurrent = a.use_recurrent_policy or a.use_naive_recurrent_policy
+    permute = a.num_mini_batch > 1 and not recurrent
     if permute:
         for b in runner.buffer:
             b.force_permutation = True
