@@ -29,6 +29,7 @@ struct GruArgs {
   const float* n2;               // [len * nc][64]
   const float* h0;               // rnn states at sample rows [*][64]; step 0 reads row src(0, c)
   const float* masks;            // [*] at sample rows
+  const float* mpos;             // update: masks gathered into position order ([len * nc]), so that no step waits for index[p] first
   float* hs;                     // [len * nc][64]  hidden after each step (rollout: the next rnn-state slot)
   float* hm;                     // [len * nc][64]  masked previous hidden, or NULL
   float* gates;                  // [len * nc][256] r | z | n | (Whn h + bhn) -> backward: dgi_n | P_r | P_z | dgh_n
@@ -126,7 +127,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
     float h[16], x[16], mask;
     {
       const long long src = valid ? (a.index ? a.index[c] : c) : 0;
-      if (valid) { load16(a.h0 + src * 64 + 16 * cq, h); load16(a.n2 + c * 64 + 16 * cq, x); mask = __ldg(a.masks + src); }
+      if (valid) { load16(a.h0 + src * 64 + 16 * cq, h); load16(a.n2 + c * 64 + 16 * cq, x); mask = a.mpos ? __ldg(a.mpos + c) : __ldg(a.masks + src); }
       else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) h[i] = x[i] = 0.0f;
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
       if (s + 1 < a.len && valid) {
         const long long pn = p + a.nc;
         load16(a.n2 + pn * 64 + 16 * cq, xn);
-        mask_n = __ldg(a.masks + (a.index ? a.index[pn] : pn));
+        mask_n = a.mpos ? __ldg(a.mpos + pn) : __ldg(a.masks + (a.index ? a.index[pn] : pn));
       } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) xn[i] = 0.0f;
@@ -258,6 +259,21 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
     for (int i = 0; i < 16; ++i) carry[i] = 0.0f;
     for (int s = a.len - 1; s >= 0; --s) {
       const long long p = (long long)s * a.nc + c;
+      // The sweep is one dependent chain per CTA (loads -> gate derivatives -> MMAs -> carry), so nothing else hides
+      // the DRAM latency of a step's 192 KB: one thread asks the L2 for the NEXT step's rows (contiguous per tile:
+      // positions are step-major) while this step runs.
+      if (tid == 32) {
+        long long tl = tile;
+        int sn = s - 1;
+        if (sn < 0) { tl = tile + gridDim.x; sn = a.len - 1; }
+        if (tl < ntiles) {
+          const long long c0 = tl * kBM, p0 = (long long)sn * a.nc + c0;
+          const uint32_t nr = (uint32_t)min((long long)kBM, a.nc - c0);
+          umma::l2_prefetch(a.gates + p0 * 256, nr * 1024u);
+          umma::l2_prefetch(a.dh + p0 * 64, nr * 256u);
+          umma::l2_prefetch(a.hm + p0 * 64, nr * 256u);
+        }
+      }
       float dt[16], u[16], v[16], w[16], dd[16];
       float mask = 0.0f;
       float* gp = a.gates + p * 256 + 16 * cq;
@@ -266,7 +282,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
         load16(gp + 64, u);                                             // z
         load16(gp + 128, v);                                            // n
         load16(a.hm + p * 64 + 16 * cq, w);                             // hm
-        mask = __ldg(a.masks + (a.index ? a.index[p] : p));
+        mask = a.mpos ? __ldg(a.mpos + p) : __ldg(a.masks + (a.index ? a.index[p] : p));
       } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) dt[i] = u[i] = v[i] = w[i] = 0.0f;
@@ -572,7 +588,15 @@ static int head_grid(long long rows) {
 }
 
 // floats of workspace per position: rollout keeps the base features only
-long long rnn_workspace_floats(long long positions, int update) { return positions * (update ? 512 : 64); }
+long long rnn_workspace_floats(long long positions, int update) { return positions * (update ? 513 : 64); }
+
+// mpos[p] = masks[index[p]]: the sweeps read their step's mask with the rest of the step's rows instead of behind a
+// dependent index load
+__global__ void gather_masks_kernel(const float* __restrict__ masks, const int64_t* __restrict__ index, float* __restrict__ mpos,
+                                    long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    mpos[i] = __ldg(masks + index[i]);
+}
 
 // One forward step for `rows` rows (rollout / evaluation): base -> GRU -> head.
 template <int MODE>
@@ -611,12 +635,14 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
   MAPPO_CUDA(cudaMemsetAsync(a.grad_partials, 0, sizeof(float) * P * (size_t)n_partials, stream));
   MAPPO_CUDA(cudaMemsetAsync(a.loss_partials, 0, sizeof(double) * 4 * (size_t)n_partials, stream));
   float* ws = static_cast<float*>(a.workspace);
-  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256;
+  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256, *mpos = ws + B * 512;
+  gather_masks_kernel<<<(int)((B + 255) / 256 < 1184 ? (B + 255) / 256 : 1184), 256, 0, stream>>>(masks, a.index, mpos, B);
+  MAPPO_CHECK_LAUNCH(who);
   a.feat = n2;
   if (int rc = launch<4>(a, cfg, stream, who)) return rc;
   GruArgs g{};
   g.L = a.L; g.params = a.params; g.nc = n_chunks; g.len = chunk_len; g.index = a.index; g.n2 = n2; g.h0 = rnn_states;
-  g.masks = masks; g.hs = hs; g.hm = hm; g.gates = gates; g.dh = dh;
+  g.masks = masks; g.mpos = mpos; g.hs = hs; g.hm = hm; g.gates = gates; g.dh = dh;
   gru_fwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(false).total, stream>>>(g);
   MAPPO_CHECK_LAUNCH(who);
   gru_head_kernel<MODE><<<head_grid(B), 256, HeadSmem::bytes, stream>>>(a, hs, dh);
