@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define MAPPO_B200_ABI_VERSION 3
+#define MAPPO_B200_ABI_VERSION 4
 
 typedef enum {
   MAPPO_OK = 0,
@@ -250,20 +250,24 @@ long long mappo_net_param_count(const mappo_net_config* cfg);
  * (float32 [rows][n_heads]) is not NULL nothing is sampled; logp_out receives log_prob(given action) and
  * entropy_out (float32 [rows], may be NULL) the mean over heads of each row's entropy; actions_out may be NULL.
  * step_offset (int64 on the device, may be NULL) is added to `step` inside the kernel: a captured CUDA graph of the
- * rollout keeps its sampling counter in HBM and advances it between launches.  (ABI v3.) */
+ * rollout keeps its sampling counter in HBM and advances it between launches.  (ABI v3.)
+ * workspace: mappo_mlp_workspace_bytes(cfg, rows) bytes of scratch for a wide observation (in_dim > 64, e.g.
+ * simple_spread with 12 or more agents), else NULL.  (ABI v4.) */
 int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
                         long long rows, const float* available_actions, int deterministic, uint64_t seed,
                         uint64_t step, long long row_offset, const float* given_actions, float* actions_out,
-                        float* logp_out, float* entropy_out, const int64_t* step_offset, void* stream);
+                        float* logp_out, float* entropy_out, const int64_t* step_offset, void* workspace,
+                        void* stream);
 
 /* Critic forward (R_Critic.forward / get_values): `rows` unique share-obs rows, each value written `group`
  * times: values_out float32 [rows][group] (group = M when the M agents of an env share one share_obs row). */
 int mappo_critic_forward(const mappo_net_config* cfg, const float* params, const float* share_obs, int obs_ld,
                          long long rows, int group, float* values_out, void* workspace, void* stream);
 
-/* Scratch bytes a critic call over `rows` rows needs in `workspace` (device memory, 16-byte aligned): 0 for
- * in_dim <= 64 (pass NULL); for a wide centralised critic (in_dim > 64, e.g. 460 = 10 agents x 46) the first layer runs
- * as separate streaming GEMMs and its [rows][64] activations / gradients plus [rows][2] row statistics live there. */
+/* Scratch bytes an actor or critic call over `rows` rows needs in `workspace` (device memory, 16-byte aligned): 0 for
+ * in_dim <= 64 (pass NULL); for a wide input (in_dim > 64, e.g. the centralised critic's 460 = 10 agents x 46, or an
+ * actor's 70 columns with 16 agents) the first layer runs as separate streaming GEMMs and its [rows][64] activations /
+ * gradients plus [rows][2] row statistics live there. */
 long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long long rows);
 
 typedef struct {
@@ -292,11 +296,13 @@ int mappo_update_num_blocks(const mappo_net_config* cfg, long long rows);
  * mappo_grad_reduce / mappo_adam_step):
  *   grad_partials float32 [blocks][P];
  *   loss_partials double [blocks][4] = {sum -min(surr1,surr2)*active, sum entropy*active (mean over heads),
- *                                       sum ratio (all heads), sum active} */
+ *                                       sum ratio (all heads), sum active}
+ * workspace: as for mappo_actor_forward.  (ABI v4.) */
 int mappo_actor_update(const mappo_net_config* cfg, const mappo_loss_config* loss, const float* params,
                        const float* obs, int obs_ld, long long rows, const int64_t* index, const float* actions,
                        const float* old_logp, const float* adv, const float* active_masks,
-                       const float* available_actions, float* grad_partials, double* loss_partials, void* stream);
+                       const float* available_actions, float* grad_partials, double* loss_partials, void* workspace,
+                       void* stream);
 
 /* Critic: forward + (clipped, huber/mse, value-normalised) value loss + backward (r_mappo.py:52-89,151-156).
  *   `rows` unique share-obs rows; each carries `group` loss terms: value_preds, returns, active_masks

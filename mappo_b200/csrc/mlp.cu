@@ -316,7 +316,7 @@ static int launch_mlp(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stre
   if (cfg->recurrent) MAPPO_UNSUPPORTED("%s: recurrent (GRU) networks are not built yet", who);
   MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim, "%s: bad input arguments", who);
   if (use_tc(cfg)) return tc::launch<MODE>(a, cfg, stream, who);
-  if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d is built for critics on the tensor-core path only", who, cfg->in_dim, kMaxIn);
+  if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d is built on the tensor-core path only", who, cfg->in_dim, kMaxIn);
   a.L = make_layout(*cfg);
   if (a.x_div < 1) a.x_div = 1;
   a.Kp = (cfg->in_dim + 3) & ~3;
@@ -356,7 +356,7 @@ extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* par
                                    long long rows, const float* available_actions, int deterministic, uint64_t seed,
                                    uint64_t step, long long row_offset, const float* given_actions,
                                    float* actions_out, float* logp_out, float* entropy_out,
-                                   const int64_t* step_offset, void* stream) {
+                                   const int64_t* step_offset, void* workspace, void* stream) {
   MAPPO_REQUIRE(logp_out && (actions_out || given_actions), "actor_forward: null outputs");
   MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_forward: critic config");
   MlpArgs a{};
@@ -364,7 +364,7 @@ extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* par
   a.deterministic = deterministic; a.k0 = (uint32_t)(seed & 0xFFFFFFFFull); a.step = (uint32_t)step;
   a.step_dev = step_offset;
   a.row_offset = row_offset; a.actions_out = actions_out; a.logp_out = logp_out;
-  a.given_actions = given_actions; a.entropy_out = entropy_out;
+  a.given_actions = given_actions; a.entropy_out = entropy_out; a.workspace = workspace;
   return launch_mlp<0>(a, cfg, (cudaStream_t)stream, "actor_forward");
 }
 
@@ -383,13 +383,13 @@ extern "C" int mappo_actor_update(const mappo_net_config* cfg, const mappo_loss_
                                   const float* obs, int obs_ld, long long rows, const int64_t* index,
                                   const float* actions, const float* old_logp, const float* adv,
                                   const float* active_masks, const float* available_actions, float* grad_partials,
-                                  double* loss_partials, void* stream) {
+                                  double* loss_partials, void* workspace, void* stream) {
   MAPPO_REQUIRE(loss && actions && old_logp && adv && grad_partials && loss_partials, "actor_update: null pointer");
   MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_update: critic config");
   MlpArgs a{};
   a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.index = index; a.actions = actions;
   a.old_logp = old_logp; a.adv = adv; a.active = active_masks; a.avail = available_actions; a.loss = *loss;
-  a.grad_partials = grad_partials; a.loss_partials = loss_partials;
+  a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
   return launch_mlp<2>(a, cfg, (cudaStream_t)stream, "actor_update");
 }
 

@@ -762,12 +762,13 @@ int launch_wide_fc1_packed(const MlpArgs& a, void* workspace, const void* packed
 int launch_wide_wgrad1_packed(const MlpArgs& a, void* workspace, const void* packed, cudaStream_t stream, const char* who);
 
 bool supports(const mappo_net_config* cfg) {
-  if (wide_supports(cfg)) return true;
-  if (!(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim < 64)) return false;
+  const bool wide = wide_supports(cfg);
+  if (wide && cfg->is_critic) return true;
+  if (!wide && !(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim < 64)) return false;
   int A = 0;
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
-  const int Kp = cfg->in_dim < 32 ? 32 : 64;
+  const int Kp = (wide || cfg->in_dim < 32) ? 32 : 64;
   return make_map(Kp, A | 1, true).total <= (uint32_t)kMaxDynSmem && make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
@@ -828,6 +829,15 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
     return launch_one<MODE, 64, 1>(a, stream, who);
   } else {
   const bool small_head = cfg->n_heads == 1 && a.L.a_total <= 8 && a.avail == nullptr;
+  if (cfg->in_dim > 64) {                         // wide observation (e.g. simple_spread with >= 12 agents): same three-kernel chain
+    MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
+    a.Kp = 32;
+    a.z1 = static_cast<float*>(a.workspace);
+    if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
+    if (int rc = small_head ? launch_one<MODE, 32, 8, true>(a, stream, who) : launch_one<MODE, 32, 16, true>(a, stream, who)) return rc;
+    if (MODE == 2) return launch_wide_wgrad1(a, a.workspace, stream, who);
+    return 0;
+  }
   if (small_head) {
     if (a.Kp == 32) return launch_one<MODE, 32, 8>(a, stream, who);
     return launch_one<MODE, 64, 8>(a, stream, who);

@@ -158,10 +158,10 @@ class AdamConfig(C.Structure):
 _NC, _LC, _AC = C.POINTER(NetConfig), C.POINTER(LossConfig), C.POINTER(AdamConfig)
 _lib._EXTRA_SIGS.update({
     "mappo_actor_forward": [_NC, _P, _P, C.c_int, C.c_longlong, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_longlong,
-                            _P, _P, _P, _P, _P, _P],
+                            _P, _P, _P, _P, _P, _P, _P],
     "mappo_advantages": [_P, _P, _P, _P, C.c_longlong, _P, _P, _P],
     "mappo_critic_forward": [_NC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P],
-    "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "mappo_actor_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "mappo_critic_update": [_NC, _LC, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P,
                             _P],
     "mappo_critic_pack_inputs": [_NC, _P, C.c_int, C.c_longlong, _P, _P, _P],
@@ -201,11 +201,12 @@ def actor_forward(cfg, params, obs, actions_out, logp_out, available_actions=Non
                   step=0, row_offset=0, given_actions=None, entropy_out=None, step_offset=None):
     """step_offset: int64 device scalar added to `step` in the kernel (CUDA-graph replays), or None."""
     obs, ld = _rows_view(obs)
+    ws = mlp_workspace(cfg, obs.shape[0], obs.device)
     with TIMERS.span("actor_forward"):
         check(_lib.lib().mappo_actor_forward(C.byref(cfg), ptr(params), _vp(obs), ld, obs.shape[0],
                                              ptr(available_actions), int(deterministic), int(seed) & (2 ** 64 - 1),
                                              int(step), int(row_offset), ptr(given_actions), ptr(actions_out),
-                                             ptr(logp_out), ptr(entropy_out), ptr(step_offset), stream_ptr()),
+                                             ptr(logp_out), ptr(entropy_out), ptr(step_offset), ptr(ws), stream_ptr()),
               "actor_forward")
 
 
@@ -231,7 +232,7 @@ _WORKSPACES = {}
 
 
 def mlp_workspace(cfg, rows, device):
-    """Scratch for a wide (in_dim > 64) critic call, grown on demand and kept per device; None when not needed."""
+    """Scratch for a wide (in_dim > 64) actor or critic call, grown on demand and kept per device; None when not needed."""
     L = _lib.lib()
     L.mappo_mlp_workspace_bytes.argtypes = [_NC, C.c_longlong]
     L.mappo_mlp_workspace_bytes.restype = C.c_longlong
@@ -345,10 +346,11 @@ def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, a
                  loss_partials, index=None):
     obs, ld = _rows_view(obs)
     rows = obs.shape[0] if index is None else index.numel()
+    ws = mlp_workspace(cfg, rows, obs.device)
     with TIMERS.span("actor_update"):
         check(_lib.lib().mappo_actor_update(C.byref(cfg), C.byref(loss), ptr(params), _vp(obs), ld, rows, ptr(index),
                                             ptr(actions), ptr(old_logp), ptr(adv), ptr(active_masks),
-                                            ptr(available_actions), ptr(grad_partials), ptr(loss_partials),
+                                            ptr(available_actions), ptr(grad_partials), ptr(loss_partials), ptr(ws),
                                             stream_ptr()), "actor_update")
 
 

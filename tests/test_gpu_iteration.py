@@ -35,6 +35,13 @@ def test_full_iteration_ippo_decentralised_critic():
     g._smoke_iteration(M=3, N=64, extra="--algorithm_name ippo --use_recurrent_policy")
 
 
+def test_full_iteration_wide_observations():
+    """15 agents: obs_dim = 4 + 2 L + 4 (M - 1) = 66 > 64, so actor and (decentralised, ippo) critic both take the wide
+    first-layer chain, rollout and update, beside the oracle."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=15, N=24, extra="--algorithm_name ippo --use_recurrent_policy")
+
+
 def _make_runner(extra, N=192, M=3):
     import torch
     from mappo_b200.config import parse_args

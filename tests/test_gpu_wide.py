@@ -8,7 +8,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _setup(S, B, flags="", seed=0):
+def _setup(S, B, flags="", seed=0, D=46, A=5):
     from mappo_b200.config import parse_args
     from mappo_b200.envs.spaces import Box, Discrete
     from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
@@ -16,14 +16,15 @@ def _setup(S, B, flags="", seed=0):
     a = parse_args(("--scenario_name simple_spread --num_agents 10 --ppo_epoch 1 " + flags).split())
     torch.manual_seed(seed)
     box = lambda n: Box(-np.inf, np.inf, (n,), np.float32)
-    pol = R_MAPPOPolicy(a, box(46), box(S), Discrete(5), device="cuda")
+    pol = R_MAPPOPolicy(a, box(D), box(S), Discrete(A), device="cuda")
     g = torch.Generator(device="cuda").manual_seed(seed + 1)
     for net in (pol.actor, pol.critic):                     # LayerNorm affines and biases away from (1, 0)
         net.flat.add_(0.05 * torch.randn(net.flat.shape, device="cuda", generator=g))
     tr = R_MAPPO(a, pol, device="cuda")
     r = lambda *s: torch.randn(*s, device="cuda", generator=g)
     share = r(B, S) * (0.5 + r(1, S).abs()) + 0.3 * r(1, S)
-    sample = (share, r(B, 46), None, None, torch.randint(0, 5, (B, 1), device="cuda", generator=g).float(),
+    sample = (share, r(B, D) * (0.5 + r(1, D).abs()), None, None,
+              torch.randint(0, A, (B, 1), device="cuda", generator=g).float(),
               0.5 * r(B, 1), 0.5 * r(B, 1) + 0.2, torch.ones(B, 1, device="cuda"),
               (torch.rand(B, 1, device="cuda", generator=g) > 0.1).float(), -1.6 + 0.1 * r(B, 1), r(B, 1), None)
     return a, pol, tr, sample
@@ -147,3 +148,39 @@ def test_packing_is_refused_with_a_row_gather():
     with pytest.raises(AssertionError):
         ops.critic_update(cfg, tr._loss_config(), flat, share, vp, ret, am, tr.value_normalizer.stats, gp, lp,
                           index=torch.randperm(600, device="cuda"), packed=packed)
+
+
+
+@pytest.mark.parametrize("D,A,B,flags", [(70, 5, 1000, ""), (118, 5, 12800 + 77, "--use_ReLU"), (70, 12, 700, ""),
+                                         (100, 5, 129, "--use_feature_normalization")])
+def test_wide_actor_logp_loss_and_gradients(D, A, B, flags):
+    """Observations wider than 64 columns (simple_spread from 12 agents up: 4 + 2 L + 4 (M - 1)): the actor takes the same
+    three-kernel chain as the wide critic (ABI v4).  Log-probs / entropy of given actions, the policy loss and the
+    PRE-clip gradients against the oracle on the same inputs; A = 12 takes the generic head path."""
+    from oracle import policy as op
+    a, pol, tr, sample = _setup(100, B, flags, D=D, A=A)
+    obs, actions, am, old_lp, adv = (sample[i] for i in (1, 4, 8, 9, 10))
+    old_lp = old_lp - (np.log(A) - 1.6)
+    sample = sample[:9] + (old_lp, adv, None)
+    sd = {k: v.detach().cpu().clone().requires_grad_("fc_h" not in k) for k, v in pol.actor.state_dict().items()}
+    z, ones = np.zeros((B, 1, 64), np.float32), np.ones((B, 1), np.float32)
+    feats, _ = op.actor_features(sd, obs.cpu().numpy(), z, ones, a.use_ReLU, a.use_feature_normalization, False)
+    logits = op.actor_logits(sd, feats, None)
+    logp, ent = op.evaluate_actions(logits, actions.cpu().numpy(), am.cpu().numpy() if a.use_policy_active_masks else None)
+    pl, ratio = op.policy_loss(logp, old_lp.cpu().numpy(), adv.cpu().numpy(), am.cpu().numpy(), a.clip_param,
+                               a.use_policy_active_masks)
+    keys = [k for k in sd if "fc_h" not in k]
+    want_g = dict(zip(keys, torch.autograd.grad(pl - ent * a.entropy_coef, [sd[k] for k in keys])))
+    got_lp, got_ent = pol.actor.evaluate_actions(obs, None, actions, None, None, am)
+    np.testing.assert_allclose(got_lp.cpu().numpy(), logp.detach().numpy(), rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(got_ent.item(), ent.item(), rtol=1e-4)
+    acts, lps, _ = pol.actor(obs, None, None, deterministic=True)      # rollout kernel: mode() of the same logits
+    assert (acts.cpu().numpy()[:, 0] == logits[0].detach().numpy().argmax(-1)).mean() > 0.999
+    vl, cgn, got_pl, got_entropy, agn, got_ratio = tr.ppo_update(sample)
+    np.testing.assert_allclose(got_pl.item(), pl.item(), rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(got_ratio.item(), ratio.mean().item(), rtol=1e-4)
+    ws = next(iter(tr._ws.values()))
+    Pa = pol.actor.flat.numel()
+    for k, gv in pol.actor.unflatten(ws["grad"][:Pa]).items():
+        w = want_g[k].numpy()
+        np.testing.assert_allclose(gv.cpu().numpy(), w, rtol=1e-4, atol=1e-4 * np.abs(w).max() + 1e-9, err_msg=k)
