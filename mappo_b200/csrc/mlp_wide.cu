@@ -36,11 +36,14 @@ __device__ __forceinline__ void load8(const float* __restrict__ row, int c, int 
 // ---- forward ---------------------------------------------------------------------------------------------
 // Shared memory: W1' as the K-major B operand (both fp16 pieces, K padded to a multiple of 16), two X buffers of
 // one 64-column K-chunk each (128 rows, both pieces), the row-exchange buffers, two mbarriers (one per X buffer).
-struct FwdMap { uint32_t W, w_piece, X, xch, bars, total; int K16; };
-__host__ __device__ inline FwdMap make_fwd_map(int D) {
+// nhalf = 2 | 4: a CTA keeps 32 | 16 of the 64 output columns of W1' (in_dim up to ~1,250 | ~2,500; x is then read once
+// per part).
+struct FwdMap { uint32_t W, w_piece, w_chunk, X, xch, bars, total; int K16; };
+__host__ __device__ inline FwdMap make_fwd_map(int D, int nhalf = 1) {
   FwdMap m;
   m.K16 = (D + 15) / 16;
-  m.w_piece = (uint32_t)(2 * m.K16) * kWChunk;
+  m.w_chunk = kWChunk / (uint32_t)nhalf;                               // bytes of one 8-column chunk of the staged W1' rows
+  m.w_piece = (uint32_t)(2 * m.K16) * m.w_chunk;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
   m.W = take(2 * m.w_piece);
@@ -62,7 +65,8 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   __shared__ float cs[64];                                              // colsum_k W'[j][k]
   const NetLayout& L = a.L;
   const int D = L.in_dim;
-  const FwdMap m = make_fwd_map(D);
+  const FwdMap m = make_fwd_map(D, a.nhalf);
+  const int JN = 64 / a.nhalf, j0 = JN * blockIdx.y, ncol = JN / 4;   // this CTA's output columns; columns per thread
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sm + m.bars);          // bars[b]: MMAs that read X buffer b
@@ -71,15 +75,15 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   {
     const float* __restrict__ P = a.params;
     const int Kp = 16 * m.K16;
-    for (int e = tid; e < 64 * Kp; e += kThreads) {
+    for (int e = tid; e < JN * Kp; e += kThreads) {
       const int j = e / Kp, k = e - j * Kp;
       float v = 0.0f;
-      if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
-      put_pair(sm + m.W, m.w_piece, 64, j, k, v);
+      if (k < D) v = P[L.w1 + (j0 + j) * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+      put_pair(sm + m.W, m.w_piece, JN, j, k, v);
     }
-    for (int j = warp; j < 64; j += kThreads / 32) {                   // one warp per output row, fixed lane order
+    for (int j = warp; j < JN; j += kThreads / 32) {                   // one warp per output row, fixed lane order
       float t = 0.0f;
-      for (int k = lane; k < D; k += 32) t += P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+      for (int k = lane; k < D; k += 32) t += P[L.w1 + (j0 + j) * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
       if (lane == 0) cs[j] = t;
@@ -93,7 +97,7 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
   const uint32_t sX = umma::smem_u32(sm + m.X), sW = umma::smem_u32(sm + m.W);
   constexpr uint32_t kXBuf = 2 * 8 * kRowChunk;
-  constexpr uint32_t kId = umma::idesc_f16(128, 64, 0, 0);
+  const uint32_t kId = umma::idesc_f16(128, JN, 0, 0);
   float2* xch = reinterpret_cast<float2*>(sm + m.xch);
   int slot = 0;
   const int nkc = (m.K16 + 3) / 4;                                     // 64-column K-chunks per tile
@@ -121,15 +125,15 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
   auto drain = [&](long long g, float ms, float rstd) {                 // accumulators -> z1 row g
     wait_commit(n - 1);
     umma::tc_fence_after();
-    float u[16], w[16];
-    umma::tmem_ld16(lane_addr + 16 * cq, u);
-    umma::tmem_ld16(lane_addr + 64 + 16 * cq, w);
+    float u[16], w[16];                                                 // the first ncol of them are this thread's
+    umma::tmem_ld16(lane_addr + ncol * cq, u);
+    umma::tmem_ld16(lane_addr + 64 + ncol * cq, w);
     if (g < a.rows) {
-      float4* out = reinterpret_cast<float4*>(a.z1 + g * 64 + 16 * cq);
-      const float* c16 = cs + 16 * cq;
+      float4* out = reinterpret_cast<float4*>(a.z1 + g * 64 + j0 + ncol * cq);
+      const float* c16 = cs + ncol * cq;
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        out[i] = make_float4(rstd * (fmaf(w[4 * i], kLoInv, u[4 * i]) - ms * c16[4 * i]),
+        if (4 * i < ncol) out[i] = make_float4(rstd * (fmaf(w[4 * i], kLoInv, u[4 * i]) - ms * c16[4 * i]),
                              rstd * (fmaf(w[4 * i + 1], kLoInv, u[4 * i + 1]) - ms * c16[4 * i + 1]),
                              rstd * (fmaf(w[4 * i + 2], kLoInv, u[4 * i + 2]) - ms * c16[4 * i + 2]),
                              rstd * (fmaf(w[4 * i + 3], kLoInv, u[4 * i + 3]) - ms * c16[4 * i + 3]));
@@ -176,9 +180,9 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
           umma::tc_fence_after();
           for (int ks = 0; ks < ksteps; ++ks) {
             const uint32_t ao = sX + b * kXBuf + (uint32_t)ks * 2 * kRowChunk;
-            const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * kWChunk;
+            const uint32_t bo = sW + (uint32_t)(4 * kc + ks) * 2 * m.w_chunk;
             const uint64_t ah = umma::smem_desc(ao, kRowChunk, 128), al = umma::smem_desc(ao + 8 * kRowChunk, kRowChunk, 128);
-            const uint64_t bh = umma::smem_desc(bo, kWChunk, 128), bl = umma::smem_desc(bo + m.w_piece, kWChunk, 128);
+            const uint64_t bh = umma::smem_desc(bo, m.w_chunk, 128), bl = umma::smem_desc(bo + m.w_piece, m.w_chunk, 128);
             const bool acc = kc > 0 || ks > 0;
             umma::mma_f16(tb, ah, bh, kId, acc);
             umma::mma_f16(tb + 64, ah, bl, kId, acc);
@@ -196,7 +200,7 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
         const float var = fmaxf(tot.y / (float)D - ms * ms, 0.0f);
         rstd = 1.0f / sqrtf(var + kLnEps);
       }
-      if (cq == 0 && cur.valid && a.xstats) { a.xstats[2 * cur.g] = cur.x0 + ms; a.xstats[2 * cur.g + 1] = rstd; }
+      if (cq == 0 && blockIdx.y == 0 && cur.valid && a.xstats) { a.xstats[2 * cur.g] = cur.x0 + ms; a.xstats[2 * cur.g + 1] = rstd; }
       prev_g = cur.g; prev_ms = ms; prev_rstd = rstd;
       cur = nxt;
       tile = ntile;
@@ -787,7 +791,7 @@ int grid_for(long long rows);                                             // mlp
 
 bool wide_supports(const mappo_net_config* cfg) {
   return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim > 64 &&
-         make_fwd_map(cfg->in_dim).total <= (uint32_t)kWideMaxSmem;
+         make_fwd_map(cfg->in_dim, 4).total <= (uint32_t)kWideMaxSmem;
 }
 
 // bytes of the caller-provided scratch: z1 / dz1 [rows][64] (the gradient overwrites the activations in place) and the
@@ -808,14 +812,16 @@ static void fill(WideArgs& w, const MlpArgs& a, void* workspace) {
 int launch_wide_fc1(const MlpArgs& a, void* workspace, cudaStream_t stream, const char* who) {
   WideArgs w{};
   fill(w, a, workspace);
-  const FwdMap m = make_fwd_map(a.L.in_dim);
+  w.nhalf = 1;
+  while (w.nhalf < 4 && make_fwd_map(a.L.in_dim, w.nhalf).total > (uint32_t)kWideMaxSmem) w.nhalf *= 2;
+  const FwdMap m = make_fwd_map(a.L.in_dim, w.nhalf);
   MAPPO_REQUIRE(m.total <= (uint32_t)kWideMaxSmem, "%s: in_dim %d too wide for the staged first layer", who, a.L.in_dim);
   static bool attr_set = false;
   if (!attr_set) {
     MAPPO_CUDA(cudaFuncSetAttribute(fc1_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideMaxSmem));
     attr_set = true;
   }
-  fc1_wide_kernel<<<grid_for(a.rows), kThreads, m.total, stream>>>(w);
+  fc1_wide_kernel<<<dim3(grid_for(a.rows), w.nhalf), kThreads, m.total, stream>>>(w);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
 }

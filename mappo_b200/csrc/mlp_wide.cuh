@@ -11,6 +11,7 @@ struct WideArgs {
   const float* params;
   const float* x; int ld; long long rows; const int64_t* index; int x_div;
   int vec;                       // 1: x rows are 16-byte aligned (float4 loads)
+  int nhalf;                     // forward: output-column parts (1, 2 or 4 = grid.y): W1' is staged 64 / nhalf columns at a time
   float* z1;                     // [rows][64]   forward: out
   float* xstats;                 // [rows][2]    forward: out, weight gradient: in
   const float* dz1;              // [rows][64]   weight gradient: in

@@ -40,6 +40,8 @@ def test_full_iteration_wide_observations():
     first-layer chain, rollout and update, beside the oracle."""
     import __graft_entry__ as g
     g._smoke_iteration(M=15, N=24, extra="--algorithm_name ippo --use_recurrent_policy")
+    # centralised critic over 15 x 66 = 990 columns (first layer in two 32-column halves)
+    g._smoke_iteration(M=15, N=24)
 
 
 def _make_runner(extra, N=192, M=3):

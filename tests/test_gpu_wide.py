@@ -49,7 +49,10 @@ def _oracle_critic(a, pol, tr, sample):
 
 
 @pytest.mark.parametrize("S,B,flags", [(460, 1000, ""), (460, 333, "--use_ReLU --use_valuenorm"), (600, 700, ""),
-                                       (100, 129, "--use_feature_normalization")])
+                                       (100, 129, "--use_feature_normalization"),
+                                       # beyond ~630 columns W1' is staged 32 output columns at a time (one pass over x per part):
+                                       (990, 700, ""), (1120, 300, "--use_ReLU --use_feature_normalization"),
+                                       (2000, 300, "")])                # 16 columns at a time
 def test_wide_critic_values_loss_and_gradients(S, B, flags):
     a, pol, tr, sample = _setup(S, B, flags)
     want_v, want_vl, want_g = _oracle_critic(a, pol, tr, sample)
