@@ -564,7 +564,8 @@ constexpr int kGruMaxSmem = 232448 - 1024;
 static int check_rnn(const mappo_net_config* cfg, const char* who) {
   if (int rc = check_net(cfg, who)) return rc;
   MAPPO_REQUIRE(cfg->recurrent, "%s: not a recurrent network", who);
-  if (cfg->in_dim >= 64) MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d >= 64 are not built", who, cfg->in_dim);
+  if (cfg->in_dim == 64 || (cfg->in_dim > 64 && !wide_fits(cfg->in_dim)))
+    MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d are not built (64, or too wide for the staged first layer)", who, cfg->in_dim);
   return 0;
 }
 
@@ -588,7 +589,10 @@ static int head_grid(long long rows) {
 }
 
 // floats of workspace per position: rollout keeps the base features only
-long long rnn_workspace_floats(long long positions, int update) { return positions * (update ? 513 : 64); }
+// + the wide first layer's scratch (z1 [64] and row statistics [2] per position) when the base reads more than 64 columns
+long long rnn_workspace_floats(long long positions, int update, int in_dim) {
+  return positions * ((update ? 513 : 64) + (in_dim > 64 ? 66 : 0));
+}
 
 // mpos[p] = masks[index[p]]: the sweeps read their step's mask with the rest of the step's rows instead of behind a
 // dependent index load
@@ -608,6 +612,7 @@ int rnn_forward(MlpArgs& a, const mappo_net_config* cfg, const float* h_in, cons
   if (int rc = set_attrs()) return rc;
   float* n2 = static_cast<float*>(a.workspace);
   a.feat = n2;
+  a.workspace = n2 + a.rows * 64;                        // the wide first layer's scratch, if the base needs one
   if (int rc = launch<4>(a, cfg, stream, who)) return rc;
   GruArgs g{};
   g.L = a.L; g.params = a.params; g.nc = a.rows; g.len = 1; g.index = nullptr; g.n2 = n2; g.h0 = h_in; g.masks = masks;
@@ -635,7 +640,9 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
   MAPPO_CUDA(cudaMemsetAsync(a.grad_partials, 0, sizeof(float) * P * (size_t)n_partials, stream));
   MAPPO_CUDA(cudaMemsetAsync(a.loss_partials, 0, sizeof(double) * 4 * (size_t)n_partials, stream));
   float* ws = static_cast<float*>(a.workspace);
-  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256, *mpos = ws + B * 512;
+  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256;
+  float* mpos = ws + B * (512 + (cfg->in_dim > 64 ? 66 : 0));
+  a.workspace = ws + B * 512;                            // the wide first layer's scratch, if the base needs one
   gather_masks_kernel<<<(int)((B + 255) / 256 < 1184 ? (B + 255) / 256 : 1184), 256, 0, stream>>>(masks, a.index, mpos, B);
   MAPPO_CHECK_LAUNCH(who);
   a.feat = n2;
@@ -672,7 +679,7 @@ using namespace mappo;
 
 extern "C" long long mappo_rnn_workspace_bytes(const mappo_net_config* cfg, long long positions, int update) {
   if (!cfg || positions < 0) return -1;
-  return cfg->recurrent ? 4 * tc::rnn_workspace_floats(positions, update) : 0;
+  return cfg->recurrent ? 4 * tc::rnn_workspace_floats(positions, update, cfg->in_dim) : 0;
 }
 
 extern "C" int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,

@@ -814,7 +814,7 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
   a.ntiles = (a.rows + kBM - 1) / kBM;
   constexpr bool kCritic = (MODE == 1 || MODE == 3 || MODE >= 4);        // one register column for the head
   if constexpr (kCritic) {
-    if (MODE < 4 && cfg->in_dim > 64) {         // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
+    if (cfg->in_dim > 64) {                     // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
       MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
       a.Kp = 32;
       a.z1 = static_cast<float*>(a.workspace);
@@ -822,7 +822,7 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
       else if (int rc = launch_wide_fc1(a, a.workspace, stream, who)) return rc;
       if (int rc = launch_one<MODE, 32, 1, true>(a, stream, who)) return rc;
       if (MODE == 3 && a.packed) return launch_wide_wgrad1_packed(a, a.workspace, a.packed, stream, who);
-      if (MODE == 3) return launch_wide_wgrad1(a, a.workspace, stream, who);
+      if (MODE == 3 || MODE == 5) return launch_wide_wgrad1(a, a.workspace, stream, who);
       return 0;
     }
     if (a.Kp == 32) return launch_one<MODE, 32, 1>(a, stream, who);

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kThreads, 1) fc1_wide_kernel(const WideArgs a)
     RowInfo ri;
     ri.g = tile * kBM + r;
     ri.valid = ri.g < a.rows;
-    const long long srow = ri.valid ? (a.index ? a.index[ri.g] / a.x_div : ri.g) : 0;
+    const long long srow = ri.valid ? ((a.index ? a.index[ri.g] : ri.g) / a.x_div) : 0;
     ri.row = a.x + srow * (long long)a.ld;
     ri.x0 = (ri.valid && L.use_fn) ? __ldg(ri.row) : 0.0f;
     return ri;
@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     for (int rr = warp; rr < kHR; rr += kThreads / 32) {
       const long long g = ht * kHR + rr;
       const bool ok = g < a.rows;
-      const long long srow = ok ? (a.index ? a.index[g] / a.x_div : g) : 0;
+      const long long srow = ok ? ((a.index ? a.index[g] : g) / a.x_div) : 0;
       const float* __restrict__ src = a.x + srow * (long long)a.ld + col0;
       float* dst = xs + rr * xs_stride;
       const int lim = ok ? D - col0 : 0;                                // valid floats of this row from col0 on
@@ -534,7 +534,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
   auto prefetch = [&](long long ht) {
     const long long g = ht * kHR + hr;
     valid = g < a.rows;
-    const long long srow = valid ? (a.index ? a.index[g] / a.x_div : g) : 0;
+    const long long srow = valid ? ((a.index ? a.index[g] : g) / a.x_div) : 0;
     const float* __restrict__ row = a.x + srow * (long long)a.ld;
     if (a.norm && valid) { mean = __ldg(a.xstats + 2 * g); rstd = __ldg(a.xstats + 2 * g + 1); }
     else { mean = 0.0f; rstd = 1.0f; }
@@ -793,6 +793,8 @@ bool wide_supports(const mappo_net_config* cfg) {
   return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim > 64 &&
          make_fwd_map(cfg->in_dim, 4).total <= (uint32_t)kWideMaxSmem;
 }
+
+bool wide_fits(int in_dim) { return make_fwd_map(in_dim, 4).total <= (uint32_t)kWideMaxSmem; }
 
 // bytes of the caller-provided scratch: z1 / dz1 [rows][64] (the gradient overwrites the activations in place) and the
 // row statistics [rows][2]

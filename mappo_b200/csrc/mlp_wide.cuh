@@ -25,6 +25,7 @@ struct WideArgs {
 };
 
 int launch_wgrad_generic(WideArgs& w, cudaStream_t stream, const char* who);
+bool wide_fits(int in_dim);      // the staged first layer (fc1_wide_kernel) has room for this many input columns
 
 }  // namespace tc
 }  // namespace mappo

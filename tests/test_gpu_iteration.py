@@ -44,6 +44,14 @@ def test_full_iteration_wide_observations():
     g._smoke_iteration(M=15, N=24)
 
 
+def test_full_iteration_recurrent_wide_inputs():
+    """GRU policies whose base reads more than 64 columns: rmappo with 5 agents (centralised critic over 5 x 26 = 130
+    columns) and ippo's default recurrent policy with 15 agents (actor and critic over 66 columns)."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=5, N=32, extra="--algorithm_name rmappo --data_chunk_length 10")
+    g._smoke_iteration(M=15, N=16, extra="--algorithm_name ippo --data_chunk_length 5")
+
+
 def _make_runner(extra, N=192, M=3):
     import torch
     from mappo_b200.config import parse_args
