@@ -349,7 +349,7 @@ extern "C" int mappo_update_num_blocks(const mappo_net_config* cfg, long long ro
 
 extern "C" long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long long rows) {
   if (!cfg || rows < 0) return -1;
-  return (cfg->in_dim > kMaxIn && use_tc(cfg)) ? tc::wide_workspace_bytes(rows) : 0;
+  return (cfg->in_dim >= kWideFrom && use_tc(cfg)) ? tc::wide_workspace_bytes(rows) : 0;
 }
 
 extern "C" int mappo_actor_forward(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,
@@ -411,14 +411,14 @@ extern "C" int mappo_critic_update(const mappo_net_config* cfg, const mappo_loss
   a.value_preds = value_preds; a.returns = returns; a.active = active_masks; a.vn_stats = vn_stats; a.loss = *loss;
   a.grad_partials = grad_partials; a.loss_partials = loss_partials; a.workspace = workspace;
   a.packed = packed_inputs;
-  MAPPO_REQUIRE(!packed_inputs || (!index && share_rows_div == 1 && cfg->in_dim > kMaxIn && use_tc(cfg)),
+  MAPPO_REQUIRE(!packed_inputs || (!index && share_rows_div == 1 && cfg->in_dim >= kWideFrom && use_tc(cfg)),
                 "critic_update: packed inputs need the wide first layer and no row gather");
   return launch_mlp<3>(a, cfg, (cudaStream_t)stream, "critic_update");
 }
 
 extern "C" long long mappo_critic_packed_bytes(const mappo_net_config* cfg, long long rows) {
   if (!cfg || rows < 0) return -1;
-  if (!(cfg->in_dim > kMaxIn && use_tc(cfg))) return 0;
+  if (!(cfg->in_dim >= kWideFrom && use_tc(cfg))) return 0;
   MlpArgs a{};
   a.L = make_layout(*cfg); a.x_div = 1;
   return tc::wide_pack_ok(a) ? tc::wide_packed_bytes(cfg->in_dim, rows) : 0;
@@ -427,7 +427,7 @@ extern "C" long long mappo_critic_packed_bytes(const mappo_net_config* cfg, long
 extern "C" int mappo_critic_pack_inputs(const mappo_net_config* cfg, const float* share_obs, int obs_ld, long long rows,
                                         void* packed, void* workspace, void* stream) {
   if (int rc = check_net(cfg, "critic_pack_inputs")) return rc;
-  MAPPO_REQUIRE(cfg->is_critic && cfg->in_dim > kMaxIn && use_tc(cfg), "critic_pack_inputs: only the wide first layer packs its inputs");
+  MAPPO_REQUIRE(cfg->is_critic && cfg->in_dim >= kWideFrom && use_tc(cfg), "critic_pack_inputs: only the wide first layer packs its inputs");
   MAPPO_REQUIRE(share_obs && packed && workspace && rows > 0 && obs_ld >= cfg->in_dim, "critic_pack_inputs: bad arguments");
   MlpArgs a{};
   a.L = make_layout(*cfg); a.x = share_obs; a.ld = obs_ld; a.rows = rows; a.x_div = 1;

@@ -564,8 +564,8 @@ constexpr int kGruMaxSmem = 232448 - 1024;
 static int check_rnn(const mappo_net_config* cfg, const char* who) {
   if (int rc = check_net(cfg, who)) return rc;
   MAPPO_REQUIRE(cfg->recurrent, "%s: not a recurrent network", who);
-  if (cfg->in_dim == 64 || (cfg->in_dim > 64 && !wide_fits(cfg->in_dim)))
-    MAPPO_UNSUPPORTED("%s: recurrent networks with in_dim %d are not built (64, or too wide for the staged first layer)", who, cfg->in_dim);
+  if (cfg->in_dim >= kWideFrom && !wide_fits(cfg->in_dim))
+    MAPPO_UNSUPPORTED("%s: in_dim %d is too wide for the staged first layer", who, cfg->in_dim);
   return 0;
 }
 
@@ -591,7 +591,7 @@ static int head_grid(long long rows) {
 // floats of workspace per position: rollout keeps the base features only
 // + the wide first layer's scratch (z1 [64] and row statistics [2] per position) when the base reads more than 64 columns
 long long rnn_workspace_floats(long long positions, int update, int in_dim) {
-  return positions * ((update ? 513 : 64) + (in_dim > 64 ? 66 : 0));
+  return positions * ((update ? 513 : 64) + (in_dim >= kWideFrom ? 66 : 0));
 }
 
 // mpos[p] = masks[index[p]]: the sweeps read their step's mask with the rest of the step's rows instead of behind a
@@ -641,7 +641,7 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
   MAPPO_CUDA(cudaMemsetAsync(a.loss_partials, 0, sizeof(double) * 4 * (size_t)n_partials, stream));
   float* ws = static_cast<float*>(a.workspace);
   float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256;
-  float* mpos = ws + B * (512 + (cfg->in_dim > 64 ? 66 : 0));
+  float* mpos = ws + B * (512 + (cfg->in_dim >= kWideFrom ? 66 : 0));
   a.workspace = ws + B * 512;                            // the wide first layer's scratch, if the base needs one
   gather_masks_kernel<<<(int)((B + 255) / 256 < 1184 ? (B + 255) / 256 : 1184), 256, 0, stream>>>(masks, a.index, mpos, B);
   MAPPO_CHECK_LAUNCH(who);

@@ -764,7 +764,7 @@ int launch_wide_wgrad1_packed(const MlpArgs& a, void* workspace, const void* pac
 bool supports(const mappo_net_config* cfg) {
   const bool wide = wide_supports(cfg);
   if (wide && cfg->is_critic) return true;
-  if (!wide && !(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim < 64)) return false;
+  if (!wide && !(cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim < kWideFrom)) return false;
   int A = 0;
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
@@ -814,7 +814,7 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
   a.ntiles = (a.rows + kBM - 1) / kBM;
   constexpr bool kCritic = (MODE == 1 || MODE == 3 || MODE >= 4);        // one register column for the head
   if constexpr (kCritic) {
-    if (cfg->in_dim > 64) {                     // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
+    if (cfg->in_dim >= kWideFrom) {             // wide first layer: fc1 GEMM, fused 64-wide kernel, fc1 weight-gradient GEMM
       MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
       a.Kp = 32;
       a.z1 = static_cast<float*>(a.workspace);
@@ -829,7 +829,7 @@ int launch(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const c
     return launch_one<MODE, 64, 1>(a, stream, who);
   } else {
   const bool small_head = cfg->n_heads == 1 && a.L.a_total <= 8 && a.avail == nullptr;
-  if (cfg->in_dim > 64) {                         // wide observation (e.g. simple_spread with >= 12 agents): same three-kernel chain
+  if (cfg->in_dim >= kWideFrom) {                 // wide observation (e.g. simple_spread with >= 12 agents): same three-kernel chain
     MAPPO_REQUIRE(a.workspace, "%s: in_dim %d needs a workspace of mappo_mlp_workspace_bytes()", who, cfg->in_dim);
     a.Kp = 32;
     a.z1 = static_cast<float*>(a.workspace);

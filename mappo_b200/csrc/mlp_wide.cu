@@ -790,7 +790,7 @@ constexpr int kWideMaxSmem = 232448 - 1024;
 int grid_for(long long rows);                                             // mlp_tc.cu
 
 bool wide_supports(const mappo_net_config* cfg) {
-  return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim > 64 &&
+  return cfg && cfg->hidden == 64 && cfg->layer_N == 1 && !cfg->recurrent && cfg->in_dim >= kWideFrom &&
          make_fwd_map(cfg->in_dim, 4).total <= (uint32_t)kWideMaxSmem;
 }
 

@@ -13,7 +13,8 @@
 namespace mappo {
 
 constexpr int kH = 64;          // hidden size this build supports
-constexpr int kMaxIn = 64;      // widest input handled by the single-chunk first layer
+constexpr int kMaxIn = 64;      // widest input handled by the single-chunk first layer (fp32 FMA kernels)
+constexpr int kWideFrom = 64;   // tensor-core path: from this width on the first layer runs outside the fused kernel (mlp_wide.cu)
 
 struct NetLayout {
   int in_dim, H, n_heads, head_dim[MAPPO_MAX_HEADS], a_total;

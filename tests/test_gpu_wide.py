@@ -52,7 +52,8 @@ def _oracle_critic(a, pol, tr, sample):
                                        (100, 129, "--use_feature_normalization"),
                                        # beyond ~630 columns W1' is staged 32 output columns at a time (one pass over x per part):
                                        (990, 700, ""), (1120, 300, "--use_ReLU --use_feature_normalization"),
-                                       (2000, 300, "")])                # 16 columns at a time
+                                       (2000, 300, ""),                 # 16 columns at a time
+                                       (64, 500, "")])                  # exactly 64: no padding column left in the fused kernel
 def test_wide_critic_values_loss_and_gradients(S, B, flags):
     a, pol, tr, sample = _setup(S, B, flags)
     want_v, want_vl, want_g = _oracle_critic(a, pol, tr, sample)
@@ -154,7 +155,7 @@ def test_packing_is_refused_with_a_row_gather():
 
 
 
-@pytest.mark.parametrize("D,A,B,flags", [(70, 5, 1000, ""), (118, 5, 12800 + 77, "--use_ReLU"), (70, 12, 700, ""),
+@pytest.mark.parametrize("D,A,B,flags", [(64, 5, 300, ""), (70, 5, 1000, ""), (118, 5, 12800 + 77, "--use_ReLU"), (70, 12, 700, ""),
                                          (100, 5, 129, "--use_feature_normalization")])
 def test_wide_actor_logp_loss_and_gradients(D, A, B, flags):
     """Observations wider than 64 columns (simple_spread from 12 agents up: 4 + 2 L + 4 (M - 1)): the actor takes the same
