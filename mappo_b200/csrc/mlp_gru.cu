@@ -413,10 +413,27 @@ __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const
   const long long ntiles = (a.rows + BM - 1) / BM;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     __syncthreads();
-    for (int r = warp; r < BM; r += NT / 32) {                            // (A) y = LN(h), one warp per row
-      const long long g = tile * BM + r;
-      float v0 = 0.0f, v1 = 0.0f;
-      if (g < a.rows) { v0 = h[g * 64 + lane]; v1 = h[g * 64 + lane + 32]; }
+    if (tid == 0 && tile + gridDim.x < ntiles) {                          // the next tile's rows: ask the L2 for them now
+      const long long g0 = (tile + gridDim.x) * BM;
+      umma::l2_prefetch(h + g0 * 64, (uint32_t)min((long long)BM, a.rows - g0) * 256u);
+    }
+    // (A) y = LN(h), one warp per row; a warp's rows are loaded eight at a time so that one DRAM round trip serves eight
+    // rows instead of one
+    constexpr int kRowsPerWarp = BM / (NT / 32), kBatch = 8;
+    static_assert(kRowsPerWarp % kBatch == 0, "rows per warp");
+#pragma unroll 1
+    for (int rb = 0; rb < kRowsPerWarp; rb += kBatch) {
+      float w0[kBatch], w1[kBatch];
+#pragma unroll
+      for (int i = 0; i < kBatch; ++i) {
+        const long long g = tile * BM + warp + (NT / 32) * (rb + i);
+        w0[i] = w1[i] = 0.0f;
+        if (g < a.rows) { w0[i] = __ldg(h + g * 64 + lane); w1[i] = __ldg(h + g * 64 + lane + 32); }
+      }
+#pragma unroll
+      for (int i = 0; i < kBatch; ++i) {
+      const int r = warp + (NT / 32) * (rb + i);
+      float v0 = w0[i], v1 = w1[i];
       float s = v0 + v1;
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
       const float mean = s * (1.0f / 64.0f);
@@ -427,6 +444,7 @@ __global__ void __launch_bounds__(256, 2) gru_head_kernel(const MlpArgs a, const
       smf[S::TY + r * kLD + lane] = v0 * rstd;
       smf[S::TY + r * kLD + lane + 32] = v1 * rstd;
       if (lane == 0) smf[S::rstd + r] = rstd;
+      }
     }
     __syncthreads();
     {                                                                     // (B) logits: two threads per row
