@@ -408,6 +408,14 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     const bool valid = g < a.rows;
     const bool has_next = tile + gridDim.x < a.ntiles;
     const long long src = (valid && a.index) ? a.index[g] : (valid ? g : 0);
+    // rows this tile will only ask for once it is under way (z1 of a wide first layer, dLoss/dn2 of a recurrent base)
+    // are exposed DRAM latency with one tile per CTA: one thread asks the L2 for the NEXT tile's now
+    if ((WIDE || MODE == 5) && has_next && tid == 96) {
+      const long long g0 = (tile + gridDim.x) * kBM;
+      const uint32_t bytes = (uint32_t)min((long long)kBM, a.rows - g0) * 256u;
+      if (WIDE) umma::l2_prefetch(a.z1 + g0 * 64, bytes);
+      if (MODE == 5) umma::l2_prefetch(a.feat + g0 * 64, bytes);
+    }
     // per-row scalars of the register loss path, requested now and consumed after the second layer
     float p_actf = 0.0f;                              // converted at its use: no wait on the load up here
     float p_old = 0.0f, p_adv = 0.0f, p_active = 1.0f;
