@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define MAPPO_B200_ABI_VERSION 4
+#define MAPPO_B200_ABI_VERSION 5
 
 typedef enum {
   MAPPO_OK = 0,
@@ -345,7 +345,8 @@ int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float* params, co
                             long long rows, const float* rnn_states_in, const float* masks,
                             const float* available_actions, int deterministic, uint64_t seed, uint64_t step,
                             long long row_offset, const float* given_actions, float* rnn_states_out,
-                            float* actions_out, float* logp_out, float* entropy_out, void* workspace, void* stream);
+                            float* actions_out, float* logp_out, float* entropy_out, const int64_t* step_offset,
+                            void* workspace, void* stream);     /* step_offset: as mappo_actor_forward (ABI v5) */
 
 /* share_obs row of sample i is share_obs[i / share_rows_div] (several agents' samples may share one row). */
 int mappo_critic_forward_rnn(const mappo_net_config* cfg, const float* params, const float* share_obs, int obs_ld,

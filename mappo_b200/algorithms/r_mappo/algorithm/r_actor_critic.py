@@ -189,12 +189,19 @@ class R_Actor(_FlatNet):
                      row_offset=0, rnn_in=None, masks=None, rnn_out=None):
         """Hot-path entry: writes float32 action ids and log-probs (and, recurrent, the next rnn state) straight into
         buffer slots."""
-        dev_step = self.step_dev if (step is None and not self._recurrent) else None
+        dev_step = self.step_dev if step is None else None
         if step is None:
             step = self._calls
         self._calls += 1
         if not self.discrete:
             available_actions = None
+        if dev_step is not None and self._recurrent:
+            ops.actor_forward_rnn(self.cfg, self.flat, obs, rnn_in, masks, rnn_out, actions_out, logp_out,
+                                  available_actions=None if available_actions is None else available_actions.contiguous(),
+                                  deterministic=deterministic, seed=self.sample_seed, step=0, row_offset=row_offset,
+                                  step_offset=dev_step)
+            dev_step.add_(1)
+            return
         if dev_step is not None:
             ops.actor_forward(self.cfg, self.flat, obs, actions_out, logp_out,
                               available_actions=None if available_actions is None else available_actions.contiguous(),

@@ -704,13 +704,14 @@ extern "C" int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float*
                                        long long rows, const float* rnn_states_in, const float* masks,
                                        const float* available_actions, int deterministic, uint64_t seed, uint64_t step,
                                        long long row_offset, const float* given_actions, float* rnn_states_out,
-                                       float* actions_out, float* logp_out, float* entropy_out, void* workspace,
-                                       void* stream) {
+                                       float* actions_out, float* logp_out, float* entropy_out,
+                                       const int64_t* step_offset, void* workspace, void* stream) {
   MAPPO_REQUIRE(logp_out && (actions_out || given_actions), "actor_forward_rnn: null outputs");
   MAPPO_REQUIRE(!cfg || !cfg->is_critic, "actor_forward_rnn: critic config");
   MlpArgs a{};
   a.params = params; a.x = obs; a.ld = obs_ld; a.rows = rows; a.avail = available_actions;
   a.deterministic = deterministic; a.k0 = (uint32_t)(seed & 0xFFFFFFFFull); a.step = (uint32_t)step;
+  a.step_dev = step_offset;
   a.row_offset = row_offset; a.actions_out = actions_out; a.logp_out = logp_out;
   a.given_actions = given_actions; a.entropy_out = entropy_out; a.workspace = workspace;
   return tc::rnn_forward<0>(a, cfg, rnn_states_in, masks, rnn_states_out, (cudaStream_t)stream, "actor_forward_rnn");

@@ -276,19 +276,20 @@ def _h2(x, rows):
 
 
 def actor_forward_rnn(cfg, params, obs, rnn_in, masks, rnn_out, actions_out, logp_out, available_actions=None,
-                      deterministic=False, seed=0, step=0, row_offset=0, given_actions=None, entropy_out=None):
+                      deterministic=False, seed=0, step=0, row_offset=0, given_actions=None, entropy_out=None,
+                      step_offset=None):
     obs, ld = _rows_view(obs)
     rows = obs.shape[0]
     ws = rnn_workspace(cfg, rows, 0, obs.device)
     L = _lib.lib()
     L.mappo_actor_forward_rnn.argtypes = [_NC, _P, _P, C.c_int, C.c_longlong, _P, _P, _P, C.c_int, C.c_uint64, C.c_uint64,
-                                          C.c_longlong, _P, _P, _P, _P, _P, _P, _P]
+                                          C.c_longlong, _P, _P, _P, _P, _P, _P, _P, _P]
     with TIMERS.span("actor_forward"):
         check(L.mappo_actor_forward_rnn(C.byref(cfg), ptr(params), _vp(obs), ld, rows, ptr(_h2(rnn_in, rows)),
                                         ptr(_f32c(masks.reshape(rows), "masks")), ptr(available_actions),
                                         int(deterministic), int(seed) & (2 ** 64 - 1), int(step), int(row_offset),
                                         ptr(given_actions), ptr(_h2(rnn_out, rows)), ptr(actions_out), ptr(logp_out),
-                                        ptr(entropy_out), ptr(ws), stream_ptr()), "actor_forward_rnn")
+                                        ptr(entropy_out), ptr(step_offset), ptr(ws), stream_ptr()), "actor_forward_rnn")
 
 
 def critic_forward_rnn(cfg, params, share_obs, rnn_in, masks, rnn_out, values_out, share_rows_div=1):

@@ -61,12 +61,12 @@ class MPERunner(Runner):
 
     def _graph_eligible(self):
         """A graph replays fixed launches: nothing on the path may depend on host state that changes between
-        iterations.  That rules out host-drawn permutations (num_mini_batch > 1, the recurrent generators), a learning
+        iterations.  That rules out host-drawn permutations (num_mini_batch > 1, the naive recurrent generator), a learning
         rate schedule, the NCCL hooks and per-kernel event timing; the sampling counter and the Adam step counts move
         into HBM (R_Actor.use_device_step, FusedAdam.use_device_step)."""
         from ... import ops
         t, b = self.trainer, self.buffer
-        return (self.use_cuda_graph and not b._recurrent and t.num_mini_batch == 1 and not b.force_permutation
+        return (self.use_cuda_graph and not t._use_naive_recurrent and t.num_mini_batch == 1 and not b.force_permutation
                 and not self.use_linear_lr_decay and t.all_reduce is None and not ops.TIMERS.enabled)
 
     def _iteration_on_stream(self):

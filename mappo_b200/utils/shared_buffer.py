@@ -131,8 +131,20 @@ class SharedReplayBuffer(object):
         L = data_chunk_length
         data_chunks = (N * T * M) // L
         mini_batch_size = data_chunks // num_mini_batch
-        rand = torch.randperm(data_chunks).to(self.device)
         dev = self.device
+        if num_mini_batch == 1 and not self.force_permutation:
+            # one minibatch = every chunk: the losses are means over it and each chunk carries its own initial state, so
+            # the permutation (shared_buffer.py:397) only reorders the sums -- chunks are taken in storage order, the
+            # index is built once, and nothing on the path depends on the host any more (CUDA-graph capture)
+            key = (L, mini_batch_size)
+            if getattr(self, "_chunk_rows_key", None) != key:
+                idx = torch.arange(mini_batch_size, device=dev)
+                pos = idx[None, :] * L + torch.arange(L, device=dev)[:, None]
+                self._chunk_rows = ((pos % T) * (N * M) + pos // T).reshape(-1).contiguous()
+                self._chunk_rows_key = key
+            yield self._chunk_rows, mini_batch_size, L
+            return
+        rand = torch.randperm(data_chunks).to(self.device)
         for i in range(num_mini_batch):
             idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size]
             pos = idx[None, :] * L + torch.arange(L, device=dev)[:, None]            # stream positions, [N, M, T] order

@@ -66,15 +66,16 @@ def _make_runner(extra, N=192, M=3):
     return r
 
 
-@pytest.mark.parametrize("M", [3, 10])
-def test_cuda_graph_iteration_equals_eager(M):
+@pytest.mark.parametrize("M,extra", [(3, ""), (10, ""), (3, "--algorithm_name rmappo --data_chunk_length 10")])
+def test_cuda_graph_iteration_equals_eager(M, extra):
     """--use_cuda_graph: iteration 1 eager with device-resident counters, iteration 2 captured,
     iterations 3+ replayed.  Same Philox streams and the same kernels as the eager runner, so the sampled actions are
     identical; the Adam bias corrections come from pow() on the device instead of the host (<= 1 ulp of float32 apart),
-    hence a tolerance on the parameters instead of equality."""
+    hence a tolerance on the parameters instead of equality.  rmappo: with num_mini_batch == 1 the chunks are taken in
+    storage order (their permutation only reorders the sums), so the recurrent update is capturable too."""
     import numpy as np
     import torch
-    eager, graph = _make_runner("", M=M), _make_runner("--use_cuda_graph", M=M)
+    eager, graph = _make_runner(extra, M=M), _make_runner("--use_cuda_graph " + extra, M=M)
     assert graph._graph_eligible() and not eager._graph_eligible()
     for it in range(5):
         ie, ig = eager.run_episode(), graph.run_episode()

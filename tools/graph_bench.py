@@ -11,10 +11,10 @@ from mappo_b200.envs.mpe.MPE_env import MPEVecEnv  # noqa: E402
 from mappo_b200.runner.shared.mpe_runner import MPERunner  # noqa: E402
 
 
-def run(N, M, graph, steps=10, warm=4):
+def run(N, M, graph, steps=10, warm=4, extra=""):
     a = parse_args(("--scenario_name simple_spread --num_agents %d --num_landmarks 3 --n_rollout_threads %d "
-                    "--episode_length 25 --ppo_epoch 10 --lr 7e-4 --critic_lr 7e-4 --seed 1 %s"
-                    % (M, N, "--use_cuda_graph" if graph else "")).split())
+                    "--episode_length 25 --ppo_epoch 10 --lr 7e-4 --critic_lr 7e-4 --seed 1 %s %s"
+                    % (M, N, "--use_cuda_graph" if graph else "", extra)).split())
     envs = MPEVecEnv(a, device="cuda:0")
     r = MPERunner({"all_args": a, "envs": envs, "device": torch.device("cuda:0"), "num_agents": M, "run_dir": None})
     r.warmup()
@@ -35,4 +35,7 @@ if __name__ == "__main__":
     out = {}
     for name, N, M in (("C1_128envs", 128, 3), ("4096envs", 4096, 3), ("C2_65536envs", 65536, 3), ("C5_16384x10", 16384, 10)):
         out[name] = {"eager": run(N, M, False), "graph": run(N, M, True)}
+    rm = "--algorithm_name rmappo --data_chunk_length 10"
+    for name, N, M in (("rmappo_128envs", 128, 3), ("rmappo_4096envs", 4096, 3)):
+        out[name] = {"eager": run(N, M, False, extra=rm), "graph": run(N, M, True, extra=rm)}
     print(json.dumps(out))
