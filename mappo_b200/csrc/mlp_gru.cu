@@ -40,7 +40,8 @@ constexpr uint32_t kGChunk = 192 * 16;                   // bytes of one 8-colum
 constexpr uint32_t kGPiece = 8 * kGChunk;                // one fp16 piece of a [192][64] weight
 constexpr uint32_t kTile = 2 * 8 * kRowChunk;            // a [128][64] operand tile, both pieces
 
-struct GruMap { uint32_t Wih, Whh, T0, T1, T2, bias, bars, total; };
+constexpr uint32_t kStageFloats = 32 * 64;                 // one lane quarter's staging tile: 32 rows x 64 floats
+struct GruMap { uint32_t Wih, Whh, T0, T1, T2, bias, bars, stage, total; };
 __host__ __device__ inline GruMap make_gru_map(bool bwd) {
   GruMap m;
   uint32_t o = 0;
@@ -52,6 +53,7 @@ __host__ __device__ inline GruMap make_gru_map(bool bwd) {
   m.T2 = take(bwd ? kTile : 0);
   m.bias = take(4 * 64 * 4);
   m.bars = take(64);
+  m.stage = take(bwd ? 4 * kStageFloats * 4 : 2 * 4 * kStageFloats * 4);    // row staging: one (bwd) or two (fwd) tiles per lane quarter
   m.total = o;
   return m;
 }
@@ -86,6 +88,29 @@ __device__ __forceinline__ void store16(float* __restrict__ p, const float (&v)[
 #pragma unroll
   for (int i = 0; i < 4; ++i) q[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
 }
+// ---- coalesced row stores ----------------------------------------------------------------------------------
+// Thread (row, column quarter) owns 16 columns of its row (the TMEM lane mapping), so a direct st.global.v4 touches 32
+// rows per warp instruction: 32 L1 wavefronts for 512 bytes.  Measured with clock64 (C4): those stores were 15 of the 20
+// thousand cycles of a forward step.  The four warps that share a lane quarter (32 rows) therefore pass each array
+// through a 32 x 64 staging tile -- 16-byte pieces XOR-swizzled by the row, conflict-free in both directions -- and
+// write two whole rows per warp instruction.
+__device__ __forceinline__ float4* stage_piece(float* st, int row, int piece) {
+  return reinterpret_cast<float4*>(st) + row * 16 + (piece ^ (row & 7));
+}
+__device__ __forceinline__ void put_rows(float* st, int lane, int cq, const float (&v)[16]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) *stage_piece(st, lane, 4 * cq + i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+// gdst: row 0 of the quarter's 32 rows, `stride` floats between rows; rows >= nvalid are padding of a ragged tile
+__device__ __forceinline__ void flush_rows(float* st, float* __restrict__ gdst, int stride, int nvalid, int lane, int cq) {
+  const int j = 32 * cq + lane, pc = j & 15, r0 = j >> 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = r0 + 8 * i;
+    if (row < nvalid) *reinterpret_cast<float4*>(gdst + (long long)row * stride + 4 * pc) = *stage_piece(st, row, pc);
+  }
+}
+
 // acc0 + 2^-12 acc1 of this thread's 16 columns
 __device__ __forceinline__ void tmem_pair16(uint32_t a0, uint32_t a1, float (&v)[16]) {
   float w[16];
@@ -121,9 +146,22 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
                      id64 = umma::idesc_f16(128, 64, 0, 0);
   uint32_t ph = 0;
   const long long ntiles = (a.nc + kBM - 1) / kBM;
+  float* stage = reinterpret_cast<float*>(sm + m.stage) + (size_t)q4 * 2 * kStageFloats;   // this quarter's two staging tiles
+  uint32_t sk = 0;                                                       // arrays staged so far (alternates the tiles)
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long c = tile * kBM + r;
     const bool valid = c < a.nc;
+    const long long c0 = tile * kBM + 32 * q4;                           // first row of this lane quarter
+    const int nvalid = (int)max(0LL, min(32LL, a.nc - c0));
+    // row 0 of the quarter in a position-indexed array with `stride` floats per row; one barrier per array: the tile
+    // written two arrays ago is only rewritten after everybody passed the barrier in between, i.e. after its reads
+    auto store_rows = [&](float* arr, long long p0, int stride, const float (&v)[16]) {
+      float* st = stage + (sk & 1) * kStageFloats;
+      put_rows(st, lane, cq, v);
+      bar_named(1 + q4, 128);
+      flush_rows(st, arr + p0 * stride, stride, nvalid, lane, cq);
+      ++sk;
+    };
     float h[16], x[16], mask;
     {
       const long long src = valid ? (a.index ? a.index[c] : c) : 0;
@@ -140,7 +178,8 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
       for (int i = 0; i < 16; ++i) h[i] *= mask;                          // hm = h_prev * mask[p]
       store_cols16(sm + m.T0, r, cq, x);
       store_cols16(sm + m.T1, r, cq, h);
-      if (valid && a.hm) store16(a.hm + p * 64 + 16 * cq, h);
+      const long long p0 = (long long)s * a.nc + c0;
+      if (a.hm) store_rows(a.hm, p0, 64, h);
       umma::fence_async_smem();
       umma::tc_fence_before();
       __syncthreads();
@@ -179,29 +218,29 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
       umma::mbar_wait(bar, ph); ph ^= 1;
       umma::tc_fence_after();
       float g[16], t[16];
-      float* gp = (valid && a.gates) ? a.gates + p * 256 + 16 * cq : nullptr;
+      float* gates = a.gates;
       tmem_pair16(la, la + 192, g);                                      // r
 #pragma unroll
       for (int i = 0; i < 16; ++i) g[i] = sigmoid_f(g[i] + bias[i]);
-      if (gp) store16(gp, g);
+      if (gates) store_rows(gates, p0, 256, g);
       tmem_pair16(la + 384, la + 448, t);                                // Whn h + bhn
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] += bias[192 + i];
-      if (gp) store16(gp + 192, t);
+      if (gates) store_rows(gates + 192, p0, 256, t);
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] *= g[i];
       tmem_pair16(la + 128, la + 192 + 128, g);                          // n
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] = tanh_fast(g[i] + bias[128 + i] + t[i]);
-      if (gp) store16(gp + 128, t);
+      if (gates) store_rows(gates + 128, p0, 256, t);
       tmem_pair16(la + 64, la + 192 + 64, g);                            // z
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         g[i] = sigmoid_f(g[i] + bias[64 + i]);
         h[i] = fmaf(g[i], h[i] - t[i], t[i]);                            // (1 - z) n + z hm
       }
-      if (gp) store16(gp + 64, g);
-      if (valid) store16(a.hs + p * 64 + 16 * cq, h);
+      if (gates) store_rows(gates + 64, p0, 256, g);
+      store_rows(a.hs, p0, 64, h);
 #pragma unroll
       for (int i = 0; i < 16; ++i) x[i] = xn[i];
       mask = mask_n;
@@ -254,6 +293,18 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long c = tile * kBM + r;
     const bool valid = c < a.nc;
+    const long long c0 = tile * kBM + 32 * q4;                           // first row of this lane quarter
+    const int nvalid = (int)max(0LL, min(32LL, a.nc - c0));
+    float* stage = reinterpret_cast<float*>(sm + m.stage) + (size_t)q4 * kStageFloats;
+    // coalesced row store (see put_rows): one staging tile here, so a second barrier frees it for the next array.  A slot
+    // is only overwritten after every thread of the quarter has CONSUMED what it loaded from it (the loads feed
+    // arithmetic that precedes the put in program order), since the flush writes other threads' rows.
+    auto store_rows = [&](float* arr, long long p0, int stride, const float (&v)[16]) {
+      put_rows(stage, lane, cq, v);
+      bar_named(1 + q4, 128);
+      flush_rows(stage, arr + p0 * stride, stride, nvalid, lane, cq);
+      bar_named(1 + q4, 128);
+    };
     float carry[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) carry[i] = 0.0f;
@@ -296,22 +347,23 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
       }
       store_cols16(sm + m.T1, r, cq, w);
       store_cols16(sm + m.T2, r, cq, v);
+      const long long p0 = (long long)s * a.nc + c0;
       if (valid) {
         load16(gp, u);                                                  // r
         load16(gp + 192, dt);                                           // ghn
-        store16(gp + 128, w);                                           // P_z
-        store16(gp, v);                                                 // dgi_n
       } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) u[i] = dt[i] = 0.0f;
       }
+      store_rows(a.gates + 128, p0, 256, w);                            // dz~ (the slot held n: consumed above)
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        w[i] = v[i] * dt[i] * u[i] * (1.0f - u[i]);                     // dr~
-        v[i] *= u[i];                                                   // dgh_n = dn~ r
-      }
+      for (int i = 0; i < 16; ++i) w[i] = v[i] * dt[i] * u[i] * (1.0f - u[i]);   // dr~ (consumes r and ghn)
+      store_rows(a.gates, p0, 256, v);                                  // dgi_n (the slot held r)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] *= u[i];                        // dgh_n = dn~ r
       store_cols16(sm + m.T0, r, cq, w);
-      if (valid) { store16(gp + 64, w); store16(gp + 192, v); }
+      store_rows(a.gates + 64, p0, 256, w);                             // dr~ (the slot held z)
+      store_rows(a.gates + 192, p0, 256, v);                            // dgh_n (the slot held ghn)
       umma::fence_async_smem();
       umma::tc_fence_before();
       __syncthreads();
@@ -337,7 +389,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
       umma::mbar_wait(bar, ph); ph ^= 1;
       umma::tc_fence_after();
       tmem_pair16(la, la + 64, u);                                      // dn2
-      if (valid) store16(a.dh + p * 64 + 16 * cq, u);
+      store_rows(a.dh, p0, 64, u);                                      // (dh[p] was consumed at the top of the step)
       tmem_pair16(la + 128, la + 192, u);                               // dgh . Whh
 #pragma unroll
       for (int i = 0; i < 16; ++i) carry[i] = (u[i] + dd[i]) * mask;
