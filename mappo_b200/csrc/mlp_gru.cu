@@ -58,7 +58,14 @@ __host__ __device__ inline GruMap make_gru_map(bool bwd) {
   return m;
 }
 
-__device__ __forceinline__ float sigmoid_f(float x) { return __frcp_rn(1.0f + __expf(-x)); }
+// 1 / (1 + exp(-x)) with ex2.approx and rcp.approx (each within 1 ulp of its result; the exact reciprocal's refinement
+// steps were half of a forward step's gate arithmetic): two MUFU operations and two FMAs per element, like tanh_fast
+__device__ __forceinline__ float sigmoid_f(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+  return r;
+}
 
 __device__ __forceinline__ void stage_gru_weights(unsigned char* sm, const GruMap& m, const GruArgs& a) {
   const NetLayout& L = a.L;
