@@ -154,20 +154,17 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
   uint32_t ph = 0;
   const long long ntiles = (a.nc + kBM - 1) / kBM;
   float* stage = reinterpret_cast<float*>(sm + m.stage) + (size_t)q4 * 2 * kStageFloats;   // this quarter's two staging tiles
-  uint32_t sk = 0;                                                       // arrays staged so far (alternates the tiles)
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long c = tile * kBM + r;
     const bool valid = c < a.nc;
     const long long c0 = tile * kBM + 32 * q4;                           // first row of this lane quarter
     const int nvalid = (int)max(0LL, min(32LL, a.nc - c0));
-    // row 0 of the quarter in a position-indexed array with `stride` floats per row; one barrier per array: the tile
-    // written two arrays ago is only rewritten after everybody passed the barrier in between, i.e. after its reads
-    auto store_rows = [&](float* arr, long long p0, int stride, const float (&v)[16]) {
-      float* st = stage + (sk & 1) * kStageFloats;
+    // row 0 of the quarter in a position-indexed array with `stride` floats per row
+    auto store_rows_b = [&](float* arr, long long p0, int stride, const float (&v)[16]) {
+      float* st = stage + kStageFloats;
       put_rows(st, lane, cq, v);
       bar_named(1 + q4, 128);
       flush_rows(st, arr + p0 * stride, stride, nvalid, lane, cq);
-      ++sk;
     };
     float h[16], x[16], mask;
     {
@@ -186,7 +183,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
       store_cols16(sm + m.T0, r, cq, x);
       store_cols16(sm + m.T1, r, cq, h);
       const long long p0 = (long long)s * a.nc + c0;
-      if (a.hm) store_rows(a.hm, p0, 64, h);
+      if (a.hm) store_rows_b(a.hm, p0, 64, h);
       umma::fence_async_smem();
       umma::tc_fence_before();
       __syncthreads();
@@ -225,29 +222,51 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
       umma::mbar_wait(bar, ph); ph ^= 1;
       umma::tc_fence_after();
       float g[16], t[16];
+      // The gate rows leave one array behind the arithmetic: array k is put into one staging tile, array k + 1 is
+      // computed (MUFU-bound), then the quarter's barrier and the flush of array k -- so the barrier skew and the
+      // shared-memory round trip hide under the next gate's exponentials.  Tiles A and B alternate; a tile is rewritten
+      // only after the barrier that follows its flush.  (hm used B at the top of the step; a CTA-wide barrier lies between.)
       float* gates = a.gates;
+      float* stA = stage;
+      float* stB = stage + kStageFloats;
       tmem_pair16(la, la + 192, g);                                      // r
 #pragma unroll
       for (int i = 0; i < 16; ++i) g[i] = sigmoid_f(g[i] + bias[i]);
-      if (gates) store_rows(gates, p0, 256, g);
+      if (gates) put_rows(stA, lane, cq, g);
       tmem_pair16(la + 384, la + 448, t);                                // Whn h + bhn
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] += bias[192 + i];
-      if (gates) store_rows(gates + 192, p0, 256, t);
+      if (gates) {
+        bar_named(1 + q4, 128);
+        flush_rows(stA, gates + p0 * 256, 256, nvalid, lane, cq);
+        put_rows(stB, lane, cq, t);
+      }
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] *= g[i];
       tmem_pair16(la + 128, la + 192 + 128, g);                          // n
 #pragma unroll
       for (int i = 0; i < 16; ++i) t[i] = tanh_fast(g[i] + bias[128 + i] + t[i]);
-      if (gates) store_rows(gates + 128, p0, 256, t);
+      if (gates) {
+        bar_named(1 + q4, 128);
+        flush_rows(stB, gates + 192 + p0 * 256, 256, nvalid, lane, cq);
+        put_rows(stA, lane, cq, t);
+      }
       tmem_pair16(la + 64, la + 192 + 64, g);                            // z
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         g[i] = sigmoid_f(g[i] + bias[64 + i]);
         h[i] = fmaf(g[i], h[i] - t[i], t[i]);                            // (1 - z) n + z hm
       }
-      if (gates) store_rows(gates + 64, p0, 256, g);
-      store_rows(a.hs, p0, 64, h);
+      if (gates) {
+        bar_named(1 + q4, 128);
+        flush_rows(stA, gates + 128 + p0 * 256, 256, nvalid, lane, cq);
+        put_rows(stB, lane, cq, g);
+        bar_named(1 + q4, 128);
+        flush_rows(stB, gates + 64 + p0 * 256, 256, nvalid, lane, cq);
+      }
+      put_rows(stA, lane, cq, h);
+      bar_named(1 + q4, 128);
+      flush_rows(stA, a.hs + p0 * 64, 64, nvalid, lane, cq);
 #pragma unroll
       for (int i = 0; i < 16; ++i) x[i] = xn[i];
       mask = mask_n;
