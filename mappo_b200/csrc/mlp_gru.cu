@@ -118,6 +118,30 @@ __device__ __forceinline__ void flush_rows(float* st, float* __restrict__ gdst, 
   }
 }
 
+// The same for loads: the quarter's 128 threads fetch whole rows (two per warp instruction), several arrays in flight,
+// and each array then takes one trip through the staging tile to reach the threads that own its columns.
+__device__ __forceinline__ void fetch_rows(const float* __restrict__ gsrc, int stride, int nvalid, int lane, int cq, float4 (&q)[4]) {
+  const int j = 32 * cq + lane, pc = j & 15, r0 = j >> 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = r0 + 8 * i;
+    q[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (row < nvalid) q[i] = __ldg(reinterpret_cast<const float4*>(gsrc + (long long)row * stride + 4 * pc));
+  }
+}
+__device__ __forceinline__ void deal_rows(float* st, int bar_id, int lane, int cq, const float4 (&q)[4], float (&v)[16]) {
+  const int j = 32 * cq + lane, pc = j & 15, r0 = j >> 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) *stage_piece(st, r0 + 8 * i, pc) = q[i];
+  bar_named(bar_id, 128);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 t = *stage_piece(st, lane, 4 * cq + i);
+    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+  }
+  bar_named(bar_id, 128);                                               // the tile is free again
+}
+
 // acc0 + 2^-12 acc1 of this thread's 16 columns
 __device__ __forceinline__ void tmem_pair16(uint32_t a0, uint32_t a1, float (&v)[16]) {
   float w[16];
@@ -353,16 +377,18 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
       }
       float dt[16], u[16], v[16], w[16], dd[16];
       float mask = 0.0f;
-      float* gp = a.gates + p * 256 + 16 * cq;
-      if (valid) {
-        load16(a.dh + p * 64 + 16 * cq, dt);
-        load16(gp + 64, u);                                             // z
-        load16(gp + 128, v);                                            // n
-        load16(a.hm + p * 64 + 16 * cq, w);                             // hm
-        mask = a.mpos ? __ldg(a.mpos + p) : __ldg(a.masks + (a.index ? a.index[p] : p));
-      } else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) dt[i] = u[i] = v[i] = w[i] = 0.0f;
+      const long long p0 = (long long)s * a.nc + c0;
+      {
+        float4 q0[4], q1[4], q2[4], q3[4];                               // four arrays in flight, whole rows
+        fetch_rows(a.dh + p0 * 64, 64, nvalid, lane, cq, q0);
+        fetch_rows(a.gates + 64 + p0 * 256, 256, nvalid, lane, cq, q1);  // z
+        fetch_rows(a.gates + 128 + p0 * 256, 256, nvalid, lane, cq, q2); // n
+        fetch_rows(a.hm + p0 * 64, 64, nvalid, lane, cq, q3);            // hm
+        if (valid) mask = a.mpos ? __ldg(a.mpos + p) : __ldg(a.masks + (a.index ? a.index[p] : p));
+        deal_rows(stage, 1 + q4, lane, cq, q0, dt);
+        deal_rows(stage, 1 + q4, lane, cq, q1, u);
+        deal_rows(stage, 1 + q4, lane, cq, q2, v);
+        deal_rows(stage, 1 + q4, lane, cq, q3, w);
       }
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
@@ -373,13 +399,12 @@ __global__ void __launch_bounds__(kThreads, 1) gru_bwd_kernel(const GruArgs a) {
       }
       store_cols16(sm + m.T1, r, cq, w);
       store_cols16(sm + m.T2, r, cq, v);
-      const long long p0 = (long long)s * a.nc + c0;
-      if (valid) {
-        load16(gp, u);                                                  // r
-        load16(gp + 192, dt);                                           // ghn
-      } else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) u[i] = dt[i] = 0.0f;
+      {
+        float4 q0[4], q1[4];
+        fetch_rows(a.gates + p0 * 256, 256, nvalid, lane, cq, q0);       // r
+        fetch_rows(a.gates + 192 + p0 * 256, 256, nvalid, lane, cq, q1); // ghn
+        deal_rows(stage, 1 + q4, lane, cq, q0, u);
+        deal_rows(stage, 1 + q4, lane, cq, q1, dt);
       }
       store_rows(a.gates + 128, p0, 256, w);                            // dz~ (the slot held n: consumed above)
 #pragma unroll
