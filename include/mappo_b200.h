@@ -383,8 +383,8 @@ typedef struct {
   int32_t use_max_grad_norm;
   float bias_correction1;      /* 1 - beta1^t  (t = this step, computed on the host in double) */
   float bias_correction2_sqrt; /* sqrt(1 - beta2^t) */
-  float loss_scale;            /* entropy/value coefficients are already inside the gradients: 1.0 */
-  int32_t reserved;
+  float one_minus_beta1;       /* float(1.0 - beta1) formed in double on the host: the scalar torch hands to lerp_ */
+  float one_minus_beta2;       /* float(1.0 - beta2), the `value` of addcmul_ (1 - 0.999f in fp32 is off by 1.3e-5 relative) */
   double beta1_exact;          /* the betas in double: only read when the step count lives on the device (below) */
   double beta2_exact;
 } mappo_adam_config;
@@ -392,7 +392,7 @@ typedef struct {
 /* From the reduced sums: finish the chain rule through the folded LayerNorm affines, divide by the loss
  * denominator (loss_sum[denominator_slot], or `rows_total` if use_mean != 0), clip the global L2 norm
  * (nn.utils.clip_grad_norm_, r_mappo.py:143-146) and apply torch.optim.Adam's update in place
- * (rMAPPOPolicy.py:31-37).  grad_out (float32 [P], may be NULL) receives the final (unclipped) gradient;
+ * (rMAPPOPolicy.py:31-37).  grad_out (float32 [P], REQUIRED: it is also the kernel's scratch) receives the final (unclipped) gradient;
  * info_out (float32 [4], may be NULL) is ACCUMULATED with {loss, grad_norm, aux (entropy | 0), ratio mean | 0}.
  * step_dev (int64 on the device, may be NULL): optimiser step count kept in HBM so that a captured CUDA graph of the
  * whole iteration replays correctly -- when given, the bias corrections are computed in the kernel from

@@ -33,7 +33,7 @@ class FusedAdam:
         b1, b2 = g["betas"]
         t = self.step_count + 1
         return ops.AdamConfig(g["lr"], b1, b2, g["eps"], g["weight_decay"], float(max_grad_norm),
-                              int(bool(use_max_grad_norm)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), 1.0, 0,
+                              int(bool(use_max_grad_norm)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), 1.0 - b1, 1.0 - b2,
                               float(b1), float(b2))
 
     def state_dict(self):

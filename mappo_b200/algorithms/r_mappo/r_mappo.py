@@ -81,7 +81,10 @@ class R_MAPPO:
                       gsum=torch.empty(Pa + Pc, dtype=torch.float32, device=dev),
                       lsum=torch.empty(8, dtype=torch.float64, device=dev),
                       grad=torch.empty(Pa + Pc, dtype=torch.float32, device=dev))
-            self._ws = {key: ws}        # keep one (largest recent) workspace
+            if ops.GRAPH_PINNED:        # a captured graph replays the pointers of the workspace it was recorded with
+                self._ws[key] = ws
+            else:
+                self._ws = {key: ws}    # keep one (most recent) workspace
         return ws
 
     # ------------------------------------------------------------------ core: one minibatch on device tensors
@@ -134,6 +137,8 @@ class R_MAPPO:
         for k in ("rnn", "rnn_critic"):
             sc = self._seed_scratch.get(k)
             if sc is None or sc.shape != v[k].shape:
+                if sc is not None and ops.GRAPH_PINNED:
+                    ops._RETIRED.append(sc)
                 sc = self._seed_scratch[k] = torch.empty_like(v[k])
             sc.index_copy_(0, first_rows, v[k].index_select(0, seed_rows))
             out[k] = sc

@@ -245,6 +245,12 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
     const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
 #pragma unroll
     for (int i = 0; i < XC; ++i) xv[i] *= rstd;
+  } else {
+    // raw (un-normalised) inputs are the only operands whose magnitude the network does not bound: saturate them at
+    // the fp16 range of the hi halves so that an outlier becomes +-65504 instead of inf -> NaN in the MMA (the fp32
+    // FMA path has no such limit; MPE observations are O(1), see DESIGN.md section 4.1 "operand range")
+#pragma unroll
+    for (int i = 0; i < XC; ++i) xv[i] = fminf(fmaxf(xv[i], -65504.0f), 65504.0f);
   }
   if (ONES) {
 #pragma unroll

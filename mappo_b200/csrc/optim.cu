@@ -131,8 +131,8 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
       float grad = g[e] * clip;
       const float p = params[e];
       if (ad.weight_decay != 0.0f) grad = fmaf(ad.weight_decay, p, grad);
-      const float mm = m[e] + (grad - m[e]) * (1.0f - ad.beta1);                   // exp_avg.lerp_(grad, 1 - beta1)
-      const float vv = v[e] * ad.beta2 + (1.0f - ad.beta2) * grad * grad;          // mul_(beta2).addcmul_(g, g, 1 - beta2)
+      const float mm = m[e] + (grad - m[e]) * ad.one_minus_beta1;                   // exp_avg.lerp_(grad, 1 - beta1)
+      const float vv = v[e] * ad.beta2 + ad.one_minus_beta2 * grad * grad;          // mul_(beta2).addcmul_(g, g, 1 - beta2)
       m[e] = mm; v[e] = vv;
       const float den = sqrtf(vv) / bc2s + ad.eps;
       params[e] = p - step_size * (mm / den);

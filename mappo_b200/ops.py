@@ -151,8 +151,8 @@ class LossConfig(C.Structure):
 class AdamConfig(C.Structure):
     _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
                 ("weight_decay", C.c_float), ("max_grad_norm", C.c_float), ("use_max_grad_norm", C.c_int32),
-                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("loss_scale", C.c_float),
-                ("reserved", C.c_int32), ("beta1_exact", C.c_double), ("beta2_exact", C.c_double)]
+                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("one_minus_beta1", C.c_float),
+                ("one_minus_beta2", C.c_float), ("beta1_exact", C.c_double), ("beta2_exact", C.c_double)]
 
 
 _NC, _LC, _AC = C.POINTER(NetConfig), C.POINTER(LossConfig), C.POINTER(AdamConfig)
@@ -229,6 +229,24 @@ def advantages(returns, value_preds, active_masks, vn_stats, out=None, stats3=No
 
 
 _WORKSPACES = {}
+# A captured CUDA graph holds the raw pointers of the scratch buffers that existed at capture time.  Once a runner has
+# captured one (pin_workspaces()), a buffer that has to grow is REPLACED for eager callers but the old allocation is
+# kept alive here, so later replays never touch freed memory (eval / render / a public ppo_update() may ask for more).
+_RETIRED = []
+GRAPH_PINNED = False
+
+
+def pin_workspaces():
+    global GRAPH_PINNED
+    GRAPH_PINNED = True
+
+
+def _store_workspace(key, new):
+    old = _WORKSPACES.get(key)
+    if old is not None and GRAPH_PINNED:
+        _RETIRED.append(old)
+    _WORKSPACES[key] = new
+    return new
 
 
 def mlp_workspace(cfg, rows, device):
@@ -241,8 +259,7 @@ def mlp_workspace(cfg, rows, device):
         return None
     ws = _WORKSPACES.get(device)
     if ws is None or ws.numel() * 4 < need:
-        ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=device)
-        _WORKSPACES[device] = ws
+        ws = _store_workspace(device, torch.empty((need + 3) // 4, dtype=torch.float32, device=device))
     return ws
 
 
@@ -263,8 +280,7 @@ def rnn_workspace(cfg, positions, update, device):
     key = (device, "rnn")
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() * 4 < need:
-        ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=device)
-        _WORKSPACES[key] = ws
+        ws = _store_workspace(key, torch.empty((need + 3) // 4, dtype=torch.float32, device=device))
     return ws
 
 
@@ -369,8 +385,7 @@ def critic_pack_inputs(cfg, share_obs):
     key = (x.device, "packed")
     buf = _WORKSPACES.get(key)
     if buf is None or buf.numel() < need:
-        buf = torch.empty(need, dtype=torch.uint8, device=x.device)
-        _WORKSPACES[key] = buf
+        buf = _store_workspace(key, torch.empty(need, dtype=torch.uint8, device=x.device))
     ws = mlp_workspace(cfg, x.shape[0], x.device)
     check(L.mappo_critic_pack_inputs(C.byref(cfg), _vp(x), ld, x.shape[0], ptr(buf), ptr(ws), stream_ptr()),
           "critic_pack_inputs")

@@ -25,11 +25,14 @@ class MPERunner(Runner):
     def run(self):
         self.warmup()
         start = time.time()
-        episodes = int(self.num_env_steps) // self.episode_length // self.n_rollout_threads
+        # --n_rollout_threads is PER RANK (each rank owns that many envs, parallel.env_shard): the job advances
+        # world_size x n_rollout_threads envs per step, and --num_env_steps / the lr schedule count those
+        n_global = self.n_rollout_threads * self.trainer.world_size
+        episodes = int(self.num_env_steps) // self.episode_length // n_global
         train_infos = {}
         for episode in range(episodes):
             train_infos = self.run_episode(episode, episodes)
-            total_num_steps = (episode + 1) * self.episode_length * self.n_rollout_threads
+            total_num_steps = (episode + 1) * self.episode_length * n_global
             if episode % self.save_interval == 0 or episode == episodes - 1:
                 self.save()
             if episode % self.log_interval == 0:
@@ -88,6 +91,8 @@ class MPERunner(Runner):
             return self.trainer.train_finish(n)
         if self._graph_state == 1:
             torch.cuda.synchronize()
+            from ... import ops
+            ops.pin_workspaces()                  # scratch buffers the graph records must outlive any later growth
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._graph_updates = self._iteration_on_stream()     # records the launches; host counters advance once
