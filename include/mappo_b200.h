@@ -204,6 +204,21 @@ int mappo_advantages(const float* returns, const float* value_preds, const float
  *   -> mappo_adv_stats_reduce -> [all-reduce] -> mappo_valuenorm_apply: EMA update of vn_stats (float32[3]). */
 int mappo_moments_num_partials(long long count);
 int mappo_moments(const float* x, long long count, double* partials, void* stream);
+
+/* Allocation-free variant of mappo_moments + mappo_adv_stats_reduce: stats3 (double[3] on the device) receives
+ * {sum x, sum x^2 (x^2 rounded to float32 first), count} of x[count], the same numbers the pair above produces.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The per-block partial sums
+ * live in a file-scope `static __device__` array inside the library (148 * 8 rows of 3 doubles = 28,416 bytes, held by
+ * every GPU that loads the library until the process exits); the call performs no cudaMalloc / cudaFree and calls no
+ * allocating routine.  Limit: count <= MAPPO_MOMENTS_STATIC_MAX_COUNT elements, larger counts return
+ * MAPPO_ERR_INVALID_ARG with a message (use mappo_moments with caller scratch).  All calls on one GPU share the
+ * array: calls that overlap on the GPU (different streams, or different host threads / graphs running concurrently)
+ * RACE -- serialise them on one stream.  The array keeps the previous call's contents; nothing in it needs zeroing
+ * (every block overwrites its row and exactly the rows written are read back). */
+#define MAPPO_MOMENTS_STATIC_MAX_COUNT (1LL << 28)
+long long mappo_moments_static_max_count(void);
+int mappo_moments_static(const float* x, long long count, double* stats3, void* stream);
 int mappo_valuenorm_apply(float* vn_stats, const double* stats3, double beta, void* stream);
 /* out = (x - mean) / sqrt(var)  or  out = x * sqrt(var) + mean  (valuenorm.py:56-78), elementwise float32 */
 int mappo_valuenorm_transform(const float* vn_stats, const float* x, float* out, long long count, int denormalize,

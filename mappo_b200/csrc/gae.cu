@@ -250,6 +250,51 @@ extern "C" int mappo_moments(const float* x, long long count, double* partials, 
   return 0;
 }
 
+// ---- allocation-free variant of the batch-moments pair (no counterpart in the reference; see the header) -------------
+// The per-block partial sums that mappo_moments hands back through caller scratch live here instead: a file-scope
+// device array, present once on every GPU that loads the library until the process exits (28,416 bytes).
+constexpr int kStaticMaxPartials = 148 * 8;                       // the launch cap of moments_kernel (grid_for above)
+static __device__ __align__(256) double g_static_partials[kStaticMaxPartials * 3];
+
+// In host code `g_static_partials` is only a stand-in for the symbol: its device address is looked up once per
+// device, with that device current, and it is that pointer the kernels receive.
+static int static_partials_ptr(double** out) {
+  constexpr int kMaxDev = 64;
+  static double* cache[kMaxDev] = {nullptr};
+  int dev = 0;
+  MAPPO_CUDA(cudaGetDevice(&dev));
+  MAPPO_REQUIRE(dev >= 0 && dev < kMaxDev, "moments_static: device ordinal %d out of range", dev);
+  if (cache[dev] == nullptr) {
+    double* p = nullptr;
+    MAPPO_CUDA(cudaGetSymbolAddress((void**)&p, g_static_partials));
+    MAPPO_REQUIRE(p != nullptr, "moments_static: cudaGetSymbolAddress returned a null pointer");
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return 0;
+}
+
+extern "C" long long mappo_moments_static_max_count(void) { return MAPPO_MOMENTS_STATIC_MAX_COUNT; }
+
+extern "C" int mappo_moments_static(const float* x, long long count, double* stats3, void* stream) {
+  MAPPO_REQUIRE(x && stats3 && count > 0, "moments_static: bad arguments");
+  MAPPO_REQUIRE(count <= MAPPO_MOMENTS_STATIC_MAX_COUNT,
+                "moments_static: count %lld exceeds the maximum of %lld elements this allocation-free entry point "
+                "accepts (use mappo_moments with caller scratch)", count, (long long)MAPPO_MOMENTS_STATIC_MAX_COUNT);
+  const int nparts = mappo_moments_num_partials(count);
+  MAPPO_REQUIRE(nparts <= kStaticMaxPartials, "moments_static: %d partial rows exceed the static scratch (%d)", nparts,
+                kStaticMaxPartials);
+  double* scratch = nullptr;
+  if (int rc = static_partials_ptr(&scratch)) return rc;
+  // nothing has to start at zero: every launched block overwrites its own row, and the reduction reads exactly the
+  // rows this launch wrote (the array keeps the previous call's contents beyond them)
+  moments_kernel<<<nparts, kRedThreads, 0, (cudaStream_t)stream>>>(x, count, scratch);
+  MAPPO_CHECK_LAUNCH("moments_kernel (static scratch)");
+  stats_reduce_kernel<<<1, kRedThreads, 0, (cudaStream_t)stream>>>(scratch, nparts, stats3);
+  MAPPO_CHECK_LAUNCH("stats_reduce_kernel (static scratch)");
+  return 0;
+}
+
 extern "C" int mappo_advantages(const float* returns, const float* value_preds, const float* active_masks,
                                 const float* vn_stats, long long count, float* advantages_raw, double* partials,
                                 void* stream) {
