@@ -14,58 +14,71 @@ import numpy as np
 REFERENCE_ROOT = "/root/reference"
 
 
+# The shim classes live at MODULE level and carry `__module__ = "gym..."`: SubprocVecEnv's workers send the spaces back
+# through a Pipe (env_wrappers.py:171-172, 252-253), i.e. they are pickled by reference as `gym.spaces.Box` and must be
+# importable under that name in both processes (function-local classes cannot be pickled: the worker dies and the
+# parent blocks in recv() forever).
+class Env:
+    metadata = {}
+
+    def close(self):
+        pass
+
+
+class Space:
+    def __init__(self, shape=None, dtype=None):
+        self.shape = None if shape is None else tuple(shape)
+        self.dtype = None if dtype is None else np.dtype(dtype)
+
+
+class Discrete(Space):
+    def __init__(self, n):
+        self.n = int(n)
+        super().__init__((), np.int64)
+
+    def __repr__(self):
+        return "Discrete(%d)" % self.n
+
+
+class Box(Space):
+    def __init__(self, low, high, shape=None, dtype=np.float32):
+        if shape is None:
+            shape = np.shape(low)
+        super().__init__(shape, dtype)
+        self.low = np.full(self.shape, low, dtype=dtype)
+        self.high = np.full(self.shape, high, dtype=dtype)
+
+    def __repr__(self):
+        return "Box%s" % (self.shape,)
+
+
+class Tuple(Space):
+    def __init__(self, spaces):
+        self.spaces = tuple(spaces)
+        super().__init__(None, None)
+
+    def __getitem__(self, i):
+        return self.spaces[i]
+
+
+class EnvSpec:
+    def __init__(self, *a, **k):
+        pass
+
+
+Env.__module__ = "gym"
+for _c in (Space, Discrete, Box, Tuple):
+    _c.__module__ = "gym.spaces"
+EnvSpec.__module__ = "gym.envs.registration"
+
+
 def _gym_shim():
     gym = types.ModuleType("gym")
-
-    class Env:
-        metadata = {}
-
-        def close(self):
-            pass
-
-    class Space:
-        def __init__(self, shape=None, dtype=None):
-            self.shape = None if shape is None else tuple(shape)
-            self.dtype = None if dtype is None else np.dtype(dtype)
-
-    class Discrete(Space):
-        def __init__(self, n):
-            self.n = int(n)
-            super().__init__((), np.int64)
-
-        def __repr__(self):
-            return "Discrete(%d)" % self.n
-
-    class Box(Space):
-        def __init__(self, low, high, shape=None, dtype=np.float32):
-            if shape is None:
-                shape = np.shape(low)
-            super().__init__(shape, dtype)
-            self.low = np.full(self.shape, low, dtype=dtype)
-            self.high = np.full(self.shape, high, dtype=dtype)
-
-        def __repr__(self):
-            return "Box%s" % (self.shape,)
-
-    class Tuple(Space):
-        def __init__(self, spaces):
-            self.spaces = tuple(spaces)
-            super().__init__(None, None)
-
-        def __getitem__(self, i):
-            return self.spaces[i]
-
     spaces = types.ModuleType("gym.spaces")
     spaces.Space, spaces.Discrete, spaces.Box, spaces.Tuple = Space, Discrete, Box, Tuple
     gym.Env, gym.Space, gym.spaces = Env, Space, spaces
-
     envs = types.ModuleType("gym.envs")
     registration = types.ModuleType("gym.envs.registration")
-
-    class EnvSpec:
-        def __init__(self, *a, **k):
-            pass
-
     registration.EnvSpec = EnvSpec
     envs.registration = registration
     gym.envs = envs
@@ -107,12 +120,14 @@ def install(reference_root=REFERENCE_ROOT):
         sys.modules["tensorboardX"] = tbx
     if reference_root not in sys.path:
         sys.path.insert(0, reference_root)
+    global REFERENCE_ROOT
+    REFERENCE_ROOT = reference_root
 
 
 def reference_args(argv):
     """Build the reference's `all_args` namespace exactly as train_mpe.py does
     (onpolicy/config.py:4, scripts/train/train_mpe.py:52-80)."""
-    install()
+    install(REFERENCE_ROOT)
     from onpolicy.config import get_config
 
     parser = get_config()
