@@ -1,8 +1,10 @@
 """Generate the golden fixtures under tests/golden/ by RUNNING THE UNMODIFIED REFERENCE
 (/root/reference/onpolicy, imported through tests/golden/ref_shims.py).
 
-Run in the build container only (the GPU box has no /root/reference):
-    python tests/golden/make_golden.py [env] [gae] [gen] [ppo] [vnorm]
+Run in the build container (the GPU box has no /root/reference):
+    python tests/golden/make_golden.py [env] [gae] [gen] [ppo] [vnorm] [runner]
+`popart` is the one part recorded ON THE GPU BOX (the reference's PopArt only runs on cuda, popart.py:21-27):
+    MAPPO_REF_ROOT=baseline/_ref python tests/golden/make_golden.py popart      (writes gpurun_out/ppo_popart*_cuda.npz)
 The reference ships no tests and no golden vectors, so these fixtures -- outputs of
 the reference itself on seeded inputs -- are what pins the oracle (tests/test_oracle_*.py, CPU) and,
 through it and directly, the CUDA path (tests/test_gpu_*.py).
@@ -19,7 +21,10 @@ sys.path.insert(0, HERE)
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 import ref_shims  # noqa: E402
 
-ref_shims.install()
+# MAPPO_REF_ROOT: where the unmodified reference lives -- /root/reference in the build container, baseline/_ref (the
+# git-ignored copy tools/install_ref.sh makes; it travels with the snapshot) on the GPU box
+REF_ROOT = os.environ.get("MAPPO_REF_ROOT", ref_shims.REFERENCE_ROOT)
+ref_shims.install(REF_ROOT)
 
 
 def ref_args(scenario, M, L, algo, extra=""):
@@ -307,7 +312,16 @@ def _sd_np(module, prefix):
             if "fc_h" not in k or prefix.endswith("0.")}
 
 
-def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_updates=2):
+def _np(t):
+    return t.detach().cpu().numpy().copy()
+
+
+def _popart_state(v_out):
+    """PopArt's six tensors (popart.py:21-27).  On cuda they are plain attributes, not registered parameters."""
+    return {k: _np(getattr(v_out, k)) for k in ("weight", "bias", "mean", "mean_sq", "debiasing_term", "stddev")}
+
+
+def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_updates=2, device="cpu"):
     """Run the reference's R_MAPPO.ppo_update `n_updates` times on one crafted minibatch and record everything:
     initial weights, the sample, the six return values, PRE-clip gradients, post-step weights and Adam state."""
     from onpolicy.envs.mpe.MPE_env import MPEEnv
@@ -318,8 +332,10 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
     agent = 0 if scenario != "simple_speaker_listener" else 1
     obs_sp, sh_sp, act_sp = env.observation_space[agent], env.share_observation_space[agent], env.action_space[agent]
     torch.manual_seed(seed)
-    policy = R_MAPPOPolicy(args, obs_sp, sh_sp, act_sp)
-    trainer = R_MAPPO(args, policy)
+    device = torch.device(device)
+    policy = R_MAPPOPolicy(args, obs_sp, sh_sp, act_sp, device=device)
+    trainer = R_MAPPO(args, policy, device=device)
+    popart = bool(args.use_popart)
     # make LayerNorm affines and biases non-trivial so the folded-affine chain rule is exercised
     g = torch.Generator().manual_seed(seed + 1)
     with torch.no_grad():
@@ -328,9 +344,9 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
                 if "fc_h" in name:
                     continue
                 if prm.dim() == 1:
-                    prm.add_(torch.randn(prm.shape, generator=g) * 0.2)
+                    prm.add_((torch.randn(prm.shape, generator=g) * 0.2).to(prm.device))
                 elif "action_out" in name or "v_out" in name:
-                    prm.add_(torch.randn(prm.shape, generator=g) * 0.3)
+                    prm.add_((torch.randn(prm.shape, generator=g) * 0.3).to(prm.device))
     D, S, H = obs_sp.shape[0], sh_sp.shape[0], args.hidden_size
     rng = np.random.RandomState(seed)
     recurrent = bool(args.use_recurrent_policy)
@@ -351,10 +367,10 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
     with torch.no_grad():
         policy.actor.eval(); policy.critic.eval()
         if recurrent:   # evaluate on the chunked layout to get consistent log-probs
-            feats_a = policy.actor.base(torch.from_numpy(obs))
-            feats_a, _ = policy.actor.rnn(feats_a, torch.from_numpy(rnn_a), torch.from_numpy(masks))
+            feats_a = policy.actor.base(torch.from_numpy(obs).to(device))
+            feats_a, _ = policy.actor.rnn(feats_a, torch.from_numpy(rnn_a).to(device), torch.from_numpy(masks).to(device))
             if act_sp.__class__.__name__ == "Discrete":
-                dist = [policy.actor.act.action_out(feats_a, torch.from_numpy(avail))]
+                dist = [policy.actor.act.action_out(feats_a, torch.from_numpy(avail).to(device))]
             else:
                 dist = [ao(feats_a) for ao in policy.actor.act.action_outs]
             actions = torch.cat([d.sample() for d in dist], -1)
@@ -362,19 +378,21 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
             values, _ = policy.critic(share_obs, rnn_c, masks)
         else:
             values, actions, logp, _, _ = policy.get_actions(share_obs, obs, rnn_a, rnn_c, masks, avail)
+    actions, logp, values = actions.cpu(), logp.cpu(), values.cpu()
     actions = actions.numpy().astype(np.float32)
     old_logp = (logp.numpy() + rng.normal(0, 0.15, logp.shape)).astype(np.float32)
     adv = rng.standard_normal((B, 1)).astype(np.float32)
     value_preds = (values.numpy() + rng.normal(0, 0.25, (B, 1))).astype(np.float32)
-    if args.use_valuenorm:
+    if args.use_valuenorm or popart:
         returns = rng.normal(-5, 3, (B, 1)).astype(np.float32)
-        trainer.value_normalizer.update(torch.from_numpy(rng.normal(-4, 2, (300, 1)).astype(np.float32)))
+        if not popart:
+            trainer.value_normalizer.update(torch.from_numpy(rng.normal(-4, 2, (300, 1)).astype(np.float32)))
     else:
         returns = (values.numpy() + rng.normal(0, 1.0, (B, 1))).astype(np.float32)
     sample = (share_obs, obs, rnn_a, rnn_c, actions, value_preds, returns, masks, active, old_logp, adv, avail)
     out = dict(B=B, D=D, S=S, recurrent=int(recurrent), chunk=Lc)
     out.update({"args_" + k: np.asarray(getattr(args, k)) for k in (
-        "use_ReLU", "use_feature_normalization", "use_valuenorm", "use_huber_loss", "use_clipped_value_loss",
+        "use_popart", "use_ReLU", "use_feature_normalization", "use_valuenorm", "use_huber_loss", "use_clipped_value_loss",
         "use_policy_active_masks", "use_value_active_masks", "use_max_grad_norm", "max_grad_norm", "clip_param",
         "entropy_coef", "value_loss_coef", "huber_delta", "lr", "critic_lr", "opti_eps", "weight_decay", "hidden_size",
         "layer_N", "gain")})
@@ -387,6 +405,11 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
     out.update(_sd_np(policy.critic, "critic0."))
     if args.use_valuenorm:
         out["vn0"] = vn_stats(trainer.value_normalizer)
+    if popart:
+        out["critic_state_dict_keys"] = np.array(sorted(policy.critic.state_dict().keys()))
+        out["critic_optimizer_numel"] = sum(p.numel() for g in policy.critic_optimizer.param_groups for p in g["params"])
+        out.update({"popart0." + k: v for k, v in _popart_state(policy.critic.v_out).items()})
+        out["values0"] = values.numpy()
     trainer.prep_training()
     import torch.nn.utils as U
     real_clip = U.clip_grad_norm_
@@ -409,16 +432,22 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
         for net, nm, grads in ((policy.actor, "actor", pre[0]), (policy.critic, "critic", pre[1])):
             for (pname, _), gr in zip(net.named_parameters(), grads):
                 if gr is not None:
-                    out[tag + nm + "_grad." + pname] = gr.numpy()
+                    out[tag + nm + "_grad." + pname] = _np(gr)
             out.update(_sd_np(net, tag + nm + "."))
         for opt, nm, net in ((policy.actor_optimizer, "actor", policy.actor), (policy.critic_optimizer, "critic", policy.critic)):
             for (pname, prm) in net.named_parameters():
                 st = opt.state.get(prm, None)
                 if st:
-                    out[tag + nm + "_exp_avg." + pname] = st["exp_avg"].numpy().copy()
-                    out[tag + nm + "_exp_avg_sq." + pname] = st["exp_avg_sq"].numpy().copy()
+                    out[tag + nm + "_exp_avg." + pname] = _np(st["exp_avg"])
+                    out[tag + nm + "_exp_avg_sq." + pname] = _np(st["exp_avg_sq"])
         if args.use_valuenorm:
             out[tag + "vn"] = vn_stats(trainer.value_normalizer)
+        if popart:
+            out.update({tag + "popart." + k: v for k, v in _popart_state(policy.critic.v_out).items()})
+            with torch.no_grad():
+                v_after, _ = policy.critic(share_obs, rnn_c, masks)
+            out[tag + "values_after"] = _np(v_after)
+            out[tag + "denorm_value_preds"] = np.asarray(trainer.value_normalizer.denormalize(value_preds))
     return out
 
 
@@ -449,9 +478,160 @@ def gen_ppo():
               "cgn", fx["u0_critic_grad_norm"])
 
 
-PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen, "ppo": gen_ppo}
+# ------------------------------------------------------------------ PopArt (cuda only)
+def gen_popart():
+    """--use_popart.  PopArt.__init__ (popart.py:21-27) builds its tensors as nn.Parameter(...).to(dtype, device): on
+    the reference's default cuda:0 (train_mpe.py:86-96) that `.to()` returns a PLAIN tensor, so weight / bias / mean /
+    mean_sq / debiasing_term / stddev are ordinary attributes: not in parameters(), not in state_dict(), never seen by
+    the optimiser or by clip_grad_norm_, and only PopArt.update's rescale (popart.py:69-70) moves weight / bias.  On
+    CPU `.to()` returns the registered Parameter itself and update() raises TypeError at its first assignment.  So
+    this fixture can only be recorded where a GPU is: run it on the B200 box against baseline/_ref."""
+    assert torch.cuda.is_available(), "the reference's PopArt only runs on cuda (see docstring)"
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(HERE)), "gpurun_out")
+    os.makedirs(out_dir, exist_ok=True)
+    for tag, kw in (("popart_cuda", dict(scenario="simple_spread", M=3, L=3, algo="mappo",
+                                         extra="--use_ReLU --lr 7e-4 --critic_lr 7e-4 --use_popart --use_valuenorm",
+                                         B=700, seed=13, n_updates=3)),
+                    ("popart_mse_cuda", dict(scenario="simple_spread", M=3, L=3, algo="mappo",
+                                             extra="--use_popart --use_valuenorm --use_huber_loss --max_grad_norm 0.5",
+                                             B=300, seed=15, n_updates=2))):
+        fx = make_ppo_fixture(device="cuda:0", **kw)
+        path = os.path.join(out_dir, "ppo_%s.npz" % tag)
+        np.savez_compressed(path, torch_version=str(torch.__version__), **fx)
+        print("wrote", path, os.path.getsize(path), "value_loss", fx["u0_value_loss"], "cgn", fx["u0_critic_grad_norm"],
+              "state_dict keys with v_out:", [k for k in fx["critic_state_dict_keys"] if "v_out" in k],
+              "optimizer numel", fx["critic_optimizer_numel"])
+
+
+# ------------------------------------------------------------------ whole-runner fixtures (two consecutive iterations)
+def make_runner_fixture(scenario, M, L, algo, extra, N=8, iters=2, seed=1):
+    """Run the reference's OWN MPERunner.run() (runner/shared/mpe_runner.py:16-79) for `iters` iterations on a
+    DummyVecEnv of N reference envs and record, by wrapping (never editing) its methods: the world state behind every
+    observation (warm-up reset, every auto-reset), the sampled actions, the buffer after each rollout / compute, the
+    normalised advantages train() forms (r_mappo.py:174-182, restated verbatim on the same buffer), the six train_info
+    scalars, and the weights / ValueNorm state after each iteration."""
+    from pathlib import Path
+    import tempfile
+    from onpolicy.envs.mpe.MPE_env import MPEEnv
+    from onpolicy.envs.env_wrappers import DummyVecEnv
+    from onpolicy.runner.shared.mpe_runner import MPERunner
+    T = 25
+    args = ref_args(scenario, M, L, algo, "--n_rollout_threads %d --num_env_steps %d --cuda --n_training_threads 1 "
+                    "--log_interval 1000 --save_interval 1000 %s" % (N, iters * T * N, extra))
+    args.n_rollout_threads = N
+    torch.manual_seed(seed); np.random.seed(seed)
+
+    def env_fn(rank):
+        def init():
+            e = MPEEnv(args)
+            e.seed(seed + rank * 1000)
+            return e
+        return init
+    envs = DummyVecEnv([env_fn(i) for i in range(N)])
+    run_dir = Path(tempfile.mkdtemp(prefix="mappo_ref_run_"))
+    runner = MPERunner({"all_args": args, "envs": envs, "eval_envs": None, "num_agents": M,
+                        "device": torch.device("cpu"), "run_dir": run_dir})
+    pol, tr, buf = runner.policy, runner.trainer, runner.buffer
+    out = dict(N=N, M=M, L=L, T=T, iters=iters, scenario=scenario, algo=algo,
+               recurrent=int(bool(args.use_recurrent_policy)), chunk=args.data_chunk_length)
+    out.update({"args_" + k: np.asarray(getattr(args, k)) for k in (
+        "use_ReLU", "use_feature_normalization", "use_valuenorm", "use_huber_loss", "use_clipped_value_loss",
+        "use_policy_active_masks", "use_value_active_masks", "use_max_grad_norm", "max_grad_norm", "clip_param",
+        "entropy_coef", "value_loss_coef", "huber_delta", "lr", "critic_lr", "opti_eps", "weight_decay", "hidden_size",
+        "layer_N", "recurrent_N", "gain", "ppo_epoch", "num_mini_batch", "gamma", "gae_lambda", "use_gae",
+        "use_proper_time_limits", "use_centralized_V")})
+    out.update(_sd_np(pol.actor, "actor0."))
+    out.update(_sd_np(pol.critic, "critic0."))
+    states = lambda: [world_state(e) for e in envs.envs]
+    rec = dict(step_states=[], actions_env=[], obs=[], rewards=[], dones=[])
+    it = {"k": 0}
+    real_reset, real_step, real_compute, real_train = envs.reset, envs.step, runner.compute, runner.train
+
+    def reset_spy():
+        o = real_reset()
+        st = states()
+        out["warm_p_pos"] = np.array([x[0] for x in st]); out["warm_lm_pos"] = np.array([x[2] for x in st])
+        out["warm_goal"] = np.array([x[4] for x in st]); out["warm_obs"] = np.array(o)
+        return o
+
+    def step_spy(actions_env):
+        r = real_step(actions_env)
+        st = states()                                          # after any auto-reset: what the returned obs shows
+        rec["step_states"].append((np.array([x[0] for x in st]), np.array([x[1] for x in st]),
+                                   np.array([x[2] for x in st]), np.array([x[4] for x in st])))
+        rec["actions_env"].append(np.array(actions_env)); rec["obs"].append(np.array(r[0]))
+        rec["rewards"].append(np.array(r[1])); rec["dones"].append(np.array(r[2]))
+        return r
+
+    def compute_spy():
+        k = it["k"]
+        for name in ("obs", "share_obs", "masks", "rewards", "actions", "action_log_probs", "rnn_states",
+                     "rnn_states_critic", "active_masks", "bad_masks"):
+            out["it%d_buf_%s" % (k, name)] = getattr(buf, name).copy()
+        out["it%d_value_preds_rollout" % k] = buf.value_preds.copy()
+        real_compute()
+        out["it%d_returns" % k] = buf.returns.copy()
+        out["it%d_value_preds" % k] = buf.value_preds.copy()
+
+    def train_spy():
+        k = it["k"]
+        vn = tr.value_normalizer
+        if vn is not None:
+            out["it%d_vn_before" % k] = vn_stats(vn)
+            adv = buf.returns[:-1] - vn.denormalize(buf.value_preds[:-1])
+        else:
+            adv = buf.returns[:-1] - buf.value_preds[:-1]
+        cp = adv.copy(); cp[buf.active_masks[:-1] == 0.0] = np.nan          # r_mappo.py:177-181, verbatim
+        out["it%d_adv" % k] = (adv - np.nanmean(cp)) / (np.nanstd(cp) + 1e-5)
+        info = real_train()
+        for name, v in info.items():
+            out["it%d_info_%s" % (k, name)] = float(v)
+        out.update(_sd_np(pol.actor, "it%d_actor." % k))
+        out.update(_sd_np(pol.critic, "it%d_critic." % k))
+        if vn is not None:
+            out["it%d_vn_after" % k] = vn_stats(vn)
+        for name in ("obs", "masks", "rnn_states", "rnn_states_critic"):      # after_update: slot 0 of the next rollout
+            out["it%d_after_%s0" % (k, name)] = getattr(buf, name)[0].copy()
+        for key, arr in rec.items():
+            if key == "step_states":
+                out["it%d_p_pos" % k] = np.array([x[0] for x in arr]); out["it%d_p_vel" % k] = np.array([x[1] for x in arr])
+                out["it%d_lm_pos" % k] = np.array([x[2] for x in arr]); out["it%d_goal" % k] = np.array([x[3] for x in arr])
+            else:
+                out["it%d_%s" % (k, key)] = np.array(arr)
+            arr.clear()
+        it["k"] += 1
+        return info
+
+    envs.reset, envs.step, runner.compute, runner.train = reset_spy, step_spy, compute_spy, train_spy
+    runner.run()                                               # the reference's own loop
+    assert it["k"] == iters
+    return out
+
+
+RUNNER_CASES = {
+    # C1's flags (train_mpe_spread.sh:4-17 with the MLP policy), 8 envs, 2 epochs
+    "spread_mappo": dict(scenario="simple_spread", M=3, L=3, algo="mappo",
+                         extra="--use_ReLU --gain 0.01 --lr 7e-4 --critic_lr 7e-4 --ppo_epoch 2 --num_mini_batch 1"),
+    # C4's flags (train_mpe_reference.sh): shared GRU, chunks of 10
+    "reference_rmappo": dict(scenario="simple_reference", M=2, L=3, algo="rmappo",
+                             extra="--use_ReLU --gain 0.01 --lr 7e-4 --critic_lr 7e-4 --ppo_epoch 2 --num_mini_batch 1 "
+                                   "--data_chunk_length 10"),
+}
+
+
+def gen_runner():
+    for tag, kw in RUNNER_CASES.items():
+        fx = make_runner_fixture(**kw)
+        path = os.path.join(HERE, "runner_%s.npz" % tag)
+        np.savez_compressed(path, **fx)
+        print("wrote", path, os.path.getsize(path), {k[9:]: round(float(v), 6) for k, v in fx.items() if k.startswith("it1_info_")})
+
+
+PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen, "ppo": gen_ppo, "runner": gen_runner,
+         "popart": gen_popart}
+DEFAULT_PARTS = ["env", "vnorm", "gae", "gen", "ppo", "runner"]
 
 if __name__ == "__main__":
-    todo = sys.argv[1:] or list(PARTS)
+    todo = sys.argv[1:] or DEFAULT_PARTS
     for p in todo:
         PARTS[p]()
