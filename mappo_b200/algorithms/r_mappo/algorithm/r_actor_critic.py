@@ -186,9 +186,20 @@ class R_Actor(_FlatNet):
         return actions.long(), logp, rnn_states
 
     def forward_into(self, obs, actions_out, logp_out, available_actions=None, deterministic=False, step=None,
-                     row_offset=0, rnn_in=None, masks=None, rnn_out=None):
+                     row_offset=0, rnn_in=None, masks=None, rnn_out=None, given_actions=None):
         """Hot-path entry: writes float32 action ids and log-probs (and, recurrent, the next rnn state) straight into
-        buffer slots."""
+        buffer slots.  given_actions (float32 ids, same shape as actions_out): evaluate those instead of sampling
+        (replay of a recorded rollout); they are copied into actions_out."""
+        if given_actions is not None:
+            if actions_out.data_ptr() != given_actions.data_ptr():
+                actions_out.copy_(given_actions.reshape(actions_out.shape))
+            self._calls += 1
+            ga = actions_out.reshape(obs.shape[0], -1)
+            if self._recurrent:
+                ops.actor_forward_rnn(self.cfg, self.flat, obs, rnn_in, masks, rnn_out, None, logp_out, given_actions=ga)
+            else:
+                ops.actor_forward(self.cfg, self.flat, obs, None, logp_out, given_actions=ga)
+            return
         dev_step = self.step_dev if step is None else None
         if step is None:
             step = self._calls

@@ -105,12 +105,17 @@ class MPERunner(Runner):
         self._graph.replay()
         return self.trainer.train_finish(self._graph_updates)
 
-    def _rollout(self):
+    def _rollout(self, given_actions=None, reset_states=None):
+        """given_actions [T, N, M, heads] (device float32 ids) / reset_states {step: state dict in the reference's per-env
+        layout}: replay a recorded rollout -- the recorded actions are evaluated instead of sampled and the recorded
+        reset states are installed where the envs auto-reset (tests/test_gpu_runner.py: the reference's own runs)."""
         for step in range(self.episode_length):
-            values, actions, action_log_probs, rnn_states, rnn_states_critic, actions_env = self.collect(step)
+            ga = None if given_actions is None else given_actions[step]
+            values, actions, action_log_probs, rnn_states, rnn_states_critic, actions_env = self.collect(step, ga)
+            rs = None if reset_states is None else reset_states.get(step)
             obs, rewards, masks = self.envs.step_ids(actions_env, out_obs=self.buffer.obs[step + 1],
                                                      out_rewards=self.buffer.rewards[step],
-                                                     out_masks=self.buffer.masks[step + 1])
+                                                     out_masks=self.buffer.masks[step + 1], reset_state=rs)
             data = obs, rewards, masks, None, values, actions, action_log_probs, rnn_states, rnn_states_critic
             self.insert(data)
 
@@ -122,7 +127,7 @@ class MPERunner(Runner):
         self.envs.reset(out_obs=b.obs[0])
 
     @torch.no_grad()
-    def collect(self, step):
+    def collect(self, step, given_actions=None):
         """mpe_runner.py:95-123 with outputs written in place.  `actions_env` is the action-id slot itself: the env
         kernel decodes ids, so the one-hot conversion (:110-121) disappears."""
         b = self.buffer
@@ -133,7 +138,7 @@ class MPERunner(Runner):
             # rnn.py:24-28: h = GRU(x, h * mask); the new states go straight into slot step + 1
             pol.actor.forward_into(b.obs[step].view(N * M, -1), b.actions[step], b.action_log_probs[step],
                                    row_offset=self.envs._cfg.env_id_offset * M, rnn_in=b.rnn_states[step],
-                                   masks=b.masks[step], rnn_out=b.rnn_states[step + 1])
+                                   masks=b.masks[step], rnn_out=b.rnn_states[step + 1], given_actions=given_actions)
             uniq = b.share_obs_unique()
             if self.use_centralized_V and uniq is not None:
                 pol.critic.forward_into(uniq[step], b.value_preds[step], rnn_in=b.rnn_states_critic[step],
@@ -145,7 +150,7 @@ class MPERunner(Runner):
             return (b.value_preds[step], b.actions[step], b.action_log_probs[step], b.rnn_states[step + 1],
                     b.rnn_states_critic[step + 1], b.actions[step])
         pol.actor.forward_into(b.obs[step].view(N * M, -1), b.actions[step], b.action_log_probs[step],
-                               row_offset=self.envs._cfg.env_id_offset * M)
+                               row_offset=self.envs._cfg.env_id_offset * M, given_actions=given_actions)
         if self.use_centralized_V:
             pol.critic.forward_into(b.share_obs_unique()[step], b.value_preds[step], group=M)
         else:

@@ -81,7 +81,8 @@ class OracleMAPPO:
         self.obs[0] = self._stack_obs(self.env.reset(state))
 
     @torch.no_grad()
-    def collect(self, step):
+    def collect(self, step, given_actions=None):
+        """given_actions [N, M, heads]: evaluate those instead of sampling (replay of a recorded reference rollout)"""
         a = self.a
         N, M = self.N, self.M
         obs = self.obs[step].reshape(N * M, -1)
@@ -91,17 +92,23 @@ class OracleMAPPO:
         mk = self.masks[step].reshape(N * M, 1)
         feats, h = op.actor_features(self.actor, obs, z, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
         logits = op.actor_logits(self.actor, feats, None)
-        acts, lps, _ = op.act_forward(logits, False, seed=self.sample_seed, step=self.calls,
-                                      row_offset=self.row_offset)
+        if given_actions is not None:
+            acts = torch.as_tensor(np.asarray(given_actions).reshape(N * M, -1)).long()
+            lps, _ = op.evaluate_actions(logits, acts)
+        else:
+            acts, lps, _ = op.act_forward(logits, False, seed=self.sample_seed, step=self.calls,
+                                          row_offset=self.row_offset)
         self.calls += 1
         values, hc = op.critic_values(self.critic, sh, zc, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
         self._h = (h.numpy().reshape(N, M, 1, -1), hc.numpy().reshape(N, M, 1, -1))
         return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, -1), lps.numpy().reshape(N, M, -1)
 
-    def rollout(self):
+    def rollout(self, given_actions=None, reset_states=None):
+        """given_actions [T, N, M, heads] / reset_states {step: state dict}: replay a recorded rollout"""
         for step in range(self.T):
-            values, actions, logp = self.collect(step)
-            obs, rewards, dones, _ = self.env.step(actions)
+            values, actions, logp = self.collect(step, None if given_actions is None else given_actions[step])
+            obs, rewards, dones, _ = self.env.step(actions, reset_state=None if reset_states is None
+                                                   else reset_states.get(step))
             self.obs[step + 1] = self._stack_obs(obs)
             self.actions[step] = actions
             self.action_log_probs[step] = logp
