@@ -143,21 +143,49 @@ def cpu_iteration_rate(n_envs, steps, warmup, threads):
     return n_envs * T_EP * M_AGENTS * steps / dt, dt / steps
 
 
+def reference_rate(n_envs, steps, warmup, threads):
+    """agent-steps/s of the UNMODIFIED reference (baseline/_ref through baseline/ref_harness.py): its own SubprocVecEnv
+    (one worker process per env) + MPERunner + R_MAPPO on torch CPU, flags of train_mpe_spread.sh with the MLP policy."""
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import ref_harness
+    if not ref_harness.available():
+        return None
+    fl = ref_harness.c1_flags(n_envs, threads, scenario=SCENARIO, num_agents=M_AGENTS, num_landmarks=N_LANDMARKS,
+                              algo=ALGO, ppo_epoch=PPO_EPOCH)
+    return ref_harness.time_reference(fl, steps, warmup)
+
+
 def run_reference(ns):
-    """--impl reference: the CPU path alone, rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores, rank 0 only.
+    The reference is the unmodified `onpolicy` package from baseline/_ref when it travelled with the snapshot (kind
+    "reference"); otherwise the CPU port oracle/iteration.py (kind "port")."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     cores = len(os.sched_getaffinity(0))
-    n_envs = ns.cpu_envs
-    val, sec = cpu_iteration_rate(n_envs, ns.steps, ns.warmup, cores)
-    sample = "%d envs x %d iterations (each a full rollout+GAE+%d-epoch update) of the same workload" % (
-        n_envs, ns.steps, PPO_EPOCH)
+    threads = cores if ns.ref_threads <= 0 else ns.ref_threads
+    r = None if ns.ref_kind == "port" else reference_rate(ns.ref_envs, ns.steps, ns.warmup, threads)
+    if r is not None:
+        val, sec, n_envs, kind = r["value"], r["sec_per_iter"], r["n_envs"], "reference"
+        sample = ("unmodified onpolicy (baseline/_ref): SubprocVecEnv x %d worker processes + MPERunner + R_MAPPO on torch "
+                  "CPU (%d training threads), %d timed iterations (each a full rollout+GAE+%d-epoch update); median "
+                  "iteration %.3f s = collect %.3f + env step %.3f + insert %.3f + compute %.3f + train %.3f; the reference "
+                  "cannot spawn 65,536 env processes, so its own configuration size (C1) is the sample and agent-steps/s "
+                  "is size-normalised" % (n_envs, threads, ns.steps, PPO_EPOCH, r["sec_median"], r["split"]["collect"],
+                                          r["split"]["env_step"], r["split"]["insert"], r["split"]["compute"],
+                                          r["split"]["train"]))
+    else:
+        n_envs, kind = ns.cpu_envs, "port"
+        val, sec = cpu_iteration_rate(n_envs, ns.steps, ns.warmup, cores)
+        sample = "%d envs x %d iterations (each a full rollout+GAE+%d-epoch update) of the same workload, oracle/iteration.py" % (
+            n_envs, ns.steps, PPO_EPOCH)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": ns.gpus, "steps": ns.steps,
         "warmup": ns.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(ns.envs, ns.gpus), "cpu_sample_envs": n_envs},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "vs_baseline": None, "dtype": "f32 (policy, buffer), f64 (env physics)", "data": "synthetic",
+        "config": {"workload": workload_name(ns.envs, ns.gpus), "cpu_sample_envs": n_envs,
+                   "same_config_note": "same scenario, policy, T, ppo_epoch and minibatching as the GPU arm; envs per "
+                                       "iteration bounded to what the CPU implementation can run (metric is per agent-step)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -381,6 +409,14 @@ def main():
                     help="timed iterations of the cpu_baseline leg (about 10 s on 16 cores)")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
+    ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=128,
+                    help="SubprocVecEnv workers of the unmodified reference (C1: 128, train_mpe_spread.sh)")
+    ap.add_argument("--ref-threads", dest="ref_threads", type=int, default=0,
+                    help="n_training_threads of the reference arm (0 = all host cores; the reference's default is 1)")
+    ap.add_argument("--ref-kind", dest="ref_kind", default="auto", choices=["auto", "port"],
+                    help="auto: the unmodified reference from baseline/_ref when present, else the port")
+    ap.add_argument("--ref-iters", dest="ref_iters", type=int, default=5,
+                    help="timed iterations of the unmodified reference in the cpu_baseline leg of the GPU arm")
     ns = ap.parse_args()
     set_workload(ns.agents, ns.config)
     if ns.config in ("c3", "c3r", "c4") and ns.envs == 65536:
