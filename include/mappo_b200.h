@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define MAPPO_B200_ABI_VERSION 5
+#define MAPPO_B200_ABI_VERSION 6
 
 typedef enum {
   MAPPO_OK = 0,
@@ -203,6 +203,12 @@ int mappo_advantages(const float* returns, const float* value_preds, const float
  *   moments: per-block partial {sum x, sum x^2, n} of `x[count]` (optionally only where weights != 0)
  *   -> mappo_adv_stats_reduce -> [all-reduce] -> mappo_valuenorm_apply: EMA update of vn_stats (float32[3]). */
 int mappo_moments_num_partials(long long count);
+/* PopArt.update's rescale of the value head (popart.py:52-70, as it runs on cuda): with (mean, var) the debiased
+ * statistics before (`old_stats`) and after (`new_stats`, both float32[3] like vn_stats) the EMA step,
+ *   weight <- weight * sqrt(old_var) / sqrt(new_var),   bias <- (sqrt(old_var) * bias + old_mean - new_mean) / sqrt(new_var)
+ * on head_w [n_out][n_in] and head_b [n_out] (slices of the critic's flat parameter buffer).  (ABI v6.) */
+int mappo_popart_rescale(const float* old_stats, const float* new_stats, float* head_w, float* head_b, int n_in,
+                         int n_out, void* stream);
 int mappo_moments(const float* x, long long count, double* partials, void* stream);
 
 /* Allocation-free variant of mappo_moments + mappo_adv_stats_reduce: stats3 (double[3] on the device) receives
@@ -402,6 +408,11 @@ typedef struct {
   float one_minus_beta2;       /* float(1.0 - beta2), the `value` of addcmul_ (1 - 0.999f in fp32 is off by 1.3e-5 relative) */
   double beta1_exact;          /* the betas in double: only read when the step count lives on the device (below) */
   double beta2_exact;
+  int32_t frozen_head;         /* != 0: the head's weight / bias slots are not optimiser parameters -- they are left out of
+                                * the global norm and of the update (their gradient still feeds the LayerNorm-affine chain
+                                * rule in front of the head).  --use_popart on cuda: PopArt's weight / bias are plain
+                                * tensors, absent from critic.parameters() (popart.py:21-27, rMAPPOPolicy.py:35-37).  ABI v6 */
+  int32_t reserved2;
 } mappo_adam_config;
 
 /* From the reduced sums: finish the chain rule through the folded LayerNorm affines, divide by the loss

@@ -37,7 +37,7 @@ def lib():
                 "(there is no CPU or PyTorch fallback for the hot path)." % LIB_PATH)
         _lib = C.CDLL(LIB_PATH)
         _declare(_lib)
-        if _lib.mappo_abi_version() != 5:
+        if _lib.mappo_abi_version() != 6:
             raise MappoError("mappo_b200: ABI version mismatch")
     return _lib
 

@@ -15,6 +15,7 @@ class FusedAdam:
 
     def __init__(self, net, lr, eps, weight_decay, betas=(0.9, 0.999)):
         self.net = net
+        self.frozen_head = bool(getattr(net, "_head_outside_optimizer", False))   # PopArt head (see utils/popart.py)
         self.param_groups = [dict(lr=lr, eps=eps, weight_decay=weight_decay, betas=betas)]
         self.exp_avg = torch.zeros_like(net.flat)
         self.exp_avg_sq = torch.zeros_like(net.flat)
@@ -34,7 +35,7 @@ class FusedAdam:
         t = self.step_count + 1
         return ops.AdamConfig(g["lr"], b1, b2, g["eps"], g["weight_decay"], float(max_grad_norm),
                               int(bool(use_max_grad_norm)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), 1.0 - b1, 1.0 - b2,
-                              float(b1), float(b2))
+                              float(b1), float(b2), int(self.frozen_head), 0)
 
     def state_dict(self):
         return dict(exp_avg=self.exp_avg.clone(), exp_avg_sq=self.exp_avg_sq.clone(), step=self.step_count,

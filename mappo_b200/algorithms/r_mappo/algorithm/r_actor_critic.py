@@ -99,9 +99,10 @@ class _FlatNet(nn.Module):
         self._recurrent = bool(args.use_recurrent_policy or args.use_naive_recurrent_policy)
         self._recurrent_N = args.recurrent_N
         self.device_ = torch.device(device)
-        if args.use_popart:
-            raise NotImplementedError("--use_popart raises TypeError inside the reference's PopArt.update "
-                                      "(popart.py:61); not built, see DESIGN.md section 7")
+        # --use_popart (r_actor_critic.py:139-140): the value head is a PopArt whose tensors, on the reference's default
+        # cuda device, are not registered parameters (algorithms/utils/popart.py here): kept in `.flat` for the kernels,
+        # left out of named_parameters() / state_dict() and of the optimiser
+        self._head_outside_optimizer = bool(args.use_popart) and is_critic
         if self._recurrent and args.recurrent_N != 1:
             raise NotImplementedError("recurrent_N > 1")
         self.cfg = ops.net_config(in_dim, args.hidden_size, args.layer_N, args.use_ReLU,
@@ -113,7 +114,7 @@ class _FlatNet(nn.Module):
         flat = torch.empty(total, dtype=torch.float32, device=self.device_)
         self.register_buffer("flat", flat, persistent=False)
         off = 0
-        self._slices = {}
+        self._slices, self._shapes = {}, {}
         for k, v in init.items():
             if "fc_h" in k:      # registered-but-never-executed template (mlp.py:20-27): kept for checkpoints
                 p = nn.Parameter(v.to(self.device_), requires_grad=False)
@@ -122,9 +123,17 @@ class _FlatNet(nn.Module):
                 flat[off:off + n].copy_(v.reshape(-1))
                 p = nn.Parameter(flat[off:off + n].view(v.shape), requires_grad=False)
                 self._slices[k] = (off, off + n)
+                self._shapes[k] = tuple(v.shape)
                 off += n
+            if self._head_outside_optimizer and k.startswith("v_out."):
+                continue         # PopArt's weight / bias: plain tensors on cuda, not parameters
             _attach(self, k, p)
         assert off == total
+        if self._head_outside_optimizer:
+            from ...utils.popart import PopArt
+            self.v_out = PopArt(args.hidden_size, 1, device=self.device_,
+                                weight=self.flat_view("v_out.weight").view(self._shapes["v_out.weight"]),
+                                bias=self.flat_view("v_out.bias"))
 
     def flat_view(self, key):
         a, b = self._slices[key]
@@ -132,7 +141,7 @@ class _FlatNet(nn.Module):
 
     def unflatten(self, vec):
         """{reference key: view} of a flat vector laid out like `.flat` (gradients, Adam moments)."""
-        return {k: vec[a:b].view(dict(self.named_parameters())[k].shape) for k, (a, b) in self._slices.items()}
+        return {k: vec[a:b].view(self._shapes[k]) for k, (a, b) in self._slices.items()}
 
     def load_state_dict(self, state_dict, strict=True):
         own = dict(self.named_parameters())

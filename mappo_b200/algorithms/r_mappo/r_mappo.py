@@ -40,11 +40,9 @@ class R_MAPPO:
         assert (self._use_popart and self._use_valuenorm) == False, \
             ("self._use_popart and self._use_valuenorm can not be set True simultaneously")
         if self._use_popart:
-            # the reference's own PopArt cannot run: PopArt.update assigns plain tensors to registered nn.Parameters
-            # (popart.py:61,66-67) -> TypeError at the first cal_value_loss (probed on the unmodified reference)
-            raise NotImplementedError("--use_popart raises TypeError inside the reference's PopArt.update "
-                                      "(popart.py:61); not built, see DESIGN.md section 7")
-        self.value_normalizer = ValueNorm(1, device=self.device) if self._use_valuenorm else None
+            self.value_normalizer = self.policy.critic.v_out            # r_mappo.py:45-46
+        else:
+            self.value_normalizer = ValueNorm(1, device=self.device) if self._use_valuenorm else None
         # multi-GPU hook: callable(tensor) summing it in place over ranks (torch.distributed.all_reduce); None on 1 GPU
         self.all_reduce = None
         self.pack_wide_inputs = os.environ.get("MAPPO_PACK_WIDE", "1") != "0"   # A/B switch for the packed first layer
@@ -62,7 +60,8 @@ class R_MAPPO:
 
     def _loss_config(self):
         return ops.LossConfig(self.clip_param, self.entropy_coef, self.value_loss_coef, self.huber_delta,
-                              int(self._use_huber_loss), int(self._use_clipped_value_loss), int(self._use_valuenorm),
+                              int(self._use_huber_loss), int(self._use_clipped_value_loss),
+                              int(self._use_valuenorm or self._use_popart),
                               int(self._use_policy_active_masks), int(self._use_value_active_masks), 0)
 
     def _workspace(self, rows_a, rows_c):
@@ -105,11 +104,16 @@ class R_MAPPO:
                          ws["gpa"], ws["lpa"], index=index)
         ops.grad_reduce(ws["gpa"], ws["lpa"], ws["nba"], gsa, lsa)
         # ValueNorm.update(return_batch) happens inside the value loss, before normalize (r_mappo.py:65-67)
+        old_stats = None
         if self.value_normalizer is not None:
-            self.value_normalizer.update(returns if vn_batch is None else vn_batch, moments=vn_moments)
+            kw = dict(defer_rescale=True) if self._use_popart else {}
+            old_stats = self.value_normalizer.update(returns if vn_batch is None else vn_batch, moments=vn_moments, **kw)
         ops.critic_update(pol.critic.cfg, loss, pol.critic.flat, share_obs, value_preds, returns, active,
                           None if self.value_normalizer is None else self.value_normalizer.stats,
                           ws["gpc"], ws["lpc"], group=group, index=index, share_rows_div=share_rows_div, packed=packed)
+        if self._use_popart:
+            # popart.py:69-70: the head is rescaled by update(); `values` of this loss were formed with the old head
+            self.value_normalizer.rescale(old_stats)
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows_a
         if self.all_reduce is not None:
@@ -157,12 +161,16 @@ class R_MAPPO:
         ops.actor_update_rnn(pol.actor.cfg, loss, pol.actor.flat, v["obs"], n_chunks, L, idx, v["rnn"], v["masks"],
                              v["actions"], v["logp"], v["adv"], v["active"], v["avail"], ws["gpa"], ws["lpa"])
         ops.grad_reduce(ws["gpa"], ws["lpa"], ws["nba"], gsa, lsa)
+        old_stats = None
         if self.value_normalizer is not None:
-            self.value_normalizer.update(v["returns"].index_select(0, idx))
+            kw = dict(defer_rescale=True) if self._use_popart else {}
+            old_stats = self.value_normalizer.update(v["returns"].index_select(0, idx), **kw)
         ops.critic_update_rnn(pol.critic.cfg, loss, pol.critic.flat, v["share"], n_chunks, L, idx, v["rnn_critic"],
                               v["masks"], v["value_preds"], v["returns"], v["active"],
                               None if self.value_normalizer is None else self.value_normalizer.stats,
                               ws["gpc"], ws["lpc"], share_rows_div=v["M"] if v["share_is_unique"] else 1)
+        if self._use_popart:
+            self.value_normalizer.rescale(old_stats)
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows
         if self.all_reduce is not None:
@@ -191,7 +199,7 @@ class R_MAPPO:
         values, value_preds_batch = check(values, self.device), check(value_preds_batch, self.device)
         return_batch, active_masks_batch = check(return_batch, self.device), check(active_masks_batch, self.device)
         clipped = value_preds_batch + (values - value_preds_batch).clamp(-self.clip_param, self.clip_param)
-        if self._use_valuenorm:
+        if self._use_popart or self._use_valuenorm:                  # r_mappo.py:64-67
             self.value_normalizer.update(return_batch)
             target = self.value_normalizer.normalize(return_batch).view_as(return_batch)
         else:

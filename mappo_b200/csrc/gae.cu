@@ -199,6 +199,16 @@ valuenorm_transform_kernel(const float* __restrict__ st, const float* __restrict
     out[i] = denorm ? (x[i] * sd + mean) : ((x[i] - mean) / sd);
 }
 
+// popart.py:52-70 (the two assignments at the end of PopArt.update), float32 like torch
+__global__ void popart_rescale_kernel(const float* __restrict__ old_st, const float* __restrict__ new_st,
+                                      float* __restrict__ w, float* __restrict__ b, int n_in, int n_out) {
+  float om, os, nm, ns;
+  vn_mean_std(old_st, om, os);
+  vn_mean_std(new_st, nm, ns);
+  for (int e = threadIdx.x; e < n_in * n_out; e += blockDim.x) w[e] = w[e] * os / ns;
+  for (int j = threadIdx.x; j < n_out; j += blockDim.x) b[j] = (os * b[j] + om - nm) / ns;
+}
+
 static inline int grid_for(long long count, int threads, int cap) {
   long long g = (count + threads - 1) / threads;
   if (g < 1) g = 1;
@@ -302,6 +312,14 @@ extern "C" int mappo_advantages(const float* returns, const float* value_preds, 
   advantages_kernel<<<mappo_moments_num_partials(count), kRedThreads, 0, (cudaStream_t)stream>>>(
       returns, value_preds, active_masks, vn_stats, count, advantages_raw, partials);
   MAPPO_CHECK_LAUNCH("advantages_kernel");
+  return 0;
+}
+
+extern "C" int mappo_popart_rescale(const float* old_stats, const float* new_stats, float* head_w, float* head_b, int n_in,
+                                    int n_out, void* stream) {
+  MAPPO_REQUIRE(old_stats && new_stats && head_w && head_b && n_in > 0 && n_out > 0, "popart_rescale: bad arguments");
+  popart_rescale_kernel<<<1, 64, 0, (cudaStream_t)stream>>>(old_stats, new_stats, head_w, head_b, n_in, n_out);
+  MAPPO_CHECK_LAUNCH("popart_rescale_kernel");
   return 0;
 }
 

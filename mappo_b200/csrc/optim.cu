@@ -96,6 +96,17 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
     __syncthreads();                                    // heads accumulate into the same affine slots
   }
   __syncthreads();
+  // a head outside the optimiser (PopArt on cuda): its G has done its work in the chain rule above; take it out of the
+  // norm, of grad_out and of the update
+  auto in_head = [&](int e) {
+    for (int h = 0; h < L.n_heads; ++h)
+      if ((e >= L.wh[h] && e < L.wh[h] + L.head_dim[h] * H) || (e >= L.bh[h] && e < L.bh[h] + L.head_dim[h])) return true;
+    return false;
+  };
+  if (ad.frozen_head) {
+    for (int e = tid; e < L.total; e += kOptThreads) if (in_head(e)) g[e] = 0.0f;
+    __syncthreads();
+  }
   // 2. loss denominator, global L2 norm
   const double denom = lsum[denom_slot];
   const float inv = (float)(1.0 / denom);
@@ -128,6 +139,7 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
     }
     const float step_size = ad.lr / bc1;
     for (int e = tid; e < L.total; e += kOptThreads) {
+      if (ad.frozen_head && in_head(e)) continue;
       float grad = g[e] * clip;
       const float p = params[e];
       if (ad.weight_decay != 0.0f) grad = fmaf(ad.weight_decay, p, grad);

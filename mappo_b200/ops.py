@@ -61,6 +61,7 @@ _lib._EXTRA_SIGS.update({
     "mappo_moments": [_P, C.c_longlong, _P, _P],
     "mappo_valuenorm_apply": [_P, _P, C.c_double, _P],
     "mappo_valuenorm_transform": [_P, _P, _P, C.c_longlong, C.c_int, _P],
+    "mappo_popart_rescale": [_P, _P, _P, _P, C.c_int, C.c_int, _P],
 })
 
 
@@ -125,6 +126,12 @@ def valuenorm_apply(vn_stats, stats3, beta):
     check(_lib.lib().mappo_valuenorm_apply(ptr(vn_stats), ptr(stats3), float(beta), stream_ptr()), "valuenorm_apply")
 
 
+def popart_rescale(old_stats, new_stats, head_w, head_b):
+    """PopArt.update's rescale of the value head (popart.py:69-70); head_w [n_out, n_in], head_b [n_out] in place."""
+    check(_lib.lib().mappo_popart_rescale(ptr(old_stats), ptr(new_stats), ptr(head_w), ptr(head_b),
+                                          int(head_w.shape[1]), int(head_w.shape[0]), stream_ptr()), "popart_rescale")
+
+
 def valuenorm_transform(vn_stats, x, denormalize, out=None):
     if out is None:
         out = torch.empty_like(x)
@@ -152,7 +159,8 @@ class AdamConfig(C.Structure):
     _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
                 ("weight_decay", C.c_float), ("max_grad_norm", C.c_float), ("use_max_grad_norm", C.c_int32),
                 ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float), ("one_minus_beta1", C.c_float),
-                ("one_minus_beta2", C.c_float), ("beta1_exact", C.c_double), ("beta2_exact", C.c_double)]
+                ("one_minus_beta2", C.c_float), ("beta1_exact", C.c_double), ("beta2_exact", C.c_double),
+                ("frozen_head", C.c_int32), ("reserved2", C.c_int32)]
 
 
 _NC, _LC, _AC = C.POINTER(NetConfig), C.POINTER(LossConfig), C.POINTER(AdamConfig)

@@ -21,7 +21,7 @@ def test_library_exports_every_declared_symbol():
     assert len(syms) >= 8
     missing = [s for s in syms if not hasattr(lib, s)]
     assert not missing, missing
-    assert lib.mappo_abi_version() == 5 and lib.mappo_sm_arch() == 100
+    assert lib.mappo_abi_version() == 6 and lib.mappo_sm_arch() == 100
 
 
 def test_obs_widths_match_reference_shapes():

@@ -25,7 +25,7 @@ def build(fx, seed=1):
     a = fx_args(fx)
     args = types.SimpleNamespace(**a)
     args.use_recurrent_policy = bool(fx["recurrent"]); args.use_naive_recurrent_policy = False
-    args.recurrent_N = 1; args.use_popart = False; args.use_orthogonal = True; args.seed = seed
+    args.recurrent_N = 1; args.use_popart = bool(a.get("use_popart", False)); args.use_orthogonal = True; args.seed = seed
     args.ppo_epoch = 1; args.num_mini_batch = 1; args.data_chunk_length = int(fx["chunk"])
     heads = [int(h) for h in fx["act_heads"]]
     act = Discrete(heads[0]) if len(heads) == 1 else MultiDiscrete([[0, h - 1] for h in heads])
