@@ -10,9 +10,14 @@ shared MLP policy (Tanh), ppo_epoch = 10, num_mini_batch = 1, GAE + ValueNorm; w
 
 Prints ONE JSON line (rank 0).  `value`: device-resident runner.  `e2e`: the same iteration driven through the
 reference-facing vec-env / policy / buffer calls with HOST (pinned) buffers at the boundary, copies in the timed
-region.  `roofline`: the dominant kernel (fused actor forward+loss+backward), timed with CUDA events inside the
-timed region.  `cpu_baseline`: the CPU restatement of the reference path (oracle/iteration.py) timed on this
-box's host cores on a bounded sample.  `--impl reference` times that CPU path alone.
+region.  `roofline`: the dominant kernel (fused actor forward+loss+backward) at top level plus `kernels`, one entry per
+kernel of the iteration (actor / critic update, rollout forwards, env step, GAE, gradient reduce, Adam), each timed
+with CUDA events inside the timed region.  `cpu_baseline`: the UNMODIFIED reference (baseline/_ref: SubprocVecEnv x 128
+worker processes + MPERunner + R_MAPPO on torch CPU, the C1 flags of train_mpe_spread.sh) timed on this box's host
+cores on a bounded sample; `cpu_baseline_port`: the CPU port (oracle/iteration.py) as a second figure.
+`--impl reference` times the unmodified reference alone.  Under torchrun (N > 1) the line also carries `dp_check`:
+replicas bit-identical after an update, and the reduced gradient of a 2-rank job equal to the single-GPU gradient on
+the union of the env shards.
 """
 import argparse
 import json
@@ -249,6 +254,66 @@ def host_boundary_iteration(runner, envs, hb):
     return h2d, d2h, info
 
 
+def _replica_checksum(trainers):
+    """int64[4] per rank: order-sensitive checksums of the raw parameter / ValueNorm bits (bit-identical replicas give
+    identical numbers)."""
+    import torch
+    acc = []
+    for tr in trainers:
+        parts = [tr.policy.actor.flat, tr.policy.critic.flat, tr.policy.actor_optimizer.exp_avg_sq,
+                 tr.policy.critic_optimizer.exp_avg_sq]
+        if tr.value_normalizer is not None:
+            parts.append(tr.value_normalizer.stats)
+        bits = torch.cat([p.reshape(-1).view(torch.int32).to(torch.int64) for p in parts])
+        w = torch.arange(1, bits.numel() + 1, device=bits.device, dtype=torch.int64)
+        acc.append(torch.stack([bits.sum(), (bits * w).sum(), (bits ^ w).sum(), torch.tensor(bits.numel(), device=bits.device)]))
+    return torch.stack(acc).sum(0)
+
+
+def _replicas_identical(trainers, dist, world):
+    import torch
+    mine = _replica_checksum(trainers)
+    allc = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allc, mine)
+    return all(bool((c == allc[0]).all()) for c in allc)
+
+
+def dp_check(device, rank, world, dist, n_small=512):
+    """Multi-rank parity where the driver runs: `world` ranks x n_small envs (global env ids
+    rank * n_small ...) do one rollout + GAE + ONE ppo_update with the NCCL hooks; rank 0 then does the same on ONE GPU
+    with the union of the envs (world x n_small, no collective).  Env resets and action sampling are Philox streams
+    keyed by the global env id / row, so both see the same trajectories; the advantage moments, the ValueNorm batch
+    moments and the gradient sums are global in both.  Reports the distance of the reduced gradient and of the six
+    train_info scalars, and whether the replicas' parameters are bit-identical after the update."""
+    import torch
+    out = {"envs_per_rank": n_small, "ranks": world}
+
+    def one_update(n, rk, wd):
+        _, envs, r = build_runner(n, device, rk, wd)
+        tr = r.trainer
+        tr.ppo_epoch = 1
+        r.warmup(); r._rollout(); r.compute()
+        info = r.train()
+        ws = next(iter(tr._ws.values()))
+        return r, tr, ws["grad"].clone(), info
+
+    r, tr, g_multi, info_multi = one_update(n_small, rank, world)
+    out["replicas_identical"] = _replicas_identical([tr], dist, world)
+    if rank == 0:
+        _, tr1, g_single, info_single = one_update(n_small * world, 0, 1)
+        scale = float(g_single.abs().max())
+        out["grad_vs_single_gpu_max_rel"] = float((g_multi - g_single).abs().max()) / scale
+        out["info_vs_single_gpu_max_rel"] = max(abs(info_multi[k] - info_single[k]) / (abs(info_single[k]) + 1e-12)
+                                                for k in info_single)
+        pa = float((tr.policy.actor.flat - tr1.policy.actor.flat).abs().max())
+        pc = float((tr.policy.critic.flat - tr1.policy.critic.flat).abs().max())
+        out["params_vs_single_gpu_max_abs"] = max(pa, pc)
+        out["tolerance"] = "gradient 1e-5 relative to max|g| (summation order only)"
+        out["ok"] = bool(out["replicas_identical"] and out["grad_vs_single_gpu_max_rel"] < 1e-5)
+    dist.barrier()
+    return out
+
+
 def run_ours(ns):
     import torch
     from mappo_b200 import _lib, ops
@@ -274,6 +339,9 @@ def run_ours(ns):
             dist.barrier()
         torch.cuda.synchronize()
 
+    dp = None
+    if dist is not None and not SEPARATED and not ns.no_dp_check:
+        dp = dp_check(device, rank, world, dist)
     runner.warmup()
     for _ in range(ns.warmup):
         runner.run_episode()
@@ -295,6 +363,9 @@ def run_ours(ns):
     ms = float(ms.item())
     launches = _lib.launch_count() - launches0
     ops.TIMERS.enabled = False
+    if dp is not None:
+        dp["replicas_identical_after_timed_region"] = _replicas_identical(
+            runner.trainer if SEPARATED else [runner.trainer], dist, world)
     kt = ops.TIMERS.summary()
     clocks = sampler.stop() if rank == 0 else None
     value = agent_steps * world * ns.steps / (ms * 1e-3)
@@ -332,6 +403,7 @@ def run_ours(ns):
     if dist is not None:
         dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
     e2e_value = agent_steps * world * e_steps / (float(e_ms.item()) * 1e-3)
+    e2e_wall_s = time.perf_counter() - t0                      # the e2e leg alone (the CPU legs run later)
     envs.set_host_io(False)
 
     if rank != 0:
@@ -362,15 +434,34 @@ def run_ours(ns):
                 "note": "algorithmic fp32-equivalent FLOP; the kernel issues 3-4 fp16 MMAs per product and is bound by "
                         "the fp32 epilogues between the GEMMs (see DESIGN.md 4.1, profiles/)"}
     share = {k: {"launches": v[0], "ms_per_step": v[1] / ns.steps} for k, v in kt.items()}
+    tr0 = runner.trainer[0] if SEPARATED else runner.trainer
+    ws0 = next(iter(tr0._ws.values()))
+    roofline["kernels"] = kernel_rooflines(kt, n_envs, ns.steps, peaks, ws0["nba"], ws0["nbc"],
+                                           tr0.policy.actor.flat.numel(), tr0.policy.critic.flat.numel())
+    timed = sum(e["ms_per_step"] for e in roofline["kernels"])
+    roofline["kernels_ms_per_step"] = timed
+    roofline["kernels_share_of_step"] = timed / (ms / ns.steps)
 
-    # ---- CPU baseline beside it (N = 1 only)
-    cpu = None
+    # ---- CPU baseline beside it (N = 1 only): the unmodified reference (child process: its 128 env workers are
+    # forked from a process that never initialised CUDA), and the CPU port as a second figure
+    cpu = cpu_port = None
     if world == 1 and not ns.no_cpu:
         cores = len(os.sched_getaffinity(0))
-        v, sec = cpu_iteration_rate(ns.cpu_envs, ns.cpu_iters, 1, cores)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "%d envs x %d full iterations after 1 warm-up (%.2f s each) of the same workload, "
-                         "oracle/iteration.py, torch %d threads" % (ns.cpu_envs, ns.cpu_iters, sec, cores)}
+        try:
+            cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", str(ns.ref_iters),
+                   "--warmup", "1", "--ref-envs", str(ns.ref_envs), "--ref-threads", str(ns.ref_threads),
+                   "--agents", str(M_AGENTS)]
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=900)
+            line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+            cpu = json.loads(line)["cpu_baseline"]
+        except Exception as ex:                                  # noqa: BLE001 -- the figure is reported, never fatal
+            cpu = {"value": None, "unit": UNIT, "cores": cores, "kind": "reference", "sample": "failed: %r" % (ex,)}
+        if cpu.get("kind") == "reference" and not ns.no_port:
+            v, sec = cpu_iteration_rate(ns.cpu_envs, ns.cpu_iters, 1, cores)
+            cpu_port = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": "%d envs x %d full iterations after 1 warm-up (%.2f s each) of the same workload, "
+                                  "oracle/iteration.py (numpy env batched over envs + torch CPU autograd), torch %d threads"
+                                  % (ns.cpu_envs, ns.cpu_iters, sec, cores)}
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": ns.steps, "warmup": ns.warmup,
            "ms_per_step": ms / ns.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -378,12 +469,83 @@ def run_ours(ns):
            "config": {"workload": workload_name(n_envs, world), "agent_steps_per_step": agent_steps * world,
                       "l2": "inputs larger than L2 (rollout buffer 0.4 GB per GPU)"},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                   "steps": e_steps, "wall_s": time.perf_counter() - t0},
-           "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "kernel_ms_per_step": share,
+                   "steps": e_steps, "wall_s": e2e_wall_s},
+           "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_port": cpu_port,
+           "kernel_ms_per_step": share,
            "clocks": clocks, "train_info": info}
+    if dp is not None:
+        out["dp_check"] = dp
+        out["collective"] = "NCCL all-reduce (torch.distributed): gradient sums + loss sums per ppo_update, advantage and ValueNorm moments once per iteration"
     print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def kernel_rooflines(kt, n_envs, steps, peaks, nblocks_a, nblocks_c, P_a, P_c):
+    """Per-kernel roofline entries for the bench line (north_star: "each kernel at a stated fraction of its HBM or
+    tensor roofline").  Times: CUDA events around every launch inside the timed region (ops.TIMERS, on the launching
+    stream).  Algorithmic work: SURVEY.md section 8(d) formulas (fp32 storage; FLOP = 2 x MAC, training pass = 3 x
+    forward minus the first-layer data gradient).  Denominators: MEASURED_PEAKS.json (HBM copy bandwidth; bf16 tensor
+    sustained, since every kernel is timed inside a long step).  `traffic`: dram__bytes_read.sum + dram__bytes_write.sum
+    of one launch from the committed `ncu --set full` summaries (profiles/r02_traffic.json), C2 shape only."""
+    M, L, D, S, A, T = M_AGENTS, N_LANDMARKS, D_OBS, S_OBS, N_ACT, T_EP
+    hbm = peaks.get("hbm_gbs", 6650.0)
+    tens = peaks.get("bf16_tflops_sustained", 1400.0)
+    src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
+    rows_a, rows_c = n_envs * M, n_envs                      # per rollout step: actor rows, unique share_obs rows
+    B = n_envs * T * M
+    fwd_a = 2 * (D * H + H * H + H * A)
+    fwd_c = 2 * (S * H + H * H + H)
+    env_bytes = 4 * (4 * M + 2 * L + M + 1) + 4 * (4 * M + M * D + M) + M      # per env, SURVEY 8(d): 367 B at C2
+    gae_bytes_traj = (T + 2 * (T + 1)) * 4 + 2 * T * 4 + 4                    # per (env, agent) trajectory: 512 B
+    traffic = {}
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
+        if CONFIG == "C2" and n_envs == tj.get("n_envs"):
+            traffic = tj.get("kernels", {})
+    except Exception:
+        pass
+    spec = [
+        ("actor_update", "mlp_tc_kernel<MODE 2> actor forward + PPO loss + backward", "tensor",
+         B * (3 * fwd_a - 2 * D * H), "%d rows x (3 x %d - 2 D H) FLOP" % (B, fwd_a)),
+        ("critic_update", "mlp_tc_kernel<MODE 3> critic forward + value loss + backward (one row per env-step, group = M)",
+         "tensor", n_envs * T * (3 * fwd_c - 2 * S * H), "%d rows x (3 x %d - 2 S H) FLOP" % (n_envs * T, fwd_c)),
+        ("actor_forward", "mlp_tc_kernel<MODE 0> rollout actor forward + sampling", "tensor", rows_a * fwd_a,
+         "%d rows x %d FLOP" % (rows_a, fwd_a)),
+        ("critic_forward", "mlp_tc_kernel<MODE 1> rollout critic forward", "tensor", rows_c * fwd_c,
+         "%d rows x %d FLOP" % (rows_c, fwd_c)),
+        ("env_step", "env_kernel<simple_spread> physics + reward + obs + auto-reset", "hbm", n_envs * env_bytes,
+         "%d envs x %d B" % (n_envs, env_bytes)),
+        ("gae_returns", "gae_kernel backward scan + ValueNorm denormalise + raw advantages", "hbm",
+         n_envs * M * gae_bytes_traj, "%d trajectories x %d B" % (n_envs * M, gae_bytes_traj)),
+        ("grad_reduce", "grad_reduce_kernel (fixed-order sum of the per-CTA partial rows)", "hbm", None, None),
+        ("adam_step", "adam_step_kernel (affine chain rule + global-norm clip + Adam)", "hbm", None, None),
+    ]
+    out = []
+    for key, name, bound, work, formula in spec:
+        n, tot = kt.get(key, (0, 0.0))
+        if n == 0:
+            continue
+        ms = tot / n
+        if key == "grad_reduce":      # two launches per update: actor and critic partials, read once, sums written
+            work = ((nblocks_a + 1) * P_a + (nblocks_c + 1) * P_c) * 4 // 2
+            formula = "mean of (%d + 1) x %d and (%d + 1) x %d floats" % (nblocks_a, P_a, nblocks_c, P_c)
+        if key == "adam_step":        # params + m + v read and written, sums read, gradient written
+            work = (P_a + P_c) * 4 * 8 // 2
+            formula = "mean of 8 x 4 B x %d and x %d parameters" % (P_a, P_c)
+        e = {"key": key, "kernel": name, "bound": bound, "launches_per_step": n / steps, "ms_per_launch": ms,
+             "ms_per_step": tot / steps, "work_per_launch": work, "work_formula": formula,
+             "traffic": traffic.get(key)}
+        if bound == "tensor":
+            ach = work / (ms * 1e-3) / 1e12
+            e.update(achieved=ach, peak=tens, unit="TFLOP/s", frac=ach / tens,
+                     frac_of_fp32_fma_peak=ach / 74.4)
+        else:
+            ach = work / (ms * 1e-3) / 1e9
+            e.update(achieved=ach, peak=hbm, unit="GB/s", frac=ach / hbm)
+        e["peak_source"] = src
+        out.append(e)
+    return out
 
 
 def actor_update_flops_per_row():
@@ -405,10 +567,12 @@ def main():
     ap.add_argument("--cpu-envs", dest="cpu_envs", type=int, default=1024,
                     help="envs of the bounded CPU sample (the port's throughput peaks near 1,024 envs per iteration: "
                          "58 k agent-steps/s on 8 cores against 40 k at 8,192)")
-    ap.add_argument("--cpu-iters", dest="cpu_iters", type=int, default=20,
-                    help="timed iterations of the cpu_baseline leg (about 10 s on 16 cores)")
+    ap.add_argument("--cpu-iters", dest="cpu_iters", type=int, default=10,
+                    help="timed iterations of the port's leg (about 5 s on 16 cores)")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
+    ap.add_argument("--no-dp-check", dest="no_dp_check", action="store_true")
+    ap.add_argument("--no-port", dest="no_port", action="store_true", help="skip the second (port) CPU figure")
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=128,
                     help="SubprocVecEnv workers of the unmodified reference (C1: 128, train_mpe_spread.sh)")
     ap.add_argument("--ref-threads", dest="ref_threads", type=int, default=0,

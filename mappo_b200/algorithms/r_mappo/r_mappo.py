@@ -111,9 +111,7 @@ class R_MAPPO:
         ops.critic_update(pol.critic.cfg, loss, pol.critic.flat, share_obs, value_preds, returns, active,
                           None if self.value_normalizer is None else self.value_normalizer.stats,
                           ws["gpc"], ws["lpc"], group=group, index=index, share_rows_div=share_rows_div, packed=packed)
-        if self._use_popart:
-            # popart.py:69-70: the head is rescaled by update(); `values` of this loss were formed with the old head
-            self.value_normalizer.rescale(old_stats)
+
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows_a
         if self.all_reduce is not None:
@@ -130,6 +128,11 @@ class R_MAPPO:
                       copt.exp_avg, copt.exp_avg_sq, gsc, lsc, 1, rows_global, ws["grad"][Pa:], self._info[4:],
                       apply_update=True, step_dev=copt.step_dev)
         copt.step_count += 1
+        if self._use_popart:
+            # popart.py:69-70: update() rescales the head.  Done last: the loss and its backward pass (including the
+            # chain rule through the LayerNorm affine in front of the head, inside mappo_adam_step) belong to the head
+            # the forward pass used
+            self.value_normalizer.rescale(old_stats)
         self._info_total += self._info
         return ws
 
@@ -169,8 +172,6 @@ class R_MAPPO:
                               v["masks"], v["value_preds"], v["returns"], v["active"],
                               None if self.value_normalizer is None else self.value_normalizer.stats,
                               ws["gpc"], ws["lpc"], share_rows_div=v["M"] if v["share_is_unique"] else 1)
-        if self._use_popart:
-            self.value_normalizer.rescale(old_stats)
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows
         if self.all_reduce is not None:
@@ -187,6 +188,11 @@ class R_MAPPO:
                       copt.exp_avg, copt.exp_avg_sq, gsc, lsc, 1, rows_global, ws["grad"][Pa:], self._info[4:],
                       apply_update=True, step_dev=copt.step_dev)
         copt.step_count += 1
+        if self._use_popart:
+            # popart.py:69-70: update() rescales the head.  Done last: the loss and its backward pass (including the
+            # chain rule through the LayerNorm affine in front of the head, inside mappo_adam_step) belong to the head
+            # the forward pass used
+            self.value_normalizer.rescale(old_stats)
         self._info_total += self._info
         return ws
 
