@@ -342,6 +342,12 @@ def run_ours(ns):
     dp = None
     if dist is not None and not SEPARATED and not ns.no_dp_check:
         dp = dp_check(device, rank, world, dist)
+    if ns.dp_check_only:
+        if rank == 0:
+            print(json.dumps({"dp_check": dp, "n_gpus": world}))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     runner.warmup()
     for _ in range(ns.warmup):
         runner.run_episode()
@@ -572,6 +578,8 @@ def main():
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
     ap.add_argument("--no-dp-check", dest="no_dp_check", action="store_true")
+    ap.add_argument("--dp-check-only", dest="dp_check_only", action="store_true",
+                    help="under torchrun: run the multi-rank parity check, print it and exit (tests/test_gpu_dist.py)")
     ap.add_argument("--no-port", dest="no_port", action="store_true", help="skip the second (port) CPU figure")
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=128,
                     help="SubprocVecEnv workers of the unmodified reference (C1: 128, train_mpe_spread.sh)")
