@@ -583,8 +583,11 @@ def main():
     ap.add_argument("--no-port", dest="no_port", action="store_true", help="skip the second (port) CPU figure")
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=128,
                     help="SubprocVecEnv workers of the unmodified reference (C1: 128, train_mpe_spread.sh)")
-    ap.add_argument("--ref-threads", dest="ref_threads", type=int, default=0,
-                    help="n_training_threads of the reference arm (0 = all host cores; the reference's default is 1)")
+    ap.add_argument("--ref-threads", dest="ref_threads", type=int, default=1,
+                    help="n_training_threads of the reference arm: 1 = the reference's own default (config.py:168, "
+                         "train_mpe_spread.sh) and the faster setting on the B200 box's 16 cores, where the 128 env worker "
+                         "processes already occupy every core (measured: 23.0 k agent-steps/s with 1, 15.6 k with 16); "
+                         "0 = all host cores")
     ap.add_argument("--ref-kind", dest="ref_kind", default="auto", choices=["auto", "port"],
                     help="auto: the unmodified reference from baseline/_ref when present, else the port")
     ap.add_argument("--ref-iters", dest="ref_iters", type=int, default=5,

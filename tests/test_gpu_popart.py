@@ -32,7 +32,7 @@ def test_popart_update_matches_the_reference_on_cuda(tag, golden_dir):
     values = pol.get_values(s[0], s[3], s[7])
     np.testing.assert_allclose(values.cpu().numpy(), fx["values0"], rtol=1e-4, atol=2e-5)
     Pa = pol.actor.flat.numel()
-    n_updates = len([k for k in fx.files if k.endswith("_value_loss")])
+    n_updates = len([k for k in fx.files if k.startswith("u") and k.endswith("_value_loss")])
     for u in range(n_updates):
         vl, cgn, pl, ent, agn, ratio = tr.ppo_update(s)
         t = "u%d_" % u
