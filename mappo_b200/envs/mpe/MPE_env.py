@@ -49,7 +49,7 @@ class MPEVecEnv:
     """`envs` object of the runners: reset() / step(actions) / step_async / step_wait / close, attributes
     num_envs, observation_space, share_observation_space, action_space (lists of length M)."""
 
-    def __init__(self, args, num_envs=None, device="cuda", seed=None, env_id_offset=0, host_io=False):
+    def __init__(self, args, num_envs=None, device="cuda", seed=None, env_id_offset=0, host_io=False, auto_reset=True):
         name = args.scenario_name
         if name not in SCENARIOS:
             raise NotImplementedError("Can not support the %s scenario on the device env" % name)
@@ -81,7 +81,11 @@ class MPEVecEnv:
         self.device = torch.device(device)
         L = _lib.lib()
         M, NL, N = self.num_agents, self.num_landmarks, self.num_envs
-        self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length, self.num_adversaries,
+        # auto_reset=False (the single-env facade, envs/mpe/environment.py): the kernel's done test `step >= episode_length`
+        # never fires, so the env keeps stepping past the episode end like the reference's bare MultiAgentEnv
+        self._auto_reset = bool(auto_reset)
+        self._cfg = _lib.EnvConfig(self.scenario, N, M, NL, self.episode_length if auto_reset else 2 ** 31 - 1,
+                                   self.num_adversaries,
                                    int(seed if seed is not None else getattr(args, "seed", 1)) & (2 ** 64 - 1),
                                    int(env_id_offset))
         L.mappo_env_num_landmarks.argtypes = [C.POINTER(_lib.EnvConfig)]
@@ -296,5 +300,7 @@ class MPEVecEnv:
 
 
 def MPEEnv(args, **kw):
-    """Name-compatible constructor (onpolicy/envs/mpe/MPE_env.py:5)."""
-    return MPEVecEnv(args, **kw)
+    """onpolicy/envs/mpe/MPE_env.py:5-31: ONE env with the reference's per-agent-list MultiAgentEnv API
+    (envs/mpe/environment.py here).  The batched env the runners use is MPEVecEnv."""
+    from .environment import MultiAgentEnv
+    return MultiAgentEnv(args, **kw)

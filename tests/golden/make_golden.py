@@ -627,9 +627,45 @@ def gen_runner():
         print("wrote", path, os.path.getsize(path), {k[9:]: round(float(v), 6) for k, v in fx.items() if k.startswith("it1_info_")})
 
 
-PARTS = {"env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen, "ppo": gen_ppo, "runner": gen_runner,
+# ------------------------------------------------------------------ checkpoint written by the reference
+def gen_ckpt():
+    """actor.pt / critic.pt / vnorm.pt exactly as the reference's Runner.save writes them (base_runner.py:127-135:
+    torch.save of the three state_dicts), plus what those weights compute on a fixed input, for the restore test."""
+    from onpolicy.envs.mpe.MPE_env import MPEEnv
+    from onpolicy.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    from onpolicy.algorithms.r_mappo.r_mappo import R_MAPPO
+    args = ref_args("simple_spread", 3, 3, "mappo", "--use_ReLU")
+    env = MPEEnv(args)
+    torch.manual_seed(21)
+    policy = R_MAPPOPolicy(args, env.observation_space[0], env.share_observation_space[0], env.action_space[0])
+    trainer = R_MAPPO(args, policy)
+    g = torch.Generator().manual_seed(22)
+    with torch.no_grad():
+        for net in (policy.actor, policy.critic):
+            for name, prm in net.named_parameters():
+                if "fc_h" not in name:
+                    prm.add_(torch.randn(prm.shape, generator=g) * 0.1)
+    trainer.value_normalizer.update(torch.randn(100, 1, generator=g) * 2 - 3)
+    d = os.path.join(HERE, "ref_ckpt")
+    os.makedirs(d, exist_ok=True)
+    torch.save(policy.actor.state_dict(), os.path.join(d, "actor.pt"))
+    torch.save(policy.critic.state_dict(), os.path.join(d, "critic.pt"))
+    torch.save(trainer.value_normalizer.state_dict(), os.path.join(d, "vnorm.pt"))
+    obs = torch.randn(64, 18, generator=g).numpy()
+    share = torch.randn(64, 54, generator=g).numpy()
+    z, m = np.zeros((64, 1, 64), np.float32), np.ones((64, 1), np.float32)
+    with torch.no_grad():
+        policy.actor.eval(); policy.critic.eval()
+        values, actions, logp, _, _ = policy.get_actions(share, obs, z, z, m, None, deterministic=True)
+    np.savez_compressed(os.path.join(d, "io.npz"), obs=obs, share_obs=share, values=values.numpy(), actions=actions.numpy(),
+                        log_probs=logp.numpy(), vn=vn_stats(trainer.value_normalizer),
+                        denorm=trainer.value_normalizer.denormalize(values.numpy()))
+    print("wrote", d, sorted(os.listdir(d)))
+
+
+PARTS = {"ckpt": gen_ckpt, "env": gen_env, "vnorm": gen_vnorm, "gae": gen_gae, "gen": gen_gen, "ppo": gen_ppo, "runner": gen_runner,
          "popart": gen_popart}
-DEFAULT_PARTS = ["env", "vnorm", "gae", "gen", "ppo", "runner"]
+DEFAULT_PARTS = ["env", "vnorm", "gae", "gen", "ppo", "runner", "ckpt"]
 
 if __name__ == "__main__":
     todo = sys.argv[1:] or DEFAULT_PARTS

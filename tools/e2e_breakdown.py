@@ -28,10 +28,18 @@ def main():
         torch.cuda.synchronize()
         T[name] = T.get(name, 0.0) + time.perf_counter() - t0
     eye = np.eye(bench.N_ACT, dtype=np.float32)
+    # pinned-copy bandwidth of this box (what bounds the obs D2H of every step)
+    big_d = torch.empty(64 << 20, dtype=torch.uint8, device=dev); big_h = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
+    for name, (dst, src) in (("d2h", (big_h, big_d)), ("h2d", (big_d, big_h))):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        for _ in range(10):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        print("pinned %s: %.1f GB/s" % (name, 10 * 64 / 1024 / (time.perf_counter() - t0)))
     t_all = time.perf_counter()
     for step in range(b.episode_length):
         t0 = time.perf_counter()
-        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step].reshape(N * M, -1), b.obs[step].view(N * M, -1), None, None, None)
+        values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step], b.obs[step].view(N * M, -1), None, None, None)
         tick("policy", t0); t0 = time.perf_counter()
         hb["values"].copy_(values.view(N, M, 1), non_blocking=True)
         hb["actions"].copy_(actions.view(N, M, 1), non_blocking=True)
