@@ -218,36 +218,41 @@ def build_runner(n_envs, device, rank, world, host_io=False):
 
 def host_boundary_iteration(runner, envs, hb):
     """One iteration driven like the reference's MPERunner.run body (runner/shared/mpe_runner.py:24-40,95-139) with
-    HOST arrays crossing every reference-facing call: policy outputs come back to the host (`_t2n`), one-hot
-    `actions_env` goes in through envs.step, obs / rewards / dones come back as host arrays, and buffer.insert
-    receives host arrays.  Returns (h2d_bytes, d2h_bytes)."""
+    HOST arrays crossing every reference-facing call: policy outputs come back to the host (`_t2n` -> the library's
+    drop-in `host_mirror.t2n`: pinned, one sync), the one-hot `actions_env` is built on the host and goes in through
+    envs.step, obs / rewards / dones come back as host arrays, masks are built on the host, and buffer.insert receives
+    host arrays.  Arrays the library itself brought out of the device (obs, rewards, policy outputs) are recognised
+    by insert and served device -> device (INTEGRATION.md "pass-through"); only bytes that really cross PCIe are
+    counted.  Returns (h2d_bytes, d2h_bytes, info)."""
     import numpy as np
     import torch
+    from mappo_b200 import host_mirror
     b, pol = runner.buffer, runner.trainer.policy
     N, M = b.n_rollout_threads, b.num_agents
     h2d = d2h = 0
+
+    def crossing(x):                       # bytes insert() has to send host -> device for this argument
+        return 0 if host_mirror.lookup(x) is not None else x.nbytes
+
     for step in range(b.episode_length):
         # cent_obs = the buffer's share_obs slot [N, M, S] (its M rows per env are one stored row: R_Critic.forward
         # evaluates each env once); the reference passes np.concatenate of the same slot (mpe_runner.py:99)
         values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step], b.obs[step].view(N * M, -1), None, None, None)
-        hb["values"].copy_(values.view(N, M, 1), non_blocking=True)
-        hb["actions"].copy_(actions.view(N, M, 1), non_blocking=True)
-        hb["logp"].copy_(logp.view(N, M, 1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        d2h += hb["values"].numel() * 4 + hb["actions"].numel() * 8 + hb["logp"].numel() * 4
-        oh = hb["onehot"]                                                # mpe_runner.py:110-121 (np.eye(n)[actions]), as a
-        oh.zero_().scatter_(2, hb["actions"], 1.0)                       # multi-threaded scatter into a pinned array
+        values = host_mirror.t2n(values.view(N, M, 1), "values")          # mpe_runner.py:102-104: np.split(_t2n(.))
+        actions = host_mirror.t2n(actions.view(N, M, 1), "actions")
+        logp = host_mirror.t2n(logp.view(N, M, 1), "logp")
+        d2h += values.nbytes + actions.nbytes + logp.nbytes
+        oh = hb["onehot"]                                                # mpe_runner.py:110-121 (np.eye(n)[actions]) as a
+        oh.zero_().scatter_(2, torch.from_numpy(actions), 1)             # scatter into a pinned uint8 array
         actions_env = oh.numpy()
         obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
         h2d += actions_env.nbytes
-        d2h += obs.nbytes + rewards.nbytes + dones.nbytes
-        masks = np.ones((N, M, 1), dtype=np.float32)
-        masks[dones] = 0.0                                               # mpe_runner.py:128-131
+        d2h += obs.nbytes + rewards.nbytes + dones.nbytes + N * M * 4    # + the individual rewards behind `infos`
+        masks = hb["masks"].numpy()
+        np.subtract(1.0, dones[..., None], out=masks)                    # mpe_runner.py:128-131 (masks[dones] = 0)
         share_obs = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))   # :133-137 (a view)
-        b.insert(share_obs, obs, None, None, hb["actions"].numpy(), hb["logp"].numpy(), hb["values"].numpy(), rewards,
-                 masks)
-        h2d += obs.nbytes + hb["actions"].numel() * 8 + hb["logp"].numel() * 4 + hb["values"].numel() * 4 + \
-            rewards.nbytes + masks.nbytes
+        h2d += crossing(obs) + crossing(actions) + crossing(logp) + crossing(values) + crossing(rewards) + crossing(masks)
+        b.insert(share_obs, obs, None, None, actions, logp, values, rewards, masks)
     runner.compute()
     info = runner.train()                                                # six scalars come back to the host
     d2h += 8 * 4
@@ -393,8 +398,7 @@ def run_ours(ns):
     # ---- e2e: host buffers at the reference-facing boundary
     envs.set_host_io(True)
     pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
-    hb = {"values": pin(n_envs, M_AGENTS, 1), "actions": pin(n_envs, M_AGENTS, 1, dt=torch.int64),
-          "logp": pin(n_envs, M_AGENTS, 1), "onehot": pin(n_envs, M_AGENTS, N_ACT)}
+    hb = {"onehot": pin(n_envs, M_AGENTS, N_ACT, dt=torch.uint8), "masks": pin(n_envs, M_AGENTS, 1)}
     host_boundary_iteration(runner, envs, hb)               # warm-up of the host path
     barrier()
     e_steps = max(1, min(ns.steps, ns.e2e_steps))

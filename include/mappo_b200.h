@@ -439,6 +439,14 @@ int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, 
 int mappo_gather_rows(const float* src, long long row_stride, int row_div, int width, const int64_t* index,
                       long long n, float* dst, void* stream);
 
+/* One-hot `actions_env` rows -> float action ids on the device: replaces the inverse of the runner's
+ * np.eye(n)[actions] (onpolicy/runner/shared/mpe_runner.py:110-121; MultiDiscrete: the heads' one-hots concatenated,
+ * :111-117) that MultiAgentEnv._set_action undoes per agent (environment.py:194-256).  onehot: [rows][sum(head_dim)]
+ * of float32 (dtype 0), float64 (1) or uint8 (2) on the DEVICE; head_dim_host: n_heads ints on the HOST;
+ * ids: [rows][ids_ld] float32, column h = index of the first maximum of head h.  (ABI v6.) */
+int mappo_onehot_to_ids(const void* onehot, int dtype, long long rows, int n_heads, const int* head_dim_host,
+                        float* ids, int ids_ld, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * 5. Hardware self-test of the tcgen05 (5th-gen tensor core) operand layouts the policy kernels rely on: stages
  *    tiles A [a_rows][a_cols] and B [b_rows][b_cols] (fp32, tf32-representable values) in the library's

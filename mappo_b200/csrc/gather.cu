@@ -28,9 +28,49 @@ gather_rows_kernel(const float* __restrict__ src, long long row_stride, int row_
   }
 }
 
+// one-hot `actions_env` rows (the reference's np.eye(n)[actions], shared/mpe_runner.py:110-121; MultiDiscrete: the
+// heads' one-hots concatenated) -> float action ids, one thread per (row, head): index of the first maximum
+struct OneHotArgs { int n_heads; int dim[MAPPO_MAX_HEADS]; int off[MAPPO_MAX_HEADS]; int width; };
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+onehot_to_ids_kernel(const T* __restrict__ onehot, long long rows, OneHotArgs a, float* __restrict__ ids, int ids_ld) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= rows * a.n_heads) return;
+  const long long r = i / a.n_heads;
+  const int h = (int)(i - r * a.n_heads);
+  const T* __restrict__ p = onehot + r * a.width + a.off[h];
+  int best = 0;
+  T bv = p[0];
+  for (int q = 1; q < a.dim[h]; ++q) { const T v = p[q]; if (v > bv) { bv = v; best = q; } }
+  ids[r * ids_ld + h] = (float)best;
+}
+
 }  // namespace mappo
 
 using namespace mappo;
+
+extern "C" int mappo_onehot_to_ids(const void* onehot, int dtype, long long rows, int n_heads, const int* head_dim_host,
+                                   float* ids, int ids_ld, void* stream) {
+  MAPPO_REQUIRE(onehot && ids && head_dim_host && rows > 0 && n_heads >= 1 && n_heads <= MAPPO_MAX_HEADS && ids_ld >= n_heads,
+                "onehot_to_ids: bad arguments");
+  OneHotArgs a{};
+  a.n_heads = n_heads;
+  int w = 0;
+  for (int h = 0; h < n_heads; ++h) {
+    MAPPO_REQUIRE(head_dim_host[h] >= 1, "onehot_to_ids: head_dim");
+    a.dim[h] = head_dim_host[h]; a.off[h] = w; w += head_dim_host[h];
+  }
+  a.width = w;
+  const int grid = ceil_div(rows * n_heads, 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == 0) onehot_to_ids_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(onehot), rows, a, ids, ids_ld);
+  else if (dtype == 1) onehot_to_ids_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(onehot), rows, a, ids, ids_ld);
+  else if (dtype == 2) onehot_to_ids_kernel<uint8_t><<<grid, 256, 0, st>>>(static_cast<const uint8_t*>(onehot), rows, a, ids, ids_ld);
+  else MAPPO_REQUIRE(false, "onehot_to_ids: dtype %d (0 = float32, 1 = float64, 2 = uint8)", dtype);
+  MAPPO_CHECK_LAUNCH("onehot_to_ids_kernel");
+  return 0;
+}
 
 extern "C" int mappo_gather_rows(const float* src, long long row_stride, int row_div, int width,
                                  const int64_t* index, long long n, float* dst, void* stream) {

@@ -127,6 +127,7 @@ class MPEVecEnv:
         self._dones = torch.empty(N, M, dtype=torch.uint8, device=dev)
         self._indiv = torch.empty(N, M, dtype=torch.float32, device=dev)
         self._pending = None
+        self._ids_scratch = None
         self.closed = False
         self._host = None
         self.set_host_io(host_io)
@@ -150,6 +151,12 @@ class MPEVecEnv:
             h["dones"].copy_(self._dones, non_blocking=True)
             h["indiv"].copy_(self._indiv, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        # the device copies stay valid until the next step: handing these host arrays back (SharedReplayBuffer.insert)
+        # is served device -> device (host_mirror)
+        from ... import host_mirror
+        host_mirror.register(h["obs"], obs_dev.view(self.num_envs, self.obs_width))
+        if with_step_outputs:
+            host_mirror.register(h["rew"], self._rew_last.view(self.num_envs, self.num_agents, 1))
         obs = self._shape_obs(h["obs"])
         return obs.numpy() if torch.is_tensor(obs) else [o.numpy() for o in obs]
 
@@ -175,19 +182,27 @@ class MPEVecEnv:
         if isinstance(actions, (list, tuple)):  # ragged per-agent list (separated runner)
             cols = [self.actions_to_ids_one(a, i) for i, a in enumerate(actions)]
             return torch.stack(cols, dim=1).contiguous()
-        a = torch.as_tensor(actions, device=self.device) if not torch.is_tensor(actions) else actions.to(self.device)
+        from ... import gather, host_mirror
         N, M = self.num_envs, self.num_agents
+        twin = host_mirror.lookup(actions) if not torch.is_tensor(actions) or not actions.is_cuda else None
+        if twin is not None:
+            a = twin                                                     # ids a host_mirror.t2n call just brought out
+        elif torch.is_tensor(actions):
+            a = actions.to(self.device, non_blocking=True)
+        else:
+            a = torch.from_numpy(np.ascontiguousarray(actions)).to(self.device, non_blocking=True)
         a = a.reshape(N, M, -1)
         if a.shape[-1] == self.act_width and all(len(h) == self.act_width for h in self.head_sizes):
             return a.to(torch.float32).contiguous()
         sizes = self.head_sizes[0]
         assert all(h == sizes for h in self.head_sizes) and a.shape[-1] == sum(sizes), \
             "actions must be ids [N,M,%d] or one-hot [N,M,%d]" % (self.act_width, sum(sizes))
-        ids, off = [], 0
-        for s in sizes:
-            ids.append(a[..., off:off + s].argmax(dim=-1))
-            off += s
-        return torch.stack(ids, dim=-1).to(torch.float32).contiguous()
+        if a.dtype not in (torch.float32, torch.float64, torch.uint8):
+            a = a.to(torch.float32)
+        if self._ids_scratch is None:
+            self._ids_scratch = torch.zeros(N, M, self.act_width, dtype=torch.float32, device=self.device)
+        gather.onehot_to_ids(a.reshape(N * M, -1).contiguous(), sizes, self._ids_scratch.view(N * M, -1))   # one launch
+        return self._ids_scratch
 
     def actions_to_ids_one(self, a, agent):
         a = torch.as_tensor(a, device=self.device) if not torch.is_tensor(a) else a.to(self.device)

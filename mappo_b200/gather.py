@@ -10,6 +10,21 @@ _lib._EXTRA_SIGS["mappo_gather_rows"] = [C.c_void_p, C.c_longlong, C.c_int, C.c_
                                          C.c_void_p, C.c_void_p]
 
 
+_lib._EXTRA_SIGS["mappo_onehot_to_ids"] = [C.c_void_p, C.c_int, C.c_longlong, C.c_int, C.POINTER(C.c_int), C.c_void_p,
+                                           C.c_int, C.c_void_p]
+_ONEHOT_DTYPES = {torch.float32: 0, torch.float64: 1, torch.uint8: 2}
+
+
+def onehot_to_ids(onehot, head_dims, out):
+    """onehot: CUDA [rows, sum(head_dims)] float32 / float64 / uint8 (contiguous); out: float32 [rows, >= heads]."""
+    assert onehot.is_cuda and onehot.is_contiguous() and onehot.dtype in _ONEHOT_DTYPES, "one-hot must be f32/f64/u8 CUDA"
+    rows = onehot.shape[0]
+    hd = (C.c_int * len(head_dims))(*[int(d) for d in head_dims])
+    check(_lib.lib().mappo_onehot_to_ids(ptr(onehot), _ONEHOT_DTYPES[onehot.dtype], rows, len(head_dims), hd, ptr(out),
+                                         int(out.shape[-1]), stream_ptr()), "onehot_to_ids")
+    return out
+
+
 def gather_rows(src, lead_dims, index):
     """src: float32 CUDA tensor whose first `lead_dims` dims enumerate rows (row-major) and whose remaining dims
     are a contiguous row; may be a broadcast (stride-0) view over trailing lead dims.  -> [len(index), width]."""

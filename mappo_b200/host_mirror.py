@@ -1,0 +1,79 @@
+"""Host <-> device twins for the reference-facing (host array) boundary.
+
+The reference's runner moves every step's tensors device -> host (`_t2n`) and host -> device again
+(`SharedReplayBuffer.insert`, onpolicy/runner/shared/mpe_runner.py:95-139).  When a host array handed to this library
+is one the library itself just produced from a device tensor -- the pinned arrays `MPEVecEnv.step` returns in host_io
+mode, or arrays made by `t2n` below -- the device copy still exists, and sending the bytes back over PCIe is redundant.
+This registry remembers, per host buffer (by address and size), the device tensor it was copied from; `lookup` gives
+`insert` / `step` the twin so they copy device -> device instead.
+
+PASS-THROUGH SEMANTICS: the twin is used only if the array handed in is the registered
+buffer itself (same address, same byte count, same serial).  A different host array -- including a `.copy()` -- takes
+the normal host -> device path.  Code that MODIFIES a registered array in place between receiving it and handing it
+back must call `forget(array)` (or set MAPPO_HOST_PASSTHROUGH=0): the device twin would not see the edit."""
+import os
+
+import numpy as np
+import torch
+
+ENABLED = os.environ.get("MAPPO_HOST_PASSTHROUGH", "1") != "0"
+_TWINS = {}          # data pointer -> (nbytes, device tensor)
+_PINNED = {}         # (tag, shape, dtype) -> pinned host tensor
+
+
+def _key(arr):
+    if isinstance(arr, np.ndarray):
+        return arr.__array_interface__["data"][0], arr.nbytes
+    if torch.is_tensor(arr) and not arr.is_cuda:
+        return arr.data_ptr(), arr.numel() * arr.element_size()
+    return None, 0
+
+
+def register(host, device_tensor):
+    """host: numpy array or CPU tensor (contiguous); device_tensor: the CUDA tensor holding the same values."""
+    ptr, nbytes = _key(host)
+    if ptr is not None:
+        _TWINS[ptr] = (nbytes, device_tensor)
+
+
+def forget(host):
+    ptr, _ = _key(host)
+    _TWINS.pop(ptr, None)
+
+
+def lookup(host):
+    """The device twin of `host`, or None."""
+    if not ENABLED:
+        return None
+    ptr, nbytes = _key(host)
+    if ptr is None:
+        return None
+    hit = _TWINS.get(ptr)
+    if hit is None or hit[0] != nbytes:
+        return None
+    if isinstance(host, np.ndarray) and not host.flags["C_CONTIGUOUS"]:
+        return None
+    return hit[1]
+
+
+def pinned(tag, shape, dtype):
+    k = (tag, tuple(shape), dtype)
+    t = _PINNED.get(k)
+    if t is None:
+        t = _PINNED[k] = torch.empty(*shape, dtype=dtype).pin_memory()
+    return t
+
+
+def t2n(x, tag="t2n"):
+    """Drop-in for the reference's `_t2n(x)` = x.detach().cpu().numpy() (runner/shared/mpe_runner.py:8-9): one
+    asynchronous copy into a reused PINNED buffer + one stream synchronise, and the result is registered as the twin
+    of `x`, so that handing it back (buffer.insert) costs a device -> device copy.  `tag` separates arrays of equal
+    shape that are alive at the same time (values / log-probs)."""
+    x = x.detach()
+    if not x.is_cuda:
+        return x.numpy()
+    h = pinned(tag, x.shape, x.dtype)
+    h.copy_(x, non_blocking=True)
+    torch.cuda.current_stream(x.device).synchronize()
+    register(h, x)
+    return h.numpy()

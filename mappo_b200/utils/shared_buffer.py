@@ -34,6 +34,12 @@ def _act_shape(space):
 
 
 def _dev(x, device):
+    """Host array / tensor -> float32 device tensor.  An array the library itself produced from a device tensor (the
+    vec env's host outputs, host_mirror.t2n) is served by its device twin instead of a PCIe copy."""
+    from .. import host_mirror
+    twin = host_mirror.lookup(x)
+    if twin is not None and twin.device == torch.device(device):
+        return twin if twin.dtype == torch.float32 else twin.to(torch.float32)
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(x)
     return x.to(device=device, dtype=torch.float32, non_blocking=True)

@@ -1,0 +1,100 @@
+"""GPU: the host-array boundary (what bench.py's `e2e` drives): pass-through of arrays the library itself brought out
+of the device (mappo_b200/host_mirror.py), the ordinary host -> device path for any other array, and the one-launch
+one-hot -> id decode (mappo_onehot_to_ids) against the reference's np.eye(n)[actions] convention
+(runner/shared/mpe_runner.py:110-121)."""
+import types
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _env_and_buffer(N=64, scenario="simple_spread", M=3):
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    from mappo_b200.utils.shared_buffer import SharedReplayBuffer
+    a = parse_args(("--scenario_name %s --num_agents %d --num_landmarks 3 --n_rollout_threads %d --episode_length 25"
+                    % (scenario, M, N)).split())
+    env = MPEVecEnv(a, device="cuda:0", host_io=True)
+    buf = SharedReplayBuffer(a, M, env.observation_space[0], env.share_observation_space[0], env.action_space[0], device="cuda:0")
+    return a, env, buf
+
+
+def test_pass_through_and_ordinary_host_arrays_give_the_same_buffer():
+    from mappo_b200 import host_mirror
+    a, env, buf = _env_and_buffer()
+    N, M = 64, 3
+    env.reset()
+    rng = np.random.RandomState(0)
+    ids = rng.randint(0, 5, (N, M))
+    obs, rew, dones, infos = env.step(np.eye(5)[ids])                        # float64 one-hot, like the reference
+    assert isinstance(obs, np.ndarray) and host_mirror.lookup(obs) is not None and host_mirror.lookup(rew) is not None
+    zeros = np.zeros((N, M, 1), np.float32)
+    share = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))
+    # (1) the registered arrays themselves: served device -> device
+    buf.insert(share, obs, None, None, zeros, zeros, zeros, rew, 1.0 - dones[..., None].astype(np.float32))
+    got1, r1 = buf.obs[1].cpu().numpy().copy(), buf.rewards[0].cpu().numpy().copy()
+    np.testing.assert_array_equal(got1, obs); np.testing.assert_array_equal(r1, rew)
+    # (2) a DIFFERENT host array with different contents takes the host -> device path and round-trips
+    other = obs.copy() + 1.0
+    assert host_mirror.lookup(other) is None
+    buf.step = 0
+    buf.insert(share, other, None, None, zeros, zeros, zeros, rew.copy() * 2, zeros + 1)
+    np.testing.assert_array_equal(buf.obs[1].cpu().numpy(), other)
+    np.testing.assert_array_equal(buf.rewards[0].cpu().numpy(), rew * 2)
+    # (3) an in-place edit of a registered array must be declared: forget() sends it over PCIe again
+    obs += 3.0
+    host_mirror.forget(obs)
+    buf.step = 0
+    buf.insert(share, obs, None, None, zeros, zeros, zeros, rew, zeros + 1)
+    np.testing.assert_array_equal(buf.obs[1].cpu().numpy(), obs)
+
+
+def test_t2n_twin_feeds_insert_and_env_step():
+    from mappo_b200 import host_mirror
+    a, env, buf = _env_and_buffer()
+    N, M = 64, 3
+    env.reset()
+    dev_actions = torch.randint(0, 5, (N, M, 1), device="cuda:0")
+    dev_vals = torch.randn(N, M, 1, device="cuda:0")
+    acts, vals = host_mirror.t2n(dev_actions, "actions"), host_mirror.t2n(dev_vals, "values")
+    assert acts.dtype == np.int64 and (acts == dev_actions.cpu().numpy()).all()
+    assert host_mirror.lookup(acts) is dev_actions and host_mirror.lookup(vals) is dev_vals
+    obs, rew, dones, _ = env.step(acts)                                     # ids form, served by the twin
+    env2_ids = env._ids_scratch if env._ids_scratch is not None else None
+    zeros = np.zeros((N, M, 1), np.float32)
+    buf.insert(None, obs, None, None, acts, zeros, vals, rew, zeros + 1)
+    np.testing.assert_array_equal(buf.actions[0].cpu().numpy(), acts.astype(np.float32))
+    np.testing.assert_array_equal(buf.value_preds[0].cpu().numpy(), vals)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.float32, np.float64])
+def test_onehot_decode_equals_argmax(dtype):
+    from mappo_b200 import gather
+    rng = np.random.RandomState(1)
+    rows = 100_003
+    for sizes in ([5], [5, 10], [3]):
+        ids = np.stack([rng.randint(0, s, rows) for s in sizes], -1)
+        oh = np.concatenate([np.eye(s)[ids[:, h]] for h, s in enumerate(sizes)], -1).astype(dtype)
+        out = torch.full((rows, len(sizes) + 1), -1.0, device="cuda:0")
+        gather.onehot_to_ids(torch.from_numpy(oh).cuda(), sizes, out)
+        np.testing.assert_array_equal(out[:, :len(sizes)].cpu().numpy(), ids.astype(np.float32))
+        assert (out[:, len(sizes)] == -1).all()
+
+
+def test_env_step_accepts_every_one_hot_dtype_and_ids():
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    a = types.SimpleNamespace(scenario_name="simple_reference", num_agents=2, num_landmarks=3, episode_length=25,
+                              n_rollout_threads=32, seed=4)
+    rng = np.random.RandomState(2)
+    ids = np.stack([rng.randint(0, 5, (32, 2)), rng.randint(0, 10, (32, 2))], -1)           # MultiDiscrete [5, 10]
+    oh = np.concatenate([np.eye(5)[ids[..., 0]], np.eye(10)[ids[..., 1]]], -1)
+    outs = []
+    for arg in (ids.astype(np.float32), oh, oh.astype(np.float32), oh.astype(np.uint8), torch.as_tensor(oh).cuda()):
+        env = MPEVecEnv(a, device="cuda:0", host_io=True)
+        env.reset()
+        outs.append(env.step(arg)[0].copy())
+    for o in outs[1:]:
+        np.testing.assert_array_equal(o, outs[0])
