@@ -238,18 +238,19 @@ def host_boundary_iteration(runner, envs, hb):
         # cent_obs = the buffer's share_obs slot [N, M, S] (its M rows per env are one stored row: R_Critic.forward
         # evaluates each env once); the reference passes np.concatenate of the same slot (mpe_runner.py:99)
         values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step], b.obs[step].view(N * M, -1), None, None, None)
-        values = host_mirror.t2n(values.view(N, M, 1), "values")          # mpe_runner.py:102-104: np.split(_t2n(.))
-        actions = host_mirror.t2n(actions.view(N, M, 1), "actions")
-        logp = host_mirror.t2n(logp.view(N, M, 1), "logp")
+        out = host_mirror.t2n_many({"values": values.view(N, M, 1), "actions": actions.view(N, M, 1),
+                                    "logp": logp.view(N, M, 1)})          # mpe_runner.py:102-104: np.split(_t2n(.))
+        values, actions, logp = out["values"], out["actions"], out["logp"]
         d2h += values.nbytes + actions.nbytes + logp.nbytes
-        oh = hb["onehot"]                                                # mpe_runner.py:110-121 (np.eye(n)[actions]) as a
-        oh.zero_().scatter_(2, torch.from_numpy(actions), 1)             # scatter into a pinned uint8 array
-        actions_env = oh.numpy()
+        actions_env = hb["onehot"].numpy()                               # mpe_runner.py:110-121 (np.eye(n)[actions]):
+        flat = actions_env.reshape(-1)                                   # uint8 one-hot written into a pinned array
+        flat[:] = 0
+        flat[hb["row5"] + actions.reshape(-1)] = 1
         obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
         h2d += actions_env.nbytes
         d2h += obs.nbytes + rewards.nbytes + dones.nbytes + N * M * 4    # + the individual rewards behind `infos`
         masks = hb["masks"].numpy()
-        np.subtract(1.0, dones[..., None], out=masks)                    # mpe_runner.py:128-131 (masks[dones] = 0)
+        masks[..., 0] = ~dones                                           # mpe_runner.py:128-131 (masks[dones] = 0)
         share_obs = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))   # :133-137 (a view)
         h2d += crossing(obs) + crossing(actions) + crossing(logp) + crossing(values) + crossing(rewards) + crossing(masks)
         b.insert(share_obs, obs, None, None, actions, logp, values, rewards, masks)
@@ -398,7 +399,9 @@ def run_ours(ns):
     # ---- e2e: host buffers at the reference-facing boundary
     envs.set_host_io(True)
     pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
-    hb = {"onehot": pin(n_envs, M_AGENTS, N_ACT, dt=torch.uint8), "masks": pin(n_envs, M_AGENTS, 1)}
+    import numpy as _np
+    hb = {"onehot": pin(n_envs, M_AGENTS, N_ACT, dt=torch.uint8), "masks": pin(n_envs, M_AGENTS, 1),
+          "row5": _np.arange(n_envs * M_AGENTS, dtype=_np.int64) * N_ACT}
     host_boundary_iteration(runner, envs, hb)               # warm-up of the host path
     barrier()
     e_steps = max(1, min(ns.steps, ns.e2e_steps))

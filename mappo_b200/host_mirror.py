@@ -64,6 +64,20 @@ def pinned(tag, shape, dtype):
     return t
 
 
+def t2n_many(named):
+    """Several `_t2n` calls under ONE stream synchronise: named = {tag: cuda tensor} -> {tag: numpy array}."""
+    out, dev = {}, None
+    for tag, x in named.items():
+        x = x.detach()
+        h = pinned(tag, x.shape, x.dtype)
+        h.copy_(x, non_blocking=True)
+        register(h, x)
+        out[tag], dev = h.numpy(), x.device
+    if dev is not None:
+        torch.cuda.current_stream(dev).synchronize()
+    return out
+
+
 def t2n(x, tag="t2n"):
     """Drop-in for the reference's `_t2n(x)` = x.detach().cpu().numpy() (runner/shared/mpe_runner.py:8-9): one
     asynchronous copy into a reused PINNED buffer + one stream synchronise, and the result is registered as the twin

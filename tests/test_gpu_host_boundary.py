@@ -61,7 +61,8 @@ def test_t2n_twin_feeds_insert_and_env_step():
     dev_vals = torch.randn(N, M, 1, device="cuda:0")
     acts, vals = host_mirror.t2n(dev_actions, "actions"), host_mirror.t2n(dev_vals, "values")
     assert acts.dtype == np.int64 and (acts == dev_actions.cpu().numpy()).all()
-    assert host_mirror.lookup(acts) is dev_actions and host_mirror.lookup(vals) is dev_vals
+    assert host_mirror.lookup(acts).data_ptr() == dev_actions.data_ptr()
+    assert host_mirror.lookup(vals).data_ptr() == dev_vals.data_ptr()
     obs, rew, dones, _ = env.step(acts)                                     # ids form, served by the twin
     env2_ids = env._ids_scratch if env._ids_scratch is not None else None
     zeros = np.zeros((N, M, 1), np.float32)

@@ -18,7 +18,8 @@ def main():
     envs.set_host_io(True)
     M = bench.M_AGENTS
     pin = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt).pin_memory()
-    hb = {"onehot": pin(n_envs, M, bench.N_ACT, dt=torch.uint8), "masks": pin(n_envs, M, 1)}
+    hb = {"onehot": pin(n_envs, M, bench.N_ACT, dt=torch.uint8), "masks": pin(n_envs, M, 1),
+          "row5": np.arange(n_envs * M, dtype=np.int64) * bench.N_ACT}
     from mappo_b200 import host_mirror
     bench.host_boundary_iteration(runner, envs, hb)
     b, pol = runner.buffer, runner.trainer.policy
@@ -40,14 +41,15 @@ def main():
         t0 = time.perf_counter()
         values, actions, logp, rs, rsc = pol.get_actions(b.share_obs[step], b.obs[step].view(N * M, -1), None, None, None)
         tick("policy", t0); t0 = time.perf_counter()
-        values = host_mirror.t2n(values.view(N, M, 1), "values"); actions = host_mirror.t2n(actions.view(N, M, 1), "actions")
-        logp = host_mirror.t2n(logp.view(N, M, 1), "logp")
+        out = host_mirror.t2n_many({"values": values.view(N, M, 1), "actions": actions.view(N, M, 1), "logp": logp.view(N, M, 1)})
+        values, actions, logp = out["values"], out["actions"], out["logp"]
         tick("d2h policy outputs (t2n)", t0); t0 = time.perf_counter()
-        actions_env = hb["onehot"].zero_().scatter_(2, torch.from_numpy(actions), 1).numpy()
+        actions_env = hb["onehot"].numpy()
+        flat = actions_env.reshape(-1); flat[:] = 0; flat[hb["row5"] + actions.reshape(-1)] = 1
         tick("host one-hot (uint8)", t0); t0 = time.perf_counter()
         obs, rewards, dones, infos = envs.step(actions_env)
         tick("envs.step (h2d + kernel + d2h)", t0); t0 = time.perf_counter()
-        masks = hb["masks"].numpy(); np.subtract(1.0, dones[..., None], out=masks)
+        masks = hb["masks"].numpy(); masks[..., 0] = ~dones
         share_obs = np.broadcast_to(obs.reshape(N, 1, -1), (N, M, obs.shape[-1] * M))
         tick("host masks", t0); t0 = time.perf_counter()
         b.insert(share_obs, obs, None, None, actions, logp, values, rewards, masks)
