@@ -320,6 +320,57 @@ def dp_check(device, rank, world, dist, n_small=512):
     return out
 
 
+def run_c5(ns, device, rank, world, dist, peaks):
+    """The north_star target beside the contract line: BASELINE config C5 -- simple_spread with 10 agents, 16,384 envs
+    per GPU (1,310,720 concurrent agents on 8 GPUs), shared MLP policy, centralised critic over 460 columns, NCCL
+    gradient all-reduce -- timed like the contract line (device-resident runner, CUDA events, max over ranks), with
+    its own per-kernel roofline list.  Returns the dict printed under the key `c5` (rank 0) or None."""
+    import torch
+    from mappo_b200 import ops
+    saved = (M_AGENTS, D_OBS, S_OBS, SCENARIO, ALGO, SEPARATED, PPO_EPOCH, CONFIG)
+    set_workload(10, "c5")
+    n_envs, steps, warm = ns.c5_envs, max(3, min(ns.steps, 5)), 2
+    try:
+        _, envs, runner = build_runner(n_envs, device, rank, world)
+        runner.warmup()
+        for _ in range(warm):
+            runner.run_episode()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ops.TIMERS.reset(); ops.TIMERS.enabled = True
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            info = runner.run_episode()
+        e1.record()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+        if dist is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms.item())
+        ops.TIMERS.enabled = False
+        kt = ops.TIMERS.summary()
+        if rank != 0:
+            return None
+        agent_steps = n_envs * T_EP * M_AGENTS
+        tr = runner.trainer
+        ws0 = next(iter(tr._ws.values()))
+        kernels = kernel_rooflines(kt, n_envs, steps, peaks, ws0["nba"], ws0["nbc"], tr.policy.actor.flat.numel(),
+                                   tr.policy.critic.flat.numel())
+        return {"workload": workload_name(n_envs, world), "value": agent_steps * world * steps / (ms * 1e-3), "unit": UNIT,
+                "ms_per_step": ms / steps, "steps": steps, "warmup": warm, "concurrent_agents": n_envs * M_AGENTS * world,
+                "agent_steps_per_step": agent_steps * world, "kernels": kernels,
+                "kernels_share_of_step": sum(e["ms_per_step"] for e in kernels) / (ms / steps),
+                "note": "critic_update spans the wide first layer's three kernels (fc1 GEMM on packed tiles, fused 64-wide "
+                        "kernel, fc1 weight-gradient GEMM; DESIGN.md 4.2); the first and last are HBM-bound streams",
+                "train_info": info}
+    finally:
+        globals().update(dict(zip(("M_AGENTS", "D_OBS", "S_OBS", "SCENARIO", "ALGO", "SEPARATED", "PPO_EPOCH", "CONFIG"), saved)))
+
+
 def run_ours(ns):
     import torch
     from mappo_b200 import _lib, ops
@@ -419,17 +470,20 @@ def run_ours(ns):
     e2e_wall_s = time.perf_counter() - t0                      # the e2e leg alone (the CPU legs run later)
     envs.set_host_io(False)
 
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    c5 = None
+    if CONFIG == "C2" and (ns.c5 or world >= 8):
+        c5 = run_c5(ns, device, rank, world, dist, peaks)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
 
     # ---- roofline of the dominant kernel (see DESIGN.md "Kernels" for the per-row work)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
     rows = agent_steps                                        # one actor_update launch covers the whole batch
     flop_row = actor_update_flops_per_row()
     n, tot = kt.get("actor_update", (0, 0.0))
@@ -486,6 +540,8 @@ def run_ours(ns):
            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_port": cpu_port,
            "kernel_ms_per_step": share,
            "clocks": clocks, "train_info": info}
+    if c5 is not None:
+        out["c5"] = c5
     if dp is not None:
         out["dp_check"] = dp
         out["collective"] = "NCCL all-reduce (torch.distributed): gradient sums + loss sums per ppo_update, advantage and ValueNorm moments once per iteration"
@@ -584,6 +640,9 @@ def main():
                     help="timed iterations of the port's leg (about 5 s on 16 cores)")
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=5)
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
+    ap.add_argument("--c5", action="store_true", help="also measure BASELINE config C5 (10 agents) and print it under the "
+                                                      "key `c5`; on by default at 8 GPUs (the north_star target)")
+    ap.add_argument("--c5-envs", dest="c5_envs", type=int, default=16384, help="envs per GPU of the C5 measurement")
     ap.add_argument("--no-dp-check", dest="no_dp_check", action="store_true")
     ap.add_argument("--dp-check-only", dest="dp_check_only", action="store_true",
                     help="under torchrun: run the multi-rank parity check, print it and exit (tests/test_gpu_dist.py)")

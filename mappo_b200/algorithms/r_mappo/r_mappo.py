@@ -51,9 +51,11 @@ class R_MAPPO:
         self._info = torch.zeros(8, **self.tpdv)       # actor {loss, gnorm, entropy, ratio}, critic {loss, gnorm, -, -}
         self._info_total = torch.zeros(8, **self.tpdv)
 
-    def set_all_reduce(self, fn, world_size):
-        """Data-parallel update: `fn(tensor)` sums a CUDA tensor in place over the ranks (NCCL all-reduce)."""
+    def set_all_reduce(self, fn, world_size, many=None):
+        """Data-parallel update: `fn(tensor)` sums a CUDA tensor in place over the ranks (NCCL all-reduce); `many(list)`
+        does the same for several tensors as one coalesced collective (default: one `fn` call each)."""
         self.all_reduce = fn
+        self.all_reduce_many = many if many is not None else (lambda ts: [fn(t) for t in ts])
         self.world_size = int(world_size)
         if self.value_normalizer is not None:
             self.value_normalizer.all_reduce = fn
@@ -115,7 +117,7 @@ class R_MAPPO:
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows_a
         if self.all_reduce is not None:
-            self.all_reduce(ws["gsum"]); self.all_reduce(ws["lsum"])
+            self.all_reduce_many([ws["gsum"], ws["lsum"]])
             rows_global = rows_a * self.world_size
         self._info.zero_()
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer
@@ -175,7 +177,7 @@ class R_MAPPO:
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows
         if self.all_reduce is not None:
-            self.all_reduce(ws["gsum"]); self.all_reduce(ws["lsum"])
+            self.all_reduce_many([ws["gsum"], ws["lsum"]])
             rows_global = rows * self.world_size
         self._info.zero_()
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer
