@@ -544,7 +544,9 @@ def run_ours(ns):
         out["c5"] = c5
     if dp is not None:
         out["dp_check"] = dp
-        out["collective"] = "NCCL all-reduce (torch.distributed): gradient sums + loss sums per ppo_update, advantage and ValueNorm moments once per iteration"
+        out["collective"] = ("NCCL all-reduce (torch.distributed): ONE float64 buffer [actor grad sums | critic grad sums | "
+                             "8 loss sums] per ppo_update; advantage moments and ValueNorm batch moments (3 doubles each) "
+                             "once per iteration")
     print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()

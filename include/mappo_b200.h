@@ -398,6 +398,12 @@ int mappo_critic_update_rnn(const mappo_net_config* cfg, const mappo_loss_config
 int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
                       float* grad_sum, double* loss_sum, void* stream);
 
+/* The same with grad_sum in float64: a data-parallel job keeps [actor gradient sums | critic gradient sums | the two
+ * double[4] loss sums] in ONE float64 buffer, so that a ppo_update needs ONE all-reduce instead of one
+ * per dtype; mappo_adam_step_f64 reads it.  (ABI v6.) */
+int mappo_grad_reduce_f64(const float* grad_partials, const double* loss_partials, int blocks, long long P,
+                          double* grad_sum, double* loss_sum, void* stream);
+
 typedef struct {
   float lr, beta1, beta2, eps, weight_decay;
   float max_grad_norm;         /* args.max_grad_norm */
@@ -428,6 +434,11 @@ int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_config* adam, 
                     float* exp_avg_sq, const float* grad_sum, const double* loss_sum, int denominator_slot,
                     long long rows_total, int apply_update, float* grad_out, float* info_out, long long* step_dev,
                     void* stream);
+
+int mappo_adam_step_f64(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params, float* exp_avg,
+                        float* exp_avg_sq, const double* grad_sum, const double* loss_sum, int denominator_slot,
+                        long long rows_total, int apply_update, float* grad_out, float* info_out, long long* step_dev,
+                        void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 4. Minibatch gather (the generator API; the update kernels take `index` and gather in place).

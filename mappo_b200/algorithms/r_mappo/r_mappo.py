@@ -51,11 +51,10 @@ class R_MAPPO:
         self._info = torch.zeros(8, **self.tpdv)       # actor {loss, gnorm, entropy, ratio}, critic {loss, gnorm, -, -}
         self._info_total = torch.zeros(8, **self.tpdv)
 
-    def set_all_reduce(self, fn, world_size, many=None):
-        """Data-parallel update: `fn(tensor)` sums a CUDA tensor in place over the ranks (NCCL all-reduce); `many(list)`
-        does the same for several tensors as one coalesced collective (default: one `fn` call each)."""
+    def set_all_reduce(self, fn, world_size):
+        """Data-parallel update: `fn(tensor)` sums a CUDA tensor in place over the ranks (NCCL all-reduce)."""
         self.all_reduce = fn
-        self.all_reduce_many = many if many is not None else (lambda ts: [fn(t) for t in ts])
+        self._ws = {}                       # the reduce buffers are laid out differently with a collective attached
         self.world_size = int(world_size)
         if self.value_normalizer is not None:
             self.value_normalizer.all_reduce = fn
@@ -79,9 +78,15 @@ class R_MAPPO:
                       gpc=torch.empty(nbc, Pc, dtype=torch.float32, device=dev),
                       lpa=torch.empty(nba, 4, dtype=torch.float64, device=dev),
                       lpc=torch.empty(nbc, 4, dtype=torch.float64, device=dev),
-                      gsum=torch.empty(Pa + Pc, dtype=torch.float32, device=dev),
-                      lsum=torch.empty(8, dtype=torch.float64, device=dev),
                       grad=torch.empty(Pa + Pc, dtype=torch.float32, device=dev))
+            if self.all_reduce is not None:
+                # data parallel: [actor grad sums | critic grad sums | 2 x 4 loss sums] in ONE float64 buffer -> one
+                # all-reduce per ppo_update (the reduce kernel writes it, mappo_adam_step_f64 reads it)
+                ws["red"] = torch.empty(Pa + Pc + 8, dtype=torch.float64, device=dev)
+                ws["gsum"], ws["lsum"] = ws["red"][:Pa + Pc], ws["red"][Pa + Pc:]
+            else:
+                ws.update(gsum=torch.empty(Pa + Pc, dtype=torch.float32, device=dev),
+                          lsum=torch.empty(8, dtype=torch.float64, device=dev))
             if ops.GRAPH_PINNED:        # a captured graph replays the pointers of the workspace it was recorded with
                 self._ws[key] = ws
             else:
@@ -117,7 +122,7 @@ class R_MAPPO:
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows_a
         if self.all_reduce is not None:
-            self.all_reduce_many([ws["gsum"], ws["lsum"]])
+            self.all_reduce(ws["red"])
             rows_global = rows_a * self.world_size
         self._info.zero_()
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer
@@ -177,7 +182,7 @@ class R_MAPPO:
         ops.grad_reduce(ws["gpc"], ws["lpc"], ws["nbc"], gsc, lsc)
         rows_global = rows
         if self.all_reduce is not None:
-            self.all_reduce_many([ws["gsum"], ws["lsum"]])
+            self.all_reduce(ws["red"])
             rows_global = rows * self.world_size
         self._info.zero_()
         aopt, copt = pol.actor_optimizer, pol.critic_optimizer

@@ -9,9 +9,10 @@ namespace mappo {
 // column sums over the per-CTA partial rows, fixed order (deterministic): 32 row slices per column are summed
 // independently (rows s, s + 32, ...: ~10 loads in flight per thread at 296 partial rows) and combined in slice order
 constexpr int kRedSlices = 32, kRedCols = 32;
+template <typename GT>
 __global__ void __launch_bounds__(kRedSlices * kRedCols)
 grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, int blocks, long long P,
-                   float* __restrict__ gsum, double* __restrict__ lsum) {
+                   GT* __restrict__ gsum, double* __restrict__ lsum) {
   __shared__ float part[kRedSlices][kRedCols];
   const int c = threadIdx.x % kRedCols, sl = threadIdx.x / kRedCols;
   const long long e = blockIdx.x * (long long)kRedCols + c;
@@ -24,7 +25,7 @@ grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, 
     float t = part[0][c];
 #pragma unroll
     for (int q = 1; q < kRedSlices; ++q) t += part[q][c];
-    gsum[e] = t;
+    gsum[e] = (GT)t;
   }
   if (blockIdx.x == 0 && threadIdx.x < 4) {
     double t = 0.0;
@@ -36,15 +37,17 @@ grad_reduce_kernel(const float* __restrict__ gp, const double* __restrict__ lp, 
 constexpr int kOptThreads = 1024;
 
 // one Linear's slots: dW[j][k] = g[k] G[j][k] + be[k] db[j];  dg[k] = sum_j W[j][k] G[j][k];  dbe[k] = sum_j W[j][k] db[j]
-__device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const float* __restrict__ G, float* __restrict__ out,
+template <typename GT>
+__device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const GT* __restrict__ G, float* __restrict__ out,
                                               int w_off, int b_off, int rows, int cols, int g_off, int be_off,
                                               bool accumulate_affine) {
   const int tid = threadIdx.x;
   for (int e = tid; e < rows * cols; e += kOptThreads) {
     const int j = e / cols, k = e - j * cols;
-    out[w_off + e] = (g_off >= 0) ? fmaf(P[g_off + k], G[w_off + e], P[be_off + k] * G[b_off + j]) : G[w_off + e];
+    out[w_off + e] = (g_off >= 0) ? fmaf(P[g_off + k], (float)G[w_off + e], P[be_off + k] * (float)G[b_off + j])
+                                  : (float)G[w_off + e];
   }
-  for (int j = tid; j < rows; j += kOptThreads) out[b_off + j] = G[b_off + j];
+  for (int j = tid; j < rows; j += kOptThreads) out[b_off + j] = (float)G[b_off + j];
   if (g_off >= 0) {
     // 64 columns at a time, 16 row slices per column (rows s, s + 16, ...), combined in slice order
     __shared__ float pdg[16][64], pdbe[16][64];
@@ -55,8 +58,8 @@ __device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const
       if (k < cols) {
         for (int j = sl; j < rows; j += 16) {
           const float w = P[w_off + j * cols + k];
-          dg = fmaf(w, G[w_off + j * cols + k], dg);
-          dbe = fmaf(w, G[b_off + j], dbe);
+          dg = fmaf(w, (float)G[w_off + j * cols + k], dg);
+          dbe = fmaf(w, (float)G[b_off + j], dbe);
         }
       }
       pdg[sl][kk] = dg; pdbe[sl][kk] = dbe;
@@ -73,9 +76,10 @@ __device__ __forceinline__ void unfold_linear(const float* __restrict__ P, const
   }
 }
 
+template <typename GT>
 __global__ void __launch_bounds__(kOptThreads)
 adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restrict__ params, float* __restrict__ m,
-                 float* __restrict__ v, const float* __restrict__ gsum, const double* __restrict__ lsum,
+                 float* __restrict__ v, const GT* __restrict__ gsum, const double* __restrict__ lsum,
                  int denom_slot, long long rows_total, int apply_update, float* __restrict__ g, float* info,
                  long long* step_dev) {
   const int tid = threadIdx.x;
@@ -169,12 +173,40 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
 
 using namespace mappo;
 
-extern "C" int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
-                                 float* grad_sum, double* loss_sum, void* stream) {
+template <typename GT>
+static int grad_reduce_any(const float* grad_partials, const double* loss_partials, int blocks, long long P, GT* grad_sum,
+                           double* loss_sum, void* stream) {
   MAPPO_REQUIRE(grad_partials && loss_partials && grad_sum && loss_sum && blocks > 0 && P > 0, "grad_reduce: bad arguments");
-  grad_reduce_kernel<<<ceil_div(P, kRedCols), kRedSlices * kRedCols, 0, (cudaStream_t)stream>>>(
+  grad_reduce_kernel<GT><<<ceil_div(P, kRedCols), kRedSlices * kRedCols, 0, (cudaStream_t)stream>>>(
       grad_partials, loss_partials, blocks, P, grad_sum, loss_sum);
   MAPPO_CHECK_LAUNCH("grad_reduce_kernel");
+  return 0;
+}
+
+extern "C" int mappo_grad_reduce(const float* grad_partials, const double* loss_partials, int blocks, long long P,
+                                 float* grad_sum, double* loss_sum, void* stream) {
+  return grad_reduce_any<float>(grad_partials, loss_partials, blocks, P, grad_sum, loss_sum, stream);
+}
+
+extern "C" int mappo_grad_reduce_f64(const float* grad_partials, const double* loss_partials, int blocks, long long P,
+                                     double* grad_sum, double* loss_sum, void* stream) {
+  return grad_reduce_any<double>(grad_partials, loss_partials, blocks, P, grad_sum, loss_sum, stream);
+}
+
+template <typename GT>
+static int adam_step_any(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params, float* exp_avg,
+                         float* exp_avg_sq, const GT* grad_sum, const double* loss_sum, int denominator_slot,
+                         long long rows_total, int apply_update, float* grad_out, float* info_out, long long* step_dev,
+                         void* stream) {
+  if (int rc = check_net(cfg, "adam_step")) return rc;
+  MAPPO_REQUIRE(adam && params && grad_sum && loss_sum && grad_out, "adam_step: null pointer (grad_out is required)");
+  MAPPO_REQUIRE(!apply_update || (exp_avg && exp_avg_sq), "adam_step: null optimiser state");
+  MAPPO_REQUIRE(denominator_slot >= 0 && denominator_slot < 4 && rows_total > 0, "adam_step: bad denominator");
+  const NetLayout L = make_layout(*cfg);
+  adam_step_kernel<GT><<<1, kOptThreads, 0, (cudaStream_t)stream>>>(L, *adam, params, exp_avg, exp_avg_sq, grad_sum,
+                                                                   loss_sum, denominator_slot, rows_total, apply_update,
+                                                                   grad_out, info_out, step_dev);
+  MAPPO_CHECK_LAUNCH("adam_step_kernel");
   return 0;
 }
 
@@ -182,14 +214,14 @@ extern "C" int mappo_adam_step(const mappo_net_config* cfg, const mappo_adam_con
                                float* exp_avg, float* exp_avg_sq, const float* grad_sum, const double* loss_sum,
                                int denominator_slot, long long rows_total, int apply_update, float* grad_out,
                                float* info_out, long long* step_dev, void* stream) {
-  if (int rc = check_net(cfg, "adam_step")) return rc;
-  MAPPO_REQUIRE(adam && params && grad_sum && loss_sum && grad_out, "adam_step: null pointer (grad_out is required)");
-  MAPPO_REQUIRE(!apply_update || (exp_avg && exp_avg_sq), "adam_step: null optimiser state");
-  MAPPO_REQUIRE(denominator_slot >= 0 && denominator_slot < 4 && rows_total > 0, "adam_step: bad denominator");
-  const NetLayout L = make_layout(*cfg);
-  adam_step_kernel<<<1, kOptThreads, 0, (cudaStream_t)stream>>>(L, *adam, params, exp_avg, exp_avg_sq, grad_sum,
-                                                               loss_sum, denominator_slot, rows_total, apply_update,
-                                                               grad_out, info_out, step_dev);
-  MAPPO_CHECK_LAUNCH("adam_step_kernel");
-  return 0;
+  return adam_step_any<float>(cfg, adam, params, exp_avg, exp_avg_sq, grad_sum, loss_sum, denominator_slot, rows_total,
+                              apply_update, grad_out, info_out, step_dev, stream);
+}
+
+extern "C" int mappo_adam_step_f64(const mappo_net_config* cfg, const mappo_adam_config* adam, float* params,
+                                   float* exp_avg, float* exp_avg_sq, const double* grad_sum, const double* loss_sum,
+                                   int denominator_slot, long long rows_total, int apply_update, float* grad_out,
+                                   float* info_out, long long* step_dev, void* stream) {
+  return adam_step_any<double>(cfg, adam, params, exp_avg, exp_avg_sq, grad_sum, loss_sum, denominator_slot, rows_total,
+                               apply_update, grad_out, info_out, step_dev, stream);
 }

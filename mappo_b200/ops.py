@@ -174,7 +174,9 @@ _lib._EXTRA_SIGS.update({
                             _P],
     "mappo_critic_pack_inputs": [_NC, _P, C.c_int, C.c_longlong, _P, _P, _P],
     "mappo_grad_reduce": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
+    "mappo_grad_reduce_f64": [_P, _P, C.c_int, C.c_longlong, _P, _P, _P],
     "mappo_adam_step": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P],
+    "mappo_adam_step_f64": [_NC, _AC, _P, _P, _P, _P, _P, C.c_int, C.c_longlong, C.c_int, _P, _P, _P, _P],
 })
 
 
@@ -413,8 +415,9 @@ def critic_update(cfg, loss, params, share_obs, value_preds, returns, active_mas
 
 
 def grad_reduce(grad_partials, loss_partials, blocks, grad_sum, loss_sum):
+    fn = _lib.lib().mappo_grad_reduce_f64 if grad_sum.dtype == torch.float64 else _lib.lib().mappo_grad_reduce
     with TIMERS.span("grad_reduce"):
-        check(_lib.lib().mappo_grad_reduce(ptr(grad_partials), ptr(loss_partials), int(blocks), grad_sum.numel(),
+        check(fn(ptr(grad_partials), ptr(loss_partials), int(blocks), grad_sum.numel(),
                                            ptr(grad_sum), ptr(loss_sum), stream_ptr()), "grad_reduce")
 
 
@@ -422,8 +425,9 @@ def adam_step(cfg, adam, params, exp_avg, exp_avg_sq, grad_sum, loss_sum, denomi
               info_out=None, apply_update=True, step_dev=None):
     """step_dev: int64 device scalar holding the optimiser step count (read for the bias corrections and incremented
     by the kernel), or None for the host-computed corrections in `adam`."""
+    fn = _lib.lib().mappo_adam_step_f64 if grad_sum.dtype == torch.float64 else _lib.lib().mappo_adam_step
     with TIMERS.span("adam_step"):
-        check(_lib.lib().mappo_adam_step(C.byref(cfg), C.byref(adam), ptr(params), ptr(exp_avg), ptr(exp_avg_sq),
+        check(fn(C.byref(cfg), C.byref(adam), ptr(params), ptr(exp_avg), ptr(exp_avg_sq),
                                          ptr(grad_sum), ptr(loss_sum), int(denominator_slot), int(rows_total),
                                          int(apply_update), ptr(grad_out), ptr(info_out), ptr(step_dev), stream_ptr()),
               "adam_step")

@@ -4,9 +4,10 @@ the GPUs; gloo in the CPU tests).
 The reference has no counterpart (single device).  What shards and what is exchanged:
   * envs: rank r owns the global env ids [r*N, (r+1)*N); reset draws are Philox streams keyed by the GLOBAL env id, so
     a rollout does not depend on how the envs are sharded; no exchange during rollout, insert or GAE;
-  * update: parameters and Adam state are replicated; per `ppo_update` the ranks sum (all-reduce) ONE flat fp32 buffer
-    [actor grads | critic grads] of UNNORMALISED gradient sums and one double[8] of loss sums / active counts, then
-    every rank divides by the global count, clips and steps identically (mappo_adam_step);
+  * update: parameters and Adam state are replicated; per `ppo_update` the ranks sum (all-reduce) ONE flat float64
+    buffer [actor grads | critic grads | 8 loss sums / active counts] of UNNORMALISED sums (written by
+    mappo_grad_reduce_f64), then every rank divides by the global count, clips and steps identically
+    (mappo_adam_step_f64);
   * statistics: the advantage moments (double[3]: sum, sum of squares, count) once per iteration and the ValueNorm
     batch moments (double[3]) once per `ppo_update`.
 """
@@ -43,26 +44,10 @@ def sum_all_reduce():
     return fn
 
 
-def sum_all_reduce_many():
-    """callable(list of tensors): in-place sums over ranks issued as ONE coalesced collective -- on NCCL the tensors
-    (here: the fp32 gradient sums and the f64 loss sums of one ppo_update) travel in a single ncclGroupStart/End
-    launch instead of one launch each; the payloads are latency-bound, so launches are the cost."""
-    def fn(tensors):
-        if dist.get_backend() == "nccl" and hasattr(dist, "_coalescing_manager"):
-            with dist._coalescing_manager():
-                for t in tensors:
-                    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        else:
-            for t in tensors:
-                dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return tensors
-    return fn
-
-
 def attach(trainer, world):
     """Make `trainer` (R_MAPPO) data-parallel over the initialised process group."""
     if world > 1:
-        trainer.set_all_reduce(sum_all_reduce(), world, many=sum_all_reduce_many())
+        trainer.set_all_reduce(sum_all_reduce(), world)
     return trainer
 
 
