@@ -242,10 +242,7 @@ def host_boundary_iteration(runner, envs, hb):
                                     "logp": logp.view(N, M, 1)})          # mpe_runner.py:102-104: np.split(_t2n(.))
         values, actions, logp = out["values"], out["actions"], out["logp"]
         d2h += values.nbytes + actions.nbytes + logp.nbytes
-        actions_env = hb["onehot"].numpy()                               # mpe_runner.py:110-121 (np.eye(n)[actions]):
-        flat = actions_env.reshape(-1)                                   # uint8 one-hot written into a pinned array
-        flat[:] = 0
-        flat[hb["row5"] + actions.reshape(-1)] = 1
+        actions_env = host_mirror.onehot(actions, [N_ACT])               # mpe_runner.py:110-121 (np.eye(n)[actions]), uint8
         obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
         h2d += actions_env.nbytes
         d2h += obs.nbytes + rewards.nbytes + dones.nbytes + N * M * 4    # + the individual rewards behind `infos`

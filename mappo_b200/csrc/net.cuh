@@ -16,9 +16,13 @@ constexpr int kH = 64;          // hidden size this build supports
 constexpr int kMaxIn = 64;      // widest input handled by the single-chunk first layer (fp32 FMA kernels)
 constexpr int kWideFrom = 64;   // tensor-core path: from this width on the first layer runs outside the fused kernel (mlp_wide.cu)
 
+constexpr int kMaxLayerN = 3;   // mlp.py:20-28: fc2 = layer_N clones of fc_h (hidden -> hidden blocks after fc1)
+
 struct NetLayout {
   int in_dim, H, n_heads, head_dim[MAPPO_MAX_HEADS], a_total;
   int use_fn, use_relu, recurrent, is_critic;
+  int layer_N;
+  int wx[kMaxLayerN - 1], bx[kMaxLayerN - 1], gx[kMaxLayerN - 1], bex[kMaxLayerN - 1];   // fc2[1 ..] (layer_N > 1)
   // offsets into the flat buffer
   int fn_g, fn_b;               // [in] each (valid if use_fn)
   int w1, b1, g1, be1;          // fc1
@@ -38,6 +42,11 @@ __host__ __device__ inline NetLayout make_layout(const mappo_net_config& c) {
   if (c.use_feature_norm) { L.fn_g = o; o += D; L.fn_b = o; o += D; }
   L.w1 = o; o += H * D; L.b1 = o; o += H; L.g1 = o; o += H; L.be1 = o; o += H;
   L.w2 = o; o += H * H; L.b2 = o; o += H; L.g2 = o; o += H; L.be2 = o; o += H;
+  L.layer_N = c.layer_N < 1 ? 1 : (c.layer_N > kMaxLayerN ? kMaxLayerN : c.layer_N);
+  for (int l = 0; l < kMaxLayerN - 1; ++l) {
+    L.wx[l] = L.bx[l] = L.gx[l] = L.bex[l] = -1;
+    if (l + 1 < L.layer_N) { L.wx[l] = o; o += H * H; L.bx[l] = o; o += H; L.gx[l] = o; o += H; L.bex[l] = o; o += H; }
+  }
   L.wih = L.whh = L.bih = L.bhh = L.gr = L.ber = -1;
   if (c.recurrent) {
     L.wih = o; o += 3 * H * H; L.whh = o; o += 3 * H * H; L.bih = o; o += 3 * H; L.bhh = o; o += 3 * H;
@@ -56,11 +65,19 @@ __host__ __device__ inline NetLayout make_layout(const mappo_net_config& c) {
   return L;
 }
 
+// offsets of hidden block l (0 = fc2[0]) and of the LayerNorm affine that precedes the heads
+__host__ __device__ inline int layer_w(const NetLayout& L, int l) { return l == 0 ? L.w2 : L.wx[l - 1]; }
+__host__ __device__ inline int layer_b(const NetLayout& L, int l) { return l == 0 ? L.b2 : L.bx[l - 1]; }
+__host__ __device__ inline int layer_g(const NetLayout& L, int l) { return l == 0 ? L.g2 : L.gx[l - 1]; }
+__host__ __device__ inline int layer_be(const NetLayout& L, int l) { return l == 0 ? L.be2 : L.bex[l - 1]; }
+
 static inline int check_net(const mappo_net_config* c, const char* who) {
   MAPPO_REQUIRE(c, "%s: null net config", who);
   MAPPO_REQUIRE(c->in_dim > 0 && c->n_heads >= 1 && c->n_heads <= MAPPO_MAX_HEADS, "%s: bad in_dim/n_heads", who);
   if (c->hidden != kH) MAPPO_UNSUPPORTED("%s: hidden_size %d (this build: 64)", who, c->hidden);
-  if (c->layer_N != 1) MAPPO_UNSUPPORTED("%s: layer_N %d (this build: 1)", who, c->layer_N);
+  if (c->layer_N < 1 || c->layer_N > kMaxLayerN) MAPPO_UNSUPPORTED("%s: layer_N %d (this build: 1 .. %d)", who, c->layer_N, kMaxLayerN);
+  if (c->layer_N != 1 && c->recurrent) MAPPO_UNSUPPORTED("%s: layer_N %d with a recurrent network (this build: 1)", who, c->layer_N);
+  if (c->layer_N != 1 && c->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: layer_N %d with in_dim %d > %d", who, c->layer_N, c->in_dim, kMaxIn);
   int a = 0;
   for (int h = 0; h < c->n_heads; ++h) { MAPPO_REQUIRE(c->head_dim[h] >= 1, "%s: head_dim", who); a += c->head_dim[h]; }
   MAPPO_REQUIRE(a <= 16, "%s: at most 16 action logits in total", who);

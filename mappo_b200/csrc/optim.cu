@@ -87,9 +87,11 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
   // 1. chain rule through the folded affines (net.cuh)
   unfold_linear(params, gsum, g, L.w1, L.b1, H, D, L.use_fn ? L.fn_g : -1, L.fn_b, false);
   unfold_linear(params, gsum, g, L.w2, L.b2, H, H, L.g1, L.be1, false);
-  // what follows fc2's LayerNorm: the heads, or (recurrent) the GRU input weights; the GRU's own LayerNorm then
-  // precedes the heads, and W_hh sees the raw hidden state (no affine)
-  int hg = L.g2, hbe = L.be2;
+  for (int l = 1; l < L.layer_N; ++l)      // fc2[l] follows the LayerNorm of fc2[l - 1] (mlp.py:26-28)
+    unfold_linear(params, gsum, g, layer_w(L, l), layer_b(L, l), H, H, layer_g(L, l - 1), layer_be(L, l - 1), false);
+  // what follows the last hidden LayerNorm: the heads, or (recurrent) the GRU input weights; the GRU's own LayerNorm
+  // then precedes the heads, and W_hh sees the raw hidden state (no affine)
+  int hg = layer_g(L, L.layer_N - 1), hbe = layer_be(L, L.layer_N - 1);
   if (L.recurrent) {
     unfold_linear(params, gsum, g, L.wih, L.bih, 3 * H, H, L.g2, L.be2, false);
     unfold_linear(params, gsum, g, L.whh, L.bhh, 3 * H, H, -1, -1, false);

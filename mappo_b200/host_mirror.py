@@ -91,3 +91,20 @@ def t2n(x, tag="t2n"):
     torch.cuda.current_stream(x.device).synchronize()
     register(h, x)
     return h.numpy()
+
+
+def onehot(actions, head_dims, tag="onehot"):
+    """Drop-in for the runner's `np.eye(n)[actions]` (runner/shared/mpe_runner.py:110-121; MultiDiscrete: heads
+    concatenated): int64 ids [..., heads] on the host -> uint8 one-hot [..., sum(head_dims)] in a reused pinned array
+    (one C pass, mappo_host_onehot_u8).  `MPEVecEnv.step` takes it as is (1 byte per logit over PCIe)."""
+    import ctypes as C
+    from . import _lib
+    a = np.ascontiguousarray(actions, dtype=np.int64)
+    heads = len(head_dims)
+    rows = a.size // heads
+    out = pinned(tag, tuple(a.shape[:-1]) + (int(sum(head_dims)),), torch.uint8)
+    L = _lib.lib()
+    L.mappo_host_onehot_u8.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_int), C.c_void_p]
+    hd = (C.c_int * heads)(*[int(d) for d in head_dims])
+    _lib.check(L.mappo_host_onehot_u8(C.c_void_p(a.ctypes.data), rows, heads, hd, C.c_void_p(out.data_ptr())), "host_onehot_u8")
+    return out.numpy()

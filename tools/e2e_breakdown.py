@@ -44,8 +44,7 @@ def main():
         out = host_mirror.t2n_many({"values": values.view(N, M, 1), "actions": actions.view(N, M, 1), "logp": logp.view(N, M, 1)})
         values, actions, logp = out["values"], out["actions"], out["logp"]
         tick("d2h policy outputs (t2n)", t0); t0 = time.perf_counter()
-        actions_env = hb["onehot"].numpy()
-        flat = actions_env.reshape(-1); flat[:] = 0; flat[hb["row5"] + actions.reshape(-1)] = 1
+        actions_env = host_mirror.onehot(actions, [bench.N_ACT])
         tick("host one-hot (uint8)", t0); t0 = time.perf_counter()
         obs, rewards, dones, infos = envs.step(actions_env)
         tick("envs.step (h2d + kernel + d2h)", t0); t0 = time.perf_counter()
