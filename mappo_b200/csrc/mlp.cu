@@ -281,6 +281,280 @@ __global__ void __launch_bounds__(NT, 1) mlp_kernel(const MlpArgs a) {
   (void)CRITIC;
 }
 
+// ---- layer_N > 1 (mlp.py:20-28: fc2 = layer_N hidden blocks Linear -> act -> LayerNorm after fc1) -----------------------
+// The same fp32 tile algorithm with NL hidden blocks: tiles T[0 .. NL+1] (input, n after fc1, n after each block), one
+// folded weight pair per block, gradients of every block in registers.  BM = 64 rows per tile keeps NL = 3 inside
+// 227 KB of shared memory.  Off the tensor-core path on purpose: the reference's MPE scripts all run layer_N = 1.
+template <int BM, int NL>
+struct SmemDeep {
+  static constexpr int W1t = 0;                                   // [64][64]
+  static constexpr int Wt = W1t + 64 * 64;                        // [NL][64][64]  Wt[l][k][j] = W_l[j][k] g_prev[k]
+  static constexpr int Wf = Wt + NL * 64 * 64;                    // [NL][64][64]  Wf[l][j][k] (dgrad operand)
+  static constexpr int Whf = Wf + NL * 64 * 64;                   // [16][64]
+  static constexpr int b1f = Whf + kMaxA * 64;                    // [64]
+  static constexpr int bf = b1f + 64;                             // [NL][64]
+  static constexpr int bhf = bf + NL * 64;                        // [16]
+  static constexpr int T = bhf + kMaxA;                           // [NL + 2][BM][kLD]
+  static constexpr int mean = T + (NL + 2) * BM * kLD;            // [NL + 1][BM]
+  static constexpr int rstd = mean + (NL + 1) * BM;               // [NL + 1][BM]
+  static constexpr int dlog = rstd + (NL + 1) * BM;               // [BM][kDL]
+  static constexpr int total = dlog + BM * kDL;
+  static constexpr size_t bytes = sizeof(float) * (size_t)total;
+};
+
+template <int BM, int NL, bool UPDATE>
+__device__ __forceinline__ void stage_weights_deep(float* sm, const MlpArgs& a) {
+  using S = SmemDeep<BM, NL>;
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  const int D = L.in_dim, Kp = a.Kp, nt = blockDim.x, tid = threadIdx.x;
+  for (int e = tid; e < 64 * 64; e += nt) {
+    const int j = e & 63, k = e >> 6;
+    float v = 0.0f;
+    if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+    if (k < Kp) sm[S::W1t + k * 64 + j] = v;
+    for (int l = 0; l < NL; ++l) {
+      const int gprev = l == 0 ? L.g1 : layer_g(L, l - 1);
+      const float w = P[layer_w(L, l) + j * 64 + k] * P[gprev + k];
+      sm[S::Wt + l * 4096 + k * 64 + j] = w;
+      if (UPDATE) sm[S::Wf + l * 4096 + j * 64 + k] = w;
+    }
+  }
+  const int glast = layer_g(L, NL - 1), belast = layer_be(L, NL - 1);
+  for (int e = tid; e < kMaxA * 64; e += nt) {
+    const int aidx = e >> 6, k = e & 63;
+    float v = 0.0f;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    if (h < L.n_heads) v = P[L.wh[h] + (aidx - off) * 64 + k] * P[glast + k];
+    sm[S::Whf + aidx * 64 + k] = v;
+  }
+  if (tid < 64) {
+    const int j = tid;
+    float s1 = P[L.b1 + j];
+    if (L.use_fn) for (int k = 0; k < D; ++k) s1 = fmaf(P[L.w1 + j * D + k], P[L.fn_b + k], s1);
+    sm[S::b1f + j] = s1;
+    for (int l = 0; l < NL; ++l) {
+      const int beprev = l == 0 ? L.be1 : layer_be(L, l - 1);
+      float s2 = P[layer_b(L, l) + j];
+      for (int k = 0; k < 64; ++k) s2 = fmaf(P[layer_w(L, l) + j * 64 + k], P[beprev + k], s2);
+      sm[S::bf + l * 64 + j] = s2;
+    }
+  } else if (tid < 64 + kMaxA) {
+    const int aidx = tid - 64;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    float s = 0.0f;
+    if (h < L.n_heads) {
+      s = P[L.bh[h] + (aidx - off)];
+      for (int k = 0; k < 64; ++k) s = fmaf(P[L.wh[h] + (aidx - off) * 64 + k], P[belast + k], s);
+    }
+    sm[S::bhf + aidx] = s;
+  }
+}
+
+template <int BM, int NT, int MODE, int NL>
+__global__ void __launch_bounds__(NT, 1) mlp_deep_kernel(const MlpArgs a) {
+  constexpr bool UPDATE = (MODE >= 2);
+  constexpr int NTY = NT / 16, RPT = BM / NTY, JT = 64 / NTY, NQ = (kMaxA * 64 + NT - 1) / NT;
+  static_assert(RPT * NTY == BM && JT * NTY == 64 && JT % 4 == 0, "tile shape");
+  using S = SmemDeep<BM, NL>;
+  extern __shared__ __align__(16) float sm[];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const NetLayout& L = a.L;
+  const int A = L.a_total, relu = L.use_relu, K4 = a.Kp >> 2;
+  auto tile_of = [&](int i) { return sm + S::T + i * (BM * kLD); };
+  auto mean_of = [&](int i) { return sm + S::mean + i * BM; };
+  auto rstd_of = [&](int i) { return sm + S::rstd + i * BM; };
+
+  stage_weights_deep<BM, NL, UPDATE>(sm, a);
+
+  float G1[JT][4], db1[JT], Gx[NL][JT][4], dbx[NL][JT], gh[NQ], dbh[NQ];
+  double lacc[4] = {0.0, 0.0, 0.0, 0.0};
+  if (UPDATE) {
+#pragma unroll
+    for (int j = 0; j < JT; ++j) {
+      db1[j] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) G1[j][c] = 0.0f;
+#pragma unroll
+      for (int l = 0; l < NL; ++l) {
+        dbx[l][j] = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) Gx[l][j][c] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) gh[q] = dbh[q] = 0.0f;
+  }
+  const int j0 = ty * JT, tk = tx;
+  const bool k1_active = (4 * tk < a.Kp);
+
+  for (long long tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+    __syncthreads();
+    load_input_tile<BM>(tile_of(0), a, tile);
+    __syncthreads();
+    float acc[RPT][4];
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    gemm_tile<RPT, NTY>(tile_of(0), kLD, K4, sm + S::W1t, acc, ty, tx);
+    act_ln_store<RPT, NTY>(acc, sm + S::b1f, relu, tile_of(1), mean_of(0), rstd_of(0), ty, tx);
+    __syncthreads();
+#pragma unroll
+    for (int l = 0; l < NL; ++l) {                       // hidden blocks (mlp.py:26-28)
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+      gemm_tile<RPT, NTY>(tile_of(1 + l), kLD, 16, sm + S::Wt + l * 4096, acc, ty, tx);
+      act_ln_store<RPT, NTY>(acc, sm + S::bf + l * 64, relu, tile_of(2 + l), mean_of(1 + l), rstd_of(1 + l), ty, tx);
+      __syncthreads();
+    }
+    float* Tlast = tile_of(NL + 1);
+    if (tid < BM) {
+      const long long g = tile * BM + tid;
+      float l[kMaxA];
+      if (g < a.rows) {
+        row_logits(Tlast + tid * kLD, sm + S::Whf, sm + S::bhf, A, l);
+        const long long src = a.index ? a.index[g] : g;
+        if (MODE == 0) actor_rollout_row(a, g, l);
+        if (MODE == 1) for (int m = 0; m < a.group; ++m) a.values_out[g * a.group + m] = l[0];
+        if (MODE == 2) actor_loss_row(a, src, l, sm + S::dlog + tid * kDL, lacc);
+        if (MODE == 3) {
+          const float dv = critic_loss_row(a, src, l[0], lacc);
+          float* dl = sm + S::dlog + tid * kDL;
+          dl[0] = dv;
+          for (int q = 1; q < kMaxA; ++q) dl[q] = 0.0f;
+        }
+      } else if (UPDATE) {
+        float* dl = sm + S::dlog + tid * kDL;
+        for (int q = 0; q < kMaxA; ++q) dl[q] = 0.0f;
+      }
+    }
+    if (!UPDATE) continue;
+    __syncthreads();
+    // head weight gradient and dn of the last block
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const int o = tid + NT * q;
+      if (o < A * 64) {
+        const int aa = o >> 6, k = o & 63;
+        float s = 0.0f, sb = 0.0f;
+        for (int r = 0; r < BM; ++r) {
+          const float d = sm[S::dlog + r * kDL + aa];
+          s = fmaf(d, Tlast[r * kLD + k], s);
+          sb += d;
+        }
+        gh[q] += s;
+        if (k == 0) dbh[q] += sb;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+    for (int aa = 0; aa < A; ++aa) {
+      const float4 w = *reinterpret_cast<const float4*>(sm + S::Whf + aa * 64 + 4 * tx);
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        const float d = sm[S::dlog + (ty + NTY * i) * kDL + aa];
+        acc[i][0] = fmaf(d, w.x, acc[i][0]); acc[i][1] = fmaf(d, w.y, acc[i][1]);
+        acc[i][2] = fmaf(d, w.z, acc[i][2]); acc[i][3] = fmaf(d, w.w, acc[i][3]);
+      }
+    }
+    __syncthreads();                                     // head wgrad finished reading the last n tile
+    ln_act_bwd_store<RPT, NTY>(acc, relu, Tlast, mean_of(NL), rstd_of(NL), ty, tx);     // T[NL+1] := dz of block NL-1
+    __syncthreads();
+#pragma unroll
+    for (int l = NL - 1; l >= 0; --l) {
+      // block l: weight gradient from (dz_l, its input n) and the data gradient into that input
+      wgrad_tile<BM, JT>(tile_of(2 + l), tile_of(1 + l), Gx[l], dbx[l], j0, tk, true);
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f;
+      gemm_tile<RPT, NTY>(tile_of(2 + l), kLD, 16, sm + S::Wf + l * 4096, acc, ty, tx);
+      __syncthreads();                                   // the weight gradient finished reading the input tile
+      ln_act_bwd_store<RPT, NTY>(acc, relu, tile_of(1 + l), mean_of(l), rstd_of(l), ty, tx);   // := dz of the producer
+      __syncthreads();
+    }
+    wgrad_tile<BM, JT>(tile_of(1), tile_of(0), G1, db1, j0, tk, k1_active);             // fc1 (no dgrad into the inputs)
+  }
+
+  if (!UPDATE) return;
+  float* __restrict__ gp = a.grad_partials + (size_t)blockIdx.x * L.total;
+  for (int e = tid; e < L.total; e += NT) gp[e] = 0.0f;
+  __syncthreads();
+  const int D = L.in_dim;
+#pragma unroll
+  for (int jj = 0; jj < JT; ++jj) {
+    const int j = j0 + jj;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int k = 4 * tk + c;
+      if (k < D) gp[L.w1 + j * D + k] = G1[jj][c];
+#pragma unroll
+      for (int l = 0; l < NL; ++l) gp[layer_w(L, l) + j * 64 + k] = Gx[l][jj][c];
+    }
+    if (tk == 0) {
+      gp[L.b1 + j] = db1[jj];
+#pragma unroll
+      for (int l = 0; l < NL; ++l) gp[layer_b(L, l) + j] = dbx[l][jj];
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const int o = tid + NT * q;
+    if (o < A * 64) {
+      const int aa = o >> 6, k = o & 63;
+      int h = 0, off = 0;
+      while (aa >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+      gp[L.wh[h] + (aa - off) * 64 + k] = gh[q];
+      if (k == 0) gp[L.bh[h] + (aa - off)] = dbh[q];
+    }
+  }
+  __shared__ double red[4][32];
+  for (int q = 0; q < 4; ++q) {
+    double v = lacc[q];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) red[q][tid >> 5] = v;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double v = 0.0;
+    for (int w = 0; w < NT / 32; ++w) v += red[tid][w];
+    a.loss_partials[(size_t)blockIdx.x * 4 + tid] = v;
+  }
+}
+
+constexpr int kDeepBM = 64;
+
+static int blocks_for_deep(long long rows) {
+  const long long ntiles = (rows + kDeepBM - 1) / kDeepBM;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  return (int)(ntiles < sms ? (ntiles < 1 ? 1 : ntiles) : sms);
+}
+
+template <int MODE, int NL>
+static int launch_deep_nl(MlpArgs& a, cudaStream_t stream, const char* who) {
+  using S = SmemDeep<kDeepBM, NL>;
+  auto kern = mlp_deep_kernel<kDeepBM, 256, MODE, NL>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MAPPO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));
+    attr_set = true;
+  }
+  kern<<<blocks_for_deep(a.rows), 256, S::bytes, stream>>>(a);
+  MAPPO_CHECK_LAUNCH(who);
+  return 0;
+}
+
+template <int MODE>
+static int launch_deep(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stream, const char* who) {
+  a.L = make_layout(*cfg);
+  if (a.x_div < 1) a.x_div = 1;
+  a.Kp = (cfg->in_dim + 3) & ~3;
+  a.ntiles = (a.rows + kDeepBM - 1) / kDeepBM;
+  if (cfg->layer_N == 2) return launch_deep_nl<MODE, 2>(a, stream, who);
+  return launch_deep_nl<MODE, 3>(a, stream, who);
+}
+
 // ---- host side -------------------------------------------------------------------------------------
 constexpr int kBM = 128, kNT = 256;
 
@@ -315,6 +589,7 @@ static int launch_mlp(MlpArgs& a, const mappo_net_config* cfg, cudaStream_t stre
   if (int rc = check_net(cfg, who)) return rc;
   if (cfg->recurrent) MAPPO_UNSUPPORTED("%s: recurrent (GRU) networks are not built yet", who);
   MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim, "%s: bad input arguments", who);
+  if (cfg->layer_N > 1) return launch_deep<MODE>(a, cfg, stream, who);      // extra hidden blocks: fp32 tile kernel
   if (use_tc(cfg)) return tc::launch<MODE>(a, cfg, stream, who);
   if (cfg->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: in_dim %d > %d is built on the tensor-core path only", who, cfg->in_dim, kMaxIn);
   a.L = make_layout(*cfg);
@@ -343,6 +618,7 @@ extern "C" long long mappo_net_param_count(const mappo_net_config* cfg) {
 }
 
 extern "C" int mappo_update_num_blocks(const mappo_net_config* cfg, long long rows) {
+  if (cfg && cfg->layer_N > 1) return blocks_for_deep(rows);
   if (use_tc(cfg) || (cfg && cfg->recurrent)) return 2 * tc::grid_for(rows);   // two partial rows per CTA (hi / lo operand halves)
   return blocks_for(rows);
 }

@@ -28,8 +28,12 @@ def _t(x):
     return x if torch.is_tensor(x) else torch.as_tensor(np.asarray(x), dtype=torch.float32)
 
 
-def mlp_base(sd, x, use_relu, use_feature_norm=True, layer_N=1, prefix="base."):
+def mlp_base(sd, x, use_relu, use_feature_norm=True, layer_N=None, prefix="base."):
     act = torch.relu if use_relu else torch.tanh
+    if layer_N is None:                                     # mlp.py:20-28: as many fc2 blocks as the state dict holds
+        layer_N = 0
+        while prefix + "mlp.fc2.%d.0.weight" % layer_N in sd:
+            layer_N += 1
     if use_feature_norm:
         x = F.layer_norm(x, x.shape[-1:], sd[prefix + "feature_norm.weight"], sd[prefix + "feature_norm.bias"])
     x = act(F.linear(x, sd[prefix + "mlp.fc1.0.weight"], sd[prefix + "mlp.fc1.0.bias"]))

@@ -347,6 +347,9 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
                     prm.add_((torch.randn(prm.shape, generator=g) * 0.2).to(prm.device))
                 elif "action_out" in name or "v_out" in name:
                     prm.add_((torch.randn(prm.shape, generator=g) * 0.3).to(prm.device))
+                elif "fc2" in name and args.layer_N > 1:
+                    # the hidden blocks start as identical clones of fc_h (mlp.py:20-22): make them differ
+                    prm.add_((torch.randn(prm.shape, generator=g) * 0.05).to(prm.device))
     D, S, H = obs_sp.shape[0], sh_sp.shape[0], args.hidden_size
     rng = np.random.RandomState(seed)
     recurrent = bool(args.use_recurrent_policy)
@@ -463,14 +466,20 @@ PPO_CASES = {
     # unclipped value loss, no feature norm, listener of speaker_listener (D=11, S=14)
     "mlp_listener": dict(scenario="simple_speaker_listener", M=2, L=3, algo="mappo",
                          extra="--use_clipped_value_loss --use_feature_normalization --share_policy", B=257, seed=7),
+    # layer_N > 1 (config.py:201): two and three hidden blocks after fc1
+    "mlp_layer2": dict(scenario="simple_spread", M=3, L=3, algo="mappo", extra="--use_ReLU --layer_N 2", B=500, seed=11),
+    "mlp_layer3_relu": dict(scenario="simple_spread", M=3, L=3, algo="mappo",
+                            extra="--layer_N 3 --use_huber_loss --max_grad_norm 0.5", B=333, seed=12),
     # C4: simple_reference, shared GRU policy (rmappo), MultiDiscrete heads (5, 10), chunks of 10 steps
     "gru_reference": dict(scenario="simple_reference", M=2, L=3, algo="rmappo",
                           extra="--use_ReLU --lr 7e-4 --critic_lr 7e-4 --data_chunk_length 10", B=370, seed=9),
 }
 
 
-def gen_ppo():
+def gen_ppo(only=None):
     for tag, kw in PPO_CASES.items():
+        if only and tag not in only:
+            continue
         fx = make_ppo_fixture(**kw)
         path = os.path.join(HERE, "ppo_%s.npz" % tag)
         np.savez_compressed(path, **fx)

@@ -52,6 +52,14 @@ def test_full_iteration_recurrent_wide_inputs():
     g._smoke_iteration(M=15, N=16, extra="--algorithm_name ippo --data_chunk_length 5")
 
 
+def test_full_iteration_two_and_three_hidden_blocks():
+    """--layer_N 2 / 3 (config.py:201, mlp.py:20-28): rollout and update through the fp32 tile kernel with extra hidden
+    blocks, beside the oracle iteration."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=3, N=64, extra="--layer_N 2")
+    g._smoke_iteration(M=3, N=48, extra="--layer_N 3 --algorithm_name ippo --use_recurrent_policy")
+
+
 def _make_runner(extra, N=192, M=3):
     import torch
     from mappo_b200.config import parse_args

@@ -10,7 +10,7 @@ import torch
 from ppo_common import fx_args, sd_from
 
 pytestmark = pytest.mark.gpu
-CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener"]
+CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener", "mlp_layer2", "mlp_layer3_relu"]   # the last two: layer_N = 2, 3
 
 
 def make_space(n):
