@@ -317,6 +317,38 @@ def dp_check(device, rank, world, dist, n_small=512):
     return out
 
 
+def run_c1(ns, device):
+    """BASELINE config C1 -- the reference's own configuration (128 envs, train_mpe_spread.sh) and exactly what the
+    reference arm (`--impl reference`) runs -- on one GPU: the same configuration on both arms.  Timed eagerly and with
+    the whole iteration captured as one CUDA graph (--use_cuda_graph); at this size the iteration is launch-bound."""
+    import torch
+    from mappo_b200.config import parse_args
+    from mappo_b200.envs.mpe.MPE_env import MPEVecEnv
+    from mappo_b200.runner.shared.mpe_runner import MPERunner
+    out = {"workload": "C1: MPE simple_spread M=3 L=3, 128 envs x 1 GPU, T=25, shared MLP (Tanh, H=64), ppo_epoch=10, "
+                       "num_mini_batch=1, GAE+ValueNorm (the reference arm's configuration)",
+           "agent_steps_per_step": 128 * T_EP * 3, "unit": UNIT}
+    for key, extra in (("eager", []), ("cuda_graph", ["--use_cuda_graph"])):
+        a = parse_args(flags(128) + extra)
+        torch.manual_seed(1)
+        envs = MPEVecEnv(a, device=device)
+        r = MPERunner({"all_args": a, "envs": envs, "eval_envs": None, "device": device, "num_agents": 3, "run_dir": None})
+        r.warmup()
+        for _ in range(5):
+            r.run_episode()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 50
+        e0.record()
+        for _ in range(n):
+            r.run_episode()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        out[key] = {"ms_per_step": ms, "value": 128 * T_EP * 3 / (ms * 1e-3), "steps": n, "warmup": 5}
+    return out
+
+
 def run_c5(ns, device, rank, world, dist, peaks):
     """The north_star target beside the contract line: BASELINE config C5 -- simple_spread with 10 agents, 16,384 envs
     per GPU (1,310,720 concurrent agents on 8 GPUs), shared MLP policy, centralised critic over 460 columns, NCCL
@@ -475,6 +507,9 @@ def run_ours(ns):
     c5 = None
     if CONFIG == "C2" and (ns.c5 or world >= 8):
         c5 = run_c5(ns, device, rank, world, dist, peaks)
+    c1 = None
+    if CONFIG == "C2" and world == 1 and not ns.no_c1 and M_AGENTS == 3:
+        c1 = run_c1(ns, device)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -537,6 +572,8 @@ def run_ours(ns):
            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_port": cpu_port,
            "kernel_ms_per_step": share,
            "clocks": clocks, "train_info": info}
+    if c1 is not None:
+        out["c1"] = c1
     if c5 is not None:
         out["c5"] = c5
     if dp is not None:
@@ -642,6 +679,7 @@ def main():
     ap.add_argument("--c5", action="store_true", help="also measure BASELINE config C5 (10 agents) and print it under the "
                                                       "key `c5`; on by default at 8 GPUs (the north_star target)")
     ap.add_argument("--c5-envs", dest="c5_envs", type=int, default=16384, help="envs per GPU of the C5 measurement")
+    ap.add_argument("--no-c1", dest="no_c1", action="store_true", help="skip the C1 (128 envs) figures of the `c1` key")
     ap.add_argument("--no-dp-check", dest="no_dp_check", action="store_true")
     ap.add_argument("--dp-check-only", dest="dp_check_only", action="store_true",
                     help="under torchrun: run the multi-rank parity check, print it and exit (tests/test_gpu_dist.py)")
