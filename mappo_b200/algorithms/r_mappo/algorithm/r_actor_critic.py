@@ -103,10 +103,11 @@ class _FlatNet(nn.Module):
         # cuda device, are not registered parameters (algorithms/utils/popart.py here): kept in `.flat` for the kernels,
         # left out of named_parameters() / state_dict() and of the optimiser
         self._head_outside_optimizer = bool(args.use_popart) and is_critic
-        if self._recurrent and args.recurrent_N != 1:
-            raise NotImplementedError("recurrent_N > 1")
+        if self._recurrent and not 1 <= args.recurrent_N <= 2:
+            raise NotImplementedError("recurrent_N = %d (this build: 1 or 2 GRU layers)" % args.recurrent_N)
         self.cfg = ops.net_config(in_dim, args.hidden_size, args.layer_N, args.use_ReLU,
-                                  args.use_feature_normalization, self._recurrent, head_dims, is_critic)
+                                  args.use_feature_normalization, args.recurrent_N if self._recurrent else 0,
+                                  head_dims, is_critic)
         init = _reference_init(args, in_dim, head_dims, is_critic)
         live = [k for k in init if "fc_h" not in k]
         total = sum(init[k].numel() for k in live)
@@ -262,7 +263,8 @@ class R_Actor(_FlatNet):
         """rnn.py:30-77 (training branch): obs [L*N, D] step-major, rnn_states [N, 1, H] -- L sequential single-step
         evaluations with the hidden state carried on the device."""
         B, nh = obs.shape[0], len(self.head_dims)
-        h = check(rnn_states, self.device_).to(torch.float32).reshape(-1, self.hidden_size).contiguous()
+        h = check(rnn_states, self.device_).to(torch.float32)
+        h = h.reshape(-1, self._recurrent_N * self.hidden_size).contiguous()       # [N, recurrent_N * H]
         N = h.shape[0]
         Lc = B // N
         action = check(action, self.device_).reshape(B, nh).to(torch.float32).contiguous()

@@ -254,9 +254,9 @@ class R_MAPPO:
         c = lambda x: None if x is None else check(x, dev).to(torch.float32).contiguous()
         obs, share_obs = c(obs), c(share_obs)
         B = obs.shape[0]
-        N = c(rs).reshape(-1, 64).shape[0]
+        H = 64 * int(self.policy.actor._recurrent_N)         # a sample's state: [recurrent_N, 64]
+        N = c(rs).reshape(-1, H).shape[0]
         L = B // N
-        H = 64
         # rnn states exist per chunk only: place them at the rows of step 0 (the only rows the kernels read them at)
         def spread(x):
             full = torch.zeros(B, H, dtype=torch.float32, device=dev)

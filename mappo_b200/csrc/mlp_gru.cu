@@ -34,6 +34,10 @@ struct GruArgs {
   float* hm;                     // [len * nc][64]  masked previous hidden, or NULL
   float* gates;                  // [len * nc][256] r | z | n | (Whn h + bhn) -> backward: dgi_n | P_r | P_z | dgh_n
   float* dh;                     // backward: [len * nc][64] dLoss/dh direct (in), dLoss/dn2 (out, in place)
+  // which GRU layer this sweep runs (recurrent_N = 2 runs the sweeps once per layer): offsets of its four parameter
+  // blocks, the LayerNorm affine folded into W_ih (layer 0: fc2's; -1 = none: layer 1 reads raw hidden states), and the
+  // row stride of h0 (the stored rnn states are [*][recurrent_N][64])
+  int wih, whh, bih, bhh, fold_g, fold_be, h0_ld;
 };
 
 constexpr uint32_t kGChunk = 192 * 16;                   // bytes of one 8-column chunk of a 192-row weight tile
@@ -72,16 +76,16 @@ __device__ __forceinline__ void stage_gru_weights(unsigned char* sm, const GruMa
   const float* __restrict__ P = a.params;
   for (int e = threadIdx.x; e < 192 * 64; e += kThreads) {
     const int j = e >> 6, k = e & 63;
-    put_pair(sm + m.Wih, kGPiece, 192, j, k, P[L.wih + e] * P[L.g2 + k]);
-    put_pair(sm + m.Whh, kGPiece, 192, j, k, P[L.whh + e]);
+    put_pair(sm + m.Wih, kGPiece, 192, j, k, P[a.wih + e] * (a.fold_g >= 0 ? P[a.fold_g + k] : 1.0f));
+    put_pair(sm + m.Whh, kGPiece, 192, j, k, P[a.whh + e]);
   }
   float* b = reinterpret_cast<float*>(sm + m.bias);       // [0,128): r, z (input + hidden bias); [128,192): b_in; [192,256): b_hn
   if (threadIdx.x < 192) {
     const int j = threadIdx.x;
-    float s = P[L.bih + j];
-    for (int k = 0; k < 64; ++k) s = fmaf(P[L.wih + j * 64 + k], P[L.be2 + k], s);
-    if (j < 128) b[j] = s + P[L.bhh + j];
-    else { b[j] = s; b[j + 64] = P[L.bhh + j]; }
+    float s = P[a.bih + j];
+    if (a.fold_be >= 0) for (int k = 0; k < 64; ++k) s = fmaf(P[a.wih + j * 64 + k], P[a.fold_be + k], s);
+    if (j < 128) b[j] = s + P[a.bhh + j];
+    else { b[j] = s; b[j + 64] = P[a.bhh + j]; }
   }
 }
 
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(kThreads, 1) gru_fwd_kernel(const GruArgs a) {
     float h[16], x[16], mask;
     {
       const long long src = valid ? (a.index ? a.index[c] : c) : 0;
-      if (valid) { load16(a.h0 + src * 64 + 16 * cq, h); load16(a.n2 + c * 64 + 16 * cq, x); mask = a.mpos ? __ldg(a.mpos + c) : __ldg(a.masks + src); }
+      if (valid) { load16(a.h0 + src * a.h0_ld + 16 * cq, h); load16(a.n2 + c * 64 + 16 * cq, x); mask = a.mpos ? __ldg(a.mpos + c) : __ldg(a.masks + src); }
       else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) h[i] = x[i] = 0.0f;
@@ -709,10 +713,18 @@ static int head_grid(long long rows) {
   return (int)(nt < g ? nt : g);
 }
 
-// floats of workspace per position: rollout keeps the base features only
-// + the wide first layer's scratch (z1 [64] and row statistics [2] per position) when the base reads more than 64 columns
-long long rnn_workspace_floats(long long positions, int update, int in_dim) {
-  return positions * ((update ? 513 : 64) + (in_dim >= kWideFrom ? 66 : 0));
+// floats of workspace per position: rollout keeps the base features only (+ per GRU layer of a stacked network a
+// contiguous copy of its incoming and outgoing state); an update keeps n2, dh and per layer hs | hm | gates, + 1 for the
+// gathered masks; + the wide first layer's scratch (z1 [64] and row statistics [2]) when the base reads > 64 columns
+long long rnn_workspace_floats(long long positions, int update, int in_dim, int layers) {
+  const int extra = layers > 1 ? (update ? (layers - 1) * 384 : layers * 128) : 0;
+  return positions * ((update ? 513 : 64) + extra + (in_dim >= kWideFrom ? 66 : 0));
+}
+
+// the sweep arguments of GRU layer l (rnn.py:13: layer l > 0 reads the raw hidden states of the layer below)
+static void set_layer(GruArgs& g, const NetLayout& L, int l) {
+  if (l == 0) { g.wih = L.wih; g.whh = L.whh; g.bih = L.bih; g.bhh = L.bhh; g.fold_g = L.g2; g.fold_be = L.be2; }
+  else { g.wih = L.wih1; g.whh = L.whh1; g.bih = L.bih1; g.bhh = L.bhh1; g.fold_g = -1; g.fold_be = -1; }
 }
 
 // mpos[p] = masks[index[p]]: the sweeps read their step's mask with the rest of the step's rows instead of behind a
@@ -723,7 +735,8 @@ __global__ void gather_masks_kernel(const float* __restrict__ masks, const int64
     mpos[i] = __ldg(masks + index[i]);
 }
 
-// One forward step for `rows` rows (rollout / evaluation): base -> GRU -> head.
+// One forward step for `rows` rows (rollout / evaluation): base -> GRU (recurrent_N layers) -> head.
+// h_in / h_out: [rows][recurrent_N][64] (rnn.py:24-28: every layer's state is multiplied by the mask before the step).
 template <int MODE>
 int rnn_forward(MlpArgs& a, const mappo_net_config* cfg, const float* h_in, const float* masks, float* h_out,
                 cudaStream_t stream, const char* who) {
@@ -731,21 +744,45 @@ int rnn_forward(MlpArgs& a, const mappo_net_config* cfg, const float* h_in, cons
   MAPPO_REQUIRE(a.params && a.x && a.rows > 0 && a.ld >= cfg->in_dim && h_in && masks && h_out && a.workspace,
                 "%s: bad arguments", who);
   if (int rc = set_attrs()) return rc;
-  float* n2 = static_cast<float*>(a.workspace);
+  const int RN = cfg->recurrent;
+  const long long rows = a.rows;
+  float* ws = static_cast<float*>(a.workspace);
+  float* n2 = ws;
   a.feat = n2;
-  a.workspace = n2 + a.rows * 64;                        // the wide first layer's scratch, if the base needs one
+  a.workspace = n2 + rows * 64;                          // the wide first layer's scratch, if the base needs one
   if (int rc = launch<4>(a, cfg, stream, who)) return rc;
   GruArgs g{};
-  g.L = a.L; g.params = a.params; g.nc = a.rows; g.len = 1; g.index = nullptr; g.n2 = n2; g.h0 = h_in; g.masks = masks;
-  g.hs = h_out;
-  gru_fwd_kernel<<<grid_for(a.rows), kThreads, make_gru_map(false).total, stream>>>(g);
-  MAPPO_CHECK_LAUNCH(who);
-  gru_head_kernel<MODE><<<head_grid(a.rows), 256, HeadSmem::bytes, stream>>>(a, h_out, nullptr);
+  g.L = a.L; g.params = a.params; g.nc = rows; g.len = 1; g.index = nullptr; g.masks = masks; g.h0_ld = 64;
+  const float* h_top = h_out;
+  if (RN == 1) {
+    set_layer(g, a.L, 0);
+    g.n2 = n2; g.h0 = h_in; g.hs = h_out;
+    gru_fwd_kernel<<<grid_for(rows), kThreads, make_gru_map(false).total, stream>>>(g);
+    MAPPO_CHECK_LAUNCH(who);
+  } else {
+    // stacked layers: each sweep works on contiguous [rows][64] copies of its state slice
+    float* lay = ws + rows * (64 + (cfg->in_dim >= kWideFrom ? 66 : 0));
+    const float* x = n2;
+    for (int l = 0; l < RN; ++l) {
+      float* hin = lay + (size_t)(2 * l) * rows * 64;
+      float* hs = lay + (size_t)(2 * l + 1) * rows * 64;
+      MAPPO_CUDA(cudaMemcpy2DAsync(hin, 256, h_in + 64 * l, (size_t)RN * 256, 256, (size_t)rows, cudaMemcpyDeviceToDevice, stream));
+      set_layer(g, a.L, l);
+      g.n2 = x; g.h0 = hin; g.hs = hs;
+      gru_fwd_kernel<<<grid_for(rows), kThreads, make_gru_map(false).total, stream>>>(g);
+      MAPPO_CHECK_LAUNCH(who);
+      MAPPO_CUDA(cudaMemcpy2DAsync(h_out + 64 * l, (size_t)RN * 256, hs, 256, 256, (size_t)rows, cudaMemcpyDeviceToDevice, stream));
+      x = hs;
+    }
+    h_top = x;
+  }
+  gru_head_kernel<MODE><<<head_grid(rows), 256, HeadSmem::bytes, stream>>>(a, h_top, nullptr);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
 }
 
 // One PPO minibatch of n_chunks sequences of chunk_len steps: positions p = s * n_chunks + c, sample row index[p].
+// rnn_states: [*][recurrent_N][64] at sample rows.
 template <int MODE>
 int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int chunk_len, const float* rnn_states,
                const float* masks, int n_partials, cudaStream_t stream, const char* who) {
@@ -755,35 +792,51 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
                 a.index && a.workspace && a.grad_partials && a.loss_partials, "%s: bad arguments", who);
   MAPPO_REQUIRE(n_partials >= 2 * grid_for(B), "%s: %d partial rows, need %d", who, n_partials, 2 * grid_for(B));
   if (int rc = set_attrs()) return rc;
+  const int RN = cfg->recurrent;
   a.rows = B;
   a.L = make_layout(*cfg);
   const size_t P = (size_t)a.L.total;
   MAPPO_CUDA(cudaMemsetAsync(a.grad_partials, 0, sizeof(float) * P * (size_t)n_partials, stream));
   MAPPO_CUDA(cudaMemsetAsync(a.loss_partials, 0, sizeof(double) * 4 * (size_t)n_partials, stream));
   float* ws = static_cast<float*>(a.workspace);
-  float *n2 = ws, *hs = ws + B * 64, *hm = ws + B * 128, *dh = ws + B * 192, *gates = ws + B * 256;
-  float* mpos = ws + B * (512 + (cfg->in_dim >= kWideFrom ? 66 : 0));
+  const int wide = cfg->in_dim >= kWideFrom ? 66 : 0;
+  float *n2 = ws, *dh = ws + B * 192;
+  float *hs[kMaxRecurrentN], *hm[kMaxRecurrentN], *gates[kMaxRecurrentN];
+  hs[0] = ws + B * 64; hm[0] = ws + B * 128; gates[0] = ws + B * 256;
+  float* mpos = ws + B * (512 + wide);
+  for (int l = 1; l < RN; ++l) {
+    float* base = ws + B * (513 + wide) + (size_t)(l - 1) * B * 384;
+    hs[l] = base; hm[l] = base + B * 64; gates[l] = base + B * 128;
+  }
   a.workspace = ws + B * 512;                            // the wide first layer's scratch, if the base needs one
   gather_masks_kernel<<<(int)((B + 255) / 256 < 1184 ? (B + 255) / 256 : 1184), 256, 0, stream>>>(masks, a.index, mpos, B);
   MAPPO_CHECK_LAUNCH(who);
   a.feat = n2;
   if (int rc = launch<4>(a, cfg, stream, who)) return rc;
   GruArgs g{};
-  g.L = a.L; g.params = a.params; g.nc = n_chunks; g.len = chunk_len; g.index = a.index; g.n2 = n2; g.h0 = rnn_states;
-  g.masks = masks; g.mpos = mpos; g.hs = hs; g.hm = hm; g.gates = gates; g.dh = dh;
-  gru_fwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(false).total, stream>>>(g);
+  g.L = a.L; g.params = a.params; g.nc = n_chunks; g.len = chunk_len; g.index = a.index;
+  g.masks = masks; g.mpos = mpos; g.dh = dh; g.h0_ld = 64 * RN;
+  for (int l = 0; l < RN; ++l) {                          // forward sweeps, bottom up
+    set_layer(g, a.L, l);
+    g.n2 = l == 0 ? n2 : hs[l - 1]; g.h0 = rnn_states + 64 * l; g.hs = hs[l]; g.hm = hm[l]; g.gates = gates[l];
+    gru_fwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(false).total, stream>>>(g);
+    MAPPO_CHECK_LAUNCH(who);
+  }
+  gru_head_kernel<MODE><<<head_grid(B), 256, HeadSmem::bytes, stream>>>(a, hs[RN - 1], dh);
   MAPPO_CHECK_LAUNCH(who);
-  gru_head_kernel<MODE><<<head_grid(B), 256, HeadSmem::bytes, stream>>>(a, hs, dh);
-  MAPPO_CHECK_LAUNCH(who);
-  gru_bwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(true).total, stream>>>(g);
-  MAPPO_CHECK_LAUNCH(who);
-  WideArgs w{};
-  w.rows = B; w.index = nullptr; w.x_div = 1; w.vec = 1; w.ld = 256; w.D = 192; w.dz_ld = 64; w.norm = 0;
-  w.total = a.L.total; w.transposed = 1; w.grad_partials = a.grad_partials;
-  w.x = gates; w.dz1 = n2; w.rot = 128; w.out_w = a.L.wih; w.out_b = a.L.bih;
-  if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
-  w.x = gates + 64; w.dz1 = hm; w.rot = 0; w.out_w = a.L.whh; w.out_b = a.L.bhh;
-  if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
+  for (int l = RN - 1; l >= 0; --l) {                     // backward sweeps, top down: dh becomes dLoss/d(input of layer l)
+    set_layer(g, a.L, l);
+    g.n2 = l == 0 ? n2 : hs[l - 1]; g.h0 = rnn_states + 64 * l; g.hs = hs[l]; g.hm = hm[l]; g.gates = gates[l];
+    gru_bwd_kernel<<<grid_for(n_chunks), kThreads, make_gru_map(true).total, stream>>>(g);
+    MAPPO_CHECK_LAUNCH(who);
+    WideArgs w{};
+    w.rows = B; w.index = nullptr; w.x_div = 1; w.vec = 1; w.ld = 256; w.D = 192; w.dz_ld = 64; w.norm = 0;
+    w.total = a.L.total; w.transposed = 1; w.grad_partials = a.grad_partials;
+    w.x = gates[l]; w.dz1 = const_cast<float*>(g.n2); w.rot = 128; w.out_w = g.wih; w.out_b = g.bih;
+    if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
+    w.x = gates[l] + 64; w.dz1 = hm[l]; w.rot = 0; w.out_w = g.whh; w.out_b = g.bhh;
+    if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
+  }
   a.feat = dh;
   return launch<5>(a, cfg, stream, who);
 }
@@ -800,7 +853,7 @@ using namespace mappo;
 
 extern "C" long long mappo_rnn_workspace_bytes(const mappo_net_config* cfg, long long positions, int update) {
   if (!cfg || positions < 0) return -1;
-  return cfg->recurrent ? 4 * tc::rnn_workspace_floats(positions, update, cfg->in_dim) : 0;
+  return cfg->recurrent ? 4 * tc::rnn_workspace_floats(positions, update, cfg->in_dim, cfg->recurrent) : 0;
 }
 
 extern "C" int mappo_actor_forward_rnn(const mappo_net_config* cfg, const float* params, const float* obs, int obs_ld,

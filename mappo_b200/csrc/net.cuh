@@ -16,6 +16,7 @@ constexpr int kH = 64;          // hidden size this build supports
 constexpr int kMaxIn = 64;      // widest input handled by the single-chunk first layer (fp32 FMA kernels)
 constexpr int kWideFrom = 64;   // tensor-core path: from this width on the first layer runs outside the fused kernel (mlp_wide.cu)
 
+constexpr int kMaxRecurrentN = 2;   // mappo_net_config.recurrent carries recurrent_N (0 = feed-forward)
 constexpr int kMaxLayerN = 3;   // mlp.py:20-28: fc2 = layer_N clones of fc_h (hidden -> hidden blocks after fc1)
 
 struct NetLayout {
@@ -27,7 +28,9 @@ struct NetLayout {
   int fn_g, fn_b;               // [in] each (valid if use_fn)
   int w1, b1, g1, be1;          // fc1
   int w2, b2, g2, be2;          // fc2[0]
-  int wih, whh, bih, bhh, gr, ber;   // rnn (valid if recurrent)
+  int wih, whh, bih, bhh, gr, ber;   // rnn layer 0 and its LayerNorm (valid if recurrent)
+  int wih1, whh1, bih1, bhh1;        // rnn layer 1 (recurrent_N = 2: nn.GRU(num_layers = 2), rnn.py:13); -1 otherwise
+  int rnn_layers;                    // recurrent_N (0 if not recurrent)
   int wh[MAPPO_MAX_HEADS], bh[MAPPO_MAX_HEADS];
   int total;
 };
@@ -48,8 +51,13 @@ __host__ __device__ inline NetLayout make_layout(const mappo_net_config& c) {
     if (l + 1 < L.layer_N) { L.wx[l] = o; o += H * H; L.bx[l] = o; o += H; L.gx[l] = o; o += H; L.bex[l] = o; o += H; }
   }
   L.wih = L.whh = L.bih = L.bhh = L.gr = L.ber = -1;
-  if (c.recurrent) {
+  L.wih1 = L.whh1 = L.bih1 = L.bhh1 = -1;
+  L.rnn_layers = c.recurrent < 0 ? 0 : (c.recurrent > kMaxRecurrentN ? kMaxRecurrentN : c.recurrent);
+  if (c.recurrent) {     // nn.GRU.named_parameters(): weight_ih_l0, weight_hh_l0, bias_ih_l0, bias_hh_l0, then layer 1, then rnn.norm
     L.wih = o; o += 3 * H * H; L.whh = o; o += 3 * H * H; L.bih = o; o += 3 * H; L.bhh = o; o += 3 * H;
+    if (L.rnn_layers > 1) {
+      L.wih1 = o; o += 3 * H * H; L.whh1 = o; o += 3 * H * H; L.bih1 = o; o += 3 * H; L.bhh1 = o; o += 3 * H;
+    }
     L.gr = o; o += H; L.ber = o; o += H;
   }
   L.a_total = 0;
@@ -76,6 +84,7 @@ static inline int check_net(const mappo_net_config* c, const char* who) {
   MAPPO_REQUIRE(c->in_dim > 0 && c->n_heads >= 1 && c->n_heads <= MAPPO_MAX_HEADS, "%s: bad in_dim/n_heads", who);
   if (c->hidden != kH) MAPPO_UNSUPPORTED("%s: hidden_size %d (this build: 64)", who, c->hidden);
   if (c->layer_N < 1 || c->layer_N > kMaxLayerN) MAPPO_UNSUPPORTED("%s: layer_N %d (this build: 1 .. %d)", who, c->layer_N, kMaxLayerN);
+  if (c->recurrent < 0 || c->recurrent > kMaxRecurrentN) MAPPO_UNSUPPORTED("%s: recurrent_N %d (this build: 1 .. %d)", who, c->recurrent, kMaxRecurrentN);
   if (c->layer_N != 1 && c->recurrent) MAPPO_UNSUPPORTED("%s: layer_N %d with a recurrent network (this build: 1)", who, c->layer_N);
   if (c->layer_N != 1 && c->in_dim > kMaxIn) MAPPO_UNSUPPORTED("%s: layer_N %d with in_dim %d > %d", who, c->layer_N, c->in_dim, kMaxIn);
   int a = 0;

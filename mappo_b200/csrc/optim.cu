@@ -95,6 +95,10 @@ adam_step_kernel(const NetLayout L, const mappo_adam_config ad, float* __restric
   if (L.recurrent) {
     unfold_linear(params, gsum, g, L.wih, L.bih, 3 * H, H, L.g2, L.be2, false);
     unfold_linear(params, gsum, g, L.whh, L.bhh, 3 * H, H, -1, -1, false);
+    if (L.rnn_layers > 1) {             // layer 1 reads the raw hidden state of layer 0: no affine in front of either matrix
+      unfold_linear(params, gsum, g, L.wih1, L.bih1, 3 * H, H, -1, -1, false);
+      unfold_linear(params, gsum, g, L.whh1, L.bhh1, 3 * H, H, -1, -1, false);
+    }
     hg = L.gr; hbe = L.ber;
   }
   for (int h = 0; h < L.n_heads; ++h) {

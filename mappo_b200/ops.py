@@ -182,8 +182,9 @@ _lib._EXTRA_SIGS.update({
 
 def net_config(in_dim, hidden, layer_N, use_relu, use_feature_norm, recurrent, head_dims, is_critic):
     hd = (C.c_int32 * 4)(*(list(head_dims) + [0] * (4 - len(head_dims))))
+    # `recurrent` carries recurrent_N (0 = feed-forward; True counts as 1)
     return NetConfig(int(in_dim), int(hidden), int(layer_N), int(bool(use_relu)), int(bool(use_feature_norm)),
-                     int(bool(recurrent)), len(head_dims), hd, int(bool(is_critic)))
+                     int(recurrent), len(head_dims), hd, int(bool(is_critic)))
 
 
 def net_param_count(cfg):
@@ -295,9 +296,10 @@ def rnn_workspace(cfg, positions, update, device):
 
 
 def _h2(x, rows):
-    """rnn states [rows, recurrent_N = 1, H] (or [rows, H]) -> contiguous float32 [rows, H] view"""
+    """rnn states [rows, recurrent_N, H] (or [rows, H]) -> contiguous float32 [rows, recurrent_N * H] view"""
     x = x.reshape(rows, -1)
-    assert x.dtype == torch.float32 and x.is_cuda and x.is_contiguous() and x.shape[1] == 64, "rnn states must be contiguous [rows, 64]"
+    assert x.dtype == torch.float32 and x.is_cuda and x.is_contiguous() and x.shape[1] % 64 == 0, \
+        "rnn states must be contiguous [rows, recurrent_N * 64]"
     return x
 
 

@@ -53,8 +53,8 @@ class OracleMAPPO:
         self.actions = np.zeros((T, N, M, A), f)
         self.action_log_probs = np.zeros((T, N, M, A), f)
         self.rewards = np.zeros((T, N, M, 1), f)
-        self.rnn_states = np.zeros((T + 1, N, M, 1, args.hidden_size), f)
-        self.rnn_states_critic = np.zeros((T + 1, N, M, 1, args.hidden_size), f)
+        self.rnn_states = np.zeros((T + 1, N, M, args.recurrent_N, args.hidden_size), f)
+        self.rnn_states_critic = np.zeros((T + 1, N, M, args.recurrent_N, args.hidden_size), f)
         self.calls = 0
 
     # ------------------------------------------------------------------ rollout
@@ -87,8 +87,9 @@ class OracleMAPPO:
         N, M = self.N, self.M
         obs = self.obs[step].reshape(N * M, -1)
         sh = self.share_at(step).reshape(N * M, -1)
-        z = self.rnn_states[step].reshape(N * M, 1, -1)
-        zc = self.rnn_states_critic[step].reshape(N * M, 1, -1)
+        RN = self.rnn_states.shape[3]
+        z = self.rnn_states[step].reshape(N * M, RN, -1)
+        zc = self.rnn_states_critic[step].reshape(N * M, RN, -1)
         mk = self.masks[step].reshape(N * M, 1)
         feats, h = op.actor_features(self.actor, obs, z, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
         logits = op.actor_logits(self.actor, feats, None)
@@ -100,7 +101,7 @@ class OracleMAPPO:
                                           row_offset=self.row_offset)
         self.calls += 1
         values, hc = op.critic_values(self.critic, sh, zc, mk, a.use_ReLU, a.use_feature_normalization, self.rec)
-        self._h = (h.numpy().reshape(N, M, 1, -1), hc.numpy().reshape(N, M, 1, -1))
+        self._h = (h.numpy().reshape(N, M, RN, -1), hc.numpy().reshape(N, M, RN, -1))
         return values.numpy().reshape(N, M, 1), acts.numpy().reshape(N, M, -1), lps.numpy().reshape(N, M, -1)
 
     def rollout(self, given_actions=None, reset_states=None):
@@ -129,7 +130,7 @@ class OracleMAPPO:
         a = self.a
         N, M = self.N, self.M
         sh = self.share_at(-1).reshape(N * M, -1)
-        z = self.rnn_states_critic[-1].reshape(N * M, 1, -1)
+        z = self.rnn_states_critic[-1].reshape(N * M, self.rnn_states_critic.shape[3], -1)
         nv, _ = op.critic_values(self.critic, sh, z, self.masks[-1].reshape(N * M, 1), a.use_ReLU,
                                  a.use_feature_normalization, self.rec)
         vp, ret = ob.compute_returns(self.rewards, self.value_preds, self.masks, nv.numpy().reshape(N, M, 1), a.gamma,
@@ -171,8 +172,9 @@ class OracleMAPPO:
         z = zc = np.zeros((nb, 1, a.hidden_size), np.float32)
         ones = np.ones((nb, 1), np.float32)
         if self.rec:
-            z = self.rnn_states[:-1].reshape(B, 1, -1)[rnn_rows]
-            zc = self.rnn_states_critic[:-1].reshape(B, 1, -1)[rnn_rows]
+            RN = self.rnn_states.shape[3]
+            z = self.rnn_states[:-1].reshape(B, RN, -1)[rnn_rows]
+            zc = self.rnn_states_critic[:-1].reshape(B, RN, -1)[rnn_rows]
             ones = take(self.masks[:-1].reshape(B, 1))
         asd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.actor.items()}
         csd = {k: v.requires_grad_("fc_h" not in k) for k, v in self.critic.items()}
@@ -267,8 +269,8 @@ class _AgentLearner(OracleMAPPO):
         self.action_log_probs = np.zeros((T, N, 1, heads), f)
         self.rewards = np.zeros((T, N, 1, 1), f)
         self.rec = bool(args.use_recurrent_policy or args.use_naive_recurrent_policy)
-        self.rnn_states = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
-        self.rnn_states_critic = np.zeros((T + 1, N, 1, 1, args.hidden_size), f)
+        self.rnn_states = np.zeros((T + 1, N, 1, args.recurrent_N, args.hidden_size), f)
+        self.rnn_states_critic = np.zeros((T + 1, N, 1, args.recurrent_N, args.hidden_size), f)
         self.calls = 0
 
     def share_at(self, t):

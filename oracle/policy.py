@@ -45,10 +45,10 @@ def mlp_base(sd, x, use_relu, use_feature_norm=True, layer_N=None, prefix="base.
     return x
 
 
-def gru_cell(sd, x, h, prefix="rnn.rnn."):
-    """One torch.nn.GRU step, gate order (r, z, n); n = tanh(W_in x + b_in + r*(W_hn h + b_hn))."""
-    gi = F.linear(x, sd[prefix + "weight_ih_l0"], sd[prefix + "bias_ih_l0"])
-    gh = F.linear(h, sd[prefix + "weight_hh_l0"], sd[prefix + "bias_hh_l0"])
+def gru_cell(sd, x, h, prefix="rnn.rnn.", layer=0):
+    """One torch.nn.GRU step of layer `layer`, gate order (r, z, n); n = tanh(W_in x + b_in + r*(W_hn h + b_hn))."""
+    gi = F.linear(x, sd[prefix + "weight_ih_l%d" % layer], sd[prefix + "bias_ih_l%d" % layer])
+    gh = F.linear(h, sd[prefix + "weight_hh_l%d" % layer], sd[prefix + "bias_hh_l%d" % layer])
     i_r, i_z, i_n = gi.chunk(3, -1)
     h_r, h_z, h_n = gh.chunk(3, -1)
     r = torch.sigmoid(i_r + h_r)
@@ -58,20 +58,24 @@ def gru_cell(sd, x, h, prefix="rnn.rnn."):
 
 
 def rnn_layer(sd, x, hxs, masks):
-    """rnn.py:24-80 with recurrent_N = 1: h is multiplied by mask[t] before every step; the feature passed
+    """rnn.py:24-80: h is multiplied by mask[t] before every step; the feature passed
     on is LayerNorm(h_new), the state returned is the raw h_new.  x: [T*N, H] time-major, hxs: [N, 1, H]."""
     N = hxs.shape[0]
     T = x.shape[0] // N
     x = x.view(T, N, -1)
     m = masks.view(T, N, 1)
-    h = hxs[:, 0]
+    RN = hxs.shape[1]                                   # recurrent_N stacked layers (nn.GRU(num_layers=recurrent_N), rnn.py:13)
+    h = [hxs[:, l] for l in range(RN)]
     outs = []
     for t in range(T):
-        h = gru_cell(sd, x[t], h * m[t])
-        outs.append(h)
+        inp = x[t]
+        for l in range(RN):                             # every layer's state is masked before the step (rnn.py:27,62-66)
+            h[l] = gru_cell(sd, inp, h[l] * m[t], layer=l)
+            inp = h[l]
+        outs.append(inp)
     y = torch.stack(outs, 0).reshape(T * N, -1)
     y = F.layer_norm(y, y.shape[-1:], sd["rnn.norm.weight"], sd["rnn.norm.bias"])
-    return y, h.unsqueeze(1)
+    return y, torch.stack(h, 1)
 
 
 def head_keys(sd):

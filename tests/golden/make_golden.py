@@ -357,8 +357,9 @@ def make_ppo_fixture(scenario, M, L, algo, extra, B, seed, zero_avail=False, n_u
     Nc = B // Lc if recurrent else B
     obs = rng.standard_normal((B, D)).astype(np.float32) * 0.7
     share_obs = rng.standard_normal((B, S)).astype(np.float32) * 0.7
-    rnn_a = (rng.standard_normal((Nc, 1, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
-    rnn_c = (rng.standard_normal((Nc, 1, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
+    RN = args.recurrent_N
+    rnn_a = (rng.standard_normal((Nc, RN, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
+    rnn_c = (rng.standard_normal((Nc, RN, H)) * 0.5).astype(np.float32) if recurrent else np.zeros((B, 1, H), np.float32)
     masks = (rng.uniform(size=(B, 1)) > 0.08).astype(np.float32)
     active = (rng.uniform(size=(B, 1)) > 0.1).astype(np.float32)
     avail = None
@@ -466,6 +467,9 @@ PPO_CASES = {
     # unclipped value loss, no feature norm, listener of speaker_listener (D=11, S=14)
     "mlp_listener": dict(scenario="simple_speaker_listener", M=2, L=3, algo="mappo",
                          extra="--use_clipped_value_loss --use_feature_normalization --share_policy", B=257, seed=7),
+    # recurrent_N = 2 (config.py:219; nn.GRU(num_layers=2), rnn.py:13): simple_reference, MultiDiscrete heads, chunks of 10
+    "gru2_reference": dict(scenario="simple_reference", M=2, L=3, algo="rmappo",
+                           extra="--recurrent_N 2 --lr 7e-4 --critic_lr 7e-4 --data_chunk_length 10", B=330, seed=19),
     # layer_N > 1 (config.py:201): two and three hidden blocks after fc1
     "mlp_layer2": dict(scenario="simple_spread", M=3, L=3, algo="mappo", extra="--use_ReLU --layer_N 2", B=500, seed=11),
     "mlp_layer3_relu": dict(scenario="simple_spread", M=3, L=3, algo="mappo",

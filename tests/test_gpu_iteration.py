@@ -52,6 +52,15 @@ def test_full_iteration_recurrent_wide_inputs():
     g._smoke_iteration(M=15, N=16, extra="--algorithm_name ippo --data_chunk_length 5")
 
 
+def test_full_iteration_two_gru_layers():
+    """--recurrent_N 2 (config.py:219, rnn.py:13): stacked GRU layers through rollout (states [N, M, 2, 64]), chunked
+    update with back-propagation through both layers, beside the oracle iteration."""
+    import __graft_entry__ as g
+    g._smoke_iteration(M=2, N=64, scenario="simple_reference",
+                       extra="--algorithm_name rmappo --data_chunk_length 10 --recurrent_N 2")
+    g._smoke_iteration(M=3, N=32, extra="--algorithm_name rmappo --data_chunk_length 5 --recurrent_N 2")
+
+
 def test_full_iteration_two_and_three_hidden_blocks():
     """--layer_N 2 / 3 (config.py:201, mlp.py:20-28): rollout and update through the fp32 tile kernel with extra hidden
     blocks, beside the oracle iteration."""

@@ -25,7 +25,8 @@ def build(fx, seed=1):
     a = fx_args(fx)
     args = types.SimpleNamespace(**a)
     args.use_recurrent_policy = bool(fx["recurrent"]); args.use_naive_recurrent_policy = False
-    args.recurrent_N = 1; args.use_popart = bool(a.get("use_popart", False)); args.use_orthogonal = True; args.seed = seed
+    args.recurrent_N = int(fx["sample_rnn_states"].shape[1]) if (bool(fx["recurrent"]) and "sample_rnn_states" in fx.files) else 1
+    args.use_popart = bool(a.get("use_popart", False)); args.use_orthogonal = True; args.seed = seed
     args.ppo_epoch = 1; args.num_mini_batch = 1; args.data_chunk_length = int(fx["chunk"])
     heads = [int(h) for h in fx["act_heads"]]
     act = Discrete(heads[0]) if len(heads) == 1 else MultiDiscrete([[0, h - 1] for h in heads])
@@ -88,7 +89,7 @@ def test_state_dict_keys_and_forward_vs_oracle(tag, golden_dir):
     np.testing.assert_allclose(ent.item(), ent_e.item(), rtol=1e-5)
 
 
-@pytest.mark.parametrize("tag", CASES + ["gru_reference"])
+@pytest.mark.parametrize("tag", CASES + ["gru_reference", "gru2_reference"])   # the last: recurrent_N = 2
 def test_ppo_update_matches_reference(tag, golden_dir):
     """Two consecutive ppo_updates on the reference's own minibatch: losses, PRE-clip gradients, post-step
     parameters, Adam moments, ValueNorm statistics."""

@@ -8,7 +8,7 @@ import torch
 
 from ppo_common import oracle_update, sd_from
 
-CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener", "gru_reference", "mlp_layer2", "mlp_layer3_relu"]
+CASES = ["mlp_tanh", "mlp_relu_opts", "mlp_listener", "gru_reference", "mlp_layer2", "mlp_layer3_relu", "gru2_reference"]
 
 
 @pytest.mark.parametrize("tag", CASES)
