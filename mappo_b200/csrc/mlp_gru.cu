@@ -718,7 +718,7 @@ static int head_grid(long long rows) {
 // gathered masks; + the wide first layer's scratch (z1 [64] and row statistics [2]) when the base reads > 64 columns
 long long rnn_workspace_floats(long long positions, int update, int in_dim, int layers) {
   const int extra = layers > 1 ? (update ? (layers - 1) * 384 : layers * 128) : 0;
-  return positions * ((update ? 513 : 64) + extra + (in_dim >= kWideFrom ? 66 : 0));
+  return positions * ((update ? 513 : 64) + extra + (in_dim >= kWideFrom ? 66 : 0)) + (layers > 1 ? 64 : 0);   // + alignment slack
 }
 
 // the sweep arguments of GRU layer l (rnn.py:13: layer l > 0 reads the raw hidden states of the layer below)
@@ -761,7 +761,7 @@ int rnn_forward(MlpArgs& a, const mappo_net_config* cfg, const float* h_in, cons
     MAPPO_CHECK_LAUNCH(who);
   } else {
     // stacked layers: each sweep works on contiguous [rows][64] copies of its state slice
-    float* lay = ws + rows * (64 + (cfg->in_dim >= kWideFrom ? 66 : 0));
+    float* lay = ws + ((rows * (64 + (cfg->in_dim >= kWideFrom ? 66 : 0)) + 63) & ~63LL);      // 256-byte aligned rows
     const float* x = n2;
     for (int l = 0; l < RN; ++l) {
       float* hin = lay + (size_t)(2 * l) * rows * 64;
@@ -805,7 +805,7 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
   hs[0] = ws + B * 64; hm[0] = ws + B * 128; gates[0] = ws + B * 256;
   float* mpos = ws + B * (512 + wide);
   for (int l = 1; l < RN; ++l) {
-    float* base = ws + B * (513 + wide) + (size_t)(l - 1) * B * 384;
+    float* base = ws + ((B * (513 + wide) + 63) & ~63LL) + (size_t)(l - 1) * B * 384;     // 256-byte aligned rows
     hs[l] = base; hm[l] = base + B * 64; gates[l] = base + B * 128;
   }
   a.workspace = ws + B * 512;                            // the wide first layer's scratch, if the base needs one
