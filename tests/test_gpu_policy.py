@@ -248,3 +248,30 @@ def test_critic_on_the_buffers_replicated_share_obs_view(golden_dir):
     full3 = torch.randn(N, M, S, device="cuda")
     torch.testing.assert_close(pol.get_values(full3, None, None), pol.get_values(full3.reshape(N * M, S), None, None),
                                rtol=0, atol=0)
+
+
+def test_raw_inputs_beyond_the_fp16_range_do_not_poison_the_tensor_core_path():
+    """--use_feature_normalization off: raw observations are the one operand the network does not bound.  The fp16 `hi`
+    halves of the tensor-core operands saturate at +-65504 instead of turning into inf -> NaN (DESIGN.md 4.1 "operand
+    range"): an outlier row stays finite and the other rows are untouched."""
+    from mappo_b200.envs.spaces import Discrete
+    from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
+    args = types.SimpleNamespace(hidden_size=64, layer_N=1, use_ReLU=False, use_feature_normalization=False,
+                                 use_orthogonal=True, use_recurrent_policy=False, use_naive_recurrent_policy=False,
+                                 recurrent_N=1, use_popart=False, gain=0.01, use_policy_active_masks=True, seed=1,
+                                 lr=7e-4, critic_lr=7e-4, opti_eps=1e-5, weight_decay=0.0)
+    torch.manual_seed(0)
+    pol = R_MAPPOPolicy(args, make_space(18), make_space(54), Discrete(5), device="cuda")
+    obs = torch.randn(300, 18, device="cuda")
+    share = torch.randn(300, 54, device="cuda")
+    a0, lp0, _ = pol.actor(obs, None, None, None, deterministic=True)
+    v0 = pol.get_values(share, None, None)
+    obs2, share2 = obs.clone(), share.clone()
+    obs2[7, 3] = 1e6; obs2[9, 0] = -3e38; share2[11, 5] = 1e7
+    a1, lp1, _ = pol.actor(obs2, None, None, None, deterministic=True)
+    v1 = pol.get_values(share2, None, None)
+    assert torch.isfinite(lp1).all() and torch.isfinite(v1).all()
+    keep = torch.ones(300, dtype=torch.bool, device="cuda"); keep[[7, 9]] = False
+    assert torch.equal(lp1[keep], lp0[keep]) and torch.equal(a1[keep], a0[keep])
+    keepv = torch.ones(300, dtype=torch.bool, device="cuda"); keepv[11] = False
+    assert torch.equal(v1[keepv], v0[keepv])
