@@ -41,7 +41,9 @@ struct Map {
 // raw_floats > 0: a landing buffer for the NEXT tile's input rows as one bulk (TMA) copy -- used when the rows of a tile
 // are contiguous in global memory (no gather, row stride = in_dim), so that no thread issues row-divergent loads.
 // vhead: scalar (value) head whose weight gradient accumulates in registers: no n2 / dlogits operand tiles.
-__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0, bool vhead = false) {
+// early: the NEXT tile's fc1 is issued at the second synchronisation of the tile (see the kernel): both X buffers are busy
+// over the span the partial logits live, so they get a private region.
+__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0, bool vhead = false, bool early = false) {
   Map m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
@@ -64,7 +66,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.bhf = take(kMaxA * 4);
   m.dbh = take(update ? kBM * AS * 4 : 0);
   m.xch = take(2 * 4 * kBM * 8);
-  m.xlog_in_x = (update && (uint32_t)(4 * kBM * AS * 4) <= kNP * m.x_piece) ? 1 : 0;
+  m.xlog_in_x = (update && !early && (uint32_t)(4 * kBM * AS * 4) <= kNP * m.x_piece) ? 1 : 0;
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 3);
   m.bars = take(64);
@@ -154,12 +156,12 @@ __device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a16, uint32_t b
 // this thread's 16 accumulator columns: acc0 + 2^-12 acc1
 // DUAL: both blocks in flight under one wait (16 more live registers for the duration of the load)
 template <bool DUAL>
-__device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16]) {
+__device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16], uint32_t c0 = kColAcc, uint32_t c1 = kColAcc1) {
   float w[16];
-  if (DUAL) umma::tmem_ld16x2(lane_addr + kColAcc + 16 * cq, lane_addr + kColAcc1 + 16 * cq, v, w);
+  if (DUAL) umma::tmem_ld16x2(lane_addr + c0 + 16 * cq, lane_addr + c1 + 16 * cq, v, w);
   else {
-    umma::tmem_ld16(lane_addr + kColAcc + 16 * cq, v);
-    umma::tmem_ld16(lane_addr + kColAcc1 + 16 * cq, w);
+    umma::tmem_ld16(lane_addr + c0 + 16 * cq, v);
+    umma::tmem_ld16(lane_addr + c1 + 16 * cq, w);
   }
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
@@ -306,6 +308,12 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
   sums[0] = -fminf(s1, s2) * active; sums[1] = ent * active; sums[2] = ratio; sums[3] = active;
 }
 
+// which instantiations run the EARLY schedule (see the kernel): update, fused first layer, 32-wide input tile (the
+// second accumulator pair needs 128 free TMEM columns), head narrow enough for a private partial-logit region
+__host__ __device__ constexpr bool early_tile(int mode, int kp, int amax, bool wide) {
+  return (mode == 2 || mode == 3 || mode == 5) && !wide && kp == 32 && amax <= 8;
+}
+
 // ---- the kernel ------------------------------------------------------------------------------------------
 // MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic; recurrent networks (mlp_gru.cu) use
 // 4 = base features only (n2 rows written to a.feat) and 5 = base backward from dLoss/dn2 rows read from a.feat.
@@ -324,18 +332,30 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE == 2 || MODE == 3 || MODE == 5);
   constexpr bool HEAD = (MODE < 4);
   constexpr bool VHEAD = (MODE == 3);                                  // critic update: head gradient in registers
+  // EARLY (update kernels with a 32-wide input tile and a head of at most 8 logits): fc1 owns a second accumulator pair
+  // (TMEM columns 352 / 416; the head gradient moves to 480), the NEXT tile's input rows are staged while fc2 runs, and
+  // its fc1 is issued together with the data-gradient GEMM at the tile's second synchronisation -- the tile boundary
+  // has no MMA wait left.  DEFER: operand stores only the weight-gradient GEMMs read (n2, dlogits) and the head-bias
+  // sums wait until the data-gradient GEMM is running; the head weight gradient joins the last group of the tile.
+  constexpr bool EARLY = early_tile(MODE, KP, AMAX, WIDE);
+  constexpr bool DEFER = UPDATE && !WIDE;
+  constexpr uint32_t kF0 = EARLY ? 352u : kColAcc, kF1 = EARLY ? 416u : kColAcc1, kGh = EARLY ? 480u : kColGh;
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
   const NetLayout& L = a.L;
   const int A = AFIX > 0 ? AFIX : L.a_total, relu = ACT >= 0 ? ACT : L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD);
+  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD, EARLY);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
   uint64_t* tbar = bar + 1;                                           // arrival of a bulk-copied input tile
   uint64_t* gbar = bar + 2;                                           // completion of the weight-gradient MMAs (background)
-  if (tid == 0) { umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::mbar_init(gbar, 1); umma::fence_mbar_init(); }
+  uint64_t* fbar = bar + 3;                                           // EARLY: completion of fc1
+  if (tid == 0) {
+    umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::mbar_init(gbar, 1); umma::mbar_init(fbar, 1);
+    umma::fence_mbar_init();
+  }
   const float* raw = reinterpret_cast<const float*>(sm + m.raw);
   const uint32_t raw_bytes = (uint32_t)(kBM * D) * 4u;
   uint32_t tph = 0;
@@ -394,10 +414,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128 + 16, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
   if (!WIDE && issuer_next && umma::elect_one()) {
-    issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
-    umma::mma_commit(bar);
+    issue_rowgemm<KP / 16>(tb + kF0, tb + kF1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
+    umma::mma_commit(EARLY ? fbar : bar);
   }
-  uint32_t ph = 0, gph = 0;
+  uint32_t ph = 0, gph = 0, fph = 0;
   int buf = 0;
   bool first = true;
   float db1[WIDE ? 16 : 1], ghv[VHEAD ? 16 : 1];      // WIDE: the fc1 weight gradient (and its ones column) lives outside
@@ -442,9 +462,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         n1[4 * i] = z.x; n1[4 * i + 1] = z.y; n1[4 * i + 2] = z.z; n1[4 * i + 3] = z.w;
       }
     } else {
-      umma::mbar_wait(bar, ph); ph ^= 1;
+      if (EARLY) { umma::mbar_wait(fbar, fph); fph ^= 1; }
+      else { umma::mbar_wait(bar, ph); ph ^= 1; }
       umma::tc_fence_after();
-      load_acc16<true>(lane_addr, cq, n1);
+      load_acc16<true>(lane_addr, cq, n1, kF0, kF1);
     }
     act_ln16(n1, b1f, b1s, relu, xch, slot, cq, r, q4, mean1, rstd1);
     store_cols16(sm + m.N1, r, cq, n1);
@@ -459,10 +480,14 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // rollout: the next tile's input rows are staged while fc2 runs, and its fc1 is issued as soon as every warp has
     // its fc2 accumulators in registers, so both GEMMs hide under epilogue work
     if (!UPDATE && !WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
+    if (EARLY) {                                                          // the same under fc2 of the update
+      if (!first) { umma::mbar_wait(gbar, gph); gph ^= 1; }               // previous tile's G1 / Gh: frees the other X buffer, BS, n2, dlogits
+      if (has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
+    }
     // ---- layer 2 epilogue + head
     float n2[16], mean2, rstd2;
     umma::mbar_wait(bar, ph); ph ^= 1;
-    if (UPDATE && !WIDE && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }   // previous tile's G1: frees the other X buffer and BS
+    if (UPDATE && !WIDE && !EARLY && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }   // previous tile's G1: frees the other X buffer and BS
     umma::tc_fence_after();
     load_acc16<true>(lane_addr, cq, n2);
     if (!UPDATE && !WIDE) {
@@ -478,7 +503,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       }
     }
     act_ln16(n2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
-    if (UPDATE && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
+    if (UPDATE && HEAD && !VHEAD && !DEFER) store_cols16(sm + m.BS2, r, cq, n2);
     if (MODE == 4 && valid) {
       float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
 #pragma unroll
@@ -553,6 +578,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (cq == 0) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) lacc[q] += mine[q];
+      }
+    }
+    // what only the head's weight / bias gradients need: the dlogits operand tile, the head-bias sums, (DEFER) n2
+    auto head_operands = [&]() {
+      if (HEAD && cq == 0) {
         float d16[16];
         float* dbh = reinterpret_cast<float*>(sm + m.dbh) + r * AS;
 #pragma unroll
@@ -571,11 +601,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
           }
         }
       }
-    }
-    if (VHEAD) {
+      if (VHEAD) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) ghv[i] = fmaf(dl[0], n2[i], ghv[i]);      // G_v[k] += dv n2[k]
-    }
+        for (int i = 0; i < 16; ++i) ghv[i] = fmaf(dl[0], n2[i], ghv[i]);    // G_v[k] += dv n2[k]
+      }
+      if (DEFER && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
+    };
+    if (!DEFER) head_operands();
     // ---- back through the head and layer 2
     float dz[16];
 #pragma unroll
@@ -606,12 +638,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::tc_fence_after();
       issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
-      if (HEAD && !VHEAD) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);                             // Gh += n2^T dlogits
+      if (EARLY && has_next) {                                                                  // the next tile's fc1
+        issue_bulk(tile + 2 * (long long)gridDim.x);
+        issue_rowgemm<KP / 16>(tb + kF0, tb + kF1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+                               128, 2 * kWChunk16, kIdFwd);
+        umma::mma_commit(fbar);
+      }
+      if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kGh, sB2, sDL, kIdGh, !first);            // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
       umma::mma_commit(gbar);
     }
+    if (DEFER) head_operands();
     // ---- next tile's input rows, staged while the tensor cores work
-    if (!WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
+    if (!WIDE && !EARLY && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
@@ -637,12 +676,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     __syncthreads();
     if (issuer_next && umma::elect_one()) {
       umma::tc_fence_after();
-      if (has_next) issue_bulk(tile + 2 * (long long)gridDim.x);
-      if (has_next) {
+      if (!EARLY && has_next) {
+        issue_bulk(tile + 2 * (long long)gridDim.x);
         issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(bar);
       }
+      if (HEAD && !VHEAD && DEFER) issue_wgrad(tb + kGh, sB2, sDL, kIdGh, !first);             // Gh += n2^T dlogits
       issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);                      // G1 += dz1^T x
       umma::mma_commit(gbar);
     }
@@ -697,8 +737,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         gp[L.b2 + mrow] = u[0] * lane_scale;
       }
       if (HEAD && !VHEAD && cq == 3) {                                    // warps 12..15: head gradient, lanes = hidden unit
-        umma::tmem_ld16(lane_addr + kColGh, u);
-        umma::tmem_ld16(lane_addr + kColGh + 16, w);
+        umma::tmem_ld16(lane_addr + kGh, u);
+        umma::tmem_ld16(lane_addr + kGh + 16, w);
         int h = 0, off = 0;
 #pragma unroll
         for (int q = 0; q < AMAX; ++q) {
@@ -783,18 +823,22 @@ bool supports(const mappo_net_config* cfg) {
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
   const int Kp = (wide || cfg->in_dim < 32) ? 32 : 64;
-  return make_map(Kp, A | 1, true).total <= (uint32_t)kMaxDynSmem && make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
+  const bool early = !wide && Kp == 32 && A <= 8;                      // early_tile() of the instantiation launch() picks
+  return make_map(Kp, A | 1, true, 0, false, early).total <= (uint32_t)kMaxDynSmem &&
+         make_map(Kp, A | 1, true, 0, false, false).total <= (uint32_t)kMaxDynSmem &&
+         make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
 template <int MODE, int KP, int AMAX, bool WIDE, int AFIX, int ACT>
 static int launch_inst(MlpArgs& a, cudaStream_t stream, const char* who) {
   constexpr bool kUpd = (MODE == 2 || MODE == 3 || MODE == 5);
+  constexpr bool kEarly = early_tile(MODE, KP, AMAX, WIDE);
   // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
   a.raw_ok = 0;
   if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && (reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 &&
-      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3).total <= (uint32_t)kMaxDynSmem)
+      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3, kEarly).total <= (uint32_t)kMaxDynSmem)
     a.raw_ok = 1;
-  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3);
+  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3, kEarly);
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE, AFIX, ACT>;
   static bool attr_set = false;
   if (!attr_set) {
