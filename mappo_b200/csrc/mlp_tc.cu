@@ -442,15 +442,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (WIDE) umma::l2_prefetch(a.z1 + g0 * 64, bytes);
       if (MODE == 5) umma::l2_prefetch(a.feat + g0 * 64, bytes);
     }
-    // per-row scalars of the register loss path, requested now and consumed after the second layer
-    float p_actf = 0.0f;                              // converted at its use: no wait on the load up here
+    // per-row scalars of the register loss path: requested once fc2 is issued (below), consumed after the second layer
+    float p_actf = 0.0f;                              // converted at its use: no wait on the load
     float p_old = 0.0f, p_adv = 0.0f, p_active = 1.0f;
-    if (MODE == 2 && AMAX == 8 && valid) {
-      p_actf = __ldg(a.actions + src);
-      p_old = __ldg(a.old_logp + src);
-      p_adv = __ldg(a.adv + src);
-      if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
-    }
     // ---- layer 1 epilogue
     float n1[16], mean1, rstd1;
     if (WIDE) {
@@ -480,6 +474,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // rollout: the next tile's input rows are staged while fc2 runs, and its fc1 is issued as soon as every warp has
     // its fc2 accumulators in registers, so both GEMMs hide under epilogue work
     if (!UPDATE && !WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
+    if (MODE == 2 && AMAX == 8 && valid) {
+      p_actf = __ldg(a.actions + src);
+      p_old = __ldg(a.old_logp + src);
+      p_adv = __ldg(a.adv + src);
+      if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
+    }
     if (EARLY) {                                                          // the same under fc2 of the update
       if (!first) { umma::mbar_wait(gbar, gph); gph ^= 1; }               // previous tile's G1 / Gh: frees the other X buffer, BS, n2, dlogits
       if (has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
