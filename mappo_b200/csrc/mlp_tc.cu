@@ -480,6 +480,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       p_adv = __ldg(a.adv + src);
       if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
     }
+    if (MODE == 3 && valid && cq == 0) {                                  // value-loss inputs of this row's terms: warm the L1
+      const long long o = src * a.group, e = o + a.group - 1;
+      umma::l1_prefetch(a.returns + o); umma::l1_prefetch(a.returns + e);
+      umma::l1_prefetch(a.value_preds + o); umma::l1_prefetch(a.value_preds + e);
+      if (a.loss.use_value_active_masks && a.active) { umma::l1_prefetch(a.active + o); umma::l1_prefetch(a.active + e); }
+    }
     if (EARLY) {                                                          // the same under fc2 of the update
       if (!first) { umma::mbar_wait(gbar, gph); gph ^= 1; }               // previous tile's G1 / Gh: frees the other X buffer, BS, n2, dlogits
       if (has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
