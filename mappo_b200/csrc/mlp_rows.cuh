@@ -37,6 +37,7 @@ struct MlpArgs {
   // recurrent networks (mlp_gru.cu): n2 rows out (base features) / dLoss/dn2 rows in (base backward), [rows][64]
   float* feat;
   int raw_ok;                      // mlp_tc.cu: input tiles are contiguous and arrive by bulk copy
+  int rowp_ok;                     // mlp_tc.cu: so do the per-row loss scalars (actions, old log-probs, advantages, active masks)
 };
 
 // log-softmax over l[0..n): returns logsumexp, writes logp in place

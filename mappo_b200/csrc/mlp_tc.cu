@@ -2,11 +2,12 @@
 //
 // One persistent CTA per SM (512 threads) walks tiles of 128 rows.  Every dense contraction of the tile -- fc1, fc2,
 // the data gradient through fc2, and the three weight gradients -- is a `tcgen05.mma.kind::f16` on fp16 operand
-// PAIRS: each fp32 operand x is carried as hi = fp16(x) and lo = fp16((x - hi) * 2^12) -- 22 significant bits, and
-// an absolute resolution of 2^-36 below the fp16 normal range; valid for |x| < 65504, which LayerNorm outputs
-// (|n| <= sqrt(63)), folded weights and per-sample gradients satisfy -- and the products hi*hi and
-// (hi*lo + lo*hi) accumulate in fp32 in two tensor-memory accumulators that the epilogue combines as
-// acc0 + 2^-12 acc1 (the weight gradients keep all four products in separate accumulator blocks).
+// PAIRS: each fp32 operand x is scaled by a power of two S fixed per operand class (mlp_tc_common.cuh: 64 for
+// LayerNorm outputs and weights, 16 for input rows and per-sample gradients) and carried as hi = fp16(S x) and
+// lo = fp16(S x - hi) -- 22 significant bits, an absolute resolution of 2^-25 / S, valid for |x| < 65504 / S.  Both
+// halves carry the same scale, so the products hi*hi + hi*lo + lo*hi accumulate in ONE fp32 tensor-memory
+// accumulator whose power-of-two scale the epilogue removes inside its first FFMA; the weight gradients stack the
+// hi and lo halves of A along M and of B along N (four equally scaled blocks, added when they leave the kernel).
 // Operands live in shared memory in the chunk-major layout of umma.cuh, where the same bytes serve as the K-major
 // operand of the forward / data-gradient GEMMs and as the MN-major operand of the weight-gradient GEMMs, so every
 // activation is written to shared memory exactly once.  Everything between the GEMMs (bias, tanh / ReLU,
@@ -22,15 +23,16 @@ namespace mappo {
 namespace tc {
 
 constexpr int kTmemCols = 512;
+constexpr float kRawMax = 4094.0f;                  // 65504 / kSX, rounded down to an fp16-exact value after scaling
 // TMEM column map.  The BIAS gradients sum_rows dz come off the tensor cores too: the n1 operand tile ends in a constant
 // chunk whose first column is 1 (column 128 of G2), and the input tile carries a 1 in its first padding column
 // (column in_dim of G1; W1' is zero there, so the forward pass does not see it).
-constexpr uint32_t kColAcc = 0, kColAcc1 = 64, kColG2 = 128, kColG1 = 288, kColGh = 448;
+constexpr uint32_t kColAcc = 0, kColF = 64, kColG2 = 128, kColG1 = 272, kColGh = 400;   // 64 | 64 | 144 | <= 128 | 32
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
 struct Map {
-  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, b1s, b2s, bhf, dbh, xch, xlog, red, bars, raw, total;
-  uint32_t x_piece, w1_piece, x_buf;
+  uint32_t X, N1, BS, BS2, W1, W2, DL, Whf, b1f, b2f, b1s, b2s, bhf, dbh, xch, xlog, red, bars, rowp, raw, total;
+  uint32_t x_piece, w1_piece, x_buf, n1_lo;
   int xlog_in_x;                 // 1: the head's partial logits live in the idle X buffer (see below), `xlog` unused
 };
 // The partial logits [4 column quarters][128 rows][AS] are written after the second layer and read before the
@@ -52,7 +54,8 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   const uint32_t ones = update ? 2 * kRowChunk : 0;  // the constant [1 0 .. 0] columns behind the n1 tile (bias gradient)
   m.x_buf = kNP * m.x_piece;
   m.X = take(2 * m.x_buf);                         // two buffers: this tile's rows and the next tile's
-  m.N1 = take(kNP * 8 * kRowChunk + ones);
+  m.N1 = take(kNP * 8 * kRowChunk + ones);          // [hi | lo | ones]: ONE B operand of the fc2 weight gradient (N = 144)
+  m.n1_lo = 8 * kRowChunk;
   m.BS = take(update ? kNP * 8 * kRowChunk : 0);    // dz2, then dz1
   m.BS2 = take(update && !vhead ? kNP * 8 * kRowChunk : 0);   // n2 (operand of the head weight gradient)
   m.W1 = take(kNP * m.w1_piece);
@@ -70,6 +73,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 3);
   m.bars = take(64);
+  m.rowp = take(update ? 4 * kBM * 4 : 0);           // per-row loss scalars of one tile, [4][128] (bulk copy, see rowp_ok)
   m.raw = take((uint32_t)raw_floats * 4);
   m.total = o;
   return m;
@@ -84,11 +88,11 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     const int j = e / Kp, k = e - j * Kp;
     float v = 0.0f;
     if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
-    put_pair(sm + m.W1, m.w1_piece, 64, j, k, v);
+    put_pair_u(sm + m.W1, m.w1_piece, 64, j, k, v * kSW);
   }
   for (int e = tid; e < 64 * 64; e += kThreads) {
     const int j = e >> 6, k = e & 63;
-    put_pair(sm + m.W2, 8 * kWChunk, 64, j, k, P[L.w2 + j * 64 + k] * P[L.g1 + k]);
+    put_pair_u(sm + m.W2, 8 * kWChunk, 64, j, k, P[L.w2 + j * 64 + k] * P[L.g1 + k] * kSW);
   }
   float* Whf = reinterpret_cast<float*>(sm + m.Whf);
   for (int e = tid; e < kMaxA * 64; e += kThreads) {
@@ -128,9 +132,9 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
 // Operand addresses and strides arrive in 16-BYTE UNITS (shared-memory base >> 4 plus compile-time offsets), so a
 // descriptor costs one uniform add (umma::smem_desc16).
 constexpr uint32_t kRowChunk16 = kRowChunk >> 4, kWChunk16 = kWChunk >> 4;
-// forward-type GEMM: ACC0[128][64] = A_hi . B_hi^T, ACC1 = A_hi . B_lo^T + A_lo . B_hi^T; A K-major 128-row tile
+// forward-type GEMM: ACC[128][64] = A_hi . B_hi^T + A_hi . B_lo^T + A_lo . B_hi^T; A K-major 128-row tile
 template <int KSTEPS>
-__device__ __forceinline__ void issue_rowgemm(uint32_t acc0, uint32_t acc1, uint32_t a16, uint32_t a_piece16,
+__device__ __forceinline__ void issue_rowgemm(uint32_t acc, uint32_t a16, uint32_t a_piece16,
                                               uint32_t b16, uint32_t b_piece16, uint32_t b_lbo, uint32_t b_sbo,
                                               uint32_t b_kstep16, uint32_t idesc) {
 #pragma unroll
@@ -138,12 +142,14 @@ __device__ __forceinline__ void issue_rowgemm(uint32_t acc0, uint32_t acc1, uint
     const uint32_t ao = a16 + (uint32_t)ks * 2 * kRowChunk16, bo = b16 + (uint32_t)ks * b_kstep16;
     const uint64_t ah = umma::smem_desc16(ao, kRowChunk, 128), al = umma::smem_desc16(ao + a_piece16, kRowChunk, 128);
     const uint64_t bh = umma::smem_desc16(bo, b_lbo, b_sbo), bl = umma::smem_desc16(bo + b_piece16, b_lbo, b_sbo);
-    umma::mma_f16(acc0, ah, bh, idesc, ks > 0);
-    umma::mma_f16(acc1, ah, bl, idesc, ks > 0);
-    umma::mma_f16(acc1, al, bh, idesc, true);
+    umma::mma_f16(acc, ah, bh, idesc, ks > 0);
+    umma::mma_f16(acc, ah, bl, idesc, true);
+    umma::mma_f16(acc, al, bh, idesc, true);
   }
 }
-// weight-gradient GEMM: G[128 = (hi cols | lo cols) of A][N] += A^T . B over the 128 tile rows; both MN-major
+// weight-gradient GEMM: G[128 = (hi cols | lo cols) of A][N = (hi cols | lo cols [| ones]) of B] += A^T . B over the
+// 128 tile rows; both MN-major.  One instruction per 16 rows yields all four products in four accumulator blocks
+// (same scale: they are simply added when they leave the kernel).
 __device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a16, uint32_t b16, uint32_t idesc, bool accum) {
 #pragma unroll
   for (int ks = 0; ks < kBM / 16; ++ks) {
@@ -153,29 +159,23 @@ __device__ __forceinline__ void issue_wgrad(uint32_t g, uint32_t a16, uint32_t b
   }
 }
 
-// this thread's 16 accumulator columns: acc0 + 2^-12 acc1
-// DUAL: both blocks in flight under one wait (16 more live registers for the duration of the load)
-template <bool DUAL>
-__device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16], uint32_t c0 = kColAcc, uint32_t c1 = kColAcc1) {
-  float w[16];
-  if (DUAL) umma::tmem_ld16x2(lane_addr + c0 + 16 * cq, lane_addr + c1 + 16 * cq, v, w);
-  else {
-    umma::tmem_ld16(lane_addr + c0 + 16 * cq, v);
-    umma::tmem_ld16(lane_addr + c1 + 16 * cq, w);
-  }
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = fmaf(w[i], kLoInv, v[i]);
+// this thread's 16 accumulator columns (still carrying the product of the two operand scales)
+__device__ __forceinline__ void load_acc16(uint32_t lane_addr, int cq, float (&v)[16], uint32_t col) {
+  umma::tmem_ld16(lane_addr + col + 16 * cq, v);
 }
 
-// activation -> LayerNorm (no affine) of this thread's 16 columns; returns n in t[], (mean, rstd) of the row.
-// tanh takes its argument pre-scaled: 2 log2(e) (z + b) = fma(z, 2 log2(e), bias_s) with bias_s = 2 log2(e) b, so the
-// bias add and the scaling are one FFMA; the normalisation is one FFMA per element, n = fma(t, rstd, -mean rstd).
-__device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict__ bias, const float* __restrict__ bias_s,
+// activation -> LayerNorm (no affine) of this thread's 16 columns.  In: accumulator columns t[] = z / inv (inv = 1 over
+// the product of the operand scales; 1 for rows that arrive unscaled).  Out: t[] = kSN n (what the operand tile and the
+// backward pass hold), (mean, rstd) of the row.
+// tanh takes its argument pre-scaled: 2 log2(e) (z + b) = fma(t, 2 log2(e) inv, bias_s) with bias_s = 2 log2(e) b, so the
+// unscaling, the bias add and the scaling are one FFMA; the normalisation is one FFMA per element.
+__device__ __forceinline__ void act_ln16(float (&t)[16], float inv, const float* __restrict__ bias, const float* __restrict__ bias_s,
                                          int relu, float2* xch, int& slot, int cq, int r, int q4, float& mean, float& rstd) {
   float s = 0.0f, q = 0.0f;
+  const float ts = kTanhScale * inv;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    t[i] = relu ? fmaxf(t[i] + bias[i], 0.0f) : tanh_scaled(fmaf(t[i], kTanhScale, bias_s[i]));
+    t[i] = relu ? fmaxf(fmaf(t[i], inv, bias[i]), 0.0f) : tanh_scaled(fmaf(t[i], ts, bias_s[i]));
     s += t[i];
     q = fmaf(t[i], t[i], q);
   }
@@ -183,27 +183,29 @@ __device__ __forceinline__ void act_ln16(float (&t)[16], const float* __restrict
   mean = tot.x * (1.0f / 64.0f);
   const float var = fmaxf(fmaf(-mean, mean, tot.y * (1.0f / 64.0f)), 0.0f);
   rstd = 1.0f / sqrtf(var + kLnEps);
-  const float nmr = -(mean * rstd);
+  const float rs = rstd * kSN, nmr = -(mean * rstd) * kSN;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) t[i] = fmaf(t[i], rstd, nmr);
+  for (int i = 0; i < 16; ++i) t[i] = fmaf(t[i], rs, nmr);
 }
 
-// dn (gradient w.r.t. the LayerNorm output n) -> dz (gradient w.r.t. the pre-activation), in place:
-// dz = rstd (dn - mean(dn) - n mean(dn n)) act'(z), with rstd folded into the two FFMAs
-__device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[16], float mean, float rstd, int relu,
-                                             float2* xch, int& slot, int cq, int r, int q4) {
+// dn (gradient w.r.t. the LayerNorm output, times 1 / dn_inv) -> out_s dz (gradient w.r.t. the pre-activation, times the
+// scale of the operand tile it goes to), in place; n[] = kSN n as act_ln16 left it:
+// dz = rstd (dn - mean(dn) - n mean(dn n)) act'(z), every power-of-two factor folded into the three row coefficients
+__device__ __forceinline__ void ln_act_bwd16(float (&dn)[16], const float (&n)[16], float mean, float rstd, int relu, float dn_inv,
+                                             float out_s, float2* xch, int& slot, int cq, int r, int q4) {
   float s1 = 0.0f, s2 = 0.0f;
 #pragma unroll
   for (int i = 0; i < 16; ++i) { s1 += dn[i]; s2 = fmaf(dn[i], n[i], s2); }
   const float2 tot = row_sum2(s1, s2, xch, slot, cq, r, q4);
-  const float rs1 = -(tot.x * (1.0f / 64.0f)) * rstd, rs2 = -(tot.y * (1.0f / 64.0f)) * rstd;
-  const float sd = 1.0f / rstd, nz = -(mean * rstd);
+  const float c1 = rstd * (dn_inv * out_s);
+  const float c0 = -(tot.x * (1.0f / 64.0f)) * c1, c2 = -(tot.y * (1.0f / 64.0f)) * (c1 * (1.0f / (kSN * kSN)));
+  const float sd = (1.0f / rstd) * (1.0f / kSN), nz = -(mean * rstd) * kSN;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
     float da;
-    if (relu) da = (n[i] != nz) ? 1.0f : 0.0f;            // t == 0  <=>  n == fma(0, rstd, -mean rstd), bit for bit
+    if (relu) da = (n[i] != nz) ? 1.0f : 0.0f;            // t == 0  <=>  kSN n == fma(0, rstd kSN, nz), bit for bit
     else { const float t = fmaf(n[i], sd, mean); da = fmaf(-t, t, 1.0f); }
-    dn[i] = fmaf(n[i], rs2, fmaf(dn[i], rstd, rs1)) * da;
+    dn[i] = fmaf(n[i], c2, fmaf(dn[i], c1, c0)) * da;
   }
 }
 
@@ -246,22 +248,22 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
     }
     const float rstd = 1.0f / sqrtf(row_sum2(q, 0.0f, xch, slot, cq, r, q4).x / (float)D + kLnEps);
 #pragma unroll
-    for (int i = 0; i < XC; ++i) xv[i] *= rstd;
+    for (int i = 0; i < XC; ++i) xv[i] *= rstd * kSX;
   } else {
     // raw (un-normalised) inputs are the only operands whose magnitude the network does not bound: saturate them at
-    // the fp16 range of the hi halves so that an outlier becomes +-65504 instead of inf -> NaN in the MMA (the fp32
-    // FMA path has no such limit; MPE observations are O(1), see DESIGN.md section 4.1 "operand range")
+    // the fp16 range of the scaled hi halves so that an outlier becomes +-4094 instead of inf -> NaN in the MMA (the
+    // fp32 FMA path has no such limit; MPE observations are O(1), see DESIGN.md section 4.1 "operand range")
 #pragma unroll
-    for (int i = 0; i < XC; ++i) xv[i] = fminf(fmaxf(xv[i], -65504.0f), 65504.0f);
+    for (int i = 0; i < XC; ++i) xv[i] = fminf(fmaxf(xv[i], -kRawMax), kRawMax) * kSX;
   }
   if (ONES) {
 #pragma unroll
-    for (int i = 0; i < XC; ++i) if (XC * cq + i == D) xv[i] = 1.0f;
+    for (int i = 0; i < XC; ++i) if (XC * cq + i == D) xv[i] = kSX;
   }
 #pragma unroll
   for (int h = 0; h < XC / 8; ++h) {
     uint4 hi, lo;
-    split8(xv + 8 * h, hi, lo);
+    split8u(xv + 8 * h, hi, lo);
     const uint32_t off = (uint32_t)(XC / 8 * cq + h) * kRowChunk + (uint32_t)r * 16;
     *reinterpret_cast<uint4*>(xs + off) = hi;
     *reinterpret_cast<uint4*>(xs + x_piece + off) = lo;
@@ -308,10 +310,10 @@ __device__ __forceinline__ void actor_loss_regs(const mappo_loss_config& c, int 
   sums[0] = -fminf(s1, s2) * active; sums[1] = ent * active; sums[2] = ratio; sums[3] = active;
 }
 
-// which instantiations run the EARLY schedule (see the kernel): update, fused first layer, 32-wide input tile (the
-// second accumulator pair needs 128 free TMEM columns), head narrow enough for a private partial-logit region
+// which instantiations run the EARLY schedule (see the kernel): update, fused first layer, and a shared-memory map
+// that still fits with a private partial-logit region (32-wide input tile and at most 8 logits, or the critic)
 __host__ __device__ constexpr bool early_tile(int mode, int kp, int amax, bool wide) {
-  return (mode == 2 || mode == 3 || mode == 5) && !wide && kp == 32 && amax <= 8;
+  return (mode == 2 || mode == 3 || mode == 5) && !wide && (kp == 32 ? amax <= 8 : mode == 3);
 }
 
 // ---- the kernel ------------------------------------------------------------------------------------------
@@ -332,14 +334,16 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr bool UPDATE = (MODE == 2 || MODE == 3 || MODE == 5);
   constexpr bool HEAD = (MODE < 4);
   constexpr bool VHEAD = (MODE == 3);                                  // critic update: head gradient in registers
-  // EARLY (update kernels with a 32-wide input tile and a head of at most 8 logits): fc1 owns a second accumulator pair
-  // (TMEM columns 352 / 416; the head gradient moves to 480), the NEXT tile's input rows are staged while fc2 runs, and
-  // its fc1 is issued together with the data-gradient GEMM at the tile's second synchronisation -- the tile boundary
-  // has no MMA wait left.  DEFER: operand stores only the weight-gradient GEMMs read (n2, dlogits) and the head-bias
+  // EARLY (update kernels whose shared-memory map has room for a private partial-logit region): fc1 owns a second
+  // accumulator (TMEM columns 64..127), the NEXT tile's input rows are staged while fc2 runs, and its fc1 is issued
+  // together with the data-gradient GEMM at the tile's second synchronisation -- the tile boundary has no MMA wait left.  DEFER: operand stores only the weight-gradient GEMMs read (n2, dlogits) and the head-bias
   // sums wait until the data-gradient GEMM is running; the head weight gradient joins the last group of the tile.
   constexpr bool EARLY = early_tile(MODE, KP, AMAX, WIDE);
   constexpr bool DEFER = UPDATE && !WIDE;
-  constexpr uint32_t kF0 = EARLY ? 352u : kColAcc, kF1 = EARLY ? 416u : kColAcc1, kGh = EARLY ? 480u : kColGh;
+  constexpr uint32_t kF = EARLY ? kColF : kColAcc;
+  // 1 / (product of the operand scales) of the three row GEMMs, and of the weight-gradient accumulators
+  constexpr float kInvFc1 = WIDE ? 1.0f : 1.0f / (kSX * kSW), kInvFc2 = 1.0f / (kSN * kSW), kInvDg = 1.0f / (kSD * kSW);
+  constexpr float kInvG2 = 1.0f / (kSD * kSN), kInvG1 = 1.0f / (kSD * kSX), kInvGh = 1.0f / (kSN * kSD);
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
@@ -352,10 +356,31 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   uint64_t* tbar = bar + 1;                                           // arrival of a bulk-copied input tile
   uint64_t* gbar = bar + 2;                                           // completion of the weight-gradient MMAs (background)
   uint64_t* fbar = bar + 3;                                           // EARLY: completion of fc1
+  uint64_t* pbar = bar + 4;                                           // arrival of a tile's per-row loss scalars
   if (tid == 0) {
     umma::mbar_init(bar, 1); umma::mbar_init(tbar, 1); umma::mbar_init(gbar, 1); umma::mbar_init(fbar, 1);
+    umma::mbar_init(pbar, 1);
     umma::fence_mbar_init();
   }
+  // per-row scalars of the register loss path (action, old log-prob, advantage, active mask): with contiguous rows they
+  // arrive as four 512-byte bulk copies per tile, requested a tile ahead by one thread -- no thread holds a global
+  // load across the second layer, and nothing of their DRAM latency is exposed
+  constexpr bool ROWP = (MODE == 2 && AMAX == 8);
+  const float* rowp = reinterpret_cast<const float*>(sm + m.rowp);
+  const bool rowp_active = ROWP && a.loss.use_policy_active_masks && a.active;
+  uint32_t pph = 0;
+  auto rowp_tile = [&](long long t) { return ROWP && a.rowp_ok && t < a.ntiles && (t + 1) * kBM <= a.rows; };
+  auto issue_rowp = [&](long long t) {                                // one thread
+    if (!rowp_tile(t)) return;
+    const uint32_t dst = umma::smem_u32(sm + m.rowp), mb = umma::smem_u32(pbar), bytes = kBM * 4u;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes * (rowp_active ? 4u : 3u)) : "memory");
+    auto copy = [&](uint32_t slot_, const float* src_) {
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst + slot_ * bytes), "l"(src_ + t * kBM), "r"(bytes), "r"(mb) : "memory");
+    };
+    copy(0u, a.actions); copy(1u, a.old_logp); copy(2u, a.adv);
+    if (rowp_active) copy(3u, a.active);
+  };
   const float* raw = reinterpret_cast<const float*>(sm + m.raw);
   const uint32_t raw_bytes = (uint32_t)(kBM * D) * 4u;
   uint32_t tph = 0;
@@ -379,7 +404,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   stage_weights_tc(sm, m, a, !WIDE, UPDATE);
   if (UPDATE && tid < kBM) {                                            // the ones columns (written once)
-    const uint4 one = make_uint4(0x00003C00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
+    const uint4 one = make_uint4(0x00005400u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);   // fp16(kSN) = 64
     auto put = [&](unsigned char* base) {
       *reinterpret_cast<uint4*>(base + tid * 16) = one;
       *reinterpret_cast<uint4*>(base + kRowChunk + tid * 16) = zero;
@@ -396,14 +421,14 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   umma::tc_fence_after();
   // MMA groups are issued by one elected lane of warps 0 / 1 / 2 (three different schedulers) in turn
   const bool issuer_fc2 = (warp == 0), issuer_bwd = (warp == 1), issuer_next = (warp == 2);
-  if (issuer_next && umma::elect_one()) issue_bulk(tile + gridDim.x);
+  if (issuer_next && umma::elect_one()) { issue_bulk(tile + gridDim.x); issue_rowp(tile); }
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
   const uint32_t x_bytes = m.x_buf;
   const uint32_t b16 = umma::smem_u32(sm) >> 4;                         // operand addresses in 16-byte units
   const uint32_t sX = b16 + (m.X >> 4), sN1 = b16 + (m.N1 >> 4), sBS = b16 + (m.BS >> 4), sB2 = b16 + (m.BS2 >> 4);
   const uint32_t sW1 = b16 + (m.W1 >> 4), sW2 = b16 + (m.W2 >> 4), sDL = b16 + (m.DL >> 4);
-  const uint32_t x_piece16 = m.x_piece >> 4, w1_piece16 = m.w1_piece >> 4, x_bytes16 = x_bytes >> 4;
+  const uint32_t x_piece16 = m.x_piece >> 4, w1_piece16 = m.w1_piece >> 4, x_bytes16 = x_bytes >> 4, n1_lo16 = m.n1_lo >> 4;
   const float* Whf = reinterpret_cast<const float*>(sm + m.Whf);
   const float* b1f = reinterpret_cast<const float*>(sm + m.b1f) + 16 * cq;
   const float* b2f = reinterpret_cast<const float*>(sm + m.b2f) + 16 * cq;
@@ -414,7 +439,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   constexpr uint32_t kIdG2 = umma::idesc_f16(128, 128 + 16, 1, 1), kIdG1 = umma::idesc_f16(128, kNP * KP, 1, 1);
   constexpr uint32_t kIdGh = umma::idesc_f16(128, 32, 1, 1);
   if (!WIDE && issuer_next && umma::elect_one()) {
-    issue_rowgemm<KP / 16>(tb + kF0, tb + kF1, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
+    issue_rowgemm<KP / 16>(tb + kF, sX, x_piece16, sW1, w1_piece16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
     umma::mma_commit(EARLY ? fbar : bar);
   }
   uint32_t ph = 0, gph = 0, fph = 0;
@@ -459,22 +484,22 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (EARLY) { umma::mbar_wait(fbar, fph); fph ^= 1; }
       else { umma::mbar_wait(bar, ph); ph ^= 1; }
       umma::tc_fence_after();
-      load_acc16<true>(lane_addr, cq, n1, kF0, kF1);
+      load_acc16(lane_addr, cq, n1, kF);
     }
-    act_ln16(n1, b1f, b1s, relu, xch, slot, cq, r, q4, mean1, rstd1);
-    store_cols16(sm + m.N1, r, cq, n1);
+    act_ln16(n1, kInvFc1, b1f, b1s, relu, xch, slot, cq, r, q4, mean1, rstd1);
+    store_cols16u(sm + m.N1, m.n1_lo, r, cq, n1);
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
     if (issuer_fc2 && umma::elect_one()) {
       umma::tc_fence_after();
-      issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sN1, 8 * kRowChunk16, sW2, 8 * kWChunk16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
+      issue_rowgemm<4>(tb + kColAcc, sN1, n1_lo16, sW2, 8 * kWChunk16, kWChunk, 128, 2 * kWChunk16, kIdFwd);
       umma::mma_commit(bar);
     }
     // rollout: the next tile's input rows are staged while fc2 runs, and its fc1 is issued as soon as every warp has
     // its fc2 accumulators in registers, so both GEMMs hide under epilogue work
     if (!UPDATE && !WIDE && has_next) stage_next(tile + gridDim.x, sm + m.X + (buf ^ 1) * x_bytes, slot);
-    if (MODE == 2 && AMAX == 8 && valid) {
+    if (MODE == 2 && AMAX == 8 && valid && !rowp_tile(tile)) {
       p_actf = __ldg(a.actions + src);
       p_old = __ldg(a.old_logp + src);
       p_adv = __ldg(a.adv + src);
@@ -495,7 +520,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     umma::mbar_wait(bar, ph); ph ^= 1;
     if (UPDATE && !WIDE && !EARLY && !first) { umma::mbar_wait(gbar, gph); gph ^= 1; }   // previous tile's G1: frees the other X buffer and BS
     umma::tc_fence_after();
-    load_acc16<true>(lane_addr, cq, n2);
+    load_acc16(lane_addr, cq, n2, kColAcc);
     if (!UPDATE && !WIDE) {
       umma::fence_async_smem();
       umma::tc_fence_before();
@@ -503,17 +528,18 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (has_next && issuer_next && umma::elect_one()) {
         issue_bulk(tile + 2 * (long long)gridDim.x);
         umma::tc_fence_after();
-        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+        issue_rowgemm<KP / 16>(tb + kColAcc, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(bar);
       }
     }
-    act_ln16(n2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
-    if (UPDATE && HEAD && !VHEAD && !DEFER) store_cols16(sm + m.BS2, r, cq, n2);
+    act_ln16(n2, kInvFc2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
+    if (UPDATE && HEAD && !VHEAD && !DEFER) store_cols16u(sm + m.BS2, 8 * kRowChunk, r, cq, n2);
     if (MODE == 4 && valid) {
       float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) fo[i] = make_float4(n2[4 * i], n2[4 * i + 1], n2[4 * i + 2], n2[4 * i + 3]);
+      for (int i = 0; i < 4; ++i)
+        fo[i] = make_float4(n2[4 * i] * (1.0f / kSN), n2[4 * i + 1] * (1.0f / kSN), n2[4 * i + 2] * (1.0f / kSN), n2[4 * i + 3] * (1.0f / kSN));
     }
     float* xlog = reinterpret_cast<float*>(sm + (m.xlog_in_x ? m.X + (buf ^ 1) * x_bytes : m.xlog));
     if (HEAD) {
@@ -528,7 +554,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
             const float4 w = w4[i];
             s = fmaf(n2[4 * i], w.x, fmaf(n2[4 * i + 1], w.y, fmaf(n2[4 * i + 2], w.z, fmaf(n2[4 * i + 3], w.w, s))));
           }
-          mine[q] = s;
+          mine[q] = s * (1.0f / kSN);                       // n2[] holds kSN n2
         }
       }
     }
@@ -560,6 +586,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       double mine[4] = {0.0, 0.0, 0.0, 0.0};
       if (MODE == 2 && AMAX == 8) {
         float sums[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (rowp_tile(tile)) {                                            // a full tile: every row is valid
+          umma::mbar_wait(pbar, pph); pph ^= 1;
+          p_actf = rowp[r]; p_old = rowp[kBM + r]; p_adv = rowp[2 * kBM + r];
+          if (rowp_active) p_active = rowp[3 * kBM + r];
+        }
         if (valid) actor_loss_regs<AMAX>(a.loss, A, l, (int)p_actf, p_old, p_adv, p_active, dl, sums);
         else {
 #pragma unroll
@@ -595,12 +626,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         for (int q = 0; q < 16; ++q) {
           d16[q] = (q < AMAX) ? dl[q < AMAX ? q : 0] : 0.0f;
           if (q < AMAX && q < A) dbh[q] += d16[q];
+          d16[q] *= kSD;
         }
         if (!VHEAD) {
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             uint4 hi, lo;
-            split8(d16 + 8 * h, hi, lo);
+            split8u(d16 + 8 * h, hi, lo);
             const uint32_t off = (uint32_t)h * kRowChunk + (uint32_t)r * 16;
             *reinterpret_cast<uint4*>(sm + m.DL + off) = hi;
             *reinterpret_cast<uint4*>(sm + m.DL + 2 * kRowChunk + off) = lo;
@@ -609,9 +641,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       }
       if (VHEAD) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) ghv[i] = fmaf(dl[0], n2[i], ghv[i]);    // G_v[k] += dv n2[k]
+        for (int i = 0; i < 16; ++i) ghv[i] = fmaf(dl[0], n2[i], ghv[i]);    // G_v[k] += dv (kSN n2[k])
       }
-      if (DEFER && HEAD && !VHEAD) store_cols16(sm + m.BS2, r, cq, n2);
+      if (DEFER && HEAD && !VHEAD) store_cols16u(sm + m.BS2, 8 * kRowChunk, r, cq, n2);
     };
     if (!DEFER) head_operands();
     // ---- back through the head and layer 2
@@ -635,23 +667,24 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         }
       }
     }
-    ln_act_bwd16(dz, n2, mean2, rstd2, relu, xch, slot, cq, r, q4);
-    store_cols16(sm + m.BS, r, cq, dz);
+    ln_act_bwd16(dz, n2, mean2, rstd2, relu, 1.0f, kSD, xch, slot, cq, r, q4);
+    store_cols16u(sm + m.BS, 8 * kRowChunk, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
     if (issuer_bwd && umma::elect_one()) {
       umma::tc_fence_after();
-      issue_rowgemm<4>(tb + kColAcc, tb + kColAcc1, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
+      issue_rowgemm<4>(tb + kColAcc, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
+      if (ROWP && has_next) issue_rowp(tile + gridDim.x);            // this tile's scalars were read before the barrier
       if (EARLY && has_next) {                                                                  // the next tile's fc1
         issue_bulk(tile + 2 * (long long)gridDim.x);
-        issue_rowgemm<KP / 16>(tb + kF0, tb + kF1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+        issue_rowgemm<KP / 16>(tb + kF, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(fbar);
       }
-      if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kGh, sB2, sDL, kIdGh, !first);            // Gh += n2^T dlogits
-      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);                                       // G2 += dz2^T n1
+      if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);   // Gh += n2^T dlogits
+      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);               // G2 += dz2^T [n1 | 1]
       umma::mma_commit(gbar);
     }
     if (DEFER) head_operands();
@@ -660,8 +693,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     // ---- layer 1 backward
     umma::mbar_wait(bar, ph); ph ^= 1;
     umma::tc_fence_after();
-    load_acc16<true>(lane_addr, cq, dz);
-    ln_act_bwd16(dz, n1, mean1, rstd1, relu, xch, slot, cq, r, q4);
+    load_acc16(lane_addr, cq, dz, kColAcc);
+    ln_act_bwd16(dz, n1, mean1, rstd1, relu, kInvDg, WIDE ? 1.0f : kSD, xch, slot, cq, r, q4);
     if (WIDE) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) db1[WIDE ? i : 0] += dz[i];
@@ -676,7 +709,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       continue;
     }
     umma::mbar_wait(gbar, gph); gph ^= 1;                                 // this tile's G2 has read dz2 out of BS
-    store_cols16(sm + m.BS, r, cq, dz);
+    store_cols16u(sm + m.BS, 8 * kRowChunk, r, cq, dz);
     umma::fence_async_smem();
     umma::tc_fence_before();
     __syncthreads();
@@ -684,12 +717,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::tc_fence_after();
       if (!EARLY && has_next) {
         issue_bulk(tile + 2 * (long long)gridDim.x);
-        issue_rowgemm<KP / 16>(tb + kColAcc, tb + kColAcc1, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
+        issue_rowgemm<KP / 16>(tb + kColAcc, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(bar);
       }
-      if (HEAD && !VHEAD && DEFER) issue_wgrad(tb + kGh, sB2, sDL, kIdGh, !first);             // Gh += n2^T dlogits
-      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);                      // G1 += dz1^T x
+      if (HEAD && !VHEAD && DEFER) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);   // Gh += n2^T dlogits
+      issue_wgrad(tb + kColG1, sBS, sX + buf * x_bytes16, kIdG1, !first);   // G1 += dz1^T [x | 1]
       umma::mma_commit(gbar);
     }
     buf ^= 1;
@@ -719,38 +752,37 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       }
     }
     __syncthreads();                                                      // zero fill + red visible
-    float* __restrict__ gp = gp0 + (size_t)(q4 >> 1) * L.total;
+    float* __restrict__ gp = gp0 + (size_t)(q4 >> 1) * L.total;           // lanes 64..127: the lo halves of A, second partial row
     const int mrow = r & 63;
-    const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;                  // lanes 64..127 hold the (scaled) lo halves of A
     {
       float u[16], w[16];
       umma::tmem_ld16(lane_addr + kColG2 + 16 * cq, u);
       umma::tmem_ld16(lane_addr + kColG2 + 64 + 16 * cq, w);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) gp[L.w2 + mrow * 64 + 16 * cq + i] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+      for (int i = 0; i < 16; ++i) gp[L.w2 + mrow * 64 + 16 * cq + i] = (u[i] + w[i]) * kInvG2;
       if (!WIDE && cq < KP / 16) {
         umma::tmem_ld16(lane_addr + kColG1 + 16 * cq, u);
         umma::tmem_ld16(lane_addr + kColG1 + KP + 16 * cq, w);
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const int k = 16 * cq + i;
-          if (k < D) gp[L.w1 + mrow * D + k] = fmaf(w[i], kLoInv, u[i]) * lane_scale;
-          if (k == D) gp[L.b1 + mrow] = u[i] * lane_scale;             // the ones column of the input tile
+          if (k < D) gp[L.w1 + mrow * D + k] = (u[i] + w[i]) * kInvG1;
+          if (k == D) gp[L.b1 + mrow] = u[i] * kInvG1;                  // the ones column of the input tile (holds kSX)
         }
       }
-      if (cq == 0) {                                                      // bias gradients: the ones columns
+      if (cq == 0) {                                                      // bias gradients: the ones chunk (holds kSN)
         umma::tmem_ld16(lane_addr + kColG2 + 128, u);
-        gp[L.b2 + mrow] = u[0] * lane_scale;
+        gp[L.b2 + mrow] = u[0] * kInvG2;
       }
       if (HEAD && !VHEAD && cq == 3) {                                    // warps 12..15: head gradient, lanes = hidden unit
-        umma::tmem_ld16(lane_addr + kGh, u);
-        umma::tmem_ld16(lane_addr + kGh + 16, w);
+        umma::tmem_ld16(lane_addr + kColGh, u);
+        umma::tmem_ld16(lane_addr + kColGh + 16, w);
         int h = 0, off = 0;
 #pragma unroll
         for (int q = 0; q < AMAX; ++q) {
           if (q < A) {
             while (q >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
-            gp[L.wh[h] + (q - off) * 64 + mrow] = fmaf(w[q], kLoInv, u[q]) * lane_scale;
+            gp[L.wh[h] + (q - off) * 64 + mrow] = (u[q] + w[q]) * kInvGh;
           }
         }
       }
@@ -765,7 +797,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (VHEAD) {
         float s3 = 0.0f;
         for (int q = 0; q < 4; ++q) s3 += red[512 + (4 * c + q) * 16 + i];
-        gp0[L.wh[0] + tid] = s3;
+        gp0[L.wh[0] + tid] = s3 * (1.0f / kSN);                          // accumulated against kSN n2
       }
     } else if (HEAD && tid < 64 + A) {
       const int q = tid - 64;
@@ -829,7 +861,7 @@ bool supports(const mappo_net_config* cfg) {
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
   const int Kp = (wide || cfg->in_dim < 32) ? 32 : 64;
-  const bool early = !wide && Kp == 32 && A <= 8;                      // early_tile() of the instantiation launch() picks
+  const bool early = !wide && (Kp == 32 ? A <= 8 : cfg->is_critic != 0);   // early_tile() of the instantiation launch() picks
   return make_map(Kp, A | 1, true, 0, false, early).total <= (uint32_t)kMaxDynSmem &&
          make_map(Kp, A | 1, true, 0, false, false).total <= (uint32_t)kMaxDynSmem &&
          make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
@@ -845,6 +877,8 @@ static int launch_inst(MlpArgs& a, cudaStream_t stream, const char* who) {
       make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3, kEarly).total <= (uint32_t)kMaxDynSmem)
     a.raw_ok = 1;
   const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3, kEarly);
+  auto al16 = [](const void* p_) { return (reinterpret_cast<uintptr_t>(p_) & 15u) == 0; };
+  a.rowp_ok = (MODE == 2 && a.index == nullptr && al16(a.actions) && al16(a.old_logp) && al16(a.adv) && al16(a.active)) ? 1 : 0;
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE, AFIX, ACT>;
   static bool attr_set = false;
   if (!attr_set) {

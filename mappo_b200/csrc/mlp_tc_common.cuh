@@ -72,6 +72,53 @@ __device__ __forceinline__ float2 row_sum2(float a, float b, float2* xch, int& s
   return make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
 }
 
+// ---- uniformly scaled operand pairs (mlp_tc.cu) ----------------------------------------------------------
+// x' = S x with S a power of two fixed per operand class; hi = fp16(x'), lo = fp16(x' - hi): both halves carry the SAME
+// scale, so hi*hi + hi*lo + lo*hi accumulate in ONE fp32 accumulator (scaled by the product of the two operand scales,
+// undone for free in the epilogue's first FFMA).  S keeps lo out of the fp16 subnormals for the magnitudes that matter
+// (absolute resolution 2^-25 / S) and bounds the range to |x| < 65504 / S.
+constexpr float kSN = 64.0f;      // LayerNorm outputs (|n| <= sqrt(63))
+constexpr float kSX = 16.0f;      // input rows (normalised: |x| <= sqrt(in_dim); raw: saturated at +-4094)
+constexpr float kSW = 64.0f;      // folded weights
+constexpr float kSD = 16.0f;      // per-sample gradients (dz2, dz1, dlogits)
+
+// two scaled fp32 -> packed fp16 hi pair and packed fp16 residual pair: F2FP, 2 x FHFMA (x' - hi, exact), F2FP
+__device__ __forceinline__ void split2u(float a, float b, uint32_t& hi, uint32_t& lo) {
+  const __half2 hh = __floats2half2_rn(a, b);
+  hi = *reinterpret_cast<const uint32_t*>(&hh);
+  float da, db;
+  asm("{\n\t.reg .b16 l, h, m;\n\tmov.b32 {l, h}, %2;\n\tmov.b16 m, 0xBC00;\n\t"
+      "fma.rn.f32.f16 %0, l, m, %3;\n\tfma.rn.f32.f16 %1, h, m, %4;\n\t}"
+      : "=f"(da), "=f"(db) : "r"(hi), "f"(a), "f"(b));
+  const __half2 ll = __floats2half2_rn(da, db);
+  lo = *reinterpret_cast<const uint32_t*>(&ll);
+}
+__device__ __forceinline__ void split8u(const float* v, uint4& hi, uint4& lo) {
+  split2u(v[0], v[1], hi.x, lo.x);
+  split2u(v[2], v[3], hi.y, lo.y);
+  split2u(v[4], v[5], hi.z, lo.z);
+  split2u(v[6], v[7], hi.w, lo.w);
+}
+// this thread's 16 (scaled) columns of row r -> hi piece at `tile`, lo piece `lo_off` bytes behind it
+__device__ __forceinline__ void store_cols16u(unsigned char* tile, uint32_t lo_off, int r, int cq, const float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint4 hi, lo;
+    split8u(v + 8 * h, hi, lo);
+    const uint32_t off = (uint32_t)(2 * cq + h) * kRowChunk + (uint32_t)r * 16;
+    *reinterpret_cast<uint4*>(tile + off) = hi;
+    *reinterpret_cast<uint4*>(tile + lo_off + off) = lo;
+  }
+}
+// one (scaled) fp32 value -> (hi, lo) fp16 at (r, c) of an R-row chunk-major tile
+__device__ __forceinline__ void put_pair_u(unsigned char* tile, uint32_t piece, int R, int r, int c, float v) {
+  const __half hi = __float2half_rn(v);
+  const __half lo = __float2half_rn(v - __half2float(hi));
+  const uint32_t off = umma::tile_off16(R, r, c);
+  *reinterpret_cast<__half*>(tile + off) = hi;
+  *reinterpret_cast<__half*>(tile + piece + off) = lo;
+}
+
 // one fp32 value -> (hi, lo) fp16 at (r, c) of an R-row chunk-major tile
 __device__ __forceinline__ void put_pair(unsigned char* tile, uint32_t piece, int R, int r, int c, float v) {
   const __half hi = __float2half_rn(v);
