@@ -219,7 +219,6 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
   const long long g = tile * kBM + r;
   const bool valid = g < a.rows;
   float xv[XC];
-  const long long srow = valid ? ((a.index ? a.index[g] : g) / a.x_div) : 0;
   if (raw) {                                          // the tile's rows already sit in shared memory
     const float* row = raw + r * D;
 #pragma unroll
@@ -228,6 +227,8 @@ __device__ __forceinline__ void stage_x(const MlpArgs& a, long long tile, unsign
       xv[i] = (c < D) ? row[c] : 0.0f;
     }
   } else {
+    long long srow = valid ? (a.index ? a.index[g] : g) : 0;
+    if (a.x_div != 1) srow /= a.x_div;                 // (a 64-bit division: only the grouped critic rows pay for it)
     const float* __restrict__ row = a.x + srow * (long long)a.ld;
 #pragma unroll
     for (int i = 0; i < XC; ++i) {
