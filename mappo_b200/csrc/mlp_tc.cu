@@ -677,6 +677,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       umma::tc_fence_after();
       issue_rowgemm<4>(tb + kColAcc, sBS, 8 * kRowChunk16, sW2, 8 * kWChunk16, 128, kWChunk, 16, kIdDgrad);
       umma::mma_commit(bar);                                                                    // dn1 = dz2 W2'
+      if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);   // Gh += n2^T dlogits
+      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);               // G2 += dz2^T [n1 | 1]
+      umma::mma_commit(gbar);                                          // (frees BS for dz1: ahead of the next tile's fc1)
       if (ROWP && has_next) issue_rowp(tile + gridDim.x);            // this tile's scalars were read before the barrier
       if (EARLY && has_next) {                                                                  // the next tile's fc1
         issue_bulk(tile + 2 * (long long)gridDim.x);
@@ -684,9 +687,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
                                128, 2 * kWChunk16, kIdFwd);
         umma::mma_commit(fbar);
       }
-      if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);   // Gh += n2^T dlogits
-      issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);               // G2 += dz2^T [n1 | 1]
-      umma::mma_commit(gbar);
     }
     if (DEFER) head_operands();
     // ---- next tile's input rows, staged while the tensor cores work
