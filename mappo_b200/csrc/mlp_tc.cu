@@ -175,7 +175,8 @@ __device__ __forceinline__ void act_ln16(float (&t)[16], float inv, const float*
   const float ts = kTanhScale * inv;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    t[i] = relu ? fmaxf(fmaf(t[i], inv, bias[i]), 0.0f) : tanh_scaled(fmaf(t[i], ts, bias_s[i]));
+    const float y = fmaf(t[i], ts, bias_s[i]);
+    t[i] = relu ? fmaxf(fmaf(t[i], inv, bias[i]), 0.0f) : ((i & 1) ? tanh_scaled_fma(y) : tanh_scaled(y));
     s += t[i];
     q = fmaf(t[i], t[i], q);
   }
