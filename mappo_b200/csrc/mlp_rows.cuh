@@ -166,5 +166,35 @@ __device__ __forceinline__ float critic_loss_row(const MlpArgs& a, long long src
   return dv;
 }
 
+// The same with the ValueNorm statistics taken once per kernel (mean, 1 / sd handed in: the target is
+// (return - mean) * inv_sd, one rounding away from the division above) and the loss sums only where they are kept
+// (`sums`: warp-uniform in the tensor-core kernels, where four threads share a row but one of them owns the sums).
+__device__ __forceinline__ float critic_loss_row_pre(const MlpArgs& a, long long src, float v, float mean, float inv_sd,
+                                                     bool sums, double* acc4) {
+  const mappo_loss_config& c = a.loss;
+  float dv = 0.0f;
+  for (int m = 0; m < a.group; ++m) {
+    const long long o = src * a.group + m;
+    const float active = (c.use_value_active_masks && a.active) ? a.active[o] : 1.0f;
+    const float vp = a.value_preds[o];
+    const float target = c.use_value_norm ? (a.returns[o] - mean) * inv_sd : a.returns[o];
+    const float diff = v - vp;
+    const float vclip = vp + fminf(fmaxf(diff, -c.clip_param), c.clip_param);
+    const float e_c = target - vclip, e_o = target - v;
+    const float l_c = c.use_huber_loss ? huber(e_c, c.huber_delta) : 0.5f * e_c * e_c;
+    const float l_o = c.use_huber_loss ? huber(e_o, c.huber_delta) : 0.5f * e_o * e_o;
+    const float g_o = -(c.use_huber_loss ? huber_d(e_o, c.huber_delta) : e_o);
+    const bool in_clip = (diff >= -c.clip_param) && (diff <= c.clip_param);
+    const float g_c = in_clip ? -(c.use_huber_loss ? huber_d(e_c, c.huber_delta) : e_c) : 0.0f;
+    float loss, g;
+    if (!c.use_clipped_value_loss) { loss = l_o; g = g_o; }
+    else if (l_o > l_c) { loss = l_o; g = g_o; }
+    else if (l_o < l_c) { loss = l_c; g = g_c; }
+    else { loss = l_o; g = 0.5f * (g_o + g_c); }            // torch.max ties split evenly
+    dv += active * g * c.value_loss_coef;
+    if (sums) { acc4[0] += (double)(loss * active); acc4[1] += (double)active; }
+  }
+  return dv;
+}
 
 }  // namespace mappo

@@ -349,6 +349,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ double lred[4][kThreads / 32];
+  __shared__ float vn_s[2];                                            // ValueNorm mean and 1 / sd (critic update)
   const NetLayout& L = a.L;
   const int A = AFIX > 0 ? AFIX : L.a_total, relu = ACT >= 0 ? ACT : L.use_relu, D = L.in_dim, AS = A | 1;
   const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD, EARLY);
@@ -403,6 +404,15 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       stage_x<KP, UPDATE>(a, t, xs, m.x_piece, reinterpret_cast<float2*>(sm + m.xch), slot_ref, cq, r, q4);
     }
   };
+  if (MODE == 3 && tid == 32) {                                        // valuenorm.py:31-35,56-65 (ValueNorm.normalize)
+    float mean = 0.0f, sd = 1.0f;
+    if (a.loss.use_value_norm) {
+      const float db = fmaxf(a.vn_stats[2], 1e-5f);
+      mean = a.vn_stats[0] / db;
+      sd = sqrtf(fmaxf(a.vn_stats[1] / db - mean * mean, 1e-2f));
+    }
+    vn_s[0] = mean; vn_s[1] = 1.0f / sd;
+  }
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   stage_weights_tc(sm, m, a, !WIDE, UPDATE);
   if (UPDATE && tid < kBM) {                                            // the ones columns (written once)
@@ -610,7 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
 #pragma unroll
         for (int q = 0; q < AMAX; ++q) dl[q] = dt[q];
       } else {
-        dl[0] = valid ? critic_loss_row(a, src, l[0], mine) : 0.0f;
+        dl[0] = valid ? critic_loss_row_pre(a, src, l[0], vn_s[0], vn_s[1], cq == 0, mine) : 0.0f;
 #pragma unroll
         for (int q = 1; q < AMAX; ++q) dl[q] = 0.0f;
       }
