@@ -169,15 +169,16 @@ __device__ __forceinline__ float critic_loss_row(const MlpArgs& a, long long src
 // The same with the ValueNorm statistics taken once per kernel (mean, 1 / sd handed in: the target is
 // (return - mean) * inv_sd, one rounding away from the division above) and the loss sums only where they are kept
 // (`sums`: warp-uniform in the tensor-core kernels, where four threads share a row but one of them owns the sums).
-__device__ __forceinline__ float critic_loss_row_pre(const MlpArgs& a, long long src, float v, float mean, float inv_sd,
-                                                     bool sums, double* acc4) {
+// ret / vpred / act: the three per-term arrays (global, or a tile's copy in shared memory), o0: this row's first term.
+__device__ __forceinline__ float critic_loss_row_pre(const MlpArgs& a, const float* ret, const float* vpred, const float* act,
+                                                     long long o0, float v, float mean, float inv_sd, bool sums, double* acc4) {
   const mappo_loss_config& c = a.loss;
   float dv = 0.0f;
   for (int m = 0; m < a.group; ++m) {
-    const long long o = src * a.group + m;
-    const float active = (c.use_value_active_masks && a.active) ? a.active[o] : 1.0f;
-    const float vp = a.value_preds[o];
-    const float target = c.use_value_norm ? (a.returns[o] - mean) * inv_sd : a.returns[o];
+    const long long o = o0 + m;
+    const float active = act ? act[o] : 1.0f;
+    const float vp = vpred[o];
+    const float target = c.use_value_norm ? (ret[o] - mean) * inv_sd : ret[o];
     const float diff = v - vp;
     const float vclip = vp + fminf(fmaxf(diff, -c.clip_param), c.clip_param);
     const float e_c = target - vclip, e_o = target - v;

@@ -23,6 +23,7 @@ namespace mappo {
 namespace tc {
 
 constexpr int kTmemCols = 512;
+constexpr int kRowpGroup = 4;                       // largest critic `group` whose loss inputs arrive by bulk copy
 constexpr float kRawMax = 4094.0f;                  // 65504 / kSX, rounded down to an fp16-exact value after scaling
 // TMEM column map.  The BIAS gradients sum_rows dz come off the tensor cores too: the n1 operand tile ends in a constant
 // chunk whose first column is 1 (column 128 of G2), and the input tile carries a 1 in its first padding column
@@ -73,7 +74,8 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 3);
   m.bars = take(64);
-  m.rowp = take(update ? 4 * kBM * 4 : 0);           // per-row loss scalars of one tile, [4][128] (bulk copy, see rowp_ok)
+  m.rowp = take(update ? 3 * kRowpGroup * kBM * 4 : 0);   // per-row loss scalars of one tile (bulk copy, see rowp_ok):
+                                                     // actor [4][128], critic [3][128 * group], group <= kRowpGroup
   m.raw = take((uint32_t)raw_floats * 4);
   m.total = o;
   return m;
@@ -352,7 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __shared__ float vn_s[2];                                            // ValueNorm mean and 1 / sd (critic update)
   const NetLayout& L = a.L;
   const int A = AFIX > 0 ? AFIX : L.a_total, relu = ACT >= 0 ? ACT : L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD, EARLY);
+  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD || !HEAD, EARLY);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
@@ -368,21 +370,28 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   // per-row scalars of the register loss path (action, old log-prob, advantage, active mask): with contiguous rows they
   // arrive as four 512-byte bulk copies per tile, requested a tile ahead by one thread -- no thread holds a global
   // load across the second layer, and nothing of their DRAM latency is exposed
-  constexpr bool ROWP = (MODE == 2 && AMAX == 8);
+  constexpr bool ROWP = (MODE == 2 && AMAX == 8) || MODE == 3;
   const float* rowp = reinterpret_cast<const float*>(sm + m.rowp);
-  const bool rowp_active = ROWP && a.loss.use_policy_active_masks && a.active;
+  const bool rowp_active = ROWP && (MODE == 3 ? a.loss.use_value_active_masks : a.loss.use_policy_active_masks) && a.active;
   uint32_t pph = 0;
   auto rowp_tile = [&](long long t) { return ROWP && a.rowp_ok && t < a.ntiles && (t + 1) * kBM <= a.rows; };
   auto issue_rowp = [&](long long t) {                                // one thread
     if (!rowp_tile(t)) return;
-    const uint32_t dst = umma::smem_u32(sm + m.rowp), mb = umma::smem_u32(pbar), bytes = kBM * 4u;
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes * (rowp_active ? 4u : 3u)) : "memory");
+    const uint32_t per_row = MODE == 3 ? (uint32_t)a.group : 1u;        // critic: `group` terms share a row's value
+    const uint32_t dst = umma::smem_u32(sm + m.rowp), mb = umma::smem_u32(pbar), bytes = kBM * 4u * per_row;
+    const uint32_t ncopy = MODE == 3 ? (rowp_active ? 3u : 2u) : (rowp_active ? 4u : 3u);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes * ncopy) : "memory");
     auto copy = [&](uint32_t slot_, const float* src_) {
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                   ::"r"(dst + slot_ * bytes), "l"(src_ + t * kBM), "r"(bytes), "r"(mb) : "memory");
+                   ::"r"(dst + slot_ * bytes), "l"(src_ + t * (long long)(kBM * per_row)), "r"(bytes), "r"(mb) : "memory");
     };
-    copy(0u, a.actions); copy(1u, a.old_logp); copy(2u, a.adv);
-    if (rowp_active) copy(3u, a.active);
+    if (MODE == 3) {
+      copy(0u, a.returns); copy(1u, a.value_preds);
+      if (rowp_active) copy(2u, a.active);
+    } else {
+      copy(0u, a.actions); copy(1u, a.old_logp); copy(2u, a.adv);
+      if (rowp_active) copy(3u, a.active);
+    }
   };
   const float* raw = reinterpret_cast<const float*>(sm + m.raw);
   const uint32_t raw_bytes = (uint32_t)(kBM * D) * 4u;
@@ -517,7 +526,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       p_adv = __ldg(a.adv + src);
       if (a.loss.use_policy_active_masks && a.active) p_active = __ldg(a.active + src);
     }
-    if (MODE == 3 && valid && cq == 0) {                                  // value-loss inputs of this row's terms: warm the L1
+    if (MODE == 3 && valid && cq == 0 && !rowp_tile(tile)) {              // value-loss inputs of this row's terms: warm the L1
       const long long o = src * a.group, e = o + a.group - 1;
       umma::l1_prefetch(a.returns + o); umma::l1_prefetch(a.returns + e);
       umma::l1_prefetch(a.value_preds + o); umma::l1_prefetch(a.value_preds + e);
@@ -620,7 +629,16 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
 #pragma unroll
         for (int q = 0; q < AMAX; ++q) dl[q] = dt[q];
       } else {
-        dl[0] = valid ? critic_loss_row_pre(a, src, l[0], vn_s[0], vn_s[1], cq == 0, mine) : 0.0f;
+        const bool act_on = a.loss.use_value_active_masks && a.active;
+        if (rowp_tile(tile)) {                                            // a full tile, its loss inputs in shared memory
+          umma::mbar_wait(pbar, pph); pph ^= 1;
+          const int per = kBM * a.group;
+          dl[0] = critic_loss_row_pre(a, rowp, rowp + per, act_on ? rowp + 2 * per : nullptr, (long long)r * a.group, l[0],
+                                      vn_s[0], vn_s[1], cq == 0, mine);
+        } else {
+          dl[0] = valid ? critic_loss_row_pre(a, a.returns, a.value_preds, act_on ? a.active : nullptr, src * a.group, l[0],
+                                              vn_s[0], vn_s[1], cq == 0, mine) : 0.0f;
+        }
 #pragma unroll
         for (int q = 1; q < AMAX; ++q) dl[q] = 0.0f;
       }
@@ -873,9 +891,12 @@ bool supports(const mappo_net_config* cfg) {
   for (int h = 0; h < cfg->n_heads; ++h) A += cfg->head_dim[h];
   if (cfg->is_critic) A = 1;
   const int Kp = (wide || cfg->in_dim < 32) ? 32 : 64;
-  const bool early = !wide && (Kp == 32 ? A <= 8 : cfg->is_critic != 0);   // early_tile() of the instantiation launch() picks
-  return make_map(Kp, A | 1, true, 0, false, early).total <= (uint32_t)kMaxDynSmem &&
-         make_map(Kp, A | 1, true, 0, false, false).total <= (uint32_t)kMaxDynSmem &&
+  // the maps of the instantiations launch() picks for this network: update (MODE 3 for a critic: no n2 / dlogits tiles)
+  // with its early_tile() setting, and rollout
+  const bool critic = cfg->is_critic != 0;
+  const bool early = early_tile(critic ? 3 : 2, Kp, critic ? 1 : (A <= 8 ? 8 : 16), wide);
+  return make_map(Kp, A | 1, true, 0, critic, early).total <= (uint32_t)kMaxDynSmem &&
+         (critic || make_map(Kp, A | 1, true, 0, false, false).total <= (uint32_t)kMaxDynSmem) &&   // (availability masks: AMAX 16)
          make_map(Kp, A | 1, false).total <= (uint32_t)kMaxDynSmem;
 }
 
@@ -886,11 +907,14 @@ static int launch_inst(MlpArgs& a, cudaStream_t stream, const char* who) {
   // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
   a.raw_ok = 0;
   if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && (reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 &&
-      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3, kEarly).total <= (uint32_t)kMaxDynSmem)
+      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3 || MODE == 5, kEarly).total <= (uint32_t)kMaxDynSmem)
     a.raw_ok = 1;
-  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3, kEarly);
+  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3 || MODE == 5, kEarly);
   auto al16 = [](const void* p_) { return (reinterpret_cast<uintptr_t>(p_) & 15u) == 0; };
-  a.rowp_ok = (MODE == 2 && a.index == nullptr && al16(a.actions) && al16(a.old_logp) && al16(a.adv) && al16(a.active)) ? 1 : 0;
+  a.rowp_ok = 0;
+  if (MODE == 2) a.rowp_ok = (a.index == nullptr && al16(a.actions) && al16(a.old_logp) && al16(a.adv) && al16(a.active)) ? 1 : 0;
+  if (MODE == 3)
+    a.rowp_ok = (a.index == nullptr && a.group >= 1 && a.group <= kRowpGroup && al16(a.returns) && al16(a.value_preds) && al16(a.active)) ? 1 : 0;
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE, AFIX, ACT>;
   static bool attr_set = false;
   if (!attr_set) {
