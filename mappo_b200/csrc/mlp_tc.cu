@@ -46,7 +46,9 @@ struct Map {
 // vhead: scalar (value) head whose weight gradient accumulates in registers: no n2 / dlogits operand tiles.
 // early: the NEXT tile's fc1 is issued at the second synchronisation of the tile (see the kernel): both X buffers are busy
 // over the span the partial logits live, so they get a private region.
-__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0, bool vhead = false, bool early = false) {
+// rowp_floats > 0: a landing buffer for a tile's per-row loss scalars (see rowp_ok in the kernel), when it fits.
+__host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_floats = 0, bool vhead = false, bool early = false,
+                                        int rowp_floats = 0) {
   Map m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
@@ -74,15 +76,16 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.xlog = m.xlog_in_x ? 0u : take(4 * kBM * AS * 4);
   m.red = take(16 * 16 * 4 * 3);
   m.bars = take(64);
-  m.rowp = take(update ? 3 * kRowpGroup * kBM * 4 : 0);   // per-row loss scalars of one tile (bulk copy, see rowp_ok):
-                                                     // actor [4][128], critic [3][128 * group], group <= kRowpGroup
+  m.rowp = take((uint32_t)rowp_floats * 4);          // actor [4][128], critic [3][128 * group]
   m.raw = take((uint32_t)raw_floats * 4);
   m.total = o;
   return m;
 }
 
-// ---- prologue: fold the LayerNorm affines into the following Linear (net.cuh), split into fp16 pairs, stage
-__device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a, bool with_w1, bool update) {
+// ---- prologue: fold the LayerNorm affines into the following Linear (net.cuh), split into fp16 pairs, stage.
+// The plain form, kept for the update kernels: their main loop's code generation is sensitive to what precedes it
+// (the spread-out form below made the actor update 1.4 % slower), and 9 us of prologue are 0.5 % of their run time.
+__device__ __forceinline__ void stage_weights_serial(unsigned char* sm, const Map& m, const MlpArgs& a, bool with_w1, bool update) {
   const NetLayout& L = a.L;
   const float* __restrict__ P = a.params;
   const int D = L.in_dim, Kp = a.Kp, tid = threadIdx.x;
@@ -126,6 +129,80 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     }
     reinterpret_cast<float*>(sm + m.bhf)[aidx] = s;
   }
+  float* dbh = reinterpret_cast<float*>(sm + m.dbh);
+  for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
+}
+
+// ---- the same for the rollout kernels, whose launches are short (70 / 30 us) and many (51 per iteration).
+// Every launch of every CTA pays for it, and all of it is L2 latency: the loops have compile-time trip counts so that a
+// thread's loads go out together, and the three bias folds (64 + 64 + 16 dot products) are spread over all 16 warps
+// -- two elements per lane and a shuffle reduction -- instead of 80 threads walking 64 dependent steps each.
+template <int KP>
+__device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a, bool with_w1, bool update) {
+  const NetLayout& L = a.L;
+  const float* __restrict__ P = a.params;
+  const int D = L.in_dim, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (with_w1) {
+#pragma unroll
+    for (int it = 0; it < 64 * KP / kThreads; ++it) {
+      const int e = tid + it * kThreads, j = e / KP, k = e % KP;
+      float v = 0.0f;
+      if (k < D) v = P[L.w1 + j * D + k] * (L.use_fn ? P[L.fn_g + k] : 1.0f);
+      put_pair_u(sm + m.W1, m.w1_piece, 64, j, k, v * kSW);
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 64 * 64 / kThreads; ++it) {
+    const int e = tid + it * kThreads, j = e >> 6, k = e & 63;
+    put_pair_u(sm + m.W2, 8 * kWChunk, 64, j, k, P[L.w2 + j * 64 + k] * P[L.g1 + k] * kSW);
+  }
+  float* Whf = reinterpret_cast<float*>(sm + m.Whf);
+#pragma unroll
+  for (int it = 0; it < kMaxA * 64 / kThreads; ++it) {
+    const int e = tid + it * kThreads, aidx = e >> 6, k = e & 63;
+    float v = 0.0f;
+    int h = 0, off = 0;
+    while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
+    if (h < L.n_heads) v = P[L.wh[h] + (aidx - off) * 64 + k] * P[L.g2 + k];
+    Whf[aidx * 64 + k] = v;
+  }
+  auto warp_sum = [](float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  };
+  // b1' = b1 + W1 beta_fn, b2' = b2 + W2 beta_1: warp w folds rows 4w .. 4w + 3
+  float p1[4], p2[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int j = 4 * warp + i;
+    p1[i] = 0.0f;
+    if (L.use_fn) {                                    // (a wide first layer, mlp_wide.cu, leaves its bias to this kernel too)
+      for (int k = lane; k < D; k += 32) p1[i] = fmaf(P[L.w1 + j * D + k], P[L.fn_b + k], p1[i]);
+    }
+    p2[i] = fmaf(P[L.w2 + j * 64 + lane + 32], P[L.be1 + lane + 32], P[L.w2 + j * 64 + lane] * P[L.be1 + lane]);
+  }
+  // head biases: warp w folds logit w
+  float ph = 0.0f;
+  int hh = 0, hoff = 0;
+  while (hh < L.n_heads && warp >= hoff + L.head_dim[hh]) { hoff += L.head_dim[hh]; ++hh; }
+  if (hh < L.n_heads) {
+    const float* wr = P + L.wh[hh] + (warp - hoff) * 64;
+    ph = fmaf(wr[lane + 32], P[L.be2 + lane + 32], wr[lane] * P[L.be2 + lane]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { p1[i] = warp_sum(p1[i]); p2[i] = warp_sum(p2[i]); }
+  ph = warp_sum(ph);
+  if (lane < 4) {
+    const int j = 4 * warp + lane;
+    const float s1 = P[L.b1 + j] + (lane == 0 ? p1[0] : lane == 1 ? p1[1] : lane == 2 ? p1[2] : p1[3]);
+    const float s2 = P[L.b2 + j] + (lane == 0 ? p2[0] : lane == 1 ? p2[1] : lane == 2 ? p2[2] : p2[3]);
+    reinterpret_cast<float*>(sm + m.b1f)[j] = s1;
+    reinterpret_cast<float*>(sm + m.b1s)[j] = s1 * kTanhScale;
+    reinterpret_cast<float*>(sm + m.b2f)[j] = s2;
+    reinterpret_cast<float*>(sm + m.b2s)[j] = s2 * kTanhScale;
+  }
+  if (lane == 0) reinterpret_cast<float*>(sm + m.bhf)[warp] = (hh < L.n_heads) ? P[L.bh[hh] + (warp - hoff)] + ph : 0.0f;
   float* dbh = reinterpret_cast<float*>(sm + m.dbh);
   for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
 }
@@ -320,6 +397,9 @@ __host__ __device__ constexpr bool early_tile(int mode, int kp, int amax, bool w
   return (mode == 2 || mode == 3 || mode == 5) && !wide && (kp == 32 ? amax <= 8 : mode == 3);
 }
 
+// floats of the per-row loss-scalar landing buffer of one tile
+__host__ __device__ constexpr int rowp_floats(int mode, int group) { return mode == 3 ? 3 * kBM * group : 4 * kBM; }
+
 // ---- the kernel ------------------------------------------------------------------------------------------
 // MODE: 0 rollout actor, 1 rollout critic, 2 update actor, 3 update critic; recurrent networks (mlp_gru.cu) use
 // 4 = base features only (n2 rows written to a.feat) and 5 = base backward from dLoss/dn2 rows read from a.feat.
@@ -354,7 +434,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __shared__ float vn_s[2];                                            // ValueNorm mean and 1 / sd (critic update)
   const NetLayout& L = a.L;
   const int A = AFIX > 0 ? AFIX : L.a_total, relu = ACT >= 0 ? ACT : L.use_relu, D = L.in_dim, AS = A | 1;
-  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD || !HEAD, EARLY);
+  const Map m = make_map(KP, AS, UPDATE, a.raw_ok ? kBM * D : 0, VHEAD || !HEAD, EARLY, a.rowp_ok ? rowp_floats(MODE, a.group) : 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + m.bars);           // completion of the last committed MMA group
@@ -423,7 +503,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
     vn_s[0] = mean; vn_s[1] = 1.0f / sd;
   }
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
-  stage_weights_tc(sm, m, a, !WIDE, UPDATE);
+  if (UPDATE) stage_weights_serial(sm, m, a, !WIDE, UPDATE);
+  else stage_weights_tc<KP>(sm, m, a, !WIDE, UPDATE);
   if (UPDATE && tid < kBM) {                                            // the ones columns (written once)
     const uint4 one = make_uint4(0x00005400u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);   // fp16(kSN) = 64
     auto put = [&](unsigned char* base) {
@@ -905,16 +986,23 @@ static int launch_inst(MlpArgs& a, cudaStream_t stream, const char* who) {
   constexpr bool kUpd = (MODE == 2 || MODE == 3 || MODE == 5);
   constexpr bool kEarly = early_tile(MODE, KP, AMAX, WIDE);
   // bulk-copied input tiles: contiguous rows only, and only if the landing buffer still fits
-  a.raw_ok = 0;
-  if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && (reinterpret_cast<uintptr_t>(a.x) & 15u) == 0 &&
-      make_map(KP, a.L.a_total | 1, kUpd, kBM * a.L.in_dim, MODE == 3 || MODE == 5, kEarly).total <= (uint32_t)kMaxDynSmem)
-    a.raw_ok = 1;
-  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, MODE == 3 || MODE == 5, kEarly);
   auto al16 = [](const void* p_) { return (reinterpret_cast<uintptr_t>(p_) & 15u) == 0; };
+  const bool vh = (MODE == 3 || MODE == 5);
+  auto fits = [&](int raw_f, int rowp_f) {
+    return make_map(KP, a.L.a_total | 1, kUpd, raw_f, vh, kEarly, rowp_f).total <= (uint32_t)kMaxDynSmem;
+  };
+  // per-row loss scalars by bulk copy (a few KB), then bulk-copied input tiles (the landing buffer is the larger one):
+  // contiguous rows only, and only if the buffers still fit
   a.rowp_ok = 0;
-  if (MODE == 2) a.rowp_ok = (a.index == nullptr && al16(a.actions) && al16(a.old_logp) && al16(a.adv) && al16(a.active)) ? 1 : 0;
+  if (MODE == 2) a.rowp_ok = (AMAX == 8 && a.index == nullptr && al16(a.actions) && al16(a.old_logp) && al16(a.adv) && al16(a.active)) ? 1 : 0;
   if (MODE == 3)
     a.rowp_ok = (a.index == nullptr && a.group >= 1 && a.group <= kRowpGroup && al16(a.returns) && al16(a.value_preds) && al16(a.active)) ? 1 : 0;
+  const int rowp_f = rowp_floats(MODE, a.group);
+  if (a.rowp_ok && !fits(0, rowp_f)) a.rowp_ok = 0;
+  a.raw_ok = 0;
+  if (!WIDE && a.index == nullptr && a.x_div == 1 && a.ld == a.L.in_dim && al16(a.x) && fits(kBM * a.L.in_dim, a.rowp_ok ? rowp_f : 0))
+    a.raw_ok = 1;
+  const Map m = make_map(KP, a.L.a_total | 1, kUpd, a.raw_ok ? kBM * a.L.in_dim : 0, vh, kEarly, a.rowp_ok ? rowp_f : 0);
   auto kern = mlp_tc_kernel<MODE, KP, AMAX, WIDE, AFIX, ACT>;
   static bool attr_set = false;
   if (!attr_set) {

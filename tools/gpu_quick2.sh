@@ -5,6 +5,6 @@ python - <<EOP
 import json
 for l in open("gpurun_out/bench_q.json"):
     if l.startswith("{"):
-        d=json.loads(l); print(d["value"], d["ms_per_step"], d["e2e"]["value"])
+        d=json.loads(l); print(d["value"], d["ms_per_step"], d["e2e"]["value"], d.get("clocks"))
         for k in d["roofline"]["kernels"][:4]: print(k["key"], k["ms_per_launch"])
 EOP
