@@ -307,6 +307,12 @@ typedef struct {
 /* number of partial rows the update kernels write for `rows` rows of network `cfg` on the current device */
 int mappo_update_num_blocks(const mappo_net_config* cfg, long long rows);
 
+/* Which kernels serve network `cfg` (host-side decision, no device call; no counterpart in the reference):
+ *   0  fp32 tile kernels (mlp.cu: layer_N > 1, hidden != 64, shared-memory map of the fused kernel too large, or
+ *      MAPPO_MLP_IMPL=fma), 1  fused tcgen05 kernels (mlp_tc.cu), 2  the same behind a wide first layer (mlp_wide.cu),
+ *   3  recurrent chain (mlp_gru.cu over the fused base); -1 for a configuration check_net() refuses. */
+int mappo_mlp_kernel_path(const mappo_net_config* cfg);
+
 /* Actor: forward + clipped-surrogate/entropy loss + backward over one minibatch (r_mappo.py:115-141).
  *   index: int64 [rows] row gather into the flat buffers (the minibatch permutation,
  *          shared_buffer.py:246-247), or NULL for the identity (num_mini_batch == 1: the loss is a mean,

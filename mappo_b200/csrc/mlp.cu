@@ -623,6 +623,13 @@ extern "C" int mappo_update_num_blocks(const mappo_net_config* cfg, long long ro
   return blocks_for(rows);
 }
 
+extern "C" int mappo_mlp_kernel_path(const mappo_net_config* cfg) {
+  if (!cfg || check_net(cfg, "mappo_mlp_kernel_path")) return -1;
+  if (cfg->recurrent) return 3;
+  if (cfg->layer_N > 1 || !use_tc(cfg)) return 0;
+  return cfg->in_dim >= kWideFrom ? 2 : 1;
+}
+
 extern "C" long long mappo_mlp_workspace_bytes(const mappo_net_config* cfg, long long rows) {
   if (!cfg || rows < 0) return -1;
   return (cfg->in_dim >= kWideFrom && use_tc(cfg)) ? tc::wide_workspace_bytes(rows) : 0;

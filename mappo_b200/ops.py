@@ -371,6 +371,15 @@ def update_num_blocks(cfg, rows):
     return int(L.mappo_update_num_blocks(C.byref(cfg), int(rows)))
 
 
+def kernel_path(cfg):
+    """0 fp32 tile kernels, 1 fused tcgen05 kernels, 2 the same behind a wide first layer, 3 recurrent chain (host-side
+    decision of the library, include/mappo_b200.h: mappo_mlp_kernel_path)"""
+    L = _lib.lib()
+    L.mappo_mlp_kernel_path.argtypes = [_NC]
+    L.mappo_mlp_kernel_path.restype = C.c_int
+    return int(L.mappo_mlp_kernel_path(C.byref(cfg)))
+
+
 def actor_update(cfg, loss, params, obs, actions, old_logp, adv, active_masks, available_actions, grad_partials,
                  loss_partials, index=None):
     obs, ld = _rows_view(obs)

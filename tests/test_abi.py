@@ -49,3 +49,20 @@ def test_obs_widths_of_the_adversarial_scenarios():
     # simple_world_comm.py:281-288, probed on the reference (4 adversaries, 2 good agents, 1 obstacle): 34 / 28
     assert [L.mappo_env_obs_dim_cfg(cfg(7, 6, 1, 4), i) for i in range(6)] == [34, 34, 34, 34, 28, 28]
     assert L.mappo_env_num_landmarks(cfg(7, 6, 1, 4)) == 5 and L.mappo_env_num_landmarks(cfg(0, 3, 3)) == 3
+
+
+def test_benchmark_networks_take_the_tensor_core_kernels():
+    """Host-side decision of the library (mappo_mlp_kernel_path, no device call): the networks of BASELINE.json's
+    configurations must be served by the fused tcgen05 kernels -- a shared-memory map that outgrows the SM silently
+    sends a network to the fp32 tile kernels (4x slower), which no parity test notices."""
+    from mappo_b200 import ops
+    path = lambda in_dim, heads, critic, **kw: ops.kernel_path(ops.net_config(
+        in_dim, 64, kw.get("layer_N", 1), kw.get("relu", False), True, kw.get("rnn", 0), heads, critic))
+    for relu in (False, True):
+        assert path(18, [5], False, relu=relu) == 1 and path(54, [1], True, relu=relu) == 1        # C1 / C2 / C3: 3 agents
+        assert path(60, [5], False, relu=relu) == 1 and path(600, [1], True, relu=relu) == 2       # C5: 10 agents, 10 landmarks
+        assert path(46, [5], False, relu=relu) == 1 and path(460, [1], True, relu=relu) == 2       # 10 agents, 3 landmarks
+    assert path(66, [5], False) == 2                                                               # 15 agents: wide actor too
+    assert path(11, [3, 5], False) == 1 and path(21, [5, 10], False) == 1                          # speaker_listener / reference heads
+    assert path(18, [5], False, rnn=1) == 3 and path(54, [1], True, rnn=2) == 3                    # C4: GRU chain
+    assert path(18, [5], False, layer_N=2) == 0                                                    # deep base: fp32 tiles
