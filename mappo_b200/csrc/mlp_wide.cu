@@ -475,6 +475,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
 
   float xr[kXChunksPerThread][8], dr[8], mean = 0.0f, rstd = 1.0f;
   bool valid = false;
+  const float sx = a.norm ? kSN : kSD;                    // x is LayerNorm output (C5) or a gradient array (GRU chain)
   // 16-byte aligned rows: the next half tile is copied asynchronously into shared-memory landing tiles, consecutive
   // threads fetching consecutive 16-byte units of a row (coalesced: a warp touches 4 lines, not 32), the moment the
   // current tile has been read out; each thread then picks up its (row, chunk) values from the landing tile.
@@ -568,7 +569,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     }
     if (n > 0) umma::mbar_wait(bar, (n - 1) & 1);                       // the operand buffer is free again
     {
+      // uniformly scaled operand pairs (mlp_tc_common.cuh): both halves of an operand carry one power-of-two scale, folded
+      // into the normalisation here and taken out of the accumulators (and the column sums) when they leave the kernel
       uint4 hi, lo;
+      const float rs = rstd * sx;
 #pragma unroll
       for (int i = 0; i < kXChunksPerThread; ++i) {
         const int ch = cs + 8 * i;
@@ -576,16 +580,18 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
           float v[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            v[e] = (valid && col0 + 8 * ch + e < D) ? (xr[i][e] - mean) * rstd : 0.0f;
+            v[e] = (valid && col0 + 8 * ch + e < D) ? (xr[i][e] - mean) * rs : 0.0f;
             if (COLSUM) csum[i][e] += v[e];
           }
-          split8(v, hi, lo);
+          split8u(v, hi, lo);
           const uint32_t off = (uint32_t)ch * kHChunk + (uint32_t)hr * 16;
           *reinterpret_cast<uint4*>(sm + m.B + off) = hi;
           *reinterpret_cast<uint4*>(sm + m.B + m.b_piece + off) = lo;
         }
       }
-      split8(dr, hi, lo);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) dr[e] *= kSD;
+      split8u(dr, hi, lo);
       const uint32_t off = (uint32_t)cs * kHChunk + (uint32_t)hr * 16;
       *reinterpret_cast<uint4*>(sm + m.A + off) = hi;
       *reinterpret_cast<uint4*>(sm + m.A + 8 * kHChunk + off) = lo;
@@ -616,7 +622,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
     float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * a.total + a.out_w;
     const int j = r & 63;
-    const float lane_scale = (q4 >> 1) ? kLoInv : 1.0f;
+    const float ginv = 1.0f / (sx * kSD);
     for (int blk = cq; blk < colw / 16; blk += 4) {
       float u[16], w[16];
       umma::tmem_ld16(lane_addr + 16 * blk, u);
@@ -625,7 +631,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       for (int i = 0; i < 16; ++i) {
         const int k = col0 + 16 * blk + i;
         if (k < D) {
-          const float val = fmaf(w[i], kLoInv, u[i]) * lane_scale;
+          const float val = (u[i] + w[i]) * ginv;
           if (a.transposed) gp[(size_t)((k + a.rot) % D) * 64 + j] = val;
           else gp[(size_t)j * D + k] = val;
         }
@@ -647,7 +653,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       const int c8 = tid / (kXChunksPerThread * 8), ie = tid % (kXChunksPerThread * 8);
       const int ch = c8 + 8 * (ie >> 3), k = col0 + 8 * ch + (ie & 7);
       if (ch < nchx && k < D)
-        a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b + (k + a.rot) % D] = csred[0][c8][ie] + csred[1][c8][ie];
+        a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b + (k + a.rot) % D] = (csred[0][c8][ie] + csred[1][c8][ie]) * (1.0f / sx);
     }
   }
   umma::tc_fence_before();
