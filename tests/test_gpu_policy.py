@@ -252,8 +252,8 @@ def test_critic_on_the_buffers_replicated_share_obs_view(golden_dir):
 
 def test_raw_inputs_beyond_the_fp16_range_do_not_poison_the_tensor_core_path():
     """--use_feature_normalization off: raw observations are the one operand the network does not bound.  The fp16 `hi`
-    halves of the tensor-core operands saturate at +-65504 instead of turning into inf -> NaN (DESIGN.md 4.1 "operand
-    range"): an outlier row stays finite and the other rows are untouched."""
+    halves of the tensor-core operands (input rows carry the scale 16) saturate at +-4094 instead of turning into
+    inf -> NaN (DESIGN.md 4.1 "operand range"): an outlier row stays finite and the other rows are untouched."""
     from mappo_b200.envs.spaces import Discrete
     from mappo_b200.algorithms.r_mappo.algorithm.rMAPPOPolicy import R_MAPPOPolicy
     args = types.SimpleNamespace(hidden_size=64, layer_N=1, use_ReLU=False, use_feature_normalization=False,
