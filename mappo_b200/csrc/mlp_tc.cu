@@ -69,7 +69,7 @@ __host__ __device__ inline Map make_map(int Kp, int AS, bool update, int raw_flo
   m.b2f = take(64 * 4);
   m.b1s = take(64 * 4);                             // biases times 2 log2(e): tanh straight from the accumulator
   m.b2s = take(64 * 4);
-  m.bhf = take(kMaxA * 4);
+  m.bhf = take(2 * kMaxA * 4);                       // head biases (folded), then the row sums of the folded head weights
   m.dbh = take(update ? kBM * AS * 4 : 0);
   m.xch = take(2 * 4 * kBM * 8);
   m.xlog_in_x = (update && !early && (uint32_t)(4 * kBM * AS * 4) <= kNP * m.x_piece) ? 1 : 0;
@@ -122,12 +122,17 @@ __device__ __forceinline__ void stage_weights_serial(unsigned char* sm, const Ma
     const int aidx = tid - 64;
     int h = 0, off = 0;
     while (h < L.n_heads && aidx >= off + L.head_dim[h]) { off += L.head_dim[h]; ++h; }
-    float s = 0.0f;
+    float s = 0.0f, sw = 0.0f;
     if (h < L.n_heads) {
       s = P[L.bh[h] + (aidx - off)];
-      for (int k = 0; k < 64; ++k) s = fmaf(P[L.wh[h] + (aidx - off) * 64 + k], P[L.be2 + k], s);
+      for (int k = 0; k < 64; ++k) {
+        const float w = P[L.wh[h] + (aidx - off) * 64 + k];
+        s = fmaf(w, P[L.be2 + k], s);
+        sw = fmaf(w, P[L.g2 + k], sw);
+      }
     }
     reinterpret_cast<float*>(sm + m.bhf)[aidx] = s;
+    reinterpret_cast<float*>(sm + m.bhf)[kMaxA + aidx] = sw;
   }
   float* dbh = reinterpret_cast<float*>(sm + m.dbh);
   for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
@@ -137,7 +142,7 @@ __device__ __forceinline__ void stage_weights_serial(unsigned char* sm, const Ma
 // Every launch of every CTA pays for it, and all of it is L2 latency: the loops have compile-time trip counts so that a
 // thread's loads go out together, and the three bias folds (64 + 64 + 16 dot products) are spread over all 16 warps
 // -- two elements per lane and a shuffle reduction -- instead of 80 threads walking 64 dependent steps each.
-template <int KP>
+template <int KP, bool SWF>
 __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m, const MlpArgs& a, bool with_w1, bool update) {
   const NetLayout& L = a.L;
   const float* __restrict__ P = a.params;
@@ -183,16 +188,18 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     p2[i] = fmaf(P[L.w2 + j * 64 + lane + 32], P[L.be1 + lane + 32], P[L.w2 + j * 64 + lane] * P[L.be1 + lane]);
   }
   // head biases: warp w folds logit w
-  float ph = 0.0f;
+  float ph = 0.0f, pw = 0.0f;
   int hh = 0, hoff = 0;
   while (hh < L.n_heads && warp >= hoff + L.head_dim[hh]) { hoff += L.head_dim[hh]; ++hh; }
   if (hh < L.n_heads) {
     const float* wr = P + L.wh[hh] + (warp - hoff) * 64;
     ph = fmaf(wr[lane + 32], P[L.be2 + lane + 32], wr[lane] * P[L.be2 + lane]);
+    if (SWF) pw = fmaf(wr[lane + 32], P[L.g2 + lane + 32], wr[lane] * P[L.g2 + lane]);   // only the fused head exchange reads it
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i) { p1[i] = warp_sum(p1[i]); p2[i] = warp_sum(p2[i]); }
   ph = warp_sum(ph);
+  if (SWF) pw = warp_sum(pw);
   if (lane < 4) {
     const int j = 4 * warp + lane;
     const float s1 = P[L.b1 + j] + (lane == 0 ? p1[0] : lane == 1 ? p1[1] : lane == 2 ? p1[2] : p1[3]);
@@ -202,7 +209,10 @@ __device__ __forceinline__ void stage_weights_tc(unsigned char* sm, const Map& m
     reinterpret_cast<float*>(sm + m.b2f)[j] = s2;
     reinterpret_cast<float*>(sm + m.b2s)[j] = s2 * kTanhScale;
   }
-  if (lane == 0) reinterpret_cast<float*>(sm + m.bhf)[warp] = (hh < L.n_heads) ? P[L.bh[hh] + (warp - hoff)] + ph : 0.0f;
+  if (lane == 0) {
+    reinterpret_cast<float*>(sm + m.bhf)[warp] = (hh < L.n_heads) ? P[L.bh[hh] + (warp - hoff)] + ph : 0.0f;
+    reinterpret_cast<float*>(sm + m.bhf)[kMaxA + warp] = pw;
+  }
   float* dbh = reinterpret_cast<float*>(sm + m.dbh);
   for (int e = tid; update && e < kBM * (L.a_total | 1); e += kThreads) dbh[e] = 0.0f;
 }
@@ -504,7 +514,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   }
   if (warp == 0) umma::tmem_alloc(&tmem_base_s, UPDATE ? kTmemCols : 128);
   if (UPDATE) stage_weights_serial(sm, m, a, !WIDE, UPDATE);
-  else stage_weights_tc<KP>(sm, m, a, !WIDE, UPDATE);
+  else stage_weights_tc<KP, (HEAD && AMAX == 8)>(sm, m, a, !WIDE, UPDATE);
   if (UPDATE && tid < kBM) {                                            // the ones columns (written once)
     const uint4 one = make_uint4(0x00005400u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);   // fp16(kSN) = 64
     auto put = [&](unsigned char* base) {
@@ -635,7 +645,55 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
         umma::mma_commit(bar);
       }
     }
-    act_ln16(n2, kInvFc2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
+    // FUSE (the register-loss head of at most 8 logits): the head's partial dot products are taken on the activations BEFORE the LayerNorm,
+    // inside the MUFU-paced activation loop, and travel with the row's LayerNorm partial sums through ONE exchange:
+    // logit = b' + rstd (sum_k t_k w'_k - mean sum_k w'_k).  Otherwise: LayerNorm exchange, then the logits' own.
+    constexpr bool FUSE = HEAD && AMAX == 8;                 // (the single-logit critic head measured 6 % slower in the rollout)
+    float* xlog = reinterpret_cast<float*>(sm + (m.xlog_in_x ? m.X + (buf ^ 1) * x_bytes : m.xlog));
+    float l[AMAX];
+    if (FUSE) {
+      float s = 0.0f, q = 0.0f;
+      const float ts = kTanhScale * kInvFc2;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float y = fmaf(n2[i], ts, b2s[i]);
+        n2[i] = relu ? fmaxf(fmaf(n2[i], kInvFc2, b2f[i]), 0.0f) : ((i & 1) ? tanh_scaled_fma(y) : tanh_scaled(y));
+        s += n2[i];
+        q = fmaf(n2[i], n2[i], q);
+      }
+      float* mine = xlog + (size_t)(cq * kBM + r) * AS;
+#pragma unroll
+      for (int qq = 0; qq < AMAX; ++qq) {
+        if (qq < A) {
+          const float4* w4 = reinterpret_cast<const float4*>(Whf + qq * 64 + 16 * cq);
+          float d = 0.0f;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 w = w4[i];
+            d = fmaf(n2[4 * i], w.x, fmaf(n2[4 * i + 1], w.y, fmaf(n2[4 * i + 2], w.z, fmaf(n2[4 * i + 3], w.w, d))));
+          }
+          mine[qq] = d;
+        }
+      }
+      const float2 tot = row_sum2(s, q, xch, slot, cq, r, q4);            // its barrier also publishes the partial dots
+      mean2 = tot.x * (1.0f / 64.0f);
+      const float var = fmaxf(fmaf(-mean2, mean2, tot.y * (1.0f / 64.0f)), 0.0f);
+      rstd2 = 1.0f / sqrtf(var + kLnEps);
+      const float rs = rstd2 * kSN, nmr = -(mean2 * rstd2) * kSN;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) n2[i] = fmaf(n2[i], rs, nmr);
+#pragma unroll
+      for (int qq = 0; qq < AMAX; ++qq) {
+        l[qq] = 0.0f;
+        if (qq < A) {
+          const float* p = xlog + (size_t)r * AS + qq;
+          const float dsum = (p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]);
+          l[qq] = fmaf(rstd2, fmaf(-mean2, bhf[kMaxA + qq], dsum), bhf[qq]);
+        }
+      }
+    } else {
+      act_ln16(n2, kInvFc2, b2f, b2s, relu, xch, slot, cq, r, q4, mean2, rstd2);
+    }
     if (UPDATE && HEAD && !VHEAD && !DEFER) store_cols16u(sm + m.BS2, 8 * kRowChunk, r, cq, n2);
     if (MODE == 4 && valid) {
       float4* fo = reinterpret_cast<float4*>(a.feat + g * 64 + 16 * cq);
@@ -643,8 +701,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       for (int i = 0; i < 4; ++i)
         fo[i] = make_float4(n2[4 * i] * (1.0f / kSN), n2[4 * i + 1] * (1.0f / kSN), n2[4 * i + 2] * (1.0f / kSN), n2[4 * i + 3] * (1.0f / kSN));
     }
-    float* xlog = reinterpret_cast<float*>(sm + (m.xlog_in_x ? m.X + (buf ^ 1) * x_bytes : m.xlog));
-    if (HEAD) {
+    if (HEAD && !FUSE) {
       float* mine = xlog + (size_t)(cq * kBM + r) * AS;
 #pragma unroll
       for (int q = 0; q < AMAX; ++q) {
@@ -659,16 +716,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
           mine[q] = s * (1.0f / kSN);                       // n2[] holds kSN n2
         }
       }
-    }
-    if (HEAD) bar_named(1 + q4, 128);
-    float l[AMAX];
+      bar_named(1 + q4, 128);
 #pragma unroll
-    for (int q = 0; q < AMAX; ++q) {
-      l[q] = 0.0f;
-      if (HEAD && q < A) {
-        const float* p = xlog + (size_t)r * AS + q;
-        l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
+      for (int q = 0; q < AMAX; ++q) {
+        l[q] = 0.0f;
+        if (q < A) {
+          const float* p = xlog + (size_t)r * AS + q;
+          l[q] = bhf[q] + ((p[0] + p[(size_t)kBM * AS]) + (p[(size_t)2 * kBM * AS] + p[(size_t)3 * kBM * AS]));
+        }
       }
+    }
+    if (!HEAD) {
+#pragma unroll
+      for (int q = 0; q < AMAX; ++q) l[q] = 0.0f;
     }
     if (!UPDATE) {
       if (cq == 0 && valid) {
