@@ -850,8 +850,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
       if (HEAD && !VHEAD && !DEFER) issue_wgrad(tb + kColGh, sB2, sDL, kIdGh, !first);   // Gh += n2^T dlogits
       issue_wgrad(tb + kColG2, sBS, sN1, kIdG2, !first);               // G2 += dz2^T [n1 | 1]
       umma::mma_commit(gbar);                                          // (frees BS for dz1: ahead of the next tile's fc1)
-      if (ROWP && has_next) issue_rowp(tile + gridDim.x);            // this tile's scalars were read before the barrier
-      if (EARLY && has_next) {                                                                  // the next tile's fc1
+    }
+    if (issuer_next && has_next && umma::elect_one()) {              // (another lane quadrant shares the issue time)
+      umma::tc_fence_after();
+      if (ROWP) issue_rowp(tile + gridDim.x);                        // this tile's scalars were read before the barrier
+      if (EARLY) {                                                                              // the next tile's fc1
         issue_bulk(tile + 2 * (long long)gridDim.x);
         issue_rowgemm<KP / 16>(tb + kF, sX + (buf ^ 1) * x_bytes16, x_piece16, sW1, w1_piece16, kWChunk,
                                128, 2 * kWChunk16, kIdFwd);
