@@ -832,9 +832,11 @@ int rnn_update(MlpArgs& a, const mappo_net_config* cfg, long long n_chunks, int 
     WideArgs w{};
     w.rows = B; w.index = nullptr; w.x_div = 1; w.vec = 1; w.ld = 256; w.D = 192; w.dz_ld = 64; w.norm = 0;
     w.total = a.L.total; w.transposed = 1; w.grad_partials = a.grad_partials;
+    // ONE pass over the 256-column gradient rows `dgi_n | dr~ | dz~ | dgh_n` yields both weight gradients: dW_ih from the
+    // columns [0, 192) against n2 (stored rotated: n, r, z -> r, z, n), dW_hh from [64, 256) against hm
+    w.D = 256; w.win = 192;
     w.x = gates[l]; w.dz1 = const_cast<float*>(g.n2); w.rot = 128; w.out_w = g.wih; w.out_b = g.bih;
-    if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
-    w.x = gates[l] + 64; w.dz1 = hm[l]; w.rot = 0; w.out_w = g.whh; w.out_b = g.bhh;
+    w.dz2 = hm[l]; w.off2 = 64; w.rot2 = 0; w.out_w2 = g.whh; w.out_b2 = g.bhh;
     if (int rc = launch_wgrad_generic(w, stream, who)) return rc;
   }
   a.feat = dh;

@@ -418,27 +418,30 @@ __global__ void __launch_bounds__(kPkThreads, 1) fc1_packed_kernel(const WideArg
 }
 
 // ---- weight gradient ---------------------------------------------------------------------------------------
-// CTA (column group cg, row split sp) accumulates G[128 = dz1 hi | dz1 lo][colw] over its 64-row half tiles in two TMEM
-// blocks (x^ hi at column 0, x^ lo at column 256).  Operands are MN-major (the contraction runs over the rows): A =
+// CTA (column group cg, row split sp) accumulates G[128 = dz1 hi | dz1 lo][colw] over its 64-row half tiles in ONE TMEM
+// block (x^ hi and x^ lo are equally scaled and go into the same columns); DUAL: a second dz operand (dz2) accumulates
+// against the same x^ tiles into the block at column 256.  Operands are MN-major (the contraction runs over the rows): A =
 // dz1 [64 rows][128], B = x^ [64 rows][colw] per piece.  One operand buffer; the next half tile's values are
 // prefetched into registers while the tensor cores read the current one.
 constexpr int kHR = 64;                                    // rows per half tile
 constexpr uint32_t kHChunk = kHR * 16;                     // bytes of one 8-column chunk of a 64-row operand tile
-constexpr int kMaxColw = 240;
-constexpr int kXChunksPerThread = 4;                       // ceil(30 chunks / 8 column subsets)
+constexpr int kMaxColw = 256;
+constexpr int kXChunksPerThread = 4;                       // ceil(32 chunks / 8 column subsets)
 
 constexpr int kDzStride = 68;                              // floats per staged dz row (64 + 4: conflict-free float4 reads)
-struct WgMap { uint32_t A, B, b_piece, stage, stage_dz, xs_stride, bars, total; };
-__host__ __device__ inline WgMap make_wg_map(int colw) {
+struct WgMap { uint32_t A, A2, B, b_piece, stage, stage_dz, stage_dz2, xs_stride, bars, total; };
+__host__ __device__ inline WgMap make_wg_map(int colw, bool dual = false) {
   WgMap m;
   uint32_t o = 0;
   auto take = [&](uint32_t bytes) { uint32_t r = o; o += (bytes + 127u) & ~127u; return r; };
   m.A = take(16 * kHChunk);
+  m.A2 = take(dual ? 16 * kHChunk : 0);
   m.b_piece = (uint32_t)(colw / 8) * kHChunk;
   m.B = take(2 * m.b_piece);
   m.xs_stride = (uint32_t)colw + 4;                        // floats per staged x row
   m.stage = take(kHR * m.xs_stride * 4);                   // landing tiles of the asynchronous, row-coalesced loads: x ...
   m.stage_dz = take(kHR * kDzStride * 4);                  // ... and dz
+  m.stage_dz2 = take(dual ? kHR * kDzStride * 4 : 0);
   m.bars = take(64);
   m.total = o;
   return m;
@@ -449,13 +452,13 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src, int bytes
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(umma::smem_u32(dst)), "l"(src), "r"(bytes) : "memory");
 }
 
-template <bool COLSUM>
+template <bool COLSUM, bool DUAL>
 __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs a) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_base_s;
   __shared__ float csred[2][8][kXChunksPerThread * 8];
   const int D = a.D, colw = a.colw;
-  const WgMap m = make_wg_map(colw);
+  const WgMap m = make_wg_map(colw, DUAL);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cg = blockIdx.x % a.ncg, sp = blockIdx.x / a.ncg;
   const int col0 = cg * colw;
@@ -469,11 +472,11 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
   __syncthreads();
   umma::tc_fence_after();
   const uint32_t tb = tmem_base_s;
-  const uint32_t sA = umma::smem_u32(sm + m.A), sB = umma::smem_u32(sm + m.B);
+  const uint32_t sA = umma::smem_u32(sm + m.A), sA2 = umma::smem_u32(sm + m.A2), sB = umma::smem_u32(sm + m.B);
   const uint32_t idesc = umma::idesc_f16(128, colw, 1, 1);
   const long long nht = (a.rows + kHR - 1) / kHR;
 
-  float xr[kXChunksPerThread][8], dr[8], mean = 0.0f, rstd = 1.0f;
+  float xr[kXChunksPerThread][8], dr[8], dr2[8], mean = 0.0f, rstd = 1.0f;
   bool valid = false;
   const float sx = a.norm ? kSN : kSD;                    // x is LayerNorm output (C5) or a gradient array (GRU chain)
   // 16-byte aligned rows: the next half tile is copied asynchronously into shared-memory landing tiles, consecutive
@@ -483,6 +486,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
   bool valid_n = false;
   float* xs = reinterpret_cast<float*>(sm + m.stage);
   float* dzs = reinterpret_cast<float*>(sm + m.stage_dz);
+  float* dzs2 = reinterpret_cast<float*>(sm + m.stage_dz2);
   const int xs_stride = (int)m.xs_stride, upr = colw / 4;     // 16-byte units per staged x row
   (void)upr;
   auto issue_async = [&](long long ht) {
@@ -510,6 +514,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       const bool ok = g < a.rows;
       const int q = lane & 15;
       cp_async16(dzs + rr * kDzStride + 4 * q, a.dz1 + (ok ? g : 0) * a.dz_ld + 4 * q, ok ? 16 : 0);
+      if (DUAL) cp_async16(dzs2 + rr * kDzStride + 4 * q, a.dz2 + (ok ? g : 0) * a.dz_ld + 4 * q, ok ? 16 : 0);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
@@ -528,6 +533,11 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     const float4* p = reinterpret_cast<const float4*>(dzs + hr * kDzStride + 8 * cs);
     const float4 d0 = p[0], d1 = p[1];
     dr[0] = d0.x; dr[1] = d0.y; dr[2] = d0.z; dr[3] = d0.w; dr[4] = d1.x; dr[5] = d1.y; dr[6] = d1.z; dr[7] = d1.w;
+    if (DUAL) {
+      const float4* p2 = reinterpret_cast<const float4*>(dzs2 + hr * kDzStride + 8 * cs);
+      const float4 e0 = p2[0], e1 = p2[1];
+      dr2[0] = e0.x; dr2[1] = e0.y; dr2[2] = e0.z; dr2[3] = e0.w; dr2[4] = e1.x; dr2[5] = e1.y; dr2[6] = e1.z; dr2[7] = e1.w;
+    }
     valid = valid_n; mean = mean_n; rstd = rstd_n;
     __syncthreads();                                                    // landing tiles free for the next half tile
   };
@@ -548,9 +558,14 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       const float4 p = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * a.dz_ld + 8 * cs));
       const float4 q = __ldg(reinterpret_cast<const float4*>(a.dz1 + g * a.dz_ld + 8 * cs + 4));
       dr[0] = p.x; dr[1] = p.y; dr[2] = p.z; dr[3] = p.w; dr[4] = q.x; dr[5] = q.y; dr[6] = q.z; dr[7] = q.w;
+      if (DUAL) {
+        const float4 p2 = __ldg(reinterpret_cast<const float4*>(a.dz2 + g * a.dz_ld + 8 * cs));
+        const float4 q2 = __ldg(reinterpret_cast<const float4*>(a.dz2 + g * a.dz_ld + 8 * cs + 4));
+        dr2[0] = p2.x; dr2[1] = p2.y; dr2[2] = p2.z; dr2[3] = p2.w; dr2[4] = q2.x; dr2[5] = q2.y; dr2[6] = q2.z; dr2[7] = q2.w;
+      }
     } else {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) dr[i] = 0.0f;
+      for (int i = 0; i < 8; ++i) { dr[i] = 0.0f; dr2[i] = 0.0f; }
     }
   };
 
@@ -595,6 +610,13 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
       const uint32_t off = (uint32_t)cs * kHChunk + (uint32_t)hr * 16;
       *reinterpret_cast<uint4*>(sm + m.A + off) = hi;
       *reinterpret_cast<uint4*>(sm + m.A + 8 * kHChunk + off) = lo;
+      if (DUAL) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dr2[e] *= kSD;
+        split8u(dr2, hi, lo);
+        *reinterpret_cast<uint4*>(sm + m.A2 + off) = hi;
+        *reinterpret_cast<uint4*>(sm + m.A2 + 8 * kHChunk + off) = lo;
+      }
     }
     umma::fence_async_smem();
     umma::tc_fence_before();
@@ -607,7 +629,12 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
         const uint64_t dh = umma::smem_desc(sB + (uint32_t)ks * 256, 128, kHChunk);
         const uint64_t dl = umma::smem_desc(sB + m.b_piece + (uint32_t)ks * 256, 128, kHChunk);
         umma::mma_f16(tb, da, dh, idesc, n > 0 || ks > 0);
-        umma::mma_f16(tb + 256, da, dl, idesc, n > 0 || ks > 0);
+        umma::mma_f16(tb, da, dl, idesc, true);
+        if (DUAL) {
+          const uint64_t da2 = umma::smem_desc(sA2 + (uint32_t)ks * 256, 128, kHChunk);
+          umma::mma_f16(tb + 256, da2, dh, idesc, n > 0 || ks > 0);
+          umma::mma_f16(tb + 256, da2, dl, idesc, true);
+        }
       }
       umma::mma_commit(bar);
     }
@@ -620,21 +647,24 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     umma::tc_fence_after();
     const int q4 = warp & 3, cq = warp >> 2, r = 32 * q4 + lane;
     const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
-    float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * a.total + a.out_w;
+    float* __restrict__ gp = a.grad_partials + (size_t)(2 * sp + (q4 >> 1)) * a.total;
     const int j = r & 63;
     const float ginv = 1.0f / (sx * kSD);
+    const int win = DUAL ? a.win : D;
     for (int blk = cq; blk < colw / 16; blk += 4) {
       float u[16], w[16];
       umma::tmem_ld16(lane_addr + 16 * blk, u);
-      umma::tmem_ld16(lane_addr + 256 + 16 * blk, w);
+      if (DUAL) umma::tmem_ld16(lane_addr + 256 + 16 * blk, w);
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int k = col0 + 16 * blk + i;
-        if (k < D) {
-          const float val = (u[i] + w[i]) * ginv;
-          if (a.transposed) gp[(size_t)((k + a.rot) % D) * 64 + j] = val;
-          else gp[(size_t)j * D + k] = val;
+        if (k < win) {
+          const float val = u[i] * ginv;
+          if (a.transposed) gp[a.out_w + (size_t)((k + a.rot) % win) * 64 + j] = val;
+          else gp[a.out_w + (size_t)j * D + k] = val;
         }
+        if (DUAL && k >= a.off2 && k < a.off2 + win)
+          gp[a.out_w2 + (size_t)((k - a.off2 + a.rot2) % win) * 64 + j] = w[i] * ginv;
       }
     }
   }
@@ -652,8 +682,13 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad1_wide_kernel(const WideArgs
     if (tid < 8 * kXChunksPerThread * 8) {
       const int c8 = tid / (kXChunksPerThread * 8), ie = tid % (kXChunksPerThread * 8);
       const int ch = c8 + 8 * (ie >> 3), k = col0 + 8 * ch + (ie & 7);
-      if (ch < nchx && k < D)
-        a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b + (k + a.rot) % D] = (csred[0][c8][ie] + csred[1][c8][ie]) * (1.0f / sx);
+      if (ch < nchx && k < D) {
+        const float v = (csred[0][c8][ie] + csred[1][c8][ie]) * (1.0f / sx);
+        const int win = DUAL ? a.win : D;
+        if (k < win) a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b + (k + a.rot) % win] = v;
+        if (DUAL && k >= a.off2 && k < a.off2 + win)
+          a.grad_partials[(size_t)(2 * sp) * a.total + a.out_b2 + (k - a.off2 + a.rot2) % win] = v;
+      }
     }
   }
   umma::tc_fence_before();
@@ -900,15 +935,21 @@ int launch_wgrad_generic(WideArgs& w, cudaStream_t stream, const char* who) {
   if (ns < 1) ns = 1;
   if (ns > nht) ns = nht;
   w.nsplit = (int)ns;
-  const WgMap m = make_wg_map(w.colw);
+  const bool dual = w.dz2 != nullptr;
+  MAPPO_REQUIRE(!dual || (w.ncg == 1 && w.transposed && w.out_b >= 0 && w.win > 0 && w.off2 + w.win <= D),
+                "%s: the dual weight gradient needs one column group (D <= %d), transposed outputs and both bias slots", who, kMaxColw);
+  const WgMap m = make_wg_map(w.colw, dual);
   static bool attr_set = false;
   if (!attr_set) {
-    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    MAPPO_CUDA(cudaFuncSetAttribute(wgrad1_wide_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
     attr_set = true;
   }
-  if (w.out_b >= 0) wgrad1_wide_kernel<true><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
-  else wgrad1_wide_kernel<false><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  MAPPO_REQUIRE(m.total <= 216 * 1024, "%s: weight-gradient shared-memory map too large (%u B)", who, m.total);
+  if (dual) wgrad1_wide_kernel<true, true><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  else if (w.out_b >= 0) wgrad1_wide_kernel<true, false><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
+  else wgrad1_wide_kernel<false, false><<<w.ncg * w.nsplit, kThreads, m.total, stream>>>(w);
   MAPPO_CHECK_LAUNCH(who);
   return 0;
 }

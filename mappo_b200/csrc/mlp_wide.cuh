@@ -22,6 +22,10 @@ struct WideArgs {
   int out_w;                     // slot offset of G in a partial row
   int transposed, rot;           // 0: G stored [j][k] (row stride D); 1: stored [(k + rot) % D][j] (row stride 64)
   int out_b;                     // >= 0: slot offset of the column sums of x, stored at (k + rot) % D; -1: none
+  // dual form (the recurrent chain's two weight gradients from ONE pass over the gradient rows): a second dz operand and a
+  // second output; output 1 takes the x columns [0, win), output 2 the columns [off2, off2 + win), each stored at
+  // (k' + rot) % win with k' counted from its window's first column.  win == 0: single form (window = D).
+  const float* dz2; int win, off2, rot2, out_w2, out_b2;
 };
 
 int launch_wgrad_generic(WideArgs& w, cudaStream_t stream, const char* who);
