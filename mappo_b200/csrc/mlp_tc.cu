@@ -532,7 +532,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_tc_kernel(const MlpArgs a) {
   __syncthreads();
   umma::tc_fence_after();
   // MMA groups are issued by one elected lane of warps 0 / 1 / 2 (three different schedulers) in turn
-  const bool issuer_fc2 = (warp == 0), issuer_bwd = (warp == 1), issuer_next = (warp == 2);
+  // (column quarter 3: the quarter-0 warps already carry the per-row extras -- loss sums, dlogits tile, head-bias sums)
+  const bool issuer_fc2 = (warp == 12), issuer_bwd = (warp == 13), issuer_next = (warp == 14);
   if (issuer_next && umma::elect_one()) { issue_bulk(tile + gridDim.x); issue_rowp(tile); }
   const uint32_t tb = tmem_base_s;
   const uint32_t lane_addr = tb + ((uint32_t)(32 * q4) << 16);
