@@ -66,3 +66,4 @@ def test_benchmark_networks_take_the_tensor_core_kernels():
     assert path(11, [3, 5], False) == 1 and path(21, [5, 10], False) == 1                          # speaker_listener / reference heads
     assert path(18, [5], False, rnn=1) == 3 and path(54, [1], True, rnn=2) == 3                    # C4: GRU chain
     assert path(18, [5], False, layer_N=2) == 0                                                    # deep base: fp32 tiles
+    assert path(40, [16], False) == 0 and path(40, [8], False) == 1 and path(31, [16], False) == 1  # 64-wide tile + 16 logits: 229 KB
