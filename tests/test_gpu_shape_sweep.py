@@ -61,3 +61,38 @@ def test_update_gradients_across_shapes(D, S, A, group, rows_c, flags):
     Pa = pol.actor.flat.numel()
     _check(pol.actor, ws["grad"][:Pa], ga, "actor update D=%d A=%d rows=%d" % (D, A, B))
     _check(pol.critic, ws["grad"][Pa:], gc, "critic update S=%d group=%d rows=%d" % (S, group, rows_c))
+
+
+@pytest.mark.parametrize("D,S,A,group,rows_c,flags", CASES)
+def test_rollout_forward_across_shapes(D, S, A, group, rows_c, flags):
+    """The rollout kernels (MODE 0 / 1) at the same shapes: values, deterministic and sampled actions, their log-probs --
+    against the float32 oracle forward (oracle/policy.py), with the tolerances of tests/test_gpu_policy.py."""
+    from test_gpu_large_batch import _policy
+    from mappo_b200.envs.spaces import Discrete
+    from oracle import policy as op
+    B = rows_c * group
+    a, pol, tr, g = _policy(flags, D, S, Discrete(A), seed=D + A)
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    obs = r(B, D) * (0.4 + r(1, D).abs()) + 0.3 * r(1, D)
+    share = r(rows_c, S) * (0.4 + r(1, S).abs()) + 0.3 * r(1, S)
+    cpu = lambda net: {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    asd, csd = cpu(pol.actor), cpu(pol.critic)
+    z = lambda n: np.zeros((n, 1, 64), np.float32)
+    ones = lambda n: np.ones((n, 1), np.float32)
+    feats, _ = op.actor_features(asd, obs.cpu().numpy(), z(B), ones(B), a.use_ReLU, a.use_feature_normalization, False)
+    logits = op.actor_logits(asd, feats, None)
+    v_ref, _ = op.critic_values(csd, share.cpu().numpy(), z(rows_c), ones(rows_c), a.use_ReLU, a.use_feature_normalization, False)
+    values = pol.get_values(share, None, None)
+    np.testing.assert_allclose(values.cpu().numpy().reshape(-1), np.asarray(v_ref).reshape(-1), rtol=1e-4, atol=2e-5)
+    a_ref, lp_ref, _ = op.act_forward(logits, True)
+    act, lp, _ = pol.actor(obs, None, None, None, deterministic=True)
+    same = act.cpu().numpy() == a_ref.numpy()
+    assert same.mean() > 0.995 or B < 200
+    np.testing.assert_allclose(lp.cpu().numpy()[same], lp_ref.numpy()[same], rtol=1e-4, atol=2e-5)
+    pol.actor.sample_seed = 7
+    acts = torch.empty(B, 1, device="cuda"); lps = torch.empty_like(acts)
+    pol.actor.forward_into(obs, acts, lps, step=3, row_offset=11)
+    a_s, lp_s, margin = op.act_forward(logits, False, seed=7, step=3, row_offset=11)
+    diff = acts.cpu().numpy() != a_s.numpy()
+    assert not (diff & (margin.numpy() > 1e-5)).any(), "sampled action differs away from a CDF boundary"
+    np.testing.assert_allclose(lps.cpu().numpy()[~diff], lp_s.numpy()[~diff], rtol=1e-4, atol=2e-5)
