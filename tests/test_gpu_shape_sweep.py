@@ -96,3 +96,35 @@ def test_rollout_forward_across_shapes(D, S, A, group, rows_c, flags):
     diff = acts.cpu().numpy() != a_s.numpy()
     assert not (diff & (margin.numpy() > 1e-5)).any(), "sampled action differs away from a CDF boundary"
     np.testing.assert_allclose(lps.cpu().numpy()[~diff], lp_s.numpy()[~diff], rtol=1e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("S,group,rows_c,packed", [(64, 1, 300, False), (65, 3, 1000, True), (100, 2, 129, False),
+                                                    (250, 3, 1500, False), (256, 1, 1500, True), (257, 4, 700, False),
+                                                    (481, 5, 900, True), (513, 2, 640, False), (1000, 3, 333, True)])
+def test_wide_first_layer_across_widths(S, group, rows_c, packed):
+    """The wide first layer (csrc/mlp_wide.cu) at widths on both sides of its column-group boundaries (one weight-gradient
+    column group holds <= 256 columns) and of the packed tiles' 16-column chunks: critic update vs the float64 oracle."""
+    from test_gpu_large_batch import _policy, _critic_oracle64, _check, _threads
+    from mappo_b200 import ops
+    from mappo_b200.envs.spaces import Discrete
+    B = rows_c * group
+    a, pol, tr, g = _policy("--use_ReLU", 18, S, Discrete(5), seed=S)
+    assert ops.kernel_path(pol.critic.cfg) == 2
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    share = r(rows_c, S) * (0.4 + r(1, S).abs()) + 0.3 * r(1, S)
+    obs = r(B, 18)
+    acts = torch.randint(0, 5, (B, 1), device="cuda", generator=g).float()
+    old_logp = -1.6 + 0.1 * r(B, 1)
+    adv, vp, ret = r(B), 0.5 * r(B), -5.0 + 3.0 * r(B)
+    active = (torch.rand(B, device="cuda", generator=g) > 0.1).float()
+    tr.value_normalizer.update(-4.0 + 2.0 * torch.randn(300, 1, device="cuda", generator=g))
+    vn_before = tr.value_normalizer.stats.cpu().numpy().copy()
+    torch.set_num_threads(_threads())
+    try:
+        vl, gc = _critic_oracle64(a, pol, tr, share, group, vp.view(B, 1), ret.view(B, 1), active.view(B, 1), vn_before)
+    finally:
+        torch.set_num_threads(1)
+    pk = ops.critic_pack_inputs(pol.critic.cfg, share) if packed else None
+    ws = tr._update(obs, share, group, acts, old_logp, adv, vp, ret, active, None, B, packed=pk)
+    np.testing.assert_allclose(tr._info[4].item(), vl, rtol=1e-4, atol=1e-6)
+    _check(pol.critic, ws["grad"][pol.actor.flat.numel():], gc, "wide critic S=%d group=%d rows=%d" % (S, group, rows_c))
