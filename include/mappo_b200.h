@@ -466,6 +466,23 @@ int mappo_gather_rows(const float* src, long long row_stride, int row_div, int w
  * the host; one pass in C instead of a NumPy fancy-index scatter.  (ABI v6.) */
 int mappo_host_onehot_u8(const int64_t* ids_host, long long rows, int n_heads, const int* head_dim_host,
                          uint8_t* out_host);
+/* the same from float32 ids (what the policy returns: R_Actor stores actions as floats, act.py:41-81), sparing the
+ * runner an int64 conversion pass */
+int mappo_host_onehot_u8_f32(const float* ids_host, long long rows, int n_heads, const int* head_dim_host,
+                             uint8_t* out_host);
+
+/* Up to 8 device -> device copies in ONE launch: SharedReplayBuffer.insert (onpolicy/utils/shared_buffer.py:121-147)
+ * stores six arrays per step; as separate copies they cost six launches of host time each step of a host-driven
+ * rollout.  Pointers 4-byte aligned, sizes multiples of 4 bytes; segments must not overlap.  (No reference counterpart:
+ * the reference's insert is NumPy assignment.) */
+typedef struct mappo_copy_list {
+  int32_t n;                   /* segments in use, 1..8 */
+  int32_t reserved;
+  const void* src[8];
+  void* dst[8];
+  long long bytes[8];
+} mappo_copy_list;
+int mappo_copy_segments(const mappo_copy_list* list, void* stream);
 int mappo_onehot_to_ids(const void* onehot, int dtype, long long rows, int n_heads, const int* head_dim_host,
                         float* ids, int ids_ld, void* stream);
 

@@ -41,3 +41,21 @@ extern "C" int mappo_host_onehot_u8(const int64_t* ids_host, long long rows, int
   }
   return 0;
 }
+
+extern "C" int mappo_host_onehot_u8_f32(const float* ids_host, long long rows, int n_heads, const int* head_dim_host,
+                                    uint8_t* out_host) {
+  MAPPO_REQUIRE(ids_host && out_host && head_dim_host && rows > 0 && n_heads >= 1 && n_heads <= MAPPO_MAX_HEADS,
+                "host_onehot_u8_f32: bad arguments");
+  int width = 0, off[MAPPO_MAX_HEADS];
+  for (int h = 0; h < n_heads; ++h) { off[h] = width; width += head_dim_host[h]; }
+  memset(out_host, 0, (size_t)rows * width);
+  for (long long r = 0; r < rows; ++r) {
+    uint8_t* row = out_host + r * width;
+    for (int h = 0; h < n_heads; ++h) {
+      const long long a = (long long)ids_host[r * n_heads + h];
+      MAPPO_REQUIRE(a >= 0 && a < head_dim_host[h], "host_onehot_u8_f32: action id %lld out of range at row %lld", (long long)a, r);
+      row[off[h] + a] = 1;
+    }
+  }
+  return 0;
+}

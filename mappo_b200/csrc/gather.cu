@@ -81,3 +81,43 @@ extern "C" int mappo_gather_rows(const float* src, long long row_stride, int row
   MAPPO_CHECK_LAUNCH("gather_rows_kernel");
   return 0;
 }
+
+// ---- several device -> device copies in one launch (SharedReplayBuffer.insert) ------------------------------------
+namespace mappo {
+// every block walks every segment with a grid stride: 16-byte pieces where both pointers allow it, 4-byte words otherwise
+__global__ void __launch_bounds__(256) copy_segments_kernel(const mappo_copy_list l) {
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x, nt = (long long)gridDim.x * blockDim.x;
+  for (int s = 0; s < l.n; ++s) {
+    const char* __restrict__ src = static_cast<const char*>(l.src[s]);
+    char* __restrict__ dst = static_cast<char*>(l.dst[s]);
+    const long long bytes = l.bytes[s];
+    const bool wide = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15u) == 0;
+    if (wide) {
+      const long long n16 = bytes >> 4;
+      for (long long i = t0; i < n16; i += nt) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+      for (long long i = (n16 << 2) + t0; i < (bytes >> 2); i += nt)
+        reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+    } else {
+      for (long long i = t0; i < (bytes >> 2); i += nt)
+        reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+    }
+  }
+}
+}  // namespace mappo
+
+extern "C" int mappo_copy_segments(const mappo_copy_list* list, void* stream) {
+  MAPPO_REQUIRE(list && list->n >= 1 && list->n <= 8, "copy_segments: 1..8 segments");
+  long long total = 0;
+  for (int s = 0; s < list->n; ++s) {
+    MAPPO_REQUIRE(list->src[s] && list->dst[s] && list->bytes[s] > 0 && (list->bytes[s] & 3) == 0 &&
+                  ((reinterpret_cast<uintptr_t>(list->src[s]) | reinterpret_cast<uintptr_t>(list->dst[s])) & 3u) == 0,
+                  "copy_segments: segment %d needs 4-byte aligned pointers and a size that is a multiple of 4", s);
+    total += list->bytes[s];
+  }
+  long long blocks = (total / 16 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  mappo::copy_segments_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(*list);
+  MAPPO_CHECK_LAUNCH("copy_segments_kernel");
+  return 0;
+}

@@ -70,3 +70,24 @@ def gather_rows(src, lead_dims, index):
     check(_lib.lib().mappo_gather_rows(C.c_void_p(src.data_ptr()), int(row_stride), int(row_div), int(width),
                                        ptr(index), index.numel(), ptr(out), stream_ptr()), "gather_rows")
     return out
+
+
+class _CopyList(C.Structure):
+    _fields_ = [("n", C.c_int32), ("reserved", C.c_int32), ("src", C.c_void_p * 8), ("dst", C.c_void_p * 8),
+                ("bytes", C.c_longlong * 8)]
+
+
+_lib._EXTRA_SIGS["mappo_copy_segments"] = [C.POINTER(_CopyList), C.c_void_p]
+
+
+def copy_segments(pairs):
+    """pairs: [(dst, src)] of contiguous CUDA tensors of equal dtype and element count (4-byte elements) -> the copies in
+    one launch per 8 pairs (mappo_copy_segments)."""
+    fn = _lib.lib().mappo_copy_segments
+    for i in range(0, len(pairs), 8):
+        cl = _CopyList()
+        chunk = pairs[i:i + 8]
+        cl.n = len(chunk)
+        for k, (dst, src) in enumerate(chunk):
+            cl.src[k], cl.dst[k], cl.bytes[k] = src.data_ptr(), dst.data_ptr(), dst.numel() * dst.element_size()
+        check(fn(C.byref(cl), stream_ptr()), "copy_segments")

@@ -99,12 +99,15 @@ def onehot(actions, head_dims, tag="onehot"):
     (one C pass, mappo_host_onehot_u8).  `MPEVecEnv.step` takes it as is (1 byte per logit over PCIe)."""
     import ctypes as C
     from . import _lib
-    a = np.ascontiguousarray(actions, dtype=np.int64)
+    a = np.asarray(actions)
+    f32 = a.dtype == np.float32                  # what the policy returns (act.py stores ids as floats): no int64 pass
+    a = np.ascontiguousarray(a, dtype=np.float32 if f32 else np.int64)
     heads = len(head_dims)
     rows = a.size // heads
     out = pinned(tag, tuple(a.shape[:-1]) + (int(sum(head_dims)),), torch.uint8)
     L = _lib.lib()
-    L.mappo_host_onehot_u8.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_int), C.c_void_p]
+    fn = L.mappo_host_onehot_u8_f32 if f32 else L.mappo_host_onehot_u8
+    fn.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_int), C.c_void_p]
     hd = (C.c_int * heads)(*[int(d) for d in head_dims])
-    _lib.check(L.mappo_host_onehot_u8(C.c_void_p(a.ctypes.data), rows, heads, hd, C.c_void_p(out.data_ptr())), "host_onehot_u8")
+    _lib.check(fn(C.c_void_p(a.ctypes.data), rows, heads, hd, C.c_void_p(out.data_ptr())), "host_onehot_u8")
     return out.numpy()

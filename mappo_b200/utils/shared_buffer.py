@@ -176,7 +176,13 @@ class SharedReplayBuffer(object):
             return
         if torch.is_tensor(src) and src.is_cuda and src.data_ptr() == dst.data_ptr() and src.numel() == dst.numel():
             return
-        dst.copy_(_dev(src, self.device).reshape(dst.shape))
+        d = _dev(src, self.device)
+        pend = getattr(self, "_pending", None)
+        if pend is not None and d.dtype == dst.dtype == torch.float32 and d.is_contiguous() and dst.is_contiguous() \
+                and d.numel() == dst.numel():
+            pend.append((dst, d))               # inside insert(): batched into one launch (mappo_copy_segments)
+        else:
+            dst.copy_(d.reshape(dst.shape))
 
     def _materialise_avail(self):
         if self._avail_all_ones:
@@ -187,6 +193,7 @@ class SharedReplayBuffer(object):
     def insert(self, share_obs, obs, rnn_states_actor, rnn_states_critic, actions, action_log_probs,
                value_preds, rewards, masks, bad_masks=None, active_masks=None, available_actions=None):
         s = self.step
+        self._pending = []                      # (dst, src) device copies of this insert: ONE launch at the end
         self._put(self.obs[s + 1], obs)
         if not self._share_is_view:
             self._put(self.share_obs[s + 1], share_obs)
@@ -205,6 +212,9 @@ class SharedReplayBuffer(object):
         if available_actions is not None:
             self._materialise_avail()
             self._put(self.available_actions[s + 1], available_actions)
+        pending, self._pending = self._pending, None
+        if pending:
+            _gather.copy_segments(pending)
         self.step = (self.step + 1) % self.episode_length
 
     def after_update(self):

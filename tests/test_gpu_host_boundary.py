@@ -99,3 +99,30 @@ def test_env_step_accepts_every_one_hot_dtype_and_ids():
         outs.append(env.step(arg)[0].copy())
     for o in outs[1:]:
         np.testing.assert_array_equal(o, outs[0])
+
+
+def test_copy_segments_and_batched_insert_equal_plain_copies():
+    """mappo_copy_segments: up to 8 device copies per launch (SharedReplayBuffer.insert batches its stores through it);
+    aligned (16-byte pieces) and 4-byte-aligned segments, more than 8 pairs, odd sizes."""
+    from mappo_b200 import gather
+    g = torch.Generator(device="cuda").manual_seed(3)
+    sizes = [1, 3, 4, 5, 1023, 4096, 65536 * 54 + 3, 7, 128, 129, 1000001]
+    base = [torch.randn(n + 1, device="cuda", generator=g) for n in sizes]
+    srcs = [b[1:] if i % 2 else b[:-1] for i, b in enumerate(base)]                 # every other one 4 bytes off a 16-byte boundary
+    dsts = [torch.full((n + 2,), -7.0, device="cuda") for n in sizes]
+    gather.copy_segments([(d[1:-1] if i % 3 == 0 else d[:n], s) for i, (d, s, n) in enumerate(zip(dsts, srcs, sizes))])
+    for i, (d, s, n) in enumerate(zip(dsts, srcs, sizes)):
+        got = d[1:-1] if i % 3 == 0 else d[:n]
+        assert torch.equal(got, s), (i, n)
+        assert (d[-1] == -7.0) and (i % 3 != 0 or d[0] == -7.0), "wrote outside segment %d" % i
+
+
+def test_host_onehot_from_float_ids_equals_the_int64_form():
+    from mappo_b200 import host_mirror
+    rng = np.random.default_rng(0)
+    for heads in ([5], [3, 5], [5, 10]):
+        ids = np.stack([rng.integers(0, h, size=(64, 3)) for h in heads], axis=-1)
+        a = host_mirror.onehot(ids.astype(np.int64), heads, tag="oh_i").copy()
+        b = host_mirror.onehot(ids.astype(np.float32), heads, tag="oh_f").copy()
+        want = np.concatenate([np.eye(h, dtype=np.uint8)[ids[..., k]] for k, h in enumerate(heads)], axis=-1)
+        assert a.dtype == b.dtype == np.uint8 and (a == want).all() and (b == want).all()
