@@ -128,3 +128,49 @@ def test_wide_first_layer_across_widths(S, group, rows_c, packed):
     ws = tr._update(obs, share, group, acts, old_logp, adv, vp, ret, active, None, B, packed=pk)
     np.testing.assert_allclose(tr._info[4].item(), vl, rtol=1e-4, atol=1e-6)
     _check(pol.critic, ws["grad"][pol.actor.flat.numel():], gc, "wide critic S=%d group=%d rows=%d" % (S, group, rows_c))
+
+
+@pytest.mark.parametrize("D,S,L,Nc,heads,relu,rN", [
+    (7, 14, 1, 77, [5], False, 1),              # one-step chunks, a ragged half tile of chunks
+    (21, 42, 10, 129, [5, 10], True, 1),        # C4's networks, one chunk over a tile
+    (21, 42, 25, 64, [5, 10], False, 2),        # two stacked GRU layers, whole-episode chunks
+    (40, 54, 5, 1000, [3], False, 1),           # 64-wide input tiles on both base kernels
+    (66, 132, 10, 200, [5], True, 1),           # wide first layer in front of the GRU
+])
+def test_recurrent_update_across_shapes(D, S, L, Nc, heads, relu, rN):
+    """The recurrent chain (base forward, GRU sweeps, head, ONE dual weight-gradient pass per layer, base backward) at chunk
+    counts / lengths / widths off the benchmark's: losses and PRE-clip gradients vs float64 autograd through the oracle."""
+    from test_gpu_large_batch import _policy, _mask_kinks, _actor_oracle64, _critic_oracle64, _check, _threads
+    from mappo_b200.envs.spaces import Discrete, MultiDiscrete
+    B = L * Nc
+    space = Discrete(heads[0]) if len(heads) == 1 else MultiDiscrete([[0, h - 1] for h in heads])
+    a, pol, tr, g = _policy("--algorithm_name rmappo --data_chunk_length %d --recurrent_N %d%s" % (L, rN, "" if relu else " --use_ReLU"),
+                            D, S, space, seed=D + L)
+    assert bool(a.use_ReLU) == relu
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    obs = r(B, D) * (0.4 + r(1, D).abs())
+    share = r(B, S) * (0.4 + r(1, S).abs())
+    rnn_a, rnn_c = 0.5 * r(Nc, rN, 64), 0.5 * r(Nc, rN, 64)
+    masks = (torch.rand(B, 1, device="cuda", generator=g) > 0.08).float()
+    acts = torch.stack([torch.randint(0, h, (B,), device="cuda", generator=g) for h in heads], -1).float()
+    old_logp = torch.stack([-np.log(h) + 0.1 * r(B) for h in heads], -1)
+    adv, vp, ret = r(B, 1), 0.5 * r(B, 1), -5.0 + 3.0 * r(B, 1)
+    active = (torch.rand(B, 1, device="cuda", generator=g) > 0.1).float()
+    if D < 64:
+        active = _mask_kinks(a, pol, obs, share, 1, active)
+    tr.value_normalizer.update(-4.0 + 2.0 * torch.randn(300, 1, device="cuda", generator=g))
+    vn_before = tr.value_normalizer.stats.cpu().numpy().copy()
+    torch.set_num_threads(_threads())
+    try:
+        pl, ent, ratio, ga = _actor_oracle64(a, pol, obs, acts, old_logp, adv, active, rnn=rnn_a, masks=masks)
+        vl, gc = _critic_oracle64(a, pol, tr, share, 1, vp, ret, active, vn_before, rnn=rnn_c, masks=masks)
+    finally:
+        torch.set_num_threads(1)
+    got = tr.ppo_update((share, obs, rnn_a, rnn_c, acts, vp, ret, masks, active, old_logp, adv, None))
+    np.testing.assert_allclose(got[2].item(), pl, rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(got[3].item(), ent, rtol=1e-5)
+    np.testing.assert_allclose(got[0].item(), vl, rtol=1e-4, atol=1e-6)
+    ws = next(iter(tr._ws.values()))
+    Pa = pol.actor.flat.numel()
+    _check(pol.actor, ws["grad"][:Pa], ga, "recurrent actor D=%d L=%d Nc=%d rN=%d" % (D, L, Nc, rN))
+    _check(pol.critic, ws["grad"][Pa:], gc, "recurrent critic S=%d L=%d Nc=%d rN=%d" % (S, L, Nc, rN))
