@@ -88,3 +88,51 @@ def test_critic_update_bulk_copies_equal_plain_loads(group):
     if group == 1:
         idx = torch.arange(rows_c, device="cuda", dtype=torch.int64)
         _same(bulk, _critic(pol, tr, share, vp, ret, active, 1, index=idx), "identity index")
+
+
+def test_update_kernels_are_bit_reproducible_run_to_run():
+    """Every buffer of a tile is reused by the next one under mbarrier / bulk-copy ordering (next tile's rows, its loss
+    scalars, the operand tiles the background weight-gradient MMAs still read): an ordering hole shows up as run-to-run
+    differences.  Six runs of both update kernels at ~17 tiles per CTA, and of the recurrent chain, must agree bit for bit."""
+    B = 148 * 17 * 128 + 55
+    a, pol, tr, (obs, share, acts, old_logp, adv, active, vp, ret) = _setup(3, B - B % 3)
+    Bc = (B - B % 3) // 3
+    first_a = first_c = None
+    for _ in range(6):
+        ga = _actor(pol, tr, obs, acts, old_logp, adv, active)
+        gc = _critic(pol, tr, share, vp, ret, active, 3)
+        if first_a is None:
+            first_a, first_c = ga, gc
+        else:
+            _same(first_a, ga, "actor update, repeated run")
+            _same(first_c, gc, "critic update (%d rows x group 3), repeated run" % Bc)
+
+
+def test_recurrent_update_is_bit_reproducible_run_to_run():
+    from test_gpu_large_batch import _policy
+    from mappo_b200.envs.spaces import MultiDiscrete
+    D, S, L, Nc = 21, 42, 10, 148 * 128 * 3 + 17
+    Bn = L * Nc
+    a, pol, tr, g = _policy("--algorithm_name rmappo --data_chunk_length 10 --use_ReLU", D, S, MultiDiscrete([[0, 4], [0, 9]]))
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    obs, share = r(Bn, D), r(Bn, S)
+    rnn_a, rnn_c = 0.5 * r(Nc, 1, 64), 0.5 * r(Nc, 1, 64)
+    masks = (torch.rand(Bn, 1, device="cuda", generator=g) > 0.08).float()
+    acts = torch.stack([torch.randint(0, 5, (Bn,), device="cuda", generator=g),
+                        torch.randint(0, 10, (Bn,), device="cuda", generator=g)], -1).float()
+    old_logp = torch.stack([-1.6 + 0.1 * r(Bn), -2.3 + 0.1 * r(Bn)], -1)
+    adv, vp, ret = r(Bn, 1), 0.5 * r(Bn, 1), -5.0 + 3.0 * r(Bn, 1)
+    active = (torch.rand(Bn, 1, device="cuda", generator=g) > 0.1).float()
+    sample = (share, obs, rnn_a, rnn_c, acts, vp, ret, masks, active, old_logp, adv, None)
+    flat0 = (pol.actor.flat.clone(), pol.critic.flat.clone())
+    vn0 = tr.value_normalizer.stats.clone()
+    first = None
+    for _ in range(4):
+        pol.actor.flat.copy_(flat0[0]); pol.critic.flat.copy_(flat0[1]); tr.value_normalizer.stats.copy_(vn0)
+        tr.ppo_update(sample, update_actor=False)
+        ws = next(iter(tr._ws.values()))
+        grad = ws["grad"].clone()
+        if first is None:
+            first = grad
+        else:
+            assert torch.equal(first, grad), "recurrent update differs run to run by %.3e" % (first - grad).abs().max().item()
