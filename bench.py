@@ -243,8 +243,11 @@ def host_boundary_iteration(runner, envs, hb):
         values, actions, logp = out["values"], out["actions"], out["logp"]
         d2h += values.nbytes + actions.nbytes + logp.nbytes
         actions_env = host_mirror.onehot(actions, [N_ACT])               # mpe_runner.py:110-121 (np.eye(n)[actions]), uint8
+        if host_mirror.lookup(actions_env) is not None:                  # built next to the ids on the device: came OUT as bytes
+            d2h += actions_env.nbytes
+        else:                                                            # built on the host: goes IN with envs.step
+            h2d += actions_env.nbytes
         obs, rewards, dones, infos = envs.step(actions_env)              # host in, host out
-        h2d += actions_env.nbytes
         d2h += obs.nbytes + rewards.nbytes + dones.nbytes + N * M * 4    # + the individual rewards behind `infos`
         masks = hb["masks"].numpy()
         masks[..., 0] = ~dones                                           # mpe_runner.py:128-131 (masks[dones] = 0)

@@ -91,3 +91,15 @@ def copy_segments(pairs):
         for k, (dst, src) in enumerate(chunk):
             cl.src[k], cl.dst[k], cl.bytes[k] = src.data_ptr(), dst.data_ptr(), dst.numel() * dst.element_size()
         check(fn(C.byref(cl), stream_ptr()), "copy_segments")
+
+
+_lib._EXTRA_SIGS["mappo_ids_to_onehot_u8"] = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
+
+
+def ids_to_onehot(ids, head_dims, out):
+    """ids: CUDA float32 [rows, >= heads] (contiguous); out: CUDA uint8 [rows, sum(head_dims)]."""
+    assert ids.is_cuda and ids.dtype == torch.float32 and ids.is_contiguous() and out.dtype == torch.uint8 and out.is_contiguous()
+    hd = (C.c_int * len(head_dims))(*[int(d) for d in head_dims])
+    check(_lib.lib().mappo_ids_to_onehot_u8(ptr(ids), ids.shape[0], int(ids.shape[-1]), len(head_dims), hd, ptr(out),
+                                            stream_ptr()), "ids_to_onehot_u8")
+    return out

@@ -19,6 +19,7 @@ import torch
 ENABLED = os.environ.get("MAPPO_HOST_PASSTHROUGH", "1") != "0"
 _TWINS = {}          # data pointer -> (nbytes, device tensor)
 _PINNED = {}         # (tag, shape, dtype) -> pinned host tensor
+_DEVICE_SCRATCH = {}  # (tag, shape) -> device uint8 tensor (one-hot built on the device)
 
 
 def _key(arr):
@@ -99,12 +100,29 @@ def onehot(actions, head_dims, tag="onehot"):
     (one C pass, mappo_host_onehot_u8).  `MPEVecEnv.step` takes it as is (1 byte per logit over PCIe)."""
     import ctypes as C
     from . import _lib
+    heads = len(head_dims)
+    twin = lookup(actions)
+    if twin is not None and twin.dtype in (torch.float32, torch.int64, torch.int32) and twin.shape[-1] == heads:
+        # the ids are a host copy this library made of a device tensor: build the one-hot next to them (one small
+        # kernel), bring it out as bytes, and remember the device copy -- `MPEVecEnv.step` then needs no upload at all
+        from . import gather
+        shape = tuple(twin.shape[:-1]) + (int(sum(head_dims)),)
+        dev = _DEVICE_SCRATCH.get((tag, shape))
+        if dev is None:
+            dev = _DEVICE_SCRATCH[(tag, shape)] = torch.empty(shape, dtype=torch.uint8, device=twin.device)
+        ids = twin.to(torch.float32).contiguous()        # (the policy returns int64 ids, as torch's Categorical does)
+        gather.ids_to_onehot(ids.view(-1, heads), head_dims, dev.view(-1, shape[-1]))
+        out = pinned(tag, shape, torch.uint8)
+        out.copy_(dev, non_blocking=True)
+        torch.cuda.current_stream(twin.device).synchronize()
+        register(out, dev)
+        return out.numpy()
     a = np.asarray(actions)
     f32 = a.dtype == np.float32                  # what the policy returns (act.py stores ids as floats): no int64 pass
     a = np.ascontiguousarray(a, dtype=np.float32 if f32 else np.int64)
-    heads = len(head_dims)
     rows = a.size // heads
     out = pinned(tag, tuple(a.shape[:-1]) + (int(sum(head_dims)),), torch.uint8)
+    forget(out)                                  # (a device one-hot registered for this buffer earlier is stale now)
     L = _lib.lib()
     fn = L.mappo_host_onehot_u8_f32 if f32 else L.mappo_host_onehot_u8
     fn.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_int), C.c_void_p]

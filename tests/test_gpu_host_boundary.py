@@ -126,3 +126,24 @@ def test_host_onehot_from_float_ids_equals_the_int64_form():
         b = host_mirror.onehot(ids.astype(np.float32), heads, tag="oh_f").copy()
         want = np.concatenate([np.eye(h, dtype=np.uint8)[ids[..., k]] for k, h in enumerate(heads)], axis=-1)
         assert a.dtype == b.dtype == np.uint8 and (a == want).all() and (b == want).all()
+
+
+def test_onehot_of_pass_through_ids_is_built_on_the_device_and_feeds_the_env():
+    """ids that are a host copy the library made (t2n) -> host_mirror.onehot builds the one-hot on the device, returns the
+    same bytes as the host loop, and registers the device copy so that MPEVecEnv.step uploads nothing."""
+    from mappo_b200 import host_mirror
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for heads in ([5], [3, 5]):
+        ids_dev = torch.stack([torch.randint(0, h, (96, 3), device="cuda", generator=g) for h in heads], -1)
+        if len(heads) == 2:
+            ids_dev = ids_dev.float()                        # int64 (what the policy returns) and float32 ids
+        ids_host = host_mirror.t2n(ids_dev, tag="ids%d" % len(heads))
+        assert host_mirror.lookup(ids_host) is not None
+        oh = host_mirror.onehot(ids_host, heads, tag="ohd%d" % len(heads))
+        want = np.concatenate([np.eye(h, dtype=np.uint8)[ids_host[..., k].astype(int)] for k, h in enumerate(heads)], -1)
+        assert oh.dtype == np.uint8 and oh.shape == want.shape and (oh == want).all()
+        twin = host_mirror.lookup(oh)
+        assert twin is not None and twin.is_cuda and (twin.cpu().numpy() == want).all()
+        # an ordinary array of the same values takes the host loop and is NOT registered
+        oh2 = host_mirror.onehot(ids_host.copy(), heads, tag="ohh%d" % len(heads))
+        assert (oh2 == want).all() and host_mirror.lookup(oh2) is None
