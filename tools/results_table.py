@@ -26,7 +26,7 @@ def head(b, r, n2, n8, r8, c):
          "round-1 verdict saw plus this round's parity / boundary work; round 1 itself: `profiles/r01_results.md`).\n",
          "| configuration | agent-steps/s | ms per iteration | notes |\n|---|---|---|---|"]
     o.append("| C2: simple_spread, 3 agents, 65,536 envs, shared MLP, 1 GPU (`python bench.py --steps 20 --warmup 5`) | %s (138.5 M) "
-             "| %.2f (35.50) | e2e through host arrays %s (82.2 M; round 1: 66 – 69 M): H2D 44 MB + D2H 477 MB per iteration |"
+             "| %.2f (35.50) | e2e through host arrays %s (82.2 M; round 1: 66 – 69 M): H2D 20 MB + D2H 501 MB per iteration |"
              % (M(b["value"]), b["ms_per_step"], M(b["e2e"]["value"])))
     o.append("| the UNMODIFIED reference on the same box (`--impl reference`: SubprocVecEnv x 128 + MPERunner + R_MAPPO, torch CPU, "
              "%d cores) | %.1f k | %.0f | `cpu_baseline.kind = \"reference\"` (%.1f k inside the C2 line); the CPU port "
@@ -86,7 +86,7 @@ def tables(b, n2, n8):
         o.append("| %d | %s | %.1e | %.1e | %.1e | %s |"
                  % (q["ranks"], q["replicas_identical"], q["grad_vs_single_gpu_max_rel"], q["info_vs_single_gpu_max_rel"],
                     q["params_vs_single_gpu_max_abs"], q["replicas_identical_after_timed_region"]))
-    o.append("\n## Tests on the B200\n\n`python -m pytest tests -q -m gpu`: 183 passed, 1 skipped on one GPU (the 2-rank test needs "
+    o.append("\n## Tests on the B200\n\n`python -m pytest tests -q -m gpu`: 184 passed, 1 skipped on one GPU (the 2-rank test needs "
              "2 GPUs and passes under `gpurun --gpus 2`); `tests/test_zz_no_alloc.py` passes alone and last.  Large-batch gradient "
              "distances with the end-of-round kernels (`tests/test_gpu_large_batch.py`, worst |dg| / max|g| per case): actor "
              "8.3e-6, critic (group 3) 1.1e-6, ReLU group 1 5.5e-6 / 2.5e-6, wide critic packed 1.3e-5, unpacked 3.4e-6, packed "
