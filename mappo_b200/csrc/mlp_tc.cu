@@ -26,8 +26,8 @@ constexpr int kTmemCols = 512;
 constexpr int kRowpGroup = 4;                       // largest critic `group` whose loss inputs arrive by bulk copy
 constexpr float kRawMax = 4094.0f;                  // 65504 / kSX, rounded down to an fp16-exact value after scaling
 // TMEM column map.  The BIAS gradients sum_rows dz come off the tensor cores too: the n1 operand tile ends in a constant
-// chunk whose first column is 1 (column 128 of G2), and the input tile carries a 1 in its first padding column
-// (column in_dim of G1; W1' is zero there, so the forward pass does not see it).
+// chunk whose first column is 1 (times the tile's scale; column 128 of G2), and the input tile carries a (scaled) 1 in its
+// first padding column (column in_dim of G1; W1' is zero there, so the forward pass does not see it).
 constexpr uint32_t kColAcc = 0, kColF = 64, kColG2 = 128, kColG1 = 272, kColGh = 400;   // 64 | 64 | 144 | <= 128 | 32
 
 // shared-memory map (byte offsets); Kp = in_dim rounded up to 32 or 64, AS = odd stride of the partial-logit rows
