@@ -465,7 +465,8 @@ int mappo_gather_rows(const float* src, long long row_stride, int row_div, int w
  * [rows][sum(head_dim)].  Used when the ids handed to the runner's one-hot helper are a host copy the library made of a
  * device tensor (host_mirror pass-through): the one-hot is built next to the ids and crosses PCIe once, as bytes. */
 int mappo_ids_to_onehot_u8(const float* ids, long long rows, int ids_ld, int n_heads, const int* head_dim_host,
-                           uint8_t* onehot, void* stream);
+                           uint8_t* onehot, int32_t* bad_flag /* device, set to 1 by an id outside its head, or NULL */,
+                           void* stream);
 /* HOST helper (no device work): the runner's one-hot `actions_env = np.eye(n)[actions]`
  * (onpolicy/runner/shared/mpe_runner.py:110-121) as uint8 [rows][sum(head_dim)] from int64 ids [rows][n_heads], both on
  * the host; one pass in C instead of a NumPy fancy-index scatter.  (ABI v6.) */

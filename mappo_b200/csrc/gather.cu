@@ -48,14 +48,17 @@ onehot_to_ids_kernel(const T* __restrict__ onehot, long long rows, OneHotArgs a,
 
 // the forward direction on the device: float ids [rows][ids_ld] -> uint8 one-hot [rows][width], one thread per output byte
 __global__ void __launch_bounds__(256)
-ids_to_onehot_kernel(const float* __restrict__ ids, long long rows, int ids_ld, OneHotArgs a, uint8_t* __restrict__ out) {
+ids_to_onehot_kernel(const float* __restrict__ ids, long long rows, int ids_ld, OneHotArgs a, uint8_t* __restrict__ out,
+                     int32_t* __restrict__ bad) {
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (i >= rows * a.width) return;
   const long long r = i / a.width;
   const int c = (int)(i - r * a.width);
   int h = 0;
   while (h + 1 < a.n_heads && c >= a.off[h + 1]) ++h;
-  out[i] = ((int)ids[r * ids_ld + h] == c - a.off[h]) ? 1 : 0;
+  const int id = (int)ids[r * ids_ld + h];
+  out[i] = (id == c - a.off[h]) ? 1 : 0;
+  if (bad && c == a.off[h] && (id < 0 || id >= a.dim[h])) atomicExch(bad, 1);     // np.eye(n)[id] would raise IndexError
 }
 
 }  // namespace mappo
@@ -63,7 +66,7 @@ ids_to_onehot_kernel(const float* __restrict__ ids, long long rows, int ids_ld, 
 using namespace mappo;
 
 extern "C" int mappo_ids_to_onehot_u8(const float* ids, long long rows, int ids_ld, int n_heads, const int* head_dim_host,
-                                      uint8_t* onehot, void* stream) {
+                                      uint8_t* onehot, int32_t* bad_flag, void* stream) {
   MAPPO_REQUIRE(ids && onehot && head_dim_host && rows > 0 && n_heads >= 1 && n_heads <= MAPPO_MAX_HEADS && ids_ld >= n_heads,
                 "ids_to_onehot_u8: bad arguments");
   OneHotArgs a{};
@@ -74,7 +77,7 @@ extern "C" int mappo_ids_to_onehot_u8(const float* ids, long long rows, int ids_
     a.dim[h] = head_dim_host[h]; a.off[h] = w; w += head_dim_host[h];
   }
   a.width = w;
-  ids_to_onehot_kernel<<<ceil_div(rows * w, 256), 256, 0, (cudaStream_t)stream>>>(ids, rows, ids_ld, a, onehot);
+  ids_to_onehot_kernel<<<ceil_div(rows * w, 256), 256, 0, (cudaStream_t)stream>>>(ids, rows, ids_ld, a, onehot, bad_flag);
   MAPPO_CHECK_LAUNCH("ids_to_onehot_kernel");
   return 0;
 }

@@ -93,13 +93,15 @@ def copy_segments(pairs):
         check(fn(C.byref(cl), stream_ptr()), "copy_segments")
 
 
-_lib._EXTRA_SIGS["mappo_ids_to_onehot_u8"] = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
+_lib._EXTRA_SIGS["mappo_ids_to_onehot_u8"] = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p,
+                                              C.c_void_p]
 
 
-def ids_to_onehot(ids, head_dims, out):
-    """ids: CUDA float32 [rows, >= heads] (contiguous); out: CUDA uint8 [rows, sum(head_dims)]."""
+def ids_to_onehot(ids, head_dims, out, bad=None):
+    """ids: CUDA float32 [rows, >= heads] (contiguous); out: CUDA uint8 [rows, sum(head_dims)]; bad: CUDA int32 [1]
+    the kernel sets to 1 if an id lies outside its head (np.eye(n)[id] raises there), or None."""
     assert ids.is_cuda and ids.dtype == torch.float32 and ids.is_contiguous() and out.dtype == torch.uint8 and out.is_contiguous()
     hd = (C.c_int * len(head_dims))(*[int(d) for d in head_dims])
     check(_lib.lib().mappo_ids_to_onehot_u8(ptr(ids), ids.shape[0], int(ids.shape[-1]), len(head_dims), hd, ptr(out),
-                                            stream_ptr()), "ids_to_onehot_u8")
+                                            ptr(bad), stream_ptr()), "ids_to_onehot_u8")
     return out

@@ -111,10 +111,18 @@ def onehot(actions, head_dims, tag="onehot"):
         if dev is None:
             dev = _DEVICE_SCRATCH[(tag, shape)] = torch.empty(shape, dtype=torch.uint8, device=twin.device)
         ids = twin.to(torch.float32).contiguous()        # (the policy returns int64 ids, as torch's Categorical does)
-        gather.ids_to_onehot(ids.view(-1, heads), head_dims, dev.view(-1, shape[-1]))
-        out = pinned(tag, shape, torch.uint8)
+        bad = _DEVICE_SCRATCH.get((tag, "bad"))
+        if bad is None:
+            bad = _DEVICE_SCRATCH[(tag, "bad")] = torch.zeros(1, dtype=torch.int32, device=twin.device)
+        gather.ids_to_onehot(ids.view(-1, heads), head_dims, dev.view(-1, shape[-1]), bad)
+        out, flag = pinned(tag, shape, torch.uint8), pinned(tag + ".bad", (1,), torch.int32)
         out.copy_(dev, non_blocking=True)
+        flag.copy_(bad, non_blocking=True)
         torch.cuda.current_stream(twin.device).synchronize()
+        if int(flag[0]) != 0:                        # the reference's np.eye(n)[actions] raises IndexError here
+            bad.zero_()
+            forget(out)
+            raise IndexError("host_mirror.onehot: an action id lies outside its head %r" % (list(head_dims),))
         register(out, dev)
         return out.numpy()
     a = np.asarray(actions)

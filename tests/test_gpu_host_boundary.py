@@ -147,3 +147,17 @@ def test_onehot_of_pass_through_ids_is_built_on_the_device_and_feeds_the_env():
         # an ordinary array of the same values takes the host loop and is NOT registered
         oh2 = host_mirror.onehot(ids_host.copy(), heads, tag="ohh%d" % len(heads))
         assert (oh2 == want).all() and host_mirror.lookup(oh2) is None
+
+
+def test_onehot_of_pass_through_ids_refuses_an_id_outside_its_head():
+    """np.eye(5)[7] raises IndexError in the reference's runner: so do both forms of the drop-in."""
+    import pytest as _pt
+    from mappo_b200 import host_mirror
+    ids_dev = torch.tensor([[0.0], [4.0], [7.0]], device="cuda")
+    ids_host = host_mirror.t2n(ids_dev, tag="ids_bad")
+    with _pt.raises(IndexError):
+        host_mirror.onehot(ids_host, [5], tag="oh_bad")
+    ok = host_mirror.onehot(host_mirror.t2n(torch.tensor([[0.0], [4.0]], device="cuda"), tag="ids_ok"), [5], tag="oh_bad2")
+    assert (ok == np.eye(5, dtype=np.uint8)[[0, 4]]).all()
+    with _pt.raises(Exception):
+        host_mirror.onehot(np.array([[0], [7]], dtype=np.int64), [5], tag="oh_bad3")

@@ -86,7 +86,7 @@ def tables(b, n2, n8):
         o.append("| %d | %s | %.1e | %.1e | %.1e | %s |"
                  % (q["ranks"], q["replicas_identical"], q["grad_vs_single_gpu_max_rel"], q["info_vs_single_gpu_max_rel"],
                     q["params_vs_single_gpu_max_abs"], q["replicas_identical_after_timed_region"]))
-    o.append("\n## Tests on the B200\n\n`python -m pytest tests -q -m gpu`: 184 passed, 1 skipped on one GPU (the 2-rank test needs "
+    o.append("\n## Tests on the B200\n\n`python -m pytest tests -q -m gpu`: 185 passed, 1 skipped on one GPU (the 2-rank test needs "
              "2 GPUs and passes under `gpurun --gpus 2`); `tests/test_zz_no_alloc.py` passes alone and last.  Large-batch gradient "
              "distances with the end-of-round kernels (`tests/test_gpu_large_batch.py`, worst |dg| / max|g| per case): actor "
              "8.3e-6, critic (group 3) 1.1e-6, ReLU group 1 5.5e-6 / 2.5e-6, wide critic packed 1.3e-5, unpacked 3.4e-6, packed "
